@@ -1,0 +1,86 @@
+"""Deterministic synthetic workloads.
+
+Library-independent generators so every arm (CUDA path, CPU oracle, cv2 cross-checks) sees identical bytes.
+RNG = counter-based splitmix64: output i (0-based) of stream `seed` is mix(seed + (i+1)*GAMMA).
+"""
+from __future__ import annotations
+
+import numpy as np
+
+_GAMMA = np.uint64(0x9E3779B97F4A7C15)
+_M1 = np.uint64(0xBF58476D1CE4E5B9)
+_M2 = np.uint64(0x94D049BB133111EB)
+
+
+def splitmix64(seed: int, n: int, offset: int = 0) -> np.ndarray:
+    """n outputs of the splitmix64 stream `seed`, starting at output index `offset`."""
+    with np.errstate(over="ignore"):
+        i = np.arange(offset + 1, offset + n + 1, dtype=np.uint64)
+        z = np.uint64(seed & 0xFFFFFFFFFFFFFFFF) + i * _GAMMA
+        z = (z ^ (z >> np.uint64(30))) * _M1
+        z = (z ^ (z >> np.uint64(27))) * _M2
+        return z ^ (z >> np.uint64(31))
+
+
+def _binomial_axis(a: np.ndarray, axis: int) -> np.ndarray:
+    """[1,4,6,4,1] pass along `axis`, reflect-101 border, (sum + 8) >> 4."""
+    a = a.astype(np.int32)
+    pad = [(0, 0), (0, 0)]
+    pad[axis] = (2, 2)
+    p = np.pad(a, pad, mode="reflect")
+    n = a.shape[axis]
+    sl = lambda k: tuple(slice(k, k + n) if ax == axis else slice(None) for ax in range(2))
+    s = p[sl(0)] + 4 * p[sl(1)] + 6 * p[sl(2)] + 4 * p[sl(3)] + p[sl(4)]
+    return (s + 8) >> 4
+
+
+def textured_frame(w: int, h: int, seed: int, band: bool = True) -> np.ndarray:
+    """8-bit textured frame: 4x nearest-upsampled random blocks, binomial smoothing, +-6 integer noise, plus a
+    low-contrast band (middle third of the rows: weak checkerboard on the left half -> FAST-7 fallback cells, flat
+    on the right half -> empty cells)."""
+    bw, bh = -(-w // 4), -(-h // 4)
+    base = (splitmix64(seed, bw * bh) >> np.uint64(56)).astype(np.uint8).reshape(bh, bw)
+    img = np.repeat(np.repeat(base, 4, axis=0), 4, axis=1)[:h, :w]
+    img = _binomial_axis(_binomial_axis(img, 1), 0)
+    noise = ((splitmix64(seed, w * h, offset=bw * bh) >> np.uint64(56)).astype(np.int32) % 13 - 6).reshape(h, w)
+    img = np.clip(img + noise, 0, 255).astype(np.uint8)
+    if band:
+        y0, y1 = h // 2 - h // 6, h // 2 + h // 6
+        yy, xx = np.mgrid[y0:y1, 0:w]
+        weak = (96 + 12 * (((xx >> 4) + (yy >> 4)) & 1)).astype(np.uint8)
+        img[y0:y1, :] = np.where(xx < w // 2, weak, np.uint8(128))
+    return np.ascontiguousarray(img)
+
+
+class Sequence:
+    """EuRoC-shaped sequence (config C2): integer-shifted crops of one master texture plus fresh +-3 noise."""
+
+    def __init__(self, w: int = 752, h: int = 480, master_seed: int = 0):
+        self.w, self.h = w, h
+        self.mw, self.mh = w + 528, h + 288      # 1280 x 768 for 752 x 480
+        self.master = textured_frame(self.mw, self.mh, master_seed)
+
+    def offset(self, t: int) -> tuple[int, int]:
+        return t % 512, (t // 4) % 256
+
+    def frame(self, t: int) -> np.ndarray:
+        x0, y0 = self.offset(t)
+        crop = self.master[y0:y0 + self.h, x0:x0 + self.w].astype(np.int32)
+        noise = ((splitmix64(1000 + t, self.w * self.h) >> np.uint64(56)).astype(np.int32) % 7 - 3)
+        return np.clip(crop + noise.reshape(self.h, self.w), 0, 255).astype(np.uint8)
+
+    def frames(self, t0: int, n: int) -> np.ndarray:
+        return np.stack([self.frame(t) for t in range(t0, t0 + n)])
+
+
+def landmark_cloud(n: int, seed: int, xv: np.ndarray | None = None):
+    """tools/simu_greedy.cc:30-145 recipe with splitmix64 instead of the unseeded rand(): landmarks x,y in [-4,4],
+    z in [0,8]; octave = round(7 U); match score = round(100 U).  Returns (world[n,3] f32, octave[n] i32,
+    score[n] i32, U[n,2] noise in [-1,1))."""
+    u = (splitmix64(seed, 7 * n) >> np.uint64(11)).astype(np.float64) / float(1 << 53)
+    u = u.reshape(n, 7)
+    world = np.stack([u[:, 0] * 8 - 4, u[:, 1] * 8 - 4, u[:, 2] * 8], axis=1).astype(np.float32)
+    octave = np.round(u[:, 3] * 7).astype(np.int32)
+    score = np.round(u[:, 4] * 100).astype(np.int32)
+    pix_noise = (u[:, 5:7] * 2 - 1).astype(np.float32)
+    return world, octave, score, pix_noise

@@ -1,0 +1,315 @@
+"""TEST INFRASTRUCTURE ONLY: ctypes access to the CPU oracle (oracle/liboracle.so).
+
+Importable only from tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs.
+The product package (gf_orb_slam_b200) never imports this module.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"),
+                     ("octave", "<i4"), ("class_id", "<i4")])
+
+
+def build(force: bool = False) -> str:
+    so = os.path.join(_HERE, "liboracle.so")
+    srcs = [os.path.join(_HERE, f) for f in os.listdir(_HERE) if f.endswith((".cpp", ".hpp"))]
+    if force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
+        subprocess.check_call(["make", "-C", _HERE, "-B", "liboracle.so"], stdout=subprocess.DEVNULL)
+    return so
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        _LIB = C.CDLL(build())
+        L = _LIB
+        L.orc_obs_create_f.restype = C.c_void_p
+        L.orc_obs_create_fufv.restype = C.c_void_p
+        L.orc_extractor_create.restype = C.c_void_p
+        L.orc_frame_create.restype = C.c_void_p
+        L.orc_logdet.restype = C.c_double
+    return _LIB
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+# ---------------------------------------------------------------- primitives
+def resize(src: np.ndarray, dw: int, dh: int) -> np.ndarray:
+    src = np.ascontiguousarray(src, np.uint8)
+    dst = np.empty((dh, dw), np.uint8)
+    lib().orc_resize(_p(src), src.shape[1], src.shape[0], src.shape[1], _p(dst), dw, dh, dw)
+    return dst
+
+
+def border101(src: np.ndarray, b: int) -> np.ndarray:
+    src = np.ascontiguousarray(src, np.uint8)
+    h, w = src.shape
+    dst = np.empty((h + 2 * b, w + 2 * b), np.uint8)
+    lib().orc_border101(_p(src), w, h, w, _p(dst), w + 2 * b, b)
+    return dst
+
+
+def blur(src: np.ndarray, variant: int = 0) -> np.ndarray:
+    src = np.ascontiguousarray(src, np.uint8)
+    h, w = src.shape
+    dst = np.empty_like(src)
+    lib().orc_blur(_p(src), w, h, w, _p(dst), w, variant)
+    return dst
+
+
+def fast(img: np.ndarray, th: int, nonmax: bool = True) -> np.ndarray:
+    img = np.ascontiguousarray(img, np.uint8)
+    h, w = img.shape
+    cap = max(16, w * h // 4)
+    out = np.zeros(cap, KP_DTYPE)
+    n = lib().orc_fast(_p(img), w, h, w, th, int(nonmax), _p(out), cap)
+    return out[:n]
+
+
+def fast_atan2(y: np.ndarray, x: np.ndarray) -> np.ndarray:
+    y = np.ascontiguousarray(y, np.float32); x = np.ascontiguousarray(x, np.float32)
+    out = np.empty_like(y)
+    lib().orc_fastatan2(_p(y), _p(x), _p(out), y.size)
+    return out
+
+
+def retain_best(resp: np.ndarray, n_keep: int, variant: int = 0) -> np.ndarray:
+    resp = np.ascontiguousarray(resp, np.float32)
+    out = np.empty(resp.size, np.int32)
+    n = lib().orc_retain_best(_p(resp), resp.size, n_keep, variant, _p(out))
+    return out[:n]
+
+
+def sincosf(x: np.ndarray):
+    x = np.ascontiguousarray(x, np.float32)
+    s = np.empty_like(x); c = np.empty_like(x)
+    lib().orc_sincosf(_p(x), _p(s), _p(c), x.size)
+    return s, c
+
+
+def rand_stream(seed: int, n: int) -> np.ndarray:
+    out = np.empty(n, np.int32)
+    lib().orc_rand_stream(C.c_uint(seed), n, _p(out))
+    return out
+
+
+def descriptor_distance(a: np.ndarray, b: np.ndarray) -> int:
+    a = np.ascontiguousarray(a, np.uint8); b = np.ascontiguousarray(b, np.uint8)
+    return lib().orc_descriptor_distance(_p(a), _p(b))
+
+
+# ---------------------------------------------------------------- extractor
+class ORBextractor:
+    def __init__(self, nfeatures=1000, scaleFactor=1.2, nlevels=8, scoreType=1, fastTh=20, minFastTh=7,
+                 blurVariant=0, retainVariant=0):
+        self.args = (nfeatures, scaleFactor, nlevels, scoreType, fastTh, minFastTh, blurVariant, retainVariant)
+        self.nfeatures, self.nlevels = nfeatures, nlevels
+        self.h = C.c_void_p(lib().orc_extractor_create(nfeatures, C.c_float(scaleFactor), nlevels, scoreType, fastTh,
+                                                        minFastTh, blurVariant, retainVariant))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().orc_extractor_destroy(self.h)
+            self.h = None
+
+    def __call__(self, img: np.ndarray):
+        img = np.ascontiguousarray(img, np.uint8)
+        cap = self.nfeatures + 64
+        kps = np.zeros(cap, KP_DTYPE)
+        desc = np.zeros((cap, 32), np.uint8)
+        n = lib().orc_extractor_run(self.h, _p(img), img.shape[1], img.shape[0], img.shape[1], _p(kps), _p(desc), cap)
+        if n < 0:
+            raise RuntimeError(f"oracle extractor error {n}")
+        return kps[:n].copy(), desc[:n].copy()
+
+    def run_batch(self, imgs: np.ndarray, threads: int = 1):
+        imgs = np.ascontiguousarray(imgs, np.uint8)
+        nf, h, w = imgs.shape
+        cap = self.nfeatures
+        kps = np.zeros((nf, cap), KP_DTYPE)
+        desc = np.zeros((nf, cap, 32), np.uint8)
+        counts = np.zeros(nf, np.int32)
+        a = self.args
+        lib().orc_extractor_run_batch(a[0], C.c_float(a[1]), a[2], a[4], a[5], a[6], a[7], _p(imgs), w, h, nf, threads,
+                                      _p(kps), _p(desc), _p(counts), cap)
+        return kps, desc, counts
+
+    def pyramid(self, img: np.ndarray):
+        img = np.ascontiguousarray(img, np.uint8)
+        lib().orc_extractor_pyramid(self.h, _p(img), img.shape[1], img.shape[0], img.shape[1])
+        return [self.level(l) for l in range(self.nlevels)]
+
+    def level(self, l: int) -> np.ndarray:
+        """bordered plane (h+32, w+32) of level l as currently held (blurred in place after a full run)"""
+        w = C.c_int(); h = C.c_int(); s = C.c_int(); nf = C.c_int()
+        lib().orc_extractor_level_info(self.h, l, C.byref(w), C.byref(h), C.byref(s), C.byref(nf))
+        buf = np.empty((h.value + 32, s.value), np.uint8)
+        lib().orc_extractor_level_copy(self.h, l, _p(buf))
+        return buf
+
+    def features_per_level(self):
+        out = []
+        for l in range(self.nlevels):
+            w = C.c_int(); h = C.c_int(); s = C.c_int(); nf = C.c_int()
+            lib().orc_extractor_level_info(self.h, l, C.byref(w), C.byref(h), C.byref(s), C.byref(nf))
+            out.append(nf.value)
+        return out
+
+    def tables(self):
+        sc = np.zeros(self.nlevels, np.float32); inv = np.zeros(self.nlevels, np.float32); um = np.zeros(16, np.int32)
+        lib().orc_extractor_tables(self.h, _p(sc), _p(inv), _p(um))
+        return sc, inv, um
+
+    def level_keypoints(self, l: int) -> np.ndarray:
+        cap = 4 * self.nfeatures + 64
+        out = np.zeros(cap, KP_DTYPE)
+        n = lib().orc_extractor_level_keypoints(self.h, l, _p(out), cap)
+        return out[:n].copy()
+
+
+# ---------------------------------------------------------------- frame + matcher
+class Frame:
+    def __init__(self, kps: np.ndarray, desc: np.ndarray, w: int, h: int, nlevels: int = 8, scaleFactor: float = 1.2):
+        self.kps = np.ascontiguousarray(kps, KP_DTYPE)
+        self.desc = np.ascontiguousarray(desc, np.uint8)
+        self.N = self.kps.size
+        self.h = C.c_void_p(lib().orc_frame_create(_p(self.kps), _p(self.desc), self.N, w, h, nlevels, C.c_float(scaleFactor)))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().orc_frame_destroy(self.h)
+            self.h = None
+
+    def set_camera(self, fx, fy, cx, cy, Tcw=None):
+        T = None if Tcw is None else np.ascontiguousarray(Tcw, np.float32)
+        lib().orc_frame_set_camera(self.h, C.c_float(fx), C.c_float(fy), C.c_float(cx), C.c_float(cy), _p(T))
+
+    def set_mappoints(self, mp: np.ndarray, outlier: np.ndarray | None = None):
+        mp = np.ascontiguousarray(mp, np.int32)
+        o = None if outlier is None else np.ascontiguousarray(outlier, np.uint8)
+        lib().orc_frame_set_mappoints(self.h, _p(mp), _p(o))
+
+    def matches(self):
+        mp = np.empty(self.N, np.int32); sc = np.empty(self.N, np.int32)
+        lib().orc_frame_get_matches(self.h, _p(mp), _p(sc))
+        return mp, sc
+
+    def features_in_area(self, x, y, r, minL=-1, maxL=-1) -> np.ndarray:
+        out = np.empty(max(self.N, 1), np.int32)
+        n = lib().orc_frame_features_in_area(self.h, C.c_float(x), C.c_float(y), C.c_float(r), minL, maxL, _p(out), out.size)
+        return out[:n].copy()
+
+
+def search_by_projection(F: Frame, u, v, level, viewCos, flags, desc, th: float, nnratio: float) -> int:
+    u = np.ascontiguousarray(u, np.float32); v = np.ascontiguousarray(v, np.float32)
+    level = np.ascontiguousarray(level, np.int32); viewCos = np.ascontiguousarray(viewCos, np.float32)
+    flags = np.ascontiguousarray(flags, np.uint8); desc = np.ascontiguousarray(desc, np.uint8)
+    return lib().orc_search_by_projection(F.h, u.size, _p(u), _p(v), _p(level), _p(viewCos), _p(flags), _p(desc),
+                                          C.c_float(th), C.c_float(nnratio))
+
+
+def search_by_projection_frames(cur: Frame, last: Frame, last_world: np.ndarray, th: float, nnratio=0.9, checkOri=True) -> int:
+    lw = np.ascontiguousarray(last_world, np.float32)
+    return lib().orc_search_by_projection_frames(cur.h, last.h, _p(lw), C.c_float(th), C.c_float(nnratio), int(checkOri))
+
+
+def search_for_initialization(F1: Frame, F2: Frame, prev_matched: np.ndarray, window: int, nnratio=0.9, checkOri=True):
+    pm = np.ascontiguousarray(prev_matched, np.float32).copy()
+    m12 = np.empty(F1.N, np.int32)
+    n = lib().orc_search_for_initialization(F1.h, F2.h, _p(pm), _p(m12), window, C.c_float(nnratio), int(checkOri))
+    return n, m12, pm
+
+
+def window_search(F1: Frame, F2: Frame, window: int, minL=-1, maxL=0x7FFFFFFF, nnratio=0.9, checkOri=True):
+    m2 = np.empty(F2.N, np.int32)
+    n = lib().orc_window_search(F1.h, F2.h, window, _p(m2), minL, maxL, C.c_float(nnratio), int(checkOri))
+    return n, m2
+
+
+# ---------------------------------------------------------------- observability
+class Observability:
+    def __init__(self, *, f=None, fu=None, fv=None, nRows=480, nCols=752, Cx=0.0, Cy=0.0, k1=0.0, k2=0.0, dx=None, dy=None):
+        d = C.c_double
+        if f is not None:
+            self.h = C.c_void_p(lib().orc_obs_create_f(d(f), nRows, nCols, d(Cx), d(Cy), d(k1), d(k2), d(dx), d(dy)))
+        else:
+            self.h = C.c_void_p(lib().orc_obs_create_fufv(d(fu), d(fv), nRows, nCols, d(Cx), d(Cy), d(k1), d(k2)))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().orc_obs_destroy(self.h)
+            self.h = None
+
+    def set_xv(self, xv):
+        xv = np.ascontiguousarray(xv, np.float64)
+        lib().orc_obs_set_xv(self.h, _p(xv))
+
+    def get_xv(self):
+        xv = np.empty(13, np.float64)
+        lib().orc_obs_get_xv(self.h, _p(xv))
+        return xv
+
+    def update(self, t0, Tcw_prev, t1, Twc_cur):
+        a = np.ascontiguousarray(Tcw_prev, np.float32); b = np.ascontiguousarray(Twc_cur, np.float32)
+        lib().orc_obs_update(self.h, C.c_double(t0), _p(a), C.c_double(t1), _p(b))
+
+    def predict(self, dt, nseg):
+        lib().orc_obs_predict(self.h, C.c_double(dt), nseg)
+
+    def kine(self, seg=0):
+        Xv = np.empty(13); FQ = np.empty((4, 4)); FO = np.empty((4, 3)); F = np.empty((13, 13))
+        FQi = np.empty((4, 4)); FOi = np.empty((4, 3)); T = np.empty((4, 4), np.float32)
+        lib().orc_obs_get_kine(self.h, seg, _p(Xv), _p(FQ), _p(FO), _p(F), _p(FQi), _p(FOi), _p(T))
+        return dict(Xv=Xv, F_Q=FQ, F_Omg=FO, F=F, F_Q_inSeg=FQi, F_Omg_inSeg=FOi, Tcw=T)
+
+    def H_complete(self, Xv, yi, zi):
+        Xv = np.ascontiguousarray(Xv, np.float64); yi = np.ascontiguousarray(yi, np.float64); zi = np.ascontiguousarray(zi, np.float64)
+        H13 = np.empty((2, 3)); H47 = np.empty((2, 4))
+        lib().orc_obs_H_complete(self.h, _p(Xv), _p(yi), _p(zi), _p(H13), _p(H47))
+        return H13, H47
+
+    def H_simplified(self, Xv, yi):
+        Xv = np.ascontiguousarray(Xv, np.float64); yi = np.ascontiguousarray(yi, np.float64)
+        H13 = np.empty((2, 3)); H47 = np.empty((2, 4)); uv = np.empty(2, np.float32)
+        lib().orc_obs_H_simplified(self.h, _p(Xv), _p(yi), _p(H13), _p(H47), _p(uv))
+        return H13, H47, uv
+
+    def build_frame(self, world, octave, score, valid, level_sigma2, seg=0):
+        world = np.ascontiguousarray(world, np.float32); octave = np.ascontiguousarray(octave, np.int32)
+        score = np.ascontiguousarray(score, np.int32); valid = np.ascontiguousarray(valid, np.uint8)
+        ls = np.ascontiguousarray(level_sigma2, np.float32)
+        n = world.shape[0]
+        blocks = np.zeros((n, 7, 7)); obs = np.zeros(n); H = np.zeros((n, 2, 7))
+        lib().orc_obs_build_frame(self.h, seg, _p(world), _p(octave), _p(score), _p(valid), n, _p(ls), _p(blocks), _p(obs), _p(H))
+        return blocks, obs, H
+
+    def build_map(self, world, track_in_view, check_viz, bounds, seg=0):
+        world = np.ascontiguousarray(world, np.float32); tv = np.ascontiguousarray(track_in_view, np.uint8)
+        n = world.shape[0]
+        blocks = np.zeros((n, 7, 7)); obs = np.zeros(n); uv = np.zeros((n, 2), np.float32)
+        lib().orc_obs_build_map(self.h, seg, _p(world), _p(tv), n, int(check_viz), *[int(b) for b in bounds], _p(blocks), _p(obs), _p(uv))
+        return blocks, obs, uv
+
+
+def logdet(M: np.ndarray) -> float:
+    M = np.ascontiguousarray(M, np.float64)
+    return lib().orc_logdet(_p(M), M.shape[0])
+
+
+def select(blocks: np.ndarray, k: int, mtd: int = 2, sample_scale: float = 23.0, seed: int = 1, scores=None):
+    blocks = np.ascontiguousarray(blocks, np.float64)
+    n = blocks.shape[0]
+    sc = None if scores is None else np.ascontiguousarray(scores, np.float64)
+    idx = np.empty(n, np.int32); ld = np.zeros(n, np.float64)
+    m = lib().orc_obs_select(_p(blocks), _p(sc), n, k, mtd, C.c_double(sample_scale), C.c_long(seed), _p(idx), _p(ld))
+    return idx[:m].copy(), ld[:m].copy()

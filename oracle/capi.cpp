@@ -1,0 +1,222 @@
+// TEST INFRASTRUCTURE ONLY (see oracle.hpp).  extern "C" surface so tests/ and bench.py's cpu_baseline leg can
+// drive the oracle through ctypes.  Not part of the product ABI (that is include/gforb.h).
+#include "oracle.hpp"
+#include <cmath>
+#include <algorithm>
+#include <cstdlib>
+#include <cstring>
+#include <thread>
+
+using namespace oracle;
+
+extern "C" {
+
+// ------------------------------------------------------------------ primitives
+int orc_cvround(double v) { return cvRound(v); }
+void orc_fastatan2(const float* y, const float* x, float* out, int n) { for (int i = 0; i < n; i++) out[i] = fastAtan2(y[i], x[i]); }
+void orc_resize(const uint8_t* src, int sw, int sh, int sstep, uint8_t* dst, int dw, int dh, int dstep) { resizeLinear8u(src, sw, sh, sstep, dst, dw, dh, dstep); }
+void orc_border101(const uint8_t* src, int w, int h, int sstep, uint8_t* dst, int dstep, int b) { copyMakeBorder101(src, w, h, sstep, dst, dstep, b); }
+void orc_blur(const uint8_t* src, int w, int h, int sstep, uint8_t* dst, int dstep, int variant) { gaussianBlur7x7(src, w, h, sstep, dst, dstep, variant); }
+int orc_fast(const uint8_t* img, int w, int h, int step, int th, int nonmax, KeyPoint* out, int cap) {
+    std::vector<KeyPoint> k;
+    FAST9_16(img, w, h, step, th, nonmax != 0, k);
+    int n = (int)std::min<size_t>(k.size(), cap);
+    memcpy(out, k.data(), sizeof(KeyPoint) * n);
+    return (int)k.size();
+}
+// responses in; out_idx = indices (into the input) of the surviving keypoints in their output order
+int orc_retain_best(const float* resp, int n_in, int n_keep, int variant, int* out_idx) {
+    std::vector<KeyPoint> k(n_in);
+    for (int i = 0; i < n_in; i++) { k[i] = KeyPoint{0, 0, 0, 0, resp[i], 0, i}; }
+    retainBest(k, n_keep, variant);
+    for (size_t i = 0; i < k.size(); i++) out_idx[i] = k[i].class_id;
+    return (int)k.size();
+}
+void orc_sincosf(const float* x, float* s, float* c, int n) { for (int i = 0; i < n; i++) { s[i] = sinf(x[i]); c[i] = cosf(x[i]); } }
+void orc_rand_stream(unsigned seed, int n, int* out) { srand(seed); for (int i = 0; i < n; i++) out[i] = rand(); }
+
+// ------------------------------------------------------------------ extractor
+void* orc_extractor_create(int nfeatures, float scaleFactor, int nlevels, int scoreType, int fastTh, int minFastTh,
+                           int blurVariant, int retainVariant) {
+    return new ORBextractor(nfeatures, scaleFactor, nlevels, scoreType, fastTh, minFastTh, blurVariant, retainVariant);
+}
+void orc_extractor_destroy(void* h) { delete (ORBextractor*)h; }
+int orc_extractor_run(void* h, const uint8_t* img, int w, int ht, int step, KeyPoint* kps, uint8_t* desc, int cap) {
+    ORBextractor* e = (ORBextractor*)h;
+    std::vector<KeyPoint> k; std::vector<uint8_t> d;
+    int rc = (*e)(img, w, ht, step, k, d);
+    if (rc < 0) return rc;
+    int n = (int)std::min<size_t>(k.size(), cap);
+    if (kps) memcpy(kps, k.data(), sizeof(KeyPoint) * n);
+    if (desc) memcpy(desc, d.data(), (size_t)32 * n);
+    return (int)k.size();
+}
+// many frames, `threads` worker threads, one extractor instance per thread (the reference extractor is single-threaded)
+int orc_extractor_run_batch(int nfeatures, float scaleFactor, int nlevels, int fastTh, int minFastTh, int blurVariant,
+                            int retainVariant, const uint8_t* imgs, int w, int ht, int nframes, int threads,
+                            KeyPoint* kps, uint8_t* desc, int* counts, int cap) {
+    if (threads < 1) threads = 1;
+    std::vector<std::thread> pool;
+    for (int t = 0; t < threads; t++)
+        pool.emplace_back([=]() {
+            ORBextractor e(nfeatures, scaleFactor, nlevels, FAST_SCORE, fastTh, minFastTh, blurVariant, retainVariant);
+            std::vector<KeyPoint> k; std::vector<uint8_t> d;
+            for (int f = t; f < nframes; f += threads) {
+                e(imgs + (size_t)f * w * ht, w, ht, w, k, d);
+                int n = (int)std::min<size_t>(k.size(), cap);
+                counts[f] = n;
+                if (kps) memcpy(kps + (size_t)f * cap, k.data(), sizeof(KeyPoint) * n);
+                if (desc) memcpy(desc + (size_t)f * cap * 32, d.data(), (size_t)32 * n);
+            }
+        });
+    for (auto& th : pool) th.join();
+    return 0;
+}
+int orc_extractor_pyramid(void* h, const uint8_t* img, int w, int ht, int step) {
+    ((ORBextractor*)h)->ComputePyramid(img, w, ht, step); return 0;
+}
+void orc_extractor_level_info(void* h, int level, int* w, int* ht, int* step, int* nfeat) {
+    ORBextractor* e = (ORBextractor*)h;
+    *w = e->mvImagePyramid[level].w; *ht = e->mvImagePyramid[level].h; *step = e->mvImagePyramid[level].step;
+    *nfeat = e->mnFeaturesPerLevel[level];
+}
+void orc_extractor_level_copy(void* h, int level, uint8_t* dst) {
+    ORBextractor* e = (ORBextractor*)h;
+    memcpy(dst, e->mvImagePyramid[level].buf.data(), e->mvImagePyramid[level].buf.size());
+}
+void orc_extractor_tables(void* h, float* scale, float* invScale, int* umax16) {
+    ORBextractor* e = (ORBextractor*)h;
+    for (int i = 0; i < e->nlevels; i++) { scale[i] = e->mvScaleFactor[i]; invScale[i] = e->mvInvScaleFactor[i]; }
+    for (int i = 0; i < 16; i++) umax16[i] = e->umax[i];
+}
+// per-level keypoints (level coordinates, angle filled) of the last run
+int orc_extractor_level_keypoints(void* h, int level, KeyPoint* out, int cap) {
+    ORBextractor* e = (ORBextractor*)h;
+    if (level >= (int)e->lastAllKeypoints.size()) return 0;
+    auto& v = e->lastAllKeypoints[level];
+    int n = (int)std::min<size_t>(v.size(), cap);
+    memcpy(out, v.data(), sizeof(KeyPoint) * n);
+    return (int)v.size();
+}
+
+// ------------------------------------------------------------------ frame / matcher
+void* orc_frame_create(const KeyPoint* kps, const uint8_t* desc, int n, int imgW, int imgH, int nlevels, float scaleFactor) {
+    Frame* f = new Frame();
+    f->init(kps, desc, n, imgW, imgH, nlevels, scaleFactor);
+    return f;
+}
+void orc_frame_destroy(void* f) { delete (Frame*)f; }
+void orc_frame_set_camera(void* fp, float fx, float fy, float cx, float cy, const float* Tcw) {
+    Frame* f = (Frame*)fp; f->fx = fx; f->fy = fy; f->cx = cx; f->cy = cy; if (Tcw) memcpy(f->mTcw, Tcw, 64);
+}
+void orc_frame_set_mappoints(void* fp, const int* mp, const uint8_t* outlier) {
+    Frame* f = (Frame*)fp;
+    for (int i = 0; i < f->N; i++) { f->mvpMapPoints[i] = mp[i]; if (outlier) f->mvbOutlier[i] = outlier[i]; }
+}
+void orc_frame_get_matches(void* fp, int* mp, int* score) {
+    Frame* f = (Frame*)fp;
+    for (int i = 0; i < f->N; i++) { mp[i] = f->mvpMapPoints[i]; score[i] = f->mvpMatchScore[i]; }
+}
+int orc_frame_features_in_area(void* fp, float x, float y, float r, int minL, int maxL, int* out, int cap) {
+    auto v = ((Frame*)fp)->GetFeaturesInArea(x, y, r, minL, maxL);
+    for (size_t i = 0; i < v.size() && (int)i < cap; i++) out[i] = (int)v[i];
+    return (int)v.size();
+}
+int orc_descriptor_distance(const uint8_t* a, const uint8_t* b) { return ORBmatcher::DescriptorDistance(a, b); }
+
+// map-point SoA: flags bit0 = mbTrackInView, bit1 = isBad
+int orc_search_by_projection(void* fp, int M, const float* u, const float* v, const int* level, const float* viewCos,
+                             const uint8_t* flags, const uint8_t* desc, float th, float nnratio) {
+    std::vector<MapPointView> mps(M);
+    for (int i = 0; i < M; i++) {
+        mps[i].mTrackProjX = u[i]; mps[i].mTrackProjY = v[i]; mps[i].mnTrackScaleLevel = level[i];
+        mps[i].mTrackViewCos = viewCos[i]; mps[i].mbTrackInView = flags[i] & 1; mps[i].isBad = (flags[i] >> 1) & 1;
+        memcpy(mps[i].desc, desc + (size_t)32 * i, 32);
+    }
+    ORBmatcher m(nnratio, true);
+    return m.SearchByProjection(*(Frame*)fp, mps, th);
+}
+int orc_search_by_projection_frames(void* cur, void* last, const float* lastWorldPos, float th, float nnratio, int checkOri) {
+    ORBmatcher m(nnratio, checkOri != 0);
+    return m.SearchByProjection(*(Frame*)cur, *(const Frame*)last, lastWorldPos, th);
+}
+int orc_search_for_initialization(void* f1, void* f2, float* prevMatched, int* matches12, int windowSize, float nnratio, int checkOri) {
+    Frame* F1 = (Frame*)f1;
+    ORBmatcher m(nnratio, checkOri != 0);
+    std::vector<float> pm(prevMatched, prevMatched + 2 * (size_t)F1->N);
+    std::vector<int> m12;
+    int n = m.SearchForInitialization(*F1, *(Frame*)f2, pm, m12, windowSize);
+    memcpy(prevMatched, pm.data(), sizeof(float) * pm.size());
+    memcpy(matches12, m12.data(), sizeof(int) * m12.size());
+    return n;
+}
+int orc_window_search(void* f1, void* f2, int windowSize, int* matches2, int minLevel, int maxLevel, float nnratio, int checkOri) {
+    ORBmatcher m(nnratio, checkOri != 0);
+    std::vector<int> m2;
+    int n = m.WindowSearch(*(Frame*)f1, *(Frame*)f2, windowSize, m2, minLevel, maxLevel);
+    memcpy(matches2, m2.data(), sizeof(int) * m2.size());
+    return n;
+}
+
+// ------------------------------------------------------------------ observability
+void* orc_obs_create_f(double f, int nRows, int nCols, double Cx, double Cy, double k1, double k2, double dx, double dy) {
+    return new Observability(f, nRows, nCols, Cx, Cy, k1, k2, dx, dy);
+}
+void* orc_obs_create_fufv(double fu, double fv, int nRows, int nCols, double Cx, double Cy, double k1, double k2) {
+    return new Observability(fu, fv, nRows, nCols, Cx, Cy, k1, k2);
+}
+void orc_obs_destroy(void* o) { delete (Observability*)o; }
+void orc_obs_set_xv(void* o, const double* Xv) { memcpy(((Observability*)o)->Xv, Xv, 13 * sizeof(double)); }
+void orc_obs_get_xv(void* o, double* Xv) { memcpy(Xv, ((Observability*)o)->Xv, 13 * sizeof(double)); }
+void orc_obs_update(void* o, double t0, const float* Tcw_prev, double t1, const float* Twc_cur) { ((Observability*)o)->updatePWLSVec(t0, Tcw_prev, t1, Twc_cur); }
+void orc_obs_predict(void* o, double dt, int nseg) { ((Observability*)o)->predictPWLSVec(dt, nseg); }
+void orc_obs_get_kine(void* o, int seg, double* Xv, double* F_Q, double* F_Omg, double* F, double* F_Q_inSeg,
+                      double* F_Omg_inSeg, float* Tcw) {
+    KineStruct& k = ((Observability*)o)->kinematic[seg];
+    memcpy(Xv, k.Xv, sizeof(k.Xv)); memcpy(F_Q, k.F_Q, sizeof(k.F_Q)); memcpy(F_Omg, k.F_Omg, sizeof(k.F_Omg));
+    memcpy(F, k.F, sizeof(k.F)); memcpy(F_Q_inSeg, k.F_Q_inSeg, sizeof(k.F_Q_inSeg));
+    memcpy(F_Omg_inSeg, k.F_Omg_inSeg, sizeof(k.F_Omg_inSeg)); memcpy(Tcw, k.Tcw, sizeof(k.Tcw));
+}
+void orc_obs_H_complete(void* o, const double* Xv, const double* yi, const double* zi, double* H13, double* H47) {
+    double dh[6]; float ru, rv;
+    ((Observability*)o)->compute_H_subblock_complete(Xv, yi, zi, H13, H47, dh, ru, rv);
+}
+int orc_obs_H_simplified(void* o, const double* Xv, const double* yi, double* H13, double* H47, float* uv) {
+    double dh[6];
+    return ((Observability*)o)->compute_H_subblock_simplied(Xv, yi, H13, H47, dh, false, uv[0], uv[1]);
+}
+void orc_obs_build_frame(void* o, int seg, const float* worldPos, const int* octave, const int* matchScore,
+                         const uint8_t* valid, int n, const float* levelSigma2, double* blocks, double* obsScore, double* H_meas) {
+    Observability* ob = (Observability*)o; ob->mKineIdx = seg;
+    ob->batchInfoMat_Frame(worldPos, octave, matchScore, valid, n, levelSigma2, blocks, obsScore, H_meas);
+}
+void orc_obs_build_map(void* o, int seg, const float* worldPos, const uint8_t* trackInView, int n, int check_viz,
+                       int minX, int maxX, int minY, int maxY, double* blocks, double* obsScore, float* uv) {
+    Observability* ob = (Observability*)o; ob->mKineIdx = seg;
+    ob->batchInfoMat_Map(worldPos, trackInView, n, check_viz != 0, minX, maxX, minY, maxY, blocks, obsScore, uv);
+}
+double orc_logdet(const double* M, int n) { return logDet(M, n); }
+// mtd: 1 baseline greedy, 2 lazier greedy selection, 3 automatic (deletion if 2k>n), 5 deletion.
+// seed >= 0 -> srand(seed) first (glibc default stream == seed 1).  Returns number selected; out_idx = pool indices
+// in selection order (deletion: ascending pool order); out_logdet[i] = log-det after pick i (selection modes).
+int orc_obs_select(const double* blocks, const double* obsScore, int n, int k, int mtd, double sampleScale, long seed,
+                   int* out_idx, double* out_logdet) {
+    Observability ob(1.0, 1.0, 480, 640, 320, 240, 0, 0);
+    ob.lmkSelectPool.resize(n);
+    for (int i = 0; i < n; i++) {
+        GoodPoint& g = ob.lmkSelectPool[i];
+        g.idx = i; g.obs_score = obsScore ? obsScore[i] : 1.0; g.selected = false; g.upper_bound = 0;
+        memcpy(g.obs_block, blocks + (size_t)49 * i, sizeof(g.obs_block));
+    }
+    if (seed >= 0) srand((unsigned)seed);
+    std::vector<GoodPoint> sub;
+    if (mtd == 1) ob.maxVolSelection_BaselineGreedy(&sub, k);
+    else if (mtd == 2) ob.maxVolSelection_LazierGreedy(0, n, &sub, k, sampleScale, 1e30);
+    else if (mtd == 3) ob.maxVolAutomatic_LazierGreedy(0, n, &sub, k, sampleScale, 1e30);
+    else if (mtd == 5) ob.maxVolDeletion_LazierGreedy(0, n, &sub, k, sampleScale, 1e30);
+    else return -1;
+    for (size_t i = 0; i < sub.size(); i++) { out_idx[i] = (int)sub[i].idx; if (out_logdet) out_logdet[i] = sub[i].upper_bound; }
+    return (int)sub.size();
+}
+
+}  // extern "C"

@@ -1,0 +1,332 @@
+// TEST INFRASTRUCTURE ONLY (see oracle.hpp).  CPU restatement of the per-frame-tracking parts of
+// ORB_SLAM::Frame (src/Frame.cc:118-131, 300-377) and ORB_SLAM::ORBmatcher (src/ORBmatcher.cc:384-465, 696-702,
+// 979-1086, 1172-1287, 2081-2202, 2338-2400; include/ORBmatcher.h:71-145).
+// MapPoint* / NULL is flattened to an int id / -1.
+#include "oracle.hpp"
+#include <algorithm>
+#include <climits>
+#include <cmath>
+#include <cstring>
+
+namespace oracle {
+
+// src/Frame.cc:55-134 (the parts that matter to matching; no undistortion: mDistCoef(0)==0 -> mvKeysUn=mvKeys)
+void Frame::init(const KeyPoint* kps, const uint8_t* desc, int n, int imgW, int imgH, int nlevels, float scaleFactor) {
+    N = n;
+    mvKeysUn.assign(kps, kps + n);
+    mDescriptors.assign(desc, desc + (size_t)n * 32);
+    mvpMapPoints.assign(n, -1);
+    mvpMatchScore.assign(n, 999);
+    mvbOutlier.assign(n, 0);
+    mnMinX = 0; mnMaxX = imgW; mnMinY = 0; mnMaxY = imgH;              // src/Frame.cc:489-493
+    mfGridElementWidthInv = static_cast<float>(FRAME_GRID_COLS) / static_cast<float>(mnMaxX - mnMinX);
+    mfGridElementHeightInv = static_cast<float>(FRAME_GRID_ROWS) / static_cast<float>(mnMaxY - mnMinY);
+    mvScaleFactors.resize(nlevels);
+    mvLevelSigma2.resize(nlevels);
+    mvScaleFactors[0] = 1.0f; mvLevelSigma2[0] = 1.0f;
+    for (int i = 1; i < nlevels; i++) {
+        mvScaleFactors[i] = mvScaleFactors[i - 1] * scaleFactor;
+        mvLevelSigma2[i] = mvScaleFactors[i] * mvScaleFactors[i];
+    }
+    for (int i = 0; i < FRAME_GRID_COLS; i++)
+        for (int j = 0; j < FRAME_GRID_ROWS; j++) mGrid[i][j].clear();
+    for (size_t i = 0; i < mvKeysUn.size(); i++) {
+        int gx, gy;
+        if (PosInGrid(mvKeysUn[i], gx, gy)) mGrid[gx][gy].push_back(i);
+    }
+}
+
+// src/Frame.cc:367-377
+bool Frame::PosInGrid(const KeyPoint& kp, int& posX, int& posY) const {
+    posX = std::round((kp.x - mnMinX) * mfGridElementWidthInv);
+    posY = std::round((kp.y - mnMinY) * mfGridElementHeightInv);
+    if (posX < 0 || posX >= FRAME_GRID_COLS || posY < 0 || posY >= FRAME_GRID_ROWS) return false;
+    return true;
+}
+
+// src/Frame.cc:300-365
+std::vector<size_t> Frame::GetFeaturesInArea(float x, float y, float r, int minLevel, int maxLevel) const {
+    std::vector<size_t> vIndices;
+    int nMinCellX = std::floor((x - mnMinX - r) * mfGridElementWidthInv);
+    nMinCellX = std::max(0, nMinCellX);
+    if (nMinCellX >= FRAME_GRID_COLS) return vIndices;
+    int nMaxCellX = std::ceil((x - mnMinX + r) * mfGridElementWidthInv);
+    nMaxCellX = std::min(FRAME_GRID_COLS - 1, nMaxCellX);
+    if (nMaxCellX < 0) return vIndices;
+    int nMinCellY = std::floor((y - mnMinY - r) * mfGridElementHeightInv);
+    nMinCellY = std::max(0, nMinCellY);
+    if (nMinCellY >= FRAME_GRID_ROWS) return vIndices;
+    int nMaxCellY = std::ceil((y - mnMinY + r) * mfGridElementHeightInv);
+    nMaxCellY = std::min(FRAME_GRID_ROWS - 1, nMaxCellY);
+    if (nMaxCellY < 0) return vIndices;
+
+    bool bCheckLevels = true, bSameLevel = false;
+    if (minLevel == -1 && maxLevel == -1) bCheckLevels = false;
+    else if (minLevel == maxLevel) bSameLevel = true;
+
+    for (int ix = nMinCellX; ix <= nMaxCellX; ix++)
+        for (int iy = nMinCellY; iy <= nMaxCellY; iy++) {
+            const std::vector<size_t>& vCell = mGrid[ix][iy];
+            for (size_t j = 0; j < vCell.size(); j++) {
+                const KeyPoint& kpUn = mvKeysUn[vCell[j]];
+                if (bCheckLevels && !bSameLevel) {
+                    if (kpUn.octave < minLevel || kpUn.octave > maxLevel) continue;
+                } else if (bSameLevel) {
+                    if (kpUn.octave != minLevel) continue;
+                }
+                if (std::abs(kpUn.x - x) > r || std::abs(kpUn.y - y) > r) continue;
+                vIndices.push_back(vCell[j]);
+            }
+        }
+    return vIndices;
+}
+
+// src/ORBmatcher.cc:2384-2400 (bit-hack popcount, restated verbatim in spirit)
+int ORBmatcher::DescriptorDistance(const uint8_t* a, const uint8_t* b) {
+    int dist = 0;
+    for (int i = 0; i < 8; i++) {
+        uint32_t pa, pb;
+        memcpy(&pa, a + 4 * i, 4);
+        memcpy(&pb, b + 4 * i, 4);
+        unsigned int v = pa ^ pb;
+        v = v - ((v >> 1) & 0x55555555);
+        v = (v & 0x33333333) + ((v >> 2) & 0x33333333);
+        dist += (((v + (v >> 4)) & 0xF0F0F0F) * 0x1010101) >> 24;
+    }
+    return dist;
+}
+
+// src/ORBmatcher.cc:696-702  (float compared against the double literal 0.998)
+float ORBmatcher::RadiusByViewingCos(float viewCos) {
+    if (viewCos > 0.998) return 2.5;
+    else return 4.0;
+}
+
+// include/ORBmatcher.h:71-145 == loop body of src/ORBmatcher.cc:384-465
+int ORBmatcher::SearchByProjection_OnePoint(Frame& F, const MapPointView& mp, int mpId, float th) {
+    const bool bFactor = th != 1.0;
+    if (!mp.mbTrackInView) return -1;
+    if (mp.isBad) return -1;
+    const int nPredictedLevel = mp.mnTrackScaleLevel;
+    float r = RadiusByViewingCos(mp.mTrackViewCos);
+    if (bFactor) r *= th;
+    std::vector<size_t> vNearIndices = F.GetFeaturesInArea(mp.mTrackProjX, mp.mTrackProjY,
+                                                           r * F.mvScaleFactors[nPredictedLevel],
+                                                           nPredictedLevel - 1, nPredictedLevel);
+    if (vNearIndices.empty()) return -1;
+    int bestDist = INT_MAX, bestLevel = -1, bestDist2 = INT_MAX, bestLevel2 = -1, bestIdx = -1;
+    for (size_t idx : vNearIndices) {
+        if (F.mvpMapPoints[idx] >= 0) continue;
+        const int dist = DescriptorDistance(mp.desc, &F.mDescriptors[idx * 32]);
+        if (dist < bestDist) {
+            bestDist2 = bestDist; bestDist = dist;
+            bestLevel2 = bestLevel; bestLevel = F.mvKeysUn[idx].octave;
+            bestIdx = idx;
+        } else if (dist < bestDist2) {
+            bestLevel2 = F.mvKeysUn[idx].octave;
+            bestDist2 = dist;
+        }
+    }
+    if (bestDist <= TH_HIGH) {
+        if (bestLevel == bestLevel2 && bestDist > mfNNratio * bestDist2) return -1;
+        F.mvpMapPoints[bestIdx] = mpId;
+        F.mvpMatchScore[bestIdx] = bestDist;
+        return bestIdx;
+    }
+    return -1;
+}
+
+int ORBmatcher::SearchByProjection(Frame& F, const std::vector<MapPointView>& vpMapPoints, float th) {
+    int nmatches = 0;
+    for (size_t iMP = 0; iMP < vpMapPoints.size(); iMP++)
+        if (SearchByProjection_OnePoint(F, vpMapPoints[iMP], (int)iMP, th) >= 0) nmatches++;
+    return nmatches;
+}
+
+// src/ORBmatcher.cc:2081-2202
+int ORBmatcher::SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, const float* lastWorldPos, float th) {
+    int nmatches = 0;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = 1.0f / HISTO_LENGTH;
+    const float* T = CurrentFrame.mTcw;
+    for (size_t i = 0; i < LastFrame.mvpMapPoints.size(); i++) {
+        if (LastFrame.mvpMapPoints[i] < 0) continue;
+        if (LastFrame.mvbOutlier[i]) continue;
+        const float* X = lastWorldPos + 3 * i;
+        // cv::Mat x3Dc = Rcw*x3Dw+tcw: CV_32F gemm accumulates each row dot product in double, then casts to
+        // float (cv::gemm's small-matrix path for 32F uses double accumulators), then adds tcw in float.
+        float xc3[3];
+        for (int r = 0; r < 3; r++) {
+            double s = (double)T[r * 4 + 0] * X[0] + (double)T[r * 4 + 1] * X[1] + (double)T[r * 4 + 2] * X[2];
+            xc3[r] = (float)s + T[r * 4 + 3];
+        }
+        const float xc = xc3[0], yc = xc3[1];
+        const float invzc = 1.0 / xc3[2];
+        float u = CurrentFrame.fx * xc * invzc + CurrentFrame.cx;
+        float v = CurrentFrame.fy * yc * invzc + CurrentFrame.cy;
+        if (u < CurrentFrame.mnMinX || u > CurrentFrame.mnMaxX) continue;
+        if (v < CurrentFrame.mnMinY || v > CurrentFrame.mnMaxY) continue;
+        int nPredictedOctave = LastFrame.mvKeysUn[i].octave;
+        float radius = th * CurrentFrame.mvScaleFactors[nPredictedOctave];
+        std::vector<size_t> vIndices2 = CurrentFrame.GetFeaturesInArea(u, v, radius, nPredictedOctave - 1, nPredictedOctave + 1);
+        if (vIndices2.empty()) continue;
+        const uint8_t* dMP = &LastFrame.mDescriptors[i * 32];
+        int bestDist = INT_MAX, bestIdx2 = -1;
+        for (size_t i2 : vIndices2) {
+            if (CurrentFrame.mvpMapPoints[i2] >= 0) continue;
+            int dist = DescriptorDistance(dMP, &CurrentFrame.mDescriptors[i2 * 32]);
+            if (dist < bestDist) { bestDist = dist; bestIdx2 = i2; }
+        }
+        if (bestDist <= TH_HIGH) {
+            CurrentFrame.mvpMapPoints[bestIdx2] = LastFrame.mvpMapPoints[i];
+            CurrentFrame.mvpMatchScore[bestIdx2] = bestDist;
+            nmatches++;
+            if (mbCheckOrientation) {
+                float rot = LastFrame.mvKeysUn[i].angle - CurrentFrame.mvKeysUn[bestIdx2].angle;
+                if (rot < 0.0) rot += 360.0f;
+                int bin = std::round(rot * factor);
+                if (bin == HISTO_LENGTH) bin = 0;
+                rotHist[bin].push_back(bestIdx2);
+            }
+        }
+    }
+    if (mbCheckOrientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        ComputeThreeMaxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++)
+            if (i != ind1 && i != ind2 && i != ind3)
+                for (int idx : rotHist[i]) {
+                    CurrentFrame.mvpMapPoints[idx] = -1;
+                    CurrentFrame.mvpMatchScore[idx] = 999;
+                    nmatches--;
+                }
+    }
+    return nmatches;
+}
+
+// src/ORBmatcher.cc:1172-1287
+int ORBmatcher::SearchForInitialization(const Frame& F1, const Frame& F2, std::vector<float>& vbPrevMatched,
+                                        std::vector<int>& vnMatches12, int windowSize) {
+    int nmatches = 0;
+    vnMatches12.assign(F1.mvKeysUn.size(), -1);
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = 1.0f / HISTO_LENGTH;
+    std::vector<int> vMatchedDistance(F2.mvKeysUn.size(), INT_MAX);
+    std::vector<int> vnMatches21(F2.mvKeysUn.size(), -1);
+    for (size_t i1 = 0; i1 < F1.mvKeysUn.size(); i1++) {
+        const KeyPoint& kp1 = F1.mvKeysUn[i1];
+        int level1 = kp1.octave;
+        if (level1 > 0) continue;
+        std::vector<size_t> vIndices2 = F2.GetFeaturesInArea(vbPrevMatched[2 * i1], vbPrevMatched[2 * i1 + 1],
+                                                             windowSize, level1, level1);
+        if (vIndices2.empty()) continue;
+        const uint8_t* d1 = &F1.mDescriptors[i1 * 32];
+        int bestDist = INT_MAX, bestDist2 = INT_MAX, bestIdx2 = -1;
+        for (size_t i2 : vIndices2) {
+            int dist = DescriptorDistance(d1, &F2.mDescriptors[i2 * 32]);
+            if (vMatchedDistance[i2] <= dist) continue;
+            if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestIdx2 = i2; }
+            else if (dist < bestDist2) bestDist2 = dist;
+        }
+        if (bestDist <= TH_LOW) {
+            if (bestDist < (float)bestDist2 * mfNNratio) {
+                if (vnMatches21[bestIdx2] >= 0) {
+                    vnMatches12[vnMatches21[bestIdx2]] = -1;
+                    nmatches--;
+                }
+                vnMatches12[i1] = bestIdx2;
+                vnMatches21[bestIdx2] = i1;
+                vMatchedDistance[bestIdx2] = bestDist;
+                nmatches++;
+                if (mbCheckOrientation) {
+                    float rot = F1.mvKeysUn[i1].angle - F2.mvKeysUn[bestIdx2].angle;
+                    if (rot < 0.0) rot += 360.0f;
+                    int bin = std::round(rot * factor);
+                    if (bin == HISTO_LENGTH) bin = 0;
+                    rotHist[bin].push_back(i1);
+                }
+            }
+        }
+    }
+    if (mbCheckOrientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        ComputeThreeMaxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (int idx1 : rotHist[i])
+                if (vnMatches12[idx1] >= 0) { vnMatches12[idx1] = -1; nmatches--; }
+        }
+    }
+    for (size_t i1 = 0; i1 < vnMatches12.size(); i1++)
+        if (vnMatches12[i1] >= 0) {
+            vbPrevMatched[2 * i1] = F2.mvKeysUn[vnMatches12[i1]].x;
+            vbPrevMatched[2 * i1 + 1] = F2.mvKeysUn[vnMatches12[i1]].y;
+        }
+    return nmatches;
+}
+
+// src/ORBmatcher.cc:979-1086.  F1.mvpMapPoints[i1] >= 0 plays the role of a non-NULL, non-bad MapPoint.
+int ORBmatcher::WindowSearch(const Frame& F1, const Frame& F2, int windowSize, std::vector<int>& vpMapPointMatches2,
+                             int minScaleLevel, int maxScaleLevel) {
+    int nmatches = 0;
+    vpMapPointMatches2.assign(F2.mvpMapPoints.size(), -1);
+    std::vector<int> vnMatches21(F2.mvKeysUn.size(), -1);
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = 1.0f / HISTO_LENGTH;
+    const bool bMinLevel = minScaleLevel > 0;
+    const bool bMaxLevel = maxScaleLevel < INT_MAX;
+    for (size_t i1 = 0; i1 < F1.mvpMapPoints.size(); i1++) {
+        if (F1.mvpMapPoints[i1] < 0) continue;
+        const KeyPoint& kp1 = F1.mvKeysUn[i1];
+        int level1 = kp1.octave;
+        if (bMinLevel && level1 < minScaleLevel) continue;
+        if (bMaxLevel && level1 > maxScaleLevel) continue;
+        std::vector<size_t> vIndices2 = F2.GetFeaturesInArea(kp1.x, kp1.y, windowSize, level1, level1);
+        if (vIndices2.empty()) continue;
+        const uint8_t* d1 = &F1.mDescriptors[i1 * 32];
+        int bestDist = INT_MAX, bestDist2 = INT_MAX, bestIdx2 = -1;
+        for (size_t i2 : vIndices2) {
+            if (vpMapPointMatches2[i2] >= 0) continue;
+            int dist = DescriptorDistance(d1, &F2.mDescriptors[i2 * 32]);
+            if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestIdx2 = i2; }
+            else if (dist < bestDist2) bestDist2 = dist;
+        }
+        if (bestDist <= bestDist2 * mfNNratio && bestDist <= TH_HIGH) {
+            vpMapPointMatches2[bestIdx2] = F1.mvpMapPoints[i1];
+            vnMatches21[bestIdx2] = i1;
+            nmatches++;
+            float rot = F1.mvKeysUn[i1].angle - F2.mvKeysUn[bestIdx2].angle;
+            if (rot < 0.0) rot += 360.0f;
+            int bin = std::round(rot * factor);
+            if (bin == HISTO_LENGTH) bin = 0;
+            rotHist[bin].push_back(bestIdx2);
+        }
+    }
+    if (mbCheckOrientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        ComputeThreeMaxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++)
+            if (i != ind1 && i != ind2 && i != ind3)
+                for (int idx : rotHist[i]) {
+                    vpMapPointMatches2[idx] = -1;
+                    vnMatches21[idx] = -1;
+                    nmatches--;
+                }
+    }
+    return nmatches;
+}
+
+// src/ORBmatcher.cc:2338-2379
+void ORBmatcher::ComputeThreeMaxima(const std::vector<int>* histo, int L, int& ind1, int& ind2, int& ind3) {
+    int max1 = 0, max2 = 0, max3 = 0;
+    for (int i = 0; i < L; i++) {
+        const int s = histo[i].size();
+        if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+        else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+        else if (s > max3) { max3 = s; ind3 = i; }
+    }
+    if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+    else if (max3 < 0.1f * (float)max1) ind3 = -1;
+}
+
+}  // namespace oracle
