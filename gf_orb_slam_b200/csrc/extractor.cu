@@ -1,0 +1,947 @@
+// B200-native ORB extraction: batch-first CUDA implementation of ORB_SLAM::ORBextractor::operator()
+// (reference src/ORBextractor.cc:769-875).  Stages (each a kernel over the whole batch):
+//   K1a border0      level-0 copy + reflect-101 ring                      (ComputePyramid :990)
+//   K1b resize       level l-1 -> l, 11-bit fixed-point bilinear + ring    (ComputePyramid :943,:982)
+//   K2  detect       one CTA per (cell, frame): FAST-9/16 score, cell-confined NMS, ordered candidate list,
+//                    counts at iniThFAST and minThFAST                     (ComputeKeyPoints :573-628)
+//   K3b quota        per (frame, level): threshold fallback + quota redistribution (:673-721)
+//   K3c cell_retain  per cell: retainBest emulation                        (:733-745)
+//   K3d level_retain per (frame, level): retainBest(nDesired)              (:748-752)
+//   K4  orient       warp per keypoint: IC_Angle + KeyPoint emission       (:131-158, :738-745, :865-871)
+//   K5  blur         7x7 Gaussian of every level ROI                       (:842)
+//   K6  describe     warp per keypoint: steered BRIEF                      (:161-201)
+// Data layout in HBM: per frame one "pyramid block" holding all bordered level planes (pitch multiple of 128 B,
+// ROI at (16,16)), a second block with the blurred ROIs, a candidate buffer (packed u32 score|y|x), per-level
+// keypoint buffers.  All integer work is bit-exact by construction; float steps use un-fused IEEE ops.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <vector>
+#include "common.cuh"
+
+namespace gforb {
+
+// ------------------------------------------------------------------------------------------------ plans
+struct LevelPlan {
+    int w, h, pitch, rows;        // ROI size; bordered plane = rows x pitch bytes (rows = h + 32)
+    unsigned long long off;       // byte offset of the plane inside a frame's pyramid block
+    int nDesired, levelCols, levelRows, cellW, cellH, nCells, cellBase, nfeaturesCell;
+    int kpBase, kpCap;            // slice of the per-frame level-keypoint buffer
+    int xtab, ytab;               // offsets (in int2 units) of the resize tables for l-1 -> l
+    int scaledPatchSize;
+    float scale;
+};
+struct CellPlan {
+    int level, x0, y0, x1, y1;    // interior rectangle in level ROI coordinates [x0,x1) x [y0,y1) (may be empty)
+    int skipped;                  // 1: the reference `continue`s before FAST (hX<=0 / hY<=0)
+    int candBase, candCap;
+};
+struct BlurTile { int level, x0, y0; };
+
+__constant__ signed char c_pattern[256 * 4];
+__constant__ int c_umax[16];
+__constant__ int c_gauss[2][7] = {{18, 34, 48, 56, 48, 34, 18}, {18, 34, 49, 55, 49, 34, 18}};
+
+static const signed char h_pattern[256][4] = {
+#include "brief_pattern.inc"
+};
+
+__device__ __forceinline__ int reflect101(int p, int len) {
+    if (len == 1) return 0;
+    while (p < 0 || p >= len) p = p < 0 ? -p : 2 * (len - 1) - p;
+    return p;
+}
+
+// ------------------------------------------------------------------------------------------------ K1a
+__global__ void __launch_bounds__(256) k_border0(const uint8_t* __restrict__ img, int w, int h, int stride,
+                                                 size_t frameStride, uint8_t* __restrict__ pyr, size_t framePyr,
+                                                 LevelPlan L, int batch) {
+    const int chunksPerRow = L.pitch >> 4;
+    const long long total = (long long)batch * L.rows * chunksPerRow;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        int xc = (int)(i % chunksPerRow);
+        long long t = i / chunksPerRow;
+        int Y = (int)(t % L.rows);
+        int b = (int)(t / L.rows);
+        const uint8_t* srow = img + (size_t)b * frameStride + (size_t)reflect101(Y - EDGE, h) * stride;
+        int X0 = xc << 4;
+        uint4 out;
+        const uint8_t* sp = srow + (X0 - EDGE);
+        if (X0 >= EDGE && X0 + 15 < EDGE + w && ((reinterpret_cast<uintptr_t>(sp) & 15) == 0)) {
+            out = ldg_nc_u4(sp);
+        } else {
+            uint32_t wv[4];
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                uint32_t v = 0;
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    int X = X0 + q * 4 + k;
+                    uint32_t px = (X < w + 2 * EDGE) ? srow[reflect101(X - EDGE, w)] : 0u;
+                    v |= px << (8 * k);
+                }
+                wv[q] = v;
+            }
+            out = make_uint4(wv[0], wv[1], wv[2], wv[3]);
+        }
+        *reinterpret_cast<uint4*>(pyr + (size_t)b * framePyr + L.off + (size_t)Y * L.pitch + X0) = out;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ K1b
+// tabs: int2 {src index, a0 | a1 << 16}; cv::resize INTER_LINEAR 8U fixed point
+__global__ void __launch_bounds__(256) k_resize(uint8_t* __restrict__ pyr, size_t framePyr, LevelPlan S, LevelPlan D,
+                                                const int2* __restrict__ tabs, int batch) {
+    const int2* __restrict__ xt = tabs + D.xtab;
+    const int2* __restrict__ yt = tabs + D.ytab;
+    const int quadsPerRow = D.pitch >> 2;
+    const long long total = (long long)batch * D.rows * quadsPerRow;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        int xq = (int)(i % quadsPerRow);
+        long long t = i / quadsPerRow;
+        int Y = (int)(t % D.rows);
+        int b = (int)(t / D.rows);
+        const uint8_t* sroi = pyr + (size_t)b * framePyr + S.off + (size_t)EDGE * S.pitch + EDGE;
+        int y = reflect101(Y - EDGE, D.h);
+        int2 ty = __ldg(&yt[y]);
+        int b0 = (short)(ty.y & 0xffff), b1 = (short)(ty.y >> 16);
+        const uint8_t* r0 = sroi + (size_t)ty.x * S.pitch;
+        const uint8_t* r1 = r0 + S.pitch;     // row sy+1 (the ring makes it addressable; b1 == 0 when clamped)
+        uint32_t outv = 0;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            int X = (xq << 2) + k;
+            uint32_t px = 0;
+            if (X < D.w + 2 * EDGE) {
+                int x = reflect101(X - EDGE, D.w);
+                int2 tx = __ldg(&xt[x]);
+                int a0 = (short)(tx.y & 0xffff), a1 = (short)(tx.y >> 16);
+                int h0 = r0[tx.x] * a0 + r0[tx.x + 1] * a1;
+                int h1 = r1[tx.x] * a0 + r1[tx.x + 1] * a1;
+                int v = (((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2;
+                px = (uint32_t)min(max(v, 0), 255);
+            }
+            outv |= px << (8 * k);
+        }
+        *reinterpret_cast<uint32_t*>(pyr + (size_t)b * framePyr + D.off + (size_t)Y * D.pitch + (xq << 2)) = outv;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ K2 detect
+// FAST-9/16 corner score in the pixel domain: with M1 = min over the 16 arcs of (max of the arc's 9 pixels) and
+// M2 = max over arcs of (min of the arc), cornerScore = max(v - M1, M2 - v) - 1 and corner(t) <=> score >= t
+// (OpenCV's cornerScore<16> restated).  Packed evaluation: two horizontally adjacent pixels share
+// one u16x2 register and the arc windows are reduced with the native 3-input VIMNMX3.U16x2.
+static const int DET_THREADS = 256;
+static const int DET_BAND = 16;           // interior rows per band
+
+__device__ __forceinline__ uint32_t pair_at(const uint8_t* row, int x) {
+    // bytes row[x], row[x+1] -> u16x2 {lo = row[x], hi = row[x+1]}
+    return (uint32_t)row[x] | ((uint32_t)row[x + 1] << 16);
+}
+
+// scores for the pixel pair (x, x+1) on smem row pointer `c` (centre row), row stride ps
+__device__ __forceinline__ uint32_t fast_score_pair(const uint8_t* c, int ps, int minTh) {
+    uint32_t p[16];
+    p[0] = pair_at(c + 3 * ps, 0);   p[1] = pair_at(c + 3 * ps, 1);   p[2] = pair_at(c + 2 * ps, 2);
+    p[3] = pair_at(c + ps, 3);       p[4] = pair_at(c, 3);            p[5] = pair_at(c - ps, 3);
+    p[6] = pair_at(c - 2 * ps, 2);   p[7] = pair_at(c - 3 * ps, 1);   p[8] = pair_at(c - 3 * ps, 0);
+    p[9] = pair_at(c - 3 * ps, -1);  p[10] = pair_at(c - 2 * ps, -2); p[11] = pair_at(c - ps, -3);
+    p[12] = pair_at(c, -3);          p[13] = pair_at(c + ps, -3);     p[14] = pair_at(c + 2 * ps, -2);
+    p[15] = pair_at(c + 3 * ps, -1);
+    const uint32_t v = pair_at(c, 0);
+    uint32_t mn3[16], mx3[16];
+#pragma unroll
+    for (int i = 0; i < 16; i++) {
+        mn3[i] = __vimin3_u16x2(p[i], p[(i + 1) & 15], p[(i + 2) & 15]);
+        mx3[i] = __vimax3_u16x2(p[i], p[(i + 1) & 15], p[(i + 2) & 15]);
+    }
+    uint32_t M1 = 0xffffffffu, M2 = 0u;   // M1 = min over arcs of max9, M2 = max over arcs of min9
+#pragma unroll
+    for (int i = 0; i < 16; i++) {
+        uint32_t mx9 = __vimax3_u16x2(mx3[i], mx3[(i + 3) & 15], mx3[(i + 6) & 15]);
+        uint32_t mn9 = __vimin3_u16x2(mn3[i], mn3[(i + 3) & 15], mn3[(i + 6) & 15]);
+        M1 = __vminu2(M1, mx9);
+        M2 = __vmaxu2(M2, mn9);
+    }
+    // score = max(v - M1, M2 - v) - 1, clamped at 0 (values below minTh are irrelevant and zeroed)
+    uint32_t a = __vsubus2(v, M1), bq = __vsubus2(M2, v);
+    uint32_t s = __vsubus2(__vmaxu2(a, bq), 0x00010001u);
+    uint32_t lo = s & 0xffffu, hi = s >> 16;
+    lo = lo >= (uint32_t)minTh ? lo : 0u;
+    hi = hi >= (uint32_t)minTh ? hi : 0u;
+    return lo | (hi << 16);
+}
+
+__global__ void __launch_bounds__(DET_THREADS) k_detect(const uint8_t* __restrict__ pyr, size_t framePyr,
+                                                        const LevelPlan* __restrict__ levels,
+                                                        const CellPlan* __restrict__ cells, int nCellsTotal,
+                                                        uint32_t* __restrict__ cand, size_t frameCand,
+                                                        int* __restrict__ cnt7, int* __restrict__ cnt20,
+                                                        int iniTh, int minTh, int pixPitch, int* __restrict__ errflag) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    const int cellId = blockIdx.x, b = blockIdx.y;
+    const CellPlan C = cells[cellId];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    __shared__ int s_rowCnt[DET_BAND];
+    __shared__ int s_n20, s_base;
+    if (tid == 0) { s_n20 = 0; s_base = 0; }
+    const int Wc = C.x1 - C.x0, Hc = C.y1 - C.y0;
+    if (C.skipped || Wc <= 0 || Hc <= 0) {
+        if (tid == 0) { cnt7[(size_t)b * nCellsTotal + cellId] = 0; cnt20[(size_t)b * nCellsTotal + cellId] = 0; }
+        return;
+    }
+    const LevelPlan L = levels[C.level];
+    const uint8_t* roi = pyr + (size_t)b * framePyr + L.off + (size_t)EDGE * L.pitch + EDGE;
+    // smem: pixel tile [DET_BAND + 8][pixPitch] then score tile [DET_BAND + 2][scPitch], scPitch = pixPitch
+    uint8_t* pix = smem;
+    uint8_t* sc = smem + (size_t)(DET_BAND + 8) * pixPitch;
+    uint32_t* masks = reinterpret_cast<uint32_t*>(sc + (size_t)(DET_BAND + 2) * pixPitch);
+    const int maskWords = (Wc + 31) >> 5;
+    const int gx0 = (C.x0 - 4) & ~3;                 // global x of smem column 0 (4-aligned, >= x0-7)
+    const int spanW = ((C.x1 + 4 + 3) & ~3) - gx0;    // columns staged (multiple of 4)
+    uint32_t* candOut = cand + (size_t)b * frameCand + C.candBase;
+    __syncthreads();
+
+    for (int yb = C.y0; yb < C.y1; yb += DET_BAND) {
+        const int rowsB = min(DET_BAND, C.y1 - yb);
+        // ---- stage pixel rows [yb-4, yb+rowsB+4) x [gx0, gx0+spanW) (always inside the bordered plane: the
+        //      interior lies >= 16 px inside the level)
+        const int nRowsPix = rowsB + 8, wordsPerRow = spanW >> 2;
+        for (int i = tid; i < nRowsPix * wordsPerRow; i += DET_THREADS) {
+            int r = i / wordsPerRow, wq = i - r * wordsPerRow;
+            const uint8_t* g = roi + (ptrdiff_t)(yb - 4 + r) * L.pitch + gx0 + (wq << 2);
+            *reinterpret_cast<uint32_t*>(pix + r * pixPitch + (wq << 2)) = __ldg(reinterpret_cast<const uint32_t*>(g));
+        }
+        // zero the score tile (rows yb-1 .. yb+rowsB, cols x0-1 .. x1)
+        for (int i = tid; i < ((rowsB + 2) * pixPitch) >> 2; i += DET_THREADS) reinterpret_cast<uint32_t*>(sc)[i] = 0u;
+        __syncthreads();
+        // ---- scores for interior rows max(yb-1,y0) .. min(yb+rowsB, y1-1), pixel pairs along x
+        const int ys0 = max(yb - 1, C.y0), ys1 = min(yb + rowsB + 1, C.y1);
+        const int pairsPerRow = (Wc + 1) >> 1;
+        for (int i = tid; i < (ys1 - ys0) * pairsPerRow; i += DET_THREADS) {
+            int r = i / pairsPerRow, pq = i - r * pairsPerRow;
+            int y = ys0 + r, x = C.x0 + (pq << 1);
+            const uint8_t* c = pix + (y - (yb - 4)) * pixPitch + (x - gx0);
+            uint32_t s2 = fast_score_pair(c, pixPitch, minTh);
+            uint8_t* so = sc + (y - (yb - 1)) * pixPitch + (x - C.x0 + 1);
+            so[0] = (uint8_t)(s2 & 0xff);
+            if (x + 1 < C.x1) so[1] = (uint8_t)(s2 >> 16);
+        }
+        if (tid < DET_BAND) s_rowCnt[tid] = 0;
+        __syncthreads();
+        // ---- NMS (8-neighbourhood, strict, neighbours outside the cell interior are 0) -> per-row bit masks
+        for (int r = warp; r < rowsB; r += DET_THREADS / 32) {
+            const uint8_t* s1 = sc + (r + 1) * pixPitch + 1;    // score row of y = yb + r, col index = x - x0
+            int rowCount = 0, n20 = 0;
+            for (int wq = 0; wq < maskWords; wq++) {
+                int xr = (wq << 5) + lane;
+                bool keep = false;
+                if (xr < Wc) {
+                    int s = s1[xr];
+                    if (s) {
+                        const uint8_t* u = s1 - pixPitch + xr;
+                        const uint8_t* d = s1 + pixPitch + xr;
+                        keep = s > s1[xr - 1] && s > s1[xr + 1] && s > u[-1] && s > u[0] && s > u[1] && s > d[-1] &&
+                               s > d[0] && s > d[1];
+                        if (keep && s >= iniTh) n20++;
+                    }
+                }
+                uint32_t m = __ballot_sync(0xffffffffu, keep);
+                if (lane == 0) masks[r * maskWords + wq] = m;
+                rowCount += __popc(m);
+            }
+            n20 = __reduce_add_sync(0xffffffffu, n20);
+            if (lane == 0) { s_rowCnt[r] = rowCount; if (n20) atomicAdd(&s_n20, n20); }
+        }
+        __syncthreads();
+        // ---- ordered (row-major) emission
+        const int base0 = s_base;
+        for (int r = warp; r < rowsB; r += DET_THREADS / 32) {
+            int off = base0;
+            for (int q = 0; q < r; q++) off += s_rowCnt[q];
+            const uint8_t* s1 = sc + (r + 1) * pixPitch + 1;
+            for (int wq = 0; wq < maskWords; wq++) {
+                uint32_t m = masks[r * maskWords + wq];
+                if ((m >> lane) & 1u) {
+                    int xr = (wq << 5) + lane;
+                    int pos = off + __popc(m & ((1u << lane) - 1u));
+                    if (pos < C.candCap)
+                        candOut[pos] = ((uint32_t)s1[xr] << 24) | ((uint32_t)(yb + r) << 12) | (uint32_t)(C.x0 + xr);
+                    else
+                        atomicExch(errflag, GFORB_ERR_OVERFLOW);
+                }
+                off += __popc(m);
+            }
+        }
+        __syncthreads();
+        if (tid == 0) {
+            int t = 0;
+            for (int q = 0; q < rowsB; q++) t += s_rowCnt[q];
+            s_base = base0 + t;
+        }
+        __syncthreads();
+    }
+    if (tid == 0) {
+        cnt7[(size_t)b * nCellsTotal + cellId] = s_base;
+        cnt20[(size_t)b * nCellsTotal + cellId] = s_n20;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ K3b quota
+// src/ORBextractor.cc:621-628 (threshold fallback), :673-721 (quota redistribution).  One thread per (frame, level).
+__global__ void k_quota(const LevelPlan* __restrict__ levels, const CellPlan* __restrict__ cells, int nLevels,
+                        int nCellsTotal, const int* __restrict__ cnt7, const int* __restrict__ cnt20,
+                        int* __restrict__ nTotalOut, int* __restrict__ nToRetainOut, int* __restrict__ cellOutOff,
+                        int* __restrict__ lvlPre, int batch, int* __restrict__ errflag) {
+    int gi = blockIdx.x * blockDim.x + threadIdx.x;
+    if (gi >= batch * nLevels) return;
+    const int b = gi / nLevels, l = gi - b * nLevels;
+    const LevelPlan L = levels[l];
+    const size_t cb = (size_t)b * nCellsTotal + L.cellBase;
+    int* nTotal = nTotalOut + cb;
+    int* nToRetain = nToRetainOut + cb;
+    // bNoMore is kept in the sign bit of cellOutOff during the loop (scratch), rewritten as offsets at the end
+    int* noMore = cellOutOff + cb;
+    int nNoMore = 0, nToDistribute = 0;
+    for (int c = 0; c < L.nCells; c++) {
+        if (cells[L.cellBase + c].skipped) { nTotal[c] = 0; nToRetain[c] = 0; noMore[c] = 0; continue; }
+        int n20 = cnt20[cb + c], n7 = cnt7[cb + c];
+        int nKeys = (n20 <= 3) ? n7 : n20;          // "if size()<=3 -> clear; FAST(cell, 7)"
+        nTotal[c] = (n20 <= 3) ? nKeys : -nKeys - 1; // sign encodes which threshold produced the list (>=0: minTh)
+        if (nKeys > L.nfeaturesCell) { nToRetain[c] = L.nfeaturesCell; noMore[c] = 0; }
+        else { nToRetain[c] = nKeys; nToDistribute += L.nfeaturesCell - nKeys; noMore[c] = 1; nNoMore++; }
+    }
+    while (nToDistribute > 0 && nNoMore < L.nCells) {
+        int nNew = L.nfeaturesCell + (int)ceilf(__fdiv_rn((float)nToDistribute, (float)(L.nCells - nNoMore)));
+        nToDistribute = 0;
+        for (int c = 0; c < L.nCells; c++) {
+            if (!noMore[c]) {
+                int tot = nTotal[c] >= 0 ? nTotal[c] : -nTotal[c] - 1;
+                if (tot > nNew) { nToRetain[c] = nNew; }
+                else { nToRetain[c] = tot; nToDistribute += nNew - tot; noMore[c] = 1; nNoMore++; }
+            }
+        }
+    }
+    int off = 0;
+    for (int c = 0; c < L.nCells; c++) { noMore[c] = off; off += nToRetain[c]; }
+    lvlPre[(size_t)b * nLevels + l] = off;
+    if (off > L.kpCap) atomicExch(errflag, GFORB_ERR_OVERFLOW);
+}
+
+// ------------------------------------------------------------------------------------------------ K3c
+// per cell: filter the candidate list to the threshold in force (order preserved), retainBest, append at the
+// cell's offset of the level buffer.  One warp per cell; the selection itself is sequential (lane 0).
+static const int RET_WARPS = 4;
+static const int RET_SMEM = 1536;   // entries per warp kept in shared memory
+__global__ void __launch_bounds__(RET_WARPS * 32) k_cell_retain(const CellPlan* __restrict__ cells,
+                                                                const LevelPlan* __restrict__ levels, int nCellsTotal,
+                                                                uint32_t* __restrict__ cand, size_t frameCand,
+                                                                const int* __restrict__ cnt7,
+                                                                const int* __restrict__ nTotalArr,
+                                                                const int* __restrict__ nToRetainArr,
+                                                                const int* __restrict__ cellOutOff,
+                                                                uint32_t* __restrict__ lvlKp, size_t frameKp, int iniTh,
+                                                                int retainVariant) {
+    __shared__ uint32_t s_buf[RET_WARPS][RET_SMEM];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int cellId = blockIdx.x * RET_WARPS + warp, b = blockIdx.y;
+    if (cellId >= nCellsTotal) return;
+    const CellPlan C = cells[cellId];
+    const size_t ci = (size_t)b * nCellsTotal + cellId;
+    const int nKeep = nToRetainArr[ci];
+    if (nKeep <= 0) return;
+    const int enc = nTotalArr[ci];
+    const bool useIni = enc < 0;
+    const int nTot = useIni ? -enc - 1 : enc;
+    const int nAll = cnt7[ci];
+    uint32_t* list = cand + (size_t)b * frameCand + C.candBase;
+    uint32_t* work = (nTot <= RET_SMEM) ? s_buf[warp] : list;     // large lists: compact in place in global memory
+    // ordered filter (in place is safe: writes never pass reads within a 32-chunk processed after a warp sync)
+    int outN = 0;
+    for (int i0 = 0; i0 < nAll; i0 += 32) {
+        int i = i0 + lane;
+        uint32_t v = (i < nAll) ? list[i] : 0u;
+        bool keep = (i < nAll) && (!useIni || (int)(v >> 24) >= iniTh);
+        uint32_t m = __ballot_sync(0xffffffffu, keep);
+        __syncwarp();
+        if (keep) work[outN + __popc(m & ((1u << lane) - 1u))] = v;
+        outN += __popc(m);
+        __syncwarp();
+    }
+    __syncwarp();
+    if (lane == 0 && outN > nKeep) retain_best_first_n(work, outN, nKeep, retainVariant, ScoreGreater());
+    __syncwarp();
+    const int dstOff = cellOutOff[ci];
+    if (dstOff + nKeep > levels[C.level].kpCap) return;      // overflow already flagged by k_quota
+    uint32_t* dst = lvlKp + (size_t)b * frameKp + levels[C.level].kpBase + dstOff;
+    for (int i = lane; i < nKeep; i += 32) dst[i] = work[i];
+}
+
+// ------------------------------------------------------------------------------------------------ K3d
+__global__ void __launch_bounds__(128) k_level_retain(const LevelPlan* __restrict__ levels, int nLevels,
+                                                      uint32_t* __restrict__ lvlKp, size_t frameKp,
+                                                      const int* __restrict__ lvlPre, int* __restrict__ lvlCount,
+                                                      int batch, int retainVariant) {
+    const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (gw >= batch * nLevels) return;
+    const int b = gw / nLevels, l = gw - b * nLevels;
+    const LevelPlan L = levels[l];
+    int n = lvlPre[gw];
+    if (n > L.kpCap) n = L.kpCap;
+    if (lane == 0) {
+        uint32_t* v = lvlKp + (size_t)b * frameKp + L.kpBase;
+        if (n > L.nDesired) n = retain_best_first_n(v, n, L.nDesired, retainVariant, ScoreGreater());
+        lvlCount[gw] = n;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ K4 orient
+// IC_Angle on the unblurred level (src/ORBextractor.cc:131-158) + KeyPoint emission (:738-745, :865-871).
+// One warp per keypoint slot; lane v handles rows +-v of the circular patch.
+__global__ void __launch_bounds__(256) k_orient(const uint8_t* __restrict__ pyr, size_t framePyr,
+                                                const LevelPlan* __restrict__ levels, int nLevels,
+                                                const uint32_t* __restrict__ lvlKp, size_t frameKp, int kpCapTotal,
+                                                const int* __restrict__ lvlCount, GforbKeyPoint* __restrict__ kps,
+                                                int32_t* __restrict__ counts, int nfeatures) {
+    const int slot = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), b = blockIdx.y, lane = threadIdx.x & 31;
+    if (slot >= kpCapTotal) return;
+    int l = 0, base = 0;
+    while (l + 1 < nLevels && slot >= levels[l + 1].kpBase) { base += lvlCount[b * nLevels + l]; l++; }
+    const LevelPlan L = levels[l];
+    const int i = slot - L.kpBase;
+    const int n = lvlCount[b * nLevels + l];
+    if (slot == 0 && lane == 0) {
+        int tot = 0;
+        for (int q = 0; q < nLevels; q++) tot += lvlCount[b * nLevels + q];
+        counts[b] = tot;
+    }
+    if (i >= n) return;
+    const uint32_t e = lvlKp[(size_t)b * frameKp + slot];
+    const int x = e & 0xfff, y = (e >> 12) & 0xfff, score = e >> 24;
+    const uint8_t* center = pyr + (size_t)b * framePyr + L.off + (size_t)(EDGE + y) * L.pitch + EDGE + x;
+    int m10 = 0, m01 = 0;
+    if (lane <= HALF_PATCH) {
+        const int v = lane;
+        if (v == 0) {
+            for (int u = -HALF_PATCH; u <= HALF_PATCH; ++u) m10 += u * center[u];
+        } else {
+            const int d = c_umax[v];
+            int vsum = 0;
+            const uint8_t* pp = center + v * L.pitch;
+            const uint8_t* pm = center - v * L.pitch;
+            for (int u = -d; u <= d; ++u) {
+                int vp = pp[u], vm = pm[u];
+                vsum += vp - vm;
+                m10 += u * (vp + vm);
+            }
+            m01 = v * vsum;
+        }
+    }
+    m10 = __reduce_add_sync(0xffffffffu, m10);
+    m01 = __reduce_add_sync(0xffffffffu, m01);
+    if (lane == 0) {
+        GforbKeyPoint k;
+        float fx = (float)x, fy = (float)y;
+        if (l != 0) { fx = __fmul_rn(fx, L.scale); fy = __fmul_rn(fy, L.scale); }
+        k.x = fx; k.y = fy;
+        k.size = (float)L.scaledPatchSize;
+        k.angle = fast_atan2_deg((float)m01, (float)m10);
+        k.response = (float)score;
+        k.octave = l;
+        k.class_id = -1;
+        kps[(size_t)b * nfeatures + base + i] = k;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ K5 blur
+// 7x7 separable Gaussian with OpenCV's 8U fixed-point rounding: tile 128 x 32 outputs per CTA,
+// rows staged in shared memory, horizontal pass into u16, vertical pass + (acc + 2^15) >> 16.
+static const int BL_TW = 128, BL_TH = 32, BL_THREADS = 256;
+static const int BL_PW = BL_TW + 8;       // staged width (x0-4 .. x0+131), multiple of 4
+__global__ void __launch_bounds__(BL_THREADS) k_blur(const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blr,
+                                                     size_t framePyr, const LevelPlan* __restrict__ levels,
+                                                     const BlurTile* __restrict__ tiles, int variant) {
+    __shared__ __align__(16) uint8_t s_in[(BL_TH + 6) * BL_PW];
+    __shared__ __align__(16) uint16_t s_h[(BL_TH + 6) * BL_TW];
+    const BlurTile T = tiles[blockIdx.x];
+    const int b = blockIdx.y, tid = threadIdx.x;
+    const LevelPlan L = levels[T.level];
+    const uint8_t* plane = pyr + (size_t)b * framePyr + L.off;
+    // stage rows y0-3 .. y0+BL_TH+2, cols x0-4 .. x0+BL_TW+3 (plane coordinates = ROI + 16)
+    const int wordsPerRow = BL_PW >> 2;
+    for (int i = tid; i < (BL_TH + 6) * wordsPerRow; i += BL_THREADS) {
+        int r = i / wordsPerRow, wq = i - r * wordsPerRow;
+        int py = T.y0 - 3 + r + EDGE, px = T.x0 - 4 + (wq << 2) + EDGE;
+        uint32_t v = 0;
+        if (py < L.rows && px + 3 < L.pitch) v = __ldg(reinterpret_cast<const uint32_t*>(plane + (size_t)py * L.pitch + px));
+        *reinterpret_cast<uint32_t*>(s_in + r * BL_PW + (wq << 2)) = v;
+    }
+    __syncthreads();
+    int k[7];
+#pragma unroll
+    for (int i = 0; i < 7; i++) k[i] = c_gauss[variant][i];
+    for (int i = tid; i < (BL_TH + 6) * BL_TW; i += BL_THREADS) {
+        int r = i / BL_TW, x = i - r * BL_TW;
+        const uint8_t* p = s_in + r * BL_PW + x + 1;     // p[0] = column x-3
+        int s = 0;
+#pragma unroll
+        for (int q = 0; q < 7; q++) s += k[q] * p[q];
+        s_h[i] = (uint16_t)s;
+    }
+    __syncthreads();
+    uint8_t* oroi = blr + (size_t)b * framePyr + L.off + (size_t)EDGE * L.pitch + EDGE;
+    for (int i = tid; i < BL_TH * (BL_TW >> 2); i += BL_THREADS) {
+        int r = i / (BL_TW >> 2), xq = i - r * (BL_TW >> 2);
+        int y = T.y0 + r, x = T.x0 + (xq << 2);
+        if (y >= L.h || x >= L.w) continue;
+        uint32_t outv = 0;
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+            int s = 0;
+#pragma unroll
+            for (int q = 0; q < 7; q++) s += k[q] * s_h[(r + q) * BL_TW + (xq << 2) + c];
+            int v = (s + 32768) >> 16;
+            outv |= (uint32_t)min(max(v, 0), 255) << (8 * c);
+        }
+        uint8_t* o = oroi + (size_t)y * L.pitch + x;
+        if (x + 3 < L.w) *reinterpret_cast<uint32_t*>(o) = outv;
+        else for (int c = 0; c < 4 && x + c < L.w; c++) o[c] = (uint8_t)(outv >> (8 * c));
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ K6 describe
+// src/ORBextractor.cc:161-201.  Warp per keypoint, lane j builds descriptor byte j (8 tests, 16 taps).  Taps inside
+// the level ROI read the blurred plane, taps in the 16-px ring read the unblurred reflect-101 ring (the reference
+// blurs the ROI in place and leaves the ring untouched).
+__global__ void __launch_bounds__(256) k_describe(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ blr,
+                                                  size_t framePyr, const LevelPlan* __restrict__ levels, int nLevels,
+                                                  const uint32_t* __restrict__ lvlKp, size_t frameKp, int kpCapTotal,
+                                                  const int* __restrict__ lvlCount,
+                                                  const GforbKeyPoint* __restrict__ kps, uint8_t* __restrict__ desc,
+                                                  int nfeatures) {
+    const int slot = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), b = blockIdx.y, lane = threadIdx.x & 31;
+    if (slot >= kpCapTotal) return;
+    int l = 0, base = 0;
+    while (l + 1 < nLevels && slot >= levels[l + 1].kpBase) { base += lvlCount[b * nLevels + l]; l++; }
+    const LevelPlan L = levels[l];
+    const int i = slot - L.kpBase;
+    if (i >= lvlCount[b * nLevels + l]) return;
+    const uint32_t e = lvlKp[(size_t)b * frameKp + slot];
+    const int cx = e & 0xfff, cy = (e >> 12) & 0xfff;
+    const size_t oi = (size_t)b * nfeatures + base + i;
+    const float factorPI = (float)(3.14159265358979323846 / 180.f);
+    const float angle = __fmul_rn(kps[oi].angle, factorPI);
+    const float a = glibc_cosf(angle), bb = glibc_sinf(angle);
+    const uint8_t* P = pyr + (size_t)b * framePyr + L.off + (size_t)EDGE * L.pitch + EDGE;
+    const uint8_t* B = blr + (size_t)b * framePyr + L.off + (size_t)EDGE * L.pitch + EDGE;
+    int val = 0;
+#pragma unroll
+    for (int t = 0; t < 8; t++) {
+        const signed char* pt = c_pattern + (lane * 8 + t) * 4;
+        int tv[2];
+#pragma unroll
+        for (int q = 0; q < 2; q++) {
+            float px = (float)pt[2 * q], py = (float)pt[2 * q + 1];
+            int iy = cv_round(__fadd_rn(__fmul_rn(px, bb), __fmul_rn(py, a)));
+            int ix = cv_round(__fsub_rn(__fmul_rn(px, a), __fmul_rn(py, bb)));
+            int x = cx + ix, y = cy + iy;
+            const uint8_t* src = (x >= 0 && x < L.w && y >= 0 && y < L.h) ? B : P;
+            tv[q] = src[(ptrdiff_t)y * L.pitch + x];
+        }
+        val |= (tv[0] < tv[1]) << t;
+    }
+    desc[oi * 32 + lane] = (uint8_t)val;
+}
+
+// ================================================================================================ host side
+struct Stage { const char* name; cudaEvent_t e0, e1; float ms; };
+
+}  // namespace gforb
+
+using namespace gforb;
+
+struct GforbExtractor {
+    GforbExtractorConfig cfg;
+    int device;
+    cudaStream_t ownStream;
+    // ctor tables (reference src/ORBextractor.cc:469-494)
+    std::vector<float> scale, invScale;
+    std::vector<int> featPerLevel;
+    // plan for the current image size
+    int planW = -1, planH = -1;
+    std::vector<LevelPlan> levels;
+    std::vector<CellPlan> cells;
+    std::vector<BlurTile> tiles;
+    size_t framePyr = 0, frameCand = 0, frameKp = 0;
+    int kpCapTotal = 0, nCellsTotal = 0, detSmem = 0, detPixPitch = 0;
+    // device buffers
+    uint8_t *d_img = nullptr, *d_pyr = nullptr, *d_blr = nullptr, *d_desc = nullptr;
+    GforbKeyPoint* d_kps = nullptr;
+    int32_t* d_counts = nullptr;
+    uint32_t *d_cand = nullptr, *d_lvlKp = nullptr;
+    int *d_cnt7 = nullptr, *d_cnt20 = nullptr, *d_nTotal = nullptr, *d_nToRetain = nullptr, *d_cellOff = nullptr;
+    int *d_lvlPre = nullptr, *d_lvlCount = nullptr, *d_err = nullptr;
+    LevelPlan* d_levels = nullptr;
+    CellPlan* d_cells = nullptr;
+    BlurTile* d_tiles = nullptr;
+    int2* d_tabs = nullptr;
+    size_t capPyr = 0, capCand = 0, capKp = 0, capCells = 0, capTiles = 0, capTabs = 0, capImg = 0;
+    int lastBatch = 0, lastLaunches = 0, numSMs = 148;
+    bool profiling = false;
+    std::vector<Stage> stages;
+};
+
+static int build_ctor_tables(GforbExtractor* E) {
+    // reference src/ORBextractor.cc:469-494; `scaleFactor` member is a double holding the float argument
+    const GforbExtractorConfig& c = E->cfg;
+    const double scaleFactor = (double)c.scaleFactor;
+    E->scale.assign(c.nlevels, 1.f);
+    E->invScale.assign(c.nlevels, 1.f);
+    for (int i = 1; i < c.nlevels; i++) E->scale[i] = (float)(E->scale[i - 1] * scaleFactor);
+    float invScaleFactor = (float)(1.0f / scaleFactor);
+    for (int i = 1; i < c.nlevels; i++) E->invScale[i] = E->invScale[i - 1] * invScaleFactor;
+    E->featPerLevel.assign(c.nlevels, 0);
+    float factor = (float)(1.0 / scaleFactor);
+    float nDesired = c.nfeatures * (1 - factor) / (1 - (float)pow((double)factor, (double)c.nlevels));
+    int sum = 0;
+    for (int l = 0; l < c.nlevels - 1; l++) {
+        E->featPerLevel[l] = (int)lrintf(nDesired);
+        sum += E->featPerLevel[l];
+        nDesired *= factor;
+    }
+    E->featPerLevel[c.nlevels - 1] = std::max(c.nfeatures - sum, 0);
+    return GFORB_OK;
+}
+
+static void linear_table(int ssize, int dsize, std::vector<int2>& out) {
+    // cv::resize INTER_LINEAR coefficient generation
+    double scale = 1.0 / ((double)dsize / ssize);
+    for (int d = 0; d < dsize; d++) {
+        float f = (float)((d + 0.5) * scale - 0.5);
+        int s = (int)floorf(f);
+        f -= s;
+        if (s < 0) { s = 0; f = 0; }
+        if (s >= ssize - 1) { s = ssize - 1; f = 0; }
+        int a0 = (short)lrintf((1.f - f) * 2048.f), a1 = (short)lrintf(f * 2048.f);
+        out.push_back(make_int2(s, (a0 & 0xffff) | (a1 << 16)));
+    }
+}
+
+template <class T>
+static int ensure(T** p, size_t* cap, size_t need) {
+    if (need <= *cap && *p) return GFORB_OK;
+    if (*p) cudaFree(*p);
+    *p = nullptr;
+    GF_CUDA_OK(cudaMalloc((void**)p, need * sizeof(T)));
+    *cap = need;
+    return GFORB_OK;
+}
+
+// Level / cell geometry exactly as ComputePyramid (:926-927) and ComputeKeyPoints (:540-612) derive it.
+static int build_plan(GforbExtractor* E, int w, int h) {
+    const GforbExtractorConfig& c = E->cfg;
+    const int nl = c.nlevels;
+    E->levels.assign(nl, LevelPlan());
+    E->cells.clear();
+    E->tiles.clear();
+    std::vector<int2> tabs;
+    size_t off = 0;
+    int kpBase = 0, candBase = 0, maxCellW = 0;
+    const float imageRatio = (float)w / h;
+    for (int l = 0; l < nl; l++) {
+        LevelPlan& L = E->levels[l];
+        L.w = (int)lrintf((float)w * E->invScale[l]);
+        L.h = (int)lrintf((float)h * E->invScale[l]);
+        if (L.w <= 2 * EDGE || L.h <= 2 * EDGE || L.w > 4095 || L.h > 4095) return GFORB_ERR_GEOMETRY;
+        L.pitch = (L.w + 2 * EDGE + 127) & ~127;
+        L.rows = L.h + 2 * EDGE;
+        L.off = off;
+        off += (size_t)L.pitch * L.rows;
+        off = (off + 255) & ~(size_t)255;
+        L.scale = E->scale[l];
+        L.scaledPatchSize = (int)(31 * E->scale[l]);
+        L.nDesired = E->featPerLevel[l];
+        L.levelCols = (int)sqrtf((float)L.nDesired / (5 * imageRatio));
+        L.levelRows = (int)(imageRatio * L.levelCols);
+        if (L.levelCols <= 0 || L.levelRows <= 0) return GFORB_ERR_GEOMETRY;
+        const int minB = EDGE, maxBX = L.w - EDGE, maxBY = L.h - EDGE;
+        const int W = maxBX - minB, H = maxBY - minB;
+        L.cellW = (int)ceilf((float)W / L.levelCols);
+        L.cellH = (int)ceilf((float)H / L.levelRows);
+        L.nCells = L.levelRows * L.levelCols;
+        L.nfeaturesCell = (int)ceilf((float)L.nDesired / L.nCells);
+        L.cellBase = (int)E->cells.size();
+        L.kpBase = kpBase;
+        L.kpCap = 2 * L.nDesired + L.nCells + 64;
+        kpBase += L.kpCap;
+        if (l > 0) {
+            L.xtab = (int)tabs.size(); linear_table(E->levels[l - 1].w, L.w, tabs);
+            L.ytab = (int)tabs.size(); linear_table(E->levels[l - 1].h, L.h, tabs);
+        } else { L.xtab = L.ytab = 0; }
+        for (int i = 0; i < L.levelRows; i++) {
+            const int iniY = minB + i * L.cellH - 3;
+            float hY = (float)(L.cellH + 6);
+            bool rowSkipped = false;
+            if (i == L.levelRows - 1) { hY = (float)(maxBY + 3 - iniY); if (hY <= 0) rowSkipped = true; }
+            for (int j = 0; j < L.levelCols; j++) {
+                const int iniX = minB + j * L.cellW - 3;
+                float hX = (float)(L.cellW + 6);
+                bool skipped = rowSkipped;
+                if (j == L.levelCols - 1) { hX = (float)(maxBX + 3 - iniX); if (hX <= 0) skipped = true; }
+                CellPlan C;
+                C.level = l; C.skipped = skipped ? 1 : 0;
+                C.x0 = C.y0 = C.x1 = C.y1 = 0;
+                if (!skipped) {
+                    int x1 = iniX + (int)hX, y1 = iniY + (int)hY;            // cell image = [iniX,x1) x [iniY,y1)
+                    if (iniX < 0 || iniY < 0 || x1 > L.w || y1 > L.h) return GFORB_ERR_GEOMETRY;  // cv::Mat range assert
+                    C.x0 = iniX + 3; C.y0 = iniY + 3; C.x1 = x1 - 3; C.y1 = y1 - 3;                // FAST's 3-px margin
+                    if (C.x1 < C.x0) C.x1 = C.x0;
+                    if (C.y1 < C.y0) C.y1 = C.y0;
+                }
+                const int Wc = C.x1 - C.x0, Hc = C.y1 - C.y0;
+                C.candBase = candBase;
+                C.candCap = ((Wc + 1) / 2) * ((Hc + 1) / 2);
+                candBase += C.candCap;
+                maxCellW = std::max(maxCellW, Wc);
+                E->cells.push_back(C);
+            }
+        }
+        for (int y0 = 0; y0 < L.h; y0 += BL_TH)
+            for (int x0 = 0; x0 < L.w; x0 += BL_TW) E->tiles.push_back(BlurTile{l, x0, y0});
+    }
+    E->framePyr = off;
+    E->frameCand = (size_t)candBase + 4;
+    E->frameKp = (size_t)kpBase;
+    E->kpCapTotal = kpBase;
+    E->nCellsTotal = (int)E->cells.size();
+    E->detPixPitch = (maxCellW + 16 + 3) & ~3;
+    E->detSmem = (DET_BAND + 8) * E->detPixPitch + (DET_BAND + 2) * E->detPixPitch + DET_BAND * ((maxCellW + 31) / 32) * 4 + 16;
+    if (E->detSmem > 200 * 1024) return GFORB_ERR_CAPACITY;
+    const size_t B = (size_t)c.max_batch;
+    int rc;
+    if ((rc = ensure(&E->d_pyr, &E->capPyr, E->framePyr * B))) return rc;
+    { size_t cap2 = 0; uint8_t* old = E->d_blr; if (old) cudaFree(old); E->d_blr = nullptr; if ((rc = ensure(&E->d_blr, &cap2, E->framePyr * B))) return rc; }
+    if ((rc = ensure(&E->d_cand, &E->capCand, E->frameCand * B))) return rc;
+    if ((rc = ensure(&E->d_lvlKp, &E->capKp, E->frameKp * B))) return rc;
+    size_t nc = (size_t)E->nCellsTotal * B;
+    if (nc > E->capCells) {
+        for (int** p : {&E->d_cnt7, &E->d_cnt20, &E->d_nTotal, &E->d_nToRetain, &E->d_cellOff}) { if (*p) cudaFree(*p); *p = nullptr; }
+        for (int** p : {&E->d_cnt7, &E->d_cnt20, &E->d_nTotal, &E->d_nToRetain, &E->d_cellOff}) GF_CUDA_OK(cudaMalloc((void**)p, nc * sizeof(int)));
+        E->capCells = nc;
+    }
+    if (E->d_levels) cudaFree(E->d_levels);
+    if (E->d_cells) cudaFree(E->d_cells);
+    if (E->d_tiles) cudaFree(E->d_tiles);
+    if (E->d_tabs) cudaFree(E->d_tabs);
+    GF_CUDA_OK(cudaMalloc((void**)&E->d_levels, sizeof(LevelPlan) * nl));
+    GF_CUDA_OK(cudaMalloc((void**)&E->d_cells, sizeof(CellPlan) * E->cells.size()));
+    GF_CUDA_OK(cudaMalloc((void**)&E->d_tiles, sizeof(BlurTile) * E->tiles.size()));
+    GF_CUDA_OK(cudaMalloc((void**)&E->d_tabs, sizeof(int2) * std::max<size_t>(tabs.size(), 1)));
+    GF_CUDA_OK(cudaMemcpy(E->d_levels, E->levels.data(), sizeof(LevelPlan) * nl, cudaMemcpyHostToDevice));
+    GF_CUDA_OK(cudaMemcpy(E->d_cells, E->cells.data(), sizeof(CellPlan) * E->cells.size(), cudaMemcpyHostToDevice));
+    GF_CUDA_OK(cudaMemcpy(E->d_tiles, E->tiles.data(), sizeof(BlurTile) * E->tiles.size(), cudaMemcpyHostToDevice));
+    if (!tabs.empty()) GF_CUDA_OK(cudaMemcpy(E->d_tabs, tabs.data(), sizeof(int2) * tabs.size(), cudaMemcpyHostToDevice));
+    GF_CUDA_OK(cudaFuncSetAttribute(k_detect, cudaFuncAttributeMaxDynamicSharedMemorySize, E->detSmem));
+    E->planW = w; E->planH = h;
+    return GFORB_OK;
+}
+
+extern "C" {
+
+const char* gforb_version(void) { return "gforb-b200 0.1 (sm_100a)"; }
+
+int gforb_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+    return n;
+}
+
+int gforb_extractor_create(const GforbExtractorConfig* cfg, GforbExtractor** out) {
+    if (!cfg || !out) return GFORB_ERR_ARG;
+    *out = nullptr;
+    if (cfg->nfeatures <= 0 || cfg->nlevels <= 0 || cfg->nlevels > MAX_LEVELS || !(cfg->scaleFactor > 1.0f) ||
+        cfg->scoreType != 1 || cfg->max_batch <= 0 || cfg->max_width <= 0 || cfg->max_height <= 0 ||
+        cfg->blur_variant < 0 || cfg->blur_variant > 1 || cfg->retain_variant < 0 || cfg->retain_variant > 1 ||
+        cfg->minThFAST < 1 || cfg->iniThFAST < cfg->minThFAST || cfg->iniThFAST > 254)
+        return GFORB_ERR_ARG;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0 || cfg->device < 0 || cfg->device >= ndev) {
+        fprintf(stderr, "[gforb] no usable CUDA device (requested %d of %d): the B200 path has no CPU fallback\n", cfg->device, ndev);
+        return GFORB_ERR_CUDA;
+    }
+    GF_CUDA_OK(cudaSetDevice(cfg->device));
+    GforbExtractor* E = new GforbExtractor();
+    E->cfg = *cfg;
+    E->device = cfg->device;
+    GF_CUDA_OK(cudaStreamCreateWithFlags(&E->ownStream, cudaStreamNonBlocking));
+    cudaDeviceGetAttribute(&E->numSMs, cudaDevAttrMultiProcessorCount, cfg->device);
+    build_ctor_tables(E);
+    GF_CUDA_OK(cudaMemcpyToSymbol(c_pattern, h_pattern, sizeof(h_pattern)));
+    {   // umax (src/ORBextractor.cc:500-517)
+        int umax[16];
+        int v, v0, vmax = (int)floorf(HALF_PATCH * sqrtf(2.f) / 2 + 1), vmin = (int)ceilf(HALF_PATCH * sqrtf(2.f) / 2);
+        const double hp2 = HALF_PATCH * HALF_PATCH;
+        for (v = 0; v <= vmax; ++v) umax[v] = (int)lrint(sqrt(hp2 - v * v));
+        for (v = HALF_PATCH, v0 = 0; v >= vmin; --v) {
+            while (umax[v0] == umax[v0 + 1]) ++v0;
+            umax[v] = v0;
+            ++v0;
+        }
+        GF_CUDA_OK(cudaMemcpyToSymbol(c_umax, umax, sizeof(umax)));
+    }
+    size_t B = cfg->max_batch;
+    GF_CUDA_OK(cudaMalloc((void**)&E->d_kps, B * cfg->nfeatures * sizeof(GforbKeyPoint)));
+    GF_CUDA_OK(cudaMalloc((void**)&E->d_desc, B * cfg->nfeatures * 32));
+    GF_CUDA_OK(cudaMalloc((void**)&E->d_counts, B * sizeof(int32_t)));
+    GF_CUDA_OK(cudaMalloc((void**)&E->d_lvlPre, B * cfg->nlevels * sizeof(int)));
+    GF_CUDA_OK(cudaMalloc((void**)&E->d_lvlCount, B * cfg->nlevels * sizeof(int)));
+    GF_CUDA_OK(cudaMalloc((void**)&E->d_err, sizeof(int)));
+    GF_CUDA_OK(cudaMemset(E->d_err, 0, sizeof(int)));
+    E->capImg = (size_t)cfg->max_width * cfg->max_height * B;
+    GF_CUDA_OK(cudaMalloc((void**)&E->d_img, E->capImg));
+    int rc = build_plan(E, cfg->max_width, cfg->max_height);
+    if (rc != GFORB_OK) { gforb_extractor_destroy(E); return rc; }
+    *out = E;
+    return GFORB_OK;
+}
+
+int gforb_extractor_destroy(GforbExtractor* E) {
+    if (!E) return GFORB_ERR_ARG;
+    cudaSetDevice(E->device);
+    void* ptrs[] = {E->d_img, E->d_pyr, E->d_blr, E->d_desc, E->d_kps, E->d_counts, E->d_cand, E->d_lvlKp, E->d_cnt7,
+                    E->d_cnt20, E->d_nTotal, E->d_nToRetain, E->d_cellOff, E->d_lvlPre, E->d_lvlCount, E->d_err,
+                    E->d_levels, E->d_cells, E->d_tiles, E->d_tabs};
+    for (void* p : ptrs) if (p) cudaFree(p);
+    for (auto& s : E->stages) { cudaEventDestroy(s.e0); cudaEventDestroy(s.e1); }
+    if (E->ownStream) cudaStreamDestroy(E->ownStream);
+    delete E;
+    return GFORB_OK;
+}
+
+int gforb_extractor_levels(const GforbExtractor* E) { return E ? E->cfg.nlevels : GFORB_ERR_ARG; }
+float gforb_extractor_scale_factor(const GforbExtractor* E) { return E ? E->cfg.scaleFactor : 0.f; }
+int gforb_extractor_tables(const GforbExtractor* E, float* sf, int32_t* fpl) {
+    if (!E) return GFORB_ERR_ARG;
+    for (int i = 0; i < E->cfg.nlevels; i++) { if (sf) sf[i] = E->scale[i]; if (fpl) fpl[i] = E->featPerLevel[i]; }
+    return GFORB_OK;
+}
+int gforb_extractor_last_launches(const GforbExtractor* E) { return E ? E->lastLaunches : GFORB_ERR_ARG; }
+int gforb_extractor_set_profiling(GforbExtractor* E, int on) { if (!E) return GFORB_ERR_ARG; E->profiling = on != 0; return GFORB_OK; }
+int gforb_extractor_stage_time(const GforbExtractor* E, int i, const char** name, float* ms) {
+    if (!E) return GFORB_ERR_ARG;
+    if (i >= 0 && i < (int)E->stages.size()) { if (name) *name = E->stages[i].name; if (ms) *ms = E->stages[i].ms; }
+    return (int)E->stages.size();
+}
+
+int gforb_extract(GforbExtractor* E, const uint8_t* images, int w, int h, int stride, size_t frame_stride, int batch,
+                  GforbKeyPoint* keypoints, uint8_t* descriptors, int32_t* counts, int flags, void* stream_) {
+    if (!E) return GFORB_ERR_ARG;
+    if (batch == 0 || images == nullptr || w <= 0 || h <= 0) return GFORB_OK;     // empty image: silent return (:772)
+    if (batch < 0 || stride < w) return GFORB_ERR_ARG;
+    if (batch > E->cfg.max_batch || (size_t)w * h > (size_t)E->cfg.max_width * E->cfg.max_height) return GFORB_ERR_CAPACITY;
+    GF_CUDA_OK(cudaSetDevice(E->device));
+    cudaStream_t st = (cudaStream_t)stream_;   // NULL = the CUDA default stream
+    if (w != E->planW || h != E->planH) {
+        GF_CUDA_OK(cudaStreamSynchronize(st));
+        int rc = build_plan(E, w, h);
+        if (rc != GFORB_OK) { E->planW = E->planH = -1; return rc; }
+    }
+    const GforbExtractorConfig& c = E->cfg;
+    const int nl = c.nlevels;
+    const uint8_t* dimg = images;
+    int dstride = stride;
+    size_t dfs = frame_stride;
+    if (!(flags & GFORB_IN_DEVICE)) {
+        dstride = w; dfs = (size_t)w * h;
+        if (frame_stride == (size_t)stride * h)
+            GF_CUDA_OK(cudaMemcpy2DAsync(E->d_img, w, images, stride, w, (size_t)h * batch, cudaMemcpyHostToDevice, st));
+        else
+            for (int b = 0; b < batch; b++)
+                GF_CUDA_OK(cudaMemcpy2DAsync(E->d_img + (size_t)b * dfs, w, images + (size_t)b * frame_stride, stride, w, h, cudaMemcpyHostToDevice, st));
+        dimg = E->d_img;
+    }
+    GforbKeyPoint* dk = (flags & GFORB_OUT_DEVICE) ? keypoints : E->d_kps;
+    uint8_t* dd = (flags & GFORB_OUT_DEVICE) ? descriptors : E->d_desc;
+    int32_t* dc = (flags & GFORB_OUT_DEVICE) ? counts : E->d_counts;
+    if (!dk || !dd || !dc) return GFORB_ERR_ARG;
+
+    int launches = 0;
+    size_t si = 0;
+    auto begin = [&](const char* name) {
+        if (!E->profiling) return;
+        if (si >= E->stages.size()) { Stage s; s.name = name; s.ms = 0; cudaEventCreate(&s.e0); cudaEventCreate(&s.e1); E->stages.push_back(s); }
+        E->stages[si].name = name;
+        cudaEventRecord(E->stages[si].e0, st);
+    };
+    auto end = [&]() { if (!E->profiling) return; cudaEventRecord(E->stages[si].e1, st); si++; };
+    const int gsBlocks = E->numSMs * 8;
+
+    begin("pyramid");
+    k_border0<<<gsBlocks, 256, 0, st>>>(dimg, w, h, dstride, dfs, E->d_pyr, E->framePyr, E->levels[0], batch); launches++;
+    for (int l = 1; l < nl; l++) {
+        k_resize<<<gsBlocks, 256, 0, st>>>(E->d_pyr, E->framePyr, E->levels[l - 1], E->levels[l], E->d_tabs, batch); launches++;
+    }
+    end();
+    begin("detect");
+    k_detect<<<dim3(E->nCellsTotal, batch), DET_THREADS, E->detSmem, st>>>(
+        E->d_pyr, E->framePyr, E->d_levels, E->d_cells, E->nCellsTotal, E->d_cand, E->frameCand, E->d_cnt7, E->d_cnt20,
+        c.iniThFAST, c.minThFAST, E->detPixPitch, E->d_err); launches++;
+    end();
+    begin("select");
+    k_quota<<<(batch * nl + 127) / 128, 128, 0, st>>>(E->d_levels, E->d_cells, nl, E->nCellsTotal, E->d_cnt7, E->d_cnt20,
+                                                     E->d_nTotal, E->d_nToRetain, E->d_cellOff, E->d_lvlPre, batch, E->d_err); launches++;
+    k_cell_retain<<<dim3((E->nCellsTotal + RET_WARPS - 1) / RET_WARPS, batch), RET_WARPS * 32, 0, st>>>(
+        E->d_cells, E->d_levels, E->nCellsTotal, E->d_cand, E->frameCand, E->d_cnt7, E->d_nTotal, E->d_nToRetain,
+        E->d_cellOff, E->d_lvlKp, E->frameKp, c.iniThFAST, c.retain_variant); launches++;
+    k_level_retain<<<(batch * nl * 32 + 127) / 128, 128, 0, st>>>(E->d_levels, nl, E->d_lvlKp, E->frameKp, E->d_lvlPre,
+                                                                  E->d_lvlCount, batch, c.retain_variant); launches++;
+    end();
+    begin("orient");
+    k_orient<<<dim3((E->kpCapTotal + 7) / 8, batch), 256, 0, st>>>(E->d_pyr, E->framePyr, E->d_levels, nl, E->d_lvlKp,
+                                                                    E->frameKp, E->kpCapTotal, E->d_lvlCount, dk, dc, c.nfeatures); launches++;
+    end();
+    begin("blur");
+    k_blur<<<dim3((unsigned)E->tiles.size(), batch), BL_THREADS, 0, st>>>(E->d_pyr, E->d_blr, E->framePyr, E->d_levels, E->d_tiles, c.blur_variant); launches++;
+    end();
+    begin("describe");
+    k_describe<<<dim3((E->kpCapTotal + 7) / 8, batch), 256, 0, st>>>(E->d_pyr, E->d_blr, E->framePyr, E->d_levels, nl, E->d_lvlKp,
+                                                                      E->frameKp, E->kpCapTotal, E->d_lvlCount, dk, dd, c.nfeatures); launches++;
+    end();
+    GF_CUDA_OK(cudaGetLastError());
+    E->lastLaunches = launches;
+    E->lastBatch = batch;
+    if (!(flags & GFORB_OUT_DEVICE)) {
+        if (!keypoints || !descriptors || !counts) return GFORB_ERR_ARG;
+        GF_CUDA_OK(cudaMemcpyAsync(keypoints, dk, (size_t)batch * c.nfeatures * sizeof(GforbKeyPoint), cudaMemcpyDeviceToHost, st));
+        GF_CUDA_OK(cudaMemcpyAsync(descriptors, dd, (size_t)batch * c.nfeatures * 32, cudaMemcpyDeviceToHost, st));
+        GF_CUDA_OK(cudaMemcpyAsync(counts, dc, (size_t)batch * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    }
+    if (!(flags & GFORB_ASYNC) || !(flags & GFORB_OUT_DEVICE)) {
+        GF_CUDA_OK(cudaStreamSynchronize(st));
+        int err = 0;
+        GF_CUDA_OK(cudaMemcpy(&err, E->d_err, sizeof(int), cudaMemcpyDeviceToHost));
+        if (err) { cudaMemset(E->d_err, 0, sizeof(int)); return err; }
+        if (E->profiling) for (auto& s : E->stages) cudaEventElapsedTime(&s.ms, s.e0, s.e1);
+    }
+    return GFORB_OK;
+}
+
+int gforb_extractor_debug_level(GforbExtractor* E, int b, int level, int which, uint8_t* dst, size_t dst_bytes, int* w,
+                                int* hgt, int* pitch) {
+    if (!E || level < 0 || level >= E->cfg.nlevels || b < 0 || b >= E->lastBatch) return GFORB_ERR_ARG;
+    const LevelPlan& L = E->levels[level];
+    if (w) *w = L.w;
+    if (hgt) *hgt = L.h;
+    if (pitch) *pitch = L.pitch;
+    size_t bytes = (size_t)L.pitch * L.rows;
+    if (dst) {
+        if (dst_bytes < bytes) return GFORB_ERR_CAPACITY;
+        GF_CUDA_OK(cudaSetDevice(E->device));
+        GF_CUDA_OK(cudaDeviceSynchronize());
+        GF_CUDA_OK(cudaMemcpy(dst, (which ? E->d_blr : E->d_pyr) + (size_t)b * E->framePyr + L.off, bytes, cudaMemcpyDeviceToHost));
+    }
+    return GFORB_OK;
+}
+
+}  // extern "C"
