@@ -24,6 +24,27 @@ class GforbError(RuntimeError):
         self.code = code
 
 
+class FrameSet(C.Structure):
+    _fields_ = [("keypoints", C.c_void_p), ("descriptors", C.c_void_p), ("counts", C.c_void_p), ("kp_stride", C.c_int32),
+                ("min_x", C.c_int32), ("max_x", C.c_int32), ("min_y", C.c_int32), ("max_y", C.c_int32)]
+
+
+class MapPointSet(C.Structure):
+    _fields_ = [("proj_x", C.c_void_p), ("proj_y", C.c_void_p), ("scale_level", C.c_void_p), ("view_cos", C.c_void_p),
+                ("flags", C.c_void_p), ("descriptors", C.c_void_p), ("counts", C.c_void_p), ("mp_stride", C.c_int32)]
+
+
+class MatcherConfig(C.Structure):
+    _fields_ = [("max_batch", C.c_int32), ("max_keypoints", C.c_int32), ("max_queries", C.c_int32),
+                ("cand_pool", C.c_int32), ("nlevels", C.c_int32), ("scaleFactor", C.c_float), ("device", C.c_int32)]
+
+
+class ObsConfig(C.Structure):
+    _fields_ = [("fu", C.c_double), ("fv", C.c_double), ("nRows", C.c_int32), ("nCols", C.c_int32), ("Cx", C.c_double),
+                ("Cy", C.c_double), ("k1", C.c_double), ("k2", C.c_double), ("dx", C.c_double), ("dy", C.c_double),
+                ("max_batch", C.c_int32), ("max_points", C.c_int32), ("device", C.c_int32)]
+
+
 class ExtractorConfig(C.Structure):
     _fields_ = [("nfeatures", C.c_int32), ("scaleFactor", C.c_float), ("nlevels", C.c_int32), ("scoreType", C.c_int32),
                 ("iniThFAST", C.c_int32), ("minThFAST", C.c_int32), ("blur_variant", C.c_int32),
@@ -54,8 +75,46 @@ def lib() -> C.CDLL:
         L.gforb_extractor_last_launches.argtypes = [vp]
         L.gforb_extractor_set_profiling.argtypes = [vp, i32]
         L.gforb_extractor_stage_time.argtypes = [vp, i32, C.POINTER(C.c_char_p), C.POINTER(C.c_float)]
+        f32, f64, i64, u32 = C.c_float, C.c_double, C.c_int64, C.c_uint32
+        FS, MS = C.POINTER(FrameSet), C.POINTER(MapPointSet)
+        L.gforb_matcher_create.argtypes = [C.POINTER(MatcherConfig), C.POINTER(vp)]
+        L.gforb_matcher_destroy.argtypes = [vp]
+        L.gforb_matcher_last_launches.argtypes = [vp]
+        L.gforb_descriptor_distance.argtypes = [vp, vp, vp, i32, vp, i32, vp]
+        L.gforb_features_in_area.argtypes = [vp, FS, i32, i32, vp, vp, vp, vp, vp, i32, vp, i32, vp, i32, vp]
+        L.gforb_search_for_initialization.argtypes = [vp, FS, FS, i32, vp, vp, vp, i32, f32, i32, i32, vp]
+        L.gforb_search_by_projection.argtypes = [vp, FS, MS, i32, f32, f32, vp, vp, vp, i32, vp]
+        L.gforb_search_by_projection_frames.argtypes = [vp, FS, FS, i32, vp, vp, vp, vp, f32, f32, f32, f32, f32, f32,
+                                                        i32, vp, vp, vp, i32, vp]
+        L.gforb_window_search.argtypes = [vp, FS, FS, i32, vp, i32, i32, i32, f32, i32, vp, vp, i32, vp]
+        L.gforb_allpairs_top2.argtypes = [vp, vp, i32, vp, i64, i64, vp, i32, vp]
+        L.gforb_top2_merge.argtypes = [vp, vp, i32, i32, vp, i32, vp]
+        L.gforb_obs_create.argtypes = [C.POINTER(ObsConfig), C.POINTER(vp)]
+        L.gforb_obs_destroy.argtypes = [vp]
+        L.gforb_obs_last_launches.argtypes = [vp]
+        L.gforb_obs_set_state.argtypes = [vp, vp]
+        L.gforb_obs_get_state.argtypes = [vp, vp]
+        L.gforb_obs_update_pwls.argtypes = [vp, f64, vp, f64, vp]
+        L.gforb_obs_predict_pwls.argtypes = [vp, f64, i32]
+        L.gforb_obs_num_segments.argtypes = [vp]
+        L.gforb_obs_get_segment.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp, vp]
+        L.gforb_obs_build_info_frame.argtypes = [vp, vp, vp, vp, vp, vp, vp, i32, i32, vp, i32, vp, vp, vp, i32, vp]
+        L.gforb_obs_build_info_map.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp, vp, vp, i32, vp]
+        L.gforb_obs_logdet.argtypes = [vp, vp, i32, vp, i32, vp]
+        L.gforb_obs_rand_stream.argtypes = [vp, u32, i32, vp]
+        L.gforb_obs_select.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, f64, vp, vp, vp, vp, i32, i32, vp]
         _lib = L
     return _lib
+
+# every symbol include/gforb.h declares (checked by tests/test_abi.py against the header and the built library)
+EXPORTS = """gforb_version gforb_device_count gforb_extractor_create gforb_extractor_destroy gforb_extract
+gforb_extractor_levels gforb_extractor_scale_factor gforb_extractor_tables gforb_extractor_debug_level
+gforb_extractor_last_launches gforb_extractor_set_profiling gforb_extractor_stage_time gforb_matcher_create
+gforb_matcher_destroy gforb_matcher_last_launches gforb_descriptor_distance gforb_features_in_area
+gforb_search_for_initialization gforb_search_by_projection gforb_search_by_projection_frames gforb_window_search
+gforb_allpairs_top2 gforb_top2_merge gforb_obs_create gforb_obs_destroy gforb_obs_last_launches gforb_obs_set_state
+gforb_obs_get_state gforb_obs_update_pwls gforb_obs_predict_pwls gforb_obs_num_segments gforb_obs_get_segment
+gforb_obs_build_info_frame gforb_obs_build_info_map gforb_obs_logdet gforb_obs_rand_stream gforb_obs_select""".split()
 
 
 def check(rc: int, what: str):

@@ -1,0 +1,1002 @@
+// B200-native Hamming matching: batch-first CUDA implementation of the per-frame tracking overloads of
+// ORB_SLAM::ORBmatcher (reference src/ORBmatcher.cc) and of the Frame grid they search (src/Frame.cc).
+//
+//   K7  k_grid_build   one CTA per frame: PosInGrid (Frame.cc:367-377) -> CSR over the 64x48 grid, cell index =
+//                      ix*48+iy (so one grid column range [iy0,iy1] is ONE contiguous CSR segment), entries in
+//                      insertion (= keypoint index) order, 16 B records {x, y, octave, index}.
+//   K8a k_candidates   one warp per query (map point / source keypoint): GetFeaturesInArea (Frame.cc:300-365) in
+//                      the reference's order (ix outer, iy inner, insertion order), level + window filter, 256-bit
+//                      Hamming distance (LOP3 xor + POPC on the integer pipe, 2 x 128-bit loads per descriptor);
+//                      writes packed (dist | octave | index) candidate lists.
+//   K8b k_resolve      one warp per problem: the reference's greedy loops are order dependent (claimed keypoints are
+//                      skipped, ORBmatcher.cc:426; SearchForInitialization steals, :1211-1237).  32 consecutive
+//                      queries are evaluated speculatively, one per lane, against the current claim state; the longest
+//                      prefix of lanes whose candidate lists are untouched by an earlier lane's claim commits, the
+//                      rest re-evaluate.  The result is identical to the sequential loop.  Rotation histogram +
+//                      ComputeThreeMaxima (:2338-2379) run in the same kernel.
+//   K10 k_allpairs     brute-force top-2 of n_q queries against a descriptor database shard.
+// All integer results are exact; the float window geometry uses the same un-fused float operations as the reference
+// (this TU is compiled with --fmad=false).
+#include <climits>
+#include <cstring>
+#include <vector>
+#include "common.cuh"
+#include "host_util.h"
+
+namespace gforb {
+
+static const int GRID_COLS = 64, GRID_ROWS = 48, GRID_CELLS = GRID_COLS * GRID_ROWS;
+static const int TH_HIGH = 100, TH_LOW = 50, HISTO_LENGTH = 30;
+enum { M_INIT = 0, M_WINDOW = 1, M_MAP = 2, M_LAST = 3, M_AREA = 4 };
+
+struct FrameDev {
+    const GforbKeyPoint* kps;
+    const uint8_t* desc;
+    const int32_t* counts;
+    int stride;
+};
+struct GridGeom {
+    float minX, minY, invW, invH;
+    int iminX, imaxX, iminY, imaxY;
+};
+struct GridDev {
+    const int* cellStart;     // batch x (GRID_CELLS + 1)
+    const int4* entries;      // batch x maxKp : {x bits, y bits, octave, keypoint index}
+    int maxKp;
+};
+
+// ------------------------------------------------------------------------------------------------ K7 grid
+__global__ void __launch_bounds__(256) k_grid_build(FrameDev F, GridGeom G, int* __restrict__ cellStart,
+                                                    int4* __restrict__ entries, int maxKp) {
+    __shared__ int s_start[GRID_CELLS + 1];
+    __shared__ int s_fill[GRID_CELLS];
+    __shared__ int s_part[8];
+    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int n = min(F.counts[b], maxKp);
+    const GforbKeyPoint* kp = F.kps + (size_t)b * F.stride;
+    for (int c = tid; c < GRID_CELLS; c += 256) s_fill[c] = 0;
+    __syncthreads();
+    for (int i = tid; i < n; i += 256) {
+        // PosInGrid: posX = round((kp.pt.x - mnMinX) * mfGridElementWidthInv) (round half away from zero)
+        int px = (int)roundf((kp[i].x - G.minX) * G.invW);
+        int py = (int)roundf((kp[i].y - G.minY) * G.invH);
+        if (px >= 0 && px < GRID_COLS && py >= 0 && py < GRID_ROWS) atomicAdd(&s_fill[px * GRID_ROWS + py], 1);
+    }
+    __syncthreads();
+    // exclusive scan over 3072 cells: 12 consecutive cells per thread
+    int loc[12], sum = 0;
+#pragma unroll
+    for (int k = 0; k < 12; k++) { loc[k] = sum; sum += s_fill[tid * 12 + k]; }
+    int inc = sum;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { int t = __shfl_up_sync(0xffffffffu, inc, d); if (lane >= d) inc += t; }
+    if (lane == 31) s_part[warp] = inc;
+    __syncthreads();
+    int base = inc - sum;
+    for (int w = 0; w < warp; w++) base += s_part[w];
+#pragma unroll
+    for (int k = 0; k < 12; k++) s_start[tid * 12 + k] = base + loc[k];
+    if (tid == 255) s_start[GRID_CELLS] = base + sum;
+    __syncthreads();
+    int* cs = cellStart + (size_t)b * (GRID_CELLS + 1);
+    for (int c = tid; c <= GRID_CELLS; c += 256) cs[c] = s_start[c];
+    for (int c = tid; c < GRID_CELLS; c += 256) s_fill[c] = s_start[c];
+    __syncthreads();
+    int4* ent = entries + (size_t)b * maxKp;
+    for (int i = tid; i < n; i += 256) {
+        const float x = kp[i].x, y = kp[i].y;
+        int px = (int)roundf((x - G.minX) * G.invW);
+        int py = (int)roundf((y - G.minY) * G.invH);
+        if (px >= 0 && px < GRID_COLS && py >= 0 && py < GRID_ROWS) {
+            int pos = atomicAdd(&s_fill[px * GRID_ROWS + py], 1);
+            ent[pos] = make_int4(__float_as_int(x), __float_as_int(y), kp[i].octave, i);
+        }
+    }
+    __syncthreads();
+    // restore insertion order inside each cell (the scatter above is unordered): insertion sort by keypoint index
+    for (int c = tid; c < GRID_CELLS; c += 256) {
+        const int beg = s_start[c], end = s_start[c + 1];
+        for (int i = beg + 1; i < end; i++) {
+            int4 v = ent[i];
+            int j = i - 1;
+            while (j >= beg && ent[j].w > v.w) { ent[j + 1] = ent[j]; j--; }
+            ent[j + 1] = v;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ K8a candidates
+struct QParams {
+    FrameDev src;                 // INIT / WINDOW / LAST: F1 / LastFrame
+    const float* prevMatched;     // INIT: batch x src.stride x 2
+    const int32_t* srcMp;         // WINDOW / LAST: batch x src.stride, >= 0 valid
+    const uint8_t* srcOutlier;    // LAST (may be null)
+    const float* srcWorld;        // LAST: batch x src.stride x 3
+    const float* Tcw;             // LAST: batch x 16
+    float fx, fy, cx, cy;         // LAST
+    float window;                 // INIT / WINDOW
+    int minScaleLevel, maxScaleLevel;   // WINDOW
+    float th;                     // MAP / LAST
+    const float *mpU, *mpV, *mpCos;     // MAP
+    const int32_t* mpLevel;
+    const uint8_t *mpFlags, *mpDesc;
+    const int32_t* mpCounts;
+    int mpStride;
+    const float *ax, *ay, *ar;    // AREA
+    const int32_t *aMin, *aMax;
+    int aCount, aFrame;
+    float scale[MAX_LEVELS];
+    int nlevels;
+};
+
+// Warp-cooperative GetFeaturesInArea + distance.  Returns the number of candidates; with WRITE, stores
+// (dist << 20 | octave << 16 | index) in the reference's order.
+template <bool WRITE>
+__device__ __forceinline__ int enum_candidates(const int* __restrict__ cs, const int4* __restrict__ ent,
+                                               const uint8_t* __restrict__ tdesc, const GridGeom G, float x, float y,
+                                               float r, int minL, int maxL, const uint32_t (&qd)[8],
+                                               uint32_t* __restrict__ out, int lane) {
+    const unsigned full = 0xffffffffu;
+    int cx0 = (int)floorf((x - G.minX - r) * G.invW);
+    cx0 = max(0, cx0);
+    if (cx0 >= GRID_COLS) return 0;
+    int cx1 = (int)ceilf((x - G.minX + r) * G.invW);
+    cx1 = min(GRID_COLS - 1, cx1);
+    if (cx1 < 0) return 0;
+    int cy0 = (int)floorf((y - G.minY - r) * G.invH);
+    cy0 = max(0, cy0);
+    if (cy0 >= GRID_ROWS) return 0;
+    int cy1 = (int)ceilf((y - G.minY + r) * G.invH);
+    cy1 = min(GRID_ROWS - 1, cy1);
+    if (cy1 < 0) return 0;
+    if (cx1 < cx0 || cy1 < cy0) return 0;
+    const bool checkLevels = !(minL == -1 && maxL == -1);
+    const bool same = checkLevels && (minL == maxL);
+    int total = 0;
+    for (int c0 = cx0; c0 <= cx1; c0 += 32) {
+        const int ix = c0 + lane;
+        int beg = 0, len = 0;
+        if (ix <= cx1) {
+            beg = cs[ix * GRID_ROWS + cy0];
+            len = cs[ix * GRID_ROWS + cy1 + 1] - beg;
+        }
+        int inc = len;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { int t = __shfl_up_sync(full, inc, d); if (lane >= d) inc += t; }
+        const int T = __shfl_sync(full, inc, 31);
+        const int exc = inc - len;
+        for (int base = 0; base < T; base += 32) {
+            const int flat = base + lane;
+            int lo = 0;
+#pragma unroll
+            for (int step = 16; step >= 1; step >>= 1) {
+                int v = __shfl_sync(full, inc, lo + step - 1);
+                if (v <= flat) lo += step;
+            }
+            const int sbeg = __shfl_sync(full, beg, lo), sexc = __shfl_sync(full, exc, lo);
+            bool valid = false;
+            int4 e = make_int4(0, 0, 0, 0);
+            if (flat < T) {
+                e = ent[sbeg + flat - sexc];
+                const float ex = __int_as_float(e.x), ey = __int_as_float(e.y);
+                valid = true;
+                if (checkLevels && !same) { if (e.z < minL || e.z > maxL) valid = false; }
+                else if (same) { if (e.z != minL) valid = false; }
+                if (valid && (fabsf(ex - x) > r || fabsf(ey - y) > r)) valid = false;
+            }
+            const unsigned m = __ballot_sync(full, valid);
+            if (WRITE && valid) {
+                const uint4* dp = reinterpret_cast<const uint4*>(tdesc + (size_t)e.w * 32);
+                const uint4 d0 = __ldg(dp), d1 = __ldg(dp + 1);
+                const int dist = __popc(qd[0] ^ d0.x) + __popc(qd[1] ^ d0.y) + __popc(qd[2] ^ d0.z) + __popc(qd[3] ^ d0.w) +
+                                 __popc(qd[4] ^ d1.x) + __popc(qd[5] ^ d1.y) + __popc(qd[6] ^ d1.z) + __popc(qd[7] ^ d1.w);
+                out[total + __popc(m & ((1u << lane) - 1u))] = ((uint32_t)dist << 20) | ((uint32_t)(e.z & 15) << 16) | (uint32_t)e.w;
+            }
+            total += __popc(m);
+        }
+    }
+    return total;
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(128) k_candidates(const QParams P, const FrameDev T, const GridDev Gd, const GridGeom G,
+                                                    uint32_t* __restrict__ pool, int poolCap, int* __restrict__ poolCount,
+                                                    int2* __restrict__ qMeta, int maxQ, int* __restrict__ err) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int q = blockIdx.x * 4 + warp, b = blockIdx.y;
+    const int tb = (MODE == M_AREA) ? P.aFrame : b;      // target frame
+    int Q;
+    if (MODE == M_MAP) Q = P.mpCounts[b];
+    else if (MODE == M_AREA) Q = P.aCount;
+    else Q = P.src.counts[b];
+    Q = min(Q, maxQ);
+    if (q >= Q) return;
+    float x = 0.f, y = 0.f, r = 0.f;
+    int minL = -1, maxL = -1;
+    bool active = true;
+    const uint8_t* qdp = nullptr;
+    if (MODE == M_INIT) {
+        const GforbKeyPoint* kp = P.src.kps + (size_t)b * P.src.stride + q;
+        const int level1 = kp->octave;
+        if (level1 > 0) active = false;                   // src/ORBmatcher.cc:1188-1190
+        x = P.prevMatched[((size_t)b * P.src.stride + q) * 2];
+        y = P.prevMatched[((size_t)b * P.src.stride + q) * 2 + 1];
+        r = P.window; minL = maxL = level1;
+        qdp = P.src.desc + ((size_t)b * P.src.stride + q) * 32;
+    } else if (MODE == M_WINDOW) {
+        const GforbKeyPoint* kp = P.src.kps + (size_t)b * P.src.stride + q;
+        const int level1 = kp->octave;
+        if (P.srcMp[(size_t)b * P.src.stride + q] < 0) active = false;
+        if (P.minScaleLevel > 0 && level1 < P.minScaleLevel) active = false;
+        if (P.maxScaleLevel < INT_MAX && level1 > P.maxScaleLevel) active = false;
+        x = kp->x; y = kp->y; r = P.window; minL = maxL = level1;
+        qdp = P.src.desc + ((size_t)b * P.src.stride + q) * 32;
+    } else if (MODE == M_MAP) {
+        const size_t i = (size_t)b * P.mpStride + q;
+        const uint8_t fl = P.mpFlags[i];
+        if (!(fl & 1) || (fl & 2)) active = false;        // !mbTrackInView || isBad()
+        int lvl = P.mpLevel[i];
+        lvl = min(max(lvl, 0), P.nlevels - 1);
+        float rr = (P.mpCos[i] > 0.998) ? 2.5f : 4.0f;    // RadiusByViewingCos (float vs double literal)
+        if (P.th != 1.0f) rr *= P.th;
+        x = P.mpU[i]; y = P.mpV[i];
+        r = rr * P.scale[lvl];
+        minL = P.mpLevel[i] - 1; maxL = P.mpLevel[i];
+        qdp = P.mpDesc + i * 32;
+    } else if (MODE == M_LAST) {
+        const size_t i = (size_t)b * P.src.stride + q;
+        if (P.srcMp[i] < 0) active = false;
+        if (P.srcOutlier && P.srcOutlier[i]) active = false;
+        if (active) {
+            const float* X = P.srcWorld + i * 3;
+            const float* Tm = P.Tcw + (size_t)b * 16;
+            float xc3[3];
+#pragma unroll
+            for (int rw = 0; rw < 3; rw++) {
+                double s = (double)Tm[rw * 4 + 0] * (double)X[0] + (double)Tm[rw * 4 + 1] * (double)X[1] +
+                           (double)Tm[rw * 4 + 2] * (double)X[2];
+                xc3[rw] = (float)s + Tm[rw * 4 + 3];
+            }
+            const float invzc = (float)(1.0 / (double)xc3[2]);
+            const float u = P.fx * xc3[0] * invzc + P.cx;
+            const float v = P.fy * xc3[1] * invzc + P.cy;
+            if (u < (float)G.iminX || u > (float)G.imaxX) active = false;
+            if (v < (float)G.iminY || v > (float)G.imaxY) active = false;
+            const int oct = P.src.kps[i].octave;
+            x = u; y = v;
+            r = P.th * P.scale[min(max(oct, 0), P.nlevels - 1)];
+            minL = oct - 1; maxL = oct + 1;
+        }
+        qdp = P.src.desc + i * 32;
+    } else {
+        x = P.ax[q]; y = P.ay[q]; r = P.ar[q]; minL = P.aMin[q]; maxL = P.aMax[q];
+    }
+    int2 meta = make_int2(0, 0);
+    if (active) {
+        uint32_t qd[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        if (qdp) {
+            const uint4 a0 = __ldg(reinterpret_cast<const uint4*>(qdp)), a1 = __ldg(reinterpret_cast<const uint4*>(qdp) + 1);
+            qd[0] = a0.x; qd[1] = a0.y; qd[2] = a0.z; qd[3] = a0.w; qd[4] = a1.x; qd[5] = a1.y; qd[6] = a1.z; qd[7] = a1.w;
+        }
+        const int* cs = Gd.cellStart + (size_t)tb * (GRID_CELLS + 1);
+        const int4* ent = Gd.entries + (size_t)tb * Gd.maxKp;
+        const uint8_t* tdesc = T.desc + (size_t)tb * T.stride * 32;
+        int cnt = enum_candidates<false>(cs, ent, tdesc, G, x, y, r, minL, maxL, qd, nullptr, lane);
+        if (cnt > 0) {
+            int off = 0;
+            if (lane == 0) off = atomicAdd(&poolCount[b], cnt);
+            off = __shfl_sync(0xffffffffu, off, 0);
+            if (off + cnt > poolCap) {
+                if (lane == 0) atomicExch(err, GFORB_ERR_OVERFLOW);
+            } else {
+                enum_candidates<true>(cs, ent, tdesc, G, x, y, r, minL, maxL, qd, pool + (size_t)b * poolCap + off, lane);
+                meta = make_int2(off, cnt);
+            }
+        }
+    }
+    if (lane == 0) qMeta[(size_t)b * maxQ + q] = meta;
+}
+
+// ------------------------------------------------------------------------------------------------ K8b resolve
+struct RParams {
+    FrameDev src, tgt;
+    const uint32_t* pool;
+    int poolCap;
+    const int2* qMeta;
+    int maxQ, maxKp;
+    const int32_t* qCounts;
+    const int32_t* srcMp;
+    float nnratio;
+    int checkOri;
+    int32_t* tgtMp;       // MAP / LAST: in/out batch x tgt.stride;  WINDOW: matches2 (out)
+    int32_t* tgtScore;    // MAP / LAST
+    int32_t* matches12;   // INIT: batch x src.stride
+    float* prevMatched;   // INIT
+    int32_t* nmatches;
+    int* rotBinQ;         // INIT scratch: batch x maxQ
+};
+
+__device__ __forceinline__ int rot_bin(float a1, float a2) {
+    float rot = a1 - a2;
+    if (rot < 0.0f) rot += 360.0f;
+    int bin = (int)roundf(rot * (1.0f / HISTO_LENGTH));
+    if (bin == HISTO_LENGTH) bin = 0;
+    return min(max(bin, 0), HISTO_LENGTH - 1);
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(32) k_resolve(const RParams R) {
+    extern __shared__ int sm[];
+    const unsigned full = 0xffffffffu;
+    const int b = blockIdx.x, lane = threadIdx.x;
+    int* state = sm;                          // MAP/LAST/WINDOW: id held by target keypoint (-1 free); INIT: vMatchedDistance
+    int* owner = sm + R.maxKp;                // INIT: vnMatches21;  LAST/WINDOW: rotation bin of a claimed keypoint
+    unsigned* rnd = reinterpret_cast<unsigned*>(sm + 2 * R.maxKp);
+    __shared__ int hist[32];
+    __shared__ int top3[3];
+    const int N2 = min(R.tgt.counts[b], R.maxKp);
+    const int Q = min(R.qCounts[b], R.maxQ);
+    const size_t tOff = (size_t)b * R.tgt.stride, sOff = (size_t)b * R.src.stride;
+    for (int i = lane; i < N2; i += 32) {
+        if (MODE == M_MAP || MODE == M_LAST) state[i] = R.tgtMp[tOff + i];
+        else if (MODE == M_WINDOW) state[i] = -1;
+        else state[i] = INT_MAX;
+        owner[i] = -1;
+        rnd[i] = 0xffffffffu;
+    }
+    hist[lane] = 0;
+    if (MODE == M_INIT)
+        for (int i = lane; i < R.src.stride; i += 32) {
+            R.matches12[sOff + i] = -1;
+            if (i < R.maxQ) R.rotBinQ[(size_t)b * R.maxQ + i] = -1;
+        }
+    __syncwarp();
+    int accepted = 0;
+    for (int qb = 0; qb < Q; qb += 32) {
+        const int q = qb + lane;
+        int2 meta = make_int2(0, 0);
+        if (q < Q) meta = R.qMeta[(size_t)b * R.maxQ + q];
+        const uint32_t* list = R.pool + (size_t)b * R.poolCap + meta.x;
+        const int cnt = meta.y;
+        bool done = cnt <= 0;
+        while (__any_sync(full, !done)) {
+            bool acc = false;
+            int bi = -1, best = INT_MAX;
+            if (!done) {
+                int best2 = INT_MAX, bl = -1, bl2 = -1;
+                for (int c = 0; c < cnt; c++) {
+                    const uint32_t e = list[c];
+                    const int i2 = e & 0xffff, dist = (int)(e >> 20), oct = (e >> 16) & 15;
+                    if (MODE == M_INIT) {
+                        if (state[i2] <= dist) continue;                        // :1211
+                        if (dist < best) { best2 = best; best = dist; bi = i2; }
+                        else if (dist < best2) best2 = dist;
+                    } else {
+                        if (state[i2] >= 0) continue;                           // claimed (:426, :1040, :2150)
+                        if (MODE == M_LAST) {
+                            if (dist < best) { best = dist; bi = i2; }
+                        } else if (dist < best) { best2 = best; best = dist; bl2 = bl; bl = oct; bi = i2; }
+                        else if (dist < best2) { bl2 = oct; best2 = dist; }
+                    }
+                }
+                if (MODE == M_INIT) acc = best <= TH_LOW && (float)best < (float)best2 * R.nnratio;
+                else if (MODE == M_WINDOW) acc = (float)best <= (float)best2 * R.nnratio && best <= TH_HIGH;
+                else if (MODE == M_LAST) acc = best <= TH_HIGH;
+                else acc = best <= TH_HIGH && !(bl == bl2 && (float)best > R.nnratio * (float)best2);
+                if (bi < 0) acc = false;
+            }
+            if (!done && acc) atomicMin(&rnd[bi], (unsigned)lane);
+            __syncwarp();
+            bool conflict = false;
+            if (!done)
+                for (int c = 0; c < cnt; c++)
+                    if (rnd[list[c] & 0xffff] < (unsigned)lane) { conflict = true; break; }
+            const unsigned cm = __ballot_sync(full, !done && conflict);
+            const int first = cm ? (__ffs(cm) - 1) : 32;
+            __syncwarp();
+            if (!done && acc) rnd[bi] = 0xffffffffu;
+            if (!done && lane < first) {
+                done = true;
+                if (acc) {
+                    accepted++;
+                    if (MODE == M_MAP) {
+                        state[bi] = q;
+                        R.tgtMp[tOff + bi] = q;
+                        R.tgtScore[tOff + bi] = best;
+                    } else if (MODE == M_LAST) {
+                        const int id = R.srcMp[sOff + q];
+                        state[bi] = id;
+                        R.tgtMp[tOff + bi] = id;
+                        R.tgtScore[tOff + bi] = best;
+                        if (R.checkOri) {
+                            const int bin = rot_bin(R.src.kps[sOff + q].angle, R.tgt.kps[tOff + bi].angle);
+                            owner[bi] = bin;
+                            atomicAdd(&hist[bin], 1);
+                        }
+                    } else if (MODE == M_WINDOW) {
+                        state[bi] = R.srcMp[sOff + q];
+                        const int bin = rot_bin(R.src.kps[sOff + q].angle, R.tgt.kps[tOff + bi].angle);
+                        owner[bi] = bin;
+                        atomicAdd(&hist[bin], 1);
+                    } else {
+                        const int prev = owner[bi];
+                        if (prev >= 0) R.matches12[sOff + prev] = -1;           // steal (:1230-1234)
+                        R.matches12[sOff + q] = bi;
+                        owner[bi] = q;
+                        state[bi] = best;
+                        if (R.checkOri) {
+                            const int bin = rot_bin(R.src.kps[sOff + q].angle, R.tgt.kps[tOff + bi].angle);
+                            R.rotBinQ[(size_t)b * R.maxQ + q] = bin;             // stale entries stay and count (:1249)
+                            atomicAdd(&hist[bin], 1);
+                        }
+                    }
+                }
+            }
+            __syncwarp();
+        }
+    }
+    __threadfence_block();
+    __syncwarp();
+    // ComputeThreeMaxima (:2338-2379)
+    if (lane == 0) {
+        int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            const int s = hist[i];
+            if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+            else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+            else if (s > max3) { max3 = s; ind3 = i; }
+        }
+        if ((float)max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+        else if ((float)max3 < 0.1f * (float)max1) ind3 = -1;
+        top3[0] = ind1; top3[1] = ind2; top3[2] = ind3;
+    }
+    __syncwarp();
+    const int i1 = top3[0], i2m = top3[1], i3 = top3[2];
+    int total = 0;
+    if (MODE == M_INIT) {
+        const int N1 = min(R.src.counts[b], R.maxQ);
+        for (int i = lane; i < N1; i += 32) {
+            int m = __ldcg(&R.matches12[sOff + i]);
+            if (R.checkOri && m >= 0) {
+                const int bin = __ldcg(&R.rotBinQ[(size_t)b * R.maxQ + i]);
+                if (bin >= 0 && bin != i1 && bin != i2m && bin != i3) { m = -1; R.matches12[sOff + i] = -1; }
+            }
+            if (m >= 0) {
+                total++;
+                R.prevMatched[(sOff + i) * 2] = R.tgt.kps[tOff + m].x;          // :1282-1284
+                R.prevMatched[(sOff + i) * 2 + 1] = R.tgt.kps[tOff + m].y;
+            }
+        }
+        total = __reduce_add_sync(full, total);
+    } else if (MODE == M_MAP) {
+        total = __reduce_add_sync(full, accepted);
+    } else {
+        int removed = 0;
+        if (R.checkOri)
+            for (int i = lane; i < N2; i += 32) {
+                const int bin = owner[i];
+                if (bin >= 0 && bin != i1 && bin != i2m && bin != i3) {
+                    removed++;
+                    state[i] = -1;
+                    if (MODE == M_LAST) { R.tgtMp[tOff + i] = -1; R.tgtScore[tOff + i] = 999; }
+                }
+            }
+        if (MODE == M_WINDOW)
+            for (int i = lane; i < R.tgt.stride; i += 32) R.tgtMp[tOff + i] = (i < N2) ? state[i] : -1;
+        total = __reduce_add_sync(full, accepted - removed);
+    }
+    if (lane == 0) R.nmatches[b] = total;
+}
+
+// ------------------------------------------------------------------------------------------------ B1 distance
+__global__ void __launch_bounds__(256) k_distance(const uint4* __restrict__ a, const uint4* __restrict__ b, int n,
+                                                  int32_t* __restrict__ out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    out[i] = popc256(__ldg(a + 2 * i), __ldg(a + 2 * i + 1), __ldg(b + 2 * i), __ldg(b + 2 * i + 1));
+}
+
+// ------------------------------------------------------------------------------------------------ K10 all-pairs
+// Thread = AP_R queries held in registers; CTA streams its database chunk through shared memory (broadcast LDS.128).
+// Per pair: 8 LOP3(xor) + 8 POPC + adds, then a 3-instruction top-2 update on packed (dist << 22 | row) keys.
+static const int AP_R = 4, AP_THREADS = 128, AP_TILE = 256;
+__global__ void __launch_bounds__(AP_THREADS) k_allpairs(const uint4* __restrict__ qv, int nq, const uint4* __restrict__ db,
+                                                         long long nDb, int chunkRows, long long idxBase,
+                                                         uint64_t* __restrict__ partial) {
+    __shared__ uint4 s_db[2][AP_TILE * 2];
+    const int tid = threadIdx.x;
+    const int q0 = (blockIdx.x * AP_THREADS + tid) * AP_R;
+    const long long row0 = (long long)blockIdx.y * chunkRows;
+    const int rows = (int)min((long long)chunkRows, nDb - row0);
+    uint32_t qd[AP_R][8];
+    uint32_t k1[AP_R], k2[AP_R];
+#pragma unroll
+    for (int r = 0; r < AP_R; r++) {
+        uint4 a0 = make_uint4(0, 0, 0, 0), a1 = a0;
+        if (q0 + r < nq) { a0 = __ldg(qv + 2 * (size_t)(q0 + r)); a1 = __ldg(qv + 2 * (size_t)(q0 + r) + 1); }
+        qd[r][0] = a0.x; qd[r][1] = a0.y; qd[r][2] = a0.z; qd[r][3] = a0.w;
+        qd[r][4] = a1.x; qd[r][5] = a1.y; qd[r][6] = a1.z; qd[r][7] = a1.w;
+        k1[r] = k2[r] = 0xffffffffu;
+    }
+    const uint4* src = db + 2 * (size_t)row0;
+    const int nTiles = (rows + AP_TILE - 1) / AP_TILE;
+    auto load_tile = [&](int t, int buf) {
+        const int base = t * AP_TILE, n16 = min(AP_TILE, rows - base) * 2;
+        for (int i = tid; i < AP_TILE * 2; i += AP_THREADS)
+            s_db[buf][i] = (i < n16) ? ldg_nc_u4(src + (size_t)base * 2 + i) : make_uint4(0, 0, 0, 0);
+    };
+    if (nTiles > 0) load_tile(0, 0);
+    __syncthreads();
+    for (int t = 0; t < nTiles; t++) {
+        const int buf = t & 1;
+        if (t + 1 < nTiles) load_tile(t + 1, buf ^ 1);
+        const int n = min(AP_TILE, rows - t * AP_TILE);
+        const uint32_t rowBase = (uint32_t)(t * AP_TILE);
+#pragma unroll 4
+        for (int j = 0; j < n; j++) {
+            const uint4 d0 = s_db[buf][2 * j], d1 = s_db[buf][2 * j + 1];
+#pragma unroll
+            for (int r = 0; r < AP_R; r++) {
+                const int dist = __popc(qd[r][0] ^ d0.x) + __popc(qd[r][1] ^ d0.y) + __popc(qd[r][2] ^ d0.z) +
+                                 __popc(qd[r][3] ^ d0.w) + __popc(qd[r][4] ^ d1.x) + __popc(qd[r][5] ^ d1.y) +
+                                 __popc(qd[r][6] ^ d1.z) + __popc(qd[r][7] ^ d1.w);
+                const uint32_t key = ((uint32_t)dist << 22) + (rowBase + (uint32_t)j);
+                k2[r] = min(k2[r], max(k1[r], key));
+                k1[r] = min(k1[r], key);
+            }
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int r = 0; r < AP_R; r++) {
+        if (q0 + r >= nq) continue;
+        uint64_t o1 = ~0ull, o2 = ~0ull;
+        if (k1[r] != 0xffffffffu) o1 = ((uint64_t)(k1[r] >> 22) << 32) | (uint64_t)(idxBase + row0 + (k1[r] & 0x3fffff));
+        if (k2[r] != 0xffffffffu) o2 = ((uint64_t)(k2[r] >> 22) << 32) | (uint64_t)(idxBase + row0 + (k2[r] & 0x3fffff));
+        uint64_t* o = partial + ((size_t)blockIdx.y * nq + (q0 + r)) * 2;
+        o[0] = o1; o[1] = o2;
+    }
+}
+
+// merge n_parts partial top-2 lists per query (keys are unique: they carry the global row index)
+__global__ void __launch_bounds__(256) k_top2_merge(const uint64_t* __restrict__ parts, int nParts, int nq,
+                                                    uint64_t* __restrict__ out) {
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= nq) return;
+    uint64_t a = ~0ull, b2 = ~0ull;
+    for (int p = 0; p < nParts; p++) {
+        const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(parts + ((size_t)p * nq + q) * 2);
+        uint64_t k = v.x;
+        b2 = min(b2, max(a, k)); a = min(a, k);
+        k = v.y;
+        b2 = min(b2, max(a, k)); a = min(a, k);
+    }
+    out[(size_t)q * 2] = a;
+    out[(size_t)q * 2 + 1] = b2;
+}
+
+}  // namespace gforb
+
+using namespace gforb;
+
+// ================================================================================================ host side
+struct GforbMatcher {
+    GforbMatcherConfig cfg;
+    int device = 0, numSMs = 148, poolCap = 0, lastLaunches = 0;
+    float scale[MAX_LEVELS];
+    Arena arena;
+    int* d_cellStart = nullptr;      // max_batch x 3073
+    int4* d_entries = nullptr;       // max_batch x max_keypoints
+    uint32_t* d_pool = nullptr;      // max_batch x poolCap
+    int* d_poolCount = nullptr;      // max_batch
+    int2* d_qMeta = nullptr;         // max_batch x max_queries
+    int* d_rotBinQ = nullptr;        // max_batch x max_queries
+    int* d_err = nullptr;
+    uint64_t* d_partial = nullptr;
+    size_t capPartial = 0;
+    std::vector<OutCopy> outs;
+};
+
+namespace {
+
+struct Ctx {
+    GforbMatcher* M;
+    cudaStream_t st;
+    bool inDev, outDev;
+    int rc = GFORB_OK;
+    template <class T>
+    const T* in(const T* p, size_t n) {           // pure input
+        if (!p || rc) return p;
+        if (inDev) return p;
+        T* d = (T*)M->arena.take(n * sizeof(T));
+        if (!d) { rc = GFORB_ERR_CAPACITY; return nullptr; }
+        if (cudaMemcpyAsync(d, p, n * sizeof(T), cudaMemcpyHostToDevice, st) != cudaSuccess) rc = GFORB_ERR_CUDA;
+        return d;
+    }
+    template <class T>
+    T* out(T* p, size_t n, bool copyIn) {          // output or in/out
+        if (!p || rc) return p;
+        if (outDev) return p;
+        T* d = (T*)M->arena.take(n * sizeof(T));
+        if (!d) { rc = GFORB_ERR_CAPACITY; return nullptr; }
+        if (copyIn && cudaMemcpyAsync(d, p, n * sizeof(T), cudaMemcpyHostToDevice, st) != cudaSuccess) rc = GFORB_ERR_CUDA;
+        M->outs.push_back(OutCopy{p, d, n * sizeof(T)});
+        return d;
+    }
+    FrameDev frame(const GforbFrameSet* F, int batch) {
+        FrameDev f;
+        f.stride = F->kp_stride;
+        f.kps = in(F->keypoints, (size_t)batch * F->kp_stride);
+        f.desc = in(F->descriptors, (size_t)batch * F->kp_stride * 32);
+        f.counts = in(F->counts, (size_t)batch);
+        return f;
+    }
+};
+
+GridGeom geom_of(const GforbFrameSet* F) {
+    GridGeom G;
+    G.iminX = F->min_x; G.imaxX = F->max_x; G.iminY = F->min_y; G.imaxY = F->max_y;
+    G.minX = (float)F->min_x; G.minY = (float)F->min_y;
+    G.invW = (float)GRID_COLS / (float)(F->max_x - F->min_x);       // src/Frame.cc:97-98
+    G.invH = (float)GRID_ROWS / (float)(F->max_y - F->min_y);
+    return G;
+}
+
+int begin_call(GforbMatcher* M, int batch, int flags, void* stream, Ctx& c) {
+    if (!M) return GFORB_ERR_ARG;
+    if (batch < 0) return GFORB_ERR_ARG;
+    if (batch > M->cfg.max_batch) return GFORB_ERR_CAPACITY;
+    GF_CUDA_OK(cudaSetDevice(M->device));
+    c.M = M; c.st = (cudaStream_t)stream;
+    c.inDev = (flags & GFORB_IN_DEVICE) != 0; c.outDev = (flags & GFORB_OUT_DEVICE) != 0;
+    M->arena.reset();
+    M->outs.clear();
+    M->lastLaunches = 0;
+    return GFORB_OK;
+}
+
+int end_call(GforbMatcher* M, Ctx& c, int flags) {
+    if (c.rc) return c.rc;
+    GF_CUDA_OK(cudaGetLastError());
+    for (auto& o : M->outs) GF_CUDA_OK(cudaMemcpyAsync(o.host, o.dev, o.bytes, cudaMemcpyDeviceToHost, c.st));
+    if (!(flags & GFORB_ASYNC) || !M->outs.empty()) {
+        GF_CUDA_OK(cudaStreamSynchronize(c.st));
+        int err = 0;
+        GF_CUDA_OK(cudaMemcpy(&err, M->d_err, sizeof(int), cudaMemcpyDeviceToHost));
+        if (err) { cudaMemset(M->d_err, 0, sizeof(int)); return err; }
+    }
+    return GFORB_OK;
+}
+
+int check_frames(GforbMatcher* M, const GforbFrameSet* F) {
+    if (!F || !F->keypoints || !F->descriptors || !F->counts) return GFORB_ERR_ARG;
+    if (F->kp_stride <= 0 || F->max_x <= F->min_x || F->max_y <= F->min_y) return GFORB_ERR_ARG;
+    if (F->kp_stride > M->cfg.max_keypoints) return GFORB_ERR_CAPACITY;
+    return GFORB_OK;
+}
+
+void build_grid(GforbMatcher* M, Ctx& c, const FrameDev& T, const GridGeom& G, int batch) {
+    k_grid_build<<<batch, 256, 0, c.st>>>(T, G, M->d_cellStart, M->d_entries, M->cfg.max_keypoints);
+    M->lastLaunches++;
+}
+
+template <int MODE>
+void run_candidates(GforbMatcher* M, Ctx& c, const QParams& P, const FrameDev& T, const GridGeom& G, int batch, int maxQueries) {
+    cudaMemsetAsync(M->d_poolCount, 0, sizeof(int) * batch, c.st);
+    GridDev Gd{M->d_cellStart, M->d_entries, M->cfg.max_keypoints};
+    dim3 grid((maxQueries + 3) / 4, batch);
+    k_candidates<MODE><<<grid, 128, 0, c.st>>>(P, T, Gd, G, M->d_pool, M->poolCap, M->d_poolCount, M->d_qMeta,
+                                                M->cfg.max_queries, M->d_err);
+    M->lastLaunches++;
+}
+
+template <int MODE>
+void run_resolve(GforbMatcher* M, Ctx& c, const RParams& R, int batch) {
+    const size_t smem = (size_t)3 * M->cfg.max_keypoints * sizeof(int);
+    k_resolve<MODE><<<batch, 32, smem, c.st>>>(R);
+    M->lastLaunches++;
+}
+
+void fill_scale(GforbMatcher* M, QParams& P) {
+    for (int i = 0; i < MAX_LEVELS; i++) P.scale[i] = M->scale[i < M->cfg.nlevels ? i : M->cfg.nlevels - 1];
+    P.nlevels = M->cfg.nlevels;
+}
+
+}  // namespace
+
+extern "C" {
+
+int gforb_matcher_create(const GforbMatcherConfig* cfg, GforbMatcher** out) {
+    if (!cfg || !out) return GFORB_ERR_ARG;
+    *out = nullptr;
+    if (cfg->max_batch <= 0 || cfg->max_keypoints <= 0 || cfg->max_keypoints > 16384 || cfg->max_queries <= 0 ||
+        cfg->nlevels <= 0 || cfg->nlevels > MAX_LEVELS || !(cfg->scaleFactor > 1.0f) || cfg->cand_pool < 0)
+        return GFORB_ERR_ARG;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0 || cfg->device < 0 || cfg->device >= ndev) {
+        fprintf(stderr, "[gforb] no usable CUDA device (requested %d of %d): the B200 path has no CPU fallback\n", cfg->device, ndev);
+        return GFORB_ERR_CUDA;
+    }
+    GF_CUDA_OK(cudaSetDevice(cfg->device));
+    GforbMatcher* M = new GforbMatcher();
+    M->cfg = *cfg;
+    M->device = cfg->device;
+    cudaDeviceGetAttribute(&M->numSMs, cudaDevAttrMultiProcessorCount, cfg->device);
+    // Frame::mvScaleFactors (src/Frame.cc:62-75): mvScaleFactors[i] = mvScaleFactors[i-1] * mfScaleFactor (float)
+    M->scale[0] = 1.0f;
+    for (int i = 1; i < MAX_LEVELS; i++) M->scale[i] = M->scale[i - 1] * cfg->scaleFactor;
+    M->poolCap = cfg->cand_pool > 0 ? cfg->cand_pool : 64 * cfg->max_queries;
+    const size_t B = cfg->max_batch, K = cfg->max_keypoints, Qn = cfg->max_queries;
+    GF_CUDA_OK(cudaMalloc((void**)&M->d_cellStart, B * (GRID_CELLS + 1) * sizeof(int)));
+    GF_CUDA_OK(cudaMalloc((void**)&M->d_entries, B * K * sizeof(int4)));
+    GF_CUDA_OK(cudaMalloc((void**)&M->d_pool, B * (size_t)M->poolCap * sizeof(uint32_t)));
+    GF_CUDA_OK(cudaMalloc((void**)&M->d_poolCount, B * sizeof(int)));
+    GF_CUDA_OK(cudaMalloc((void**)&M->d_qMeta, B * Qn * sizeof(int2)));
+    GF_CUDA_OK(cudaMalloc((void**)&M->d_rotBinQ, B * Qn * sizeof(int)));
+    GF_CUDA_OK(cudaMalloc((void**)&M->d_err, sizeof(int)));
+    GF_CUDA_OK(cudaMemset(M->d_err, 0, sizeof(int)));
+    // staging arena for host-pointer calls: two frame sets + one query set + outputs
+    const size_t arenaBytes = B * (K * 2 * (28 + 32 + 16) + Qn * (64 + 32)) + (4u << 20);
+    GF_CUDA_OK(M->arena.init(arenaBytes));
+    const int smem = 3 * cfg->max_keypoints * (int)sizeof(int);
+    GF_CUDA_OK(cudaFuncSetAttribute(k_resolve<M_INIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    GF_CUDA_OK(cudaFuncSetAttribute(k_resolve<M_WINDOW>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    GF_CUDA_OK(cudaFuncSetAttribute(k_resolve<M_MAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    GF_CUDA_OK(cudaFuncSetAttribute(k_resolve<M_LAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    *out = M;
+    return GFORB_OK;
+}
+
+int gforb_matcher_destroy(GforbMatcher* M) {
+    if (!M) return GFORB_ERR_ARG;
+    cudaSetDevice(M->device);
+    void* ptrs[] = {M->d_cellStart, M->d_entries, M->d_pool, M->d_poolCount, M->d_qMeta, M->d_rotBinQ, M->d_err, M->d_partial};
+    for (void* p : ptrs) if (p) cudaFree(p);
+    M->arena.release();
+    delete M;
+    return GFORB_OK;
+}
+
+int gforb_matcher_last_launches(const GforbMatcher* M) { return M ? M->lastLaunches : GFORB_ERR_ARG; }
+
+int gforb_descriptor_distance(GforbMatcher* M, const uint8_t* a, const uint8_t* b, int n, int32_t* out, int flags, void* stream) {
+    Ctx c;
+    int rc = begin_call(M, 0, flags, stream, c);
+    if (rc) return rc;
+    if (n == 0) return GFORB_OK;
+    if (!a || !b || !out || n < 0) return GFORB_ERR_ARG;
+    const uint8_t* da = c.in(a, (size_t)n * 32);
+    const uint8_t* db = c.in(b, (size_t)n * 32);
+    int32_t* dout = c.out(out, (size_t)n, false);
+    if (c.rc) return c.rc;
+    k_distance<<<(n + 255) / 256, 256, 0, c.st>>>((const uint4*)da, (const uint4*)db, n, dout);
+    M->lastLaunches++;
+    return end_call(M, c, flags);
+}
+
+int gforb_features_in_area(GforbMatcher* M, const GforbFrameSet* frames, int batch, int frame, const float* x,
+                           const float* y, const float* r, const int32_t* min_level, const int32_t* max_level,
+                           int n_queries, int32_t* out_idx, int cap, int32_t* out_n, int flags, void* stream) {
+    Ctx c;
+    int rc = begin_call(M, batch, flags, stream, c);
+    if (rc) return rc;
+    if ((rc = check_frames(M, frames))) return rc;
+    if (frame < 0 || frame >= batch || n_queries < 0 || cap <= 0 || !out_idx || !out_n) return GFORB_ERR_ARG;
+    if (n_queries > M->cfg.max_queries) return GFORB_ERR_CAPACITY;
+    if (n_queries == 0) return GFORB_OK;
+    FrameDev T = c.frame(frames, batch);
+    GridGeom G = geom_of(frames);
+    QParams P;
+    memset(&P, 0, sizeof(P));
+    fill_scale(M, P);
+    P.ax = c.in(x, n_queries); P.ay = c.in(y, n_queries); P.ar = c.in(r, n_queries);
+    P.aMin = c.in(min_level, n_queries); P.aMax = c.in(max_level, n_queries);
+    P.aCount = n_queries; P.aFrame = frame;
+    if (c.rc) return c.rc;
+    build_grid(M, c, T, G, batch);
+    run_candidates<M_AREA>(M, c, P, T, G, 1, n_queries);
+    GF_CUDA_OK(cudaStreamSynchronize(c.st));
+    // unpack on the host (parity tap, not a hot path)
+    std::vector<int2> meta(n_queries);
+    GF_CUDA_OK(cudaMemcpy(meta.data(), M->d_qMeta, sizeof(int2) * n_queries, cudaMemcpyDeviceToHost));
+    int used = 0;
+    GF_CUDA_OK(cudaMemcpy(&used, M->d_poolCount, sizeof(int), cudaMemcpyDeviceToHost));
+    std::vector<uint32_t> pool(std::max(used, 1));
+    if (used > 0 && used <= M->poolCap) GF_CUDA_OK(cudaMemcpy(pool.data(), M->d_pool, sizeof(uint32_t) * used, cudaMemcpyDeviceToHost));
+    std::vector<int32_t> idx((size_t)n_queries * cap, -1), cnt(n_queries, 0);
+    for (int q = 0; q < n_queries; q++) {
+        cnt[q] = meta[q].y;
+        for (int k = 0; k < meta[q].y && k < cap; k++) idx[(size_t)q * cap + k] = (int32_t)(pool[meta[q].x + k] & 0xffff);
+    }
+    if (c.outDev) {
+        GF_CUDA_OK(cudaMemcpy(out_idx, idx.data(), idx.size() * 4, cudaMemcpyHostToDevice));
+        GF_CUDA_OK(cudaMemcpy(out_n, cnt.data(), cnt.size() * 4, cudaMemcpyHostToDevice));
+    } else {
+        memcpy(out_idx, idx.data(), idx.size() * 4);
+        memcpy(out_n, cnt.data(), cnt.size() * 4);
+    }
+    return end_call(M, c, flags);
+}
+
+int gforb_search_for_initialization(GforbMatcher* M, const GforbFrameSet* F1, const GforbFrameSet* F2, int batch,
+                                    float* prev_matched, int32_t* matches12, int32_t* nmatches, int window_size,
+                                    float nnratio, int check_orientation, int flags, void* stream) {
+    Ctx c;
+    int rc = begin_call(M, batch, flags, stream, c);
+    if (rc) return rc;
+    if ((rc = check_frames(M, F1)) || (rc = check_frames(M, F2))) return rc;
+    if (!prev_matched || !matches12 || !nmatches) return GFORB_ERR_ARG;
+    if (F1->kp_stride > M->cfg.max_queries) return GFORB_ERR_CAPACITY;
+    if (batch == 0) return GFORB_OK;
+    FrameDev S = c.frame(F1, batch), T = c.frame(F2, batch);
+    GridGeom G = geom_of(F2);
+    QParams P;
+    memset(&P, 0, sizeof(P));
+    fill_scale(M, P);
+    float* dPrev = c.out(prev_matched, (size_t)batch * F1->kp_stride * 2, true);
+    int32_t* dM12 = c.out(matches12, (size_t)batch * F1->kp_stride, false);
+    int32_t* dN = c.out(nmatches, (size_t)batch, false);
+    if (c.rc) return c.rc;
+    P.src = S; P.prevMatched = dPrev; P.window = (float)window_size;
+    build_grid(M, c, T, G, batch);
+    run_candidates<M_INIT>(M, c, P, T, G, batch, F1->kp_stride);
+    RParams R;
+    memset(&R, 0, sizeof(R));
+    R.src = S; R.tgt = T; R.pool = M->d_pool; R.poolCap = M->poolCap; R.qMeta = M->d_qMeta; R.maxQ = M->cfg.max_queries;
+    R.maxKp = M->cfg.max_keypoints; R.qCounts = S.counts; R.nnratio = nnratio; R.checkOri = check_orientation;
+    R.matches12 = dM12; R.prevMatched = dPrev; R.nmatches = dN; R.rotBinQ = M->d_rotBinQ;
+    run_resolve<M_INIT>(M, c, R, batch);
+    return end_call(M, c, flags);
+}
+
+int gforb_search_by_projection(GforbMatcher* M, const GforbFrameSet* F, const GforbMapPointSet* mps, int batch,
+                               float th, float nnratio, int32_t* frame_mappoints, int32_t* match_score,
+                               int32_t* nmatches, int flags, void* stream) {
+    Ctx c;
+    int rc = begin_call(M, batch, flags, stream, c);
+    if (rc) return rc;
+    if ((rc = check_frames(M, F))) return rc;
+    if (!mps || !mps->proj_x || !mps->proj_y || !mps->scale_level || !mps->view_cos || !mps->flags || !mps->descriptors ||
+        !mps->counts || mps->mp_stride <= 0 || !frame_mappoints || !match_score || !nmatches)
+        return GFORB_ERR_ARG;
+    if (mps->mp_stride > M->cfg.max_queries) return GFORB_ERR_CAPACITY;
+    if (batch == 0) return GFORB_OK;
+    FrameDev T = c.frame(F, batch);
+    GridGeom G = geom_of(F);
+    QParams P;
+    memset(&P, 0, sizeof(P));
+    fill_scale(M, P);
+    const size_t nm = (size_t)batch * mps->mp_stride;
+    P.mpU = c.in(mps->proj_x, nm); P.mpV = c.in(mps->proj_y, nm); P.mpCos = c.in(mps->view_cos, nm);
+    P.mpLevel = c.in(mps->scale_level, nm); P.mpFlags = c.in(mps->flags, nm); P.mpDesc = c.in(mps->descriptors, nm * 32);
+    P.mpCounts = c.in(mps->counts, (size_t)batch); P.mpStride = mps->mp_stride; P.th = th;
+    int32_t* dMp = c.out(frame_mappoints, (size_t)batch * F->kp_stride, true);
+    int32_t* dSc = c.out(match_score, (size_t)batch * F->kp_stride, true);
+    int32_t* dN = c.out(nmatches, (size_t)batch, false);
+    if (c.rc) return c.rc;
+    build_grid(M, c, T, G, batch);
+    run_candidates<M_MAP>(M, c, P, T, G, batch, mps->mp_stride);
+    RParams R;
+    memset(&R, 0, sizeof(R));
+    R.src = T; R.tgt = T; R.pool = M->d_pool; R.poolCap = M->poolCap; R.qMeta = M->d_qMeta; R.maxQ = M->cfg.max_queries;
+    R.maxKp = M->cfg.max_keypoints; R.qCounts = P.mpCounts; R.nnratio = nnratio; R.checkOri = 0;
+    R.tgtMp = dMp; R.tgtScore = dSc; R.nmatches = dN; R.rotBinQ = M->d_rotBinQ;
+    run_resolve<M_MAP>(M, c, R, batch);
+    return end_call(M, c, flags);
+}
+
+int gforb_search_by_projection_frames(GforbMatcher* M, const GforbFrameSet* cur, const GforbFrameSet* last, int batch,
+                                      const int32_t* last_mappoints, const uint8_t* last_outlier,
+                                      const float* last_world, const float* Tcw, float fx, float fy, float cx, float cy,
+                                      float th, float nnratio, int check_orientation, int32_t* cur_mappoints,
+                                      int32_t* cur_score, int32_t* nmatches, int flags, void* stream) {
+    Ctx c;
+    int rc = begin_call(M, batch, flags, stream, c);
+    if (rc) return rc;
+    if ((rc = check_frames(M, cur)) || (rc = check_frames(M, last))) return rc;
+    if (!last_mappoints || !last_world || !Tcw || !cur_mappoints || !cur_score || !nmatches) return GFORB_ERR_ARG;
+    if (last->kp_stride > M->cfg.max_queries) return GFORB_ERR_CAPACITY;
+    if (batch == 0) return GFORB_OK;
+    FrameDev T = c.frame(cur, batch), S = c.frame(last, batch);
+    GridGeom G = geom_of(cur);
+    QParams P;
+    memset(&P, 0, sizeof(P));
+    fill_scale(M, P);
+    const size_t ns = (size_t)batch * last->kp_stride;
+    P.src = S; P.srcMp = c.in(last_mappoints, ns); P.srcOutlier = c.in(last_outlier, ns);
+    P.srcWorld = c.in(last_world, ns * 3); P.Tcw = c.in(Tcw, (size_t)batch * 16);
+    P.fx = fx; P.fy = fy; P.cx = cx; P.cy = cy; P.th = th;
+    int32_t* dMp = c.out(cur_mappoints, (size_t)batch * cur->kp_stride, true);
+    int32_t* dSc = c.out(cur_score, (size_t)batch * cur->kp_stride, true);
+    int32_t* dN = c.out(nmatches, (size_t)batch, false);
+    if (c.rc) return c.rc;
+    build_grid(M, c, T, G, batch);
+    run_candidates<M_LAST>(M, c, P, T, G, batch, last->kp_stride);
+    RParams R;
+    memset(&R, 0, sizeof(R));
+    R.src = S; R.tgt = T; R.pool = M->d_pool; R.poolCap = M->poolCap; R.qMeta = M->d_qMeta; R.maxQ = M->cfg.max_queries;
+    R.maxKp = M->cfg.max_keypoints; R.qCounts = S.counts; R.srcMp = P.srcMp; R.nnratio = nnratio;
+    R.checkOri = check_orientation; R.tgtMp = dMp; R.tgtScore = dSc; R.nmatches = dN; R.rotBinQ = M->d_rotBinQ;
+    run_resolve<M_LAST>(M, c, R, batch);
+    return end_call(M, c, flags);
+}
+
+int gforb_window_search(GforbMatcher* M, const GforbFrameSet* F1, const GforbFrameSet* F2, int batch,
+                        const int32_t* f1_mappoints, int window_size, int min_scale_level, int max_scale_level,
+                        float nnratio, int check_orientation, int32_t* matches2, int32_t* nmatches, int flags,
+                        void* stream) {
+    Ctx c;
+    int rc = begin_call(M, batch, flags, stream, c);
+    if (rc) return rc;
+    if ((rc = check_frames(M, F1)) || (rc = check_frames(M, F2))) return rc;
+    if (!f1_mappoints || !matches2 || !nmatches) return GFORB_ERR_ARG;
+    if (F1->kp_stride > M->cfg.max_queries) return GFORB_ERR_CAPACITY;
+    if (batch == 0) return GFORB_OK;
+    FrameDev S = c.frame(F1, batch), T = c.frame(F2, batch);
+    GridGeom G = geom_of(F2);
+    QParams P;
+    memset(&P, 0, sizeof(P));
+    fill_scale(M, P);
+    P.src = S; P.srcMp = c.in(f1_mappoints, (size_t)batch * F1->kp_stride);
+    P.window = (float)window_size; P.minScaleLevel = min_scale_level; P.maxScaleLevel = max_scale_level;
+    int32_t* dM2 = c.out(matches2, (size_t)batch * F2->kp_stride, false);
+    int32_t* dN = c.out(nmatches, (size_t)batch, false);
+    if (c.rc) return c.rc;
+    build_grid(M, c, T, G, batch);
+    run_candidates<M_WINDOW>(M, c, P, T, G, batch, F1->kp_stride);
+    RParams R;
+    memset(&R, 0, sizeof(R));
+    R.src = S; R.tgt = T; R.pool = M->d_pool; R.poolCap = M->poolCap; R.qMeta = M->d_qMeta; R.maxQ = M->cfg.max_queries;
+    R.maxKp = M->cfg.max_keypoints; R.qCounts = S.counts; R.srcMp = P.srcMp; R.nnratio = nnratio;
+    R.checkOri = check_orientation; R.tgtMp = dM2; R.nmatches = dN; R.rotBinQ = M->d_rotBinQ;
+    run_resolve<M_WINDOW>(M, c, R, batch);
+    return end_call(M, c, flags);
+}
+
+int gforb_allpairs_top2(GforbMatcher* M, const uint8_t* queries, int n_q, const uint8_t* db, int64_t n_db,
+                        int64_t idx_base, uint64_t* out_keys, int flags, void* stream) {
+    if (!M || !queries || !db || !out_keys || n_q < 0 || n_db < 0) return GFORB_ERR_ARG;
+    if (!(flags & GFORB_IN_DEVICE) || !(flags & GFORB_OUT_DEVICE)) return GFORB_ERR_ARG;   // database lives in HBM
+    if (n_q == 0) return GFORB_OK;
+    GF_CUDA_OK(cudaSetDevice(M->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    M->lastLaunches = 0;
+    const int qTiles = (n_q + AP_THREADS * AP_R - 1) / (AP_THREADS * AP_R);
+    // chunk the shard so that the grid covers every SM several times; chunk rows <= 2^22 (packed key)
+    long long targetBlocks = (long long)M->numSMs * 8;
+    long long chunks = std::max<long long>(1, targetBlocks / qTiles);
+    long long chunkRows = (n_db + chunks - 1) / std::max<long long>(chunks, 1);
+    chunkRows = std::max<long long>(AP_TILE, ((chunkRows + AP_TILE - 1) / AP_TILE) * AP_TILE);
+    chunkRows = std::min<long long>(chunkRows, 1 << 22);
+    const int nChunks = (int)std::max<long long>(1, (n_db + chunkRows - 1) / chunkRows);
+    const size_t need = (size_t)nChunks * n_q * 2;
+    if (need > M->capPartial) {
+        if (M->d_partial) cudaFree(M->d_partial);
+        M->d_partial = nullptr;
+        GF_CUDA_OK(cudaMalloc((void**)&M->d_partial, need * sizeof(uint64_t)));
+        M->capPartial = need;
+    }
+    k_allpairs<<<dim3(qTiles, nChunks), AP_THREADS, 0, st>>>((const uint4*)queries, n_q, (const uint4*)db, n_db,
+                                                             (int)chunkRows, idx_base, M->d_partial);
+    k_top2_merge<<<(n_q + 255) / 256, 256, 0, st>>>(M->d_partial, nChunks, n_q, out_keys);
+    M->lastLaunches = 2;
+    GF_CUDA_OK(cudaGetLastError());
+    if (!(flags & GFORB_ASYNC)) GF_CUDA_OK(cudaStreamSynchronize(st));
+    return GFORB_OK;
+}
+
+int gforb_top2_merge(GforbMatcher* M, const uint64_t* gathered, int n_shards, int n_q, uint64_t* out_keys, int flags,
+                     void* stream) {
+    if (!M || !gathered || !out_keys || n_shards <= 0 || n_q < 0) return GFORB_ERR_ARG;
+    if (!(flags & GFORB_IN_DEVICE) || !(flags & GFORB_OUT_DEVICE)) return GFORB_ERR_ARG;
+    if (n_q == 0) return GFORB_OK;
+    GF_CUDA_OK(cudaSetDevice(M->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    k_top2_merge<<<(n_q + 255) / 256, 256, 0, st>>>(gathered, n_shards, n_q, out_keys);
+    M->lastLaunches = 1;
+    GF_CUDA_OK(cudaGetLastError());
+    if (!(flags & GFORB_ASYNC)) GF_CUDA_OK(cudaStreamSynchronize(st));
+    return GFORB_OK;
+}
+
+}  // extern "C"

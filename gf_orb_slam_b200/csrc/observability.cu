@@ -1,0 +1,833 @@
+// B200-native good-feature path of ORB_SLAM::Observability (reference include/Observability.h, include/Util.hpp,
+// src/Observability.cc), DIMENSION_OF_STATE_MODEL = 7 (position + quaternion).
+//
+//   host   updatePWLSVec / predictPWLSVec   13-state kinematics, a handful of 4x4 / 13x13 matrices per frame
+//                                            (Observability.h:222-295, Util.hpp:787-1005): plain host C++.
+//   K11    k_build_info     one thread per matched point: 2x7 measurement Jacobian (compute_H_subblock_simplied,
+//                           Observability.h:460-515), octave re-weighting (reWeightInfoMat, :517-596) and the 7x7
+//                           information block H^T H (src/Observability.cc:464-470), FP64.
+//   K12    k_select         one CTA per selection problem, persistent over all rounds of maxVolSelection_LazierGreedy
+//                           / maxVolDeletion_LazierGreedy / the full greedy (src/Observability.cc:2815-3029, 2339-2542,
+//                           3031-3139): glibc-TYPE_3 rand() stream re-implemented on the device (the reference draws
+//                           from the process-global rand()), one thread per sampled candidate evaluating
+//                           logDet(cur +- block) with a register-resident 7x7 Cholesky (Util.hpp:714-731), block
+//                           arg-max with "first drawn wins" ties, in-place update of the running matrix.
+// All double arithmetic is un-fused (this TU is built with --fmad=false) and follows the CPU operation order, so the
+// information blocks and Cholesky products are bit-identical to the scalar sequence; only log() may differ in the
+// last ulp (north_star tolerance on log-det scores: 1e-5 relative).
+#include <cfloat>
+#include <cmath>
+#include <cstring>
+#include <vector>
+#include "common.cuh"
+#include "host_util.h"
+
+namespace gforb {
+
+struct CamDev { double fu, fv, Cx, Cy; };
+
+// ------------------------------------------------------------------------------------------------ K11
+__device__ __forceinline__ void h_subblock(const double* __restrict__ Xv, const CamDev cam, const double Y0, const double Y1,
+                                           const double Y2, double (&H)[14], float& u, float& v, double& hz) {
+    const double r = Xv[3], x = Xv[4], y = Xv[5], z = Xv[6];
+    // q2r (Util.hpp:302-317)
+    double R[9];
+    R[0] = r * r + x * x - y * y - z * z; R[1] = 2.0 * (x * y - r * z);         R[2] = 2.0 * (z * x + r * y);
+    R[3] = 2.0 * (x * y + r * z);         R[4] = r * r - x * x + y * y - z * z; R[5] = 2.0 * (y * z - r * x);
+    R[6] = 2.0 * (z * x - r * y);         R[7] = 2.0 * (y * z + r * x);         R[8] = r * r - x * x - y * y + z * z;
+    // R_rw = inv(R): 3x3 cofactor inverse (arma::inv tiny-matrix path)
+    const double c00 = R[4] * R[8] - R[5] * R[7], c01 = R[5] * R[6] - R[3] * R[8], c02 = R[3] * R[7] - R[4] * R[6];
+    const double det = R[0] * c00 + R[1] * c01 + R[2] * c02;
+    const double id = 1.0 / det;
+    double W[9];
+    W[0] = c00 * id; W[1] = (R[2] * R[7] - R[1] * R[8]) * id; W[2] = (R[1] * R[5] - R[2] * R[4]) * id;
+    W[3] = c01 * id; W[4] = (R[0] * R[8] - R[2] * R[6]) * id; W[5] = (R[2] * R[3] - R[0] * R[5]) * id;
+    W[6] = c02 * id; W[7] = (R[1] * R[6] - R[0] * R[7]) * id; W[8] = (R[0] * R[4] - R[1] * R[3]) * id;
+    const double t0 = Y0 - Xv[0], t1 = Y1 - Xv[1], t2 = Y2 - Xv[2];
+    const double h0 = W[0] * t0 + W[1] * t1 + W[2] * t2;
+    const double h1 = W[3] * t0 + W[4] * t1 + W[5] * t2;
+    const double h2 = W[6] * t0 + W[7] * t1 + W[8] * t2;
+    hz = h2;
+    if (h2 > 0) {
+        u = (float)((double)(float)cam.fu * h0 / h2 + (double)(float)cam.Cx);
+        v = (float)((double)(float)cam.fv * h1 / h2 + (double)(float)cam.Cy);
+    } else { u = FLT_MAX; v = FLT_MAX; }
+    // dhu_dhrl (2x3 pinhole Jacobian; zeros when |hz| < 1e-6)
+    double J[6] = {0, 0, 0, 0, 0, 0};
+    if (!(fabs(h2) < 1e-6)) {
+        J[0] = cam.fu / h2; J[2] = -h0 * cam.fu / (h2 * h2);
+        J[4] = cam.fv / h2; J[5] = -h1 * cam.fv / (h2 * h2);
+    }
+    // H13 = -(dhu_dhrl * R_rw)
+#pragma unroll
+    for (int rr = 0; rr < 2; rr++)
+#pragma unroll
+        for (int c = 0; c < 3; c++) {
+            double s = 0;
+#pragma unroll
+            for (int k = 0; k < 3; k++) s += J[rr * 3 + k] * W[k * 3 + c];
+            H[rr * 7 + c] = -1.0 * s;
+        }
+    // H47 = dhu_dhrl * (dRq_times_a_by_dq(qconj(q), t_rw) * diag(1,-1,-1,-1))   (Util.hpp:391-438)
+    const double q0 = r, qx = -x, qy = -y, qz = -z;
+    const double d0[9] = {2 * q0, -2 * qz, 2 * qy, 2 * qz, 2 * q0, -2 * qx, -2 * qy, 2 * qx, 2 * q0};
+    const double dx[9] = {2 * qx, 2 * qy, 2 * qz, 2 * qy, -2 * qx, -2 * q0, 2 * qz, 2 * q0, -2 * qx};
+    const double dy[9] = {-2 * qy, 2 * qx, 2 * q0, 2 * qx, 2 * qy, 2 * qz, -2 * q0, 2 * qz, -2 * qy};
+    const double dz[9] = {-2 * qz, -2 * q0, 2 * qx, 2 * q0, -2 * qz, 2 * qy, 2 * qx, 2 * qy, 2 * qz};
+    double D[12];
+#pragma unroll
+    for (int rr = 0; rr < 3; rr++) {
+        D[rr * 4 + 0] = (d0[rr * 3] * t0 + d0[rr * 3 + 1] * t1 + d0[rr * 3 + 2] * t2) * 1.0;
+        D[rr * 4 + 1] = (dx[rr * 3] * t0 + dx[rr * 3 + 1] * t1 + dx[rr * 3 + 2] * t2) * -1.0;
+        D[rr * 4 + 2] = (dy[rr * 3] * t0 + dy[rr * 3 + 1] * t1 + dy[rr * 3 + 2] * t2) * -1.0;
+        D[rr * 4 + 3] = (dz[rr * 3] * t0 + dz[rr * 3 + 1] * t1 + dz[rr * 3 + 2] * t2) * -1.0;
+    }
+#pragma unroll
+    for (int rr = 0; rr < 2; rr++)
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+            double s = 0;
+#pragma unroll
+            for (int k = 0; k < 3; k++) s += J[rr * 3 + k] * D[k * 4 + c];
+            H[rr * 7 + 3 + c] = s;
+        }
+}
+
+// mode 0: batchInfoMat_Frame (valid[] gate, sigma2 = levelSigma2[octave], score = match score)
+// mode 1: batchInfoMat_Map   (trackInView gate unless check_viz, identity noise, score 1 / -1 / -2 untouched)
+__global__ void __launch_bounds__(128) k_build_info(int mode, const double* __restrict__ Xv, CamDev cam,
+                                                    const float* __restrict__ world, const int32_t* __restrict__ octave,
+                                                    const int32_t* __restrict__ score, const uint8_t* __restrict__ gate,
+                                                    const int32_t* __restrict__ counts, int stride,
+                                                    const float* __restrict__ levelSigma2, int nlevels, int checkViz,
+                                                    int minX, int maxX, int minY, int maxY, double boundX, double boundY,
+                                                    double boundDepth, double* __restrict__ blocks,
+                                                    double* __restrict__ obsScore, double* __restrict__ Hmeas,
+                                                    float* __restrict__ uv) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x, b = blockIdx.y;
+    if (i >= min(counts[b], stride)) return;
+    const size_t p = (size_t)b * stride + i;
+    if (mode == 0) {
+        if (!gate[p]) { obsScore[p] = -1.0; return; }
+    } else {
+        obsScore[p] = -2.0;
+        if (!checkViz && !gate[p]) return;
+    }
+    double H[14];
+    float u, v;
+    double hz;
+    h_subblock(Xv + (size_t)b * 13, cam, (double)world[p * 3], (double)world[p * 3 + 1], (double)world[p * 3 + 2], H, u, v, hz);
+    if (uv) { uv[p * 2] = u; uv[p * 2 + 1] = v; }
+    if (mode == 1 && checkViz) {
+        bool ok = true;
+        if (hz < 0.0 + boundDepth) ok = false;
+        if ((double)u < (double)minX - boundX || (double)u > (double)maxX + boundX) ok = false;
+        if ((double)v < (double)minY - boundY || (double)v > (double)maxY + boundY) ok = false;
+        if (!ok) { obsScore[p] = -1.0; return; }
+    }
+    if (Hmeas)
+#pragma unroll
+        for (int k = 0; k < 14; k++) Hmeas[p * 14 + k] = H[k];
+    double sigma2 = 1.0;
+    if (mode == 0) sigma2 = (double)levelSigma2[min(max(octave[p], 0), nlevels - 1)];
+    const double wi = 1.0 / sqrt(sigma2);
+    double Hr[14];
+#pragma unroll
+    for (int k = 0; k < 14; k++) Hr[k] = wi * H[k];
+    double* o = blocks + p * 49;
+#pragma unroll
+    for (int rr = 0; rr < 7; rr++)
+#pragma unroll
+        for (int c = 0; c < 7; c++) o[rr * 7 + c] = Hr[rr] * Hr[c] + Hr[7 + rr] * Hr[7 + c];
+    obsScore[p] = (mode == 0) ? (double)score[p] : 1.0;
+}
+
+// ------------------------------------------------------------------------------------------------ logDet
+#define LT(i, j) ((i) * ((i) + 1) / 2 + (j))
+
+// left-looking unblocked Cholesky of the lower triangle A (packed, 28 doubles) -> product of the diagonal of L
+__device__ __forceinline__ bool chol7_prod(const double (&A)[28], double& prod) {
+    double L[28];
+#pragma unroll
+    for (int j = 0; j < 7; j++) {
+        double ajj = A[LT(j, j)];
+#pragma unroll
+        for (int k = 0; k < j; k++) ajj -= L[LT(j, k)] * L[LT(j, k)];
+        if (!(ajj > 0.0)) return false;
+        ajj = sqrt(ajj);
+        L[LT(j, j)] = ajj;
+        const double rinv = 1.0 / ajj;
+#pragma unroll
+        for (int i = j + 1; i < 7; i++) {
+            double s = A[LT(i, j)];
+#pragma unroll
+            for (int k = 0; k < j; k++) s -= L[LT(i, k)] * L[LT(j, k)];
+            L[LT(i, j)] = s * rinv;
+        }
+    }
+    double p = 1.0;
+#pragma unroll
+    for (int j = 0; j < 7; j++) p *= L[LT(j, j)];
+    prod = p;
+    return true;
+}
+
+// arma::log_det fallback: LU with partial pivoting on the full matrix, sum log|u_ii| (rare path, local memory)
+__device__ __noinline__ double lu7_logabsdet(const double* __restrict__ cur, const double* __restrict__ blk, double sgn) {
+    double A[49];
+    for (int i = 0; i < 49; i++) A[i] = cur[i] + sgn * blk[i];
+    double ld = 0;
+    for (int k = 0; k < 7; k++) {
+        int p = k;
+        for (int i = k + 1; i < 7; i++) if (fabs(A[i * 7 + k]) > fabs(A[p * 7 + k])) p = i;
+        if (p != k) for (int c = 0; c < 7; c++) { double t = A[k * 7 + c]; A[k * 7 + c] = A[p * 7 + c]; A[p * 7 + c] = t; }
+        const double piv = A[k * 7 + k];
+        ld += log(fabs(piv));
+        if (piv == 0) continue;
+        for (int i = k + 1; i < 7; i++) {
+            const double f = A[i * 7 + k] / piv;
+            for (int c = k + 1; c < 7; c++) A[i * 7 + c] -= f * A[k * 7 + c];
+        }
+    }
+    return ld;
+}
+
+// logDet(cur + sgn * blk), both 7x7 row-major (cur in shared memory, blk in global memory)
+__device__ __forceinline__ double logdet_sum(const double* __restrict__ cur, const double* __restrict__ blk, double sgn) {
+    double A[28];
+#pragma unroll
+    for (int i = 0; i < 7; i++)
+#pragma unroll
+        for (int j = 0; j <= i; j++) A[LT(i, j)] = cur[i * 7 + j] + sgn * blk[i * 7 + j];
+    double p;
+    if (chol7_prod(A, p)) return 2 * log(p);
+    return lu7_logabsdet(cur, blk, sgn);
+}
+
+__global__ void __launch_bounds__(128) k_logdet(const double* __restrict__ mats, int n, double* __restrict__ out) {
+    __shared__ double zero[49];
+    if (threadIdx.x < 49) zero[threadIdx.x] = 0.0;
+    __syncthreads();
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = logdet_sum(zero, mats + (size_t)i * 49, 1.0);
+}
+
+// ------------------------------------------------------------------------------------------------ glibc rand()
+// TYPE_3 additive feedback generator: r[i] = r[i-31] + r[i-3], output r[i] >> 1.
+struct GlibcRand {
+    uint32_t* r;    // 34-entry ring in shared memory
+    int i;          // next state index (mod 34)
+    __device__ void seed(uint32_t s) {
+        if (s == 0) s = 1;
+        int32_t word = (int32_t)s;
+        r[0] = s;
+        for (int k = 1; k < 31; k++) {
+            const int32_t hi = word / 127773, lo = word % 127773;
+            word = 16807 * lo - 2836 * hi;
+            if (word < 0) word += 2147483647;
+            r[k] = (uint32_t)word;
+        }
+        for (int k = 31; k < 34; k++) r[k] = r[k - 31];
+        i = 0;          // ring position of state index 34
+        for (int k = 0; k < 310; k++) next();
+    }
+    __device__ __forceinline__ uint32_t next() {
+        // state index n = 34 + (calls so far); ring slot = n % 34
+        const int a = (i + 3) % 34;       // n - 31  == n + 3 (mod 34)
+        const int c = (i + 31) % 34;      // n - 3
+        const uint32_t v = r[a] + r[c];
+        r[i] = v;
+        i = (i + 1) % 34;
+        return v >> 1;
+    }
+};
+
+__global__ void k_rand_stream(uint32_t seed, int n, int32_t* out) {
+    __shared__ uint32_t ring[34];
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        GlibcRand g; g.r = ring; g.seed(seed);
+        for (int k = 0; k < n; k++) out[k] = (int32_t)g.next();
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ K12 selection
+enum { MTD_GREEDY = 1, MTD_LAZIER_SELECT = 2, MTD_LAZIER_AUTO = 3, MTD_LAZIER_DELETE = 5 };
+static const int SEL_THREADS = 256;
+static const int MAX_RANDOM_QUERY_TIME = 2000;
+
+struct SelParams {
+    const double* blocks;      // batch x stride x 49
+    const double* obsScore;    // batch x stride (may be null: all valid)
+    const int32_t* counts;     // batch
+    const uint32_t* seeds;     // batch (may be null: seed 1 == the never-seeded reference process)
+    int stride, k, mtd, maxPoints;
+    double sampleScale;
+    int32_t* outIdx;           // batch x outStride
+    double* outLogdet;         // batch x outStride (may be null)
+    int32_t* outN;             // batch
+    int outStride;
+};
+
+__global__ void __launch_bounds__(SEL_THREADS) k_select(const SelParams P) {
+    extern __shared__ __align__(16) unsigned char smraw[];
+    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int n = min(P.counts[b], min(P.stride, P.maxPoints));
+    int* idxA = reinterpret_cast<int*>(smraw);
+    int* visA = idxA + P.maxPoints;
+    int* idxB = visA + P.maxPoints;
+    int* visB = idxB + P.maxPoints;
+    int* list = visB + P.maxPoints;
+    unsigned char* alive = reinterpret_cast<unsigned char*>(list + P.maxPoints);   // `selected` flag per pool entry
+    __shared__ double cur[49];
+    __shared__ double redV[SEL_THREADS / 32];
+    __shared__ int redT[SEL_THREADS / 32];
+    __shared__ uint32_t ring[34];
+    __shared__ int s_cnt, s_pick, s_pos;
+    __shared__ double s_val;
+    const double* blk = P.blocks + (size_t)b * P.stride * 49;
+    const double* sc = P.obsScore ? P.obsScore + (size_t)b * P.stride : nullptr;
+    int32_t* outIdx = P.outIdx + (size_t)b * P.outStride;
+    double* outLd = P.outLogdet ? P.outLogdet + (size_t)b * P.outStride : nullptr;
+    const int k = P.k;
+    if (n <= 0) { if (tid == 0) P.outN[b] = 0; return; }
+    if (k >= n) {        // "if (mpLimit >= edIdx - stIdx) take all" (:2832-2840)
+        for (int i = tid; i < n && i < P.outStride; i += SEL_THREADS) { outIdx[i] = i; if (outLd) outLd[i] = 0.0; }
+        if (tid == 0) P.outN[b] = min(n, P.outStride);
+        return;
+    }
+    int mtd = P.mtd;
+    if (mtd == MTD_LAZIER_AUTO) mtd = ((size_t)k * 2 > (size_t)n) ? MTD_LAZIER_DELETE : MTD_LAZIER_SELECT;   // :3141-3155
+    const bool deletion = mtd == MTD_LAZIER_DELETE;
+    const double sgn = deletion ? -1.0 : 1.0;
+    const size_t szLazier = (size_t)((double)n / (double)k * P.sampleScale);
+    // init
+    if (tid < 49) cur[tid] = (tid % 8 == 0) ? 0.00001 : 0.0;
+    for (int i = tid; i < n; i += SEL_THREADS) { idxA[i] = i; visA[i] = -1; alive[i] = deletion ? 1 : 0; }
+    __syncthreads();
+    if (deletion && tid < 49) {       // curMat += every block, in pool order (:2370-2380)
+        double s = cur[tid];
+        for (int i = 0; i < n; i++) s = s + blk[(size_t)i * 49 + tid];
+        cur[tid] = s;
+    }
+    GlibcRand rng;
+    rng.r = ring; rng.i = 0;
+    if (tid == 0 && mtd != MTD_GREEDY) rng.seed(P.seeds ? P.seeds[b] : 1u);
+    __syncthreads();
+    int m = n;                        // live columns of lmkIdx / lmkVisited
+    int* idx = idxA; int* vis = visA; int* idx2 = idxB; int* vis2 = visB;
+    const int rounds = deletion ? n - k : k;
+    int nOut = 0;
+    for (int i = 0; i < rounds; i++) {
+        // ---- candidate list of this round, in evaluation order
+        if (mtd == MTD_GREEDY) {
+            // full greedy == the reference's lazy greedy with the sum-log-diag bound (:3031-3139): evaluate every
+            // unselected valid entry (ties -> lowest pool index)
+            if (tid == 0) s_cnt = 0;
+            __syncthreads();
+            for (int base = 0; base < m; base += SEL_THREADS) {
+                const int j = base + tid;
+                const bool ok = j < m && !(sc && sc[idx[j]] < 0);
+                const unsigned bal = __ballot_sync(0xffffffffu, ok);
+                if (lane == 0) redT[warp] = __popc(bal);
+                __syncthreads();
+                int off = s_cnt;
+                for (int w = 0; w < warp; w++) off += redT[w];
+                if (ok) list[off + __popc(bal & ((1u << lane) - 1u))] = idx[j];
+                __syncthreads();
+                if (tid == 0) { int t = 0; for (int w = 0; w < SEL_THREADS / 32; w++) t += redT[w]; s_cnt += t; }
+                __syncthreads();
+            }
+        } else if (tid == 0) {
+            size_t numHit = 0, szActual = szLazier;
+            if ((size_t)m < szActual) szActual = (size_t)m;
+            int cnt = 0;
+            while (numHit < szActual) {
+                int j = 0, numRndQue = 0;
+                while (numRndQue < MAX_RANDOM_QUERY_TIME) {
+                    j = (int)(rng.next() % (uint32_t)m);
+                    if (vis[j] < i) { vis[j] = i; break; }
+                    ++numRndQue;
+                }
+                if (numRndQue >= MAX_RANDOM_QUERY_TIME) break;
+                const int que = idx[j];
+                ++numHit;
+                const bool sel = alive[que] != 0;
+                if ((deletion ? !sel : sel) || (sc && sc[que] < 0)) { --numHit; continue; }
+                list[cnt++] = que;
+            }
+            s_cnt = cnt;
+        }
+        __syncthreads();
+        const int cnt = s_cnt;
+        // ---- evaluate logDet(cur +- block) for every candidate; arg-max, first in list wins ties (strict >)
+        double bestV = -DBL_MAX; int bestT = INT_MAX;
+        for (int t = tid; t < cnt; t += SEL_THREADS) {
+            const double v = logdet_sum(cur, blk + (size_t)list[t] * 49, sgn);
+            if (v > bestV) { bestV = v; bestT = t; }
+        }
+#pragma unroll
+        for (int d = 16; d >= 1; d >>= 1) {
+            const double ov = __shfl_xor_sync(0xffffffffu, bestV, d);
+            const int ot = __shfl_xor_sync(0xffffffffu, bestT, d);
+            if (ov > bestV || (ov == bestV && ot < bestT)) { bestV = ov; bestT = ot; }
+        }
+        if (lane == 0) { redV[warp] = bestV; redT[warp] = bestT; }
+        __syncthreads();
+        if (tid == 0) {
+            double v = redV[0]; int t = redT[0];
+            for (int w = 1; w < SEL_THREADS / 32; w++)
+                if (redV[w] > v || (redV[w] == v && redT[w] < t)) { v = redV[w]; t = redT[w]; }
+            s_pick = (t == INT_MAX) ? -1 : list[t];
+            s_val = v;
+            s_pos = -1;
+        }
+        __syncthreads();
+        const int pick = s_pick;
+        if (pick < 0) break;                                  // "if (maxLmk == -1) break"
+        // ---- update the running matrix, record the pick, erase its column (order preserved)
+        if (tid < 49) cur[tid] = cur[tid] + sgn * blk[(size_t)pick * 49 + tid];
+        if (tid == 0) {
+            alive[pick] = deletion ? 0 : 1;
+            if (!deletion && i < P.outStride) { outIdx[i] = pick; if (outLd) outLd[i] = s_val; }
+        }
+        if (!deletion) nOut = i + 1;
+        for (int j = tid; j < m; j += SEL_THREADS) if (idx[j] == pick) s_pos = j;
+        __syncthreads();
+        const int pos = s_pos;
+        for (int j = tid; j < m; j += SEL_THREADS) {
+            if (j < pos) { idx2[j] = idx[j]; vis2[j] = vis[j]; }
+            else if (j > pos) { idx2[j - 1] = idx[j]; vis2[j - 1] = vis[j]; }
+        }
+        m -= 1;
+        { int* t = idx; idx = idx2; idx2 = t; t = vis; vis = vis2; vis2 = t; }
+        __syncthreads();
+    }
+    if (deletion) {
+        // survivors in ascending pool order (:2530-2540); single warp, ordered compaction
+        __syncthreads();
+        if (warp == 0) {
+            int off = 0;
+            for (int base = 0; base < n; base += 32) {
+                const int j = base + lane;
+                const bool ok = j < n && alive[j];
+                const unsigned bal = __ballot_sync(0xffffffffu, ok);
+                const int o = off + __popc(bal & ((1u << lane) - 1u));
+                if (ok && o < P.outStride) { outIdx[o] = j; if (outLd) outLd[o] = 0.0; }
+                off += __popc(bal);
+            }
+            if (lane == 0) P.outN[b] = min(off, P.outStride);
+        }
+    } else if (tid == 0) P.outN[b] = min(nOut, P.outStride);
+}
+
+}  // namespace gforb
+
+using namespace gforb;
+
+// ================================================================================================ host side
+struct KineSeg {
+    double dt, dt_inSeg;
+    double Xv[13], F_Q[16], F_Omg[12], F[169], F_Q_inSeg[16], F_Omg_inSeg[12], F_inSeg[169];
+    float Tcw[16];
+};
+
+struct GforbObs {
+    GforbObsConfig cfg;
+    int device = 0, lastLaunches = 0;
+    double Xv[13];
+    std::vector<KineSeg> kine;
+    Arena arena;
+    int* d_err = nullptr;
+    std::vector<OutCopy> outs;
+};
+
+namespace {
+
+// ---- 13-state kinematics (include/Util.hpp:440-494, 541-605, 683-697, 787-1005), all on the host
+double nrm3(const double* v) { return std::sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]); }
+
+void dcm_to_quat_f(const float* a, double* q) {      // DCM2QUAT_float
+    const float tr = a[0] + a[4] + a[8];
+    if (tr > 0) {
+        const float s = sqrtf(tr + 1.0f) * 2;
+        q[0] = 0.25f * s; q[1] = (a[7] - a[5]) / s; q[2] = (a[2] - a[6]) / s; q[3] = (a[3] - a[1]) / s;
+    } else if (a[0] > a[4] && a[0] > a[8]) {
+        const float s = 2.0f * sqrtf(1.0f + a[0] - a[4] - a[8]);
+        q[0] = (a[7] - a[5]) / s; q[1] = 0.25f * s; q[2] = (a[1] + a[3]) / s; q[3] = (a[2] + a[6]) / s;
+    } else if (a[4] > a[8]) {
+        const float s = 2.0f * sqrtf(1.0f + a[4] - a[0] - a[8]);
+        q[0] = (a[2] - a[6]) / s; q[1] = (a[1] + a[3]) / s; q[2] = 0.25f * s; q[3] = (a[5] + a[7]) / s;
+    } else {
+        const float s = 2.0f * sqrtf(1.0f + a[8] - a[0] - a[4]);
+        q[0] = (a[3] - a[1]) / s; q[1] = (a[2] + a[6]) / s; q[2] = (a[5] + a[7]) / s; q[3] = 0.25f * s;
+    }
+    if (q[0] < 0) for (int i = 0; i < 4; i++) q[i] = -1.0 * q[i];
+}
+
+void inv4_f(const float* Af, float* out) {            // cv::Mat::inv() (LU, partial pivoting) on 4x4 CV_32F
+    double A[16], I[16];
+    for (int i = 0; i < 16; i++) { A[i] = Af[i]; I[i] = (i % 5 == 0) ? 1.0 : 0.0; }
+    for (int k = 0; k < 4; k++) {
+        int p = k;
+        for (int i = k + 1; i < 4; i++) if (std::fabs(A[i * 4 + k]) > std::fabs(A[p * 4 + k])) p = i;
+        if (p != k) for (int c = 0; c < 4; c++) { std::swap(A[k * 4 + c], A[p * 4 + c]); std::swap(I[k * 4 + c], I[p * 4 + c]); }
+        const double d = 1.0 / A[k * 4 + k];
+        for (int c = 0; c < 4; c++) { A[k * 4 + c] *= d; I[k * 4 + c] *= d; }
+        for (int i = 0; i < 4; i++) {
+            if (i == k) continue;
+            const double f = A[i * 4 + k];
+            for (int c = 0; c < 4; c++) { A[i * 4 + c] -= f * A[k * 4 + c]; I[i * 4 + c] -= f * I[k * 4 + c]; }
+        }
+    }
+    for (int i = 0; i < 16; i++) out[i] = (float)I[i];
+}
+
+void dq_by_domega(const double* w, double dt, double* RES /*4x3*/) {     // dqomegadt_by_domega
+    const double m = nrm3(w);
+    if (std::fabs(m) < 1e-8) {
+        for (int i = 0; i < 12; i++) RES[i] = 0;
+        RES[3] = RES[7] = RES[11] = dt / 2;
+        return;
+    }
+    const double sh = std::sin(m * dt / 2.0), ch = std::cos(m * dt / 2.0);
+    for (int c = 0; c < 3; c++) RES[c] = (-dt / 2.0) * (w[c] / m) * sh;
+    for (int r = 0; r < 3; r++)
+        for (int c = 0; c < 3; c++) {
+            if (r == c)
+                RES[(r + 1) * 3 + c] = (dt / 2.0) * w[r] * w[r] / (m * m) * ch + (1.0 / m) * (1.0 - w[r] * w[r] / (m * m)) * sh;
+            else
+                RES[(r + 1) * 3 + c] = (w[r] * w[c] / (m * m)) * ((dt / 2.0) * ch - (1.0 / m) * sh);
+        }
+}
+
+void f_subblock(const double* Xv, double dt, double* F_Q, double* F_Omg) {   // compute_F_subblock
+    const double* w = Xv + 10;
+    const double* qo = Xv + 3;
+    const double v[3] = {w[0] * dt, w[1] * dt, w[2] * dt};
+    const double theta = nrm3(v);
+    double q[4] = {1, 0, 0, 0};
+    if (!(theta < 1e-6)) {
+        const double vn[3] = {v[0] / theta, v[1] / theta, v[2] / theta};
+        const double nn = nrm3(vn), s = std::sin(theta / 2.0);
+        q[0] = std::cos(theta / 2.0);
+        for (int i = 0; i < 3; i++) q[i + 1] = s * (vn[i] / nn);
+    }
+    {
+        const double R = q[0], X = q[1], Y = q[2], Z = q[3];
+        const double fq[16] = {R, -X, -Y, -Z, X, R, Z, -Y, Y, -Z, R, X, Z, Y, -X, R};
+        memcpy(F_Q, fq, sizeof(fq));
+    }
+    const double R = qo[0], X = qo[1], Y = qo[2], Z = qo[3];
+    const double d31[16] = {R, -X, -Y, -Z, X, R, -Z, Y, Y, Z, R, -X, Z, -Y, X, R};
+    double dq[12];
+    dq_by_domega(w, dt, dq);
+    for (int r = 0; r < 4; r++)
+        for (int c = 0; c < 3; c++) {
+            double s = 0;
+            for (int k = 0; k < 4; k++) s += d31[r * 4 + k] * dq[k * 3 + c];
+            F_Omg[r * 3 + c] = s;
+        }
+}
+
+void assemble_F(double dt, const double* F_Q, const double* F_Omg, double* F) {
+    for (int i = 0; i < 169; i++) F[i] = (i % 14 == 0) ? 1.0 : 0.0;
+    F[7] = dt; F[13 + 8] = dt; F[26 + 9] = dt;
+    for (int r = 0; r < 4; r++) {
+        for (int c = 0; c < 4; c++) F[(3 + r) * 13 + 3 + c] = F_Q[r * 4 + c];
+        for (int c = 0; c < 3; c++) F[(3 + r) * 13 + 10 + c] = F_Omg[r * 3 + c];
+    }
+}
+
+void pwls_to_homo(const double* p, float* Tcw) {      // convert_PWLS_Vec_To_Homo (+ QUAT2DCM_float)
+    const double x = p[4], y = p[5], z = p[6], r = p[3];
+    float Rwc[9];
+    Rwc[0] = r * r + x * x - y * y - z * z; Rwc[1] = 2.0 * (x * y - r * z);         Rwc[2] = 2.0 * (z * x + r * y);
+    Rwc[3] = 2.0 * (x * y + r * z);         Rwc[4] = r * r - x * x + y * y - z * z; Rwc[5] = 2.0 * (y * z - r * x);
+    Rwc[6] = 2.0 * (z * x - r * y);         Rwc[7] = 2.0 * (y * z + r * x);         Rwc[8] = r * r - x * x - y * y + z * z;
+    const float twc[3] = {(float)p[0], (float)p[1], (float)p[2]};
+    for (int i = 0; i < 16; i++) Tcw[i] = (i % 5 == 0) ? 1.f : 0.f;
+    for (int rr = 0; rr < 3; rr++) {
+        double s = 0;
+        for (int c = 0; c < 3; c++) { Tcw[rr * 4 + c] = Rwc[c * 3 + rr]; s += (double)(-Rwc[c * 3 + rr]) * twc[c]; }
+        Tcw[rr * 4 + 3] = (float)s;
+    }
+}
+
+void propagate(const KineSeg& cur, double* next) {   // propagate_PWLS
+    for (int i = 0; i < 13; i++) next[i] = cur.Xv[i];
+    for (int i = 0; i < 3; i++) next[i] = cur.Xv[i] + cur.Xv[7 + i] * cur.dt;
+    const double v[3] = {cur.Xv[10] * cur.dt, cur.Xv[11] * cur.dt, cur.Xv[12] * cur.dt};
+    double a = nrm3(v), u[3] = {0, 0, 0};
+    if (a > 0.0000001) { u[0] = v[0] / a; u[1] = v[1] / a; u[2] = v[2] / a; } else a = 0;
+    const double q2[4] = {std::cos(a / 2), u[0] * std::sin(a / 2), u[1] * std::sin(a / 2), u[2] * std::sin(a / 2)};
+    const double* q1 = cur.Xv + 3;
+    const double A = q1[0], B = q1[1], C = q1[2], D = q1[3], W = q2[0], X = q2[1], Y = q2[2], Z = q2[3];
+    const double qr[4] = {A * W - B * X - C * Y - D * Z, A * X + B * W + C * Z - D * Y, A * Y - B * Z + C * W + D * X,
+                          A * Z + B * Y - C * X + D * W};
+    const double n = std::sqrt(qr[0] * qr[0] + qr[1] * qr[1] + qr[2] * qr[2] + qr[3] * qr[3]);
+    for (int i = 0; i < 4; i++) next[3 + i] = qr[i] / n;
+}
+
+struct OCtx {
+    GforbObs* O;
+    cudaStream_t st;
+    bool inDev, outDev;
+    int rc = GFORB_OK;
+    template <class T>
+    const T* in(const T* p, size_t n) {
+        if (!p || rc) return p;
+        if (inDev) return p;
+        T* d = (T*)O->arena.take(n * sizeof(T));
+        if (!d) { rc = GFORB_ERR_CAPACITY; return nullptr; }
+        if (cudaMemcpyAsync(d, p, n * sizeof(T), cudaMemcpyHostToDevice, st) != cudaSuccess) rc = GFORB_ERR_CUDA;
+        return d;
+    }
+    template <class T>
+    T* out(T* p, size_t n) {
+        if (!p || rc) return p;
+        if (outDev) return p;
+        T* d = (T*)O->arena.take(n * sizeof(T));
+        if (!d) { rc = GFORB_ERR_CAPACITY; return nullptr; }
+        O->outs.push_back(OutCopy{p, d, n * sizeof(T)});
+        return d;
+    }
+};
+
+int obs_begin(GforbObs* O, int batch, int stride, int flags, void* stream, OCtx& c) {
+    if (!O || batch < 0 || stride < 0) return GFORB_ERR_ARG;
+    if (batch > O->cfg.max_batch || stride > O->cfg.max_points) return GFORB_ERR_CAPACITY;
+    GF_CUDA_OK(cudaSetDevice(O->device));
+    c.O = O; c.st = (cudaStream_t)stream;
+    c.inDev = (flags & GFORB_IN_DEVICE) != 0; c.outDev = (flags & GFORB_OUT_DEVICE) != 0;
+    O->arena.reset();
+    O->outs.clear();
+    O->lastLaunches = 0;
+    return GFORB_OK;
+}
+
+int obs_end(GforbObs* O, OCtx& c, int flags) {
+    if (c.rc) return c.rc;
+    GF_CUDA_OK(cudaGetLastError());
+    for (auto& o : O->outs) GF_CUDA_OK(cudaMemcpyAsync(o.host, o.dev, o.bytes, cudaMemcpyDeviceToHost, c.st));
+    if (!(flags & GFORB_ASYNC) || !O->outs.empty()) GF_CUDA_OK(cudaStreamSynchronize(c.st));
+    return GFORB_OK;
+}
+
+size_t select_smem(int maxPoints) { return (size_t)maxPoints * (5 * sizeof(int) + 1) + 16; }
+
+}  // namespace
+
+extern "C" {
+
+int gforb_obs_create(const GforbObsConfig* cfg, GforbObs** out) {
+    if (!cfg || !out) return GFORB_ERR_ARG;
+    *out = nullptr;
+    if (cfg->max_batch <= 0 || cfg->max_points <= 0 || cfg->max_points > 8192 || !(cfg->fu != 0) || !(cfg->fv != 0)) return GFORB_ERR_ARG;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0 || cfg->device < 0 || cfg->device >= ndev) {
+        fprintf(stderr, "[gforb] no usable CUDA device (requested %d of %d): the B200 path has no CPU fallback\n", cfg->device, ndev);
+        return GFORB_ERR_CUDA;
+    }
+    GF_CUDA_OK(cudaSetDevice(cfg->device));
+    GforbObs* O = new GforbObs();
+    O->cfg = *cfg;
+    O->device = cfg->device;
+    for (int i = 0; i < 13; i++) O->Xv[i] = 0;
+    const size_t B = cfg->max_batch, N = cfg->max_points;
+    // staging for host-pointer calls: world/octave/score/gate in, blocks + H + scores + uv + selection out
+    GF_CUDA_OK(O->arena.init(B * N * (12 + 4 + 4 + 1 + 392 + 112 + 8 + 8 + 4 + 8 + 64) + B * 256 + (1u << 20)));
+    GF_CUDA_OK(cudaMalloc((void**)&O->d_err, sizeof(int)));
+    GF_CUDA_OK(cudaFuncSetAttribute(k_select, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)select_smem(cfg->max_points)));
+    *out = O;
+    return GFORB_OK;
+}
+
+int gforb_obs_destroy(GforbObs* O) {
+    if (!O) return GFORB_ERR_ARG;
+    cudaSetDevice(O->device);
+    O->arena.release();
+    if (O->d_err) cudaFree(O->d_err);
+    delete O;
+    return GFORB_OK;
+}
+
+int gforb_obs_last_launches(const GforbObs* O) { return O ? O->lastLaunches : GFORB_ERR_ARG; }
+
+int gforb_obs_set_state(GforbObs* O, const double* Xv13) {
+    if (!O || !Xv13) return GFORB_ERR_ARG;
+    memcpy(O->Xv, Xv13, sizeof(O->Xv));
+    return GFORB_OK;
+}
+int gforb_obs_get_state(const GforbObs* O, double* Xv13) {
+    if (!O || !Xv13) return GFORB_ERR_ARG;
+    memcpy(Xv13, O->Xv, sizeof(O->Xv));
+    return GFORB_OK;
+}
+
+int gforb_obs_update_pwls(GforbObs* O, double t_prev, const float* Tcw_prev, double t_cur, const float* Twc_cur) {
+    if (!O || !Tcw_prev || !Twc_cur) return GFORB_ERR_ARG;
+    double* Xv = O->Xv;
+    for (int i = 0; i < 13; i++) Xv[i] = 0;
+    Xv[0] = Twc_cur[3]; Xv[1] = Twc_cur[7]; Xv[2] = Twc_cur[11];
+    const float R[9] = {Twc_cur[0], Twc_cur[1], Twc_cur[2], Twc_cur[4], Twc_cur[5], Twc_cur[6], Twc_cur[8], Twc_cur[9], Twc_cur[10]};
+    dcm_to_quat_f(R, Xv + 3);
+    float P[16], Trel[16];
+    for (int r = 0; r < 4; r++)
+        for (int c = 0; c < 4; c++) {
+            double s = 0;
+            for (int k = 0; k < 4; k++) s += (double)Tcw_prev[r * 4 + k] * Twc_cur[k * 4 + c];
+            P[r * 4 + c] = (float)s;
+        }
+    inv4_f(P, Trel);
+    const float dtf = float(t_cur - t_prev);
+    Xv[7] = Trel[3] / dtf; Xv[8] = Trel[7] / dtf; Xv[9] = Trel[11] / dtf;
+    const float o21 = Trel[9] - Trel[6], o02 = Trel[2] - Trel[8], o10 = Trel[4] - Trel[1];
+    Xv[10] = 0.5 * o21 / dtf; Xv[11] = 0.5 * o02 / dtf; Xv[12] = 0.5 * o10 / dtf;
+    return GFORB_OK;
+}
+
+int gforb_obs_predict_pwls(GforbObs* O, double dt, int num_seg) {
+    if (!O || num_seg < 0) return GFORB_ERR_ARG;
+    double cur[13];
+    memcpy(cur, O->Xv, sizeof(cur));
+    O->kine.clear();
+    for (int i = 0; i < num_seg; i++) {
+        KineSeg k;
+        k.dt = float(dt);
+        k.dt_inSeg = k.dt / float(13);
+        memcpy(k.Xv, cur, sizeof(cur));
+        pwls_to_homo(k.Xv, k.Tcw);
+        f_subblock(k.Xv, k.dt_inSeg, k.F_Q_inSeg, k.F_Omg_inSeg);
+        assemble_F(k.dt_inSeg, k.F_Q_inSeg, k.F_Omg_inSeg, k.F_inSeg);
+        f_subblock(k.Xv, k.dt, k.F_Q, k.F_Omg);
+        assemble_F(k.dt, k.F_Q, k.F_Omg, k.F);
+        propagate(k, cur);
+        O->kine.push_back(k);
+    }
+    return GFORB_OK;
+}
+
+int gforb_obs_num_segments(const GforbObs* O) { return O ? (int)O->kine.size() : GFORB_ERR_ARG; }
+
+int gforb_obs_get_segment(const GforbObs* O, int seg, double* Xv13, double* F169, double* F_Q16, double* F_Omg12,
+                          double* F_Q_inSeg16, double* F_Omg_inSeg12, float* Tcw16) {
+    if (!O || seg < 0 || seg >= (int)O->kine.size()) return GFORB_ERR_ARG;
+    const KineSeg& k = O->kine[seg];
+    if (Xv13) memcpy(Xv13, k.Xv, sizeof(k.Xv));
+    if (F169) memcpy(F169, k.F, sizeof(k.F));
+    if (F_Q16) memcpy(F_Q16, k.F_Q, sizeof(k.F_Q));
+    if (F_Omg12) memcpy(F_Omg12, k.F_Omg, sizeof(k.F_Omg));
+    if (F_Q_inSeg16) memcpy(F_Q_inSeg16, k.F_Q_inSeg, sizeof(k.F_Q_inSeg));
+    if (F_Omg_inSeg12) memcpy(F_Omg_inSeg12, k.F_Omg_inSeg, sizeof(k.F_Omg_inSeg));
+    if (Tcw16) memcpy(Tcw16, k.Tcw, sizeof(k.Tcw));
+    return GFORB_OK;
+}
+
+int gforb_obs_build_info_frame(GforbObs* O, const double* Xv, const float* world, const int32_t* octave,
+                               const int32_t* match_score, const uint8_t* valid, const int32_t* counts, int stride,
+                               int batch, const float* level_sigma2, int nlevels, double* blocks, double* obs_score,
+                               double* H_meas, int flags, void* stream) {
+    OCtx c;
+    int rc = obs_begin(O, batch, stride, flags, stream, c);
+    if (rc) return rc;
+    if (!Xv || !world || !octave || !match_score || !valid || !counts || !level_sigma2 || nlevels <= 0 || !blocks || !obs_score)
+        return GFORB_ERR_ARG;
+    if (batch == 0 || stride == 0) return GFORB_OK;
+    const size_t n = (size_t)batch * stride;
+    const double* dXv = c.in(Xv, (size_t)batch * 13);
+    const float* dW = c.in(world, n * 3);
+    const int32_t* dOct = c.in(octave, n);
+    const int32_t* dSc = c.in(match_score, n);
+    const uint8_t* dV = c.in(valid, n);
+    const int32_t* dCnt = c.in(counts, (size_t)batch);
+    const float* dLs = c.in(level_sigma2, (size_t)nlevels);
+    double* dB = c.out(blocks, n * 49);
+    double* dS = c.out(obs_score, n);
+    double* dH = c.out(H_meas, n * 14);
+    if (c.rc) return c.rc;
+    CamDev cam{O->cfg.fu, O->cfg.fv, O->cfg.Cx, O->cfg.Cy};
+    k_build_info<<<dim3((stride + 127) / 128, batch), 128, 0, c.st>>>(0, dXv, cam, dW, dOct, dSc, dV, dCnt, stride, dLs, nlevels, 0,
+                                                                       0, 0, 0, 0, 0, 0, 0, dB, dS, dH, nullptr);
+    O->lastLaunches = 1;
+    return obs_end(O, c, flags);
+}
+
+int gforb_obs_build_info_map(GforbObs* O, const double* Xv, const float* world, const uint8_t* track_in_view,
+                             const int32_t* counts, int stride, int batch, int check_viz, int min_x, int max_x,
+                             int min_y, int max_y, double* blocks, double* obs_score, float* uv, int flags, void* stream) {
+    OCtx c;
+    int rc = obs_begin(O, batch, stride, flags, stream, c);
+    if (rc) return rc;
+    if (!Xv || !world || !track_in_view || !counts || !blocks || !obs_score) return GFORB_ERR_ARG;
+    if (batch == 0 || stride == 0) return GFORB_OK;
+    const size_t n = (size_t)batch * stride;
+    const double* dXv = c.in(Xv, (size_t)batch * 13);
+    const float* dW = c.in(world, n * 3);
+    const uint8_t* dV = c.in(track_in_view, n);
+    const int32_t* dCnt = c.in(counts, (size_t)batch);
+    double* dB = c.out(blocks, n * 49);
+    double* dS = c.out(obs_score, n);
+    float* dUv = c.out(uv, n * 2);
+    if (c.rc) return c.rc;
+    CamDev cam{O->cfg.fu, O->cfg.fv, O->cfg.Cx, O->cfg.Cy};
+    // mBoundXInFrame = mBoundYInFrame = 20, mBoundDepth = 0 (include/Observability.h:129-131)
+    k_build_info<<<dim3((stride + 127) / 128, batch), 128, 0, c.st>>>(1, dXv, cam, dW, nullptr, nullptr, dV, dCnt, stride, nullptr, 1,
+                                                                       check_viz, min_x, max_x, min_y, max_y, 20.0, 20.0, 0.0, dB,
+                                                                       dS, nullptr, dUv);
+    O->lastLaunches = 1;
+    return obs_end(O, c, flags);
+}
+
+int gforb_obs_logdet(GforbObs* O, const double* mats, int n, double* out, int flags, void* stream) {
+    OCtx c;
+    int rc = obs_begin(O, 0, 0, flags, stream, c);
+    if (rc) return rc;
+    if (!mats || !out || n < 0) return GFORB_ERR_ARG;
+    if (n == 0) return GFORB_OK;
+    const double* dM = c.in(mats, (size_t)n * 49);
+    double* dO = c.out(out, (size_t)n);
+    if (c.rc) return c.rc;
+    k_logdet<<<(n + 127) / 128, 128, 0, c.st>>>(dM, n, dO);
+    O->lastLaunches = 1;
+    return obs_end(O, c, flags);
+}
+
+int gforb_obs_rand_stream(GforbObs* O, uint32_t seed, int n, int32_t* out_host) {
+    if (!O || !out_host || n <= 0) return GFORB_ERR_ARG;
+    GF_CUDA_OK(cudaSetDevice(O->device));
+    int32_t* d = nullptr;
+    GF_CUDA_OK(cudaMalloc((void**)&d, sizeof(int32_t) * n));
+    k_rand_stream<<<1, 32>>>(seed, n, d);
+    cudaError_t e = cudaMemcpy(out_host, d, sizeof(int32_t) * n, cudaMemcpyDeviceToHost);
+    cudaFree(d);
+    GF_CUDA_OK(e);
+    return GFORB_OK;
+}
+
+int gforb_obs_select(GforbObs* O, const double* blocks, const double* obs_score, const int32_t* counts, int stride,
+                     int batch, int k, int mtd, double sample_scale, const uint32_t* seeds, int32_t* out_idx,
+                     double* out_logdet, int32_t* out_n, int out_stride, int flags, void* stream) {
+    OCtx c;
+    int rc = obs_begin(O, batch, stride, flags, stream, c);
+    if (rc) return rc;
+    if (!blocks || !counts || !out_idx || !out_n || k <= 0 || out_stride <= 0) return GFORB_ERR_ARG;
+    if (mtd != MTD_GREEDY && mtd != MTD_LAZIER_SELECT && mtd != MTD_LAZIER_AUTO && mtd != MTD_LAZIER_DELETE) return GFORB_ERR_ARG;
+    if (batch == 0) return GFORB_OK;
+    const size_t n = (size_t)batch * stride;
+    SelParams P;
+    P.blocks = c.in(blocks, n * 49);
+    P.obsScore = c.in(obs_score, n);
+    P.counts = c.in(counts, (size_t)batch);
+    P.seeds = c.in(seeds, (size_t)batch);
+    P.stride = stride; P.k = k; P.mtd = mtd; P.maxPoints = O->cfg.max_points; P.sampleScale = sample_scale;
+    P.outIdx = c.out(out_idx, (size_t)batch * out_stride);
+    P.outLogdet = c.out(out_logdet, (size_t)batch * out_stride);
+    P.outN = c.out(out_n, (size_t)batch);
+    P.outStride = out_stride;
+    if (c.rc) return c.rc;
+    k_select<<<batch, SEL_THREADS, select_smem(O->cfg.max_points), c.st>>>(P);
+    O->lastLaunches = 1;
+    return obs_end(O, c, flags);
+}
+
+}  // extern "C"

@@ -1,0 +1,206 @@
+"""Host-side mirror of ORB_SLAM::ORBmatcher and of the Frame fields it reads (reference include/ORBmatcher.h:39-294,
+include/Frame.h) over the C ABI.  Arrays may be numpy (host; the library stages them) or torch CUDA tensors (device;
+zero copies).  All calls are batch-first: a `Frames` object holds B frames."""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import KP_DTYPE, FrameSet, MapPointSet, MatcherConfig, check, is_device, ptr
+
+TH_LOW, TH_HIGH, HISTO_LENGTH = 50, 100, 30      # src/ORBmatcher.cc:40-42
+
+
+def _raw(a):
+    p = ptr(a)
+    return p.value if p is not None else None
+
+
+class Frames:
+    """B frames' mvKeysUn / mDescriptors / N plus the static image bounds (Frame::mnMinX.. , src/Frame.cc:489-493).
+    keypoints: (B, stride) KP_DTYPE (numpy) or (B, stride, 7) float32 torch tensor with the same 28-byte layout."""
+
+    def __init__(self, keypoints, descriptors, counts, width: int, height: int, min_x=0, min_y=0):
+        self.keypoints, self.descriptors, self.counts = keypoints, descriptors, counts
+        self.batch = int(keypoints.shape[0])
+        self.stride = int(keypoints.shape[1])
+        self.bounds = (int(min_x), int(width), int(min_y), int(height))
+        self.device = is_device(keypoints)
+        assert is_device(descriptors) == self.device and is_device(counts) == self.device
+
+    @classmethod
+    def single(cls, kps: np.ndarray, desc: np.ndarray, width: int, height: int):
+        kps = np.ascontiguousarray(kps, KP_DTYPE)
+        n = max(kps.size, 1)
+        k = np.zeros((1, n), KP_DTYPE); k[0, :kps.size] = kps
+        d = np.zeros((1, n, 32), np.uint8); d[0, :kps.size] = desc
+        return cls(k, d, np.array([kps.size], np.int32), width, height)
+
+    def cstruct(self) -> FrameSet:
+        b = self.bounds
+        return FrameSet(_raw(self.keypoints), _raw(self.descriptors), _raw(self.counts), self.stride, b[0], b[1], b[2], b[3])
+
+
+class MapPoints:
+    """SoA of the MapPoint fields SearchByProjection reads; arrays (B, stride); flags bit0 mbTrackInView, bit1 isBad."""
+
+    def __init__(self, proj_x, proj_y, scale_level, view_cos, flags, descriptors, counts):
+        self.a = (proj_x, proj_y, scale_level, view_cos, flags, descriptors, counts)
+        self.batch, self.stride = int(proj_x.shape[0]), int(proj_x.shape[1])
+        self.device = is_device(proj_x)
+
+    def cstruct(self) -> MapPointSet:
+        return MapPointSet(*[_raw(x) for x in self.a], self.stride)
+
+
+class ORBmatcher:
+    """ORBmatcher(nnratio=0.6, checkOri=true).  One instance owns the device scratch for up to max_batch problems."""
+
+    def __init__(self, nnratio=0.6, checkOri=True, *, max_batch=1, max_keypoints=2048, max_queries=2048, cand_pool=0,
+                 nlevels=8, scaleFactor=1.2, device=0):
+        self.mfNNratio, self.mbCheckOrientation = float(nnratio), bool(checkOri)
+        cfg = MatcherConfig(max_batch, max_keypoints, max_queries, cand_pool, nlevels, scaleFactor, device)
+        self.cfg = cfg
+        h = C.c_void_p()
+        check(_lib.lib().gforb_matcher_create(C.byref(cfg), C.byref(h)), "gforb_matcher_create")
+        self._h = h
+
+    def close(self):
+        if getattr(self, "_h", None):
+            _lib.lib().gforb_matcher_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def last_launches(self) -> int:
+        return _lib.lib().gforb_matcher_last_launches(self._h)
+
+    @staticmethod
+    def _flags(in_dev: bool, out_dev: bool, sync=True) -> int:
+        return (_lib.GFORB_IN_DEVICE if in_dev else 0) | (_lib.GFORB_OUT_DEVICE if out_dev else 0) | (0 if sync else _lib.GFORB_ASYNC)
+
+    # -- static int DescriptorDistance(a, b): here for n pairs
+    def DescriptorDistance(self, a, b):
+        dev = is_device(a)
+        if dev:
+            import torch
+            n = a.numel() // 32
+            out = torch.empty(n, dtype=torch.int32, device=a.device)
+        else:
+            a = np.ascontiguousarray(a, np.uint8); b = np.ascontiguousarray(b, np.uint8)
+            n = a.size // 32
+            out = np.empty(n, np.int32)
+        check(_lib.lib().gforb_descriptor_distance(self._h, ptr(a), ptr(b), n, ptr(out), self._flags(dev, dev), None),
+              "gforb_descriptor_distance")
+        return out if (dev or n != 1) else int(out[0])
+
+    # -- Frame::GetFeaturesInArea (parity tap)
+    def GetFeaturesInArea(self, F: Frames, frame: int, x, y, r, minLevel, maxLevel, cap=512):
+        x = np.ascontiguousarray(np.atleast_1d(x), np.float32); y = np.ascontiguousarray(np.atleast_1d(y), np.float32)
+        r = np.ascontiguousarray(np.atleast_1d(r), np.float32)
+        mn = np.ascontiguousarray(np.atleast_1d(minLevel), np.int32); mx = np.ascontiguousarray(np.atleast_1d(maxLevel), np.int32)
+        n = x.size
+        idx = np.full((n, cap), -1, np.int32); cnt = np.zeros(n, np.int32)
+        fs = F.cstruct()
+        check(_lib.lib().gforb_features_in_area(self._h, C.byref(fs), F.batch, frame, ptr(x), ptr(y), ptr(r), ptr(mn), ptr(mx),
+                                                n, ptr(idx), cap, ptr(cnt), self._flags(F.device, False), None),
+              "gforb_features_in_area")
+        return [idx[i, :min(cnt[i], cap)].copy() for i in range(n)], cnt
+
+    # -- int SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize=10)
+    def SearchForInitialization(self, F1: Frames, F2: Frames, vbPrevMatched, windowSize=10, *, matches12=None,
+                                nmatches=None, stream=None, sync=True):
+        """vbPrevMatched (B, stride1, 2) float32 is updated in place; returns (nmatches[B], vnMatches12[B, stride1])."""
+        out_dev = is_device(vbPrevMatched)
+        if matches12 is None:
+            if out_dev:
+                import torch
+                matches12 = torch.empty((F1.batch, F1.stride), dtype=torch.int32, device=vbPrevMatched.device)
+                nmatches = torch.empty(F1.batch, dtype=torch.int32, device=vbPrevMatched.device)
+            else:
+                matches12 = np.empty((F1.batch, F1.stride), np.int32); nmatches = np.empty(F1.batch, np.int32)
+        f1, f2 = F1.cstruct(), F2.cstruct()
+        check(_lib.lib().gforb_search_for_initialization(
+            self._h, C.byref(f1), C.byref(f2), F1.batch, ptr(vbPrevMatched), ptr(matches12), ptr(nmatches), int(windowSize),
+            self.mfNNratio, int(self.mbCheckOrientation), self._flags(F1.device, out_dev, sync), C.c_void_p(stream or 0)),
+            "gforb_search_for_initialization")
+        return nmatches, matches12
+
+    # -- int SearchByProjection(Frame &F, const vector<MapPoint*> &vpMapPoints, th=3)
+    def SearchByProjection(self, F: Frames, mps: MapPoints, th, mvpMapPoints, mvpMatchScore, *, nmatches=None,
+                           stream=None, sync=True):
+        """mvpMapPoints / mvpMatchScore (B, stride) int32 are the frame's in/out arrays (ids, -1 = NULL; 999 default)."""
+        out_dev = is_device(mvpMapPoints)
+        if nmatches is None:
+            if out_dev:
+                import torch
+                nmatches = torch.empty(F.batch, dtype=torch.int32, device=mvpMapPoints.device)
+            else:
+                nmatches = np.empty(F.batch, np.int32)
+        fs, ms = F.cstruct(), mps.cstruct()
+        check(_lib.lib().gforb_search_by_projection(self._h, C.byref(fs), C.byref(ms), F.batch, float(th), self.mfNNratio,
+                                                    ptr(mvpMapPoints), ptr(mvpMatchScore), ptr(nmatches),
+                                                    self._flags(F.device, out_dev, sync), C.c_void_p(stream or 0)),
+              "gforb_search_by_projection")
+        return nmatches
+
+    # -- int SearchByProjection(Frame &CurrentFrame, const Frame &LastFrame, float th)
+    def SearchByProjectionFrames(self, Cur: Frames, Last: Frames, last_mappoints, last_outlier, last_world, Tcw, K, th,
+                                 cur_mappoints, cur_score, *, nmatches=None, stream=None, sync=True):
+        out_dev = is_device(cur_mappoints)
+        if nmatches is None:
+            if out_dev:
+                import torch
+                nmatches = torch.empty(Cur.batch, dtype=torch.int32, device=cur_mappoints.device)
+            else:
+                nmatches = np.empty(Cur.batch, np.int32)
+        fx, fy, cx, cy = [float(v) for v in K]
+        c, l = Cur.cstruct(), Last.cstruct()
+        check(_lib.lib().gforb_search_by_projection_frames(
+            self._h, C.byref(c), C.byref(l), Cur.batch, ptr(last_mappoints), ptr(last_outlier), ptr(last_world), ptr(Tcw),
+            fx, fy, cx, cy, float(th), self.mfNNratio, int(self.mbCheckOrientation), ptr(cur_mappoints), ptr(cur_score),
+            ptr(nmatches), self._flags(Cur.device, out_dev, sync), C.c_void_p(stream or 0)),
+            "gforb_search_by_projection_frames")
+        return nmatches
+
+    # -- int WindowSearch(F1, F2, windowSize, vpMapPointMatches2, minScaleLevel=-1, maxScaleLevel=INT_MAX)
+    def WindowSearch(self, F1: Frames, F2: Frames, f1_mappoints, windowSize, minScaleLevel=-1, maxScaleLevel=0x7FFFFFFF,
+                     *, stream=None, sync=True):
+        dev = F1.device
+        if dev:
+            import torch
+            m2 = torch.empty((F2.batch, F2.stride), dtype=torch.int32, device=F1.keypoints.device)
+            nm = torch.empty(F2.batch, dtype=torch.int32, device=F1.keypoints.device)
+        else:
+            m2 = np.empty((F2.batch, F2.stride), np.int32); nm = np.empty(F2.batch, np.int32)
+        a, b = F1.cstruct(), F2.cstruct()
+        check(_lib.lib().gforb_window_search(self._h, C.byref(a), C.byref(b), F1.batch, ptr(f1_mappoints), int(windowSize),
+                                             int(minScaleLevel), int(maxScaleLevel), self.mfNNratio,
+                                             int(self.mbCheckOrientation), ptr(m2), ptr(nm), self._flags(dev, dev, sync),
+                                             C.c_void_p(stream or 0)), "gforb_window_search")
+        return nm, m2
+
+    # -- all-pairs top-2 against a database shard resident in HBM (torch CUDA uint8 tensors)
+    def AllPairsTop2(self, queries, db, idx_base=0, *, out=None, stream=None, sync=True):
+        import torch
+        nq, ndb = queries.shape[0], db.shape[0]
+        if out is None:
+            out = torch.empty((nq, 2), dtype=torch.int64, device=queries.device)
+        check(_lib.lib().gforb_allpairs_top2(self._h, ptr(queries), nq, ptr(db), ndb, int(idx_base), ptr(out),
+                                             self._flags(True, True, sync), C.c_void_p(stream or 0)), "gforb_allpairs_top2")
+        return out
+
+    def Top2Merge(self, gathered, *, out=None, stream=None, sync=True):
+        import torch
+        ns, nq = gathered.shape[0], gathered.shape[1]
+        if out is None:
+            out = torch.empty((nq, 2), dtype=torch.int64, device=gathered.device)
+        check(_lib.lib().gforb_top2_merge(self._h, ptr(gathered), ns, nq, ptr(out), self._flags(True, True, sync),
+                                          C.c_void_p(stream or 0)), "gforb_top2_merge")
+        return out

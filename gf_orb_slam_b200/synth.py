@@ -84,3 +84,38 @@ def landmark_cloud(n: int, seed: int, xv: np.ndarray | None = None):
     score = np.round(u[:, 4] * 100).astype(np.int32)
     pix_noise = (u[:, 5:7] * 2 - 1).astype(np.float32)
     return world, octave, score, pix_noise
+
+
+def uniform01(seed: int, n: int, offset: int = 0) -> np.ndarray:
+    return (splitmix64(seed, n, offset) >> np.uint64(11)).astype(np.float64) / float(1 << 53)
+
+
+def map_points_c3(kps: np.ndarray, desc: np.ndarray, M: int, seed: int, w: int, h: int, nlevels: int = 8):
+    """Config C3: M projected map points against one frame's keypoints: uniform (u, v) for 40 % of the
+    points, the rest placed within a few pixels of a random keypoint; level in U{0..7}; viewCos in {0.9, 0.999};
+    descriptor = a random frame descriptor with k~U{0..60} flipped bits (70 %) or fully random (30 %); 3 % of the
+    points are not in view and 2 % are bad.  Returns dict of SoA arrays."""
+    n = len(kps)
+    u01 = uniform01(seed, 8 * M).reshape(M, 8)
+    pick = np.minimum((u01[:, 0] * n).astype(np.int64), n - 1)
+    near = u01[:, 1] < 0.6
+    jit = (u01[:, 2:4] * 2 - 1) * 6.0
+    px = np.where(near, kps["x"][pick] + jit[:, 0], u01[:, 2] * w).astype(np.float32)
+    py = np.where(near, kps["y"][pick] + jit[:, 1], u01[:, 3] * h).astype(np.float32)
+    level = np.where(near & (u01[:, 4] < 0.8), kps["octave"][pick] + (u01[:, 4] < 0.3), np.floor(u01[:, 4] * nlevels))
+    level = np.clip(level, 0, nlevels - 1).astype(np.int32)
+    view_cos = np.where(u01[:, 5] < 0.5, 0.9, 0.999).astype(np.float32)
+    flags = np.ones(M, np.uint8)
+    flags[u01[:, 6] < 0.03] = 0
+    flags[(u01[:, 6] >= 0.03) & (u01[:, 6] < 0.05)] = 3
+    d = desc[pick].copy()
+    bits = splitmix64(seed + 1, M * 4).view(np.uint8).reshape(M, 32)
+    rnd = u01[:, 7] < 0.3
+    d[rnd] = bits[rnd]
+    nflip = np.floor(uniform01(seed + 2, M) * 61).astype(np.int64)
+    pos = (uniform01(seed + 3, M * 60).reshape(M, 60) * 256).astype(np.int64)
+    for k in range(60):
+        sel = (~rnd) & (nflip > k)
+        b = pos[sel, k]
+        d[sel, b >> 3] ^= (1 << (b & 7)).astype(np.uint8)
+    return dict(proj_x=px, proj_y=py, scale_level=level, view_cos=view_cos, flags=flags, descriptors=np.ascontiguousarray(d))

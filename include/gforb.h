@@ -3,7 +3,7 @@
  * Drop-in boundary for ONE hot path of Aidenryan/GF_ORB_SLAM: ORB extraction -> Hamming matching -> good-feature
  * selection.  The reference has no FFI: the "operator API" is three C++ classes called synchronously from the
  * tracking thread.  Each entry point below names the reference member function it replaces (paths relative to the
- * reference tree); include/gforb/*.hpp re-creates the class signatures on top of this ABI.
+ * reference tree); the headers under include/gforb/ re-create the class signatures on top of this ABI.
  *
  * Conventions
  *  - every function returns GFORB_OK (0) or a negative GFORB_ERR_*; nothing throws.
@@ -89,6 +89,159 @@ int gforb_extractor_last_launches(const GforbExtractor* h);
  * number of stages.  Profiling is enabled with gforb_extractor_set_profiling(h, 1). */
 int gforb_extractor_set_profiling(GforbExtractor* h, int on);
 int gforb_extractor_stage_time(const GforbExtractor* h, int i, const char** name, float* ms);
+
+/* ------------------------------------------------------------------------------------------------ matching
+ * Replaces ORB_SLAM::ORBmatcher (include/ORBmatcher.h:39-294, src/ORBmatcher.cc) for the per-frame tracking
+ * overloads, plus the Frame grid it searches (src/Frame.cc:118-131, 300-377).  MapPoint* / NULL is flattened to an
+ * int32 id / -1.  Every call takes `batch` independent problems (frames / frame pairs).
+ *
+ * Pointer residency: with GFORB_IN_DEVICE all pointers inside the *Set structs and all pure-input arrays are device
+ * pointers; with GFORB_OUT_DEVICE all output and in/out arrays are device pointers.  Otherwise they are host
+ * pointers and the call stages them itself. */
+typedef struct GforbFrameSet {
+    const GforbKeyPoint* keypoints;   /* batch x kp_stride         Frame::mvKeysUn */
+    const uint8_t* descriptors;       /* batch x kp_stride x 32    Frame::mDescriptors */
+    const int32_t* counts;            /* batch                     Frame::N */
+    int32_t kp_stride;
+    int32_t min_x, max_x, min_y, max_y; /* Frame::mnMinX/mnMaxX/mnMinY/mnMaxY (src/Frame.cc:489-493) */
+} GforbFrameSet;
+
+typedef struct GforbMapPointSet {     /* the MapPoint fields SearchByProjection reads; arrays are batch x mp_stride */
+    const float* proj_x;              /* MapPoint::mTrackProjX */
+    const float* proj_y;              /* MapPoint::mTrackProjY */
+    const int32_t* scale_level;       /* MapPoint::mnTrackScaleLevel */
+    const float* view_cos;            /* MapPoint::mTrackViewCos */
+    const uint8_t* flags;             /* bit0 = mbTrackInView, bit1 = isBad() */
+    const uint8_t* descriptors;       /* MapPoint::GetDescriptor(), x 32 bytes */
+    const int32_t* counts;            /* batch: vpMapPoints.size() */
+    int32_t mp_stride;
+} GforbMapPointSet;
+
+typedef struct GforbMatcherConfig {
+    int32_t max_batch;                /* problems per call */
+    int32_t max_keypoints;            /* per frame (<= 16384) */
+    int32_t max_queries;              /* per problem: map points (SearchByProjection) or source keypoints */
+    int32_t cand_pool;                /* candidate entries per problem; 0 = 64 * max_queries */
+    int32_t nlevels;                  /* Frame::mnScaleLevels */
+    float scaleFactor;                /* Frame::mfScaleFactor -> mvScaleFactors[] */
+    int32_t device;
+} GforbMatcherConfig;
+
+typedef struct GforbMatcher GforbMatcher;
+int gforb_matcher_create(const GforbMatcherConfig* cfg, GforbMatcher** out);
+int gforb_matcher_destroy(GforbMatcher* h);
+/* kernels launched by the last call on this handle */
+int gforb_matcher_last_launches(const GforbMatcher* h);
+
+/* ORBmatcher::DescriptorDistance (src/ORBmatcher.cc:2384-2400) for n descriptor pairs: out[i] = |a_i xor b_i|. */
+int gforb_descriptor_distance(GforbMatcher* h, const uint8_t* a, const uint8_t* b, int n, int32_t* out, int flags,
+                              void* stream);
+
+/* Frame::GetFeaturesInArea (src/Frame.cc:300-365) on the grid the Frame ctor builds (:118-131, PosInGrid :367-377):
+ * n_queries windows (x, y, r, minLevel, maxLevel) against frame `frame` of `frames`; out_idx receives, per query,
+ * up to `cap` keypoint indices in the reference's order, out_n the full counts.  Parity tap for the grid. */
+int gforb_features_in_area(GforbMatcher* h, const GforbFrameSet* frames, int batch, int frame, const float* x,
+                           const float* y, const float* r, const int32_t* min_level, const int32_t* max_level,
+                           int n_queries, int32_t* out_idx, int cap, int32_t* out_n, int flags, void* stream);
+
+/* ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) (src/ORBmatcher.cc:1172-1287).
+ * prev_matched: in/out, batch x F1.kp_stride x 2;  matches12: out, batch x F1.kp_stride;  nmatches: out, batch. */
+int gforb_search_for_initialization(GforbMatcher* h, const GforbFrameSet* F1, const GforbFrameSet* F2, int batch,
+                                    float* prev_matched, int32_t* matches12, int32_t* nmatches, int window_size,
+                                    float nnratio, int check_orientation, int flags, void* stream);
+
+/* ORBmatcher::SearchByProjection(Frame& F, const vector<MapPoint*>&, th) (src/ORBmatcher.cc:384-465).
+ * frame_mappoints / match_score: in/out, batch x F.kp_stride (Frame::mvpMapPoints as ids, Frame::mvpMatchScore);
+ * nmatches: out, batch. */
+int gforb_search_by_projection(GforbMatcher* h, const GforbFrameSet* F, const GforbMapPointSet* mps, int batch,
+                               float th, float nnratio, int32_t* frame_mappoints, int32_t* match_score,
+                               int32_t* nmatches, int flags, void* stream);
+
+/* ORBmatcher::SearchByProjection(Frame& Current, const Frame& Last, th) (src/ORBmatcher.cc:2081-2202).
+ * last_mappoints: batch x last.kp_stride ids (-1 = NULL); last_outlier: same shape or NULL; last_world: batch x
+ * last.kp_stride x 3 (MapPoint::GetWorldPos of LastFrame.mvpMapPoints[i]); Tcw: batch x 16 row-major (Current.mTcw);
+ * cur_mappoints / cur_score: in/out, batch x cur.kp_stride. */
+int gforb_search_by_projection_frames(GforbMatcher* h, const GforbFrameSet* cur, const GforbFrameSet* last, int batch,
+                                      const int32_t* last_mappoints, const uint8_t* last_outlier,
+                                      const float* last_world, const float* Tcw, float fx, float fy, float cx, float cy,
+                                      float th, float nnratio, int check_orientation, int32_t* cur_mappoints,
+                                      int32_t* cur_score, int32_t* nmatches, int flags, void* stream);
+
+/* ORBmatcher::WindowSearch(F1, F2, windowSize, vpMapPointMatches2, minScaleLevel, maxScaleLevel)
+ * (src/ORBmatcher.cc:979-1086).  f1_mappoints: batch x F1.kp_stride ids (>= 0: non-NULL, not bad);
+ * matches2: out, batch x F2.kp_stride (map-point id or -1). */
+int gforb_window_search(GforbMatcher* h, const GforbFrameSet* F1, const GforbFrameSet* F2, int batch,
+                        const int32_t* f1_mappoints, int window_size, int min_scale_level, int max_scale_level,
+                        float nnratio, int check_orientation, int32_t* matches2, int32_t* nmatches, int flags,
+                        void* stream);
+
+/* Batched all-pairs Hamming top-2 of n_q query descriptors against one database shard of n_db descriptors
+ * (BASELINE.json config 5; the reference's brute-force analogue is the DescriptorDistance loop of
+ * MapPoint::ComputeDistinctiveDescriptors, src/MapPoint.cc:225-250).  out: n_q x 2 packed keys
+ * (dist << 32 | global index), best then second; ties -> lower index; idx_base = global index of db row 0.
+ * The cross-shard merge is gforb_top2_merge over the all-gathered keys (NCCL all-gather by the host layer). */
+int gforb_allpairs_top2(GforbMatcher* h, const uint8_t* queries, int n_q, const uint8_t* db, int64_t n_db,
+                        int64_t idx_base, uint64_t* out_keys, int flags, void* stream);
+int gforb_top2_merge(GforbMatcher* h, const uint64_t* gathered /* n_shards x n_q x 2 */, int n_shards, int n_q,
+                     uint64_t* out_keys /* n_q x 2 */, int flags, void* stream);
+
+/* ------------------------------------------------------------------------------------------------ good features
+ * Replaces ORB_SLAM::Observability (include/Observability.h:113-770, include/Util.hpp, src/Observability.cc) for
+ * DIMENSION_OF_STATE_MODEL = 7: kinematics (host), per-match information blocks and log-det subset selection. */
+typedef struct GforbObsConfig {
+    double fu, fv;                 /* PinHoleCamera (include/Util.hpp:131-167): ctor (f,...,dx,dy) passes fu = f/dx */
+    int32_t nRows, nCols;
+    double Cx, Cy, k1, k2, dx, dy;
+    int32_t max_batch;             /* frames / selection problems per call */
+    int32_t max_points;            /* matched map points per frame (<= 8192) */
+    int32_t device;
+} GforbObsConfig;
+
+typedef struct GforbObs GforbObs;
+int gforb_obs_create(const GforbObsConfig* cfg, GforbObs** out);
+int gforb_obs_destroy(GforbObs* h);
+int gforb_obs_last_launches(const GforbObs* h);
+
+/* Observability::Xv (13-state [r(3) q(4) v(3) w(3)]), updatePWLSVec (include/Observability.h:222-259) and
+ * predictPWLSVec (:261-295); matrices are 4x4 row-major float like the reference's cv::Mat.  Host-side. */
+int gforb_obs_set_state(GforbObs* h, const double* Xv13);
+int gforb_obs_get_state(const GforbObs* h, double* Xv13);
+int gforb_obs_update_pwls(GforbObs* h, double t_prev, const float* Tcw_prev, double t_cur, const float* Twc_cur);
+int gforb_obs_predict_pwls(GforbObs* h, double dt, int num_seg);
+int gforb_obs_num_segments(const GforbObs* h);
+/* kinematic[seg] (KineStruct, include/Observability.h:94-110); any output pointer may be NULL */
+int gforb_obs_get_segment(const GforbObs* h, int seg, double* Xv13, double* F169, double* F_Q16, double* F_Omg12,
+                          double* F_Q_inSeg16, double* F_Omg_inSeg12, float* Tcw16);
+
+/* batchInfoMat_Frame (src/Observability.cc:386-554) for `batch` frames: per matched point the 2x7 Jacobian
+ * (compute_H_subblock_simplied), octave re-weighting (reWeightInfoMat) and the 7x7 block H^T H.
+ * Xv: batch x 13 (kinematic[mKineIdx].Xv of each frame); world: batch x stride x 3 (MapPoint::GetWorldPos);
+ * valid = pMP && !mvbOutlier && mvbCandidate; blocks: batch x stride x 49 row-major; obs_score: ObsScore (match
+ * score, -1 when not valid); H_meas: batch x stride x 14 or NULL. */
+int gforb_obs_build_info_frame(GforbObs* h, const double* Xv, const float* world, const int32_t* octave,
+                               const int32_t* match_score, const uint8_t* valid, const int32_t* counts, int stride,
+                               int batch, const float* level_sigma2, int nlevels, double* blocks, double* obs_score,
+                               double* H_meas, int flags, void* stream);
+/* batchInfoMat_Map (src/Observability.cc:556-644): identity noise, optional visibility check; obs_score is 1 (built),
+ * -1 (not visible) or -2 (skipped); uv: batch x stride x 2 projections or NULL. */
+int gforb_obs_build_info_map(GforbObs* h, const double* Xv, const float* world, const uint8_t* track_in_view,
+                             const int32_t* counts, int stride, int batch, int check_viz, int min_x, int max_x,
+                             int min_y, int max_y, double* blocks, double* obs_score, float* uv, int flags, void* stream);
+/* logDet (include/Util.hpp:714-731) of n 7x7 row-major matrices. */
+int gforb_obs_logdet(GforbObs* h, const double* mats, int n, double* out, int flags, void* stream);
+/* the device's glibc-TYPE_3 rand() stream (parity tap; out_host is a host pointer) */
+int gforb_obs_rand_stream(GforbObs* h, uint32_t seed, int n, int32_t* out_host);
+
+/* Subset selection over the pool lmkSelectPool = entries 0..counts[b]-1 of problem b (src/Observability.cc):
+ * mtd 1 = maxVolSelection_BaselineGreedy (:3031), 2 = maxVolSelection_LazierGreedy (:2815),
+ * 3 = maxVolAutomatic_LazierGreedy (:3141), 5 = maxVolDeletion_LazierGreedy (:2339); k = mpLimit.
+ * The reference draws from the process-global rand(); here the stream is an input: seeds[b] (NULL = 1, the state of a
+ * process that never called srand) restarts glibc's generator for problem b.  Time caps are infinite.
+ * out_idx: batch x out_stride pool indices (selection order; deletion: ascending), out_logdet: running log-det after
+ * each pick (selection modes) or NULL, out_n: picks per problem. */
+int gforb_obs_select(GforbObs* h, const double* blocks, const double* obs_score, const int32_t* counts, int stride,
+                     int batch, int k, int mtd, double sample_scale, const uint32_t* seeds, int32_t* out_idx,
+                     double* out_logdet, int32_t* out_n, int out_stride, int flags, void* stream);
 
 #ifdef __cplusplus
 }

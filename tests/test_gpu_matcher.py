@@ -1,0 +1,243 @@
+"""GPU parity: CUDA ORBmatcher / Frame grid (through the C ABI) vs the CPU oracle -- bit-exact indices, scores, counts."""
+import numpy as np
+import pytest
+
+from gf_orb_slam_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+W, H = 752, 480
+
+
+@pytest.fixture(scope="module")
+def seq_frames():
+    """6 consecutive C2 sequence frames extracted on the GPU (parity of the extractor itself: test_gpu_extractor)."""
+    from gf_orb_slam_b200 import ORBextractor
+    seq = synth.Sequence()
+    imgs = seq.frames(0, 6)
+    ex = ORBextractor(1000, 1.2, 8, max_batch=6)
+    kps, desc, counts = ex.extract_batch(imgs)
+    return kps, desc, counts
+
+
+def _oframe(orc, kps, desc, n):
+    return orc.Frame(kps[:n], desc[:n], W, H)
+
+
+def test_descriptor_distance(orc):
+    from gf_orb_slam_b200 import ORBmatcher
+    m = ORBmatcher(max_batch=1)
+    z = np.zeros(32, np.uint8); f = np.full(32, 255, np.uint8)
+    one = z.copy(); one[17] = 0x10
+    assert m.DescriptorDistance(z, z) == 0 and m.DescriptorDistance(z, f) == 256 and m.DescriptorDistance(z, one) == 1
+    rng = np.random.default_rng(3)
+    a = rng.integers(0, 256, (500, 32), dtype=np.uint8); b = rng.integers(0, 256, (500, 32), dtype=np.uint8)
+    got = m.DescriptorDistance(a, b)
+    exp = np.array([orc.descriptor_distance(a[i], b[i]) for i in range(500)])
+    assert np.array_equal(got, exp)
+
+
+def test_features_in_area(orc, seq_frames):
+    from gf_orb_slam_b200 import ORBmatcher, Frames
+    kps, desc, counts = seq_frames
+    F = Frames(kps, desc, counts, W, H)
+    m = ORBmatcher(max_batch=6, max_keypoints=1000, max_queries=1000)
+    fo = _oframe(orc, kps[2], desc[2], counts[2])
+    rng = np.random.default_rng(1)
+    nq = 300
+    x = rng.uniform(-30, W + 30, nq).astype(np.float32); y = rng.uniform(-30, H + 30, nq).astype(np.float32)
+    r = rng.choice([2.5, 7.0, 15.0, 40.0, 100.0, 900.0], nq).astype(np.float32)
+    lv = rng.integers(0, 8, nq)
+    kind = rng.integers(0, 4, nq)
+    mn = np.where(kind == 0, -1, np.where(kind == 1, lv, lv - 1)).astype(np.int32)
+    mx = np.where(kind == 0, -1, np.where(kind == 1, lv, np.where(kind == 2, lv, lv + 1))).astype(np.int32)
+    got, cnt = m.GetFeaturesInArea(F, 2, x, y, r, mn, mx, cap=1000)
+    nonempty = 0
+    for i in range(nq):
+        exp = fo.features_in_area(x[i], y[i], r[i], int(mn[i]), int(mx[i]))
+        assert cnt[i] == len(exp)
+        assert np.array_equal(got[i], exp), i
+        nonempty += len(exp) > 0
+    assert nonempty > nq // 2
+
+
+@pytest.mark.parametrize("window,nnratio,check_ori", [(100, 0.9, True), (30, 0.7, False), (10, 0.9, True)])
+def test_search_for_initialization(orc, seq_frames, window, nnratio, check_ori):
+    from gf_orb_slam_b200 import ORBmatcher, Frames
+    kps, desc, counts = seq_frames
+    B = 5
+    F1 = Frames(kps[:B], desc[:B], counts[:B], W, H)
+    F2 = Frames(kps[1:B + 1], desc[1:B + 1], counts[1:B + 1], W, H)
+    prev = np.stack([kps["x"][:B], kps["y"][:B]], axis=-1).astype(np.float32).copy()
+    prev0 = prev.copy()
+    m = ORBmatcher(nnratio, check_ori, max_batch=B, max_keypoints=1000, max_queries=1000)
+    nm, m12 = m.SearchForInitialization(F1, F2, prev, window)
+    total = 0
+    for b in range(B):
+        f1 = _oframe(orc, kps[b], desc[b], counts[b]); f2 = _oframe(orc, kps[b + 1], desc[b + 1], counts[b + 1])
+        n, e12, epm = orc.search_for_initialization(f1, f2, prev0[b, :counts[b]], window, nnratio, check_ori)
+        assert nm[b] == n, (b, nm[b], n)
+        assert np.array_equal(m12[b, :counts[b]], e12)
+        assert np.array_equal(prev[b, :counts[b]], epm.reshape(-1, 2))
+        total += n
+    if window == 100:
+        assert total > 50          # the workload really matches something
+    # second call with the updated vbPrevMatched (the reference calls it repeatedly during initialisation)
+    nm2, m12b = m.SearchForInitialization(F1, F2, prev, window)
+    f1 = _oframe(orc, kps[0], desc[0], counts[0]); f2 = _oframe(orc, kps[1], desc[1], counts[1])
+    _, _, pm1 = orc.search_for_initialization(f1, f2, prev0[0, :counts[0]], window, nnratio, check_ori)
+    n2, e12b, _ = orc.search_for_initialization(f1, f2, pm1.reshape(-1, 2), window, nnratio, check_ori)
+    assert nm2[0] == n2 and np.array_equal(m12b[0, :counts[0]], e12b)
+    assert m.last_launches() == 3
+
+
+@pytest.mark.parametrize("M,th,nnratio", [(2000, 1.0, 0.8), (10000, 1.0, 0.8), (3000, 5.0, 0.8), (1500, 3.0, 0.6)])
+def test_search_by_projection_map(orc, M, th, nnratio):
+    """config C3: 1500 frame keypoints against 10k projected map points (plus smaller / wider-window variants)."""
+    from gf_orb_slam_b200 import ORBextractor, ORBmatcher, Frames, MapPoints
+    img = synth.textured_frame(W, H, seed=1)
+    ex = ORBextractor(1500, 1.2, 8, max_width=W, max_height=H, max_batch=1)
+    kps, desc, counts = ex.extract_batch(img[None])
+    n = int(counts[0])
+    B = 2
+    mp = [synth.map_points_c3(kps[0, :n], desc[0, :n], M, seed=50 + b, w=W, h=H) for b in range(B)]
+    stack = lambda k: np.ascontiguousarray(np.stack([mp[b][k] for b in range(B)]))
+    mps = MapPoints(stack("proj_x"), stack("proj_y"), stack("scale_level"), stack("view_cos"), stack("flags"),
+                    stack("descriptors"), np.array([M, M - 7], np.int32))
+    kB = np.repeat(kps, B, 0); dB = np.repeat(desc, B, 0); cB = np.repeat(counts, B)
+    F = Frames(kB, dB, cB, W, H)
+    fmp = np.full((B, 1500), -1, np.int32); fsc = np.full((B, 1500), 999, np.int32)
+    fmp[1, 5:40:3] = 123456          # frame 1 arrives with some keypoints already claimed
+    fmp0 = fmp.copy()
+    m = ORBmatcher(nnratio, True, max_batch=B, max_keypoints=1500, max_queries=M, cand_pool=64 * M)
+    nm = m.SearchByProjection(F, mps, th, fmp, fsc)
+    for b in range(B):
+        fo = _oframe(orc, kps[0], desc[0], n)
+        fo.set_mappoints(fmp0[b, :n])
+        Mb = M if b == 0 else M - 7
+        en = orc.search_by_projection(fo, mp[b]["proj_x"][:Mb], mp[b]["proj_y"][:Mb], mp[b]["scale_level"][:Mb],
+                                      mp[b]["view_cos"][:Mb], mp[b]["flags"][:Mb], mp[b]["descriptors"][:Mb], th, nnratio)
+        emp, esc = fo.matches()
+        assert nm[b] == en, (b, nm[b], en)
+        assert np.array_equal(fmp[b, :n], emp) and np.array_equal(fsc[b, :n], esc)
+    assert nm[0] > 100
+
+
+def _pose_and_world(kps, n, seed, shift=(3.0, -2.0)):
+    """world points that project (with Tcw) near the last frame's keypoints shifted by a few pixels"""
+    fx = fy = 458.0; cx = W / 2.0; cy = H / 2.0
+    u01 = synth.uniform01(seed, 2 * n).reshape(n, 2)
+    z = (2.0 + 6.0 * u01[:, 0]).astype(np.float32)
+    x = ((kps["x"][:n] + shift[0] - cx) / fx * z).astype(np.float32)
+    y = ((kps["y"][:n] + shift[1] - cy) / fy * z).astype(np.float32)
+    Xc = np.stack([x, y, z], 1)
+    a = 0.02
+    R = np.array([[np.cos(a), -np.sin(a), 0], [np.sin(a), np.cos(a), 0], [0, 0, 1]], np.float32)
+    t = np.array([0.1, -0.05, 0.2], np.float32)
+    Xw = ((Xc - t) @ R).astype(np.float32)               # Xc = R Xw + t
+    Tcw = np.eye(4, dtype=np.float32); Tcw[:3, :3] = R; Tcw[:3, 3] = t
+    return (fx, fy, cx, cy), Tcw, Xw
+
+
+@pytest.mark.parametrize("th,check_ori", [(15.0, True), (50.0, False)])
+def test_search_by_projection_frames(orc, seq_frames, th, check_ori):
+    from gf_orb_slam_b200 import ORBmatcher, Frames
+    kps, desc, counts = seq_frames
+    B = 3
+    Last = Frames(kps[:B], desc[:B], counts[:B], W, H)
+    Cur = Frames(kps[1:B + 1], desc[1:B + 1], counts[1:B + 1], W, H)
+    lmp = np.full((B, 1000), -1, np.int32); lout = np.zeros((B, 1000), np.uint8); lworld = np.zeros((B, 1000, 3), np.float32)
+    Tcw = np.zeros((B, 4, 4), np.float32)
+    K = None
+    for b in range(B):
+        n = counts[b]
+        # sequence offset between frame b and b+1 is (-1, 0) px or (-1,-1): add it so projections land on the match
+        K, Tcw[b], lworld[b, :n] = _pose_and_world(kps[b], n, seed=70 + b, shift=(-1.0, 0.0))
+        u = synth.uniform01(90 + b, n)
+        lmp[b, :n] = np.where(u < 0.8, 1000 + np.arange(n), -1)
+        lout[b, :n] = (u > 0.75) & (u < 0.8)
+    cmp_ = np.full((B, 1000), -1, np.int32); csc = np.full((B, 1000), 999, np.int32)
+    cmp_[2, 0:30:4] = 777
+    cmp0 = cmp_.copy()
+    m = ORBmatcher(0.9, check_ori, max_batch=B, max_keypoints=1000, max_queries=1000)
+    nm = m.SearchByProjectionFrames(Cur, Last, lmp, lout, lworld, Tcw, K, th, cmp_, csc)
+    for b in range(B):
+        fl = _oframe(orc, kps[b], desc[b], counts[b]); fc = _oframe(orc, kps[b + 1], desc[b + 1], counts[b + 1])
+        fl.set_mappoints(lmp[b, :counts[b]], lout[b, :counts[b]])
+        fc.set_mappoints(cmp0[b, :counts[b + 1]])
+        fc.set_camera(*K, Tcw[b])
+        en = orc.search_by_projection_frames(fc, fl, lworld[b, :counts[b]], th, 0.9, check_ori)
+        emp, esc = fc.matches()
+        assert nm[b] == en, (b, nm[b], en)
+        assert np.array_equal(cmp_[b, :counts[b + 1]], emp) and np.array_equal(csc[b, :counts[b + 1]], esc)
+    assert nm[0] > 50
+
+
+@pytest.mark.parametrize("window,minL,maxL", [(100, -1, 0x7FFFFFFF), (200, 1, 4)])
+def test_window_search(orc, seq_frames, window, minL, maxL):
+    from gf_orb_slam_b200 import ORBmatcher, Frames
+    kps, desc, counts = seq_frames
+    B = 3
+    F1 = Frames(kps[:B], desc[:B], counts[:B], W, H)
+    F2 = Frames(kps[1:B + 1], desc[1:B + 1], counts[1:B + 1], W, H)
+    f1mp = np.full((B, 1000), -1, np.int32)
+    for b in range(B):
+        u = synth.uniform01(33 + b, counts[b])
+        f1mp[b, :counts[b]] = np.where(u < 0.85, 5000 + np.arange(counts[b]), -1)
+    m = ORBmatcher(0.9, True, max_batch=B, max_keypoints=1000, max_queries=1000)
+    nm, m2 = m.WindowSearch(F1, F2, f1mp, window, minL, maxL)
+    for b in range(B):
+        f1 = _oframe(orc, kps[b], desc[b], counts[b]); f2 = _oframe(orc, kps[b + 1], desc[b + 1], counts[b + 1])
+        f1.set_mappoints(f1mp[b, :counts[b]])
+        en, e2 = orc.window_search(f1, f2, window, minL, maxL, 0.9, True)
+        assert nm[b] == en, (b, nm[b], en)
+        assert np.array_equal(m2[b, :counts[b + 1]], e2)
+    assert nm[0] > 50
+
+
+def test_empty_and_ragged(orc, seq_frames):
+    """frames with zero keypoints and different counts in one batch; zero map points"""
+    from gf_orb_slam_b200 import ORBmatcher, Frames, MapPoints
+    kps, desc, counts = seq_frames
+    c1 = counts[:3].copy(); c1[1] = 0
+    c2 = counts[1:4].copy(); c2[2] = 0; c2[0] = 17
+    F1 = Frames(kps[:3], desc[:3], c1, W, H); F2 = Frames(kps[1:4], desc[1:4], c2, W, H)
+    prev = np.stack([kps["x"][:3], kps["y"][:3]], axis=-1).astype(np.float32).copy()
+    prev0 = prev.copy()
+    m = ORBmatcher(0.9, True, max_batch=3, max_keypoints=1000, max_queries=1000)
+    nm, m12 = m.SearchForInitialization(F1, F2, prev, 100)
+    for b in range(3):
+        f1 = _oframe(orc, kps[b], desc[b], c1[b]); f2 = _oframe(orc, kps[b + 1], desc[b + 1], c2[b])
+        n, e12, _ = orc.search_for_initialization(f1, f2, prev0[b, :c1[b]], 100, 0.9, True)
+        assert nm[b] == n and np.array_equal(m12[b, :c1[b]], e12)
+    assert nm[1] == 0 and nm[2] == 0
+    z = lambda dt, *s: np.zeros(s, dt)
+    mps = MapPoints(z(np.float32, 3, 4), z(np.float32, 3, 4), z(np.int32, 3, 4), z(np.float32, 3, 4), z(np.uint8, 3, 4),
+                    z(np.uint8, 3, 4, 32), np.zeros(3, np.int32))
+    fmp = np.full((3, 1000), -1, np.int32); fsc = np.full((3, 1000), 999, np.int32)
+    assert np.array_equal(m.SearchByProjection(F2, mps, 1.0, fmp, fsc), [0, 0, 0]) and (fmp == -1).all()
+
+
+def test_allpairs_top2():
+    import torch
+    from gf_orb_slam_b200 import ORBmatcher
+    rng = np.random.default_rng(9)
+    nq, ndb = 777, 20011
+    q = rng.integers(0, 256, (nq, 32), dtype=np.uint8)
+    db = rng.integers(0, 256, (ndb, 32), dtype=np.uint8)
+    db[100] = q[5]; db[9000] = q[5]; db[20010] = q[776]        # exact hits + a tie (lower index must win)
+    m = ORBmatcher(max_batch=1)
+    keys = m.AllPairsTop2(torch.from_numpy(q).cuda(), torch.from_numpy(db).cuda(), idx_base=1000).cpu().numpy()
+    lut = np.array([bin(i).count("1") for i in range(256)], np.int32)
+    for s in range(0, nq, 64):
+        d = lut[q[s:s + 64, None, :] ^ db[None, :, :]].sum(-1)
+        key = d.astype(np.int64) * (1 << 32) + (np.arange(ndb, dtype=np.int64) + 1000)[None, :]
+        part = np.sort(key, axis=1)[:, :2]
+        assert np.array_equal(keys[s:s + 64], part), s
+    assert keys[5, 0] == 1100 and keys[5, 1] == 10000 and keys[776, 0] == 21010
+    # shard merge: two half-shards merged == the full result
+    h = ndb // 2
+    qd, dd = torch.from_numpy(q).cuda(), torch.from_numpy(db).cuda()
+    k0 = m.AllPairsTop2(qd, dd[:h], idx_base=1000).clone(); k1 = m.AllPairsTop2(qd, dd[h:], idx_base=1000 + h).clone()
+    merged = m.Top2Merge(torch.stack([k0, k1])).cpu().numpy()
+    assert np.array_equal(merged, keys)
