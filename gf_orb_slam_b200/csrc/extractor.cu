@@ -556,6 +556,7 @@ __global__ void __launch_bounds__(256) k_describe(const uint8_t* __restrict__ py
 
 // ================================================================================================ host side
 struct Stage { const char* name; cudaEvent_t e0, e1; float ms; };
+struct StageRec { int stage; cudaEvent_t e0, e1; };   // one (stage, call) pair recorded while profiling is on
 
 }  // namespace gforb
 
@@ -589,7 +590,9 @@ struct GforbExtractor {
     size_t capPyr = 0, capCand = 0, capKp = 0, capCells = 0, capTiles = 0, capTabs = 0, capImg = 0;
     int lastBatch = 0, lastLaunches = 0, numSMs = 148;
     bool profiling = false;
-    std::vector<Stage> stages;
+    std::vector<Stage> stages;          // per-stage name + average ms over the recorded calls
+    std::vector<StageRec> recs;         // raw event pairs since profiling was switched on
+    std::vector<cudaEvent_t> evPool;    // recycled events
 };
 
 static int build_ctor_tables(GforbExtractor* E) {
@@ -813,7 +816,8 @@ int gforb_extractor_destroy(GforbExtractor* E) {
                     E->d_cnt20, E->d_nTotal, E->d_nToRetain, E->d_cellOff, E->d_lvlPre, E->d_lvlCount, E->d_err,
                     E->d_levels, E->d_cells, E->d_tiles, E->d_tabs};
     for (void* p : ptrs) if (p) cudaFree(p);
-    for (auto& s : E->stages) { cudaEventDestroy(s.e0); cudaEventDestroy(s.e1); }
+    for (auto& r : E->recs) { cudaEventDestroy(r.e0); cudaEventDestroy(r.e1); }
+    for (auto& e : E->evPool) cudaEventDestroy(e);
     if (E->ownStream) cudaStreamDestroy(E->ownStream);
     delete E;
     return GFORB_OK;
@@ -827,10 +831,32 @@ int gforb_extractor_tables(const GforbExtractor* E, float* sf, int32_t* fpl) {
     return GFORB_OK;
 }
 int gforb_extractor_last_launches(const GforbExtractor* E) { return E ? E->lastLaunches : GFORB_ERR_ARG; }
-int gforb_extractor_set_profiling(GforbExtractor* E, int on) { if (!E) return GFORB_ERR_ARG; E->profiling = on != 0; return GFORB_OK; }
-int gforb_extractor_stage_time(const GforbExtractor* E, int i, const char** name, float* ms) {
+int gforb_extractor_set_profiling(GforbExtractor* E, int on) {
     if (!E) return GFORB_ERR_ARG;
-    if (i >= 0 && i < (int)E->stages.size()) { if (name) *name = E->stages[i].name; if (ms) *ms = E->stages[i].ms; }
+    E->profiling = on != 0;
+    if (on) {        // restart the accumulation
+        for (auto& r : E->recs) { E->evPool.push_back(r.e0); E->evPool.push_back(r.e1); }
+        E->recs.clear();
+        for (auto& s : E->stages) s.ms = 0.f;
+    }
+    return GFORB_OK;
+}
+// average device time of stage i over every call recorded since set_profiling(h, 1); the caller must have
+// synchronised the launch stream.  Returns the number of stages.
+int gforb_extractor_stage_time(const GforbExtractor* Ec, int i, const char** name, float* ms) {
+    GforbExtractor* E = const_cast<GforbExtractor*>(Ec);
+    if (!E) return GFORB_ERR_ARG;
+    if (i >= 0 && i < (int)E->stages.size()) {
+        double sum = 0; int n = 0;
+        for (auto& r : E->recs) {
+            if (r.stage != i) continue;
+            float t = 0.f;
+            if (cudaEventElapsedTime(&t, r.e0, r.e1) == cudaSuccess) { sum += t; n++; }
+        }
+        E->stages[i].ms = n ? (float)(sum / n) : 0.f;
+        if (name) *name = E->stages[i].name;
+        if (ms) *ms = E->stages[i].ms;
+    }
     return (int)E->stages.size();
 }
 
@@ -868,13 +894,21 @@ int gforb_extract(GforbExtractor* E, const uint8_t* images, int w, int h, int st
 
     int launches = 0;
     size_t si = 0;
-    auto begin = [&](const char* name) {
-        if (!E->profiling) return;
-        if (si >= E->stages.size()) { Stage s; s.name = name; s.ms = 0; cudaEventCreate(&s.e0); cudaEventCreate(&s.e1); E->stages.push_back(s); }
-        E->stages[si].name = name;
-        cudaEventRecord(E->stages[si].e0, st);
+    auto getEv = [&]() {
+        cudaEvent_t e;
+        if (!E->evPool.empty()) { e = E->evPool.back(); E->evPool.pop_back(); } else cudaEventCreate(&e);
+        return e;
     };
-    auto end = [&]() { if (!E->profiling) return; cudaEventRecord(E->stages[si].e1, st); si++; };
+    const bool prof = E->profiling && E->recs.size() < 65536;
+    auto begin = [&](const char* name) {
+        if (!prof) return;
+        if (si >= E->stages.size()) { Stage s; s.name = name; s.ms = 0; s.e0 = s.e1 = nullptr; E->stages.push_back(s); }
+        E->stages[si].name = name;
+        StageRec r; r.stage = (int)si; r.e0 = getEv(); r.e1 = getEv();
+        E->recs.push_back(r);
+        cudaEventRecord(r.e0, st);
+    };
+    auto end = [&]() { if (!prof) return; cudaEventRecord(E->recs.back().e1, st); si++; };
     const int gsBlocks = E->numSMs * 8;
 
     begin("pyramid");
@@ -922,7 +956,6 @@ int gforb_extract(GforbExtractor* E, const uint8_t* images, int w, int h, int st
         int err = 0;
         GF_CUDA_OK(cudaMemcpy(&err, E->d_err, sizeof(int), cudaMemcpyDeviceToHost));
         if (err) { cudaMemset(E->d_err, 0, sizeof(int)); return err; }
-        if (E->profiling) for (auto& s : E->stages) cudaEventElapsedTime(&s.ms, s.e0, s.e1);
     }
     return GFORB_OK;
 }

@@ -1,0 +1,214 @@
+"""The per-frame tracking front end as one batched device pipeline (BASELINE.json metric: extract + match + GF-select).
+
+For every frame t of a batch:  ORBextractor::operator() -> ORBmatcher::SearchForInitialization(frame t-1, frame t,
+window 100, nnratio 0.9, checkOri)  (the map-free frame-to-frame matcher) ->
+Observability::runMatrixBuilding(FRAME_INFO_MATRIX) + maxVolSelection_LazierGreedy (config C4: <=1000 matched points,
+pick 100, eps 0.1).  All stages run in libgforb.so kernels on one CUDA stream; torch only owns the HBM buffers.
+Frame t-1 of the first frame of a batch is the last frame of the previous batch (1-frame halo)."""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from . import synth
+from .extractor import ORBextractor
+from .matcher import Frames, ORBmatcher
+from .observability import LAZIER_GREEDY, Observability
+
+from .pipeline_consts import EUROC_CAM, SIMU_XV, level_sigma2, level_sizes, sample_scale_for  # noqa: F401
+
+
+class TrackingFrontEnd:
+    def __init__(self, width=752, height=480, nfeatures=1000, batch=64, *, n_good=100, error_bound=0.1, window=100,
+                 nnratio=0.9, device=0, cloud_seed=7):
+        self.w, self.h, self.nf, self.B, self.k = width, height, nfeatures, batch, n_good
+        self.window = window
+        self.dev = torch.device("cuda", device)
+        torch.cuda.set_device(self.dev)
+        B, nf = batch, nfeatures
+        self.ex = ORBextractor(nfeatures, 1.2, 8, max_width=width, max_height=height, max_batch=batch, device=device)
+        self.matcher = ORBmatcher(nnratio, True, max_batch=batch, max_keypoints=nfeatures, max_queries=nfeatures,
+                                  cand_pool=48 * nfeatures, device=device)
+        cam = dict(EUROC_CAM); cam["nRows"], cam["nCols"] = height, width
+        self.obs = Observability(**cam, max_batch=batch, max_points=nfeatures, device=device)
+        self.obs.set_state(SIMU_XV)
+        self.obs.predictPWLSVec(0.1, 1)
+        xv = self.obs.kinematic(0)["Xv"]
+        self.sample_scale = sample_scale_for(nfeatures, n_good, error_bound)
+        z = lambda *s, dt=torch.float32: torch.zeros(s, dtype=dt, device=self.dev)
+        self.images = z(B, height, width, dt=torch.uint8)
+        self.kps = z(B + 1, nf, 7)                       # slot 0 = halo (last frame of the previous batch)
+        self.desc = z(B + 1, nf, 32, dt=torch.uint8)
+        self.counts = z(B + 1, dt=torch.int32)
+        self.prev = z(B, nf, 2)
+        self.m12 = z(B, nf, dt=torch.int32)
+        self.nmatch = z(B, dt=torch.int32)
+        # synthetic matched map points of every keypoint slot (tools/simu_greedy.cc recipe, fixed per slot)
+        world, _, score, _ = synth.landmark_cloud(nf, cloud_seed)
+        self.world_h, self.score_h = world, score
+        self.world = torch.from_numpy(np.broadcast_to(world, (B, nf, 3)).copy()).to(self.dev)
+        self.score = torch.from_numpy(np.broadcast_to(score, (B, nf)).copy()).to(self.dev)
+        self.valid = torch.ones((B, nf), dtype=torch.uint8, device=self.dev)
+        self.octave = z(B, nf, dt=torch.int32)
+        self.Xv = torch.from_numpy(np.broadcast_to(xv, (B, 13)).copy()).to(self.dev)
+        self.xv_h = xv
+        self.sigma2_h = level_sigma2()
+        self.sigma2 = torch.from_numpy(self.sigma2_h).to(self.dev)
+        self.blocks = z(B, nf, 49, dt=torch.float64)
+        self.obs_score = z(B, nf, dt=torch.float64)
+        self.sel_idx = z(B, n_good, dt=torch.int32)
+        self.sel_ld = z(B, n_good, dt=torch.float64)
+        self.sel_n = z(B, dt=torch.int32)
+        self.seeds = torch.ones(B, dtype=torch.int32, device=self.dev)
+        self.F1 = Frames(self.kps[:B], self.desc[:B], self.counts[:B], width, height)
+        self.F2 = Frames(self.kps[1:], self.desc[1:], self.counts[1:], width, height)
+        self.kps_i32 = self.kps.view(torch.int32)
+        self.launches_per_step = 0
+        self.profile = False
+        self._ev = []                       # (stage, start, end) torch events recorded while self.profile
+        # pinned host staging for the end-to-end path
+        self.h_images = torch.zeros((B, height, width), dtype=torch.uint8).pin_memory()
+        self.h_kps = torch.zeros((B, nf, 7), dtype=torch.float32).pin_memory()
+        self.h_desc = torch.zeros((B, nf, 32), dtype=torch.uint8).pin_memory()
+        self.h_counts = torch.zeros(B, dtype=torch.int32).pin_memory()
+        self.h_m12 = torch.zeros((B, nf), dtype=torch.int32).pin_memory()
+        self.h_nmatch = torch.zeros(B, dtype=torch.int32).pin_memory()
+        self.h_sel_idx = torch.zeros((B, n_good), dtype=torch.int32).pin_memory()
+        self.h_sel_n = torch.zeros(B, dtype=torch.int32).pin_memory()
+
+    # ---- one step = one batch of B frames through the whole front end, everything resident in HBM
+    def _mark(self, name=None):
+        """stage boundary: closes the open stage and opens `name` (CUDA events on the launch stream)"""
+        if not self.profile:
+            return
+        e = torch.cuda.Event(enable_timing=True)
+        e.record()
+        if self._open is not None:
+            self._ev.append((self._open[0], self._open[1], e))
+        self._open = (name, e) if name else None
+
+    def step_device(self, images: torch.Tensor | None = None):
+        B = self.B
+        st = torch.cuda.current_stream().cuda_stream
+        img = self.images if images is None else images
+        self._open = None
+        self._mark("extract")
+        # halo: last frame of the previous batch becomes slot 0
+        self.kps[0].copy_(self.kps[B]); self.desc[0].copy_(self.desc[B]); self.counts[0:1].copy_(self.counts[B:B + 1])
+        self.ex.extract_device(img, self.kps[1:], self.desc[1:], self.counts[1:], stream=st, sync=False)
+        n = self.ex.last_launches()
+        self._mark("match")
+        self.prev.copy_(self.kps[:B, :, 0:2])                               # vbPrevMatched[i] = F1.mvKeysUn[i].pt
+        self.matcher.SearchForInitialization(self.F1, self.F2, self.prev, self.window, matches12=self.m12,
+                                             nmatches=self.nmatch, stream=st, sync=False)
+        n += self.matcher.last_launches()
+        self._mark("info")
+        self.octave.copy_(self.kps_i32[1:, :, 5])
+        self.obs.build_info_frame(self.Xv, self.world, self.octave, self.score, self.valid, self.counts[1:], self.sigma2,
+                                  blocks=self.blocks, obs_score=self.obs_score, stream=st, sync=False)
+        n += self.obs.last_launches()
+        self._mark("select")
+        self.obs.select(self.blocks, self.obs_score, self.counts[1:], self.k, LAZIER_GREEDY, self.sample_scale, self.seeds,
+                        out_idx=self.sel_idx, out_logdet=self.sel_ld, out_n=self.sel_n, stream=st, sync=False)
+        n += self.obs.last_launches()
+        self._mark(None)
+        self.launches_per_step = n
+        return n
+
+    def stage_times(self):
+        """average ms per pipeline stage over the steps recorded with self.profile (stream must be synchronised)"""
+        acc = {}
+        for name, e0, e1 in self._ev:
+            t, c = acc.get(name, (0.0, 0))
+            acc[name] = (t + e0.elapsed_time(e1), c + 1)
+        self._ev = []
+        return [(k, t / c) for k, (t, c) in acc.items()]
+
+    def pyramid_bytes(self) -> int:
+        return 2 * self.B * sum((w + 32) * (h + 32) for w, h in level_sizes(self.w, self.h))
+
+    def algorithmic_bytes(self):
+        """SURVEY 8(d) materialised-stage model per frame: B = 5P - P0 - P7 + 60 N, split per extractor stage."""
+        px = [w * h for w, h in level_sizes(self.w, self.h)]
+        P = sum(px)
+        per = {"pyramid": (P - px[-1]) + (P - px[0]), "detect": P, "select": 0, "orient": 0, "blur": 2 * P,
+               "describe": 60 * self.nf}
+        return {"per_stage": per, "extract_frame": sum(per.values()), "traffic": {}}
+
+    # ---- the same step through host buffers: H2D of the frames, D2H of every result a Tracking caller consumes
+    def step_host(self):
+        B = self.B
+        self.images.copy_(self.h_images, non_blocking=True)
+        self.step_device()
+        self.h_kps.copy_(self.kps[1:], non_blocking=True)
+        self.h_desc.copy_(self.desc[1:], non_blocking=True)
+        self.h_counts.copy_(self.counts[1:], non_blocking=True)
+        self.h_m12.copy_(self.m12, non_blocking=True)
+        self.h_nmatch.copy_(self.nmatch, non_blocking=True)
+        self.h_sel_idx.copy_(self.sel_idx, non_blocking=True)
+        self.h_sel_n.copy_(self.sel_n, non_blocking=True)
+
+    def h2d_bytes(self) -> int:
+        return self.h_images.numel()
+
+    def d2h_bytes(self) -> int:
+        return sum(t.numel() * t.element_size() for t in (self.h_kps, self.h_desc, self.h_counts, self.h_m12, self.h_nmatch,
+                                                           self.h_sel_idx, self.h_sel_n))
+
+
+def cpu_front_end(oracle, frames: np.ndarray, prev_kd, world, score, xv, sigma2, k, sample_scale, window=100, nnratio=0.9,
+                  cam=None):
+    """The same per-frame chain on the CPU oracle (checker / cpu_baseline only).  prev_kd = (kps, desc) of the frame
+    before frames[0] or None.  Returns per frame (kps, desc, matches12 or None, nmatches, sel_idx, sel_logdet)."""
+    h, w = frames.shape[1:]
+    ex = oracle.ORBextractor(1000 if world is None else world.shape[0], 1.2, 8)
+    cam = dict(EUROC_CAM) if cam is None else cam
+    ob = oracle.Observability(**cam)
+    out = []
+    for t in range(frames.shape[0]):
+        kps, desc = ex(frames[t])
+        m12, nm = None, 0
+        if prev_kd is not None:
+            f1 = oracle.Frame(prev_kd[0], prev_kd[1], w, h); f2 = oracle.Frame(kps, desc, w, h)
+            pm = np.stack([prev_kd[0]["x"], prev_kd[0]["y"]], -1).astype(np.float32)
+            nm, m12, _ = oracle.search_for_initialization(f1, f2, pm, window, nnratio, True)
+        n = len(kps)
+        ob.set_xv(xv); ob.predict(0.1, 1)
+        blocks, obs, _ = ob.build_frame(world[:n], kps["octave"], score[:n], np.ones(n, np.uint8), sigma2)
+        si, sl = oracle.select(blocks, k, 2, sample_scale, 1, scores=obs) if n > 0 else (np.zeros(0, np.int32), np.zeros(0))
+        out.append((kps, desc, m12, nm, si, sl))
+        prev_kd = (kps, desc)
+    return out
+
+
+def smoke_check(oracle, device=0, batch=3):
+    """One small batch through the CUDA front end, checked bit-exactly against the CPU oracle."""
+    seq = synth.Sequence()
+    frames = seq.frames(0, 2 * batch)
+    fe = TrackingFrontEnd(batch=batch, device=device)
+    res = []
+    for s in range(2):
+        fe.images.copy_(torch.from_numpy(frames[s * batch:(s + 1) * batch]))
+        fe.step_device()
+        torch.cuda.synchronize()
+        res.append([t.cpu().numpy().copy() for t in (fe.kps[1:], fe.desc[1:], fe.counts[1:], fe.m12, fe.nmatch, fe.sel_idx,
+                                                      fe.sel_ld, fe.sel_n)])
+    exp = cpu_front_end(oracle, frames, None, fe.world_h, fe.score_h, fe.xv_h, fe.sigma2_h, fe.k, fe.sample_scale)
+    from ._lib import KP_DTYPE
+    nmatched = 0
+    for s in range(2):
+        kps, desc, counts, m12, nmatch, sidx, sld, sn = res[s]
+        for b in range(batch):
+            t = s * batch + b
+            ek, ed, em12, enm, esi, esl = exp[t]
+            n = counts[b]
+            assert n == len(ek), ("keypoint count", t, n, len(ek))
+            gk = kps[b, :n].copy().view(KP_DTYPE).reshape(-1)
+            assert gk.tobytes() == ek.tobytes(), ("keypoints", t)
+            assert np.array_equal(desc[b, :n], ed), ("descriptors", t)
+            if t > 0:
+                assert nmatch[b] == enm and np.array_equal(m12[b, :len(em12)], em12), ("matches", t)
+                nmatched += int(enm)
+            assert sn[b] == len(esi) and np.array_equal(sidx[b, :sn[b]], esi), ("good-feature subset", t)
+            assert np.allclose(sld[b, :sn[b]], esl, rtol=1e-5), ("log-det", t)
+    return dict(frames=2 * batch, launches_per_step=fe.launches_per_step, matches=nmatched, selected=int(res[1][7].sum()))

@@ -313,3 +313,21 @@ def select(blocks: np.ndarray, k: int, mtd: int = 2, sample_scale: float = 23.0,
     idx = np.empty(n, np.int32); ld = np.zeros(n, np.float64)
     m = lib().orc_obs_select(_p(blocks), _p(sc), n, k, mtd, C.c_double(sample_scale), C.c_long(seed), _p(idx), _p(ld))
     return idx[:m].copy(), ld[:m].copy()
+
+
+def front_end_batch(imgs: np.ndarray, threads: int, world, score, xv, sigma2, k: int, sample_scale: float, window=100,
+                    nnratio=0.9, cam=None):
+    """extract + SearchForInitialization(prev, cur) + info blocks + lazier-greedy selection for every frame, frames
+    split over `threads` C++ threads (cpu_baseline / --impl reference leg of bench.py)."""
+    imgs = np.ascontiguousarray(imgs, np.uint8)
+    nf, h, w = imgs.shape
+    world = np.ascontiguousarray(world, np.float32); score = np.ascontiguousarray(score, np.int32)
+    xv = np.ascontiguousarray(xv, np.float64); sigma2 = np.ascontiguousarray(sigma2, np.float32)
+    c = cam or dict(f=5.1369248, nRows=h, nCols=w, Cx=367.215, Cy=248.375, k1=0.0, k2=0.0, dx=0.01123325985, dy=0.01123325985)
+    cam9 = np.array([c["f"], c["nRows"], c["nCols"], c["Cx"], c["Cy"], c["k1"], c["k2"], c["dx"], c["dy"]], np.float64)
+    counts = np.zeros(nf, np.int32); nmatch = np.zeros(nf, np.int32)
+    sel = np.full((nf, k), -1, np.int32); seln = np.zeros(nf, np.int32)
+    lib().orc_front_end_batch(_p(imgs), w, h, nf, threads, world.shape[0], _p(world), _p(score), _p(xv), _p(sigma2), k,
+                              C.c_double(sample_scale), window, C.c_float(nnratio), _p(cam9), _p(counts), _p(nmatch),
+                              _p(sel), _p(seln))
+    return counts, nmatch, sel, seln

@@ -220,3 +220,81 @@ int orc_obs_select(const double* blocks, const double* obsScore, int n, int k, i
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------ whole front end (cpu_baseline / --impl reference)
+// extract -> SearchForInitialization(prev, cur) -> batchInfoMat_Frame + maxVolSelection_LazierGreedy for every frame,
+// frames split into contiguous chunks over `threads` std::threads (one extractor per thread, 1-frame halo per chunk:
+// the reference extractor/matcher are single-threaded per frame).  rand() is replaced by a thread-local random_r
+// (same glibc TYPE_3 generator, seed 1 per frame) so threads neither race nor contend on glibc's lock.
+#include <stdlib.h>
+namespace {
+thread_local struct random_data tl_rd;
+thread_local char tl_state[128];
+thread_local bool tl_init = false;
+int tl_rand() { int32_t r; random_r(&tl_rd, &r); return (int)r; }
+void tl_srand(unsigned seed) {
+    if (!tl_init) { memset(&tl_rd, 0, sizeof(tl_rd)); initstate_r(seed, tl_state, sizeof(tl_state), &tl_rd); tl_init = true; }
+    srandom_r(seed, &tl_rd);
+}
+}  // namespace
+
+extern "C" int orc_front_end_batch(const uint8_t* imgs, int w, int ht, int nframes, int threads, int nfeatures,
+                                   const float* world, const int* score, const double* xv13, const float* sigma2, int k,
+                                   double sampleScale, int window, float nnratio, const double* cam9, int* out_counts,
+                                   int* out_nmatch, int* out_sel, int* out_seln) {
+    if (threads < 1) threads = 1;
+    if (threads > nframes) threads = nframes;
+    std::vector<std::thread> pool;
+    for (int t = 0; t < threads; t++)
+        pool.emplace_back([=]() {
+            const int s = (int)((long long)nframes * t / threads), e = (int)((long long)nframes * (t + 1) / threads);
+            ORBextractor ex(nfeatures, 1.2f, 8, FAST_SCORE, 20, 7, 0, 0);
+            Observability ob(cam9[0], (int)cam9[1], (int)cam9[2], cam9[3], cam9[4], cam9[5], cam9[6], cam9[7], cam9[8]);
+            ob.rand_fn = &tl_rand;
+            memcpy(ob.Xv, xv13, sizeof(ob.Xv));
+            ob.predictPWLSVec(0.1, 1);
+            std::vector<KeyPoint> kp[2]; std::vector<uint8_t> de[2];
+            int cur = 0;
+            bool havePrev = false;
+            if (s > 0) { ex(imgs + (size_t)(s - 1) * w * ht, w, ht, w, kp[cur], de[cur]); havePrev = true; cur ^= 1; }
+            std::vector<double> blocks, obsScore;
+            std::vector<uint8_t> valid;
+            std::vector<int> oct;
+            for (int f = s; f < e; f++) {
+                ex(imgs + (size_t)f * w * ht, w, ht, w, kp[cur], de[cur]);
+                const int n = (int)kp[cur].size();
+                out_counts[f] = n;
+                int nm = 0;
+                if (havePrev) {
+                    Frame F1, F2;
+                    F1.init(kp[cur ^ 1].data(), de[cur ^ 1].data(), (int)kp[cur ^ 1].size(), w, ht, 8, 1.2f);
+                    F2.init(kp[cur].data(), de[cur].data(), n, w, ht, 8, 1.2f);
+                    std::vector<float> pm(2 * kp[cur ^ 1].size());
+                    for (size_t i = 0; i < kp[cur ^ 1].size(); i++) { pm[2 * i] = kp[cur ^ 1][i].x; pm[2 * i + 1] = kp[cur ^ 1][i].y; }
+                    std::vector<int> m12;
+                    ORBmatcher m(nnratio, true);
+                    nm = m.SearchForInitialization(F1, F2, pm, m12, window);
+                }
+                out_nmatch[f] = nm;
+                blocks.assign((size_t)n * 49, 0.0); obsScore.assign(n, 0.0); valid.assign(n, 1); oct.resize(n);
+                for (int i = 0; i < n; i++) oct[i] = kp[cur][i].octave;
+                ob.mKineIdx = 0;
+                ob.batchInfoMat_Frame(world, oct.data(), score, valid.data(), n, sigma2, blocks.data(), obsScore.data(), nullptr);
+                ob.lmkSelectPool.resize(n);
+                for (int i = 0; i < n; i++) {
+                    GoodPoint& g = ob.lmkSelectPool[i];
+                    g.idx = i; g.obs_score = obsScore[i]; g.selected = false; g.upper_bound = 0;
+                    memcpy(g.obs_block, &blocks[(size_t)49 * i], sizeof(g.obs_block));
+                }
+                tl_srand(1);
+                std::vector<GoodPoint> sub;
+                if (n > 0) ob.maxVolSelection_LazierGreedy(0, n, &sub, k, sampleScale, 1e30);
+                out_seln[f] = (int)sub.size();
+                for (size_t i = 0; i < sub.size() && (int)i < k; i++) out_sel[(size_t)f * k + i] = (int)sub[i].idx;
+                havePrev = true;
+                cur ^= 1;
+            }
+        });
+    for (auto& th : pool) th.join();
+    return 0;
+}
