@@ -104,8 +104,8 @@ def cpu_leg(frames, threads, fe_consts):
 
 def consts():
     from gf_orb_slam_b200 import synth
-    from gf_orb_slam_b200.pipeline_consts import SIMU_XV, level_sigma2, sample_scale_for
-    world, _, score, _ = synth.landmark_cloud(NFEAT, 7)
+    from gf_orb_slam_b200.pipeline_consts import SIMU_XV, level_sigma2, sample_scale_for, simu_visible_from
+    world, _, score, _ = synth.landmark_cloud(NFEAT, 7, visible_from=simu_visible_from(W_, H_))
     return world, score, SIMU_XV, level_sigma2(), NGOOD, sample_scale_for(NFEAT, NGOOD, 0.1)
 
 

@@ -212,48 +212,11 @@ __global__ void __launch_bounds__(128) k_logdet(const double* __restrict__ mats,
     if (i < n) out[i] = logdet_sum(zero, mats + (size_t)i * 49, 1.0);
 }
 
-// ------------------------------------------------------------------------------------------------ glibc rand()
-// TYPE_3 additive feedback generator: r[i] = r[i-31] + r[i-3], output r[i] >> 1.
-struct GlibcRand {
-    uint32_t* r;    // 34-entry ring in shared memory
-    int i;          // next state index (mod 34)
-    __device__ void seed(uint32_t s) {
-        if (s == 0) s = 1;
-        int32_t word = (int32_t)s;
-        r[0] = s;
-        for (int k = 1; k < 31; k++) {
-            const int32_t hi = word / 127773, lo = word % 127773;
-            word = 16807 * lo - 2836 * hi;
-            if (word < 0) word += 2147483647;
-            r[k] = (uint32_t)word;
-        }
-        for (int k = 31; k < 34; k++) r[k] = r[k - 31];
-        i = 0;          // ring position of state index 34
-        for (int k = 0; k < 310; k++) next();
-    }
-    __device__ __forceinline__ uint32_t next() {
-        // state index n = 34 + (calls so far); ring slot = n % 34
-        const int a = (i + 3) % 34;       // n - 31  == n + 3 (mod 34)
-        const int c = (i + 31) % 34;      // n - 3
-        const uint32_t v = r[a] + r[c];
-        r[i] = v;
-        i = (i + 1) % 34;
-        return v >> 1;
-    }
-};
-
-__global__ void k_rand_stream(uint32_t seed, int n, int32_t* out) {
-    __shared__ uint32_t ring[34];
-    if (threadIdx.x == 0 && blockIdx.x == 0) {
-        GlibcRand g; g.r = ring; g.seed(seed);
-        for (int k = 0; k < n; k++) out[k] = (int32_t)g.next();
-    }
-}
-
 // ------------------------------------------------------------------------------------------------ K12 selection
 enum { MTD_GREEDY = 1, MTD_LAZIER_SELECT = 2, MTD_LAZIER_AUTO = 3, MTD_LAZIER_DELETE = 5 };
 static const int SEL_THREADS = 256;
 static const int MAX_RANDOM_QUERY_TIME = 2000;
+static const int RAW_RING = 512;     // pre-generated rand() outputs (power of two)
 
 struct SelParams {
     const double* blocks;      // batch x stride x 49
@@ -268,8 +231,65 @@ struct SelParams {
     int outStride;
 };
 
+// Warp-parallel glibc rand(): the additive-feedback recurrence r[n] = r[n-31] + r[n-3] splits into three independent
+// chains (n mod 3), so lanes 0..2 produce 30 new states per call; outputs (state >> 1) go to a ring the sampler reads.
+struct WarpRand {
+    uint32_t* rs;      // 64-entry state ring (shared)
+    uint32_t* raw;     // RAW_RING-entry output ring (shared), indexed by output number
+    int n;             // next state index to generate (uniform across the warp); output number = n - 344
+    __device__ void seed(uint32_t s, int lane) {
+        if (lane == 0) {
+            if (s == 0) s = 1;
+            int32_t word = (int32_t)s;
+            rs[0] = s;
+            for (int k = 1; k < 31; k++) {
+                const int32_t hi = word / 127773, lo = word % 127773;
+                word = 16807 * lo - 2836 * hi;
+                if (word < 0) word += 2147483647;
+                rs[k] = (uint32_t)word;
+            }
+            for (int k = 31; k < 34; k++) rs[k] = rs[k - 31];
+        }
+        n = 34;
+        __syncwarp();
+    }
+    __device__ __forceinline__ void gen30(int lane) {
+        if (lane < 3) {
+            uint32_t prev = rs[(n + lane - 3) & 63];
+#pragma unroll
+            for (int t = 0; t < 10; t++) {
+                const int id = n + lane + 3 * t;
+                const uint32_t v = rs[(id - 31) & 63] + prev;
+                rs[id & 63] = v;
+                if (id >= 344) raw[(id - 344) & (RAW_RING - 1)] = v >> 1;
+                prev = v;
+            }
+        }
+        n += 30;
+        __syncwarp();
+    }
+    // make outputs [rp, rp + 32) available
+    __device__ __forceinline__ void ensure(int rp, int lane) {
+        while (n - 344 < rp + 32) gen30(lane);
+    }
+};
+
+__global__ void k_rand_stream(uint32_t seed, int n, int32_t* out) {
+    __shared__ uint32_t rs[64];
+    __shared__ uint32_t raw[RAW_RING];
+    const int lane = threadIdx.x;
+    WarpRand g; g.rs = rs; g.raw = raw;
+    g.seed(seed, lane);
+    for (int base = 0; base < n; base += 32) {
+        g.ensure(base, lane);
+        if (base + lane < n) out[base + lane] = (int32_t)raw[(base + lane) & (RAW_RING - 1)];
+        __syncwarp();
+    }
+}
+
 __global__ void __launch_bounds__(SEL_THREADS) k_select(const SelParams P) {
     extern __shared__ __align__(16) unsigned char smraw[];
+    const unsigned full = 0xffffffffu;
     const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int n = min(P.counts[b], min(P.stride, P.maxPoints));
     int* idxA = reinterpret_cast<int*>(smraw);
@@ -278,10 +298,12 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const SelParams P) {
     int* visB = idxB + P.maxPoints;
     int* list = visB + P.maxPoints;
     unsigned char* alive = reinterpret_cast<unsigned char*>(list + P.maxPoints);   // `selected` flag per pool entry
+    unsigned char* okf = alive + P.maxPoints;                                      // obs_score >= 0
     __shared__ double cur[49];
     __shared__ double redV[SEL_THREADS / 32];
     __shared__ int redT[SEL_THREADS / 32];
-    __shared__ uint32_t ring[34];
+    __shared__ uint32_t s_rs[64];
+    __shared__ uint32_t s_raw[RAW_RING];
     __shared__ int s_cnt, s_pick, s_pos;
     __shared__ double s_val;
     const double* blk = P.blocks + (size_t)b * P.stride * 49;
@@ -302,16 +324,20 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const SelParams P) {
     const size_t szLazier = (size_t)((double)n / (double)k * P.sampleScale);
     // init
     if (tid < 49) cur[tid] = (tid % 8 == 0) ? 0.00001 : 0.0;
-    for (int i = tid; i < n; i += SEL_THREADS) { idxA[i] = i; visA[i] = -1; alive[i] = deletion ? 1 : 0; }
+    for (int i = tid; i < n; i += SEL_THREADS) {
+        idxA[i] = i; visA[i] = -1; alive[i] = deletion ? 1 : 0;
+        okf[i] = (sc && sc[i] < 0) ? 0 : 1;
+    }
     __syncthreads();
     if (deletion && tid < 49) {       // curMat += every block, in pool order (:2370-2380)
         double s = cur[tid];
         for (int i = 0; i < n; i++) s = s + blk[(size_t)i * 49 + tid];
         cur[tid] = s;
     }
-    GlibcRand rng;
-    rng.r = ring; rng.i = 0;
-    if (tid == 0 && mtd != MTD_GREEDY) rng.seed(P.seeds ? P.seeds[b] : 1u);
+    WarpRand rng;
+    rng.rs = s_rs; rng.raw = s_raw; rng.n = 34;
+    if (warp == 0 && mtd != MTD_GREEDY) rng.seed(P.seeds ? P.seeds[b] : 1u, lane);
+    int rp = 0;                       // rand() calls consumed so far (warp 0)
     __syncthreads();
     int m = n;                        // live columns of lmkIdx / lmkVisited
     int* idx = idxA; int* vis = visA; int* idx2 = idxB; int* vis2 = visB;
@@ -326,8 +352,8 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const SelParams P) {
             __syncthreads();
             for (int base = 0; base < m; base += SEL_THREADS) {
                 const int j = base + tid;
-                const bool ok = j < m && !(sc && sc[idx[j]] < 0);
-                const unsigned bal = __ballot_sync(0xffffffffu, ok);
+                const bool ok = j < m && okf[idx[j]];
+                const unsigned bal = __ballot_sync(full, ok);
                 if (lane == 0) redT[warp] = __popc(bal);
                 __syncthreads();
                 int off = s_cnt;
@@ -337,25 +363,47 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const SelParams P) {
                 if (tid == 0) { int t = 0; for (int w = 0; w < SEL_THREADS / 32; w++) t += redT[w]; s_cnt += t; }
                 __syncthreads();
             }
-        } else if (tid == 0) {
-            size_t numHit = 0, szActual = szLazier;
+        } else if (warp == 0) {
+            // RANDOM_ACCESS_LAZIER_GREEDY sampling (:2895-2921), 32 rand() draws per step.  A draw is "new" if its
+            // column was not visited in this round; new + valid draws count towards szActualSubset; 2000 consecutive
+            // rejections stop the round.  Only the draws the sequential loop would have made are consumed.
+            size_t szActual = szLazier;
             if ((size_t)m < szActual) szActual = (size_t)m;
-            int cnt = 0;
-            while (numHit < szActual) {
-                int j = 0, numRndQue = 0;
-                while (numRndQue < MAX_RANDOM_QUERY_TIME) {
-                    j = (int)(rng.next() % (uint32_t)m);
-                    if (vis[j] < i) { vis[j] = i; break; }
-                    ++numRndQue;
-                }
-                if (numRndQue >= MAX_RANDOM_QUERY_TIME) break;
+            int numHit = 0, cnt = 0, rej = 0;
+            bool stop = (size_t)numHit >= szActual;
+            while (!stop) {
+                rng.ensure(rp, lane);
+                const uint32_t r = s_raw[(rp + lane) & (RAW_RING - 1)];
+                const int j = (int)(r % (uint32_t)m);
+                const bool seen = vis[j] >= i;
+                const unsigned same = __match_any_sync(full, j);
+                const bool isNew = !seen && (lane == __ffs(same) - 1);
                 const int que = idx[j];
-                ++numHit;
                 const bool sel = alive[que] != 0;
-                if ((deletion ? !sel : sel) || (sc && sc[que] < 0)) { --numHit; continue; }
-                list[cnt++] = que;
+                const bool valid = isNew && !((deletion ? !sel : sel) || !okf[que]);
+                const unsigned newMask = __ballot_sync(full, isNew), validMask = __ballot_sync(full, valid);
+                const unsigned le = (lane == 31) ? full : ((2u << lane) - 1u);
+                // cut A: numHit reaches szActual at this lane
+                const bool hitA = valid && (size_t)(numHit + __popc(validMask & le)) == szActual;
+                // cut B: this rejected draw is the 2000th consecutive rejection
+                const unsigned newBefore = newMask & (le >> 1);
+                const int lastNew = newBefore ? 31 - __clz(newBefore) : -1;
+                const int run = newBefore ? lane - lastNew : rej + lane + 1;
+                const bool hitB = !isNew && run >= MAX_RANDOM_QUERY_TIME;
+                const unsigned cutMask = __ballot_sync(full, hitA || hitB);
+                const int cut = cutMask ? __ffs(cutMask) - 1 : 31;
+                const unsigned take = (cut == 31) ? full : ((2u << cut) - 1u);
+                if (isNew && lane <= cut) vis[j] = i;
+                if (valid && lane <= cut) list[cnt + __popc(validMask & (le >> 1))] = que;
+                cnt += __popc(validMask & take);
+                numHit += __popc(validMask & take);
+                const unsigned newTaken = newMask & take;
+                rej = newTaken ? cut - (31 - __clz(newTaken)) : rej + cut + 1;
+                rp += cut + 1;
+                stop = cutMask != 0;
+                __syncwarp();
             }
-            s_cnt = cnt;
+            if (lane == 0) s_cnt = cnt;
         }
         __syncthreads();
         const int cnt = s_cnt;
@@ -367,8 +415,8 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const SelParams P) {
         }
 #pragma unroll
         for (int d = 16; d >= 1; d >>= 1) {
-            const double ov = __shfl_xor_sync(0xffffffffu, bestV, d);
-            const int ot = __shfl_xor_sync(0xffffffffu, bestT, d);
+            const double ov = __shfl_xor_sync(full, bestV, d);
+            const int ot = __shfl_xor_sync(full, bestT, d);
             if (ov > bestV || (ov == bestV && ot < bestT)) { bestV = ov; bestT = ot; }
         }
         if (lane == 0) { redV[warp] = bestV; redT[warp] = bestT; }
@@ -410,7 +458,7 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const SelParams P) {
             for (int base = 0; base < n; base += 32) {
                 const int j = base + lane;
                 const bool ok = j < n && alive[j];
-                const unsigned bal = __ballot_sync(0xffffffffu, ok);
+                const unsigned bal = __ballot_sync(full, ok);
                 const int o = off + __popc(bal & ((1u << lane) - 1u));
                 if (ok && o < P.outStride) { outIdx[o] = j; if (outLd) outLd[o] = 0.0; }
                 off += __popc(bal);
@@ -419,6 +467,7 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const SelParams P) {
         }
     } else if (tid == 0) P.outN[b] = min(nOut, P.outStride);
 }
+
 
 }  // namespace gforb
 
@@ -613,7 +662,7 @@ int obs_end(GforbObs* O, OCtx& c, int flags) {
     return GFORB_OK;
 }
 
-size_t select_smem(int maxPoints) { return (size_t)maxPoints * (5 * sizeof(int) + 1) + 16; }
+size_t select_smem(int maxPoints) { return (size_t)maxPoints * (5 * sizeof(int) + 2) + 16; }
 
 }  // namespace
 

@@ -15,7 +15,8 @@ from .extractor import ORBextractor
 from .matcher import Frames, ORBmatcher
 from .observability import LAZIER_GREEDY, Observability
 
-from .pipeline_consts import EUROC_CAM, SIMU_XV, level_sigma2, level_sizes, sample_scale_for  # noqa: F401
+from .pipeline_consts import (EUROC_CAM, SIMU_XV, level_sigma2, level_sizes, sample_scale_for,  # noqa: F401
+                              simu_visible_from)
 
 
 class TrackingFrontEnd:
@@ -44,7 +45,7 @@ class TrackingFrontEnd:
         self.m12 = z(B, nf, dt=torch.int32)
         self.nmatch = z(B, dt=torch.int32)
         # synthetic matched map points of every keypoint slot (tools/simu_greedy.cc recipe, fixed per slot)
-        world, _, score, _ = synth.landmark_cloud(nf, cloud_seed)
+        world, _, score, _ = synth.landmark_cloud(nf, cloud_seed, visible_from=simu_visible_from(width, height))
         self.world_h, self.score_h = world, score
         self.world = torch.from_numpy(np.broadcast_to(world, (B, nf, 3)).copy()).to(self.dev)
         self.score = torch.from_numpy(np.broadcast_to(score, (B, nf)).copy()).to(self.dev)

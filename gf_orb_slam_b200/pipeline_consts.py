@@ -32,3 +32,9 @@ def level_sizes(w: int, h: int, nlevels=8, scale_factor=1.2):
         out.append((int(np.rint(np.float32(w) * inv)), int(np.rint(np.float32(h) * inv))))
         inv = np.float32(inv * f)
     return out
+
+
+def simu_visible_from(width=752, height=480):
+    """(Xv, fu, fv, Cx, Cy, nCols, nRows) of the tools/simu_greedy.cc fixture, for synth.landmark_cloud(visible_from=)"""
+    c = EUROC_CAM
+    return (SIMU_XV, c["f"] / c["dx"], c["f"] / c["dy"], c["Cx"], c["Cy"], width, height)

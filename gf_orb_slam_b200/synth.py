@@ -73,12 +73,32 @@ class Sequence:
         return np.stack([self.frame(t) for t in range(t0, t0 + n)])
 
 
-def landmark_cloud(n: int, seed: int, xv: np.ndarray | None = None):
+def landmark_cloud(n: int, seed: int, visible_from=None):
     """tools/simu_greedy.cc:30-145 recipe with splitmix64 instead of the unseeded rand(): landmarks x,y in [-4,4],
     z in [0,8]; octave = round(7 U); match score = round(100 U).  Returns (world[n,3] f32, octave[n] i32,
     score[n] i32, U[n,2] noise in [-1,1))."""
-    u = (splitmix64(seed, 7 * n) >> np.uint64(11)).astype(np.float64) / float(1 << 53)
-    u = u.reshape(n, 7)
+    if visible_from is not None:
+        # tools/simu_greedy.cc:108-116 keeps a landmark only if project_Point_To_Frame (include/Observability.h:
+        # 299-333) puts it in front of the camera and inside the image; draw until n such landmarks exist
+        xv, fu, fv, cx, cy, ncols, nrows = visible_from
+        q0, qx, qy, qz = [float(v) for v in xv[3:7]]
+        R = np.array([[q0 * q0 + qx * qx - qy * qy - qz * qz, 2 * (qx * qy - q0 * qz), 2 * (qz * qx + q0 * qy)],
+                      [2 * (qx * qy + q0 * qz), q0 * q0 - qx * qx + qy * qy - qz * qz, 2 * (qy * qz - q0 * qx)],
+                      [2 * (qz * qx - q0 * qy), 2 * (qy * qz + q0 * qx), q0 * q0 - qx * qx - qy * qy + qz * qz]])
+        Rinv = np.linalg.inv(R)
+        m = 8 * n + 64
+        uu = ((splitmix64(seed, 7 * m) >> np.uint64(11)).astype(np.float64) / float(1 << 53)).reshape(m, 7)
+        w = np.stack([uu[:, 0] * 8 - 4, uu[:, 1] * 8 - 4, uu[:, 2] * 8], axis=1).astype(np.float32).astype(np.float64)
+        h = (w - np.asarray(xv[:3], np.float64)) @ Rinv.T
+        with np.errstate(divide="ignore", invalid="ignore"):
+            pu = fu * h[:, 0] / h[:, 2] + cx
+            pv = fv * h[:, 1] / h[:, 2] + cy
+        ok = (h[:, 2] > 0) & (pu >= 0) & (pu <= ncols) & (pv >= 0) & (pv <= nrows)
+        u = uu[ok][:n]
+        assert u.shape[0] == n, "not enough visible landmarks"
+    else:
+        u = (splitmix64(seed, 7 * n) >> np.uint64(11)).astype(np.float64) / float(1 << 53)
+        u = u.reshape(n, 7)
     world = np.stack([u[:, 0] * 8 - 4, u[:, 1] * 8 - 4, u[:, 2] * 8], axis=1).astype(np.float32)
     octave = np.round(u[:, 3] * 7).astype(np.int32)
     score = np.round(u[:, 4] * 100).astype(np.int32)
