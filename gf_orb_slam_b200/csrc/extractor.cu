@@ -38,7 +38,9 @@ struct CellPlan {
 };
 struct BlurTile { int level, x0, y0; };
 
-__constant__ signed char c_pattern[256 * 4];
+// bit_pattern_31_ (src/ORBextractor.cc:204-462) as 256 x {x0, y0, x1, y1}; lane j of k_describe reads its 32 bytes with
+// two 128-bit loads (a per-lane index into __constant__ memory would serialise on the ADU pipe: ncu r1_v1, adu=97%)
+__device__ __align__(16) signed char g_pattern[256 * 4];
 __constant__ int c_umax[16];
 __constant__ int c_gauss[2][7] = {{18, 34, 48, 56, 48, 34, 18}, {18, 34, 49, 55, 49, 34, 18}};
 
@@ -535,14 +537,15 @@ __global__ void __launch_bounds__(256) k_describe(const uint8_t* __restrict__ py
     const float a = glibc_cosf(angle), bb = glibc_sinf(angle);
     const uint8_t* P = pyr + (size_t)b * framePyr + L.off + (size_t)EDGE * L.pitch + EDGE;
     const uint8_t* B = blr + (size_t)b * framePyr + L.off + (size_t)EDGE * L.pitch + EDGE;
+    const uint4 pw0 = reinterpret_cast<const uint4*>(g_pattern)[lane * 2], pw1 = reinterpret_cast<const uint4*>(g_pattern)[lane * 2 + 1];
+    const uint32_t pw[8] = {pw0.x, pw0.y, pw0.z, pw0.w, pw1.x, pw1.y, pw1.z, pw1.w};
     int val = 0;
 #pragma unroll
     for (int t = 0; t < 8; t++) {
-        const signed char* pt = c_pattern + (lane * 8 + t) * 4;
         int tv[2];
 #pragma unroll
         for (int q = 0; q < 2; q++) {
-            float px = (float)pt[2 * q], py = (float)pt[2 * q + 1];
+            const float px = (float)(signed char)(pw[t] >> (16 * q)), py = (float)(signed char)(pw[t] >> (16 * q + 8));
             int iy = cv_round(__fadd_rn(__fmul_rn(px, bb), __fmul_rn(py, a)));
             int ix = cv_round(__fsub_rn(__fmul_rn(px, a), __fmul_rn(py, bb)));
             int x = cx + ix, y = cy + iy;
@@ -780,7 +783,7 @@ int gforb_extractor_create(const GforbExtractorConfig* cfg, GforbExtractor** out
     GF_CUDA_OK(cudaStreamCreateWithFlags(&E->ownStream, cudaStreamNonBlocking));
     cudaDeviceGetAttribute(&E->numSMs, cudaDevAttrMultiProcessorCount, cfg->device);
     build_ctor_tables(E);
-    GF_CUDA_OK(cudaMemcpyToSymbol(c_pattern, h_pattern, sizeof(h_pattern)));
+    GF_CUDA_OK(cudaMemcpyToSymbol(g_pattern, h_pattern, sizeof(h_pattern)));
     {   // umax (src/ORBextractor.cc:500-517)
         int umax[16];
         int v, v0, vmax = (int)floorf(HALF_PATCH * sqrtf(2.f) / 2 + 1), vmin = (int)ceilf(HALF_PATCH * sqrtf(2.f) / 2);

@@ -361,7 +361,7 @@ __global__ void __launch_bounds__(32) k_resolve(const RParams R) {
         bool done = cnt <= 0;
         while (__any_sync(full, !done)) {
             bool acc = false;
-            int bi = -1, best = INT_MAX;
+            int bi = -1, bi2 = -1, best = INT_MAX;     // bi2 = the candidate that defines the second-best distance
             if (!done) {
                 int best2 = INT_MAX, bl = -1, bl2 = -1;
                 for (int c = 0; c < cnt; c++) {
@@ -369,14 +369,14 @@ __global__ void __launch_bounds__(32) k_resolve(const RParams R) {
                     const int i2 = e & 0xffff, dist = (int)(e >> 20), oct = (e >> 16) & 15;
                     if (MODE == M_INIT) {
                         if (state[i2] <= dist) continue;                        // :1211
-                        if (dist < best) { best2 = best; best = dist; bi = i2; }
-                        else if (dist < best2) best2 = dist;
+                        if (dist < best) { best2 = best; bi2 = bi; best = dist; bi = i2; }
+                        else if (dist < best2) { best2 = dist; bi2 = i2; }
                     } else {
                         if (state[i2] >= 0) continue;                           // claimed (:426, :1040, :2150)
                         if (MODE == M_LAST) {
                             if (dist < best) { best = dist; bi = i2; }
-                        } else if (dist < best) { best2 = best; best = dist; bl2 = bl; bl = oct; bi = i2; }
-                        else if (dist < best2) { bl2 = oct; best2 = dist; }
+                        } else if (dist < best) { best2 = best; bi2 = bi; best = dist; bl2 = bl; bl = oct; bi = i2; }
+                        else if (dist < best2) { bl2 = oct; best2 = dist; bi2 = i2; }
                     }
                 }
                 if (MODE == M_INIT) acc = best <= TH_LOW && (float)best < (float)best2 * R.nnratio;
@@ -387,10 +387,11 @@ __global__ void __launch_bounds__(32) k_resolve(const RParams R) {
             }
             if (!done && acc) atomicMin(&rnd[bi], (unsigned)lane);
             __syncwarp();
+            // A claim by an earlier lane only removes (MAP/LAST/WINDOW) or may remove (INIT: vMatchedDistance drops) that
+            // one target from this lane's candidate walk.  The walk's outcome is a function of its best and second-best
+            // entries alone, so it is unchanged unless one of those two was claimed this round by an earlier lane.
             bool conflict = false;
-            if (!done)
-                for (int c = 0; c < cnt; c++)
-                    if (rnd[list[c] & 0xffff] < (unsigned)lane) { conflict = true; break; }
+            if (!done) conflict = (bi >= 0 && rnd[bi] < (unsigned)lane) || (bi2 >= 0 && rnd[bi2] < (unsigned)lane);
             const unsigned cm = __ballot_sync(full, !done && conflict);
             const int first = cm ? (__ffs(cm) - 1) : 32;
             __syncwarp();

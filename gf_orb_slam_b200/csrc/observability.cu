@@ -253,17 +253,23 @@ struct WarpRand {
         n = 34;
         __syncwarp();
     }
+    // 30 new states per call.  Along each chain (lane mod 3) the recurrence is a running sum of the r[n-31] terms on top
+    // of the chain's last state, so the 30 values are one stride-3 segmented scan (4 shuffle steps, uint32 wrap-around
+    // addition is associative -> bit-identical to the sequential generator).
     __device__ __forceinline__ void gen30(int lane) {
-        if (lane < 3) {
-            uint32_t prev = rs[(n + lane - 3) & 63];
+        uint32_t a = (lane < 30) ? rs[(n + lane - 31) & 63] : 0u;
 #pragma unroll
-            for (int t = 0; t < 10; t++) {
-                const int id = n + lane + 3 * t;
-                const uint32_t v = rs[(id - 31) & 63] + prev;
-                rs[id & 63] = v;
-                if (id >= 344) raw[(id - 344) & (RAW_RING - 1)] = v >> 1;
-                prev = v;
-            }
+        for (int d = 3; d <= 24; d <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, a, d);
+            if (lane >= d) a += t;
+        }
+        const uint32_t seed0 = rs[(n + (lane % 3) - 3) & 63];
+        __syncwarp();
+        if (lane < 30) {
+            const uint32_t v = a + seed0;
+            const int id = n + lane;
+            rs[id & 63] = v;
+            if (id >= 344) raw[(id - 344) & (RAW_RING - 1)] = v >> 1;
         }
         n += 30;
         __syncwarp();
