@@ -1,0 +1,263 @@
+// K2 detect, second generation: dense FAST-9/16 score + 3x3 non-maximum suppression as a register-rolling stencil
+// (k_fast_nms), followed by an ordered per-cell compaction (k_cell_emit).  Included by extractor.cu.
+//
+// Reference semantics (src/ORBextractor.cc:573-628 + cv::FAST): FAST runs on every cell image with
+// nonmaxSuppression = true; a pixel's score does not depend on the cell, only the NMS neighbourhood does (neighbours
+// outside the cell interior count as 0), and the t = iniThFAST result is the t = minThFAST result filtered to
+// score >= iniThFAST.  The cell interiors tile [16, w-16) x [16, h-16) exactly, so one dense pass over the level with
+// per-column / per-row "cell edge" masks reproduces every per-cell NMS at once.
+//
+// k_fast_nms: one warp per strip of 120 output columns x up to 64 output rows.  Lane l owns the 4 pixels
+// x = X0 - 4 + 4 l .. +3 (two u16x2 pairs A, B); lanes 0 and 31 only provide the horizontal NMS halo.  Each input row is
+// read ONCE per strip (one coalesced 32-bit load per lane, neighbours' words by shuffle), split into even/odd bytes
+// (zero-extended u16x2) and kept in a 7-row register window that rolls down the strip; every FAST ring pair is then a
+// single PRMT, the 16 arcs are reduced with VIMNMX3.U16x2 (80 ops per pixel pair), and the NMS runs on the packed scores
+// of the last three rows.  Output: u8 map of surviving scores (0 elsewhere) in the blur plane (overwritten later by K5).
+#pragma once
+
+namespace gforb {
+
+static const int FN_OUTW = 120;          // output columns per strip (lanes 1..30)
+static const int FN_ROWS = 64;           // output rows per strip
+static const int FN_WARPS = 4;           // warps (strips) per CTA
+
+struct FnWin {                           // 7-row rolling window: even / odd bytes of the 3 words around the lane
+    uint32_t E[7][3], O[7][3];
+};
+
+// u16x2 {byte K, byte K+1} of the 12-byte window (K = 0..10), from the even/odd split words
+template <int K>
+__device__ __forceinline__ uint32_t fn_pair(const uint32_t (&E)[3], const uint32_t (&O)[3]) {
+    constexpr int j = K >> 2, q = K & 3;
+    if (q == 0) return __byte_perm(E[j], O[j], 0x5410);
+    if (q == 1) return __byte_perm(E[j], O[j], 0x3254);
+    if (q == 2) return __byte_perm(E[j], O[j], 0x7632);
+    return __byte_perm(O[j], E[j < 2 ? j + 1 : 2], 0x5432);
+}
+
+// packed corner strength of the pixel pair whose first byte is window column C, centre row = window slot (S0+3)%7:
+// returns max(v - M1, M2 - v) = score + 1 per half (0 when not a corner at any threshold)
+template <int C, int S0>
+__device__ __forceinline__ uint32_t fn_strength(const FnWin& W) {
+#define FN_ROW(d) W.E[(S0 + 3 + (d)) % 7], W.O[(S0 + 3 + (d)) % 7]
+    uint32_t p[16];
+    p[0] = fn_pair<C>(FN_ROW(3));      p[1] = fn_pair<C + 1>(FN_ROW(3));   p[2] = fn_pair<C + 2>(FN_ROW(2));
+    p[3] = fn_pair<C + 3>(FN_ROW(1));  p[4] = fn_pair<C + 3>(FN_ROW(0));   p[5] = fn_pair<C + 3>(FN_ROW(-1));
+    p[6] = fn_pair<C + 2>(FN_ROW(-2)); p[7] = fn_pair<C + 1>(FN_ROW(-3));  p[8] = fn_pair<C>(FN_ROW(-3));
+    p[9] = fn_pair<C - 1>(FN_ROW(-3)); p[10] = fn_pair<C - 2>(FN_ROW(-2)); p[11] = fn_pair<C - 3>(FN_ROW(-1));
+    p[12] = fn_pair<C - 3>(FN_ROW(0)); p[13] = fn_pair<C - 3>(FN_ROW(1));  p[14] = fn_pair<C - 2>(FN_ROW(2));
+    p[15] = fn_pair<C - 1>(FN_ROW(3));
+    const uint32_t v = fn_pair<C>(FN_ROW(0));
+#undef FN_ROW
+    uint32_t mn3[16], mx3[16];
+#pragma unroll
+    for (int i = 0; i < 16; i++) {
+        mn3[i] = __vimin3_u16x2(p[i], p[(i + 1) & 15], p[(i + 2) & 15]);
+        mx3[i] = __vimax3_u16x2(p[i], p[(i + 1) & 15], p[(i + 2) & 15]);
+    }
+    uint32_t mn9[16], mx9[16];
+#pragma unroll
+    for (int i = 0; i < 16; i++) {
+        mn9[i] = __vimin3_u16x2(mn3[i], mn3[(i + 3) & 15], mn3[(i + 6) & 15]);
+        mx9[i] = __vimax3_u16x2(mx3[i], mx3[(i + 3) & 15], mx3[(i + 6) & 15]);
+    }
+    // M2 = max over arcs of the arc minimum, M1 = min over arcs of the arc maximum (3-input trees: 8 ops each)
+    uint32_t a[6], b[6];
+#pragma unroll
+    for (int i = 0; i < 5; i++) {
+        a[i] = __vimax3_u16x2(mn9[3 * i], mn9[3 * i + 1], mn9[3 * i + 2]);
+        b[i] = __vimin3_u16x2(mx9[3 * i], mx9[3 * i + 1], mx9[3 * i + 2]);
+    }
+    a[5] = mn9[15]; b[5] = mx9[15];
+    const uint32_t M2 = __vmaxu2(__vimax3_u16x2(a[0], a[1], a[2]), __vimax3_u16x2(a[3], a[4], a[5]));
+    const uint32_t M1 = __vminu2(__vimin3_u16x2(b[0], b[1], b[2]), __vimin3_u16x2(b[3], b[4], b[5]));
+    // halves hold 0..255, so plain 32-bit subtraction of (max(x, y) - y) never borrows across halves
+    const uint32_t d1 = __vmaxu2(v, M1) - M1, d2 = __vmaxu2(M2, v) - v;
+    return __vmaxu2(d1, d2);
+}
+
+struct FnNms {                            // packed NMS state of pairs A and B for the last rows
+    uint32_t uA, uB;                      // thresholded strength of row c-1
+    uint32_t hmA, hmB;                    // max(left, right) of row c-1
+    uint32_t h3A_p, h3B_p;                // max3(left, self, right) of row c-1
+    uint32_t h3A_pp, h3B_pp;              // ... of row c-2
+};
+
+__global__ void __launch_bounds__(FN_WARPS * 32) k_fast_nms(const uint8_t* __restrict__ pyr, uint8_t* __restrict__ smap,
+                                                            size_t framePyr, const LevelPlan* __restrict__ levels,
+                                                            int nLevels, int tasksPerFrame, int minTh) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int task = blockIdx.x * FN_WARPS + warp;
+    const int b = blockIdx.y;
+    if (task >= tasksPerFrame) return;
+    int l = 0;
+    while (l + 1 < nLevels && task >= levels[l + 1].fnTaskBase) l++;
+    const LevelPlan L = levels[l];
+    task -= L.fnTaskBase;
+    const int sy = task / L.fnStripsX, sx = task - sy * L.fnStripsX;
+    const int X0 = EDGE + FN_OUTW * sx;                     // first output column (ROI coordinates)
+    const int Y0 = EDGE + FN_ROWS * sy, Y1 = min(Y0 + FN_ROWS, L.h - EDGE);
+    const int xl = X0 - 4 + 4 * lane;                      // first of this lane's 4 pixels
+    const uint8_t* roi = pyr + (size_t)b * framePyr + L.off + (size_t)EDGE * L.pitch + EDGE;
+    uint8_t* oroi = smap + (size_t)b * framePyr + L.off + (size_t)EDGE * L.pitch + EDGE;
+    const bool writer = lane >= 1 && lane <= 30 && xl < L.w - EDGE;
+    // per-column cell-edge masks: halves of the left / right neighbour pairs that must read as 0
+    uint32_t mLA, mRA, mLB, mRB;
+    {
+        uint32_t lm = 0, rm = 0;     // bit k: pixel k of this lane sits on a cell's left / right edge (or is outside)
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const int x = xl + k, cx = x - EDGE;
+            const bool inside = x >= EDGE && x < L.w - EDGE;
+            const int r = inside ? cx % L.cellW : 0;
+            if (!inside || r == 0) lm |= 1u << k;
+            if (!inside || r == L.cellW - 1 || x == L.w - EDGE - 1) rm |= 1u << k;
+        }
+        mLA = ((lm & 1) ? 0u : 0xffffu) | ((lm & 2) ? 0u : 0xffff0000u);
+        mLB = ((lm & 4) ? 0u : 0xffffu) | ((lm & 8) ? 0u : 0xffff0000u);
+        mRA = ((rm & 1) ? 0u : 0xffffu) | ((rm & 2) ? 0u : 0xffff0000u);
+        mRB = ((rm & 4) ? 0u : 0xffffu) | ((rm & 8) ? 0u : 0xffff0000u);
+    }
+    const uint32_t T2 = (uint32_t)minTh * 0x00010001u, TM1 = (uint32_t)(minTh - 1) * 0x00010001u;
+    const unsigned full = 0xffffffffu;
+    FnWin W;
+    FnNms S;
+    S.uA = S.uB = S.hmA = S.hmB = S.h3A_p = S.h3B_p = S.h3A_pp = S.h3B_pp = 0u;
+    const int Rend = Y1 + 3;
+    const uint8_t* lp = roi + (ptrdiff_t)(Y0 - 4) * L.pitch + xl;        // this lane's word of input row R
+    uint32_t nw1 = __ldg(reinterpret_cast<const uint32_t*>(lp));
+    uint32_t nh = 0;                                                     // halo word (lane 0: left, lane 31: right)
+    if (lane == 0) nh = __ldg(reinterpret_cast<const uint32_t*>(lp - 4));
+    if (lane == 31) nh = __ldg(reinterpret_cast<const uint32_t*>(lp + 4));
+    int cyN = (Y0 - EDGE) % L.cellH;                                      // (n - 16) mod cellH of the next NMS row n
+
+    auto phase = [&](auto PHc, int R) {
+        constexpr int PH = decltype(PHc)::value;
+        // ---- row R enters slot PH (its words were prefetched); prefetch row R + 1
+        const uint32_t w1 = nw1, hw = nh;
+        lp += L.pitch;
+        if (R < Rend) {
+            nw1 = __ldg(reinterpret_cast<const uint32_t*>(lp));
+            if (lane == 0) nh = __ldg(reinterpret_cast<const uint32_t*>(lp - 4));
+            if (lane == 31) nh = __ldg(reinterpret_cast<const uint32_t*>(lp + 4));
+        }
+        uint32_t w0 = __shfl_up_sync(full, w1, 1), w2 = __shfl_down_sync(full, w1, 1);
+        if (lane == 0) w0 = hw;
+        if (lane == 31) w2 = hw;
+        W.E[PH][0] = w0 & 0x00ff00ffu; W.O[PH][0] = __byte_perm(w0, 0, 0x4341);
+        W.E[PH][1] = w1 & 0x00ff00ffu; W.O[PH][1] = __byte_perm(w1, 0, 0x4341);
+        W.E[PH][2] = w2 & 0x00ff00ffu; W.O[PH][2] = __byte_perm(w2, 0, 0x4341);
+        if (R < Y0 + 2) return;
+        // ---- strength of row c = R - 3: window rows c-3 .. c+3 sit in slots (PH+1) .. (PH+7) mod 7
+        const int c = R - 3;
+        constexpr int S0 = (PH + 1) % 7;
+        uint32_t sA = fn_strength<4, S0>(W), sB = fn_strength<6, S0>(W);
+        const uint32_t uA = __vmaxu2(sA, T2) - T2, uB = __vmaxu2(sB, T2) - T2;   // score - (minTh - 1), 0 below minTh
+        const uint32_t lB = __shfl_up_sync(full, uB, 1), rA = __shfl_down_sync(full, uA, 1);
+        const uint32_t mid = __byte_perm(uA, uB, 0x5432);                          // {A.hi, B.lo}
+        const uint32_t LA = __byte_perm(lB, uA, 0x5432) & mLA, RA = mid & mRA;
+        const uint32_t LB = mid & mLB, RB = __byte_perm(uB, rA, 0x5432) & mRB;
+        const uint32_t h3A = __vimax3_u16x2(LA, uA, RA), h3B = __vimax3_u16x2(LB, uB, RB);
+        const uint32_t hmA = __vmaxu2(LA, RA), hmB = __vmaxu2(LB, RB);
+        if (c >= Y0 + 1) {
+            // ---- NMS of row n = c - 1 (strict >, neighbours outside the cell read as 0)
+            const int n = c - 1;
+            const bool top = cyN == 0, bot = (cyN == L.cellH - 1) || (n == L.h - EDGE - 1);
+            const uint32_t upA = top ? 0u : S.h3A_pp, upB = top ? 0u : S.h3B_pp;
+            const uint32_t dnA = bot ? 0u : h3A, dnB = bot ? 0u : h3B;
+            const uint32_t NA = __vimax3_u16x2(upA, dnA, S.hmA), NB = __vimax3_u16x2(upB, dnB, S.hmB);
+            const uint32_t kA = __vmaxu2(S.uA, NA) - NA, kB = __vmaxu2(S.uB, NB) - NB;   // > 0 per half iff kept
+            const uint32_t fA = (((kA + 0x7fff7fffu) >> 15) & 0x00010001u) * 0xffffu;
+            const uint32_t fB = (((kB + 0x7fff7fffu) >> 15) & 0x00010001u) * 0xffffu;
+            const uint32_t oA = (S.uA + TM1) & fA, oB = (S.uB + TM1) & fB;
+            if (writer) *reinterpret_cast<uint32_t*>(oroi + (ptrdiff_t)n * L.pitch + xl) = __byte_perm(oA, oB, 0x6420);
+            cyN = (cyN + 1 == L.cellH) ? 0 : cyN + 1;
+        }
+        S.h3A_pp = S.h3A_p; S.h3B_pp = S.h3B_p; S.h3A_p = h3A; S.h3B_p = h3B;
+        S.uA = uA; S.uB = uB; S.hmA = hmA; S.hmB = hmB;
+    };
+    for (int R = Y0 - 4; R <= Rend; R += 7) {
+        phase(std::integral_constant<int, 0>(), R);
+        if (R + 1 <= Rend) phase(std::integral_constant<int, 1>(), R + 1);
+        if (R + 2 <= Rend) phase(std::integral_constant<int, 2>(), R + 2);
+        if (R + 3 <= Rend) phase(std::integral_constant<int, 3>(), R + 3);
+        if (R + 4 <= Rend) phase(std::integral_constant<int, 4>(), R + 4);
+        if (R + 5 <= Rend) phase(std::integral_constant<int, 5>(), R + 5);
+        if (R + 6 <= Rend) phase(std::integral_constant<int, 6>(), R + 6);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ K2b cell emit
+// One warp per (cell, frame): walks the cell interior of the NMS map row-major in 16-byte chunks and appends the
+// survivors to the cell's candidate list in the reference's FAST emission order (row-major), packed
+// (score << 24 | y << 12 | x) in level-ROI coordinates; counts at minThFAST (all survivors) and at iniThFAST.
+static const int EM_WARPS = 4;
+__global__ void __launch_bounds__(EM_WARPS * 32) k_cell_emit(const uint8_t* __restrict__ smap, size_t framePyr,
+                                                             const LevelPlan* __restrict__ levels,
+                                                             const CellPlan* __restrict__ cells, int nCellsTotal,
+                                                             uint32_t* __restrict__ cand, size_t frameCand,
+                                                             int* __restrict__ cnt7, int* __restrict__ cnt20, int iniTh,
+                                                             int* __restrict__ errflag) {
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int cellId = blockIdx.x * EM_WARPS + warp, b = blockIdx.y;
+    if (cellId >= nCellsTotal) return;
+    const CellPlan C = cells[cellId];
+    const size_t ci = (size_t)b * nCellsTotal + cellId;
+    const int Wc = C.x1 - C.x0, Hc = C.y1 - C.y0;
+    if (C.skipped || Wc <= 0 || Hc <= 0) {
+        if (lane == 0) { cnt7[ci] = 0; cnt20[ci] = 0; }
+        return;
+    }
+    const LevelPlan L = levels[C.level];
+    const uint8_t* roi = smap + (size_t)b * framePyr + L.off + (size_t)EDGE * L.pitch + EDGE;
+    uint32_t* out = cand + (size_t)b * frameCand + C.candBase;
+    const int xa = C.x0 & ~15;                                  // plane column 16 + xa is 16-byte aligned
+    const int nChunk = (C.x1 - xa + 15) >> 4;
+    const int items = nChunk * Hc;
+    int total = 0, n20 = 0;
+    for (int it0 = 0; it0 < items; it0 += 32) {
+        const int id = it0 + lane;
+        uint4 v = make_uint4(0, 0, 0, 0);
+        int y = 0, xc = 0;
+        if (id < items) {
+            const int r = id / nChunk, ch = id - r * nChunk;
+            y = C.y0 + r; xc = xa + (ch << 4);
+            v = __ldg(reinterpret_cast<const uint4*>(roi + (ptrdiff_t)y * L.pitch + xc));
+        }
+        uint32_t w[4] = {v.x, v.y, v.z, v.w};
+        uint32_t nzmask = 0;                                    // bit k: byte k is a survivor inside [x0, x1)
+        if (v.x | v.y | v.z | v.w) {
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                // high bit of every non-zero byte
+                uint32_t nzb = (((w[q] & 0x7f7f7f7fu) + 0x7f7f7f7fu) | w[q]) & 0x80808080u;
+                // gather bits 7, 15, 23, 31 into a nibble
+                nzmask |= (((nzb >> 7) * 0x00204081u >> 21) & 0xfu) << (4 * q);
+            }
+            const int lo = C.x0 - xc, hi = C.x1 - xc;           // valid byte range [lo, hi)
+            if (lo > 0) nzmask &= ~((1u << lo) - 1u);
+            if (hi < 16) nzmask &= (1u << hi) - 1u;
+        }
+        const int n = __popc(nzmask);
+        if (!__any_sync(full, n > 0)) continue;
+        int inc = n;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const int t = __shfl_up_sync(full, inc, d); if (lane >= d) inc += t; }
+        int pos = total + inc - n;
+        total += __shfl_sync(full, inc, 31);
+        while (nzmask) {
+            const int k = __ffs(nzmask) - 1;
+            nzmask &= nzmask - 1;
+            const uint32_t sc = (w[k >> 2] >> (8 * (k & 3))) & 0xffu;
+            if ((int)sc >= iniTh) n20++;
+            if (pos < C.candCap) out[pos] = (sc << 24) | ((uint32_t)y << 12) | (uint32_t)(xc + k);
+            else atomicExch(errflag, GFORB_ERR_OVERFLOW);
+            pos++;
+        }
+    }
+    n20 = __reduce_add_sync(full, n20);
+    if (lane == 0) { cnt7[ci] = total; cnt20[ci] = n20; }
+}
+
+}  // namespace gforb

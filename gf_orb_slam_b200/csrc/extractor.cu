@@ -15,7 +15,9 @@
 // keypoint buffers.  All integer work is bit-exact by construction; float steps use un-fused IEEE ops.
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
+#include <type_traits>
 #include <vector>
 #include "common.cuh"
 
@@ -30,6 +32,7 @@ struct LevelPlan {
     int xtab, ytab;               // offsets (in int2 units) of the resize tables for l-1 -> l
     int scaledPatchSize;
     float scale;
+    int fnStripsX, fnStripsY, fnTaskBase;   // k_fast_nms strips (detect.cuh)
 };
 struct CellPlan {
     int level, x0, y0, x1, y1;    // interior rectangle in level ROI coordinates [x0,x1) x [y0,y1) (may be empty)
@@ -37,6 +40,10 @@ struct CellPlan {
     int candBase, candCap;
 };
 struct BlurTile { int level, x0, y0; };
+
+}  // namespace gforb
+#include "detect.cuh"
+namespace gforb {
 
 // bit_pattern_31_ (src/ORBextractor.cc:204-462) as 256 x {x0, y0, x1, y1}; lane j of k_describe reads its 32 bytes with
 // two 128-bit loads (a per-lane index into __constant__ memory would serialise on the ADU pipe: ncu r1_v1, adu=97%)
@@ -578,7 +585,9 @@ struct GforbExtractor {
     std::vector<CellPlan> cells;
     std::vector<BlurTile> tiles;
     size_t framePyr = 0, frameCand = 0, frameKp = 0;
-    int kpCapTotal = 0, nCellsTotal = 0, detSmem = 0, detPixPitch = 0;
+    int kpCapTotal = 0, nCellsTotal = 0, detSmem = 0, detPixPitch = 0, fnTasks = 0;
+    bool tiled = true;
+    int detectVersion = 2;              // GFORB_DETECT=1 selects the first-generation per-cell kernel (A/B tool)
     // device buffers
     uint8_t *d_img = nullptr, *d_pyr = nullptr, *d_blr = nullptr, *d_desc = nullptr;
     GforbKeyPoint* d_kps = nullptr;
@@ -653,7 +662,8 @@ static int build_plan(GforbExtractor* E, int w, int h) {
     E->tiles.clear();
     std::vector<int2> tabs;
     size_t off = 0;
-    int kpBase = 0, candBase = 0, maxCellW = 0;
+    int kpBase = 0, candBase = 0, maxCellW = 0, fnTasks = 0;
+    bool tiled = true;      // cell interiors tile [16, w-16) x [16, h-16) (k_fast_nms precondition)
     const float imageRatio = (float)w / h;
     for (int l = 0; l < nl; l++) {
         LevelPlan& L = E->levels[l];
@@ -678,6 +688,11 @@ static int build_plan(GforbExtractor* E, int w, int h) {
         L.nCells = L.levelRows * L.levelCols;
         L.nfeaturesCell = (int)ceilf((float)L.nDesired / L.nCells);
         L.cellBase = (int)E->cells.size();
+        L.fnStripsX = (W + FN_OUTW - 1) / FN_OUTW;
+        L.fnStripsY = (H + FN_ROWS - 1) / FN_ROWS;
+        L.fnTaskBase = fnTasks;
+        fnTasks += L.fnStripsX * L.fnStripsY;
+        if ((long long)L.cellW * (L.levelCols - 1) >= W || (long long)L.cellH * (L.levelRows - 1) >= H) tiled = false;
         L.kpBase = kpBase;
         L.kpCap = 2 * L.nDesired + L.nCells + 64;
         kpBase += L.kpCap;
@@ -721,6 +736,8 @@ static int build_plan(GforbExtractor* E, int w, int h) {
     E->frameKp = (size_t)kpBase;
     E->kpCapTotal = kpBase;
     E->nCellsTotal = (int)E->cells.size();
+    E->fnTasks = fnTasks;
+    E->tiled = tiled;
     E->detPixPitch = (maxCellW + 16 + 3) & ~3;
     E->detSmem = (DET_BAND + 8) * E->detPixPitch + (DET_BAND + 2) * E->detPixPitch + DET_BAND * ((maxCellW + 31) / 32) * 4 + 16;
     if (E->detSmem > 200 * 1024) return GFORB_ERR_CAPACITY;
@@ -783,6 +800,7 @@ int gforb_extractor_create(const GforbExtractorConfig* cfg, GforbExtractor** out
     GF_CUDA_OK(cudaStreamCreateWithFlags(&E->ownStream, cudaStreamNonBlocking));
     cudaDeviceGetAttribute(&E->numSMs, cudaDevAttrMultiProcessorCount, cfg->device);
     build_ctor_tables(E);
+    if (const char* dv = getenv("GFORB_DETECT")) E->detectVersion = atoi(dv);
     GF_CUDA_OK(cudaMemcpyToSymbol(g_pattern, h_pattern, sizeof(h_pattern)));
     {   // umax (src/ORBextractor.cc:500-517)
         int umax[16];
@@ -921,9 +939,17 @@ int gforb_extract(GforbExtractor* E, const uint8_t* images, int w, int h, int st
     }
     end();
     begin("detect");
-    k_detect<<<dim3(E->nCellsTotal, batch), DET_THREADS, E->detSmem, st>>>(
-        E->d_pyr, E->framePyr, E->d_levels, E->d_cells, E->nCellsTotal, E->d_cand, E->frameCand, E->d_cnt7, E->d_cnt20,
-        c.iniThFAST, c.minThFAST, E->detPixPitch, E->d_err); launches++;
+    if (E->detectVersion == 2 && E->tiled) {
+        k_fast_nms<<<dim3((E->fnTasks + FN_WARPS - 1) / FN_WARPS, batch), FN_WARPS * 32, 0, st>>>(
+            E->d_pyr, E->d_blr, E->framePyr, E->d_levels, nl, E->fnTasks, c.minThFAST); launches++;
+        k_cell_emit<<<dim3((E->nCellsTotal + EM_WARPS - 1) / EM_WARPS, batch), EM_WARPS * 32, 0, st>>>(
+            E->d_blr, E->framePyr, E->d_levels, E->d_cells, E->nCellsTotal, E->d_cand, E->frameCand, E->d_cnt7, E->d_cnt20,
+            c.iniThFAST, E->d_err); launches++;
+    } else {
+        k_detect<<<dim3(E->nCellsTotal, batch), DET_THREADS, E->detSmem, st>>>(
+            E->d_pyr, E->framePyr, E->d_levels, E->d_cells, E->nCellsTotal, E->d_cand, E->frameCand, E->d_cnt7, E->d_cnt20,
+            c.iniThFAST, c.minThFAST, E->detPixPitch, E->d_err); launches++;
+    }
     end();
     begin("select");
     k_quota<<<(batch * nl + 127) / 128, 128, 0, st>>>(E->d_levels, E->d_cells, nl, E->nCellsTotal, E->d_cnt7, E->d_cnt20,
