@@ -1,0 +1,117 @@
+// K5 blur, second generation: GaussianBlur(level, 7x7, sigma 2, BORDER_REFLECT_101) with OpenCV's 8U fixed-point rounding
+// (src/ORBextractor.cc:842) as a register-rolling separable stencil.  Included by extractor.cu.
+//
+// One warp per strip of 128 columns x up to BL2_ROWS rows; lane l owns pixels x = X0 + 4 l .. +3.  Each input row is
+// read once (coalesced 32-bit word per lane + neighbours' words by shuffle) and split into even / odd bytes, i.e. into
+// the stride-2 pixel pairs {b0, b2} and {b1, b3}.  The horizontal pass runs on those packed u16x2 pairs (taps sum to
+// 256 or 257, so 255 * sum fits 16 bits and a plain 32-bit IMAD never carries across halves); its result
+// {h(x), h(x+2)}, {h(x+1), h(x+3)} enters a 7-row register window and the vertical pass emits one output row per input
+// row: out = (sum_q g[q] * h[y-3+q] + 2^15) >> 16, saturated.  The ring of the source plane supplies the reflect-101
+// border (it holds the unblurred reflection; verified identical to an isolated reflect-101 blur).
+#pragma once
+
+namespace gforb {
+
+static const int BL2_ROWS = 64;
+static const int BL2_WARPS = 4;
+
+// stride-2 pair {byte J, byte J+2} of the 12-byte window (J = 0..9) from the even/odd split words
+template <int J>
+__device__ __forceinline__ uint32_t bl_pair2(const uint32_t (&E)[3], const uint32_t (&O)[3]) {
+    constexpr int j = J >> 2, q = J & 3;
+    if (q == 0) return E[j];
+    if (q == 1) return O[j];
+    if (q == 2) return __byte_perm(E[j], E[j < 2 ? j + 1 : 2], 0x5432);
+    return __byte_perm(O[j], O[j < 2 ? j + 1 : 2], 0x5432);
+}
+
+// horizontal 7-tap of the pair {pixel P, pixel P+2} (window bytes P+4-3 .. ), symmetric taps g0..g3
+template <int P>
+__device__ __forceinline__ uint32_t bl_hpass(const uint32_t (&E)[3], const uint32_t (&O)[3], uint32_t g0, uint32_t g1,
+                                             uint32_t g2, uint32_t g3) {
+    constexpr int C = 4 + P;     // window byte of pixel P
+    const uint32_t s0 = bl_pair2<C - 3>(E, O) + bl_pair2<C + 3>(E, O);
+    const uint32_t s1 = bl_pair2<C - 2>(E, O) + bl_pair2<C + 2>(E, O);
+    const uint32_t s2 = bl_pair2<C - 1>(E, O) + bl_pair2<C + 1>(E, O);
+    return g0 * s0 + g1 * s1 + g2 * s2 + g3 * bl_pair2<C>(E, O);
+}
+
+__global__ void __launch_bounds__(BL2_WARPS * 32) k_blur2(const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blr,
+                                                          size_t framePyr, const LevelPlan* __restrict__ levels, int nLevels,
+                                                          int tasksPerFrame, int variant) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int task = blockIdx.x * BL2_WARPS + warp;
+    const int b = blockIdx.y;
+    if (task >= tasksPerFrame) return;
+    int l = 0;
+    while (l + 1 < nLevels && task >= levels[l + 1].blTaskBase) l++;
+    const LevelPlan L = levels[l];
+    task -= L.blTaskBase;
+    const int sy = task / L.blStripsX, sx = task - sy * L.blStripsX;
+    const int Y0 = BL2_ROWS * sy, Y1 = min(Y0 + BL2_ROWS, L.h);
+    const int xl = 128 * sx + 4 * lane;
+    const uint8_t* roi = pyr + (size_t)b * framePyr + L.off + (size_t)EDGE * L.pitch + EDGE;
+    uint8_t* oroi = blr + (size_t)b * framePyr + L.off + (size_t)EDGE * L.pitch + EDGE;
+    const uint32_t g0 = 18, g1 = 34, g2 = variant ? 49 : 48, g3 = variant ? 55 : 56;
+    const unsigned full = 0xffffffffu;
+    const int hoff = lane < 16 ? -4 : 4;
+    const uint8_t* lp = roi + (ptrdiff_t)(Y0 - 3) * L.pitch + xl;
+    uint32_t nw1 = __ldg(reinterpret_cast<const uint32_t*>(lp));
+    uint32_t nh = __ldg(reinterpret_cast<const uint32_t*>(lp + hoff));
+    uint32_t HA[7], HB[7];       // horizontal results {h(x), h(x+2)} / {h(x+1), h(x+3)} of the last 7 input rows
+    const int Rend = Y1 + 2;
+
+    auto phase = [&](auto PHc, int R) {
+        constexpr int PH = decltype(PHc)::value;
+        const uint32_t w1 = nw1, hw = nh;
+        lp += L.pitch;
+        nw1 = __ldg(reinterpret_cast<const uint32_t*>(lp));      // row Rend + 1 <= h + 3 is inside the bordered plane
+        nh = __ldg(reinterpret_cast<const uint32_t*>(lp + hoff));
+        uint32_t w0 = __shfl_up_sync(full, w1, 1), w2 = __shfl_down_sync(full, w1, 1);
+        if (lane == 0) w0 = hw;
+        if (lane == 31) w2 = hw;
+        uint32_t E[3], O[3];
+        E[0] = w0 & 0x00ff00ffu; O[0] = __byte_perm(w0, 0, 0x4341);
+        E[1] = w1 & 0x00ff00ffu; O[1] = __byte_perm(w1, 0, 0x4341);
+        E[2] = w2 & 0x00ff00ffu; O[2] = __byte_perm(w2, 0, 0x4341);
+        HA[PH] = bl_hpass<0>(E, O, g0, g1, g2, g3);
+        HB[PH] = bl_hpass<1>(E, O, g0, g1, g2, g3);
+        if (R < Y0 + 3) return;
+        // ---- output row y = R - 3: input rows y-3 .. y+3 sit in slots (PH+1) .. (PH+7) mod 7
+        const int y = R - 3;
+#define BL_S(k) ((PH + 1 + (k)) % 7)
+        uint32_t o[4];
+#pragma unroll
+        for (int half = 0; half < 2; half++) {
+            // pixel x + 2*half (from HA) and x + 1 + 2*half (from HB)
+            const int sh = 16 * half;
+            const uint32_t a0 = ((HA[BL_S(0)] >> sh) & 0xffffu) + ((HA[BL_S(6)] >> sh) & 0xffffu);
+            const uint32_t a1 = ((HA[BL_S(1)] >> sh) & 0xffffu) + ((HA[BL_S(5)] >> sh) & 0xffffu);
+            const uint32_t a2 = ((HA[BL_S(2)] >> sh) & 0xffffu) + ((HA[BL_S(4)] >> sh) & 0xffffu);
+            const uint32_t a3 = (HA[BL_S(3)] >> sh) & 0xffffu;
+            const uint32_t b0 = ((HB[BL_S(0)] >> sh) & 0xffffu) + ((HB[BL_S(6)] >> sh) & 0xffffu);
+            const uint32_t b1 = ((HB[BL_S(1)] >> sh) & 0xffffu) + ((HB[BL_S(5)] >> sh) & 0xffffu);
+            const uint32_t b2 = ((HB[BL_S(2)] >> sh) & 0xffffu) + ((HB[BL_S(4)] >> sh) & 0xffffu);
+            const uint32_t b3 = (HB[BL_S(3)] >> sh) & 0xffffu;
+            o[2 * half] = min((g0 * a0 + g1 * a1 + g2 * a2 + g3 * a3 + 32768u) >> 16, 255u);
+            o[2 * half + 1] = min((g0 * b0 + g1 * b1 + g2 * b2 + g3 * b3 + 32768u) >> 16, 255u);
+        }
+#undef BL_S
+        const uint32_t word = o[0] | (o[1] << 8) | (o[2] << 16) | (o[3] << 24);
+        uint8_t* op = oroi + (ptrdiff_t)y * L.pitch + xl;
+        if (xl + 3 < L.w) *reinterpret_cast<uint32_t*>(op) = word;
+        else
+            for (int k = 0; k < 4 && xl + k < L.w; k++) op[k] = (uint8_t)(word >> (8 * k));
+    };
+    for (int R = Y0 - 3; R <= Rend; R += 7) {
+        phase(std::integral_constant<int, 0>(), R);
+        if (R + 1 <= Rend) phase(std::integral_constant<int, 1>(), R + 1);
+        if (R + 2 <= Rend) phase(std::integral_constant<int, 2>(), R + 2);
+        if (R + 3 <= Rend) phase(std::integral_constant<int, 3>(), R + 3);
+        if (R + 4 <= Rend) phase(std::integral_constant<int, 4>(), R + 4);
+        if (R + 5 <= Rend) phase(std::integral_constant<int, 5>(), R + 5);
+        if (R + 6 <= Rend) phase(std::integral_constant<int, 6>(), R + 6);
+    }
+}
+
+}  // namespace gforb

@@ -126,9 +126,11 @@ __global__ void __launch_bounds__(FN_WARPS * 32) k_fast_nms(const uint8_t* __res
     const int Rend = Y1 + 3;
     const uint8_t* lp = roi + (ptrdiff_t)(Y0 - 4) * L.pitch + xl;        // this lane's word of input row R
     uint32_t nw1 = __ldg(reinterpret_cast<const uint32_t*>(lp));
-    uint32_t nh = 0;                                                     // halo word (lane 0: left, lane 31: right)
-    if (lane == 0) nh = __ldg(reinterpret_cast<const uint32_t*>(lp - 4));
-    if (lane == 31) nh = __ldg(reinterpret_cast<const uint32_t*>(lp + 4));
+    // halo word (lane 0: left of its word, lane 31: right), prefetched with the lane's own word
+    // (unconditional on every lane: a predicated load would make the compiler copy the register right after the load
+    // and expose the full memory latency; the inner lanes' halo word is an L1 hit on a neighbour's word)
+    const int hoff = lane < 16 ? -4 : 4;
+    uint32_t nh = __ldg(reinterpret_cast<const uint32_t*>(lp + hoff));
     int cyN = (Y0 - EDGE) % L.cellH;                                      // (n - 16) mod cellH of the next NMS row n
 
     auto phase = [&](auto PHc, int R) {
@@ -136,11 +138,9 @@ __global__ void __launch_bounds__(FN_WARPS * 32) k_fast_nms(const uint8_t* __res
         // ---- row R enters slot PH (its words were prefetched); prefetch row R + 1
         const uint32_t w1 = nw1, hw = nh;
         lp += L.pitch;
-        if (R < Rend) {
-            nw1 = __ldg(reinterpret_cast<const uint32_t*>(lp));
-            if (lane == 0) nh = __ldg(reinterpret_cast<const uint32_t*>(lp - 4));
-            if (lane == 31) nh = __ldg(reinterpret_cast<const uint32_t*>(lp + 4));
-        }
+        // (row Rend + 1 <= h - 12 is still inside the bordered plane, so the last prefetch needs no guard)
+        nw1 = __ldg(reinterpret_cast<const uint32_t*>(lp));
+        nh = __ldg(reinterpret_cast<const uint32_t*>(lp + hoff));
         uint32_t w0 = __shfl_up_sync(full, w1, 1), w2 = __shfl_down_sync(full, w1, 1);
         if (lane == 0) w0 = hw;
         if (lane == 31) w2 = hw;

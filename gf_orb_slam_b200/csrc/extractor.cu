@@ -2,13 +2,14 @@
 // (reference src/ORBextractor.cc:769-875).  Stages (each a kernel over the whole batch):
 //   K1a border0      level-0 copy + reflect-101 ring                      (ComputePyramid :990)
 //   K1b resize       level l-1 -> l, 11-bit fixed-point bilinear + ring    (ComputePyramid :943,:982)
-//   K2  detect       one CTA per (cell, frame): FAST-9/16 score, cell-confined NMS, ordered candidate list,
-//                    counts at iniThFAST and minThFAST                     (ComputeKeyPoints :573-628)
+//   K2a fast_nms     dense FAST-9/16 score + cell-confined 3x3 NMS, register-rolling strips (detect.cuh)
+//   K2b cell_emit    per cell: ordered candidate list, counts at iniThFAST and minThFAST (ComputeKeyPoints :573-628)
+//                    (k_detect = first-generation fused per-cell kernel, kept for cell grids that do not tile the level)
 //   K3b quota        per (frame, level): threshold fallback + quota redistribution (:673-721)
 //   K3c cell_retain  per cell: retainBest emulation                        (:733-745)
 //   K3d level_retain per (frame, level): retainBest(nDesired)              (:748-752)
 //   K4  orient       warp per keypoint: IC_Angle + KeyPoint emission       (:131-158, :738-745, :865-871)
-//   K5  blur         7x7 Gaussian of every level ROI                       (:842)
+//   K5  blur2        7x7 Gaussian of every level ROI, register-rolling strips (blur.cuh)   (:842)
 //   K6  describe     warp per keypoint: steered BRIEF                      (:161-201)
 // Data layout in HBM: per frame one "pyramid block" holding all bordered level planes (pitch multiple of 128 B,
 // ROI at (16,16)), a second block with the blurred ROIs, a candidate buffer (packed u32 score|y|x), per-level
@@ -33,16 +34,17 @@ struct LevelPlan {
     int scaledPatchSize;
     float scale;
     int fnStripsX, fnStripsY, fnTaskBase;   // k_fast_nms strips (detect.cuh)
+    int blStripsX, blTaskBase;              // k_blur2 strips (blur.cuh)
 };
 struct CellPlan {
     int level, x0, y0, x1, y1;    // interior rectangle in level ROI coordinates [x0,x1) x [y0,y1) (may be empty)
     int skipped;                  // 1: the reference `continue`s before FAST (hX<=0 / hY<=0)
     int candBase, candCap;
 };
-struct BlurTile { int level, x0, y0; };
 
 }  // namespace gforb
 #include "detect.cuh"
+#include "blur.cuh"
 namespace gforb {
 
 // bit_pattern_31_ (src/ORBextractor.cc:204-462) as 256 x {x0, y0, x1, y1}; lane j of k_describe reads its 32 bytes with
@@ -62,18 +64,15 @@ __device__ __forceinline__ int reflect101(int p, int len) {
 }
 
 // ------------------------------------------------------------------------------------------------ K1a
+// level 0 = copyMakeBorder(image, 16, BORDER_REFLECT_101) (ComputePyramid :990-991).  Thread = one 16-byte chunk of a
+// bordered row; grid (row blocks, frames).
 __global__ void __launch_bounds__(256) k_border0(const uint8_t* __restrict__ img, int w, int h, int stride,
                                                  size_t frameStride, uint8_t* __restrict__ pyr, size_t framePyr,
-                                                 LevelPlan L, int batch) {
-    const int chunksPerRow = L.pitch >> 4;
-    const long long total = (long long)batch * L.rows * chunksPerRow;
-    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-        int xc = (int)(i % chunksPerRow);
-        long long t = i / chunksPerRow;
-        int Y = (int)(t % L.rows);
-        int b = (int)(t / L.rows);
-        const uint8_t* srow = img + (size_t)b * frameStride + (size_t)reflect101(Y - EDGE, h) * stride;
-        int X0 = xc << 4;
+                                                 LevelPlan L) {
+    const int Y = blockIdx.x * blockDim.y + threadIdx.y, b = blockIdx.y;
+    if (Y >= L.rows) return;
+    const uint8_t* srow = img + (size_t)b * frameStride + (size_t)reflect101(Y - EDGE, h) * stride;
+    for (int X0 = threadIdx.x << 4; X0 < L.pitch; X0 += blockDim.x << 4) {
         uint4 out;
         const uint8_t* sp = srow + (X0 - EDGE);
         if (X0 >= EDGE && X0 + 15 < EDGE + w && ((reinterpret_cast<uintptr_t>(sp) & 15) == 0)) {
@@ -85,8 +84,8 @@ __global__ void __launch_bounds__(256) k_border0(const uint8_t* __restrict__ img
                 uint32_t v = 0;
 #pragma unroll
                 for (int k = 0; k < 4; k++) {
-                    int X = X0 + q * 4 + k;
-                    uint32_t px = (X < w + 2 * EDGE) ? srow[reflect101(X - EDGE, w)] : 0u;
+                    const int X = X0 + q * 4 + k;
+                    const uint32_t px = (X < w + 2 * EDGE) ? srow[reflect101(X - EDGE, w)] : 0u;
                     v |= px << (8 * k);
                 }
                 wv[q] = v;
@@ -98,41 +97,55 @@ __global__ void __launch_bounds__(256) k_border0(const uint8_t* __restrict__ img
 }
 
 // ------------------------------------------------------------------------------------------------ K1b
-// tabs: int2 {src index, a0 | a1 << 16}; cv::resize INTER_LINEAR 8U fixed point
+// level l = resize(level l-1, INTER_LINEAR) + reflect-101 ring (ComputePyramid :943, :982-983); cv::resize 8U fixed
+// point with 11-bit coefficients: out = ((b0 * (h0 >> 4) >> 16) + (b1 * (h1 >> 4) >> 16) + 2) >> 2,
+// h = s[sx] * a0 + s[sx + 1] * a1.  tabs: int2 {src index, a0 | a1 << 16} per destination column / row.
+// Thread = 4 adjacent bordered columns x a band of RS_BAND bordered rows: the column taps live in registers and every
+// horizontally interpolated source row is computed once and reused by the next output row (scale 1.2 -> ~1.3 source
+// rows per output row instead of 2).
+static const int RS_BAND = 8;
 __global__ void __launch_bounds__(256) k_resize(uint8_t* __restrict__ pyr, size_t framePyr, LevelPlan S, LevelPlan D,
-                                                const int2* __restrict__ tabs, int batch) {
+                                                const int2* __restrict__ tabs, int quadsPerRow, int nBands) {
+    const int t = blockIdx.x * 256 + threadIdx.x, b = blockIdx.y;
+    if (t >= quadsPerRow * nBands) return;
+    const int band = t / quadsPerRow, q = t - band * quadsPerRow;
     const int2* __restrict__ xt = tabs + D.xtab;
     const int2* __restrict__ yt = tabs + D.ytab;
-    const int quadsPerRow = D.pitch >> 2;
-    const long long total = (long long)batch * D.rows * quadsPerRow;
-    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-        int xq = (int)(i % quadsPerRow);
-        long long t = i / quadsPerRow;
-        int Y = (int)(t % D.rows);
-        int b = (int)(t / D.rows);
-        const uint8_t* sroi = pyr + (size_t)b * framePyr + S.off + (size_t)EDGE * S.pitch + EDGE;
-        int y = reflect101(Y - EDGE, D.h);
-        int2 ty = __ldg(&yt[y]);
-        int b0 = (short)(ty.y & 0xffff), b1 = (short)(ty.y >> 16);
-        const uint8_t* r0 = sroi + (size_t)ty.x * S.pitch;
-        const uint8_t* r1 = r0 + S.pitch;     // row sy+1 (the ring makes it addressable; b1 == 0 when clamped)
+    int sx[4], a0[4], a1[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int X = (q << 2) + k;
+        const int x = reflect101(min(X, D.w + 2 * EDGE - 1) - EDGE, D.w);   // columns past w+32 are pitch padding
+        const int2 tx = __ldg(&xt[x]);
+        sx[k] = tx.x; a0[k] = (short)(tx.y & 0xffff); a1[k] = (short)(tx.y >> 16);
+    }
+    const uint8_t* sroi = pyr + (size_t)b * framePyr + S.off + (size_t)EDGE * S.pitch + EDGE;
+    uint8_t* dst = pyr + (size_t)b * framePyr + D.off + (q << 2);
+    int H0[4], H1[4], c0 = -0x40000000, c1 = -0x40000000;       // source rows held in H0 / H1
+    auto hrow = [&](int sy, int (&H)[4]) {
+        const uint8_t* r = sroi + (ptrdiff_t)sy * S.pitch;      // row sy+1 == S.h is the ring (b1 == 0 there)
+#pragma unroll
+        for (int k = 0; k < 4; k++) H[k] = (r[sx[k]] * a0[k] + r[sx[k] + 1] * a1[k]) >> 4;
+    };
+    const int Yend = min((band + 1) * RS_BAND, D.rows);
+    for (int Y = band * RS_BAND; Y < Yend; Y++) {
+        const int y = reflect101(Y - EDGE, D.h);
+        const int2 ty = __ldg(&yt[y]);
+        const int b0 = (short)(ty.y & 0xffff), b1 = (short)(ty.y >> 16);
+        const int r0 = ty.x, r1 = ty.x + 1;
+        if (r0 == c1) {
+#pragma unroll
+            for (int k = 0; k < 4; k++) H0[k] = H1[k];
+            c0 = c1; c1 = -0x40000000;
+        } else if (r0 != c0) { hrow(r0, H0); c0 = r0; }
+        if (r1 != c1) { hrow(r1, H1); c1 = r1; }
         uint32_t outv = 0;
 #pragma unroll
         for (int k = 0; k < 4; k++) {
-            int X = (xq << 2) + k;
-            uint32_t px = 0;
-            if (X < D.w + 2 * EDGE) {
-                int x = reflect101(X - EDGE, D.w);
-                int2 tx = __ldg(&xt[x]);
-                int a0 = (short)(tx.y & 0xffff), a1 = (short)(tx.y >> 16);
-                int h0 = r0[tx.x] * a0 + r0[tx.x + 1] * a1;
-                int h1 = r1[tx.x] * a0 + r1[tx.x + 1] * a1;
-                int v = (((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2;
-                px = (uint32_t)min(max(v, 0), 255);
-            }
-            outv |= px << (8 * k);
+            const int v = (((b0 * H0[k]) >> 16) + ((b1 * H1[k]) >> 16) + 2) >> 2;
+            outv |= (uint32_t)min(max(v, 0), 255) << (8 * k);
         }
-        *reinterpret_cast<uint32_t*>(pyr + (size_t)b * framePyr + D.off + (size_t)Y * D.pitch + (xq << 2)) = outv;
+        *reinterpret_cast<uint32_t*>(dst + (size_t)Y * D.pitch) = outv;
     }
 }
 
@@ -407,7 +420,7 @@ __global__ void __launch_bounds__(128) k_level_retain(const LevelPlan* __restric
 
 // ------------------------------------------------------------------------------------------------ K4 orient
 // IC_Angle on the unblurred level (src/ORBextractor.cc:131-158) + KeyPoint emission (:738-745, :865-871).
-// One warp per keypoint slot; lane v handles rows +-v of the circular patch.
+// One warp per keypoint slot; lane = patch column.
 __global__ void __launch_bounds__(256) k_orient(const uint8_t* __restrict__ pyr, size_t framePyr,
                                                 const LevelPlan* __restrict__ levels, int nLevels,
                                                 const uint32_t* __restrict__ lvlKp, size_t frameKp, int kpCapTotal,
@@ -429,23 +442,22 @@ __global__ void __launch_bounds__(256) k_orient(const uint8_t* __restrict__ pyr,
     const uint32_t e = lvlKp[(size_t)b * frameKp + slot];
     const int x = e & 0xfff, y = (e >> 12) & 0xfff, score = e >> 24;
     const uint8_t* center = pyr + (size_t)b * framePyr + L.off + (size_t)(EDGE + y) * L.pitch + EDGE + x;
+    // lane = patch column u = lane - 15 (lane 31 idle): every row of the circular patch is one contiguous <= 31-byte
+    // segment read by the whole warp; m10 = sum u * I, m01 = sum v * I (exact int32)
     int m10 = 0, m01 = 0;
-    if (lane <= HALF_PATCH) {
-        const int v = lane;
-        if (v == 0) {
-            for (int u = -HALF_PATCH; u <= HALF_PATCH; ++u) m10 += u * center[u];
-        } else {
-            const int d = c_umax[v];
-            int vsum = 0;
-            const uint8_t* pp = center + v * L.pitch;
-            const uint8_t* pm = center - v * L.pitch;
-            for (int u = -d; u <= d; ++u) {
-                int vp = pp[u], vm = pm[u];
-                vsum += vp - vm;
-                m10 += u * (vp + vm);
+    {
+        const int u = lane - HALF_PATCH, au = abs(u);
+        int colsum = 0;
+#pragma unroll
+        for (int v = -HALF_PATCH; v <= HALF_PATCH; ++v) {
+            const int d = c_umax[v < 0 ? -v : v];
+            if (au <= d && lane < 31) {
+                const int I = center[(ptrdiff_t)v * L.pitch + u];
+                colsum += I;
+                m01 += v * I;
             }
-            m01 = v * vsum;
         }
+        m10 = u * colsum;
     }
     m10 = __reduce_add_sync(0xffffffffu, m10);
     m01 = __reduce_add_sync(0xffffffffu, m01);
@@ -460,62 +472,6 @@ __global__ void __launch_bounds__(256) k_orient(const uint8_t* __restrict__ pyr,
         k.octave = l;
         k.class_id = -1;
         kps[(size_t)b * nfeatures + base + i] = k;
-    }
-}
-
-// ------------------------------------------------------------------------------------------------ K5 blur
-// 7x7 separable Gaussian with OpenCV's 8U fixed-point rounding: tile 128 x 32 outputs per CTA,
-// rows staged in shared memory, horizontal pass into u16, vertical pass + (acc + 2^15) >> 16.
-static const int BL_TW = 128, BL_TH = 32, BL_THREADS = 256;
-static const int BL_PW = BL_TW + 8;       // staged width (x0-4 .. x0+131), multiple of 4
-__global__ void __launch_bounds__(BL_THREADS) k_blur(const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blr,
-                                                     size_t framePyr, const LevelPlan* __restrict__ levels,
-                                                     const BlurTile* __restrict__ tiles, int variant) {
-    __shared__ __align__(16) uint8_t s_in[(BL_TH + 6) * BL_PW];
-    __shared__ __align__(16) uint16_t s_h[(BL_TH + 6) * BL_TW];
-    const BlurTile T = tiles[blockIdx.x];
-    const int b = blockIdx.y, tid = threadIdx.x;
-    const LevelPlan L = levels[T.level];
-    const uint8_t* plane = pyr + (size_t)b * framePyr + L.off;
-    // stage rows y0-3 .. y0+BL_TH+2, cols x0-4 .. x0+BL_TW+3 (plane coordinates = ROI + 16)
-    const int wordsPerRow = BL_PW >> 2;
-    for (int i = tid; i < (BL_TH + 6) * wordsPerRow; i += BL_THREADS) {
-        int r = i / wordsPerRow, wq = i - r * wordsPerRow;
-        int py = T.y0 - 3 + r + EDGE, px = T.x0 - 4 + (wq << 2) + EDGE;
-        uint32_t v = 0;
-        if (py < L.rows && px + 3 < L.pitch) v = __ldg(reinterpret_cast<const uint32_t*>(plane + (size_t)py * L.pitch + px));
-        *reinterpret_cast<uint32_t*>(s_in + r * BL_PW + (wq << 2)) = v;
-    }
-    __syncthreads();
-    int k[7];
-#pragma unroll
-    for (int i = 0; i < 7; i++) k[i] = c_gauss[variant][i];
-    for (int i = tid; i < (BL_TH + 6) * BL_TW; i += BL_THREADS) {
-        int r = i / BL_TW, x = i - r * BL_TW;
-        const uint8_t* p = s_in + r * BL_PW + x + 1;     // p[0] = column x-3
-        int s = 0;
-#pragma unroll
-        for (int q = 0; q < 7; q++) s += k[q] * p[q];
-        s_h[i] = (uint16_t)s;
-    }
-    __syncthreads();
-    uint8_t* oroi = blr + (size_t)b * framePyr + L.off + (size_t)EDGE * L.pitch + EDGE;
-    for (int i = tid; i < BL_TH * (BL_TW >> 2); i += BL_THREADS) {
-        int r = i / (BL_TW >> 2), xq = i - r * (BL_TW >> 2);
-        int y = T.y0 + r, x = T.x0 + (xq << 2);
-        if (y >= L.h || x >= L.w) continue;
-        uint32_t outv = 0;
-#pragma unroll
-        for (int c = 0; c < 4; c++) {
-            int s = 0;
-#pragma unroll
-            for (int q = 0; q < 7; q++) s += k[q] * s_h[(r + q) * BL_TW + (xq << 2) + c];
-            int v = (s + 32768) >> 16;
-            outv |= (uint32_t)min(max(v, 0), 255) << (8 * c);
-        }
-        uint8_t* o = oroi + (size_t)y * L.pitch + x;
-        if (x + 3 < L.w) *reinterpret_cast<uint32_t*>(o) = outv;
-        else for (int c = 0; c < 4 && x + c < L.w; c++) o[c] = (uint8_t)(outv >> (8 * c));
     }
 }
 
@@ -583,9 +539,8 @@ struct GforbExtractor {
     int planW = -1, planH = -1;
     std::vector<LevelPlan> levels;
     std::vector<CellPlan> cells;
-    std::vector<BlurTile> tiles;
     size_t framePyr = 0, frameCand = 0, frameKp = 0;
-    int kpCapTotal = 0, nCellsTotal = 0, detSmem = 0, detPixPitch = 0, fnTasks = 0;
+    int kpCapTotal = 0, nCellsTotal = 0, detSmem = 0, detPixPitch = 0, fnTasks = 0, blTasks = 0;
     bool tiled = true;
     int detectVersion = 2;              // GFORB_DETECT=1 selects the first-generation per-cell kernel (A/B tool)
     // device buffers
@@ -597,9 +552,8 @@ struct GforbExtractor {
     int *d_lvlPre = nullptr, *d_lvlCount = nullptr, *d_err = nullptr;
     LevelPlan* d_levels = nullptr;
     CellPlan* d_cells = nullptr;
-    BlurTile* d_tiles = nullptr;
     int2* d_tabs = nullptr;
-    size_t capPyr = 0, capCand = 0, capKp = 0, capCells = 0, capTiles = 0, capTabs = 0, capImg = 0;
+    size_t capPyr = 0, capCand = 0, capKp = 0, capCells = 0, capTabs = 0, capImg = 0;
     int lastBatch = 0, lastLaunches = 0, numSMs = 148;
     bool profiling = false;
     std::vector<Stage> stages;          // per-stage name + average ms over the recorded calls
@@ -659,10 +613,9 @@ static int build_plan(GforbExtractor* E, int w, int h) {
     const int nl = c.nlevels;
     E->levels.assign(nl, LevelPlan());
     E->cells.clear();
-    E->tiles.clear();
     std::vector<int2> tabs;
     size_t off = 0;
-    int kpBase = 0, candBase = 0, maxCellW = 0, fnTasks = 0;
+    int kpBase = 0, candBase = 0, maxCellW = 0, fnTasks = 0, blTasks = 0;
     bool tiled = true;      // cell interiors tile [16, w-16) x [16, h-16) (k_fast_nms precondition)
     const float imageRatio = (float)w / h;
     for (int l = 0; l < nl; l++) {
@@ -692,6 +645,9 @@ static int build_plan(GforbExtractor* E, int w, int h) {
         L.fnStripsY = (H + FN_ROWS - 1) / FN_ROWS;
         L.fnTaskBase = fnTasks;
         fnTasks += L.fnStripsX * L.fnStripsY;
+        L.blStripsX = (L.w + 127) / 128;
+        L.blTaskBase = blTasks;
+        blTasks += L.blStripsX * ((L.h + BL2_ROWS - 1) / BL2_ROWS);
         if ((long long)L.cellW * (L.levelCols - 1) >= W || (long long)L.cellH * (L.levelRows - 1) >= H) tiled = false;
         L.kpBase = kpBase;
         L.kpCap = 2 * L.nDesired + L.nCells + 64;
@@ -728,8 +684,6 @@ static int build_plan(GforbExtractor* E, int w, int h) {
                 E->cells.push_back(C);
             }
         }
-        for (int y0 = 0; y0 < L.h; y0 += BL_TH)
-            for (int x0 = 0; x0 < L.w; x0 += BL_TW) E->tiles.push_back(BlurTile{l, x0, y0});
     }
     E->framePyr = off;
     E->frameCand = (size_t)candBase + 4;
@@ -737,6 +691,7 @@ static int build_plan(GforbExtractor* E, int w, int h) {
     E->kpCapTotal = kpBase;
     E->nCellsTotal = (int)E->cells.size();
     E->fnTasks = fnTasks;
+    E->blTasks = blTasks;
     E->tiled = tiled;
     E->detPixPitch = (maxCellW + 16 + 3) & ~3;
     E->detSmem = (DET_BAND + 8) * E->detPixPitch + (DET_BAND + 2) * E->detPixPitch + DET_BAND * ((maxCellW + 31) / 32) * 4 + 16;
@@ -755,15 +710,12 @@ static int build_plan(GforbExtractor* E, int w, int h) {
     }
     if (E->d_levels) cudaFree(E->d_levels);
     if (E->d_cells) cudaFree(E->d_cells);
-    if (E->d_tiles) cudaFree(E->d_tiles);
     if (E->d_tabs) cudaFree(E->d_tabs);
     GF_CUDA_OK(cudaMalloc((void**)&E->d_levels, sizeof(LevelPlan) * nl));
     GF_CUDA_OK(cudaMalloc((void**)&E->d_cells, sizeof(CellPlan) * E->cells.size()));
-    GF_CUDA_OK(cudaMalloc((void**)&E->d_tiles, sizeof(BlurTile) * E->tiles.size()));
     GF_CUDA_OK(cudaMalloc((void**)&E->d_tabs, sizeof(int2) * std::max<size_t>(tabs.size(), 1)));
     GF_CUDA_OK(cudaMemcpy(E->d_levels, E->levels.data(), sizeof(LevelPlan) * nl, cudaMemcpyHostToDevice));
     GF_CUDA_OK(cudaMemcpy(E->d_cells, E->cells.data(), sizeof(CellPlan) * E->cells.size(), cudaMemcpyHostToDevice));
-    GF_CUDA_OK(cudaMemcpy(E->d_tiles, E->tiles.data(), sizeof(BlurTile) * E->tiles.size(), cudaMemcpyHostToDevice));
     if (!tabs.empty()) GF_CUDA_OK(cudaMemcpy(E->d_tabs, tabs.data(), sizeof(int2) * tabs.size(), cudaMemcpyHostToDevice));
     GF_CUDA_OK(cudaFuncSetAttribute(k_detect, cudaFuncAttributeMaxDynamicSharedMemorySize, E->detSmem));
     E->planW = w; E->planH = h;
@@ -835,7 +787,7 @@ int gforb_extractor_destroy(GforbExtractor* E) {
     cudaSetDevice(E->device);
     void* ptrs[] = {E->d_img, E->d_pyr, E->d_blr, E->d_desc, E->d_kps, E->d_counts, E->d_cand, E->d_lvlKp, E->d_cnt7,
                     E->d_cnt20, E->d_nTotal, E->d_nToRetain, E->d_cellOff, E->d_lvlPre, E->d_lvlCount, E->d_err,
-                    E->d_levels, E->d_cells, E->d_tiles, E->d_tabs};
+                    E->d_levels, E->d_cells, E->d_tabs};
     for (void* p : ptrs) if (p) cudaFree(p);
     for (auto& r : E->recs) { cudaEventDestroy(r.e0); cudaEventDestroy(r.e1); }
     for (auto& e : E->evPool) cudaEventDestroy(e);
@@ -930,12 +882,17 @@ int gforb_extract(GforbExtractor* E, const uint8_t* images, int w, int h, int st
         cudaEventRecord(r.e0, st);
     };
     auto end = [&]() { if (!prof) return; cudaEventRecord(E->recs.back().e1, st); si++; };
-    const int gsBlocks = E->numSMs * 8;
 
     begin("pyramid");
-    k_border0<<<gsBlocks, 256, 0, st>>>(dimg, w, h, dstride, dfs, E->d_pyr, E->framePyr, E->levels[0], batch); launches++;
+    {
+        const LevelPlan& L0 = E->levels[0];
+        const int tx = (L0.pitch >> 4) <= 32 ? 32 : 64, ty = 256 / tx;
+        k_border0<<<dim3((L0.rows + ty - 1) / ty, batch), dim3(tx, ty), 0, st>>>(dimg, w, h, dstride, dfs, E->d_pyr, E->framePyr, L0); launches++;
+    }
     for (int l = 1; l < nl; l++) {
-        k_resize<<<gsBlocks, 256, 0, st>>>(E->d_pyr, E->framePyr, E->levels[l - 1], E->levels[l], E->d_tabs, batch); launches++;
+        const LevelPlan& D = E->levels[l];
+        const int quads = (D.w + 2 * EDGE + 3) >> 2, nBands = (D.rows + RS_BAND - 1) / RS_BAND;
+        k_resize<<<dim3((quads * nBands + 255) / 256, batch), 256, 0, st>>>(E->d_pyr, E->framePyr, E->levels[l - 1], D, E->d_tabs, quads, nBands); launches++;
     }
     end();
     begin("detect");
@@ -965,7 +922,8 @@ int gforb_extract(GforbExtractor* E, const uint8_t* images, int w, int h, int st
                                                                     E->frameKp, E->kpCapTotal, E->d_lvlCount, dk, dc, c.nfeatures); launches++;
     end();
     begin("blur");
-    k_blur<<<dim3((unsigned)E->tiles.size(), batch), BL_THREADS, 0, st>>>(E->d_pyr, E->d_blr, E->framePyr, E->d_levels, E->d_tiles, c.blur_variant); launches++;
+    k_blur2<<<dim3((E->blTasks + BL2_WARPS - 1) / BL2_WARPS, batch), BL2_WARPS * 32, 0, st>>>(
+        E->d_pyr, E->d_blr, E->framePyr, E->d_levels, nl, E->blTasks, c.blur_variant); launches++;
     end();
     begin("describe");
     k_describe<<<dim3((E->kpCapTotal + 7) / 8, batch), 256, 0, st>>>(E->d_pyr, E->d_blr, E->framePyr, E->d_levels, nl, E->d_lvlKp,
