@@ -216,7 +216,8 @@ __global__ void __launch_bounds__(128) k_logdet(const double* __restrict__ mats,
 enum { MTD_GREEDY = 1, MTD_LAZIER_SELECT = 2, MTD_LAZIER_AUTO = 3, MTD_LAZIER_DELETE = 5 };
 static const int SEL_THREADS = 256;
 static const int MAX_RANDOM_QUERY_TIME = 2000;
-static const int RAW_RING = 512;     // pre-generated rand() outputs (power of two)
+static const int RAW_RING = 1024;    // pre-generated rand() outputs (power of two, >= SEL_WIN + 64)
+static const int SEL_WIN = 2 * SEL_THREADS;   // rand() draws examined per sampling pass (2 per thread)
 
 struct SelParams {
     const double* blocks;      // batch x stride x 49
@@ -299,10 +300,11 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const SelParams P) {
     const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int n = min(P.counts[b], min(P.stride, P.maxPoints));
     int* idxA = reinterpret_cast<int*>(smraw);
-    int* visA = idxA + P.maxPoints;
-    int* idxB = visA + P.maxPoints;
-    int* visB = idxB + P.maxPoints;
-    int* list = visB + P.maxPoints;
+    int* vis = idxA + P.maxPoints;           // lmkVisited: round stamp per column (never shifted: only stamps of the
+                                              // current round are ever compared, and a round erases no column)
+    int* idxB = vis + P.maxPoints;
+    int* win = idxB + P.maxPoints;           // per column: (pass epoch << 9 | 511 - draw) of the first draw in a pass
+    int* list = win + P.maxPoints;
     unsigned char* alive = reinterpret_cast<unsigned char*>(list + P.maxPoints);   // `selected` flag per pool entry
     unsigned char* okf = alive + P.maxPoints;                                      // obs_score >= 0
     __shared__ double cur[49];
@@ -311,6 +313,8 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const SelParams P) {
     __shared__ uint32_t s_rs[64];
     __shared__ uint32_t s_raw[RAW_RING];
     __shared__ int s_cnt, s_pick, s_pos;
+    __shared__ unsigned s_new[16], s_valid[16];
+    __shared__ int s_cut[16];
     __shared__ double s_val;
     const double* blk = P.blocks + (size_t)b * P.stride * 49;
     const double* sc = P.obsScore ? P.obsScore + (size_t)b * P.stride : nullptr;
@@ -331,7 +335,7 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const SelParams P) {
     // init
     if (tid < 49) cur[tid] = (tid % 8 == 0) ? 0.00001 : 0.0;
     for (int i = tid; i < n; i += SEL_THREADS) {
-        idxA[i] = i; visA[i] = -1; alive[i] = deletion ? 1 : 0;
+        idxA[i] = i; vis[i] = -1; win[i] = 0; alive[i] = deletion ? 1 : 0;
         okf[i] = (sc && sc[i] < 0) ? 0 : 1;
     }
     __syncthreads();
@@ -343,10 +347,11 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const SelParams P) {
     WarpRand rng;
     rng.rs = s_rs; rng.raw = s_raw; rng.n = 34;
     if (warp == 0 && mtd != MTD_GREEDY) rng.seed(P.seeds ? P.seeds[b] : 1u, lane);
-    int rp = 0;                       // rand() calls consumed so far (warp 0)
+    int rp = 0;                       // rand() calls consumed so far (uniform)
     __syncthreads();
     int m = n;                        // live columns of lmkIdx / lmkVisited
-    int* idx = idxA; int* vis = visA; int* idx2 = idxB; int* vis2 = visB;
+    int* idx = idxA; int* idx2 = idxB;
+    int epoch = 1;                    // sampling pass counter (uniform)
     const int rounds = deletion ? n - k : k;
     int nOut = 0;
     for (int i = 0; i < rounds; i++) {
@@ -369,47 +374,95 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const SelParams P) {
                 if (tid == 0) { int t = 0; for (int w = 0; w < SEL_THREADS / 32; w++) t += redT[w]; s_cnt += t; }
                 __syncthreads();
             }
-        } else if (warp == 0) {
-            // RANDOM_ACCESS_LAZIER_GREEDY sampling (:2895-2921), 32 rand() draws per step.  A draw is "new" if its
-            // column was not visited in this round; new + valid draws count towards szActualSubset; 2000 consecutive
-            // rejections stop the round.  Only the draws the sequential loop would have made are consumed.
+        } else {
+            // RANDOM_ACCESS_LAZIER_GREEDY sampling (:2895-2921), block-parallel: each pass examines the next SEL_WIN
+            // rand() draws (2 per thread, draw number d = h * 256 + tid).  A draw is "new" if its column was not visited
+            // in this round (stamp in vis[] from earlier passes, first-in-pass decided by atomicMax on win[]); new + valid
+            // draws count towards szActualSubset; 2000 consecutive rejections stop the round.  The pass is cut at the
+            // draw where the sequential loop would have stopped; only draws up to the cut are consumed and committed.
             size_t szActual = szLazier;
             if ((size_t)m < szActual) szActual = (size_t)m;
-            int numHit = 0, cnt = 0, rej = 0;
+            int numHit = 0, cntL = 0, rej = 0;
             bool stop = (size_t)numHit >= szActual;
             while (!stop) {
-                rng.ensure(rp, lane);
-                const uint32_t r = s_raw[(rp + lane) & (RAW_RING - 1)];
-                const int j = (int)(r % (uint32_t)m);
-                const bool seen = vis[j] >= i;
-                const unsigned same = __match_any_sync(full, j);
-                const bool isNew = !seen && (lane == __ffs(same) - 1);
-                const int que = idx[j];
-                const bool sel = alive[que] != 0;
-                const bool valid = isNew && !((deletion ? !sel : sel) || !okf[que]);
-                const unsigned newMask = __ballot_sync(full, isNew), validMask = __ballot_sync(full, valid);
-                const unsigned le = (lane == 31) ? full : ((2u << lane) - 1u);
-                // cut A: numHit reaches szActual at this lane
-                const bool hitA = valid && (size_t)(numHit + __popc(validMask & le)) == szActual;
-                // cut B: this rejected draw is the 2000th consecutive rejection
-                const unsigned newBefore = newMask & (le >> 1);
-                const int lastNew = newBefore ? 31 - __clz(newBefore) : -1;
-                const int run = newBefore ? lane - lastNew : rej + lane + 1;
-                const bool hitB = !isNew && run >= MAX_RANDOM_QUERY_TIME;
-                const unsigned cutMask = __ballot_sync(full, hitA || hitB);
-                const int cut = cutMask ? __ffs(cutMask) - 1 : 31;
-                const unsigned take = (cut == 31) ? full : ((2u << cut) - 1u);
-                if (isNew && lane <= cut) vis[j] = i;
-                if (valid && lane <= cut) list[cnt + __popc(validMask & (le >> 1))] = que;
-                cnt += __popc(validMask & take);
-                numHit += __popc(validMask & take);
-                const unsigned newTaken = newMask & take;
-                rej = newTaken ? cut - (31 - __clz(newTaken)) : rej + cut + 1;
+                if (warp == 0) while (rng.n - 344 < rp + SEL_WIN) rng.gen30(lane);
+                __syncthreads();
+                int jj[2]; int key[2]; bool seenPrev[2];
+#pragma unroll
+                for (int h = 0; h < 2; h++) {
+                    const int d = h * SEL_THREADS + tid;
+                    const uint32_t r = s_raw[(rp + d) & (RAW_RING - 1)];
+                    jj[h] = (int)(r % (uint32_t)m);
+                    seenPrev[h] = vis[jj[h]] >= i;
+                    key[h] = (epoch << 9) | (511 - d);
+                    if (!seenPrev[h]) atomicMax(&win[jj[h]], key[h]);
+                }
+                __syncthreads();
+                bool isNew[2], valid[2]; int que[2]; unsigned nm[2], vm[2];
+#pragma unroll
+                for (int h = 0; h < 2; h++) {
+                    isNew[h] = !seenPrev[h] && win[jj[h]] == key[h];
+                    que[h] = idx[jj[h]];
+                    const bool sel = alive[que[h]] != 0;
+                    valid[h] = isNew[h] && !((deletion ? !sel : sel) || !okf[que[h]]);
+                    nm[h] = __ballot_sync(full, isNew[h]);
+                    vm[h] = __ballot_sync(full, valid[h]);
+                    if (lane == 0) { s_new[h * 8 + warp] = nm[h]; s_valid[h * 8 + warp] = vm[h]; }
+                }
+                __syncthreads();
+                const unsigned lt = (1u << lane) - 1u;
+                int vBefore[2];
+#pragma unroll
+                for (int h = 0; h < 2; h++) {
+                    const int g = h * 8 + warp, d = h * SEL_THREADS + tid;
+                    int vb = numHit;
+                    for (int q = 0; q < g; q++) vb += __popc(s_valid[q]);
+                    vb += __popc(vm[h] & lt);
+                    vBefore[h] = vb;
+                    const bool hitA = valid[h] && (size_t)(vb + 1) == szActual;
+                    // consecutive rejections ending at this draw (only meaningful for a rejected draw)
+                    int run;
+                    if (nm[h] & lt) run = lane - (31 - __clz(nm[h] & lt));
+                    else {
+                        int q = g - 1;
+                        while (q >= 0 && s_new[q] == 0u) q--;
+                        run = (q >= 0) ? d - (q * 32 + 31 - __clz(s_new[q])) : rej + d + 1;
+                    }
+                    const bool hitB = !isNew[h] && run >= MAX_RANDOM_QUERY_TIME;
+                    const unsigned cm = __ballot_sync(full, hitA || hitB);
+                    if (lane == 0) s_cut[g] = cm ? g * 32 + __ffs(cm) - 1 : INT_MAX;
+                }
+                __syncthreads();
+                int cut = INT_MAX;
+                for (int q = 0; q < 16; q++) if (s_cut[q] != INT_MAX) { cut = s_cut[q]; break; }
+                stop = cut != INT_MAX;
+                if (!stop) cut = SEL_WIN - 1;
+                // commit the consumed draws
+#pragma unroll
+                for (int h = 0; h < 2; h++) {
+                    const int d = h * SEL_THREADS + tid;
+                    if (d <= cut) {
+                        if (isNew[h]) vis[jj[h]] = i;
+                        if (valid[h]) list[cntL + vBefore[h] - numHit] = que[h];
+                    }
+                }
+                // uniform bookkeeping: valid draws taken, trailing rejection run, draws consumed
+                int V = 0, lastNew = -1;
+                for (int q = 0; q < 16; q++) {
+                    const int lo = q * 32;
+                    if (lo > cut) break;
+                    const unsigned take = (cut - lo >= 31) ? full : ((2u << (cut - lo)) - 1u);
+                    V += __popc(s_valid[q] & take);
+                    const unsigned nw = s_new[q] & take;
+                    if (nw) lastNew = lo + 31 - __clz(nw);
+                }
+                cntL += V; numHit += V;
+                rej = (lastNew >= 0) ? cut - lastNew : rej + cut + 1;
                 rp += cut + 1;
-                stop = cutMask != 0;
-                __syncwarp();
+                epoch++;
+                __syncthreads();
             }
-            if (lane == 0) s_cnt = cnt;
+            if (tid == 0) s_cnt = cntL;
         }
         __syncthreads();
         const int cnt = s_cnt;
@@ -449,11 +502,11 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const SelParams P) {
         __syncthreads();
         const int pos = s_pos;
         for (int j = tid; j < m; j += SEL_THREADS) {
-            if (j < pos) { idx2[j] = idx[j]; vis2[j] = vis[j]; }
-            else if (j > pos) { idx2[j - 1] = idx[j]; vis2[j - 1] = vis[j]; }
+            if (j < pos) idx2[j] = idx[j];
+            else if (j > pos) idx2[j - 1] = idx[j];
         }
         m -= 1;
-        { int* t = idx; idx = idx2; idx2 = t; t = vis; vis = vis2; vis2 = t; }
+        { int* t = idx; idx = idx2; idx2 = t; }
         __syncthreads();
     }
     if (deletion) {
