@@ -1,0 +1,481 @@
+// orb_slam.hpp -- header-only C++ mirror of the reference's operator API over the C ABI in gforb.h.
+//
+// A GF-ORB-SLAM maintainer replaces
+//     #include "ORBextractor.h" / "ORBmatcher.h" / "Observability.h"
+// by this header (and links libgforb.so) to run the per-frame tracking front end on a B200.  Class and member names,
+// argument order and meaning, defaults and error behaviour follow the reference:
+//     ORB_SLAM::ORBextractor   include/ORBextractor.h:51-104,  src/ORBextractor.cc:464-998
+//     ORB_SLAM::ORBmatcher     include/ORBmatcher.h:39-294,    src/ORBmatcher.cc
+//     ORB_SLAM::Observability  include/Observability.h:113-770, src/Observability.cc
+// With -DGFORB_WITH_OPENCV the real cv::Mat / cv::KeyPoint / cv::Point2f are used; otherwise layout-compatible
+// stand-ins (namespace gforb_cv) keep the header free of dependencies.  Frame and MapPoint are reduced to the fields
+// this path reads and writes (the shim flattens them into the SoA buffers of the C ABI and scatters results back).
+// There is no CPU fallback: if no CUDA device is usable the constructors throw std::runtime_error.
+#ifndef GFORB_ORB_SLAM_HPP
+#define GFORB_ORB_SLAM_HPP
+
+#include <algorithm>
+#include <cassert>
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../gforb.h"
+
+#ifdef GFORB_WITH_OPENCV
+#include <opencv2/core/core.hpp>
+#include <opencv2/features2d/features2d.hpp>
+namespace gforb_cv = cv;
+#else
+namespace gforb_cv {
+struct Point2f { float x = 0, y = 0; Point2f() {} Point2f(float x_, float y_) : x(x_), y(y_) {} };
+struct KeyPoint {            // same 28-byte layout as cv::KeyPoint
+    Point2f pt; float size = 0, angle = -1, response = 0; int octave = 0, class_id = -1;
+};
+// 8-bit single-channel matrix (CV_8UC1) or, for poses, 32-bit float (CV_32F); owns its storage unless wrapping
+struct Mat {
+    int rows = 0, cols = 0, elem = 1;
+    size_t step = 0;
+    uint8_t* data = nullptr;
+    std::vector<uint8_t> own;
+    Mat() {}
+    Mat(const Mat& o) { *this = o; }
+    Mat& operator=(const Mat& o) {       // an owning matrix re-binds its data pointer to the copied storage
+        rows = o.rows; cols = o.cols; elem = o.elem; step = o.step; own = o.own;
+        data = (!o.own.empty() && o.data == o.own.data()) ? own.data() : o.data;
+        return *this;
+    }
+    Mat(int r, int c, uint8_t* ext, size_t stp) : rows(r), cols(c), elem(1), step(stp), data(ext) {}
+    bool empty() const { return rows == 0 || cols == 0 || data == nullptr; }
+    void create(int r, int c, int elemBytes = 1) {
+        rows = r; cols = c; elem = elemBytes; step = (size_t)c * elemBytes;
+        own.assign((size_t)r * step, 0); data = own.data();
+    }
+    uint8_t* ptr(int r = 0) { return data + (size_t)r * step; }
+    const uint8_t* ptr(int r = 0) const { return data + (size_t)r * step; }
+    Mat row(int r) const { return Mat(1, cols, const_cast<uint8_t*>(ptr(r)), step); }
+    template <class T> T& at(int r, int c) { return reinterpret_cast<T*>(ptr(r))[c]; }
+    template <class T> const T& at(int r, int c) const { return reinterpret_cast<const T*>(ptr(r))[c]; }
+};
+}  // namespace gforb_cv
+#endif
+
+namespace ORB_SLAM {
+
+static_assert(sizeof(gforb_cv::KeyPoint) == sizeof(GforbKeyPoint), "KeyPoint must be layout-compatible with cv::KeyPoint");
+
+inline void gforb_throw(int rc, const char* what) {
+    if (rc == GFORB_OK) return;
+    throw std::runtime_error(std::string(what) + ": gforb error " + std::to_string(rc));
+}
+
+// ------------------------------------------------------------------------------------------------ ORBextractor
+class ORBextractor {
+public:
+    enum { HARRIS_SCORE = 0, FAST_SCORE = 1 };
+    ORBextractor(int nfeatures = 1000, float scaleFactor = 1.2f, int nlevels = 8, int scoreType = FAST_SCORE,
+                 int fastTh = 20, int device = 0)
+        : nfeatures_(nfeatures), scaleFactor_(scaleFactor), nlevels_(nlevels), scoreType_(scoreType), fastTh_(fastTh),
+          device_(device) {
+        if (gforb_device_count() <= 0) throw std::runtime_error("ORBextractor: no CUDA device (the B200 path has no CPU fallback)");
+    }
+    ~ORBextractor() { if (h_) gforb_extractor_destroy(h_); }
+    ORBextractor(const ORBextractor&) = delete;
+    ORBextractor& operator=(const ORBextractor&) = delete;
+
+    // Compute the ORB features and descriptors on an image (include/ORBextractor.h:60-64).  The mask is ignored, as in
+    // the reference (always empty, src/Frame.cc:59).  An empty image returns silently (src/ORBextractor.cc:772-773).
+    void operator()(const gforb_cv::Mat& image, const gforb_cv::Mat& /*mask*/, std::vector<gforb_cv::KeyPoint>& keypoints,
+                    gforb_cv::Mat& descriptors) {
+        if (image.empty()) return;
+        ensure(image.cols, image.rows);
+        kp_.resize(nfeatures_);
+        desc_.resize((size_t)nfeatures_ * 32);
+        int32_t n = 0;
+        gforb_throw(gforb_extract(h_, image.data, image.cols, image.rows, (int)image.step, image.step * image.rows, 1,
+                                  kp_.data(), desc_.data(), &n, 0, nullptr), "ORBextractor::operator()");
+        keypoints.clear();                                   // src/ORBextractor.cc:816
+        if (n == 0) { descriptors = gforb_cv::Mat(); return; }
+        keypoints.resize(n);
+        std::memcpy(static_cast<void*>(keypoints.data()), kp_.data(), (size_t)n * sizeof(GforbKeyPoint));
+#ifdef GFORB_WITH_OPENCV
+        descriptors.create(n, 32, CV_8U);
+#else
+        descriptors.create(n, 32);
+#endif
+        for (int i = 0; i < n; i++) std::memcpy(descriptors.ptr(i), desc_.data() + (size_t)i * 32, 32);
+    }
+    int GetLevels() { return nlevels_; }
+    float GetScaleFactor() { return scaleFactor_; }
+
+private:
+    void ensure(int w, int h) {
+        if (h_ && w <= maxW_ && h <= maxH_) return;
+        if (h_) { gforb_extractor_destroy(h_); h_ = nullptr; }
+        GforbExtractorConfig c;
+        std::memset(&c, 0, sizeof(c));
+        c.nfeatures = nfeatures_; c.scaleFactor = scaleFactor_; c.nlevels = nlevels_; c.scoreType = scoreType_;
+        c.iniThFAST = fastTh_; c.minThFAST = 7; c.blur_variant = 0; c.retain_variant = 0;
+        c.max_width = w; c.max_height = h; c.max_batch = 1; c.device = device_;
+        gforb_throw(gforb_extractor_create(&c, &h_), "ORBextractor: create");
+        maxW_ = w; maxH_ = h;
+    }
+    int nfeatures_; float scaleFactor_; int nlevels_, scoreType_, fastTh_, device_;
+    GforbExtractor* h_ = nullptr;
+    int maxW_ = 0, maxH_ = 0;
+    std::vector<GforbKeyPoint> kp_;
+    std::vector<uint8_t> desc_;
+};
+
+// ------------------------------------------------------------------------------------------------ Frame / MapPoint views
+// The MapPoint fields the tracking matchers read (include/MapPoint.h): projection cache written by Frame::isInFrustum,
+// the representative descriptor and the world position.
+struct MapPoint {
+    float mTrackProjX = 0, mTrackProjY = 0;
+    int mnTrackScaleLevel = 0;
+    float mTrackViewCos = 0;
+    bool mbTrackInView = false, mbBad = false;
+    uint8_t mDescriptor[32] = {0};
+    float mWorldPos[3] = {0, 0, 0};
+    double ObsScore = -1;
+    bool isBad() const { return mbBad; }
+    const uint8_t* GetDescriptor() const { return mDescriptor; }
+};
+
+// The Frame fields this path touches (include/Frame.h): undistorted keypoints, descriptors, per-keypoint map-point
+// association / match score / outlier flag, image bounds and the scale pyramid parameters.
+struct Frame {
+    int N = 0;
+    std::vector<gforb_cv::KeyPoint> mvKeysUn;
+    gforb_cv::Mat mDescriptors;                      // N x 32
+    std::vector<MapPoint*> mvpMapPoints;
+    std::vector<int> mvpMatchScore;
+    std::vector<bool> mvbOutlier, mvbCandidate, mvbGoodFeature;
+    int mnMinX = 0, mnMaxX = 0, mnMinY = 0, mnMaxY = 0;   // statics in the reference (include/Frame.h:142-145)
+    int mnScaleLevels = 8;
+    float mfScaleFactor = 1.2f;
+    std::vector<float> mvLevelSigma2;
+    float mTcw[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
+    float fx = 0, fy = 0, cx = 0, cy = 0;
+
+    Frame() {}
+    // what Frame::Frame does for this path after extraction (src/Frame.cc:40-131; no distortion -> mvKeysUn = mvKeys)
+    Frame(const std::vector<gforb_cv::KeyPoint>& keys, const gforb_cv::Mat& desc, int imgW, int imgH, int nlevels = 8,
+          float scaleFactor = 1.2f)
+        : N((int)keys.size()), mvKeysUn(keys), mDescriptors(desc), mvpMapPoints(keys.size(), nullptr),
+          mvpMatchScore(keys.size(), 999), mvbOutlier(keys.size(), false), mvbCandidate(keys.size(), true),
+          mvbGoodFeature(keys.size(), false), mnMinX(0), mnMaxX(imgW), mnMinY(0), mnMaxY(imgH), mnScaleLevels(nlevels),
+          mfScaleFactor(scaleFactor) {
+        mvLevelSigma2.assign(nlevels, 1.0f);
+        float s = 1.0f;
+        for (int i = 1; i < nlevels; i++) { s = s * scaleFactor; mvLevelSigma2[i] = s * s; }
+    }
+};
+
+// ------------------------------------------------------------------------------------------------ ORBmatcher
+class ORBmatcher {
+public:
+    static const int TH_LOW = 50, TH_HIGH = 100, HISTO_LENGTH = 30;      // src/ORBmatcher.cc:40-42
+    ORBmatcher(float nnratio = 0.6f, bool checkOri = true, int device = 0)
+        : mfNNratio(nnratio), mbCheckOrientation(checkOri), device_(device) {
+        if (gforb_device_count() <= 0) throw std::runtime_error("ORBmatcher: no CUDA device (the B200 path has no CPU fallback)");
+    }
+    ~ORBmatcher() { if (h_) gforb_matcher_destroy(h_); }
+    ORBmatcher(const ORBmatcher&) = delete;
+    ORBmatcher& operator=(const ORBmatcher&) = delete;
+
+    // Hamming distance of two 32-byte descriptors (src/ORBmatcher.cc:2384-2400).  The reference calls this scalar helper
+    // from host loops; here it goes through gforb_descriptor_distance like every batched caller (n = 1).
+    int DescriptorDistance(const gforb_cv::Mat& a, const gforb_cv::Mat& b) {
+        ensure(1, 1, 8, 1.2f);
+        int32_t d = 0;
+        gforb_throw(gforb_descriptor_distance(h_, a.ptr(0), b.ptr(0), 1, &d, 0, nullptr), "DescriptorDistance");
+        return d;
+    }
+
+    // Search matches between Frame keypoints and projected MapPoints; returns the number of matches
+    // (include/ORBmatcher.h:48-50, src/ORBmatcher.cc:384-465).  F.mvpMapPoints / F.mvpMatchScore are updated in place.
+    int SearchByProjection(Frame& F, const std::vector<MapPoint*>& vpMapPoints, const float th = 3) {
+        const int M = (int)vpMapPoints.size();
+        if (F.N == 0 || M == 0) return 0;
+        ensure(F.N, M, F.mnScaleLevels, F.mfScaleFactor);
+        std::vector<float> u(M), v(M), vc(M);
+        std::vector<int32_t> lvl(M);
+        std::vector<uint8_t> fl(M), desc((size_t)M * 32);
+        for (int i = 0; i < M; i++) {
+            const MapPoint* p = vpMapPoints[i];
+            u[i] = p->mTrackProjX; v[i] = p->mTrackProjY; vc[i] = p->mTrackViewCos; lvl[i] = p->mnTrackScaleLevel;
+            fl[i] = (uint8_t)((p->mbTrackInView ? 1 : 0) | (p->isBad() ? 2 : 0));
+            std::memcpy(&desc[(size_t)i * 32], p->GetDescriptor(), 32);
+        }
+        FlatFrame ff(F);
+        std::vector<int32_t> ids = ids_of(F, vpMapPoints), score(F.mvpMatchScore.begin(), F.mvpMatchScore.end());
+        int32_t mcount = M, n = 0;
+        GforbMapPointSet mp = {u.data(), v.data(), lvl.data(), vc.data(), fl.data(), desc.data(), &mcount, M};
+        gforb_throw(gforb_search_by_projection(h_, &ff.set, &mp, 1, th, mfNNratio, ids.data(), score.data(), &n, 0, nullptr),
+                    "SearchByProjection");
+        for (int i = 0; i < F.N; i++) {
+            if (ids[i] >= 0 && ids[i] < M) F.mvpMapPoints[i] = vpMapPoints[ids[i]];
+            F.mvpMatchScore[i] = score[i];
+        }
+        return n;
+    }
+
+    // Matching for the map initialisation / frame-to-frame tracking without a map
+    // (include/ORBmatcher.h:79-80, src/ORBmatcher.cc:1172-1287).
+    int SearchForInitialization(Frame& F1, Frame& F2, std::vector<gforb_cv::Point2f>& vbPrevMatched,
+                                std::vector<int>& vnMatches12, int windowSize = 10) {
+        vnMatches12 = std::vector<int>(F1.N, -1);                  // :1175
+        if (F1.N == 0 || F2.N == 0) return 0;
+        ensure(std::max(F1.N, F2.N), F1.N, F2.mnScaleLevels, F2.mfScaleFactor);
+        FlatFrame a(F1), b(F2);
+        std::vector<float> prev((size_t)F1.N * 2);
+        for (int i = 0; i < F1.N; i++) { prev[2 * i] = vbPrevMatched[i].x; prev[2 * i + 1] = vbPrevMatched[i].y; }
+        std::vector<int32_t> m12(F1.N, -1);
+        int32_t n = 0;
+        gforb_throw(gforb_search_for_initialization(h_, &a.set, &b.set, 1, prev.data(), m12.data(), &n, windowSize,
+                                                    mfNNratio, mbCheckOrientation ? 1 : 0, 0, nullptr),
+                    "SearchForInitialization");
+        for (int i = 0; i < F1.N; i++) {
+            vnMatches12[i] = m12[i];
+            vbPrevMatched[i] = gforb_cv::Point2f(prev[2 * i], prev[2 * i + 1]);     // :1282-1284
+        }
+        return n;
+    }
+
+    // Project MapPoints tracked in the last frame into the current frame and search matches
+    // (include/ORBmatcher.h:52-54, src/ORBmatcher.cc:2081-2202).
+    int SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, float th) {
+        if (CurrentFrame.N == 0 || LastFrame.N == 0) return 0;
+        ensure(std::max(CurrentFrame.N, LastFrame.N), LastFrame.N, CurrentFrame.mnScaleLevels, CurrentFrame.mfScaleFactor);
+        FlatFrame cur(CurrentFrame), last(LastFrame);
+        const int NL = LastFrame.N;
+        std::vector<int32_t> lastIds(NL, -1);
+        std::vector<uint8_t> outl(NL, 0);
+        std::vector<float> world((size_t)NL * 3, 0.f);
+        for (int i = 0; i < NL; i++) {
+            const MapPoint* p = LastFrame.mvpMapPoints[i];
+            if (!p) continue;
+            lastIds[i] = i; outl[i] = LastFrame.mvbOutlier[i] ? 1 : 0;
+            std::memcpy(&world[(size_t)i * 3], p->mWorldPos, 12);
+        }
+        std::vector<int32_t> ids(CurrentFrame.N, -1), score(CurrentFrame.mvpMatchScore.begin(), CurrentFrame.mvpMatchScore.end());
+        for (int i = 0; i < CurrentFrame.N; i++) if (CurrentFrame.mvpMapPoints[i]) ids[i] = NL;   // already claimed
+        int32_t n = 0;
+        gforb_throw(gforb_search_by_projection_frames(h_, &cur.set, &last.set, 1, lastIds.data(), outl.data(), world.data(),
+                                                      CurrentFrame.mTcw, CurrentFrame.fx, CurrentFrame.fy, CurrentFrame.cx,
+                                                      CurrentFrame.cy, th, mfNNratio, mbCheckOrientation ? 1 : 0, ids.data(),
+                                                      score.data(), &n, 0, nullptr),
+                    "SearchByProjection(Current, Last)");
+        for (int i = 0; i < CurrentFrame.N; i++) {
+            if (ids[i] >= 0 && ids[i] < NL) CurrentFrame.mvpMapPoints[i] = LastFrame.mvpMapPoints[ids[i]];
+            else if (ids[i] < 0) CurrentFrame.mvpMapPoints[i] = nullptr;
+            CurrentFrame.mvpMatchScore[i] = score[i];
+        }
+        return n;
+    }
+
+    // src/ORBmatcher.cc:979-1086
+    int WindowSearch(Frame& F1, Frame& F2, int windowSize, std::vector<MapPoint*>& vpMapPointMatches2,
+                     int minScaleLevel = -1, int maxScaleLevel = 0x7fffffff) {
+        vpMapPointMatches2 = std::vector<MapPoint*>(F2.N, static_cast<MapPoint*>(nullptr));
+        if (F1.N == 0 || F2.N == 0) return 0;
+        ensure(std::max(F1.N, F2.N), F1.N, F2.mnScaleLevels, F2.mfScaleFactor);
+        FlatFrame a(F1), b(F2);
+        std::vector<int32_t> ids1(F1.N, -1), m2(F2.N, -1);
+        for (int i = 0; i < F1.N; i++) if (F1.mvpMapPoints[i] && !F1.mvpMapPoints[i]->isBad()) ids1[i] = i;
+        int32_t n = 0;
+        gforb_throw(gforb_window_search(h_, &a.set, &b.set, 1, ids1.data(), windowSize, minScaleLevel, maxScaleLevel,
+                                        mfNNratio, mbCheckOrientation ? 1 : 0, m2.data(), &n, 0, nullptr), "WindowSearch");
+        for (int i = 0; i < F2.N; i++) if (m2[i] >= 0) vpMapPointMatches2[i] = F1.mvpMapPoints[m2[i]];
+        return n;
+    }
+
+    float mfNNratio;
+    bool mbCheckOrientation;
+
+private:
+    struct FlatFrame {          // Frame -> GforbFrameSet (one frame); keeps the staging alive for the call
+        std::vector<uint8_t> desc;
+        int32_t count;
+        GforbFrameSet set;
+        explicit FlatFrame(const Frame& F) : desc((size_t)F.N * 32), count(F.N) {
+            for (int i = 0; i < F.N; i++) std::memcpy(&desc[(size_t)i * 32], F.mDescriptors.ptr(i), 32);
+            set.keypoints = reinterpret_cast<const GforbKeyPoint*>(F.mvKeysUn.data());
+            set.descriptors = desc.data(); set.counts = &count; set.kp_stride = F.N;
+            set.min_x = F.mnMinX; set.max_x = F.mnMaxX; set.min_y = F.mnMinY; set.max_y = F.mnMaxY;
+        }
+    };
+    static std::vector<int32_t> ids_of(const Frame& F, const std::vector<MapPoint*>& pool) {
+        // MapPoint* -> id: index into `pool` when the pointer is one of its entries, otherwise "some other map point"
+        std::vector<int32_t> ids(F.N, -1);
+        for (int i = 0; i < F.N; i++) {
+            if (!F.mvpMapPoints[i]) continue;
+            ids[i] = (int32_t)pool.size();
+            for (size_t k = 0; k < pool.size(); k++) if (pool[k] == F.mvpMapPoints[i]) { ids[i] = (int32_t)k; break; }
+        }
+        return ids;
+    }
+    void ensure(int nKeys, int nQueries, int nlevels, float scaleFactor) {
+        if (h_ && nKeys <= maxKeys_ && nQueries <= maxQ_ && nlevels == nlevels_ && scaleFactor == sf_) return;
+        if (h_) { gforb_matcher_destroy(h_); h_ = nullptr; }
+        maxKeys_ = std::max(maxKeys_, std::max(nKeys, 2048));
+        maxQ_ = std::max(maxQ_, std::max(nQueries, 2048));
+        nlevels_ = nlevels; sf_ = scaleFactor;
+        GforbMatcherConfig c;
+        std::memset(&c, 0, sizeof(c));
+        c.max_batch = 1; c.max_keypoints = maxKeys_; c.max_queries = maxQ_; c.cand_pool = 0; c.nlevels = nlevels;
+        c.scaleFactor = scaleFactor; c.device = device_;
+        gforb_throw(gforb_matcher_create(&c, &h_), "ORBmatcher: create");
+    }
+    int device_;
+    GforbMatcher* h_ = nullptr;
+    int maxKeys_ = 0, maxQ_ = 0, nlevels_ = 0;
+    float sf_ = 0;
+};
+
+// ------------------------------------------------------------------------------------------------ Observability
+// Good-feature selection (DIMENSION_OF_STATE_MODEL = 7).  GoodPoint mirrors include/Util.hpp:64-92 (idx, obs_score,
+// selected, upper_bound); the 7x7 block itself stays in HBM.
+struct GoodPoint {
+    size_t idx = 0;
+    double obs_score = -1, upper_bound = 0;
+    bool selected = false;
+};
+
+class Observability {
+public:
+    enum { FRAME_INFO_MATRIX = 1, MAP_INFO_MATRIX = 2 };                  // mat_type of runMatrixBuilding (subset)
+    // used by Tracking (src/Tracking.cc:146; k1 = k2 = 0)
+    Observability(double fu, double fv, int nRows, int nCols, double Cx, double Cy, double k1, double k2, int device = 0) {
+        init(fu, fv, nRows, nCols, Cx, Cy, k1, k2, 1.0, 1.0, device);
+    }
+    // used by the reference's tests / tools (fu = f / dx, fv = f / dy; include/Observability.h:117-160)
+    Observability(double f, int nRows, int nCols, double Cx, double Cy, double k1, double k2, double dx, double dy,
+                  int device = 0) {
+        init(f / dx, f / dy, nRows, nCols, Cx, Cy, k1, k2, dx, dy, device);
+    }
+    ~Observability() { if (h_) gforb_obs_destroy(h_); }
+    Observability(const Observability&) = delete;
+    Observability& operator=(const Observability&) = delete;
+
+    // include/Observability.h:222-259 / :261-295 (4x4 row-major float poses like the reference's cv::Mat)
+    void updatePWLSVec(const double& time_prev, const gforb_cv::Mat& Tcw_prev, const double& time_cur,
+                       const gforb_cv::Mat& Twc_cur) {
+        float a[16], b[16];
+        for (int r = 0; r < 4; r++) for (int c = 0; c < 4; c++) { a[r * 4 + c] = Tcw_prev.at<float>(r, c); b[r * 4 + c] = Twc_cur.at<float>(r, c); }
+        gforb_throw(gforb_obs_update_pwls(h_, time_prev, a, time_cur, b), "updatePWLSVec");
+    }
+    void predictPWLSVec(const double& dt, const size_t& num_seg_pred) {
+        gforb_throw(gforb_obs_predict_pwls(h_, dt, (int)num_seg_pred), "predictPWLSVec");
+    }
+    void setState(const double* Xv13) { gforb_throw(gforb_obs_set_state(h_, Xv13), "setState"); }
+
+    // the frame / map pool the next calls work on (the reference keeps pFrame / mMapPoints members)
+    Frame* pFrame = nullptr;
+    std::vector<MapPoint*>* mMapPoints = nullptr;
+    size_t mKineIdx = 0;
+
+    // src/Observability.cc:646-804: per-match information blocks for the current pFrame (FRAME_INFO_MATRIX) or the
+    // local map (MAP_INFO_MATRIX).  Time budgets are accepted and ignored (the device call is bounded by construction).
+    bool runMatrixBuilding(const size_t mat_type, const double /*time_for_build*/, const bool /*with_multi_thread*/,
+                           const bool check_viz = false) {
+        double xv[13];
+        if (gforb_obs_get_segment(h_, (int)mKineIdx, xv, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr) != GFORB_OK) return false;
+        if (mat_type == FRAME_INFO_MATRIX) {
+            if (!pFrame || pFrame->N == 0) return false;
+            Frame& F = *pFrame;
+            n_ = F.N;
+            if (n_ > maxPoints_) return false;
+            std::vector<float> world((size_t)n_ * 3, 0.f);
+            std::vector<int32_t> oct(n_), sc(n_);
+            std::vector<uint8_t> valid(n_, 0);
+            for (int i = 0; i < n_; i++) {
+                oct[i] = F.mvKeysUn[i].octave; sc[i] = F.mvpMatchScore[i];
+                const MapPoint* p = F.mvpMapPoints[i];
+                if (p && !F.mvbOutlier[i] && F.mvbCandidate[i]) { valid[i] = 1; std::memcpy(&world[(size_t)i * 3], p->mWorldPos, 12); }
+            }
+            blocks_.resize((size_t)n_ * 49); score_.resize(n_);
+            int32_t cnt = n_;
+            return gforb_obs_build_info_frame(h_, xv, world.data(), oct.data(), sc.data(), valid.data(), &cnt, n_, 1,
+                                              F.mvLevelSigma2.data(), (int)F.mvLevelSigma2.size(), blocks_.data(),
+                                              score_.data(), nullptr, 0, nullptr) == GFORB_OK;
+        }
+        if (mat_type == MAP_INFO_MATRIX) {
+            if (!mMapPoints || mMapPoints->empty() || !pFrame) return false;
+            n_ = (int)mMapPoints->size();
+            if (n_ > maxPoints_) return false;
+            std::vector<float> world((size_t)n_ * 3);
+            std::vector<uint8_t> inView(n_);
+            for (int i = 0; i < n_; i++) { std::memcpy(&world[(size_t)i * 3], (*mMapPoints)[i]->mWorldPos, 12); inView[i] = (*mMapPoints)[i]->mbTrackInView; }
+            blocks_.resize((size_t)n_ * 49); score_.resize(n_);
+            int32_t cnt = n_;
+            const bool ok = gforb_obs_build_info_map(h_, xv, world.data(), inView.data(), &cnt, n_, 1, check_viz ? 1 : 0,
+                                                     pFrame->mnMinX, pFrame->mnMaxX, pFrame->mnMinY, pFrame->mnMaxY,
+                                                     blocks_.data(), score_.data(), nullptr, 0, nullptr) == GFORB_OK;
+            for (int i = 0; ok && i < n_; i++) (*mMapPoints)[i]->ObsScore = score_[i];
+            return ok;
+        }
+        return false;
+    }
+
+    // src/Observability.cc:808-1018: build the frame blocks, pool the valid matches in index order, pick k of them.
+    // greedy_mtd: 1 baseline greedy, 2 lazier greedy, 3 automatic, 5 deletion.  rand() is an explicit stream here:
+    // rng_seed = 1 reproduces a reference process that never called srand().
+    bool setSelction_Number(const size_t num_good_inlier, const int greedy_mtd, const double time_for_select,
+                            const double error_bound, Frame* pF, std::vector<GoodPoint>* mpVec) {
+        if (!pF || !mpVec || num_good_inlier == 0) return false;          // :814-817
+        pFrame = pF;
+        const size_t N_frame = pF->mvpMapPoints.size();
+        const double sampleScale = (double)(size_t)((float)N_frame / (float)num_good_inlier * std::log(1.0 / error_bound));  // :826
+        if (!runMatrixBuilding(FRAME_INFO_MATRIX, time_for_select / 2, true, false)) return false;
+        return select_pool(num_good_inlier, greedy_mtd, sampleScale, mpVec, pF);
+    }
+    // src/Observability.cc:2815-3029 on the pool built by the last runMatrixBuilding
+    bool maxVolSelection_LazierGreedy(const size_t /*stIdx*/, const size_t /*edIdx*/, std::vector<GoodPoint>* subVec,
+                                      const size_t mpLimit, const double sampleScale, const double /*max_time*/) {
+        return select_pool(mpLimit, 2, sampleScale, subVec, nullptr);
+    }
+    uint32_t rng_seed = 1;
+
+private:
+    void init(double fu, double fv, int nRows, int nCols, double Cx, double Cy, double k1, double k2, double dx, double dy,
+              int device) {
+        if (gforb_device_count() <= 0) throw std::runtime_error("Observability: no CUDA device (the B200 path has no CPU fallback)");
+        GforbObsConfig c;
+        std::memset(&c, 0, sizeof(c));
+        c.fu = fu; c.fv = fv; c.nRows = nRows; c.nCols = nCols; c.Cx = Cx; c.Cy = Cy; c.k1 = k1; c.k2 = k2; c.dx = dx; c.dy = dy;
+        c.max_batch = 1; c.max_points = maxPoints_; c.device = device;
+        gforb_throw(gforb_obs_create(&c, &h_), "Observability: create");
+    }
+    bool select_pool(size_t k, int mtd, double sampleScale, std::vector<GoodPoint>* out, Frame* F) {
+        if (n_ <= 0 || !out) return false;
+        // lmkSelectPool = entries with a built block, in index order (:838-848)
+        std::vector<int> pool;
+        for (int i = 0; i < n_; i++) if (score_[i] >= 0) pool.push_back(i);
+        const int np = (int)pool.size();
+        out->clear();
+        if (np == 0) return true;
+        std::vector<double> pb((size_t)np * 49), ps(np), ld(std::max<size_t>(k, 1) + np);
+        for (int t = 0; t < np; t++) { std::memcpy(&pb[(size_t)t * 49], &blocks_[(size_t)pool[t] * 49], 49 * sizeof(double)); ps[t] = score_[pool[t]]; }
+        std::vector<int32_t> idx(np);
+        int32_t cnt = np, nsel = 0;
+        if (gforb_obs_select(h_, pb.data(), ps.data(), &cnt, np, 1, (int)k, mtd, sampleScale, &rng_seed, idx.data(), ld.data(),
+                             &nsel, np, 0, nullptr) != GFORB_OK) return false;
+        for (int t = 0; t < nsel; t++) {
+            GoodPoint g; g.idx = (size_t)pool[idx[t]]; g.obs_score = ps[idx[t]]; g.selected = true; g.upper_bound = ld[t];
+            out->push_back(g);
+            if (F) F->mvbGoodFeature[g.idx] = true;                       // :1009-1010
+        }
+        return true;
+    }
+    GforbObs* h_ = nullptr;
+    int maxPoints_ = 8192, n_ = 0;
+    std::vector<double> blocks_, score_;
+};
+
+}  // namespace ORB_SLAM
+#endif  // GFORB_ORB_SLAM_HPP

@@ -1,0 +1,191 @@
+// GPU parity test of the C++ drop-in shim (include/gforb/orb_slam.hpp over libgforb.so) against the CPU oracle
+// (oracle/oracle.hpp, liboracle.so): it reads like a test of the reference's own classes.
+//   ORBextractor::operator()  ->  keypoints + descriptors bit-exact
+//   ORBmatcher::SearchForInitialization / SearchByProjection / DescriptorDistance -> matches bit-exact
+//   Observability::setSelction_Number (lazier greedy) -> selected subset bit-exact, log-det within 1e-5
+// Built by __graft_entry__.build(); run by tests/test_gpu_shim.py (needs a CUDA device).
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+#include "gforb/orb_slam.hpp"
+#include "../../oracle/oracle.hpp"
+
+static int g_fail = 0;
+#define CHECK(cond, ...)                                            \
+    do {                                                            \
+        if (!(cond)) { g_fail++; printf("FAIL %s:%d: ", __FILE__, __LINE__); printf(__VA_ARGS__); printf("\n"); } \
+    } while (0)
+
+static uint64_t sm_state;
+static uint64_t splitmix() {
+    uint64_t z = (sm_state += 0x9E3779B97F4A7C15ull);
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+
+// blocky texture + noise, shifted by (dx, dy): corner-rich, and consecutive frames overlap
+static void make_frame(std::vector<uint8_t>& img, int w, int h, int dx, int dy, uint64_t noiseSeed) {
+    const int MW = w + 64, MH = h + 64;
+    static std::vector<uint8_t> master;
+    if (master.empty()) {
+        sm_state = 12345;
+        std::vector<uint8_t> base((MW / 4 + 2) * (MH / 4 + 2));
+        for (auto& b : base) b = (uint8_t)(splitmix() >> 56);
+        std::vector<int> up(MW * MH);
+        for (int y = 0; y < MH; y++) for (int x = 0; x < MW; x++) up[y * MW + x] = base[(y / 4) * (MW / 4 + 2) + x / 4];
+        master.resize(MW * MH);
+        for (int y = 0; y < MH; y++)
+            for (int x = 0; x < MW; x++) {
+                int s = 0, n = 0;
+                for (int v = -1; v <= 1; v++) for (int u = -1; u <= 1; u++) {
+                    int yy = y + v, xx = x + u;
+                    if (yy >= 0 && yy < MH && xx >= 0 && xx < MW) { s += up[yy * MW + xx]; n++; }
+                }
+                master[y * MW + x] = (uint8_t)(s / n);
+            }
+    }
+    sm_state = noiseSeed;
+    img.resize((size_t)w * h);
+    for (int y = 0; y < h; y++)
+        for (int x = 0; x < w; x++) {
+            int v = master[(y + dy) * MW + x + dx] + (int)((splitmix() >> 56) % 7) - 3;
+            img[(size_t)y * w + x] = (uint8_t)(v < 0 ? 0 : v > 255 ? 255 : v);
+        }
+}
+
+using namespace ORB_SLAM;
+
+int main() {
+    const int W = 640, H = 480;
+    std::vector<uint8_t> im1, im2;
+    make_frame(im1, W, H, 10, 8, 1);
+    make_frame(im2, W, H, 13, 9, 2);
+
+    // ---- extraction
+    ORBextractor ex(1000, 1.2f, 8, ORBextractor::FAST_SCORE, 20);
+    oracle::ORBextractor oex(1000, 1.2f, 8, oracle::FAST_SCORE, 20);
+    std::vector<gforb_cv::KeyPoint> k1, k2;
+    gforb_cv::Mat d1, d2, mask;
+    ex(gforb_cv::Mat(H, W, im1.data(), W), mask, k1, d1);
+    ex(gforb_cv::Mat(H, W, im2.data(), W), mask, k2, d2);
+    std::vector<oracle::KeyPoint> ok1, ok2;
+    std::vector<uint8_t> od1, od2;
+    CHECK(oex(im1.data(), W, H, W, ok1, od1) == 0, "oracle extract 1");
+    CHECK(oex(im2.data(), W, H, W, ok2, od2) == 0, "oracle extract 2");
+    CHECK(k1.size() == ok1.size() && k2.size() == ok2.size(), "keypoint counts %zu/%zu %zu/%zu", k1.size(), ok1.size(), k2.size(), ok2.size());
+    CHECK(k1.size() > 500, "too few keypoints: %zu", k1.size());
+    if (k1.size() == ok1.size()) {
+        CHECK(std::memcmp(k1.data(), ok1.data(), k1.size() * 28) == 0, "keypoints differ");
+        bool same = true;
+        for (size_t i = 0; i < k1.size(); i++) same = same && std::memcmp(d1.ptr((int)i), &od1[i * 32], 32) == 0;
+        CHECK(same, "descriptors differ");
+    }
+    { gforb_cv::Mat e; std::vector<gforb_cv::KeyPoint> ke(3); ex(gforb_cv::Mat(), mask, ke, e); CHECK(ke.size() == 3, "empty image must return silently"); }
+
+    // ---- matching
+    ORBmatcher m(0.9f, true);
+    oracle::ORBmatcher om(0.9f, true);
+    Frame F1(k1, d1, W, H), F2(k2, d2, W, H);
+    oracle::Frame oF1, oF2;
+    oF1.init(ok1.data(), od1.data(), (int)ok1.size(), W, H, 8, 1.2f);
+    oF2.init(ok2.data(), od2.data(), (int)ok2.size(), W, H, 8, 1.2f);
+    std::vector<gforb_cv::Point2f> prev(F1.N);
+    std::vector<float> oprev((size_t)F1.N * 2);
+    for (int i = 0; i < F1.N; i++) { prev[i] = k1[i].pt; oprev[2 * i] = k1[i].pt.x; oprev[2 * i + 1] = k1[i].pt.y; }
+    std::vector<int> m12, om12;
+    const int nm = m.SearchForInitialization(F1, F2, prev, m12, 100);
+    const int onm = om.SearchForInitialization(oF1, oF2, oprev, om12, 100);
+    CHECK(nm == onm && m12 == om12, "SearchForInitialization: %d vs %d matches", nm, onm);
+    CHECK(nm > 20, "too few matches: %d", nm);
+    bool prevSame = true;
+    for (int i = 0; i < F1.N; i++) prevSame = prevSame && prev[i].x == oprev[2 * i] && prev[i].y == oprev[2 * i + 1];
+    CHECK(prevSame, "vbPrevMatched differs");
+    CHECK(m.DescriptorDistance(d1.row(0), d2.row(0)) == oracle::ORBmatcher::DescriptorDistance(&od1[0], &od2[0]), "DescriptorDistance");
+
+    // SearchByProjection(F, map points): project frame-1 keypoints (jittered) into frame 2
+    std::vector<MapPoint> mps(F1.N);
+    std::vector<MapPoint*> vp(F1.N);
+    std::vector<oracle::MapPointView> omp(F1.N);
+    sm_state = 77;
+    for (int i = 0; i < F1.N; i++) {
+        MapPoint& p = mps[i];
+        p.mTrackProjX = k1[i].pt.x - 3.0f + (float)(splitmix() % 5) - 2.0f;
+        p.mTrackProjY = k1[i].pt.y - 1.0f + (float)(splitmix() % 5) - 2.0f;
+        p.mnTrackScaleLevel = k1[i].octave;
+        p.mTrackViewCos = (splitmix() & 1) ? 0.999f : 0.9f;
+        p.mbTrackInView = (splitmix() % 10) != 0;
+        p.mbBad = (splitmix() % 20) == 0;
+        std::memcpy(p.mDescriptor, d1.ptr(i), 32);
+        vp[i] = &p;
+        oracle::MapPointView& o = omp[i];
+        o.mTrackProjX = p.mTrackProjX; o.mTrackProjY = p.mTrackProjY; o.mnTrackScaleLevel = p.mnTrackScaleLevel;
+        o.mTrackViewCos = p.mTrackViewCos; o.mbTrackInView = p.mbTrackInView; o.isBad = p.mbBad;
+        std::memcpy(o.desc, p.mDescriptor, 32);
+    }
+    const int np = m.SearchByProjection(F2, vp, 3.0f);
+    const int onp = om.SearchByProjection(oF2, omp, 3.0f);
+    CHECK(np == onp, "SearchByProjection: %d vs %d", np, onp);
+    bool assoc = true;
+    for (int i = 0; i < F2.N; i++) {
+        const int id = F2.mvpMapPoints[i] ? (int)(F2.mvpMapPoints[i] - &mps[0]) : -1;
+        assoc = assoc && id == oF2.mvpMapPoints[i] && F2.mvpMatchScore[i] == oF2.mvpMatchScore[i];
+    }
+    CHECK(assoc, "SearchByProjection associations differ");
+    CHECK(np > 50, "too few projection matches: %d", np);
+
+    // ---- good-feature selection on the matched frame (tools/simu_greedy.cc camera)
+    const double f = 5.1369248, dxy = 0.01123325985;
+    Observability ob(f, 480, 752, 367.215, 248.375, 0.0, 0.0, dxy, dxy);
+    oracle::Observability oob(f, 480, 752, 367.215, 248.375, 0.0, 0.0, dxy, dxy);
+    const double Xv[13] = {0.3, -0.1, 1.0, 0.9992, 0.0131, 0.0314, -0.0209, 3.0, -1.0, 10.0, 0.2618, 0.6283, -0.4189};
+    ob.setState(Xv); ob.predictPWLSVec(0.1, 1);
+    std::memcpy(oob.Xv, Xv, sizeof(Xv)); oob.predictPWLSVec(0.1, 1);
+    sm_state = 99;
+    const int n2 = F2.N;
+    std::vector<float> world((size_t)n2 * 3);
+    std::vector<int> oct(n2), sc(n2);
+    std::vector<uint8_t> valid(n2, 0);
+    for (int i = 0; i < n2; i++) {
+        MapPoint* p = F2.mvpMapPoints[i];
+        if (!p) continue;
+        p->mWorldPos[0] = (float)((splitmix() >> 11) * (1.0 / 9007199254740992.0) * 4.0 - 2.0);
+        p->mWorldPos[1] = (float)((splitmix() >> 11) * (1.0 / 9007199254740992.0) * 4.0 - 2.0);
+        p->mWorldPos[2] = (float)((splitmix() >> 11) * (1.0 / 9007199254740992.0) * 6.0 + 4.0);
+        std::memcpy(&world[(size_t)i * 3], p->mWorldPos, 12);
+        valid[i] = 1;
+    }
+    for (int i = 0; i < n2; i++) { oct[i] = k2[i].octave; sc[i] = F2.mvpMatchScore[i]; }
+    std::vector<GoodPoint> good;
+    const size_t K = 40;
+    CHECK(ob.setSelction_Number(K, 2, 1.0, 0.1, &F2, &good), "setSelction_Number failed");
+    // oracle: same pool
+    std::vector<double> blocks((size_t)n2 * 49), oscore(n2);
+    oob.batchInfoMat_Frame(world.data(), oct.data(), sc.data(), valid.data(), n2, F2.mvLevelSigma2.data(), blocks.data(), oscore.data(), nullptr);
+    std::vector<int> pool;
+    for (int i = 0; i < n2; i++)
+        if (oscore[i] >= 0) {
+            oracle::GoodPoint g; g.idx = i; g.obs_score = oscore[i]; g.selected = false; g.upper_bound = 0;
+            std::memcpy(g.obs_block, &blocks[(size_t)i * 49], sizeof(g.obs_block));
+            oob.lmkSelectPool.push_back(g); pool.push_back(i);
+        }
+    const double sampleScale = (double)(size_t)((float)n2 / (float)K * std::log(1.0 / 0.1));
+    std::vector<oracle::GoodPoint> ogood;
+    srand(1);
+    oob.maxVolSelection_LazierGreedy(0, oob.lmkSelectPool.size(), &ogood, K, sampleScale, 1e9);
+    CHECK(good.size() == ogood.size() && good.size() == K, "selected %zu vs %zu (pool %zu)", good.size(), ogood.size(), pool.size());
+    bool subset = good.size() == ogood.size(), ldok = subset;
+    for (size_t t = 0; subset && t < good.size(); t++) {
+        subset = good[t].idx == ogood[t].idx;
+        ldok = ldok && std::fabs(good[t].upper_bound - ogood[t].upper_bound) <= 1e-5 * std::fabs(ogood[t].upper_bound);
+    }
+    CHECK(subset, "good-feature subset differs");
+    CHECK(ldok, "log-det trajectory differs by more than 1e-5 relative");
+
+    printf("shim test: %zu/%zu keypoints, %d init matches, %d projection matches, %zu good features: %s\n", k1.size(),
+           k2.size(), nm, np, good.size(), g_fail ? "FAILED" : "OK");
+    return g_fail ? 1 : 0;
+}
