@@ -9,10 +9,10 @@
 //
 // k_fast_nms: one warp per strip of 120 output columns x up to 64 output rows.  Lane l owns the 4 pixels
 // x = X0 - 4 + 4 l .. +3 (two u16x2 pairs A, B); lanes 0 and 31 only provide the horizontal NMS halo.  Each input row is
-// read ONCE per strip (one coalesced 32-bit load per lane, neighbours' words by shuffle), split into even/odd bytes
-// (zero-extended u16x2) and kept in a 7-row register window that rolls down the strip; every FAST ring pair is then a
-// single PRMT, the 16 arcs are reduced with VIMNMX3.U16x2 (80 ops per pixel pair), and the NMS runs on the packed scores
-// of the last three rows.  Output: u8 map of surviving scores (0 elsewhere) in the blur plane (overwritten later by K5).
+// read ONCE per strip (one coalesced 32-bit load per lane, neighbours' words by shuffle), expanded ONCE into its nine
+// zero-extended u16x2 pixel pairs and kept in a 7-row register window that rolls down the strip; the FAST ring pairs are
+// window registers, the 16 arcs are reduced with packed u16x2 min/max (VIMNMX, 94 two-input equivalents per pixel pair),
+// and the NMS runs on the packed scores of the last three rows.  Output: u8 map of surviving scores (0 elsewhere) in the blur plane (overwritten later by K5).
 #pragma once
 
 namespace gforb {
@@ -21,56 +21,61 @@ static const int FN_OUTW = 120;          // output columns per strip (lanes 1..3
 static const int FN_ROWS = 64;           // output rows per strip
 static const int FN_WARPS = 4;           // warps (strips) per CTA
 
-struct FnWin {                           // 7-row rolling window: even / odd bytes of the 3 words around the lane
-    uint32_t E[7][3], O[7][3];
+// 7-row rolling window.  A row enters as the nine zero-extended u16x2 pairs {byte K, byte K+1}, K = 1..9, of the
+// lane's 12-byte window (bytes 0..3 = left word, 4..7 = own word, 8..11 = right word): every FAST ring pair of both
+// pixel pairs (A = bytes 4,5; B = bytes 6,7) is one of them, so the arc network reads the window registers directly.
+struct FnWin {
+    uint32_t P[7][9];
 };
 
-// u16x2 {byte K, byte K+1} of the 12-byte window (K = 0..10), from the even/odd split words
-template <int K>
-__device__ __forceinline__ uint32_t fn_pair(const uint32_t (&E)[3], const uint32_t (&O)[3]) {
-    constexpr int j = K >> 2, q = K & 3;
-    if (q == 0) return __byte_perm(E[j], O[j], 0x5410);
-    if (q == 1) return __byte_perm(E[j], O[j], 0x3254);
-    if (q == 2) return __byte_perm(E[j], O[j], 0x7632);
-    return __byte_perm(O[j], E[j < 2 ? j + 1 : 2], 0x5432);
+__device__ __forceinline__ void fn_row_pairs(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t (&P)[9]) {
+    P[0] = __byte_perm(w0, 0, 0x4241);                       // K=1: {b1, b2}
+    P[1] = __byte_perm(w0, 0, 0x4342);                       // K=2: {b2, b3}
+    P[2] = __byte_perm(w0, w1, 0x0403) & 0x00ff00ffu;        // K=3: {b3, b4}
+    P[3] = __byte_perm(w1, 0, 0x4140);                       // K=4: {b4, b5}
+    P[4] = __byte_perm(w1, 0, 0x4241);                       // K=5
+    P[5] = __byte_perm(w1, 0, 0x4342);                       // K=6
+    P[6] = __byte_perm(w1, w2, 0x0403) & 0x00ff00ffu;        // K=7: {b7, b8}
+    P[7] = __byte_perm(w2, 0, 0x4140);                       // K=8
+    P[8] = __byte_perm(w2, 0, 0x4241);                       // K=9
 }
 
-// packed corner strength of the pixel pair whose first byte is window column C, centre row = window slot (S0+3)%7:
-// returns max(v - M1, M2 - v) = score + 1 per half (0 when not a corner at any threshold)
+// packed corner strength of the pixel pair whose first byte is window column C (4 or 6), centre row = window slot
+// (S0+3)%7: returns max(v - M1, M2 - v) = score + 1 per half (0 when not a corner at any threshold), with
+// M2 = max over the 16 arcs of the arc minimum, M1 = min over arcs of the arc maximum.
+// Arc network: the arcs starting at k and k+1 (k even) share the 8 pixels k+1..k+8, so
+//   max(min9(k), min9(k+1)) = min(min8(k+1), max(p[k], p[k+9])),  min8(k+1) = min(m4[k+1], m4[k+5]),
+// with m4[j] = min(m2[j], m2[j+2]), m2[j] = min(p[j], p[j+1]) for odd j: 47 two-input min/max per polarity
+// (instead of 79 for the straightforward sliding-window form).
 template <int C, int S0>
 __device__ __forceinline__ uint32_t fn_strength(const FnWin& W) {
-#define FN_ROW(d) W.E[(S0 + 3 + (d)) % 7], W.O[(S0 + 3 + (d)) % 7]
-    uint32_t p[16];
-    p[0] = fn_pair<C>(FN_ROW(3));      p[1] = fn_pair<C + 1>(FN_ROW(3));   p[2] = fn_pair<C + 2>(FN_ROW(2));
-    p[3] = fn_pair<C + 3>(FN_ROW(1));  p[4] = fn_pair<C + 3>(FN_ROW(0));   p[5] = fn_pair<C + 3>(FN_ROW(-1));
-    p[6] = fn_pair<C + 2>(FN_ROW(-2)); p[7] = fn_pair<C + 1>(FN_ROW(-3));  p[8] = fn_pair<C>(FN_ROW(-3));
-    p[9] = fn_pair<C - 1>(FN_ROW(-3)); p[10] = fn_pair<C - 2>(FN_ROW(-2)); p[11] = fn_pair<C - 3>(FN_ROW(-1));
-    p[12] = fn_pair<C - 3>(FN_ROW(0)); p[13] = fn_pair<C - 3>(FN_ROW(1));  p[14] = fn_pair<C - 2>(FN_ROW(2));
-    p[15] = fn_pair<C - 1>(FN_ROW(3));
-    const uint32_t v = fn_pair<C>(FN_ROW(0));
-#undef FN_ROW
-    uint32_t mn3[16], mx3[16];
+#define FN_P(d, dx) W.P[(S0 + 3 + (d)) % 7][C + (dx) - 1]
+    const uint32_t p[16] = {FN_P(3, 0),  FN_P(3, 1),   FN_P(2, 2),   FN_P(1, 3),  FN_P(0, 3),  FN_P(-1, 3), FN_P(-2, 2), FN_P(-3, 1),
+                            FN_P(-3, 0), FN_P(-3, -1), FN_P(-2, -2), FN_P(-1, -3), FN_P(0, -3), FN_P(1, -3), FN_P(2, -2), FN_P(3, -1)};
+    const uint32_t v = FN_P(0, 0);
+#undef FN_P
+    uint32_t m2n[8], m2x[8], m4n[8], m4x[8], cn[8], cx[8];      // index q <-> odd position j = 2q + 1
 #pragma unroll
-    for (int i = 0; i < 16; i++) {
-        mn3[i] = __vimin3_u16x2(p[i], p[(i + 1) & 15], p[(i + 2) & 15]);
-        mx3[i] = __vimax3_u16x2(p[i], p[(i + 1) & 15], p[(i + 2) & 15]);
+    for (int q = 0; q < 8; q++) {
+        m2n[q] = __vminu2(p[2 * q + 1], p[(2 * q + 2) & 15]);
+        m2x[q] = __vmaxu2(p[2 * q + 1], p[(2 * q + 2) & 15]);
     }
-    uint32_t mn9[16], mx9[16];
 #pragma unroll
-    for (int i = 0; i < 16; i++) {
-        mn9[i] = __vimin3_u16x2(mn3[i], mn3[(i + 3) & 15], mn3[(i + 6) & 15]);
-        mx9[i] = __vimax3_u16x2(mx3[i], mx3[(i + 3) & 15], mx3[(i + 6) & 15]);
+    for (int q = 0; q < 8; q++) {
+        m4n[q] = __vminu2(m2n[q], m2n[(q + 1) & 7]);
+        m4x[q] = __vmaxu2(m2x[q], m2x[(q + 1) & 7]);
     }
-    // M2 = max over arcs of the arc minimum, M1 = min over arcs of the arc maximum (3-input trees: 8 ops each)
-    uint32_t a[6], b[6];
 #pragma unroll
-    for (int i = 0; i < 5; i++) {
-        a[i] = __vimax3_u16x2(mn9[3 * i], mn9[3 * i + 1], mn9[3 * i + 2]);
-        b[i] = __vimin3_u16x2(mx9[3 * i], mx9[3 * i + 1], mx9[3 * i + 2]);
+    for (int h = 0; h < 8; h++) {                                 // k = 2h: m4[k+1] = index h, m4[k+5] = index h+2
+        const uint32_t tn = __vmaxu2(p[2 * h], p[(2 * h + 9) & 15]);
+        const uint32_t tx = __vminu2(p[2 * h], p[(2 * h + 9) & 15]);
+        cn[h] = __vimin3_u16x2(m4n[h], m4n[(h + 2) & 7], tn);
+        cx[h] = __vimax3_u16x2(m4x[h], m4x[(h + 2) & 7], tx);
     }
-    a[5] = mn9[15]; b[5] = mx9[15];
-    const uint32_t M2 = __vmaxu2(__vimax3_u16x2(a[0], a[1], a[2]), __vimax3_u16x2(a[3], a[4], a[5]));
-    const uint32_t M1 = __vminu2(__vimin3_u16x2(b[0], b[1], b[2]), __vimin3_u16x2(b[3], b[4], b[5]));
+    const uint32_t M2 = __vmaxu2(__vimax3_u16x2(cn[0], cn[1], cn[2]),
+                                 __vimax3_u16x2(cn[3], cn[4], __vimax3_u16x2(cn[5], cn[6], cn[7])));
+    const uint32_t M1 = __vminu2(__vimin3_u16x2(cx[0], cx[1], cx[2]),
+                                 __vimin3_u16x2(cx[3], cx[4], __vimin3_u16x2(cx[5], cx[6], cx[7])));
     // halves hold 0..255, so plain 32-bit subtraction of (max(x, y) - y) never borrows across halves
     const uint32_t d1 = __vmaxu2(v, M1) - M1, d2 = __vmaxu2(M2, v) - v;
     return __vmaxu2(d1, d2);
@@ -144,9 +149,7 @@ __global__ void __launch_bounds__(FN_WARPS * 32) k_fast_nms(const uint8_t* __res
         uint32_t w0 = __shfl_up_sync(full, w1, 1), w2 = __shfl_down_sync(full, w1, 1);
         if (lane == 0) w0 = hw;
         if (lane == 31) w2 = hw;
-        W.E[PH][0] = w0 & 0x00ff00ffu; W.O[PH][0] = __byte_perm(w0, 0, 0x4341);
-        W.E[PH][1] = w1 & 0x00ff00ffu; W.O[PH][1] = __byte_perm(w1, 0, 0x4341);
-        W.E[PH][2] = w2 & 0x00ff00ffu; W.O[PH][2] = __byte_perm(w2, 0, 0x4341);
+        fn_row_pairs(w0, w1, w2, W.P[PH]);
         if (R < Y0 + 2) return;
         // ---- strength of row c = R - 3: window rows c-3 .. c+3 sit in slots (PH+1) .. (PH+7) mod 7
         const int c = R - 3;
