@@ -20,6 +20,12 @@ namespace gforb {
 static const int FN_OUTW = 120;          // output columns per strip (lanes 1..30)
 static const int FN_ROWS = 64;           // output rows per strip
 static const int FN_WARPS = 4;           // warps (strips) per CTA
+#ifndef FN_QD
+#define FN_QD 1                          // prefetch depth in rows (1 or 7: must divide the 7-phase unroll)
+#endif
+#ifndef FN_MINB
+#define FN_MINB 4                        // resident CTAs per SM the register budget is capped for
+#endif
 
 // 7-row rolling window.  A row enters as the nine zero-extended u16x2 pairs {byte K, byte K+1}, K = 1..9, of the
 // lane's 12-byte window (bytes 0..3 = left word, 4..7 = own word, 8..11 = right word): every FAST ring pair of both
@@ -88,7 +94,7 @@ struct FnNms {                            // packed NMS state of pairs A and B f
     uint32_t h3A_pp, h3B_pp;              // ... of row c-2
 };
 
-__global__ void __launch_bounds__(FN_WARPS * 32) k_fast_nms(const uint8_t* __restrict__ pyr, uint8_t* __restrict__ smap,
+__global__ void __launch_bounds__(FN_WARPS * 32, FN_MINB) k_fast_nms(const uint8_t* __restrict__ pyr, uint8_t* __restrict__ smap,
                                                             size_t framePyr, const LevelPlan* __restrict__ levels,
                                                             int nLevels, int tasksPerFrame, int minTh) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -130,22 +136,28 @@ __global__ void __launch_bounds__(FN_WARPS * 32) k_fast_nms(const uint8_t* __res
     S.uA = S.uB = S.hmA = S.hmB = S.h3A_p = S.h3B_p = S.h3A_pp = S.h3B_pp = 0u;
     const int Rend = Y1 + 3;
     const uint8_t* lp = roi + (ptrdiff_t)(Y0 - 4) * L.pitch + xl;        // this lane's word of input row R
-    uint32_t nw1 = __ldg(reinterpret_cast<const uint32_t*>(lp));
-    // halo word (lane 0: left of its word, lane 31: right), prefetched with the lane's own word
-    // (unconditional on every lane: a predicated load would make the compiler copy the register right after the load
-    // and expose the full memory latency; the inner lanes' halo word is an L1 hit on a neighbour's word)
+    // Prefetch queue, 7 rows deep (one slot per unrolled phase, so every slot is a fixed register that is consumed
+    // directly, never copied while its load is in flight): slot PH holds the lane's word and its halo word (lane 0:
+    // the word to the left, lane 31: to the right; loaded unconditionally on every lane -- an L1 hit on a neighbour's
+    // word -- because a predicated load makes the compiler copy the register right after the load).
+    // Rows up to Rend + 13 <= h are inside the bordered plane (16 ring rows below the ROI), so no guard is needed.
     const int hoff = lane < 16 ? -4 : 4;
-    uint32_t nh = __ldg(reinterpret_cast<const uint32_t*>(lp + hoff));
+    uint32_t qw[FN_QD], qh[FN_QD];
+#pragma unroll
+    for (int i = 0; i < FN_QD; i++) {
+        qw[i] = __ldg(reinterpret_cast<const uint32_t*>(lp + (ptrdiff_t)i * L.pitch));
+        qh[i] = __ldg(reinterpret_cast<const uint32_t*>(lp + (ptrdiff_t)i * L.pitch + hoff));
+    }
+    lp += (ptrdiff_t)FN_QD * L.pitch;                                     // next row to prefetch
     int cyN = (Y0 - EDGE) % L.cellH;                                      // (n - 16) mod cellH of the next NMS row n
 
     auto phase = [&](auto PHc, int R) {
         constexpr int PH = decltype(PHc)::value;
-        // ---- row R enters slot PH (its words were prefetched); prefetch row R + 1
-        const uint32_t w1 = nw1, hw = nh;
+        // ---- row R enters window slot PH (its words were prefetched 7 phases ago); prefetch row R + 7
+        const uint32_t w1 = qw[PH % FN_QD], hw = qh[PH % FN_QD];
+        qw[PH % FN_QD] = __ldg(reinterpret_cast<const uint32_t*>(lp));
+        qh[PH % FN_QD] = __ldg(reinterpret_cast<const uint32_t*>(lp + hoff));
         lp += L.pitch;
-        // (row Rend + 1 <= h - 12 is still inside the bordered plane, so the last prefetch needs no guard)
-        nw1 = __ldg(reinterpret_cast<const uint32_t*>(lp));
-        nh = __ldg(reinterpret_cast<const uint32_t*>(lp + hoff));
         uint32_t w0 = __shfl_up_sync(full, w1, 1), w2 = __shfl_down_sync(full, w1, 1);
         if (lane == 0) w0 = hw;
         if (lane == 31) w2 = hw;
@@ -173,20 +185,23 @@ __global__ void __launch_bounds__(FN_WARPS * 32) k_fast_nms(const uint8_t* __res
             const uint32_t fA = (((kA + 0x7fff7fffu) >> 15) & 0x00010001u) * 0xffffu;
             const uint32_t fB = (((kB + 0x7fff7fffu) >> 15) & 0x00010001u) * 0xffffu;
             const uint32_t oA = (S.uA + TM1) & fA, oB = (S.uB + TM1) & fB;
-            if (writer) *reinterpret_cast<uint32_t*>(oroi + (ptrdiff_t)n * L.pitch + xl) = __byte_perm(oA, oB, 0x6420);
+            if (writer && n < Y1) *reinterpret_cast<uint32_t*>(oroi + (ptrdiff_t)n * L.pitch + xl) = __byte_perm(oA, oB, 0x6420);
             cyN = (cyN + 1 == L.cellH) ? 0 : cyN + 1;
         }
         S.h3A_pp = S.h3A_p; S.h3B_pp = S.h3B_p; S.h3A_p = h3A; S.h3B_p = h3B;
         S.uA = uA; S.uB = uB; S.hmA = hmA; S.hmB = hmB;
     };
+    // Whole groups of 7 phases, no per-phase guard (a conditional phase turns every window / queue register into a phi
+    // and the compiler then copies freshly loaded registers, stalling on the load): up to 6 surplus rows past Rend are
+    // processed and discarded (their NMS rows n >= Y1 are not stored; rows read stay <= h, inside the bordered plane).
     for (int R = Y0 - 4; R <= Rend; R += 7) {
         phase(std::integral_constant<int, 0>(), R);
-        if (R + 1 <= Rend) phase(std::integral_constant<int, 1>(), R + 1);
-        if (R + 2 <= Rend) phase(std::integral_constant<int, 2>(), R + 2);
-        if (R + 3 <= Rend) phase(std::integral_constant<int, 3>(), R + 3);
-        if (R + 4 <= Rend) phase(std::integral_constant<int, 4>(), R + 4);
-        if (R + 5 <= Rend) phase(std::integral_constant<int, 5>(), R + 5);
-        if (R + 6 <= Rend) phase(std::integral_constant<int, 6>(), R + 6);
+        phase(std::integral_constant<int, 1>(), R + 1);
+        phase(std::integral_constant<int, 2>(), R + 2);
+        phase(std::integral_constant<int, 3>(), R + 3);
+        phase(std::integral_constant<int, 4>(), R + 4);
+        phase(std::integral_constant<int, 5>(), R + 5);
+        phase(std::integral_constant<int, 6>(), R + 6);
     }
 }
 
