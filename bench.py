@@ -154,7 +154,7 @@ def run_ours(args):
     from gf_orb_slam_b200 import synth
     from gf_orb_slam_b200.pipeline import TrackingFrontEnd
     B = args.batch
-    fe = TrackingFrontEnd(W_, H_, NFEAT, B, n_good=NGOOD, device=local)
+    fe = TrackingFrontEnd(W_, H_, NFEAT, B, n_good=NGOOD, device=local, overlap=not args.no_overlap)
     # frames sharded across ranks: rank r takes a contiguous chunk of the 2000-frame schedule (1-frame halo inside)
     seq = synth.Sequence(W_, H_)
     chunk = 2000 // max(world_size, 1)
@@ -178,6 +178,7 @@ def run_ours(args):
         e0.record()
         for _ in range(steps):
             fn()
+        fe.sync()            # the main stream joins the selection and copy streams before the closing event
         e1.record()
         barrier()
         ms = e0.elapsed_time(e1)
@@ -262,6 +263,7 @@ def main():
     ap.add_argument("--cpu-frames", type=int, default=128, help="frames of the cpu_baseline sample")
     ap.add_argument("--ref-frames", type=int, default=32, help="frames per step of the --impl reference arm")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-overlap", action="store_true", help="run the good-feature selection on the main stream")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -17,6 +17,7 @@
 // last ulp (north_star tolerance on log-det scores: 1e-5 relative).
 #include <cfloat>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 #include "common.cuh"
@@ -542,6 +543,7 @@ struct KineSeg {
 struct GforbObs {
     GforbObsConfig cfg;
     int device = 0, lastLaunches = 0;
+    int selPad = 0;          // extra dynamic smem of k_select (GFORB_SELECT_SMEM_PAD): caps its CTAs per SM when it shares the GPU
     double Xv[13];
     std::vector<KineSeg> kine;
     Arena arena;
@@ -745,7 +747,8 @@ int gforb_obs_create(const GforbObsConfig* cfg, GforbObs** out) {
     // staging for host-pointer calls: world/octave/score/gate in, blocks + H + scores + uv + selection out
     GF_CUDA_OK(O->arena.init(B * N * (12 + 4 + 4 + 1 + 392 + 112 + 8 + 8 + 4 + 8 + 64) + B * 256 + (1u << 20)));
     GF_CUDA_OK(cudaMalloc((void**)&O->d_err, sizeof(int)));
-    GF_CUDA_OK(cudaFuncSetAttribute(k_select, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)select_smem(cfg->max_points)));
+    if (const char* e = getenv("GFORB_SELECT_SMEM_PAD")) O->selPad = atoi(e);
+    GF_CUDA_OK(cudaFuncSetAttribute(k_select, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)select_smem(cfg->max_points) + O->selPad));
     *out = O;
     return GFORB_OK;
 }
@@ -933,7 +936,7 @@ int gforb_obs_select(GforbObs* O, const double* blocks, const double* obs_score,
     P.outN = c.out(out_n, (size_t)batch);
     P.outStride = out_stride;
     if (c.rc) return c.rc;
-    k_select<<<batch, SEL_THREADS, select_smem(O->cfg.max_points), c.st>>>(P);
+    k_select<<<batch, SEL_THREADS, select_smem(O->cfg.max_points) + O->selPad, c.st>>>(P);
     O->lastLaunches = 1;
     return obs_end(O, c, flags);
 }

@@ -21,7 +21,7 @@ from .pipeline_consts import (EUROC_CAM, SIMU_XV, level_sigma2, level_sizes, sam
 
 class TrackingFrontEnd:
     def __init__(self, width=752, height=480, nfeatures=1000, batch=64, *, n_good=100, error_bound=0.1, window=100,
-                 nnratio=0.9, device=0, cloud_seed=7):
+                 nnratio=0.9, device=0, cloud_seed=7, overlap=True):
         self.w, self.h, self.nf, self.B, self.k = width, height, nfeatures, batch, n_good
         self.window = window
         self.dev = torch.device("cuda", device)
@@ -32,6 +32,7 @@ class TrackingFrontEnd:
                                   cand_pool=48 * nfeatures, device=device)
         cam = dict(EUROC_CAM); cam["nRows"], cam["nCols"] = height, width
         self.obs = Observability(**cam, max_batch=batch, max_points=nfeatures, device=device)
+        self.obs_sel = Observability(**cam, max_batch=batch, max_points=nfeatures, device=device)   # handle used on s_sel
         self.obs.set_state(SIMU_XV)
         self.obs.predictPWLSVec(0.1, 1)
         xv = self.obs.kinematic(0)["Xv"]
@@ -55,11 +56,25 @@ class TrackingFrontEnd:
         self.xv_h = xv
         self.sigma2_h = level_sigma2()
         self.sigma2 = torch.from_numpy(self.sigma2_h).to(self.dev)
-        self.blocks = z(B, nf, 49, dt=torch.float64)
-        self.obs_score = z(B, nf, dt=torch.float64)
-        self.sel_idx = z(B, n_good, dt=torch.int32)
-        self.sel_ld = z(B, n_good, dt=torch.float64)
-        self.sel_n = z(B, dt=torch.int32)
+        # the selection runs on its own stream one step behind the extractor: its inputs and outputs are double-buffered
+        self.blocks2 = [z(B, nf, 49, dt=torch.float64) for _ in range(2)]
+        self.obs_score2 = [z(B, nf, dt=torch.float64) for _ in range(2)]
+        self.cnt_sel2 = [z(B, dt=torch.int32) for _ in range(2)]
+        self.sel_idx2 = [z(B, n_good, dt=torch.int32) for _ in range(2)]
+        self.sel_ld2 = [z(B, n_good, dt=torch.float64) for _ in range(2)]
+        self.sel_n2 = [z(B, dt=torch.int32) for _ in range(2)]
+        self.overlap = overlap
+        self.s_sel = torch.cuda.Stream(device=self.dev) if overlap else None
+        self.s_copy = torch.cuda.Stream(device=self.dev)
+        self.ev_info = [torch.cuda.Event() for _ in range(2)]
+        self.ev_sel = [torch.cuda.Event() for _ in range(2)]
+        self.ev_h2d = [torch.cuda.Event() for _ in range(2)]
+        self.ev_ext = [torch.cuda.Event() for _ in range(2)]
+        self.ev_out = torch.cuda.Event()
+        self.ev_d2h = torch.cuda.Event()
+        self.ev_d2h_sel = [torch.cuda.Event() for _ in range(2)]
+        self.t = 0                          # steps issued
+        self.images2 = [self.images, z(B, height, width, dt=torch.uint8)]
         self.seeds = torch.ones(B, dtype=torch.int32, device=self.dev)
         self.F1 = Frames(self.kps[:B], self.desc[:B], self.counts[:B], width, height)
         self.F2 = Frames(self.kps[1:], self.desc[1:], self.counts[1:], width, height)
@@ -76,6 +91,7 @@ class TrackingFrontEnd:
         self.h_nmatch = torch.zeros(B, dtype=torch.int32).pin_memory()
         self.h_sel_idx = torch.zeros((B, n_good), dtype=torch.int32).pin_memory()
         self.h_sel_n = torch.zeros(B, dtype=torch.int32).pin_memory()
+        self._uploaded = False
 
     # ---- one step = one batch of B frames through the whole front end, everything resident in HBM
     def _mark(self, name=None):
@@ -88,9 +104,35 @@ class TrackingFrontEnd:
             self._ev.append((self._open[0], self._open[1], e))
         self._open = (name, e) if name else None
 
+    # the buffers of the most recently issued step (valid after sync())
+    @property
+    def blocks(self): return self.blocks2[(self.t - 1) & 1]
+    @property
+    def obs_score(self): return self.obs_score2[(self.t - 1) & 1]
+    @property
+    def sel_idx(self): return self.sel_idx2[(self.t - 1) & 1]
+    @property
+    def sel_ld(self): return self.sel_ld2[(self.t - 1) & 1]
+    @property
+    def sel_n(self): return self.sel_n2[(self.t - 1) & 1]
+
+    def sync(self):
+        """main stream waits for everything issued so far (selection stream, copy stream)"""
+        cur = torch.cuda.current_stream()
+        if self.s_sel is not None:
+            for e in self.ev_sel:
+                cur.wait_event(e)
+        cur.wait_event(self.ev_d2h)
+        for e in self.ev_d2h_sel:
+            cur.wait_event(e)
+
     def step_device(self, images: torch.Tensor | None = None):
+        """extract -> match -> info on the current stream; the good-feature selection of this step on s_sel, where it
+        overlaps the extraction of the next step (it is a latency-bound kernel that leaves the ALU pipe idle)"""
         B = self.B
-        st = torch.cuda.current_stream().cuda_stream
+        main = torch.cuda.current_stream()
+        st = main.cuda_stream
+        p = self.t & 1
         img = self.images if images is None else images
         self._open = None
         self._mark("extract")
@@ -104,16 +146,30 @@ class TrackingFrontEnd:
                                              nmatches=self.nmatch, stream=st, sync=False)
         n += self.matcher.last_launches()
         self._mark("info")
+        if self.s_sel is not None:
+            main.wait_event(self.ev_sel[p])                                 # selection of step t-2 has released buffer p
         self.octave.copy_(self.kps_i32[1:, :, 5])
-        self.obs.build_info_frame(self.Xv, self.world, self.octave, self.score, self.valid, self.counts[1:], self.sigma2,
-                                  blocks=self.blocks, obs_score=self.obs_score, stream=st, sync=False)
+        self.cnt_sel2[p].copy_(self.counts[1:])
+        self.obs.build_info_frame(self.Xv, self.world, self.octave, self.score, self.valid, self.cnt_sel2[p], self.sigma2,
+                                  blocks=self.blocks2[p], obs_score=self.obs_score2[p], stream=st, sync=False)
         n += self.obs.last_launches()
         self._mark("select")
-        self.obs.select(self.blocks, self.obs_score, self.counts[1:], self.k, LAZIER_GREEDY, self.sample_scale, self.seeds,
-                        out_idx=self.sel_idx, out_logdet=self.sel_ld, out_n=self.sel_n, stream=st, sync=False)
-        n += self.obs.last_launches()
+        if self.s_sel is not None:
+            self.ev_info[p].record(main)
+            self.s_sel.wait_event(self.ev_info[p])
+            self.s_sel.wait_event(self.ev_d2h_sel[p])                       # results of step t-2 have left sel_*2[p]
+            obs, sst = self.obs_sel, self.s_sel.cuda_stream
+        else:
+            main.wait_event(self.ev_d2h_sel[p])
+            obs, sst = self.obs, st
+        obs.select(self.blocks2[p], self.obs_score2[p], self.cnt_sel2[p], self.k, LAZIER_GREEDY, self.sample_scale, self.seeds,
+                   out_idx=self.sel_idx2[p], out_logdet=self.sel_ld2[p], out_n=self.sel_n2[p], stream=sst, sync=False)
+        n += obs.last_launches()
+        if self.s_sel is not None:
+            self.ev_sel[p].record(self.s_sel)
         self._mark(None)
         self.launches_per_step = n
+        self.t += 1
         return n
 
     def stage_times(self):
@@ -136,18 +192,43 @@ class TrackingFrontEnd:
                "describe": 60 * self.nf}
         return {"per_stage": per, "extract_frame": sum(per.values()), "traffic": {}}
 
-    # ---- the same step through host buffers: H2D of the frames, D2H of every result a Tracking caller consumes
-    def step_host(self):
-        B = self.B
-        self.images.copy_(self.h_images, non_blocking=True)
-        self.step_device()
-        self.h_kps.copy_(self.kps[1:], non_blocking=True)
-        self.h_desc.copy_(self.desc[1:], non_blocking=True)
-        self.h_counts.copy_(self.counts[1:], non_blocking=True)
-        self.h_m12.copy_(self.m12, non_blocking=True)
-        self.h_nmatch.copy_(self.nmatch, non_blocking=True)
-        self.h_sel_idx.copy_(self.sel_idx, non_blocking=True)
-        self.h_sel_n.copy_(self.sel_n, non_blocking=True)
+    # ---- the same step through host buffers: H2D of the frames, D2H of every result a Tracking caller consumes.
+    # Copies run on s_copy: the frames of step t+1 upload while step t computes (two device image buffers), results
+    # download while the selection runs.
+    def upload(self, q):
+        """enqueue the H2D copy of self.h_images into device image buffer q on the copy stream"""
+        self.s_copy.wait_event(self.ev_ext[q])                              # the extraction that last read buffer q is done
+        with torch.cuda.stream(self.s_copy):
+            self.images2[q].copy_(self.h_images, non_blocking=True)
+            self.ev_h2d[q].record(self.s_copy)
+
+    def step_host(self, first=False):
+        main = torch.cuda.current_stream()
+        q = self.t & 1
+        if first or not self._uploaded:
+            self.upload(q)
+        main.wait_event(self.ev_h2d[q])
+        main.wait_event(self.ev_d2h)                                        # previous results left the output buffers
+        self.step_device(self.images2[q])
+        p = (self.t - 1) & 1
+        self.ev_ext[q].record(main)            # (recorded after the whole main-stream part; extraction is its first stage)
+        self.ev_out.record(main)
+        self.upload(q ^ 1)                     # frames of the next step
+        self._uploaded = True
+        self.s_copy.wait_event(self.ev_out)
+        with torch.cuda.stream(self.s_copy):
+            self.h_kps.copy_(self.kps[1:], non_blocking=True)
+            self.h_desc.copy_(self.desc[1:], non_blocking=True)
+            self.h_counts.copy_(self.counts[1:], non_blocking=True)
+            self.h_m12.copy_(self.m12, non_blocking=True)
+            self.h_nmatch.copy_(self.nmatch, non_blocking=True)
+            self.ev_d2h.record(self.s_copy)
+        if self.s_sel is not None:
+            self.s_copy.wait_event(self.ev_sel[p])
+        with torch.cuda.stream(self.s_copy):
+            self.h_sel_idx.copy_(self.sel_idx2[p], non_blocking=True)
+            self.h_sel_n.copy_(self.sel_n2[p], non_blocking=True)
+            self.ev_d2h_sel[p].record(self.s_copy)
 
     def h2d_bytes(self) -> int:
         return self.h_images.numel()
@@ -191,6 +272,7 @@ def smoke_check(oracle, device=0, batch=3):
     for s in range(2):
         fe.images.copy_(torch.from_numpy(frames[s * batch:(s + 1) * batch]))
         fe.step_device()
+        fe.sync()
         torch.cuda.synchronize()
         res.append([t.cpu().numpy().copy() for t in (fe.kps[1:], fe.desc[1:], fe.counts[1:], fe.m12, fe.nmatch, fe.sel_idx,
                                                       fe.sel_ld, fe.sel_n)])
