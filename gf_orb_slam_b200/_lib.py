@@ -99,10 +99,12 @@ def lib() -> C.CDLL:
         L.gforb_obs_num_segments.argtypes = [vp]
         L.gforb_obs_get_segment.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp, vp]
         L.gforb_obs_build_info_frame.argtypes = [vp, vp, vp, vp, vp, vp, vp, i32, i32, vp, i32, vp, vp, vp, i32, vp]
-        L.gforb_obs_build_info_map.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp, vp, vp, i32, vp]
+        L.gforb_obs_build_info_map.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp, vp, vp, vp, i32, vp]
         L.gforb_obs_logdet.argtypes = [vp, vp, i32, vp, i32, vp]
         L.gforb_obs_rand_stream.argtypes = [vp, u32, i32, vp]
         L.gforb_obs_select.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, f64, vp, vp, vp, vp, i32, i32, vp]
+        L.gforb_obs_active_match.argtypes = [vp, vp, FS, MS, i32, vp, vp, vp, vp, vp, i32, i32, f32, f32, i32, vp, vp, vp, vp,
+                                             vp, vp, vp, i32, vp]
         _lib = L
     return _lib
 
@@ -114,7 +116,8 @@ gforb_matcher_destroy gforb_matcher_last_launches gforb_descriptor_distance gfor
 gforb_search_for_initialization gforb_search_by_projection gforb_search_by_projection_frames gforb_window_search
 gforb_allpairs_top2 gforb_top2_merge gforb_obs_create gforb_obs_destroy gforb_obs_last_launches gforb_obs_set_state
 gforb_obs_get_state gforb_obs_update_pwls gforb_obs_predict_pwls gforb_obs_num_segments gforb_obs_get_segment
-gforb_obs_build_info_frame gforb_obs_build_info_map gforb_obs_logdet gforb_obs_rand_stream gforb_obs_select""".split()
+gforb_obs_build_info_frame gforb_obs_build_info_map gforb_obs_logdet gforb_obs_rand_stream gforb_obs_select
+gforb_obs_active_match""".split()
 
 
 def check(rc: int, what: str):

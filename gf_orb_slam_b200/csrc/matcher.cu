@@ -489,6 +489,10 @@ __global__ void __launch_bounds__(32) k_resolve(const RParams R) {
     if (lane == 0) R.nmatches[b] = total;
 }
 
+}  // namespace gforb
+#include "active.cuh"
+namespace gforb {
+
 // ------------------------------------------------------------------------------------------------ B1 distance
 __global__ void __launch_bounds__(256) k_distance(const uint4* __restrict__ a, const uint4* __restrict__ b, int n,
                                                   int32_t* __restrict__ out) {
@@ -595,6 +599,7 @@ struct GforbMatcher {
     int* d_err = nullptr;
     uint64_t* d_partial = nullptr;
     size_t capPartial = 0;
+    uint8_t* d_active = nullptr;     // k_active_match scratch (allocated by the first gforb_obs_active_match call)
     std::vector<OutCopy> outs;
 };
 
@@ -751,7 +756,8 @@ int gforb_matcher_create(const GforbMatcherConfig* cfg, GforbMatcher** out) {
 int gforb_matcher_destroy(GforbMatcher* M) {
     if (!M) return GFORB_ERR_ARG;
     cudaSetDevice(M->device);
-    void* ptrs[] = {M->d_cellStart, M->d_entries, M->d_pool, M->d_poolCount, M->d_qMeta, M->d_rotBinQ, M->d_err, M->d_partial};
+    void* ptrs[] = {M->d_cellStart, M->d_entries, M->d_pool, M->d_poolCount, M->d_qMeta, M->d_rotBinQ, M->d_err, M->d_partial,
+                    M->d_active};
     for (void* p : ptrs) if (p) cudaFree(p);
     M->arena.release();
     delete M;
@@ -883,6 +889,66 @@ int gforb_search_by_projection(GforbMatcher* M, const GforbFrameSet* F, const Gf
     R.maxKp = M->cfg.max_keypoints; R.qCounts = P.mpCounts; R.nnratio = nnratio; R.checkOri = 0;
     R.tgtMp = dMp; R.tgtScore = dSc; R.nmatches = dN; R.rotBinQ = M->d_rotBinQ;
     run_resolve<M_MAP>(M, c, R, batch);
+    return end_call(M, c, flags);
+}
+
+int gforb_obs_active_match(GforbObs* O, GforbMatcher* M, const GforbFrameSet* F, const GforbMapPointSet* mps, int batch,
+                           const double* obs_score, const double* obs_mat, const double* H_meas, const double* base_info,
+                           const float* level_sigma2, int nlevels, int mat_type, float th, float nnratio, int num_to_match,
+                           const uint32_t* seeds, int32_t* frame_mappoints, int32_t* match_score, int32_t* nmatched,
+                           int32_t* left_idx, int32_t* left_n, double* out_info, int flags, void* stream) {
+    Ctx c;
+    int rc = begin_call(M, batch, flags, stream, c);
+    if (rc) return rc;
+    if (!O) return GFORB_ERR_ARG;
+    if ((rc = check_frames(M, F))) return rc;
+    if (!mps || !mps->proj_x || !mps->proj_y || !mps->scale_level || !mps->view_cos || !mps->flags || !mps->descriptors ||
+        !mps->counts || mps->mp_stride <= 0 || !frame_mappoints || !match_score || !nmatched || !left_idx || !left_n ||
+        !obs_mat || !H_meas || !base_info || !level_sigma2 || nlevels <= 0)
+        return GFORB_ERR_ARG;
+    // ORB_SLAM::MAP_INFO_MATRIX = 0, FRAME_INFO_MATRIX = 1; the hybrid types (2, 3) multiply the 2x7 Jacobian by the
+    // 13x13 kinematic F and exist only for DIMENSION_OF_STATE_MODEL = 13 (include/Observability.h:45, 94-102)
+    if (mat_type != 0 && mat_type != 1) return GFORB_ERR_ARG;
+    if (mps->mp_stride > M->cfg.max_queries) return GFORB_ERR_CAPACITY;
+    if (batch == 0) return GFORB_OK;
+    FrameDev T = c.frame(F, batch);
+    GridGeom G = geom_of(F);
+    QParams P;
+    memset(&P, 0, sizeof(P));
+    fill_scale(M, P);
+    const size_t nm = (size_t)batch * mps->mp_stride;
+    P.mpU = c.in(mps->proj_x, nm); P.mpV = c.in(mps->proj_y, nm); P.mpCos = c.in(mps->view_cos, nm);
+    P.mpLevel = c.in(mps->scale_level, nm); P.mpFlags = c.in(mps->flags, nm); P.mpDesc = c.in(mps->descriptors, nm * 32);
+    P.mpCounts = c.in(mps->counts, (size_t)batch); P.mpStride = mps->mp_stride; P.th = th;
+    AParams A;
+    memset(&A, 0, sizeof(A));
+    A.obsScore = c.in(obs_score, nm);
+    A.blocks = c.in(obs_mat, nm * 49);
+    A.Hmeas = c.in(H_meas, nm * 14);
+    A.baseInfo = c.in(base_info, (size_t)batch * 49);
+    A.levelSigma2 = c.in(level_sigma2, (size_t)nlevels);
+    A.seeds = c.in(seeds, (size_t)batch);
+    A.tgtMp = c.out(frame_mappoints, (size_t)batch * F->kp_stride, true);
+    A.tgtScore = c.out(match_score, (size_t)batch * F->kp_stride, true);
+    A.nmatched = c.out(nmatched, (size_t)batch, false);
+    A.leftIdx = c.out(left_idx, nm, false);
+    A.leftN = c.out(left_n, (size_t)batch, false);
+    A.outInfo = c.out(out_info, (size_t)batch * 49, false);
+    if (c.rc) return c.rc;
+    const size_t S = (size_t)M->cfg.max_batch * M->cfg.max_queries;
+    if (!M->d_active) GF_CUDA_OK(cudaMalloc((void**)&M->d_active, S * (5 * sizeof(int) + 2 * sizeof(double) + 1)));
+    const size_t n = (size_t)M->cfg.max_batch * mps->mp_stride <= S ? S : 0;
+    if (!n) return GFORB_ERR_CAPACITY;
+    A.sHeapVal = (double*)M->d_active; A.sListVal = A.sHeapVal + S;
+    A.sIdx = (int*)(A.sListVal + S); A.sVis = A.sIdx + S; A.sHeapIdx = A.sVis + S; A.sList = A.sHeapIdx + S;
+    A.sRemove = A.sList + S; A.sMark = (uint8_t*)(A.sRemove + S);
+    build_grid(M, c, T, G, batch);
+    run_candidates<M_MAP>(M, c, P, T, G, batch, mps->mp_stride);
+    A.tgt = T; A.pool = M->d_pool; A.poolCap = M->poolCap; A.qMeta = M->d_qMeta; A.maxQ = M->cfg.max_queries;
+    A.mpFlags = P.mpFlags; A.mpCounts = P.mpCounts; A.mpStride = mps->mp_stride;
+    A.nlevels = nlevels; A.nnratio = nnratio; A.numToMatch = num_to_match;
+    k_active_match<<<batch, 32, 0, c.st>>>(A);
+    M->lastLaunches++;
     return end_call(M, c, flags);
 }
 

@@ -22,6 +22,7 @@
 #include <vector>
 #include "common.cuh"
 #include "host_util.h"
+#include "logdet.cuh"
 
 namespace gforb {
 
@@ -143,68 +144,6 @@ __global__ void __launch_bounds__(128) k_build_info(int mode, const double* __re
     obsScore[p] = (mode == 0) ? (double)score[p] : 1.0;
 }
 
-// ------------------------------------------------------------------------------------------------ logDet
-#define LT(i, j) ((i) * ((i) + 1) / 2 + (j))
-
-// left-looking unblocked Cholesky of the lower triangle A (packed, 28 doubles) -> product of the diagonal of L
-__device__ __forceinline__ bool chol7_prod(const double (&A)[28], double& prod) {
-    double L[28];
-#pragma unroll
-    for (int j = 0; j < 7; j++) {
-        double ajj = A[LT(j, j)];
-#pragma unroll
-        for (int k = 0; k < j; k++) ajj -= L[LT(j, k)] * L[LT(j, k)];
-        if (!(ajj > 0.0)) return false;
-        ajj = sqrt(ajj);
-        L[LT(j, j)] = ajj;
-        const double rinv = 1.0 / ajj;
-#pragma unroll
-        for (int i = j + 1; i < 7; i++) {
-            double s = A[LT(i, j)];
-#pragma unroll
-            for (int k = 0; k < j; k++) s -= L[LT(i, k)] * L[LT(j, k)];
-            L[LT(i, j)] = s * rinv;
-        }
-    }
-    double p = 1.0;
-#pragma unroll
-    for (int j = 0; j < 7; j++) p *= L[LT(j, j)];
-    prod = p;
-    return true;
-}
-
-// arma::log_det fallback: LU with partial pivoting on the full matrix, sum log|u_ii| (rare path, local memory)
-__device__ __noinline__ double lu7_logabsdet(const double* __restrict__ cur, const double* __restrict__ blk, double sgn) {
-    double A[49];
-    for (int i = 0; i < 49; i++) A[i] = cur[i] + sgn * blk[i];
-    double ld = 0;
-    for (int k = 0; k < 7; k++) {
-        int p = k;
-        for (int i = k + 1; i < 7; i++) if (fabs(A[i * 7 + k]) > fabs(A[p * 7 + k])) p = i;
-        if (p != k) for (int c = 0; c < 7; c++) { double t = A[k * 7 + c]; A[k * 7 + c] = A[p * 7 + c]; A[p * 7 + c] = t; }
-        const double piv = A[k * 7 + k];
-        ld += log(fabs(piv));
-        if (piv == 0) continue;
-        for (int i = k + 1; i < 7; i++) {
-            const double f = A[i * 7 + k] / piv;
-            for (int c = k + 1; c < 7; c++) A[i * 7 + c] -= f * A[k * 7 + c];
-        }
-    }
-    return ld;
-}
-
-// logDet(cur + sgn * blk), both 7x7 row-major (cur in shared memory, blk in global memory)
-__device__ __forceinline__ double logdet_sum(const double* __restrict__ cur, const double* __restrict__ blk, double sgn) {
-    double A[28];
-#pragma unroll
-    for (int i = 0; i < 7; i++)
-#pragma unroll
-        for (int j = 0; j <= i; j++) A[LT(i, j)] = cur[i * 7 + j] + sgn * blk[i * 7 + j];
-    double p;
-    if (chol7_prod(A, p)) return 2 * log(p);
-    return lu7_logabsdet(cur, blk, sgn);
-}
-
 __global__ void __launch_bounds__(128) k_logdet(const double* __restrict__ mats, int n, double* __restrict__ out) {
     __shared__ double zero[49];
     if (threadIdx.x < 49) zero[threadIdx.x] = 0.0;
@@ -217,7 +156,6 @@ __global__ void __launch_bounds__(128) k_logdet(const double* __restrict__ mats,
 enum { MTD_GREEDY = 1, MTD_LAZIER_SELECT = 2, MTD_LAZIER_AUTO = 3, MTD_LAZIER_DELETE = 5 };
 static const int SEL_THREADS = 256;
 static const int MAX_RANDOM_QUERY_TIME = 2000;
-static const int RAW_RING = 1024;    // pre-generated rand() outputs (power of two, >= SEL_WIN + 64)
 static const int SEL_WIN = 2 * SEL_THREADS;   // rand() draws examined per sampling pass (2 per thread)
 
 struct SelParams {
@@ -231,55 +169,7 @@ struct SelParams {
     double* outLogdet;         // batch x outStride (may be null)
     int32_t* outN;             // batch
     int outStride;
-};
-
-// Warp-parallel glibc rand(): the additive-feedback recurrence r[n] = r[n-31] + r[n-3] splits into three independent
-// chains (n mod 3), so lanes 0..2 produce 30 new states per call; outputs (state >> 1) go to a ring the sampler reads.
-struct WarpRand {
-    uint32_t* rs;      // 64-entry state ring (shared)
-    uint32_t* raw;     // RAW_RING-entry output ring (shared), indexed by output number
-    int n;             // next state index to generate (uniform across the warp); output number = n - 344
-    __device__ void seed(uint32_t s, int lane) {
-        if (lane == 0) {
-            if (s == 0) s = 1;
-            int32_t word = (int32_t)s;
-            rs[0] = s;
-            for (int k = 1; k < 31; k++) {
-                const int32_t hi = word / 127773, lo = word % 127773;
-                word = 16807 * lo - 2836 * hi;
-                if (word < 0) word += 2147483647;
-                rs[k] = (uint32_t)word;
-            }
-            for (int k = 31; k < 34; k++) rs[k] = rs[k - 31];
-        }
-        n = 34;
-        __syncwarp();
-    }
-    // 30 new states per call.  Along each chain (lane mod 3) the recurrence is a running sum of the r[n-31] terms on top
-    // of the chain's last state, so the 30 values are one stride-3 segmented scan (4 shuffle steps, uint32 wrap-around
-    // addition is associative -> bit-identical to the sequential generator).
-    __device__ __forceinline__ void gen30(int lane) {
-        uint32_t a = (lane < 30) ? rs[(n + lane - 31) & 63] : 0u;
-#pragma unroll
-        for (int d = 3; d <= 24; d <<= 1) {
-            const uint32_t t = __shfl_up_sync(0xffffffffu, a, d);
-            if (lane >= d) a += t;
-        }
-        const uint32_t seed0 = rs[(n + (lane % 3) - 3) & 63];
-        __syncwarp();
-        if (lane < 30) {
-            const uint32_t v = a + seed0;
-            const int id = n + lane;
-            rs[id & 63] = v;
-            if (id >= 344) raw[(id - 344) & (RAW_RING - 1)] = v >> 1;
-        }
-        n += 30;
-        __syncwarp();
-    }
-    // make outputs [rp, rp + 32) available
-    __device__ __forceinline__ void ensure(int rp, int lane) {
-        while (n - 344 < rp + 32) gen30(lane);
-    }
+    long long* prof;           // optional phase-cycle counters of problem 0 (GFORB_SELECT_PROF=1), else null
 };
 
 __global__ void k_rand_stream(uint32_t seed, int n, int32_t* out) {
@@ -355,6 +245,10 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const SelParams P) {
     int epoch = 1;                    // sampling pass counter (uniform)
     const int rounds = deletion ? n - k : k;
     int nOut = 0;
+    long long tprev = 0;
+    const bool prof = P.prof && b == 0 && tid == 0;
+#define SEL_MARK(slot) if (prof) { const long long t_ = clock64(); P.prof[slot] += t_ - tprev; tprev = t_; }
+    if (prof) tprev = clock64();
     for (int i = 0; i < rounds; i++) {
         // ---- candidate list of this round, in evaluation order
         if (mtd == MTD_GREEDY) {
@@ -466,6 +360,7 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const SelParams P) {
             if (tid == 0) s_cnt = cntL;
         }
         __syncthreads();
+        SEL_MARK(0)
         const int cnt = s_cnt;
         // ---- evaluate logDet(cur +- block) for every candidate; arg-max, first in list wins ties (strict >)
         double bestV = -DBL_MAX; int bestT = INT_MAX;
@@ -490,6 +385,7 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const SelParams P) {
             s_pos = -1;
         }
         __syncthreads();
+        SEL_MARK(1)
         const int pick = s_pick;
         if (pick < 0) break;                                  // "if (maxLmk == -1) break"
         // ---- update the running matrix, record the pick, erase its column (order preserved)
@@ -509,6 +405,7 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const SelParams P) {
         m -= 1;
         { int* t = idx; idx = idx2; idx2 = t; }
         __syncthreads();
+        SEL_MARK(2)
     }
     if (deletion) {
         // survivors in ascending pool order (:2530-2540); single warp, ordered compaction
@@ -865,7 +762,8 @@ int gforb_obs_build_info_frame(GforbObs* O, const double* Xv, const float* world
 
 int gforb_obs_build_info_map(GforbObs* O, const double* Xv, const float* world, const uint8_t* track_in_view,
                              const int32_t* counts, int stride, int batch, int check_viz, int min_x, int max_x,
-                             int min_y, int max_y, double* blocks, double* obs_score, float* uv, int flags, void* stream) {
+                             int min_y, int max_y, double* blocks, double* obs_score, float* uv, double* H_meas,
+                             int flags, void* stream) {
     OCtx c;
     int rc = obs_begin(O, batch, stride, flags, stream, c);
     if (rc) return rc;
@@ -879,12 +777,13 @@ int gforb_obs_build_info_map(GforbObs* O, const double* Xv, const float* world, 
     double* dB = c.out(blocks, n * 49);
     double* dS = c.out(obs_score, n);
     float* dUv = c.out(uv, n * 2);
+    double* dH = c.out(H_meas, n * 14);
     if (c.rc) return c.rc;
     CamDev cam{O->cfg.fu, O->cfg.fv, O->cfg.Cx, O->cfg.Cy};
     // mBoundXInFrame = mBoundYInFrame = 20, mBoundDepth = 0 (include/Observability.h:129-131)
     k_build_info<<<dim3((stride + 127) / 128, batch), 128, 0, c.st>>>(1, dXv, cam, dW, nullptr, nullptr, dV, dCnt, stride, nullptr, 1,
                                                                        check_viz, min_x, max_x, min_y, max_y, 20.0, 20.0, 0.0, dB,
-                                                                       dS, nullptr, dUv);
+                                                                       dS, dH, dUv);
     O->lastLaunches = 1;
     return obs_end(O, c, flags);
 }
@@ -935,9 +834,19 @@ int gforb_obs_select(GforbObs* O, const double* blocks, const double* obs_score,
     P.outLogdet = c.out(out_logdet, (size_t)batch * out_stride);
     P.outN = c.out(out_n, (size_t)batch);
     P.outStride = out_stride;
+    P.prof = nullptr;
     if (c.rc) return c.rc;
+    static const bool wantProf = getenv("GFORB_SELECT_PROF") != nullptr;
+    if (wantProf) { GF_CUDA_OK(cudaMalloc((void**)&P.prof, 8 * sizeof(long long))); GF_CUDA_OK(cudaMemsetAsync(P.prof, 0, 8 * sizeof(long long), c.st)); }
     k_select<<<batch, SEL_THREADS, select_smem(O->cfg.max_points) + O->selPad, c.st>>>(P);
     O->lastLaunches = 1;
+    if (wantProf) {
+        long long h[8];
+        GF_CUDA_OK(cudaMemcpyAsync(h, P.prof, sizeof(h), cudaMemcpyDeviceToHost, c.st));
+        GF_CUDA_OK(cudaStreamSynchronize(c.st));
+        fprintf(stderr, "[gforb] k_select problem 0 cycles: sample %lld  eval+argmax %lld  update+erase %lld\n", h[0], h[1], h[2]);
+        cudaFree(P.prof);
+    }
     return obs_end(O, c, flags);
 }
 

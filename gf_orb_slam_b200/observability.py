@@ -11,6 +11,7 @@ from . import _lib
 from ._lib import ObsConfig, check, is_device, ptr
 
 BASELINE_GREEDY, LAZIER_GREEDY, AUTOMATIC_LAZIER, DELETION_LAZIER = 1, 2, 3, 5
+MAP_INFO_MATRIX, FRAME_INFO_MATRIX, MAP_HYBRID_MATRIX, FRAME_HYBRID_MATRIX = 0, 1, 2, 3   # include/Observability.h:94-102
 
 
 def _like(ref, shape, dtype_np, dtype_t):
@@ -90,17 +91,18 @@ class Observability:
         return (blocks, obs_score, H) if want_H else (blocks, obs_score)
 
     # ---- runMatrixBuilding(MAP_INFO_MATRIX)
-    def build_info_map(self, Xv, world, track_in_view, counts, check_viz, bounds, *, stream=None, sync=True):
+    def build_info_map(self, Xv, world, track_in_view, counts, check_viz, bounds, *, want_H=False, stream=None, sync=True):
         B, S = int(world.shape[0]), int(world.shape[1])
         dev = is_device(world)
         blocks = _like(world, (B, S, 49), np.float64, "float64")
         obs_score = _like(world, (B, S), np.float64, "float64")
         uv = _like(world, (B, S, 2), np.float32, "float32")
+        H = _like(world, (B, S, 14), np.float64, "float64") if want_H else None
         flags = (_lib.GFORB_IN_DEVICE | _lib.GFORB_OUT_DEVICE if dev else 0) | (0 if sync else _lib.GFORB_ASYNC)
         check(_lib.lib().gforb_obs_build_info_map(self._h, ptr(Xv), ptr(world), ptr(track_in_view), ptr(counts), S, B,
                                                   int(check_viz), *[int(v) for v in bounds], ptr(blocks), ptr(obs_score),
-                                                  ptr(uv), flags, C.c_void_p(stream or 0)), "gforb_obs_build_info_map")
-        return blocks, obs_score, uv
+                                                  ptr(uv), ptr(H), flags, C.c_void_p(stream or 0)), "gforb_obs_build_info_map")
+        return (blocks, obs_score, uv, H) if want_H else (blocks, obs_score, uv)
 
     def logDet(self, mats):
         dev = is_device(mats)
@@ -132,6 +134,29 @@ class Observability:
                                           float(sample_scale), ptr(seeds), ptr(out_idx), ptr(out_logdet), ptr(out_n),
                                           out_stride, flags, C.c_void_p(stream or 0)), "gforb_obs_select")
         return out_idx, out_logdet, out_n
+
+    # ---- int runActiveMapMatching(Frame*, mat_type, mBaseInfoMat, th, ORBmatcher&, num_to_match, time_for_match)
+    def runActiveMapMatching(self, F, mps, mat_type, base_info, th, matcher, num_to_match, *, obs_score, obs_mat, H_meas,
+                             level_sigma2, frame_mappoints, match_score, seeds=None, stream=None, sync=True):
+        """src/Observability.cc:1249-1524 for a batch of frames.  F: matcher.Frames, mps: matcher.MapPoints (mMapPoints
+        flattened), obs_score / obs_mat / H_meas: outputs of build_info_map(want_H=True), base_info: (B, 49) or (B, 7, 7),
+        frame_mappoints / match_score: (B, kp_stride) int32, updated in place.  Returns (nMatched[B], left_idx[B, stride],
+        left_n[B], info[B, 49])."""
+        B, S = mps.batch, mps.stride
+        dev = is_device(obs_mat)
+        nmatched = _like(obs_mat, (B,), np.int32, "int32")
+        left = _like(obs_mat, (B, S), np.int32, "int32")
+        left_n = _like(obs_mat, (B,), np.int32, "int32")
+        info = _like(obs_mat, (B, 49), np.float64, "float64")
+        fs, ms = F.cstruct(), mps.cstruct()
+        flags = (_lib.GFORB_IN_DEVICE | _lib.GFORB_OUT_DEVICE if dev else 0) | (0 if sync else _lib.GFORB_ASYNC)
+        check(_lib.lib().gforb_obs_active_match(self._h, matcher._h, C.byref(fs), C.byref(ms), B, ptr(obs_score), ptr(obs_mat),
+                                                ptr(H_meas), ptr(base_info), ptr(level_sigma2), int(level_sigma2.shape[0]),
+                                                int(mat_type), float(th), float(matcher.mfNNratio), int(num_to_match),
+                                                ptr(seeds), ptr(frame_mappoints), ptr(match_score), ptr(nmatched), ptr(left),
+                                                ptr(left_n), ptr(info), flags, C.c_void_p(stream or 0)),
+              "gforb_obs_active_match")
+        return nmatched, left, left_n, info
 
     @staticmethod
     def sample_scale_for(N_frame: int, k: int, error_bound: float) -> float:

@@ -223,10 +223,12 @@ int gforb_obs_build_info_frame(GforbObs* h, const double* Xv, const float* world
                                int batch, const float* level_sigma2, int nlevels, double* blocks, double* obs_score,
                                double* H_meas, int flags, void* stream);
 /* batchInfoMat_Map (src/Observability.cc:556-644): identity noise, optional visibility check; obs_score is 1 (built),
- * -1 (not visible) or -2 (skipped); uv: batch x stride x 2 projections or NULL. */
+ * -1 (not visible) or -2 (skipped); uv: batch x stride x 2 projections (MapPoint::u_proj, v_proj) or NULL;
+ * H_meas: batch x stride x 14 (MapPoint::H_meas = [H13 H47], read back by gforb_obs_active_match) or NULL. */
 int gforb_obs_build_info_map(GforbObs* h, const double* Xv, const float* world, const uint8_t* track_in_view,
                              const int32_t* counts, int stride, int batch, int check_viz, int min_x, int max_x,
-                             int min_y, int max_y, double* blocks, double* obs_score, float* uv, int flags, void* stream);
+                             int min_y, int max_y, double* blocks, double* obs_score, float* uv, double* H_meas,
+                             int flags, void* stream);
 /* logDet (include/Util.hpp:714-731) of n 7x7 row-major matrices. */
 int gforb_obs_logdet(GforbObs* h, const double* mats, int n, double* out, int flags, void* stream);
 /* the device's glibc-TYPE_3 rand() stream (parity tap; out_host is a host pointer) */
@@ -242,6 +244,23 @@ int gforb_obs_rand_stream(GforbObs* h, uint32_t seed, int n, int32_t* out_host);
 int gforb_obs_select(GforbObs* h, const double* blocks, const double* obs_score, const int32_t* counts, int stride,
                      int batch, int k, int mtd, double sample_scale, const uint32_t* seeds, int32_t* out_idx,
                      double* out_logdet, int32_t* out_n, int out_stride, int flags, void* stream);
+
+/* Observability::runActiveMapMatching(Frame*, mat_type, mBaseInfoMat, th, ORBmatcher&, num_to_match, time)
+ * (src/Observability.cc:1249-1524) for `batch` frames: greedy log-det ranking of the visible local-map points
+ * interleaved with ORBmatcher::SearchByProjection_OnePoint (include/ORBmatcher.h:71-145).
+ * mps: Observability::mMapPoints flattened; obs_score (batch x mp_stride, from gforb_obs_build_info_map; > 0 means
+ * MapPoint::updateAtFrameId == pFrame->mnId; NULL = every point), obs_mat = MapPoint::ObsMat (x 49), H_meas =
+ * MapPoint::H_meas (x 14), base_info = mBaseInfoMat (batch x 49), level_sigma2 = Frame::mvLevelSigma2.
+ * mat_type: 0 = MAP_INFO_MATRIX, 1 = FRAME_INFO_MATRIX (the hybrid types need DIMENSION_OF_STATE_MODEL = 13).
+ * frame_mappoints / match_score: in/out as in gforb_search_by_projection; nmatched: return value per frame;
+ * left_idx (batch x mp_stride) / left_n: mLeftMapPoints as indices into mps; out_info: batch x 49 accumulated
+ * matrix or NULL.  rand(): seeds[b] restarts glibc's generator per frame (NULL = 1); the time cap is infinite. */
+int gforb_obs_active_match(GforbObs* obs, GforbMatcher* matcher, const GforbFrameSet* F, const GforbMapPointSet* mps,
+                           int batch, const double* obs_score, const double* obs_mat, const double* H_meas,
+                           const double* base_info, const float* level_sigma2, int nlevels, int mat_type, float th,
+                           float nnratio, int num_to_match, const uint32_t* seeds, int32_t* frame_mappoints,
+                           int32_t* match_score, int32_t* nmatched, int32_t* left_idx, int32_t* left_n,
+                           double* out_info, int flags, void* stream);
 
 #ifdef __cplusplus
 }

@@ -415,7 +415,7 @@ public:
             int32_t cnt = n_;
             const bool ok = gforb_obs_build_info_map(h_, xv, world.data(), inView.data(), &cnt, n_, 1, check_viz ? 1 : 0,
                                                      pFrame->mnMinX, pFrame->mnMaxX, pFrame->mnMinY, pFrame->mnMaxY,
-                                                     blocks_.data(), score_.data(), nullptr, 0, nullptr) == GFORB_OK;
+                                                     blocks_.data(), score_.data(), nullptr, nullptr, 0, nullptr) == GFORB_OK;
             for (int i = 0; ok && i < n_; i++) (*mMapPoints)[i]->ObsScore = score_[i];
             return ok;
         }

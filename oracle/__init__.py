@@ -236,6 +236,23 @@ def window_search(F1: Frame, F2: Frame, window: int, minL=-1, maxL=0x7FFFFFFF, n
     return n, m2
 
 
+def active_match(F: Frame, u, v, level, viewCos, flags, desc, in_pool, obs_mat, H_meas, base_info, th: float, nnratio: float,
+                 num_to_match: int, seed: int = 1):
+    """Observability::runActiveMapMatching (src/Observability.cc:1249-1524): returns (nMatched, left map-point indices,
+    accumulated information matrix 7x7); F.matches() holds the updated mvpMapPoints / mvpMatchScore."""
+    u = np.ascontiguousarray(u, np.float32); v = np.ascontiguousarray(v, np.float32)
+    level = np.ascontiguousarray(level, np.int32); viewCos = np.ascontiguousarray(viewCos, np.float32)
+    flags = np.ascontiguousarray(flags, np.uint8); desc = np.ascontiguousarray(desc, np.uint8)
+    in_pool = np.ascontiguousarray(in_pool, np.uint8)
+    obs_mat = np.ascontiguousarray(obs_mat, np.float64); H_meas = np.ascontiguousarray(H_meas, np.float64)
+    cur = np.ascontiguousarray(base_info, np.float64).reshape(49).copy()
+    left = np.empty(max(u.size, 1), np.int32); nleft = C.c_int(0)
+    n = lib().orc_active_match(F.h, u.size, _p(u), _p(v), _p(level), _p(viewCos), _p(flags), _p(desc), _p(in_pool), _p(obs_mat),
+                               _p(H_meas), _p(cur), C.c_float(th), C.c_float(nnratio), int(num_to_match), C.c_long(seed),
+                               _p(left), C.byref(nleft))
+    return n, left[:nleft.value].copy(), cur.reshape(7, 7)
+
+
 # ---------------------------------------------------------------- observability
 class Observability:
     def __init__(self, *, f=None, fu=None, fv=None, nRows=480, nCols=752, Cx=0.0, Cy=0.0, k1=0.0, k2=0.0, dx=None, dy=None):
@@ -293,12 +310,14 @@ class Observability:
         lib().orc_obs_build_frame(self.h, seg, _p(world), _p(octave), _p(score), _p(valid), n, _p(ls), _p(blocks), _p(obs), _p(H))
         return blocks, obs, H
 
-    def build_map(self, world, track_in_view, check_viz, bounds, seg=0):
+    def build_map(self, world, track_in_view, check_viz, bounds, seg=0, want_H=False):
         world = np.ascontiguousarray(world, np.float32); tv = np.ascontiguousarray(track_in_view, np.uint8)
         n = world.shape[0]
         blocks = np.zeros((n, 7, 7)); obs = np.zeros(n); uv = np.zeros((n, 2), np.float32)
-        lib().orc_obs_build_map(self.h, seg, _p(world), _p(tv), n, int(check_viz), *[int(b) for b in bounds], _p(blocks), _p(obs), _p(uv))
-        return blocks, obs, uv
+        H = np.zeros((n, 2, 7)) if want_H else None
+        lib().orc_obs_build_map(self.h, seg, _p(world), _p(tv), n, int(check_viz), *[int(b) for b in bounds], _p(blocks), _p(obs), _p(uv),
+                                _p(H))
+        return (blocks, obs, uv, H) if want_H else (blocks, obs, uv)
 
 
 def logdet(M: np.ndarray) -> float:

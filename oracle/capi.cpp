@@ -191,9 +191,9 @@ void orc_obs_build_frame(void* o, int seg, const float* worldPos, const int* oct
     ob->batchInfoMat_Frame(worldPos, octave, matchScore, valid, n, levelSigma2, blocks, obsScore, H_meas);
 }
 void orc_obs_build_map(void* o, int seg, const float* worldPos, const uint8_t* trackInView, int n, int check_viz,
-                       int minX, int maxX, int minY, int maxY, double* blocks, double* obsScore, float* uv) {
+                       int minX, int maxX, int minY, int maxY, double* blocks, double* obsScore, float* uv, double* H_meas) {
     Observability* ob = (Observability*)o; ob->mKineIdx = seg;
-    ob->batchInfoMat_Map(worldPos, trackInView, n, check_viz != 0, minX, maxX, minY, maxY, blocks, obsScore, uv);
+    ob->batchInfoMat_Map(worldPos, trackInView, n, check_viz != 0, minX, maxX, minY, maxY, blocks, obsScore, uv, H_meas);
 }
 double orc_logdet(const double* M, int n) { return logDet(M, n); }
 // mtd: 1 baseline greedy, 2 lazier greedy selection, 3 automatic (deletion if 2k>n), 5 deletion.
@@ -217,6 +217,28 @@ int orc_obs_select(const double* blocks, const double* obsScore, int n, int k, i
     else return -1;
     for (size_t i = 0; i < sub.size(); i++) { out_idx[i] = (int)sub[i].idx; if (out_logdet) out_logdet[i] = sub[i].upper_bound; }
     return (int)sub.size();
+}
+
+// Observability::runActiveMapMatching (src/Observability.cc:1249-1524).  Map-point SoA as in orc_search_by_projection;
+// in_pool[i] = (updateAtFrameId == frame id); cur_mat (49) in: mBaseInfoMat, out: accumulated matrix; the frame's
+// mvpMapPoints / mvpMatchScore are updated in place; left_idx receives mLeftMapPoints, *left_n its size.
+int orc_active_match(void* fp, int M, const float* u, const float* v, const int* level, const float* viewCos,
+                     const uint8_t* flags, const uint8_t* desc, const uint8_t* in_pool, const double* obsMat,
+                     const double* H_meas, double* cur_mat, float th, float nnratio, int num_to_match, long seed,
+                     int* left_idx, int* left_n) {
+    std::vector<MapPointView> mps(M);
+    for (int i = 0; i < M; i++) {
+        mps[i].mTrackProjX = u[i]; mps[i].mTrackProjY = v[i]; mps[i].mnTrackScaleLevel = level[i];
+        mps[i].mTrackViewCos = viewCos[i]; mps[i].mbTrackInView = flags[i] & 1; mps[i].isBad = (flags[i] >> 1) & 1;
+        memcpy(mps[i].desc, desc + (size_t)32 * i, 32);
+    }
+    ORBmatcher m(nnratio, true);
+    if (seed >= 0) srand((unsigned)seed);
+    std::vector<int> left;
+    int n = runActiveMapMatching(*(Frame*)fp, mps, in_pool, obsMat, H_meas, cur_mat, th, m, num_to_match, left);
+    for (size_t i = 0; i < left.size(); i++) left_idx[i] = left[i];
+    *left_n = (int)left.size();
+    return n;
 }
 
 }  // extern "C"

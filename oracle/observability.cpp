@@ -6,6 +6,7 @@
 // are restated as plain loops: closed-form 3x3 inverse, unblocked left-looking Cholesky (OpenBLAS potf2_L order),
 // partial-pivot LU for the log_det fallback.
 #include "oracle.hpp"
+#include <queue>
 #include <algorithm>
 #include <cfloat>
 #include <cmath>
@@ -395,7 +396,7 @@ void Observability::batchInfoMat_Frame(const float* worldPos, const int* octave,
 // src/Observability.cc:556-644 (MAP_INFO_MATRIX; identity noise because F == NULL)
 void Observability::batchInfoMat_Map(const float* worldPos, const uint8_t* trackInView, int n, bool check_viz,
                                      int mnMinX, int mnMaxX, int mnMinY, int mnMaxY, double* blocks, double* obsScore,
-                                     float* uv) {
+                                     float* uv, double* H_meas) {
     if (mKineIdx >= kinematic.size()) return;
     vizMinX = mnMinX; vizMaxX = mnMaxX; vizMinY = mnMinY; vizMaxY = mnMaxY;
     for (int i = 0; i < n; i++) {
@@ -407,7 +408,7 @@ void Observability::batchInfoMat_Map(const float* worldPos, const uint8_t* track
         bool flag = compute_H_subblock_simplied(kinematic[mKineIdx].Xv, Y, H13, H47, Hp, check_viz, u, v);
         if (uv) { uv[2 * i] = u; uv[2 * i + 1] = v; }
         if (!flag) { obsScore[i] = -1.0; continue; }
-        infoBlock(H13, H47, 1.0, blocks + (size_t)49 * i, nullptr);
+        infoBlock(H13, H47, 1.0, blocks + (size_t)49 * i, H_meas ? H_meas + (size_t)14 * i : nullptr);
         obsScore[i] = 1.0;
     }
 }
@@ -567,6 +568,98 @@ void Observability::maxVolSelection_BaselineGreedy(std::vector<GoodPoint>* subVe
         lmkSelectPool[maxLmk].selected = true;
         subVec->push_back(lmkSelectPool[maxLmk]);
     }
+}
+
+
+// ------------------------------------------------------------------------------------------------ active matching
+// include/Util.hpp:47-62: the heap entry of runActiveMapMatching (std::priority_queue<SimplePoint>, operator< on score)
+namespace {
+struct SimplePoint {
+    int idx; double score;
+    SimplePoint(int i, double s) : idx(i), score(s) {}
+    bool operator<(const SimplePoint& r) const { return score < r.score; }
+};
+}  // namespace
+
+// src/Observability.cc:1249-1524
+int runActiveMapMatching(Frame& F, const std::vector<MapPointView>& mps, const uint8_t* inPool, const double* obsMat,
+                         const double* H_meas, double* curMat, float th, ORBmatcher& matcher, int num_to_match,
+                         std::vector<int>& left, int (*rand_fn)()) {
+    const size_t M = mps.size();
+    if (M == 0 || num_to_match <= 0) {                        // :1259-1272
+        for (size_t i = 0; i < M; ++i) {
+            if (mps[i].isBad) continue;
+            if (!mps[i].mbTrackInView) continue;
+            left.push_back((int)i);
+        }
+        return 0;
+    }
+    auto rnd = rand_fn ? rand_fn : &std::rand;
+    int nMatched = 0;
+    std::vector<double> lmkIdx, lmkVisited;                  // arma::mat rows of doubles (:1286-1310)
+    for (size_t i = 0; i < M; ++i) {
+        if (mps[i].isBad) continue;
+        if (!mps[i].mbTrackInView) continue;
+        if (!inPool[i]) continue;
+        lmkIdx.push_back((double)i); lmkVisited.push_back(-1);
+    }
+    const size_t N = lmkIdx.size();
+    const size_t szLazierSubset = static_cast<size_t>(float(N) / float(num_to_match) * 1.0);   // :1320
+    for (size_t i = 0; i < (size_t)num_to_match; ++i) {
+        std::priority_queue<SimplePoint> heapSubset;
+        std::vector<size_t> removeIdx;
+        size_t numHit = 0, numRndQue = 0, szActualSubset = szLazierSubset;
+        if (lmkIdx.size() < szActualSubset) szActualSubset = lmkIdx.size();
+        while (numHit < szActualSubset) {
+            size_t j = 0;
+            numRndQue = 0;
+            while (numRndQue < 2000) {
+                j = (rnd() % lmkIdx.size());
+                if (lmkVisited[j] < i) { lmkVisited[j] = i; break; }
+                ++numRndQue;
+            }
+            if (numRndQue >= 2000) break;
+            const int queIdx = (int)lmkIdx[j];
+            ++numHit;
+            double Mx[49];
+            for (int t = 0; t < 49; t++) Mx[t] = curMat[t] + obsMat[(size_t)49 * queIdx + t];
+            heapSubset.push(SimplePoint(queIdx, logDet(Mx, 7)));
+            if (numHit >= szActualSubset) {
+                const SimplePoint heapTop = heapSubset.top();
+                const int bestIdx = matcher.SearchByProjection_OnePoint(F, mps[heapTop.idx], heapTop.idx, th);
+                if (bestIdx >= 0) {
+                    // reWeightInfoMat (include/Observability.h:517-596) with the matched keypoint's octave, then
+                    // curMat += H_rw^T H_rw (:1394-1417)
+                    const float Sigma2 = F.mvLevelSigma2[F.mvKeysUn[bestIdx].octave];
+                    const double w = std::sqrt((double)Sigma2), wi = 1.0 / w;
+                    double Hr[14];
+                    for (int t = 0; t < 14; t++) Hr[t] = wi * H_meas[(size_t)14 * heapTop.idx + t];
+                    for (int r = 0; r < 7; r++)
+                        for (int c = 0; c < 7; c++) curMat[r * 7 + c] = curMat[r * 7 + c] + (Hr[r] * Hr[c] + Hr[7 + r] * Hr[7 + c]);
+                    removeIdx.push_back(heapTop.idx);
+                    ++nMatched;
+                    break;
+                } else {
+                    removeIdx.push_back(heapTop.idx);
+                    heapSubset.pop();
+                    --numHit;
+                }
+            }
+        }
+        if (numRndQue >= 2000 || heapSubset.size() == 0 || removeIdx.size() == 0) break;     // "early termination"
+        if (lmkIdx.size() == removeIdx.size()) break;                                        // "went through all map points"
+        std::sort(removeIdx.begin(), removeIdx.end());
+        std::vector<double> ni, nv;
+        size_t j = 0, k = 0;
+        while (j < lmkIdx.size()) {                           // :1459-1480
+            if (k >= removeIdx.size()) { ni.push_back(lmkIdx[j]); nv.push_back(lmkVisited[j]); ++j; }
+            else if (lmkIdx[j] < removeIdx[k]) { ni.push_back(lmkIdx[j]); nv.push_back(lmkVisited[j]); ++j; }
+            else { if (lmkIdx[j] == removeIdx[k]) ++j; ++k; }
+        }
+        lmkIdx.swap(ni); lmkVisited.swap(nv);
+    }
+    for (size_t i = 0; i < lmkIdx.size(); ++i) left.push_back((int)lmkIdx[i]);
+    return nMatched;
 }
 
 }  // namespace oracle

@@ -159,7 +159,7 @@ public:
                             int n, const float* levelSigma2, double* blocks, double* obsScore, double* H_meas /*n x 14 or null*/);
     void batchInfoMat_Map(const float* worldPos, const uint8_t* trackInView, int n, bool check_viz,
                           int mnMinX, int mnMaxX, int mnMinY, int mnMaxY, double* blocks, double* obsScore,
-                          float* uv /*n x 2 or null*/);
+                          float* uv /*n x 2 or null*/, double* H_meas = nullptr /*n x 14 or null*/);
 
     // subset selection over lmkSelectPool
     std::vector<GoodPoint> lmkSelectPool;
@@ -182,5 +182,13 @@ public:
 };
 
 double logDet(const double* M, int n);   // include/Util.hpp:714-731
+
+// Observability::runActiveMapMatching (src/Observability.cc:1249-1524) for FRAME_INFO_MATRIX / MAP_INFO_MATRIX with
+// INFORMATION_EFFICIENCY_SCORE off and an infinite time cap.  inPool[i] = (updateAtFrameId == pFrame->mnId),
+// obsMat = MapPoint::ObsMat (M x 49), H_meas = MapPoint::H_meas (M x 14, rows [H13 H47]); curMat (49, in/out) enters as
+// mBaseInfoMat and leaves as the accumulated matrix; left = mLeftMapPoints (indices into mps, appended).
+int runActiveMapMatching(Frame& F, const std::vector<MapPointView>& mps, const uint8_t* inPool, const double* obsMat,
+                         const double* H_meas, double* curMat, float th, ORBmatcher& matcher, int num_to_match,
+                         std::vector<int>& left, int (*rand_fn)() = nullptr);
 
 }  // namespace oracle
