@@ -141,6 +141,11 @@ struct MapPoint {
     uint8_t mDescriptor[32] = {0};
     float mWorldPos[3] = {0, 0, 0};
     double ObsScore = -1;
+    // written by Observability::runMatrixBuilding(MAP_INFO_MATRIX) (src/Observability.cc:627-636)
+    float u_proj = 0, v_proj = 0;
+    double H_meas[14] = {0};                         // 2x7 row-major [H13 H47]
+    double ObsMat[49] = {0};                         // 7x7 row-major
+    long unsigned int updateAtFrameId = 0;
     bool isBad() const { return mbBad; }
     const uint8_t* GetDescriptor() const { return mDescriptor; }
 };
@@ -148,6 +153,7 @@ struct MapPoint {
 // The Frame fields this path touches (include/Frame.h): undistorted keypoints, descriptors, per-keypoint map-point
 // association / match score / outlier flag, image bounds and the scale pyramid parameters.
 struct Frame {
+    long unsigned int mnId = 0;
     int N = 0;
     std::vector<gforb_cv::KeyPoint> mvKeysUn;
     gforb_cv::Mat mDescriptors;                      // N x 32
@@ -298,6 +304,7 @@ public:
     bool mbCheckOrientation;
 
 private:
+    friend class Observability;                       // runActiveMapMatching drives the one-point matcher of this handle
     struct FlatFrame {          // Frame -> GforbFrameSet (one frame); keeps the staging alive for the call
         std::vector<uint8_t> desc;
         int32_t count;
@@ -348,7 +355,7 @@ struct GoodPoint {
 
 class Observability {
 public:
-    enum { FRAME_INFO_MATRIX = 1, MAP_INFO_MATRIX = 2 };                  // mat_type of runMatrixBuilding (subset)
+    enum { MAP_INFO_MATRIX = 0, FRAME_INFO_MATRIX = 1, MAP_HYBRID_MATRIX = 2, FRAME_HYBRID_MATRIX = 3 };   // include/Observability.h:94-102
     // used by Tracking (src/Tracking.cc:146; k1 = k2 = 0)
     Observability(double fu, double fv, int nRows, int nCols, double Cx, double Cy, double k1, double k2, int device = 0) {
         init(fu, fv, nRows, nCols, Cx, Cy, k1, k2, 1.0, 1.0, device);
@@ -377,7 +384,9 @@ public:
     // the frame / map pool the next calls work on (the reference keeps pFrame / mMapPoints members)
     Frame* pFrame = nullptr;
     std::vector<MapPoint*>* mMapPoints = nullptr;
+    std::vector<MapPoint*> mLeftMapPoints;            // include/Observability.h:731
     size_t mKineIdx = 0;
+    long unsigned int mnFrameId = 0;                  // include/Observability.h:720 (set by Tracking before each call)
 
     // src/Observability.cc:646-804: per-match information blocks for the current pFrame (FRAME_INFO_MATRIX) or the
     // local map (MAP_INFO_MATRIX).  Time budgets are accepted and ignored (the device call is bounded by construction).
@@ -411,15 +420,76 @@ public:
             std::vector<float> world((size_t)n_ * 3);
             std::vector<uint8_t> inView(n_);
             for (int i = 0; i < n_; i++) { std::memcpy(&world[(size_t)i * 3], (*mMapPoints)[i]->mWorldPos, 12); inView[i] = (*mMapPoints)[i]->mbTrackInView; }
+            // points already refreshed at this frame are skipped (src/Observability.cc:586-587)
+            std::vector<uint8_t> skip(n_);
+            for (int i = 0; i < n_; i++) skip[i] = (*mMapPoints)[i]->updateAtFrameId == mnFrameId;
             blocks_.resize((size_t)n_ * 49); score_.resize(n_);
+            std::vector<float> uv((size_t)n_ * 2);
+            std::vector<double> hm((size_t)n_ * 14);
             int32_t cnt = n_;
             const bool ok = gforb_obs_build_info_map(h_, xv, world.data(), inView.data(), &cnt, n_, 1, check_viz ? 1 : 0,
                                                      pFrame->mnMinX, pFrame->mnMaxX, pFrame->mnMinY, pFrame->mnMaxY,
-                                                     blocks_.data(), score_.data(), nullptr, nullptr, 0, nullptr) == GFORB_OK;
-            for (int i = 0; ok && i < n_; i++) (*mMapPoints)[i]->ObsScore = score_[i];
+                                                     blocks_.data(), score_.data(), uv.data(), hm.data(), 0, nullptr) == GFORB_OK;
+            for (int i = 0; ok && i < n_; i++) {
+                MapPoint* p = (*mMapPoints)[i];
+                if (skip[i] || score_[i] == -2.0) continue;                // refreshed earlier / not touched by the builder
+                p->ObsScore = score_[i];
+                if (score_[i] != 1.0) continue;
+                p->u_proj = uv[(size_t)i * 2]; p->v_proj = uv[(size_t)i * 2 + 1];
+                std::memcpy(p->H_meas, &hm[(size_t)i * 14], sizeof(p->H_meas));
+                std::memcpy(p->ObsMat, &blocks_[(size_t)i * 49], sizeof(p->ObsMat));
+                p->updateAtFrameId = mnFrameId;
+            }
             return ok;
         }
         return false;
+    }
+
+    // src/Observability.cc:1249-1524.  mBaseInfoMat is a 7x7 row-major double[49] here (arma::mat in the reference); the
+    // time budget is accepted and ignored; the hybrid matrix types need the 13-state model and return 0 matches.
+    // The reference draws from the process-global rand(); `rand_seed` restarts glibc's generator for this call
+    // (1 = a process that never called srand).
+    int runActiveMapMatching(Frame* pF, const size_t mat_type, const double* mBaseInfoMat, const float th,
+                             ORBmatcher& mORBMatcher, const int num_to_match, const double /*time_for_match*/ = 1e30,
+                             uint32_t rand_seed = 1, double* curMatOut = nullptr) {
+        if (pF == nullptr || mMapPoints == nullptr) return 0;
+        if (mat_type != MAP_INFO_MATRIX && mat_type != FRAME_INFO_MATRIX) return 0;
+        const int M = (int)mMapPoints->size();
+        if (M == 0 || pF->N == 0) return 0;
+        Frame& F = *pF;
+        mORBMatcher.ensure(F.N, M, F.mnScaleLevels, F.mfScaleFactor);
+        std::vector<float> u(M), v(M), vc(M);
+        std::vector<int32_t> lvl(M);
+        std::vector<uint8_t> fl(M), desc((size_t)M * 32);
+        std::vector<double> osc(M), om((size_t)M * 49), hm((size_t)M * 14);
+        for (int i = 0; i < M; i++) {
+            const MapPoint* p = (*mMapPoints)[i];
+            fl[i] = 0; osc[i] = -1.0;
+            if (!p) continue;                                               // NULL entries are skipped (:1291)
+            u[i] = p->mTrackProjX; v[i] = p->mTrackProjY; vc[i] = p->mTrackViewCos; lvl[i] = p->mnTrackScaleLevel;
+            fl[i] = (uint8_t)((p->mbTrackInView ? 1 : 0) | (p->isBad() ? 2 : 0));
+            std::memcpy(&desc[(size_t)i * 32], p->GetDescriptor(), 32);
+            osc[i] = (p->updateAtFrameId == F.mnId) ? 1.0 : -1.0;           // :1297
+            std::memcpy(&om[(size_t)i * 49], p->ObsMat, sizeof(p->ObsMat));
+            std::memcpy(&hm[(size_t)i * 14], p->H_meas, sizeof(p->H_meas));
+        }
+        ORBmatcher::FlatFrame ff(F);
+        std::vector<int32_t> ids = ORBmatcher::ids_of(F, *mMapPoints), score(F.mvpMatchScore.begin(), F.mvpMatchScore.end());
+        std::vector<int32_t> left(M);
+        int32_t mcount = M, nMatched = 0, nLeft = 0;
+        double info[49];
+        GforbMapPointSet mp = {u.data(), v.data(), lvl.data(), vc.data(), fl.data(), desc.data(), &mcount, M};
+        gforb_throw(gforb_obs_active_match(h_, mORBMatcher.h_, &ff.set, &mp, 1, osc.data(), om.data(), hm.data(), mBaseInfoMat,
+                                           F.mvLevelSigma2.data(), (int)F.mvLevelSigma2.size(), (int)mat_type, th,
+                                           mORBMatcher.mfNNratio, num_to_match, &rand_seed, ids.data(), score.data(), &nMatched,
+                                           left.data(), &nLeft, info, 0, nullptr), "runActiveMapMatching");
+        for (int i = 0; i < F.N; i++) {
+            if (ids[i] >= 0 && ids[i] < M) F.mvpMapPoints[i] = (*mMapPoints)[ids[i]];
+            F.mvpMatchScore[i] = score[i];
+        }
+        for (int i = 0; i < nLeft; i++) mLeftMapPoints.push_back((*mMapPoints)[left[i]]);
+        if (curMatOut) std::memcpy(curMatOut, info, sizeof(info));
+        return nMatched;
     }
 
     // src/Observability.cc:808-1018: build the frame blocks, pool the valid matches in index order, pick k of them.

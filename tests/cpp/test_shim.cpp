@@ -185,7 +185,65 @@ int main() {
     CHECK(subset, "good-feature subset differs");
     CHECK(ldok, "log-det trajectory differs by more than 1e-5 relative");
 
-    printf("shim test: %zu/%zu keypoints, %d init matches, %d projection matches, %zu good features: %s\n", k1.size(),
-           k2.size(), nm, np, good.size(), g_fail ? "FAILED" : "OK");
+    // ---- active map matching (the default GF mode): fresh frame 2, every map point refreshed by the map builder
+    int nActive = 0;
+    {
+        Frame F3(k2, d2, W, H);
+        F3.mnId = 42;
+        oracle::Frame oF3;
+        oF3.init(ok2.data(), od2.data(), (int)ok2.size(), W, H, 8, 1.2f);
+        sm_state = 1234;
+        const int M = (int)mps.size();
+        std::vector<float> mw((size_t)M * 3);
+        std::vector<uint8_t> tv(M);
+        for (int i = 0; i < M; i++) {
+            MapPoint& p = mps[i];
+            p.mWorldPos[0] = (float)((splitmix() >> 11) * (1.0 / 9007199254740992.0) * 4.0 - 2.0);
+            p.mWorldPos[1] = (float)((splitmix() >> 11) * (1.0 / 9007199254740992.0) * 4.0 - 2.0);
+            p.mWorldPos[2] = (float)((splitmix() >> 11) * (1.0 / 9007199254740992.0) * 6.0 + 4.0);
+            p.updateAtFrameId = 7;
+            std::memcpy(&mw[(size_t)i * 3], p.mWorldPos, 12);
+            tv[i] = p.mbTrackInView;
+        }
+        ob.pFrame = &F3; ob.mMapPoints = &vp; ob.mnFrameId = F3.mnId;
+        CHECK(ob.runMatrixBuilding(Observability::MAP_INFO_MATRIX, 1.0, true, false), "runMatrixBuilding(MAP) failed");
+        std::vector<double> mb((size_t)M * 49), ms(M), mh((size_t)M * 14);
+        oob.batchInfoMat_Map(mw.data(), tv.data(), M, false, 0, W, 0, H, mb.data(), ms.data(), nullptr, mh.data());
+        std::vector<uint8_t> inPool(M);
+        bool built = true;
+        for (int i = 0; i < M; i++) {
+            inPool[i] = ms[i] == 1.0;
+            built = built && ((mps[i].updateAtFrameId == F3.mnId) == (ms[i] == 1.0));
+            if (ms[i] == 1.0) built = built && std::memcmp(mps[i].ObsMat, &mb[(size_t)i * 49], 392) == 0 &&
+                                      std::memcmp(mps[i].H_meas, &mh[(size_t)i * 14], 112) == 0;
+        }
+        CHECK(built, "map information blocks differ");
+        double base[49], ocur[49], cur[49];
+        for (int i = 0; i < 49; i++) base[i] = (i % 8 == 0) ? 1e-5 : 0.0;
+        std::memcpy(ocur, base, sizeof(base));
+        ORBmatcher m3(0.8f, true);
+        oracle::ORBmatcher om3(0.8f, true);
+        nActive = ob.runActiveMapMatching(&F3, Observability::MAP_INFO_MATRIX, base, 3.0f, m3, 60, 1e30, 1, cur);
+        std::vector<int> oleft;
+        srand(1);
+        const int onActive = oracle::runActiveMapMatching(oF3, omp, inPool.data(), mb.data(), mh.data(), ocur, 3.0f, om3, 60, oleft);
+        CHECK(nActive == onActive, "runActiveMapMatching: %d vs %d", nActive, onActive);
+        CHECK(nActive > 20, "too few active matches: %d", nActive);
+        bool a3 = true;
+        for (int i = 0; i < F3.N; i++) {
+            const int id = F3.mvpMapPoints[i] ? (int)(F3.mvpMapPoints[i] - &mps[0]) : -1;
+            a3 = a3 && id == oF3.mvpMapPoints[i] && F3.mvpMatchScore[i] == oF3.mvpMatchScore[i];
+        }
+        CHECK(a3, "active matching associations differ");
+        bool l3 = ob.mLeftMapPoints.size() == oleft.size();
+        for (size_t i = 0; l3 && i < oleft.size(); i++) l3 = (int)(ob.mLeftMapPoints[i] - &mps[0]) == oleft[i];
+        CHECK(l3, "mLeftMapPoints differs (%zu vs %zu)", ob.mLeftMapPoints.size(), oleft.size());
+        bool c3 = true;
+        for (int i = 0; i < 49; i++) c3 = c3 && std::fabs(cur[i] - ocur[i]) <= 1e-12 * std::fabs(ocur[i]);
+        CHECK(c3, "accumulated information matrix differs");
+    }
+
+    printf("shim test: %zu/%zu keypoints, %d init matches, %d projection matches, %zu good features, %d active matches: %s\n", k1.size(),
+           k2.size(), nm, np, good.size(), nActive, g_fail ? "FAILED" : "OK");
     return g_fail ? 1 : 0;
 }
