@@ -154,9 +154,8 @@ __global__ void __launch_bounds__(128) k_logdet(const double* __restrict__ mats,
 
 // ------------------------------------------------------------------------------------------------ K12 selection
 enum { MTD_GREEDY = 1, MTD_LAZIER_SELECT = 2, MTD_LAZIER_AUTO = 3, MTD_LAZIER_DELETE = 5 };
-static const int SEL_THREADS = 256;
 static const int MAX_RANDOM_QUERY_TIME = 2000;
-static const int SEL_WIN = 2 * SEL_THREADS;   // rand() draws examined per sampling pass (2 per thread)
+static const int SEL_WIN = 512;      // rand() draws examined per sampling pass
 
 struct SelParams {
     const double* blocks;      // batch x stride x 49
@@ -185,7 +184,14 @@ __global__ void k_rand_stream(uint32_t seed, int n, int32_t* out) {
     }
 }
 
-__global__ void __launch_bounds__(SEL_THREADS) k_select(const SelParams P) {
+// T threads per problem (64 / 128 / 256): the kernel is a 100-round dependency chain that leaves the issue slots
+// mostly idle, so what it costs the rest of the pipeline is the register file it holds while it runs (T x 128
+// registers per problem).  Small T trades a longer chain (each thread evaluates cnt / T candidates in turn) for a
+// footprint that lets the extraction kernels of the next step co-reside on the same SMs.
+template <int T>
+__global__ void __launch_bounds__(T) k_select(const SelParams P) {
+    constexpr int DPT = SEL_WIN / T;          // rand() draws examined per thread and sampling pass
+    constexpr int NW = T / 32;
     extern __shared__ __align__(16) unsigned char smraw[];
     const unsigned full = 0xffffffffu;
     const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -199,8 +205,8 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const SelParams P) {
     unsigned char* alive = reinterpret_cast<unsigned char*>(list + P.maxPoints);   // `selected` flag per pool entry
     unsigned char* okf = alive + P.maxPoints;                                      // obs_score >= 0
     __shared__ double cur[49];
-    __shared__ double redV[SEL_THREADS / 32];
-    __shared__ int redT[SEL_THREADS / 32];
+    __shared__ double redV[NW];
+    __shared__ int redT[NW];
     __shared__ uint32_t s_rs[64];
     __shared__ uint32_t s_raw[RAW_RING];
     __shared__ int s_cnt, s_pick, s_pos;
@@ -214,7 +220,7 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const SelParams P) {
     const int k = P.k;
     if (n <= 0) { if (tid == 0) P.outN[b] = 0; return; }
     if (k >= n) {        // "if (mpLimit >= edIdx - stIdx) take all" (:2832-2840)
-        for (int i = tid; i < n && i < P.outStride; i += SEL_THREADS) { outIdx[i] = i; if (outLd) outLd[i] = 0.0; }
+        for (int i = tid; i < n && i < P.outStride; i += T) { outIdx[i] = i; if (outLd) outLd[i] = 0.0; }
         if (tid == 0) P.outN[b] = min(n, P.outStride);
         return;
     }
@@ -225,7 +231,7 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const SelParams P) {
     const size_t szLazier = (size_t)((double)n / (double)k * P.sampleScale);
     // init
     if (tid < 49) cur[tid] = (tid % 8 == 0) ? 0.00001 : 0.0;
-    for (int i = tid; i < n; i += SEL_THREADS) {
+    for (int i = tid; i < n; i += T) {
         idxA[i] = i; vis[i] = -1; win[i] = 0; alive[i] = deletion ? 1 : 0;
         okf[i] = (sc && sc[i] < 0) ? 0 : 1;
     }
@@ -256,7 +262,7 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const SelParams P) {
             // unselected valid entry (ties -> lowest pool index)
             if (tid == 0) s_cnt = 0;
             __syncthreads();
-            for (int base = 0; base < m; base += SEL_THREADS) {
+            for (int base = 0; base < m; base += T) {
                 const int j = base + tid;
                 const bool ok = j < m && okf[idx[j]];
                 const unsigned bal = __ballot_sync(full, ok);
@@ -266,7 +272,7 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const SelParams P) {
                 for (int w = 0; w < warp; w++) off += redT[w];
                 if (ok) list[off + __popc(bal & ((1u << lane) - 1u))] = idx[j];
                 __syncthreads();
-                if (tid == 0) { int t = 0; for (int w = 0; w < SEL_THREADS / 32; w++) t += redT[w]; s_cnt += t; }
+                if (tid == 0) { int t = 0; for (int w = 0; w < NW; w++) t += redT[w]; s_cnt += t; }
                 __syncthreads();
             }
         } else {
@@ -282,10 +288,10 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const SelParams P) {
             while (!stop) {
                 if (warp == 0) while (rng.n - 344 < rp + SEL_WIN) rng.gen30(lane);
                 __syncthreads();
-                int jj[2]; int key[2]; bool seenPrev[2];
+                int jj[DPT]; int key[DPT]; bool seenPrev[DPT];
 #pragma unroll
-                for (int h = 0; h < 2; h++) {
-                    const int d = h * SEL_THREADS + tid;
+                for (int h = 0; h < DPT; h++) {
+                    const int d = h * T + tid;
                     const uint32_t r = s_raw[(rp + d) & (RAW_RING - 1)];
                     jj[h] = (int)(r % (uint32_t)m);
                     seenPrev[h] = vis[jj[h]] >= i;
@@ -293,23 +299,23 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const SelParams P) {
                     if (!seenPrev[h]) atomicMax(&win[jj[h]], key[h]);
                 }
                 __syncthreads();
-                bool isNew[2], valid[2]; int que[2]; unsigned nm[2], vm[2];
+                bool isNew[DPT], valid[DPT]; int que[DPT]; unsigned nm[DPT], vm[DPT];
 #pragma unroll
-                for (int h = 0; h < 2; h++) {
+                for (int h = 0; h < DPT; h++) {
                     isNew[h] = !seenPrev[h] && win[jj[h]] == key[h];
                     que[h] = idx[jj[h]];
                     const bool sel = alive[que[h]] != 0;
                     valid[h] = isNew[h] && !((deletion ? !sel : sel) || !okf[que[h]]);
                     nm[h] = __ballot_sync(full, isNew[h]);
                     vm[h] = __ballot_sync(full, valid[h]);
-                    if (lane == 0) { s_new[h * 8 + warp] = nm[h]; s_valid[h * 8 + warp] = vm[h]; }
+                    if (lane == 0) { s_new[h * NW + warp] = nm[h]; s_valid[h * NW + warp] = vm[h]; }
                 }
                 __syncthreads();
                 const unsigned lt = (1u << lane) - 1u;
-                int vBefore[2];
+                int vBefore[DPT];
 #pragma unroll
-                for (int h = 0; h < 2; h++) {
-                    const int g = h * 8 + warp, d = h * SEL_THREADS + tid;
+                for (int h = 0; h < DPT; h++) {
+                    const int g = h * NW + warp, d = h * T + tid;
                     int vb = numHit;
                     for (int q = 0; q < g; q++) vb += __popc(s_valid[q]);
                     vb += __popc(vm[h] & lt);
@@ -334,8 +340,8 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const SelParams P) {
                 if (!stop) cut = SEL_WIN - 1;
                 // commit the consumed draws
 #pragma unroll
-                for (int h = 0; h < 2; h++) {
-                    const int d = h * SEL_THREADS + tid;
+                for (int h = 0; h < DPT; h++) {
+                    const int d = h * T + tid;
                     if (d <= cut) {
                         if (isNew[h]) vis[jj[h]] = i;
                         if (valid[h]) list[cntL + vBefore[h] - numHit] = que[h];
@@ -364,7 +370,7 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const SelParams P) {
         const int cnt = s_cnt;
         // ---- evaluate logDet(cur +- block) for every candidate; arg-max, first in list wins ties (strict >)
         double bestV = -DBL_MAX; int bestT = INT_MAX;
-        for (int t = tid; t < cnt; t += SEL_THREADS) {
+        for (int t = tid; t < cnt; t += T) {
             const double v = logdet_sum(cur, blk + (size_t)list[t] * 49, sgn);
             if (v > bestV) { bestV = v; bestT = t; }
         }
@@ -378,7 +384,7 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const SelParams P) {
         __syncthreads();
         if (tid == 0) {
             double v = redV[0]; int t = redT[0];
-            for (int w = 1; w < SEL_THREADS / 32; w++)
+            for (int w = 1; w < NW; w++)
                 if (redV[w] > v || (redV[w] == v && redT[w] < t)) { v = redV[w]; t = redT[w]; }
             s_pick = (t == INT_MAX) ? -1 : list[t];
             s_val = v;
@@ -395,13 +401,8 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select(const SelParams P) {
             if (!deletion && i < P.outStride) { outIdx[i] = pick; if (outLd) outLd[i] = s_val; }
         }
         if (!deletion) nOut = i + 1;
-        for (int j = tid; j < m; j += SEL_THREADS) if (idx[j] == pick) s_pos = j;
-        __syncthreads();
-        const int pos = s_pos;
-        for (int j = tid; j < m; j += SEL_THREADS) {
-            if (j < pos) idx2[j] = idx[j];
-            else if (j > pos) idx2[j - 1] = idx[j];
-        }
+        // lmkIdx stays ascending (identity minus erased columns): every entry >= pick moves one column left
+        for (int j = tid; j < m - 1; j += T) { const int a = idx[j]; idx2[j] = (a >= pick) ? idx[j + 1] : a; }
         m -= 1;
         { int* t = idx; idx = idx2; idx2 = t; }
         __syncthreads();
@@ -440,6 +441,7 @@ struct KineSeg {
 struct GforbObs {
     GforbObsConfig cfg;
     int device = 0, lastLaunches = 0;
+    int selThreads = 0, numSMs = 148;
     int selPad = 0;          // extra dynamic smem of k_select (GFORB_SELECT_SMEM_PAD): caps its CTAs per SM when it shares the GPU
     double Xv[13];
     std::vector<KineSeg> kine;
@@ -645,7 +647,12 @@ int gforb_obs_create(const GforbObsConfig* cfg, GforbObs** out) {
     GF_CUDA_OK(O->arena.init(B * N * (12 + 4 + 4 + 1 + 392 + 112 + 8 + 8 + 4 + 8 + 64) + B * 256 + (1u << 20)));
     GF_CUDA_OK(cudaMalloc((void**)&O->d_err, sizeof(int)));
     if (const char* e = getenv("GFORB_SELECT_SMEM_PAD")) O->selPad = atoi(e);
-    GF_CUDA_OK(cudaFuncSetAttribute(k_select, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)select_smem(cfg->max_points) + O->selPad));
+    cudaDeviceGetAttribute(&O->numSMs, cudaDevAttrMultiProcessorCount, cfg->device);
+    const int selSmem = (int)select_smem(cfg->max_points) + O->selPad;
+    GF_CUDA_OK(cudaFuncSetAttribute(k_select<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, selSmem));
+    GF_CUDA_OK(cudaFuncSetAttribute(k_select<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, selSmem));
+    GF_CUDA_OK(cudaFuncSetAttribute(k_select<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, selSmem));
+    if (const char* e = getenv("GFORB_SELECT_THREADS")) O->selThreads = atoi(e);
     *out = O;
     return GFORB_OK;
 }
@@ -838,7 +845,13 @@ int gforb_obs_select(GforbObs* O, const double* blocks, const double* obs_score,
     if (c.rc) return c.rc;
     static const bool wantProf = getenv("GFORB_SELECT_PROF") != nullptr;
     if (wantProf) { GF_CUDA_OK(cudaMalloc((void**)&P.prof, 8 * sizeof(long long))); GF_CUDA_OK(cudaMemsetAsync(P.prof, 0, 8 * sizeof(long long), c.st)); }
-    k_select<<<batch, SEL_THREADS, select_smem(O->cfg.max_points) + O->selPad, c.st>>>(P);
+    // threads per problem: a few problems -> shortest chain; a GPU-filling batch -> smallest register footprint
+    int T = O->selThreads;
+    if (T != 64 && T != 128 && T != 256) T = batch <= O->numSMs / 2 ? 256 : 128;   // B200, 256 problems: 1.62 / 1.56 / 2.28 ms for 256 / 128 / 64
+    const size_t smem = select_smem(O->cfg.max_points) + O->selPad;
+    if (T == 256) k_select<256><<<batch, 256, smem, c.st>>>(P);
+    else if (T == 128) k_select<128><<<batch, 128, smem, c.st>>>(P);
+    else k_select<64><<<batch, 64, smem, c.st>>>(P);
     O->lastLaunches = 1;
     if (wantProf) {
         long long h[8];
