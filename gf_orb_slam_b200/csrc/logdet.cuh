@@ -11,23 +11,25 @@ namespace gforb {
 // ------------------------------------------------------------------------------------------------ logDet
 #define LT(i, j) ((i) * ((i) + 1) / 2 + (j))
 
-// left-looking unblocked Cholesky of the lower triangle A (packed, 28 doubles) -> product of the diagonal of L
+// left-looking unblocked Cholesky of the lower triangle A (packed, 28 doubles) -> product of the diagonal of L.
+// Every loop has the fixed bound 7 and a compile-time predicate: loops whose bound is an outer (unrolled) index were
+// left rolled by nvcc 12.9, which put A and L in local memory behind runtime indices (3x slower per factorization).
 __device__ __forceinline__ bool chol7_prod(const double (&A)[28], double& prod) {
     double L[28];
 #pragma unroll
     for (int j = 0; j < 7; j++) {
         double ajj = A[LT(j, j)];
 #pragma unroll
-        for (int k = 0; k < j; k++) ajj -= L[LT(j, k)] * L[LT(j, k)];
+        for (int k = 0; k < 7; k++) if (k < j) ajj -= L[LT(j, k)] * L[LT(j, k)];
         if (!(ajj > 0.0)) return false;
         ajj = sqrt(ajj);
         L[LT(j, j)] = ajj;
         const double rinv = 1.0 / ajj;
 #pragma unroll
-        for (int i = j + 1; i < 7; i++) {
+        for (int i = 0; i < 7; i++) if (i > j) {
             double s = A[LT(i, j)];
 #pragma unroll
-            for (int k = 0; k < j; k++) s -= L[LT(i, k)] * L[LT(j, k)];
+            for (int k = 0; k < 7; k++) if (k < j) s -= L[LT(i, k)] * L[LT(j, k)];
             L[LT(i, j)] = s * rinv;
         }
     }
@@ -64,10 +66,38 @@ __device__ __forceinline__ double logdet_sum(const double* __restrict__ cur, con
 #pragma unroll
     for (int i = 0; i < 7; i++)
 #pragma unroll
-        for (int j = 0; j <= i; j++) A[LT(i, j)] = cur[i * 7 + j] + sgn * blk[i * 7 + j];
+        for (int j = 0; j < 7; j++) if (j <= i) A[LT(i, j)] = cur[i * 7 + j] + sgn * blk[i * 7 + j];
     double p;
     if (chol7_prod(A, p)) return 2 * log(p);
     return lu7_logabsdet(cur, blk, sgn);
+}
+
+// Packed form of a block for the selection loops: the 28 entries of the lower triangle, LT order, 224 bytes = 7 whole
+// 32-byte sectors.  A candidate evaluation then moves 224 bytes through 14 128-bit loads instead of 28 sector-sized
+// fetches out of a 392-byte row-major block (the loops are bound by the SM's L2 bandwidth: ~64 B/clk).
+__device__ __forceinline__ void pack_block(const double* __restrict__ blk, double* __restrict__ pk) {
+#pragma unroll
+    for (int i = 0; i < 7; i++)
+#pragma unroll
+        for (int j = 0; j < 7; j++) if (j <= i) pk[LT(i, j)] = blk[i * 7 + j];
+}
+
+// logDet(cur + sgn * B) with the lower triangle of B read from its packed copy; bit-identical to logdet_sum (same
+// additions, same factorization).  The rare LU fallback reads the full row-major block like the row-major path.
+__device__ __forceinline__ double logdet_sum_packed(const double* __restrict__ cur, const double* __restrict__ pk,
+                                                    const double* __restrict__ blkRow, double sgn) {
+    double A[28];
+    const double2* p2 = reinterpret_cast<const double2*>(pk);
+    double B[28];
+#pragma unroll
+    for (int e = 0; e < 14; e++) { const double2 v = p2[e]; B[2 * e] = v.x; B[2 * e + 1] = v.y; }
+#pragma unroll
+    for (int i = 0; i < 7; i++)
+#pragma unroll
+        for (int j = 0; j < 7; j++) if (j <= i) A[LT(i, j)] = cur[i * 7 + j] + sgn * B[LT(i, j)];
+    double p;
+    if (chol7_prod(A, p)) return 2 * log(p);
+    return lu7_logabsdet(cur, blkRow, sgn);
 }
 
 static const int RAW_RING = 1024;    // pre-generated rand() outputs (power of two)

@@ -156,6 +156,7 @@ __global__ void __launch_bounds__(128) k_logdet(const double* __restrict__ mats,
 enum { MTD_GREEDY = 1, MTD_LAZIER_SELECT = 2, MTD_LAZIER_AUTO = 3, MTD_LAZIER_DELETE = 5 };
 static const int MAX_RANDOM_QUERY_TIME = 2000;
 static const int SEL_WIN = 512;      // rand() draws examined per sampling pass
+static const int SA_DPL = 4, SA_WIN = 32 * SA_DPL;   // k_select_ahead: draws per lane / per pass of the sampler warp
 
 struct SelParams {
     const double* blocks;      // batch x stride x 49
@@ -169,6 +170,8 @@ struct SelParams {
     int32_t* outN;             // batch
     int outStride;
     long long* prof;           // optional phase-cycle counters of problem 0 (GFORB_SELECT_PROF=1), else null
+    double* pack;              // batch x stride x 28: packed lower triangles (pack_block), scratch
+    int split;                 // 1: problems whose pool entries are all valid belong to k_select_ahead, the rest to k_select
 };
 
 __global__ void k_rand_stream(uint32_t seed, int n, int32_t* out) {
@@ -189,7 +192,7 @@ __global__ void k_rand_stream(uint32_t seed, int n, int32_t* out) {
 // registers per problem).  Small T trades a longer chain (each thread evaluates cnt / T candidates in turn) for a
 // footprint that lets the extraction kernels of the next step co-reside on the same SMs.
 template <int T>
-__global__ void __launch_bounds__(T) k_select(const SelParams P) {
+__global__ void __launch_bounds__(T, 512 / T) k_select(const SelParams P) {
     constexpr int DPT = SEL_WIN / T;          // rand() draws examined per thread and sampling pass
     constexpr int NW = T / 32;
     extern __shared__ __align__(16) unsigned char smraw[];
@@ -205,14 +208,14 @@ __global__ void __launch_bounds__(T) k_select(const SelParams P) {
     unsigned char* alive = reinterpret_cast<unsigned char*>(list + P.maxPoints);   // `selected` flag per pool entry
     unsigned char* okf = alive + P.maxPoints;                                      // obs_score >= 0
     __shared__ double cur[49];
-    __shared__ double redV[NW];
     __shared__ int redT[NW];
     __shared__ uint32_t s_rs[64];
     __shared__ uint32_t s_raw[RAW_RING];
-    __shared__ int s_cnt, s_pick, s_pos;
+    __shared__ int s_cnt;
+    __shared__ double redV[NW];
+    __shared__ int redT2[NW];
     __shared__ unsigned s_new[16], s_valid[16];
     __shared__ int s_cut[16];
-    __shared__ double s_val;
     const double* blk = P.blocks + (size_t)b * P.stride * 49;
     const double* sc = P.obsScore ? P.obsScore + (size_t)b * P.stride : nullptr;
     int32_t* outIdx = P.outIdx + (size_t)b * P.outStride;
@@ -231,11 +234,16 @@ __global__ void __launch_bounds__(T) k_select(const SelParams P) {
     const size_t szLazier = (size_t)((double)n / (double)k * P.sampleScale);
     // init
     if (tid < 49) cur[tid] = (tid % 8 == 0) ? 0.00001 : 0.0;
+    int allOk = 1;
     for (int i = tid; i < n; i += T) {
         idxA[i] = i; vis[i] = -1; win[i] = 0; alive[i] = deletion ? 1 : 0;
         okf[i] = (sc && sc[i] < 0) ? 0 : 1;
+        allOk &= okf[i];
     }
-    __syncthreads();
+    allOk = __syncthreads_and(allOk);
+    if (P.split && allOk && mtd != MTD_GREEDY) return;      // k_select_ahead owns this problem
+    double* pk = P.pack + (size_t)b * P.stride * 28;
+    for (int c = tid; c < n; c += T) pack_block(blk + (size_t)c * 49, pk + (size_t)c * 28);
     if (deletion && tid < 49) {       // curMat += every block, in pool order (:2370-2380)
         double s = cur[tid];
         for (int i = 0; i < n; i++) s = s + blk[(size_t)i * 49 + tid];
@@ -371,7 +379,8 @@ __global__ void __launch_bounds__(T) k_select(const SelParams P) {
         // ---- evaluate logDet(cur +- block) for every candidate; arg-max, first in list wins ties (strict >)
         double bestV = -DBL_MAX; int bestT = INT_MAX;
         for (int t = tid; t < cnt; t += T) {
-            const double v = logdet_sum(cur, blk + (size_t)list[t] * 49, sgn);
+            const int q = list[t];
+            const double v = logdet_sum_packed(cur, pk + (size_t)q * 28, blk + (size_t)q * 49, sgn);
             if (v > bestV) { bestV = v; bestT = t; }
         }
 #pragma unroll
@@ -380,25 +389,20 @@ __global__ void __launch_bounds__(T) k_select(const SelParams P) {
             const int ot = __shfl_xor_sync(full, bestT, d);
             if (ov > bestV || (ov == bestV && ot < bestT)) { bestV = ov; bestT = ot; }
         }
-        if (lane == 0) { redV[warp] = bestV; redT[warp] = bestT; }
+        if (lane == 0) { redV[warp] = bestV; redT2[warp] = bestT; }
         __syncthreads();
-        if (tid == 0) {
-            double v = redV[0]; int t = redT[0];
-            for (int w = 1; w < NW; w++)
-                if (redV[w] > v || (redV[w] == v && redT[w] < t)) { v = redV[w]; t = redT[w]; }
-            s_pick = (t == INT_MAX) ? -1 : list[t];
-            s_val = v;
-            s_pos = -1;
-        }
-        __syncthreads();
+        double winV = redV[0]; int winT = redT2[0];        // every thread scans the per-warp winners
+#pragma unroll
+        for (int w = 1; w < NW; w++)
+            if (redV[w] > winV || (redV[w] == winV && redT2[w] < winT)) { winV = redV[w]; winT = redT2[w]; }
         SEL_MARK(1)
-        const int pick = s_pick;
+        const int pick = winT == INT_MAX ? -1 : list[winT];
         if (pick < 0) break;                                  // "if (maxLmk == -1) break"
         // ---- update the running matrix, record the pick, erase its column (order preserved)
         if (tid < 49) cur[tid] = cur[tid] + sgn * blk[(size_t)pick * 49 + tid];
         if (tid == 0) {
             alive[pick] = deletion ? 0 : 1;
-            if (!deletion && i < P.outStride) { outIdx[i] = pick; if (outLd) outLd[i] = s_val; }
+            if (!deletion && i < P.outStride) { outIdx[i] = pick; if (outLd) outLd[i] = winV; }
         }
         if (!deletion) nOut = i + 1;
         // lmkIdx stays ascending (identity minus erased columns): every entry >= pick moves one column left
@@ -427,6 +431,209 @@ __global__ void __launch_bounds__(T) k_select(const SelParams P) {
 }
 
 
+// ------------------------------------------------------------------------------------------------ K12b selection, sampler ahead
+// When every pool entry is valid (obs_score >= 0, the normal case) the rejection sampler of the lazier-greedy loops is
+// independent of the picks: round i draws from rand() % (n - i) column NUMBERS until szActualSubset distinct columns
+// were hit, and which pool entry a column holds only matters when the list is evaluated.  So the sampler runs one
+// round AHEAD in a warp of its own (producer), while T evaluator threads (consumers) map columns to pool entries,
+// evaluate logDet(cur +- block), take the arg-max and erase the picked column.  The round's critical path shrinks to
+// evaluate -> arg-max -> update.  Hand-off through two column lists and named barriers (bar.sync / bar.arrive):
+//   FULL[p]  sampler arrives after filling list p          evaluators wait before reading it
+//   EMPTY[p] evaluators arrive after their last read of p   sampler waits before refilling it
+// The rand() stream is consumed in exactly the reference's order (rounds are sampled in order, each draw is either
+// taken or rejected by the reference's rule), so picks, order and log-dets are those of k_select.
+// barrier ids are immediates so that ptxas reserves exactly the six barriers in use
+template <int ID, int N> __device__ __forceinline__ void bar_sync_i() { asm volatile("bar.sync %0, %1;" ::"n"(ID), "n"(N) : "memory"); }
+template <int ID, int N> __device__ __forceinline__ void bar_arrive_i() { asm volatile("bar.arrive %0, %1;" ::"n"(ID), "n"(N) : "memory"); }
+template <int ID, int N> __device__ __forceinline__ void bar_sync2(int p) { if (p) bar_sync_i<ID + 1, N>(); else bar_sync_i<ID, N>(); }
+template <int ID, int N> __device__ __forceinline__ void bar_arrive2(int p) { if (p) bar_arrive_i<ID + 1, N>(); else bar_arrive_i<ID, N>(); }
+
+template <int T>
+__global__ void __launch_bounds__(T + 32, T == 256 ? 1 : (T == 128 ? 3 : 5)) k_select_ahead(const SelParams P) {
+    constexpr int NW = T / 32;                // evaluator warps; warp NW is the sampler
+    constexpr int ALL = T + 32;
+    enum { B_FULL = 1, B_EMPTY = 3, B_EVAL = 5 };
+    extern __shared__ __align__(16) unsigned char smraw[];
+    const unsigned full = 0xffffffffu;
+    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int n = min(P.counts[b], min(P.stride, P.maxPoints));
+    int* idxA = reinterpret_cast<int*>(smraw);
+    int* idxB = idxA + P.maxPoints;
+    int* vis = idxB + P.maxPoints;           // sampler only: round stamp per column
+    int* col0 = vis + P.maxPoints;           // column lists of even / odd rounds
+    int* col1 = col0 + P.maxPoints;
+    int* win = col1 + P.maxPoints;           // sampler only: key of the first draw of a column within a pass
+    __shared__ double cur[49];
+    __shared__ uint32_t s_rs[64];
+    __shared__ uint32_t s_raw[RAW_RING];
+    __shared__ int s_cnt2[2];
+    __shared__ double redV[2][NW];           // per-warp winners, double-buffered over rounds (one barrier per arg-max)
+    __shared__ int redT[2][NW];
+    const double* blk = P.blocks + (size_t)b * P.stride * 49;
+    const double* sc = P.obsScore ? P.obsScore + (size_t)b * P.stride : nullptr;
+    int32_t* outIdx = P.outIdx + (size_t)b * P.outStride;
+    double* outLd = P.outLogdet ? P.outLogdet + (size_t)b * P.outStride : nullptr;
+    const int k = P.k;
+    if (n <= 0 || k >= n) return;            // trivial problems are written by k_select (launched alongside)
+    int mtd = P.mtd;
+    if (mtd == MTD_LAZIER_AUTO) mtd = ((size_t)k * 2 > (size_t)n) ? MTD_LAZIER_DELETE : MTD_LAZIER_SELECT;
+    const bool deletion = mtd == MTD_LAZIER_DELETE;
+    const double sgn = deletion ? -1.0 : 1.0;
+    const int szLazier = (int)min((size_t)((double)n / (double)k * P.sampleScale), (size_t)n);
+    int allOk = 1;
+    for (int i = tid; i < n; i += ALL) {
+        idxA[i] = i; vis[i] = -1; win[i] = 0;
+        if (sc && sc[i] < 0) allOk = 0;
+    }
+    if (tid < 49) cur[tid] = (tid % 8 == 0) ? 0.00001 : 0.0;
+    allOk = __syncthreads_and(allOk);
+    if (!allOk) return;                      // k_select owns this problem
+    if (deletion && tid < 49) {              // curMat += every block, in pool order (:2370-2380)
+        double s = cur[tid];
+        for (int i = 0; i < n; i++) s = s + blk[(size_t)i * 49 + tid];
+        cur[tid] = s;
+    }
+    const int rounds = deletion ? n - k : k;
+    double* pk = P.pack + (size_t)b * P.stride * 28;
+    for (int c = tid; c < n; c += ALL) pack_block(blk + (size_t)c * 49, pk + (size_t)c * 28);
+    __syncthreads();
+    if (warp == NW) {
+        // ================= sampler warp: RANDOM_ACCESS_LAZIER_GREEDY draws (:2895-2921) of round i, column space n - i
+        WarpRand rng;
+        rng.rs = s_rs; rng.raw = s_raw; rng.n = 34;
+        rng.seed(P.seeds ? P.seeds[b] : 1u, lane);
+        int rp = 0;                                   // rand() calls consumed
+        int epoch = 1;                                // sampling pass counter
+        const unsigned lt = (1u << lane) - 1u;
+        for (int i = 0; i < rounds; i++) {
+            const int p = i & 1;
+            int* colp = p ? col1 : col0;
+            const int m = n - i;
+            const int szActual = min(szLazier, m);
+            if (i >= 2) bar_sync2<B_EMPTY, ALL>(p);   // the evaluators are done with round i - 2's list
+            int numHit = 0, rej = 0;
+            bool stop = szActual <= 0;
+            while (!stop) {
+                // one pass = the next 128 draws, 4 per lane (draw number d = h * 32 + lane).  A draw is "new" if its
+                // column was not visited in this round: stamp in vis[] from earlier passes, first-in-pass by atomicMax
+                // on win[] (key grows with the pass number and shrinks with d, so the earliest draw of a pass wins).
+                while (rng.n - 344 < rp + SA_WIN) rng.gen30(lane);
+                int j[SA_DPL]; int key[SA_DPL]; bool seen[SA_DPL];
+#pragma unroll
+                for (int h = 0; h < SA_DPL; h++) {
+                    const int d = h * 32 + lane;
+                    j[h] = (int)(s_raw[(rp + d) & (RAW_RING - 1)] % (uint32_t)m);
+                    seen[h] = vis[j[h]] >= i;
+                    key[h] = (epoch << 7) | (SA_WIN - 1 - d);
+                    if (!seen[h]) atomicMax(&win[j[h]], key[h]);
+                }
+                __syncwarp();
+                unsigned nm[SA_DPL]; bool isNew[SA_DPL];
+#pragma unroll
+                for (int h = 0; h < SA_DPL; h++) {
+                    isNew[h] = !seen[h] && win[j[h]] == key[h];
+                    nm[h] = __ballot_sync(full, isNew[h]);
+                }
+                int cut = INT_MAX, before = numHit, lastNew = -1;      // lastNew: last new draw before group h (uniform)
+                int hbv[SA_DPL];
+#pragma unroll
+                for (int h = 0; h < SA_DPL; h++) {
+                    const int d = h * 32 + lane;
+                    const int hb = before + __popc(nm[h] & lt);       // hits before this draw
+                    hbv[h] = hb;
+                    const bool hitA = isNew[h] && hb + 1 == szActual;  // the draw that completes the subset
+                    int run;                                            // consecutive rejections ending at this draw
+                    if (nm[h] & lt) run = lane - (31 - __clz(nm[h] & lt));
+                    else run = (lastNew >= 0) ? d - lastNew : rej + d + 1;
+                    const bool hitB = !isNew[h] && run >= MAX_RANDOM_QUERY_TIME;
+                    const unsigned cm = __ballot_sync(full, hitA || hitB);
+                    if (cm && cut == INT_MAX) cut = h * 32 + __ffs(cm) - 1;
+                    before += __popc(nm[h]);
+                    if (nm[h]) lastNew = h * 32 + 31 - __clz(nm[h]);
+                }
+                stop = cut != INT_MAX;
+                if (!stop) cut = SA_WIN - 1;                            // last draw the sequential loop consumes
+                int V = 0, lastTaken = -1;
+#pragma unroll
+                for (int h = 0; h < SA_DPL; h++) {
+                    const int d = h * 32 + lane, lo = h * 32;
+                    if (d <= cut && isNew[h]) { vis[j[h]] = i; colp[hbv[h]] = j[h]; }
+                    if (lo <= cut) {
+                        const unsigned take = (cut - lo >= 31) ? full : ((2u << (cut - lo)) - 1u);
+                        const unsigned nw = nm[h] & take;
+                        V += __popc(nw);
+                        if (nw) lastTaken = lo + 31 - __clz(nw);
+                    }
+                }
+                numHit += V;
+                rej = (lastTaken >= 0) ? cut - lastTaken : rej + cut + 1;
+                rp += cut + 1;
+                epoch++;
+                __syncwarp();
+            }
+            if (lane == 0) s_cnt2[p] = numHit;
+            __threadfence_block();
+            bar_arrive2<B_FULL, ALL>(p);
+        }
+        return;
+    }
+    // ================= evaluator threads
+    int m = n;
+    int* idx = idxA; int* idx2 = idxB;
+    int nOut = 0;
+    bool dead = false;                                // "if (maxLmk == -1) break": keep the barrier protocol, do nothing
+    long long tprev = 0;
+    const bool prof = P.prof && b == 0 && tid == 0;
+    if (prof) tprev = clock64();
+    for (int i = 0; i < rounds; i++) {
+        const int p = i & 1;
+        const int* colp = p ? col1 : col0;
+        bar_sync2<B_FULL, ALL>(p);
+        SEL_MARK(0)
+        const int cnt = dead ? 0 : s_cnt2[p];
+        // ---- logDet(cur +- block) of every drawn column's pool entry; arg-max, first drawn wins ties (strict >)
+        double bestV = -DBL_MAX; int bestT = INT_MAX;
+        for (int t = tid; t < cnt; t += T) {
+            const int q = idx[colp[t]];
+            const double v = logdet_sum_packed(cur, pk + (size_t)q * 28, blk + (size_t)q * 49, sgn);
+            if (v > bestV) { bestV = v; bestT = t; }
+        }
+#pragma unroll
+        for (int d = 16; d >= 1; d >>= 1) {
+            const double ov = __shfl_xor_sync(full, bestV, d);
+            const int ot = __shfl_xor_sync(full, bestT, d);
+            if (ov > bestV || (ov == bestV && ot < bestT)) { bestV = ov; bestT = ot; }
+        }
+        if (lane == 0) { redV[i & 1][warp] = bestV; redT[i & 1][warp] = bestT; }
+        bar_sync_i<B_EVAL, T>();
+        double winV = redV[i & 1][0]; int winT = redT[i & 1][0];   // every thread scans the per-warp winners
+#pragma unroll
+        for (int w = 1; w < NW; w++)
+            if (redV[i & 1][w] > winV || (redV[i & 1][w] == winV && redT[i & 1][w] < winT)) { winV = redV[i & 1][w]; winT = redT[i & 1][w]; }
+        const int pick = winT == INT_MAX ? -1 : idx[colp[winT]];
+        SEL_MARK(1)
+        if (i + 2 < rounds) bar_arrive2<B_EMPTY, ALL>(p);     // this thread's last read of list p is behind it
+        if (pick < 0) dead = true;
+        if (!dead) {
+            // ---- update the running matrix, record the pick, erase its column (order preserved)
+            if (tid < 49) cur[tid] = cur[tid] + sgn * blk[(size_t)pick * 49 + tid];
+            if (tid == 0 && !deletion && i < P.outStride) { outIdx[i] = pick; if (outLd) outLd[i] = winV; }
+            if (!deletion) nOut = i + 1;
+            // lmkIdx stays ascending (identity minus erased columns): every entry >= pick moves one column left
+            for (int j = tid; j < m - 1; j += T) { const int a = idx[j]; idx2[j] = (a >= pick) ? idx[j + 1] : a; }
+            m -= 1;
+            { int* t = idx; idx = idx2; idx2 = t; }
+        }
+        bar_sync_i<B_EVAL, T>();
+        SEL_MARK(2)
+    }
+    if (deletion) {
+        // survivors in ascending pool order (:2530-2540) == the columns that are left
+        for (int j = tid; j < m && j < P.outStride; j += T) { outIdx[j] = idx[j]; if (outLd) outLd[j] = 0.0; }
+        if (tid == 0) P.outN[b] = min(m, P.outStride);
+    } else if (tid == 0) P.outN[b] = min(nOut, P.outStride);
+}
+
 }  // namespace gforb
 
 using namespace gforb;
@@ -441,7 +648,7 @@ struct KineSeg {
 struct GforbObs {
     GforbObsConfig cfg;
     int device = 0, lastLaunches = 0;
-    int selThreads = 0, numSMs = 148;
+    int selThreads = 0, numSMs = 148, selAhead = 1;
     int selPad = 0;          // extra dynamic smem of k_select (GFORB_SELECT_SMEM_PAD): caps its CTAs per SM when it shares the GPU
     double Xv[13];
     std::vector<KineSeg> kine;
@@ -622,6 +829,7 @@ int obs_end(GforbObs* O, OCtx& c, int flags) {
     return GFORB_OK;
 }
 
+size_t ahead_smem(int maxPoints) { return (size_t)maxPoints * 6 * sizeof(int) + 16; }
 size_t select_smem(int maxPoints) { return (size_t)maxPoints * (5 * sizeof(int) + 2) + 16; }
 
 }  // namespace
@@ -644,7 +852,7 @@ int gforb_obs_create(const GforbObsConfig* cfg, GforbObs** out) {
     for (int i = 0; i < 13; i++) O->Xv[i] = 0;
     const size_t B = cfg->max_batch, N = cfg->max_points;
     // staging for host-pointer calls: world/octave/score/gate in, blocks + H + scores + uv + selection out
-    GF_CUDA_OK(O->arena.init(B * N * (12 + 4 + 4 + 1 + 392 + 112 + 8 + 8 + 4 + 8 + 64) + B * 256 + (1u << 20)));
+    GF_CUDA_OK(O->arena.init(B * N * (12 + 4 + 4 + 1 + 392 + 112 + 8 + 8 + 4 + 8 + 64 + 224) + B * 256 + (1u << 20)));
     GF_CUDA_OK(cudaMalloc((void**)&O->d_err, sizeof(int)));
     if (const char* e = getenv("GFORB_SELECT_SMEM_PAD")) O->selPad = atoi(e);
     cudaDeviceGetAttribute(&O->numSMs, cudaDevAttrMultiProcessorCount, cfg->device);
@@ -652,7 +860,12 @@ int gforb_obs_create(const GforbObsConfig* cfg, GforbObs** out) {
     GF_CUDA_OK(cudaFuncSetAttribute(k_select<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, selSmem));
     GF_CUDA_OK(cudaFuncSetAttribute(k_select<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, selSmem));
     GF_CUDA_OK(cudaFuncSetAttribute(k_select<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, selSmem));
+    const int aheadSmem = (int)ahead_smem(cfg->max_points);
+    GF_CUDA_OK(cudaFuncSetAttribute(k_select_ahead<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, aheadSmem));
+    GF_CUDA_OK(cudaFuncSetAttribute(k_select_ahead<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, aheadSmem));
+    GF_CUDA_OK(cudaFuncSetAttribute(k_select_ahead<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, aheadSmem));
     if (const char* e = getenv("GFORB_SELECT_THREADS")) O->selThreads = atoi(e);
+    if (getenv("GFORB_SELECT_NO_AHEAD")) O->selAhead = 0;
     *out = O;
     return GFORB_OK;
 }
@@ -842,6 +1055,8 @@ int gforb_obs_select(GforbObs* O, const double* blocks, const double* obs_score,
     P.outN = c.out(out_n, (size_t)batch);
     P.outStride = out_stride;
     P.prof = nullptr;
+    P.pack = (double*)O->arena.take(n * 28 * sizeof(double));
+    if (!P.pack) return GFORB_ERR_CAPACITY;
     if (c.rc) return c.rc;
     static const bool wantProf = getenv("GFORB_SELECT_PROF") != nullptr;
     if (wantProf) { GF_CUDA_OK(cudaMalloc((void**)&P.prof, 8 * sizeof(long long))); GF_CUDA_OK(cudaMemsetAsync(P.prof, 0, 8 * sizeof(long long), c.st)); }
@@ -849,15 +1064,25 @@ int gforb_obs_select(GforbObs* O, const double* blocks, const double* obs_score,
     int T = O->selThreads;
     if (T != 64 && T != 128 && T != 256) T = batch <= O->numSMs / 2 ? 256 : 128;   // B200, 256 problems: 1.62 / 1.56 / 2.28 ms for 256 / 128 / 64
     const size_t smem = select_smem(O->cfg.max_points) + O->selPad;
+    // lazier modes: problems whose pool is all valid go to the sampler-ahead kernel, the others (and the trivial ones)
+    // to the in-order kernel; each CTA decides for its own problem, so both kernels are launched over the batch
+    P.split = (O->selAhead && mtd != MTD_GREEDY) ? 1 : 0;
     if (T == 256) k_select<256><<<batch, 256, smem, c.st>>>(P);
     else if (T == 128) k_select<128><<<batch, 128, smem, c.st>>>(P);
     else k_select<64><<<batch, 64, smem, c.st>>>(P);
     O->lastLaunches = 1;
+    if (P.split) {
+        const size_t asm_ = ahead_smem(O->cfg.max_points);
+        if (T == 256) k_select_ahead<256><<<batch, 256 + 32, asm_, c.st>>>(P);
+        else if (T == 128) k_select_ahead<128><<<batch, 128 + 32, asm_, c.st>>>(P);
+        else k_select_ahead<64><<<batch, 64 + 32, asm_, c.st>>>(P);
+        O->lastLaunches = 2;
+    }
     if (wantProf) {
         long long h[8];
         GF_CUDA_OK(cudaMemcpyAsync(h, P.prof, sizeof(h), cudaMemcpyDeviceToHost, c.st));
         GF_CUDA_OK(cudaStreamSynchronize(c.st));
-        fprintf(stderr, "[gforb] k_select problem 0 cycles: sample %lld  eval+argmax %lld  update+erase %lld\n", h[0], h[1], h[2]);
+        fprintf(stderr, "[gforb] k_select problem 0 cycles: sample (ahead kernel: wait for the sampler) %lld  eval+argmax %lld  update+erase %lld\n", h[0], h[1], h[2]);
         cudaFree(P.prof);
     }
     return obs_end(O, c, flags);
