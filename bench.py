@@ -39,6 +39,16 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def ncu_facts():
+    """per-stage facts taken from the committed ncu --set full capture (profiles/ncu_facts.json, written by
+    tools/ncu_facts.py): DRAM bytes per frame of each stage's kernels and their busiest pipe"""
+    p = os.path.join(ROOT, "profiles", "ncu_facts.json")
+    try:
+        return json.load(open(p))
+    except Exception:
+        return {}
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -152,9 +162,9 @@ def run_ours(args):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     from gf_orb_slam_b200 import synth
-    from gf_orb_slam_b200.pipeline import TrackingFrontEnd
+    from gf_orb_slam_b200.pipeline import LanedFrontEnd
     B = args.batch
-    fe = TrackingFrontEnd(W_, H_, NFEAT, B, n_good=NGOOD, device=local, overlap=not args.no_overlap)
+    fe = LanedFrontEnd(W_, H_, NFEAT, B, lanes=args.lanes, n_good=NGOOD, device=local, overlap=not args.no_overlap)
     # frames sharded across ranks: rank r takes a contiguous chunk of the 2000-frame schedule (1-frame halo inside)
     seq = synth.Sequence(W_, H_)
     chunk = 2000 // max(world_size, 1)
@@ -163,8 +173,7 @@ def run_ours(args):
     frames = seq.frames(t0f, ndist)
     reps = (B + ndist - 1) // ndist
     host = np.concatenate([frames] * reps)[:B]
-    fe.h_images.copy_(torch.from_numpy(host))
-    fe.images.copy_(fe.h_images)
+    fe.load_host_frames(host)
     torch.cuda.synchronize()
 
     def barrier():
@@ -194,14 +203,33 @@ def run_ours(args):
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    fe.ex.set_profiling(True)
+    fe.set_extract_profiling(True)
     fe.profile = True
     ms = timed(fe.step_device, args.steps)
     fe.profile = False
-    stages = fe.ex.stage_times()
-    fe.ex.set_profiling(False)
+    stages = fe.extract_stage_times()
     pipe_stages = fe.stage_times()
     launches = fe.launches_per_step * args.steps
+    # the same stage events with the selection on the main stream (no co-running kernel): per-kernel durations that are
+    # not inflated by the selection kernel of the previous step sharing the SMs
+    ser = LanedFrontEnd(W_, H_, NFEAT, B, lanes=1, n_good=NGOOD, device=local, overlap=False)
+    ser.load_host_frames(host)
+    for _ in range(2):
+        ser.step_device()
+    ser.sync(); torch.cuda.synchronize()
+    ser.set_extract_profiling(True)
+    ser.profile = True
+    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        ser.step_device()
+    ser.sync(); e1.record(); torch.cuda.synchronize()
+    ms_serial = e0.elapsed_time(e1) / args.steps
+    ser.profile = False
+    stages_serial = ser.extract_stage_times()
+    pipe_serial = ser.stage_times()
+    del ser
+    fe.set_extract_profiling(False)
     # end to end: host (pinned) frames in, every result out, copies inside the timed region
     for _ in range(2):
         fe.step_host()
@@ -217,15 +245,26 @@ def run_ours(args):
     peak, peak_src = peaks()
     # dominant kernel of the step (DESIGN.md "Kernels"): algorithmic bytes per launch / its average launch time
     alg = fe.algorithmic_bytes()
-    dom = max(stages, key=lambda s: s[1]) if stages else ("none", 0.0)
+    in_step = dict(stages)
+    dom = max(stages_serial, key=lambda s: s[1]) if stages_serial else ("none", 0.0)     # dominant kernel by its own duration
+    dom_ms = dom[1]        # its duration on one stream with nothing co-running (same run, CUDA events); stage_ms holds the
+                           # in-step figures, which include time shared with the other lane's and the selection's kernels
     dom_bytes = alg["per_stage"].get(dom[0], 0) * B
-    ach = dom_bytes / (dom[1] * 1e-3) / 1e9 if dom[1] > 0 else 0.0
+    ach = dom_bytes / (dom_ms * 1e-3) / 1e9 if dom_ms > 0 else 0.0
+    prof = ncu_facts()
+    kfacts = prof.get("stages", {}).get(dom[0], {})
+    traffic = kfacts.get("dram_bytes_per_frame")
     roof = {"bound": "hbm", "kernel": dom[0], "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-            "traffic": alg["traffic"].get(dom[0]), "peak_source": peak_src,
+            "traffic": traffic * B if traffic is not None else None, "peak_source": peak_src,
             "algorithmic_bytes_per_launch": dom_bytes,
+            "note": "the dominant kernel is bound by the integer ALU pipe, not HBM (ncu: %s); frac is its algorithmic bytes "
+                    "over the measured copy bandwidth" % kfacts.get("ncu", "see profiles/"),
+            "ncu_source": prof.get("source"),
             "stage_ms": {n: round(t, 4) for n, t in stages}, "pipeline_ms": {n: round(t, 4) for n, t in pipe_stages},
+            "stage_ms_serial": {n: round(t, 4) for n, t in stages_serial},
+            "pipeline_ms_serial": {n: round(t, 4) for n, t in pipe_serial},
             "extract_frame_bytes": alg["extract_frame"],
-            "extract_frac_of_hbm": (alg["extract_frame"] * B / (sum(t for _, t in stages) * 1e-3) / 1e9 / peak) if stages else None}
+            "extract_frac_of_hbm": (alg["extract_frame"] * B / (sum(t for _, t in stages_serial) * 1e-3) / 1e9 / peak) if stages_serial else None}
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world_size, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
@@ -233,7 +272,8 @@ def run_ours(args):
         "config": {"workload": WORKLOAD, "frames_per_step_per_gpu": B, "distinct_frames": ndist,
                    "l2": "inputs larger than L2: per step each GPU touches %d MB of frames + %d MB of pyramid planes" % (
                        B * W_ * H_ >> 20, fe.pyramid_bytes() >> 20),
-                   "sharding": "contiguous frame chunks per GPU, 1-frame halo, no collective"},
+                   "sharding": "contiguous frame chunks per GPU, 1-frame halo, no collective",
+                   "lanes_per_gpu": args.lanes, "ms_per_step_one_stream_no_overlap": round(ms_serial, 4)},
         "roofline": roof,
         "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": fe.h2d_bytes(), "d2h_bytes_per_step": fe.d2h_bytes(),
                 "ms_per_step": ms_e2e / args.steps},
@@ -264,6 +304,7 @@ def main():
     ap.add_argument("--ref-frames", type=int, default=32, help="frames per step of the --impl reference arm")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-overlap", action="store_true", help="run the good-feature selection on the main stream")
+    ap.add_argument("--lanes", type=int, default=1, help="independent half-batch pipelines (CUDA streams) per GPU")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

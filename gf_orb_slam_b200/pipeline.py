@@ -92,6 +92,11 @@ class TrackingFrontEnd:
         self.h_sel_idx = torch.zeros((B, n_good), dtype=torch.int32).pin_memory()
         self.h_sel_n = torch.zeros(B, dtype=torch.int32).pin_memory()
         self._uploaded = False
+        # lanes (LanedFrontEnd): the frame before this lane's first frame is the last frame of another lane
+        self.halo_src = None                # TrackingFrontEnd whose slot B feeds this lane's slot 0 (None: own slot B)
+        self.halo_reader = None             # TrackingFrontEnd that reads this lane's slot B as its halo
+        self.ev_extracted = torch.cuda.Event()   # slot B of this lane holds the newest frame
+        self.ev_halo_read = torch.cuda.Event()   # this lane has copied its halo out of halo_src's slot B
 
     # ---- one step = one batch of B frames through the whole front end, everything resident in HBM
     def _mark(self, name=None):
@@ -136,9 +141,17 @@ class TrackingFrontEnd:
         img = self.images if images is None else images
         self._open = None
         self._mark("extract")
-        # halo: last frame of the previous batch becomes slot 0
-        self.kps[0].copy_(self.kps[B]); self.desc[0].copy_(self.desc[B]); self.counts[0:1].copy_(self.counts[B:B + 1])
+        # halo: the frame before this batch becomes slot 0
+        src = self.halo_src if self.halo_src is not None else self
+        if src is not self:
+            main.wait_event(src.ev_extracted)
+        self.kps[0].copy_(src.kps[src.B]); self.desc[0].copy_(src.desc[src.B]); self.counts[0:1].copy_(src.counts[src.B:src.B + 1])
+        if src is not self:
+            self.ev_halo_read.record(main)
+        if self.halo_reader is not None and self.halo_reader is not self:
+            main.wait_event(self.halo_reader.ev_halo_read)                  # slot B may be overwritten now
         self.ex.extract_device(img, self.kps[1:], self.desc[1:], self.counts[1:], stream=st, sync=False)
+        self.ev_extracted.record(main)
         n = self.ex.last_launches()
         self._mark("match")
         self.prev.copy_(self.kps[:B, :, 0:2])                               # vbPrevMatched[i] = F1.mvKeysUn[i].pt
@@ -236,6 +249,106 @@ class TrackingFrontEnd:
     def d2h_bytes(self) -> int:
         return sum(t.numel() * t.element_size() for t in (self.h_kps, self.h_desc, self.h_counts, self.h_m12, self.h_nmatch,
                                                            self.h_sel_idx, self.h_sel_n))
+
+
+class LanedFrontEnd:
+    """The same front end as `lanes` TrackingFrontEnd pipelines of batch/lanes frames each, one CUDA stream per lane:
+    while one lane runs its latency-bound tail (quota / retainBest emulation, candidate resolution) the other lane's
+    ALU-bound kernels (pyramid, FAST, blur) fill the SMs.  Lane j takes frames [j n, (j+1) n) of every batch; its halo
+    frame is the last frame of lane j-1 (of the previous batch for lane 0), handed over with events, so the results are
+    those of one TrackingFrontEnd over the whole batch."""
+
+    def __init__(self, width=752, height=480, nfeatures=1000, batch=64, lanes=2, **kw):
+        assert batch % lanes == 0
+        self.B, self.L, self.n = batch, lanes, batch // lanes
+        self.w, self.h, self.nf = width, height, nfeatures
+        dev = kw.get("device", 0)
+        self.dev = torch.device("cuda", dev)
+        torch.cuda.set_device(self.dev)
+        self.lane = [TrackingFrontEnd(width, height, nfeatures, self.n, **kw) for _ in range(lanes)]
+        self.streams = [torch.cuda.Stream(device=self.dev) for _ in range(lanes)]
+        for j, fe in enumerate(self.lane):
+            fe.halo_src = self.lane[(j - 1) % lanes]
+            fe.halo_reader = self.lane[(j + 1) % lanes]
+        self.ev_fork = torch.cuda.Event()
+        self.ev_join = [torch.cuda.Event() for _ in range(lanes)]
+        self.k, self.sample_scale = self.lane[0].k, self.lane[0].sample_scale
+        self.launches_per_step = 0
+        self._forked = False
+
+    # bench.py / smoke interface ------------------------------------------------------------------------------------
+    @property
+    def profile(self): return self.lane[0].profile
+    @profile.setter
+    def profile(self, v):
+        for fe in self.lane: fe.profile = v
+
+    def set_extract_profiling(self, on):
+        for fe in self.lane: fe.ex.set_profiling(on)
+
+    def set_overlap(self, on):
+        """False: the good-feature selection of every lane runs on the lane's main stream"""
+        for fe in self.lane:
+            if not hasattr(fe, "_s_sel_saved"): fe._s_sel_saved = fe.s_sel
+            fe.s_sel = fe._s_sel_saved if on else None
+
+    def load_host_frames(self, host: np.ndarray):
+        for j, fe in enumerate(self.lane):
+            fe.h_images.copy_(torch.from_numpy(host[j * self.n:(j + 1) * self.n]))
+            fe.images.copy_(fe.h_images)
+
+    def _fork(self):
+        """lane streams start after everything already queued on the caller's stream (once per burst of steps)"""
+        if not self._forked:
+            self.ev_fork.record(torch.cuda.current_stream())
+            for s in self.streams: s.wait_event(self.ev_fork)
+            self._forked = True
+
+    def step_device(self):
+        self._fork()
+        n = 0
+        for fe, s in zip(self.lane, self.streams):
+            with torch.cuda.stream(s):
+                n += fe.step_device()
+        self.launches_per_step = n
+        return n
+
+    def step_host(self):
+        self._fork()
+        for fe, s in zip(self.lane, self.streams):
+            with torch.cuda.stream(s):
+                fe.step_host()
+
+    def sync(self):
+        """the caller's stream waits for every lane (and the lanes' selection / copy streams)"""
+        cur = torch.cuda.current_stream()
+        for j, (fe, s) in enumerate(zip(self.lane, self.streams)):
+            with torch.cuda.stream(s):
+                fe.sync()
+                self.ev_join[j].record(s)
+            cur.wait_event(self.ev_join[j])
+        self._forked = False
+
+    def stage_times(self):
+        return _sum_stage_times([fe.stage_times() for fe in self.lane])
+
+    def extract_stage_times(self):
+        return _sum_stage_times([fe.ex.stage_times() for fe in self.lane])
+
+    def pyramid_bytes(self): return sum(fe.pyramid_bytes() for fe in self.lane)
+    def algorithmic_bytes(self): return self.lane[0].algorithmic_bytes()
+    def h2d_bytes(self): return sum(fe.h2d_bytes() for fe in self.lane)
+    def d2h_bytes(self): return sum(fe.d2h_bytes() for fe in self.lane)
+
+
+def _sum_stage_times(per_lane):
+    """[(stage, ms)] per lane -> [(stage, ms summed over the lanes)]: with L lanes of B/L frames the sum is the time the
+    stage's kernels take for the whole batch"""
+    acc = {}
+    for st in per_lane:
+        for k, t in st:
+            acc[k] = acc.get(k, 0.0) + t
+    return list(acc.items())
 
 
 def cpu_front_end(oracle, frames: np.ndarray, prev_kd, world, score, xv, sigma2, k, sample_scale, window=100, nnratio=0.9,
