@@ -493,6 +493,65 @@ __global__ void __launch_bounds__(32) k_resolve(const RParams R) {
 #include "active.cuh"
 namespace gforb {
 
+// ------------------------------------------------------------------------------------------------ Frame::isInFrustum
+// src/Frame.cc:166-227 for every map point of `batch` frames: thread per point.  cv::Mat arithmetic restated: Rcw * P
+// accumulates each row in double and casts to float before + tcw; cv::norm / Mat::dot accumulate double products.
+struct FrustumParams {
+    const float *Rcw, *tcw, *Ow;          // batch x 9 / 3 / 3
+    float fx, fy, cx, cy;
+    int minX, maxX, minY, maxY;
+    const float *world, *normal, *minDist, *maxDist;
+    const int32_t* counts;
+    int stride;
+    float cosLimit;
+    float scale[MAX_LEVELS];
+    int nlevels;
+    float *u, *v, *viewCos;
+    int32_t* level;
+    uint8_t* flags;
+};
+
+__global__ void __launch_bounds__(128) k_is_in_frustum(const FrustumParams F) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x, b = blockIdx.y;
+    if (i >= min(F.counts[b], F.stride)) return;
+    const size_t p = (size_t)b * F.stride + i;
+    const float* R = F.Rcw + (size_t)b * 9;
+    const float* t = F.tcw + (size_t)b * 3;
+    const float* O = F.Ow + (size_t)b * 3;
+    const float P0 = F.world[p * 3], P1 = F.world[p * 3 + 1], P2 = F.world[p * 3 + 2];
+    uint8_t fl = F.flags[p] & ~1;
+    bool in = true;
+    float Pc[3];
+#pragma unroll
+    for (int r = 0; r < 3; r++) {
+        const double s = (double)R[r * 3 + 0] * (double)P0 + (double)R[r * 3 + 1] * (double)P1 + (double)R[r * 3 + 2] * (double)P2;
+        Pc[r] = (float)s + t[r];
+    }
+    if (Pc[2] < 0.0f) in = false;
+    const float invz = (float)(1.0 / (double)Pc[2]);
+    const float u = F.fx * Pc[0] * invz + F.cx;
+    const float v = F.fy * Pc[1] * invz + F.cy;
+    if (u < (float)F.minX || u > (float)F.maxX) in = false;
+    if (v < (float)F.minY || v > (float)F.maxY) in = false;
+    const float PO0 = P0 - O[0], PO1 = P1 - O[1], PO2 = P2 - O[2];
+    const double n2 = (double)PO0 * (double)PO0 + (double)PO1 * (double)PO1 + (double)PO2 * (double)PO2;
+    const float dist = (float)sqrt(n2);
+    const float minD = F.minDist[p], maxD = F.maxDist[p];
+    if (dist < minD || dist > maxD) in = false;
+    const double dot = (double)PO0 * (double)F.normal[p * 3] + (double)PO1 * (double)F.normal[p * 3 + 1] + (double)PO2 * (double)F.normal[p * 3 + 2];
+    const float viewCos = (float)(dot / (double)dist);
+    if (viewCos < F.cosLimit) in = false;
+    if (in) {
+        const float ratio = dist / minD;
+        int lvl = 0;                                          // std::lower_bound(mvScaleFactors, ratio)
+        while (lvl < F.nlevels && F.scale[lvl] < ratio) lvl++;
+        if (lvl >= F.nlevels) lvl = F.nlevels - 1;
+        F.u[p] = u; F.v[p] = v; F.level[p] = lvl; F.viewCos[p] = viewCos;
+        fl |= 1;
+    }
+    F.flags[p] = fl;
+}
+
 // ------------------------------------------------------------------------------------------------ B1 distance
 __global__ void __launch_bounds__(256) k_distance(const uint4* __restrict__ a, const uint4* __restrict__ b, int n,
                                                   int32_t* __restrict__ out) {
@@ -948,6 +1007,37 @@ int gforb_obs_active_match(GforbObs* O, GforbMatcher* M, const GforbFrameSet* F,
     A.mpFlags = P.mpFlags; A.mpCounts = P.mpCounts; A.mpStride = mps->mp_stride;
     A.nlevels = nlevels; A.nnratio = nnratio; A.numToMatch = num_to_match;
     k_active_match<<<batch, 32, 0, c.st>>>(A);
+    M->lastLaunches++;
+    return end_call(M, c, flags);
+}
+
+int gforb_frame_is_in_frustum(GforbMatcher* M, int batch, const float* Rcw, const float* tcw, const float* Ow, float fx,
+                              float fy, float cx, float cy, int min_x, int max_x, int min_y, int max_y, const float* world,
+                              const float* normal, const float* min_distance, const float* max_distance,
+                              const int32_t* counts, int mp_stride, float viewing_cos_limit, float* proj_x, float* proj_y,
+                              int32_t* scale_level, float* view_cos, uint8_t* mp_flags, int flags, void* stream) {
+    Ctx c;
+    int rc = begin_call(M, batch, flags, stream, c);
+    if (rc) return rc;
+    if (!Rcw || !tcw || !Ow || !world || !normal || !min_distance || !max_distance || !counts || mp_stride <= 0 || !proj_x ||
+        !proj_y || !scale_level || !view_cos || !mp_flags)
+        return GFORB_ERR_ARG;
+    if (mp_stride > M->cfg.max_queries) return GFORB_ERR_CAPACITY;
+    if (batch == 0) return GFORB_OK;
+    const size_t nm = (size_t)batch * mp_stride;
+    FrustumParams F;
+    memset(&F, 0, sizeof(F));
+    F.Rcw = c.in(Rcw, (size_t)batch * 9); F.tcw = c.in(tcw, (size_t)batch * 3); F.Ow = c.in(Ow, (size_t)batch * 3);
+    F.fx = fx; F.fy = fy; F.cx = cx; F.cy = cy; F.minX = min_x; F.maxX = max_x; F.minY = min_y; F.maxY = max_y;
+    F.world = c.in(world, nm * 3); F.normal = c.in(normal, nm * 3);
+    F.minDist = c.in(min_distance, nm); F.maxDist = c.in(max_distance, nm);
+    F.counts = c.in(counts, (size_t)batch); F.stride = mp_stride; F.cosLimit = viewing_cos_limit;
+    for (int i = 0; i < MAX_LEVELS; i++) F.scale[i] = M->scale[i < M->cfg.nlevels ? i : M->cfg.nlevels - 1];
+    F.nlevels = M->cfg.nlevels;
+    F.u = c.out(proj_x, nm, true); F.v = c.out(proj_y, nm, true); F.level = c.out(scale_level, nm, true);
+    F.viewCos = c.out(view_cos, nm, true); F.flags = c.out(mp_flags, nm, true);
+    if (c.rc) return c.rc;
+    k_is_in_frustum<<<dim3((mp_stride + 127) / 128, batch), 128, 0, c.st>>>(F);
     M->lastLaunches++;
     return end_call(M, c, flags);
 }

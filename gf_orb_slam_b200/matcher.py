@@ -113,6 +113,22 @@ class ORBmatcher:
               "gforb_features_in_area")
         return [idx[i, :min(cnt[i], cap)].copy() for i in range(n)], cnt
 
+    # -- bool Frame::isInFrustum(MapPoint*, viewingCosLimit), batched over every map point of B frames
+    def isInFrustum(self, Rcw, tcw, Ow, fx, fy, cx, cy, bounds, world, normal, min_distance, max_distance, counts,
+                    viewingCosLimit, mps: "MapPoints", *, stream=None, sync=True):
+        """src/Frame.cc:166-227.  Rcw (B, 9), tcw / Ow (B, 3), world / normal (B, stride, 3), min/max_distance (B, stride);
+        bounds = (mnMinX, mnMaxX, mnMinY, mnMaxY).  Fills mps.proj_x / proj_y / scale_level / view_cos and bit0 of
+        mps.flags in place."""
+        px, py, lvl, vc, fl = mps.a[0], mps.a[1], mps.a[2], mps.a[3], mps.a[4]
+        dev = is_device(world)
+        check(_lib.lib().gforb_frame_is_in_frustum(self._h, mps.batch, ptr(Rcw), ptr(tcw), ptr(Ow), float(fx), float(fy),
+                                                   float(cx), float(cy), *[int(b) for b in bounds], ptr(world), ptr(normal),
+                                                   ptr(min_distance), ptr(max_distance), ptr(counts), mps.stride,
+                                                   float(viewingCosLimit), ptr(px), ptr(py), ptr(lvl), ptr(vc), ptr(fl),
+                                                   self._flags(dev, is_device(px), sync), C.c_void_p(stream or 0)),
+              "gforb_frame_is_in_frustum")
+        return fl
+
     # -- int SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize=10)
     def SearchForInitialization(self, F1: Frames, F2: Frames, vbPrevMatched, windowSize=10, *, matches12=None,
                                 nmatches=None, stream=None, sync=True):

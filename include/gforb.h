@@ -157,6 +157,17 @@ int gforb_search_by_projection(GforbMatcher* h, const GforbFrameSet* F, const Gf
                                float th, float nnratio, int32_t* frame_mappoints, int32_t* match_score,
                                int32_t* nmatches, int flags, void* stream);
 
+/* Frame::isInFrustum(MapPoint*, viewingCosLimit) (src/Frame.cc:166-227) for every map point of `batch` frames: the
+ * pass that produces the GforbMapPointSet fields SearchByProjection reads.  Rcw / tcw / Ow: batch x 9 / 3 / 3 (Frame::mRcw
+ * row-major, mtcw, mOw); world / normal: batch x mp_stride x 3 (MapPoint::GetWorldPos / GetNormal); min_distance /
+ * max_distance: MapPoint::GetMin/MaxDistanceInvariance.  proj_x, proj_y, scale_level, view_cos are written for the
+ * points in view; mp_flags: in/out, bit0 <- mbTrackInView, the other bits are kept. */
+int gforb_frame_is_in_frustum(GforbMatcher* h, int batch, const float* Rcw, const float* tcw, const float* Ow, float fx,
+                              float fy, float cx, float cy, int min_x, int max_x, int min_y, int max_y, const float* world,
+                              const float* normal, const float* min_distance, const float* max_distance,
+                              const int32_t* counts, int mp_stride, float viewing_cos_limit, float* proj_x, float* proj_y,
+                              int32_t* scale_level, float* view_cos, uint8_t* mp_flags, int flags, void* stream);
+
 /* ORBmatcher::SearchByProjection(Frame& Current, const Frame& Last, th) (src/ORBmatcher.cc:2081-2202).
  * last_mappoints: batch x last.kp_stride ids (-1 = NULL); last_outlier: same shape or NULL; last_world: batch x
  * last.kp_stride x 3 (MapPoint::GetWorldPos of LastFrame.mvpMapPoints[i]); Tcw: batch x 16 row-major (Current.mTcw);

@@ -140,6 +140,8 @@ struct MapPoint {
     bool mbTrackInView = false, mbBad = false;
     uint8_t mDescriptor[32] = {0};
     float mWorldPos[3] = {0, 0, 0};
+    float mNormalVector[3] = {0, 0, 1};              // MapPoint::GetNormal()
+    float mfMinDistance = 0, mfMaxDistance = 0;      // GetMinDistanceInvariance() / GetMaxDistanceInvariance()
     double ObsScore = -1;
     // written by Observability::runMatrixBuilding(MAP_INFO_MATRIX) (src/Observability.cc:627-636)
     float u_proj = 0, v_proj = 0;
@@ -165,6 +167,7 @@ struct Frame {
     float mfScaleFactor = 1.2f;
     std::vector<float> mvLevelSigma2;
     float mTcw[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
+    float mRcw[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}, mtcw[3] = {0, 0, 0}, mOw[3] = {0, 0, 0};   // Frame::UpdatePoseMatrices
     float fx = 0, fy = 0, cx = 0, cy = 0;
 
     Frame() {}
@@ -226,6 +229,37 @@ public:
         for (int i = 0; i < F.N; i++) {
             if (ids[i] >= 0 && ids[i] < M) F.mvpMapPoints[i] = vpMapPoints[ids[i]];
             F.mvpMatchScore[i] = score[i];
+        }
+        return n;
+    }
+
+    // Frame::isInFrustum(pMP, viewingCosLimit) (src/Frame.cc:166-227) for every point of vpMapPoints in one call
+    // (Tracking::SearchReferencePointsInFrustum loops over the local map, src/Tracking.cc): sets mbTrackInView and,
+    // for the points in view, mTrackProjX / mTrackProjY / mnTrackScaleLevel / mTrackViewCos.  Returns how many are in view.
+    int isInFrustum(Frame& F, std::vector<MapPoint*>& vpMapPoints, float viewingCosLimit) {
+        const int M = (int)vpMapPoints.size();
+        if (M == 0) return 0;
+        ensure(std::max(F.N, 1), M, F.mnScaleLevels, F.mfScaleFactor);
+        std::vector<float> world((size_t)M * 3), normal((size_t)M * 3), mind(M), maxd(M), u(M), v(M), vc(M);
+        std::vector<int32_t> lvl(M);
+        std::vector<uint8_t> fl(M, 0);
+        for (int i = 0; i < M; i++) {
+            const MapPoint* p = vpMapPoints[i];
+            std::memcpy(&world[(size_t)i * 3], p->mWorldPos, 12); std::memcpy(&normal[(size_t)i * 3], p->mNormalVector, 12);
+            mind[i] = p->mfMinDistance; maxd[i] = p->mfMaxDistance;
+        }
+        int32_t cnt = M;
+        gforb_throw(gforb_frame_is_in_frustum(h_, 1, F.mRcw, F.mtcw, F.mOw, F.fx, F.fy, F.cx, F.cy, F.mnMinX, F.mnMaxX, F.mnMinY,
+                                              F.mnMaxY, world.data(), normal.data(), mind.data(), maxd.data(), &cnt, M,
+                                              viewingCosLimit, u.data(), v.data(), lvl.data(), vc.data(), fl.data(), 0, nullptr),
+                    "isInFrustum");
+        int n = 0;
+        for (int i = 0; i < M; i++) {
+            MapPoint* p = vpMapPoints[i];
+            p->mbTrackInView = (fl[i] & 1) != 0;
+            if (!p->mbTrackInView) continue;
+            p->mTrackProjX = u[i]; p->mTrackProjY = v[i]; p->mnTrackScaleLevel = lvl[i]; p->mTrackViewCos = vc[i];
+            n++;
         }
         return n;
     }

@@ -253,6 +253,21 @@ def active_match(F: Frame, u, v, level, viewCos, flags, desc, in_pool, obs_mat, 
     return n, left[:nleft.value].copy(), cur.reshape(7, 7)
 
 
+def is_in_frustum(Rcw, tcw, Ow, fx, fy, cx, cy, bounds, world, normal, min_dist, max_dist, cos_limit, nlevels=8, scaleFactor=1.2,
+                  flags=None):
+    """Frame::isInFrustum (src/Frame.cc:166-227) for M map points -> (u, v, level, viewCos, flags)"""
+    f32 = lambda a: np.ascontiguousarray(a, np.float32)
+    Rcw, tcw, Ow, world, normal, min_dist, max_dist = map(f32, (Rcw, tcw, Ow, world, normal, min_dist, max_dist))
+    M = world.shape[0]
+    u = np.zeros(M, np.float32); v = np.zeros(M, np.float32); lvl = np.zeros(M, np.int32); vc = np.zeros(M, np.float32)
+    fl = np.zeros(M, np.uint8) if flags is None else np.ascontiguousarray(flags, np.uint8).copy()
+    cf = C.c_float
+    lib().orc_is_in_frustum(_p(Rcw), _p(tcw), _p(Ow), cf(fx), cf(fy), cf(cx), cf(cy), *[int(b) for b in bounds], nlevels,
+                            cf(scaleFactor), M, _p(world), _p(normal), _p(min_dist), _p(max_dist), cf(cos_limit), _p(u), _p(v),
+                            _p(lvl), _p(vc), _p(fl))
+    return u, v, lvl, vc, fl
+
+
 # ---------------------------------------------------------------- observability
 class Observability:
     def __init__(self, *, f=None, fu=None, fv=None, nRows=480, nCols=752, Cx=0.0, Cy=0.0, k1=0.0, k2=0.0, dx=None, dy=None):

@@ -219,6 +219,20 @@ int orc_obs_select(const double* blocks, const double* obsScore, int n, int k, i
     return (int)sub.size();
 }
 
+// Frame::isInFrustum for M map points (src/Frame.cc:166-227); flags[i] bit0 <- mbTrackInView
+void orc_is_in_frustum(const float* Rcw, const float* tcw, const float* Ow, float fx, float fy, float cx, float cy, int minX,
+                       int maxX, int minY, int maxY, int nlevels, float scaleFactor, int M, const float* world,
+                       const float* normal, const float* minDist, const float* maxDist, float cosLimit, float* u, float* v,
+                       int* level, float* viewCos, uint8_t* flags) {
+    std::vector<float> sf(nlevels, 1.0f);
+    for (int i = 1; i < nlevels; i++) sf[i] = sf[i - 1] * scaleFactor;
+    for (int i = 0; i < M; i++) {
+        const bool in = isInFrustum(Rcw, tcw, Ow, fx, fy, cx, cy, minX, maxX, minY, maxY, sf, world + 3 * i, normal + 3 * i,
+                                    minDist[i], maxDist[i], cosLimit, u[i], v[i], level[i], viewCos[i]);
+        flags[i] = (uint8_t)((flags[i] & ~1) | (in ? 1 : 0));
+    }
+}
+
 // Observability::runActiveMapMatching (src/Observability.cc:1249-1524).  Map-point SoA as in orc_search_by_projection;
 // in_pool[i] = (updateAtFrameId == frame id); cur_mat (49) in: mBaseInfoMat, out: accumulated matrix; the frame's
 // mvpMapPoints / mvpMatchScore are updated in place; left_idx receives mLeftMapPoints, *left_n its size.

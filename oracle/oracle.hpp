@@ -107,6 +107,13 @@ struct MapPointView {   // the MapPoint fields SearchByProjection reads (include
     uint8_t desc[32];
 };
 
+// Frame::isInFrustum (src/Frame.cc:166-227) on the fields it reads: Rcw (3x3 row-major), tcw, Ow, intrinsics, image
+// bounds and mvScaleFactors.  Returns mbTrackInView and, when true, fills u, v, level, viewCos.
+bool isInFrustum(const float* Rcw, const float* tcw, const float* Ow, float fx, float fy, float cx, float cy, int mnMinX,
+                 int mnMaxX, int mnMinY, int mnMaxY, const std::vector<float>& mvScaleFactors, const float* P,
+                 const float* Pn, float minDistance, float maxDistance, float viewingCosLimit, float& u, float& v,
+                 int& level, float& viewCos);
+
 class ORBmatcher {
 public:
     static const int TH_LOW = 50, TH_HIGH = 100, HISTO_LENGTH = 30;

@@ -329,4 +329,39 @@ void ORBmatcher::ComputeThreeMaxima(const std::vector<int>* histo, int L, int& i
     else if (max3 < 0.1f * (float)max1) ind3 = -1;
 }
 
+// src/Frame.cc:166-227.  cv::Mat arithmetic restated: Rcw*P accumulates each row in double and casts to float before
+// + tcw (cv::gemm, CV_32F); cv::norm and Mat::dot of CV_32F vectors accumulate double products and return double.
+bool isInFrustum(const float* Rcw, const float* tcw, const float* Ow, float fx, float fy, float cx, float cy, int mnMinX,
+                 int mnMaxX, int mnMinY, int mnMaxY, const std::vector<float>& mvScaleFactors, const float* P,
+                 const float* Pn, float minDistance, float maxDistance, float viewingCosLimit, float& u, float& v,
+                 int& level, float& viewCos) {
+    float Pc[3];
+    for (int r = 0; r < 3; r++) {
+        double s = (double)Rcw[r * 3 + 0] * P[0] + (double)Rcw[r * 3 + 1] * P[1] + (double)Rcw[r * 3 + 2] * P[2];
+        Pc[r] = (float)s + tcw[r];
+    }
+    const float PcX = Pc[0], PcY = Pc[1], PcZ = Pc[2];
+    if (PcZ < 0.0) return false;
+    const float invz = 1.0 / PcZ;
+    u = fx * PcX * invz + cx;
+    v = fy * PcY * invz + cy;
+    if (u < mnMinX || u > mnMaxX) return false;
+    if (v < mnMinY || v > mnMaxY) return false;
+    float PO[3];
+    for (int r = 0; r < 3; r++) PO[r] = P[r] - Ow[r];
+    double n2 = 0;
+    for (int r = 0; r < 3; r++) n2 += (double)PO[r] * PO[r];
+    const float dist = std::sqrt(n2);
+    if (dist < minDistance || dist > maxDistance) return false;
+    double dot = 0;
+    for (int r = 0; r < 3; r++) dot += (double)PO[r] * Pn[r];
+    viewCos = dot / dist;
+    if (viewCos < viewingCosLimit) return false;
+    const float ratio = dist / minDistance;
+    int nPredictedLevel = (int)(std::lower_bound(mvScaleFactors.begin(), mvScaleFactors.end(), ratio) - mvScaleFactors.begin());
+    if (nPredictedLevel >= (int)mvScaleFactors.size()) nPredictedLevel = (int)mvScaleFactors.size() - 1;
+    level = nPredictedLevel;
+    return true;
+}
+
 }  // namespace oracle

@@ -241,3 +241,47 @@ def test_allpairs_top2():
     k0 = m.AllPairsTop2(qd, dd[:h], idx_base=1000).clone(); k1 = m.AllPairsTop2(qd, dd[h:], idx_base=1000 + h).clone()
     merged = m.Top2Merge(torch.stack([k0, k1])).cpu().numpy()
     assert np.array_equal(merged, keys)
+
+
+def test_is_in_frustum(orc):
+    """Frame::isInFrustum (src/Frame.cc:166-227) batched: flags, projections, predicted level and viewing cosine are
+    bit-equal to the oracle for points inside, outside, behind the camera, too near / far and seen from behind."""
+    from gf_orb_slam_b200 import ORBmatcher, MapPoints
+    B, M = 3, 5000
+    fx, fy, cx, cy = 457.3, 457.6, 367.2, 248.4
+    bounds = (0, W, 0, H)
+    rng = np.random.default_rng(5)
+    Rs, ts, Os = [], [], []
+    for b in range(B):
+        a = 0.1 * (b + 1)
+        c, s_ = np.cos(a), np.sin(a)
+        R = (np.array([[c, 0, s_], [0, 1, 0], [-s_, 0, c]]) @ np.array([[1, 0, 0], [0, np.cos(0.05), -np.sin(0.05)], [0, np.sin(0.05), np.cos(0.05)]])).astype(np.float32)
+        t = np.array([0.2 * b, -0.1, 0.3], np.float32)
+        Rs.append(R.reshape(9)); ts.append(t); Os.append((-R.T.astype(np.float32) @ t).astype(np.float32))
+    Rcw = np.stack(Rs); tcw = np.stack(ts); Ow = np.stack(Os)
+    world = (rng.uniform(-6, 6, size=(B, M, 3)) * np.array([1, 1, 1.5])).astype(np.float32)
+    normal = rng.normal(size=(B, M, 3)).astype(np.float32)
+    normal[:, ::2] = world[:, ::2] - Ow[:, None, :]            # half of the normals look along the viewing ray
+    normal /= np.linalg.norm(normal, axis=2, keepdims=True).astype(np.float32)
+    dist = np.linalg.norm(world - Ow[:, None, :], axis=2).astype(np.float32)
+    min_d = (dist * rng.uniform(0.2, 1.1, size=(B, M))).astype(np.float32)
+    max_d = (dist * rng.uniform(0.9, 3.0, size=(B, M))).astype(np.float32)
+    counts = np.array([M, M - 11, M], np.int32)
+    z = lambda dt: np.zeros((B, M), dt)
+    flags = (rng.integers(0, 4, size=(B, M)) & 2).astype(np.uint8)       # bit1 (bad) must survive
+    flags0 = flags.copy()
+    mps = MapPoints(z(np.float32), z(np.float32), z(np.int32), z(np.float32), flags, np.zeros((B, M, 32), np.uint8), counts)
+    m = ORBmatcher(0.8, True, max_batch=B, max_keypoints=64, max_queries=M)
+    m.isInFrustum(Rcw, tcw, Ow, fx, fy, cx, cy, bounds, world, normal, min_d, max_d, counts, 0.5, mps)
+    nin = 0
+    for b in range(B):
+        n = int(counts[b])
+        eu, ev, el, ec, ef = orc.is_in_frustum(Rcw[b], tcw[b], Ow[b], fx, fy, cx, cy, bounds, world[b, :n], normal[b, :n],
+                                               min_d[b, :n], max_d[b, :n], 0.5, flags=flags0[b, :n])
+        assert np.array_equal(mps.a[4][b, :n], ef), b
+        assert np.array_equal(mps.a[4][b, n:], flags0[b, n:])
+        k = (ef & 1) == 1
+        nin += int(k.sum())
+        for got, exp in ((mps.a[0], eu), (mps.a[1], ev), (mps.a[2], el), (mps.a[3], ec)):
+            assert np.array_equal(got[b, :n][k], exp[k]), b
+    assert 200 < nin < B * M // 2
