@@ -1,0 +1,136 @@
+"""GPU tests of the whole front end at the bench's full size (256 frames of 752x480, 1000 keypoints, pick 100) through
+size-independent properties, plus a sampled bit-exact comparison against the CPU oracle, and agreement of the selection
+kernel's launch variants."""
+import hashlib
+import os
+
+import numpy as np
+import pytest
+
+from gf_orb_slam_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+W, H, NF, K = 752, 480, 1000, 100
+
+
+def _run(frames, batch, lanes=1):
+    """all frames through the front end in steps of `batch`; returns per-frame numpy results"""
+    import torch
+    from gf_orb_slam_b200.pipeline import LanedFrontEnd
+    fe = LanedFrontEnd(W, H, NF, batch, lanes=lanes, n_good=K)
+    n = batch // lanes
+    out = []
+    for s in range(0, frames.shape[0], batch):
+        fe.load_host_frames(frames[s:s + batch])
+        fe.step_device()
+        fe.sync()
+        torch.cuda.synchronize()
+        for j, ln in enumerate(fe.lane):
+            res = [t.cpu().numpy().copy() for t in (ln.kps[1:], ln.desc[1:], ln.counts[1:], ln.m12, ln.nmatch, ln.sel_idx,
+                                                    ln.sel_ld, ln.sel_n)]
+            for b in range(n):
+                out.append(tuple(r[b] for r in res))
+    return out
+
+
+def _sha(res, skip_first_match=True):
+    h = hashlib.sha1()
+    for t, (kps, desc, cnt, m12, nm, sidx, sld, sn) in enumerate(res):
+        c = int(cnt)
+        h.update(kps[:c].tobytes()); h.update(desc[:c].tobytes())
+        if t > 0:
+            h.update(m12.tobytes()); h.update(np.int32(nm).tobytes())
+        h.update(sidx[:int(sn)].tobytes()); h.update(sld[:int(sn)].tobytes())
+    return h.hexdigest()
+
+
+@pytest.fixture(scope="module")
+def full():
+    frames = synth.Sequence(W, H).frames(0, 256)
+    return frames, _run(frames, 256)
+
+
+def test_full_size_invariants(full):
+    frames, res = full
+    assert len(res) == 256
+    for t, (kps, desc, cnt, m12, nm, sidx, sld, sn) in enumerate(res):
+        c = int(cnt)
+        assert 0 < c <= NF
+        x, y, octv = kps[:c, 0], kps[:c, 1], kps[:c].view(np.int32)[:, 5]
+        assert (x >= 0).all() and (x < W).all() and (y >= 0).all() and (y < H).all()
+        assert (octv >= 0).all() and (octv < 8).all() and (np.diff(octv) >= 0).all()      # level-major order
+        ang = kps[:c, 3]
+        assert (ang >= 0).all() and (ang < 360).all()
+        if t > 0:
+            m = m12[m12 >= 0]
+            assert len(m) == int(nm) and len(np.unique(m)) == len(m) and (m < c).all()     # vnMatches12 is injective
+            assert int(nm) > 50                                                           # consecutive frames do match
+        s = sidx[:int(sn)]
+        assert int(sn) == min(K, c) and len(np.unique(s)) == len(s) and (s >= 0).all() and (s < c).all()
+        if c > K:
+            assert (np.diff(sld[:int(sn)]) >= 0).all()                                    # log det grows with every pick
+
+
+def test_batch_size_and_lanes_do_not_change_results(full):
+    """the same 256 frames in 4 steps of 64 (1-frame halo between steps) and in 2 lanes give the same bytes"""
+    frames, res = full
+    ref = _sha(res)
+    assert _sha(_run(frames, 64)) == ref
+    assert _sha(_run(frames, 256, lanes=2)) == ref
+    assert _sha(_run(frames, 256)) == ref                                                 # and the run is deterministic
+
+
+def test_sampled_frames_match_oracle(orc, full):
+    from gf_orb_slam_b200._lib import KP_DTYPE
+    from gf_orb_slam_b200.pipeline import TrackingFrontEnd, cpu_front_end
+    frames, res = full
+    fe = TrackingFrontEnd(W, H, NF, 1, n_good=K)            # only for the constants of the synthetic map points
+    for t in (1, 97, 255):
+        exp = cpu_front_end(orc, frames[t - 1:t + 1], None, fe.world_h, fe.score_h, fe.xv_h, fe.sigma2_h, K, fe.sample_scale)
+        ek, ed, em12, enm, esi, esl = exp[1]
+        kps, desc, cnt, m12, nm, sidx, sld, sn = res[t]
+        c = int(cnt)
+        assert c == len(ek) and kps[:c].copy().view(KP_DTYPE).reshape(-1).tobytes() == ek.tobytes()
+        assert np.array_equal(desc[:c], ed)
+        assert int(nm) == enm and np.array_equal(m12[:len(em12)], em12)
+        assert int(sn) == len(esi) and np.array_equal(sidx[:int(sn)], esi)
+        assert np.allclose(sld[:int(sn)], esl, rtol=1e-5, atol=0)        # north_star tolerance for log-det scores
+
+
+@pytest.mark.parametrize("mtd,k", [(2, 100), (5, 700), (3, 120)])
+def test_selection_variants_agree(mtd, k):
+    """threads per problem (64 / 128 / 256) and the sampler-ahead vs in-order kernels are launch choices only"""
+    from gf_orb_slam_b200.observability import Observability
+    from gf_orb_slam_b200.pipeline_consts import EUROC_CAM, SIMU_XV, level_sigma2, simu_visible_from
+    B, n = 6, 900
+    outs = []
+    for env in ({"GFORB_SELECT_THREADS": "256"}, {"GFORB_SELECT_THREADS": "128"}, {"GFORB_SELECT_THREADS": "64"},
+                {"GFORB_SELECT_NO_AHEAD": "1"}):
+        old = {key: os.environ.get(key) for key in ("GFORB_SELECT_THREADS", "GFORB_SELECT_NO_AHEAD")}
+        for key in old:
+            os.environ.pop(key, None)
+        os.environ.update(env)
+        try:
+            ob = Observability(**EUROC_CAM, max_batch=B, max_points=n)
+        finally:
+            for key, v in old.items():
+                os.environ.pop(key, None)
+                if v is not None:
+                    os.environ[key] = v
+        ob.set_state(SIMU_XV); ob.predictPWLSVec(0.1, 1)
+        Xv = np.repeat(ob.kinematic(0)["Xv"][None], B, 0)
+        cl = [synth.landmark_cloud(n, 300 + b, visible_from=simu_visible_from(W, H)) for b in range(B)]
+        world = np.stack([c[0] for c in cl]); octave = np.stack([c[1] for c in cl]).astype(np.int32)
+        score = np.stack([c[2] for c in cl]).astype(np.int32)
+        valid = np.ones((B, n), np.uint8)
+        valid[B - 1, ::13] = 0                   # the last problem has invalid pool entries -> in-order kernel
+        counts = np.array([n, n - 5, n, n // 2, n, n], np.int32)
+        blocks, osc = ob.build_info_frame(Xv, world, octave, score, valid, counts, level_sigma2())
+        idx, ld, cnt = ob.select(blocks, osc, counts, k, mtd, 9.0, np.arange(1, B + 1, dtype=np.uint32))
+        outs.append((idx.copy(), ld.copy(), cnt.copy()))
+    for o in outs[1:]:
+        assert np.array_equal(o[2], outs[0][2])
+        for b in range(B):
+            c = int(o[2][b])
+            assert np.array_equal(o[0][b, :c], outs[0][0][b, :c]) and np.array_equal(o[1][b, :c], outs[0][1][b, :c])
