@@ -420,12 +420,34 @@ __global__ void __launch_bounds__(128) k_level_retain(const LevelPlan* __restric
 
 // ------------------------------------------------------------------------------------------------ K4 orient
 // IC_Angle on the unblurred level (src/ORBextractor.cc:131-158) + KeyPoint emission (:738-745, :865-871).
-// One warp per keypoint slot; lane = patch column.
+// One warp per keypoint slot.  The circular patch (31 rows, |u| <= umax[|v|]) is cut into 31 x 8 tasks of four
+// horizontally adjacent pixels (u = -16 + 4c .. -13 + 4c); a lane takes 8 tasks, fetches the four bytes as two aligned
+// words + one funnel shift and reduces them with two IDP.4A: sum u * I with the masked column offsets as signed byte
+// weights, and the masked row sum (-> v * row sum).  All sums are exact int32.
+__device__ __forceinline__ int dp4a_s8u8(int w, uint32_t px, int acc) {
+    int d;
+    asm("dp4a.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(w), "r"(px), "r"(acc));
+    return d;
+}
+
 __global__ void __launch_bounds__(256) k_orient(const uint8_t* __restrict__ pyr, size_t framePyr,
                                                 const LevelPlan* __restrict__ levels, int nLevels,
                                                 const uint32_t* __restrict__ lvlKp, size_t frameKp, int kpCapTotal,
                                                 const int* __restrict__ lvlCount, GforbKeyPoint* __restrict__ kps,
                                                 int32_t* __restrict__ counts, int nfeatures) {
+    __shared__ int2 s_w[256];                 // task (row * 8 + chunk) -> {u weights (4 x s8), membership (4 x 0/1)}
+    {
+        const int row = threadIdx.x >> 3, c = threadIdx.x & 7, v = row - HALF_PATCH;
+        const int d = row < 2 * HALF_PATCH + 1 ? c_umax[v < 0 ? -v : v] : -1;
+        uint32_t wu = 0, w1 = 0;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const int u = -16 + 4 * c + k;
+            if ((u < 0 ? -u : u) <= d) { wu |= (uint32_t)(u & 0xff) << (8 * k); w1 |= 1u << (8 * k); }
+        }
+        s_w[threadIdx.x] = make_int2((int)wu, (int)w1);
+    }
+    __syncthreads();
     const int slot = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), b = blockIdx.y, lane = threadIdx.x & 31;
     if (slot >= kpCapTotal) return;
     int l = 0, base = 0;
@@ -441,23 +463,21 @@ __global__ void __launch_bounds__(256) k_orient(const uint8_t* __restrict__ pyr,
     if (i >= n) return;
     const uint32_t e = lvlKp[(size_t)b * frameKp + slot];
     const int x = e & 0xfff, y = (e >> 12) & 0xfff, score = e >> 24;
-    const uint8_t* center = pyr + (size_t)b * framePyr + L.off + (size_t)(EDGE + y) * L.pitch + EDGE + x;
-    // lane = patch column u = lane - 15 (lane 31 idle): every row of the circular patch is one contiguous <= 31-byte
-    // segment read by the whole warp; m10 = sum u * I, m01 = sum v * I (exact int32)
+    // plane column of u = -16 is EDGE + x - 16 = x; planes, pitches and plane offsets are multiples of 4 bytes
+    const uint32_t* w00 = reinterpret_cast<const uint32_t*>(pyr + (size_t)b * framePyr + L.off + (size_t)(EDGE + y - HALF_PATCH) * L.pitch) +
+                          (x >> 2) + (lane & 7);
+    const int sh = (x & 3) * 8, pw = L.pitch >> 2;
     int m10 = 0, m01 = 0;
-    {
-        const int u = lane - HALF_PATCH, au = abs(u);
-        int colsum = 0;
 #pragma unroll
-        for (int v = -HALF_PATCH; v <= HALF_PATCH; ++v) {
-            const int d = c_umax[v < 0 ? -v : v];
-            if (au <= d && lane < 31) {
-                const int I = center[(ptrdiff_t)v * L.pitch + u];
-                colsum += I;
-                m01 += v * I;
-            }
+    for (int it = 0; it < 8; it++) {
+        const int row = it * 4 + (lane >> 3);                     // 0..31, row 31 has empty weights
+        const int2 w = s_w[it * 32 + lane];
+        if (row < 2 * HALF_PATCH + 1) {
+            const uint32_t* wp = w00 + row * pw;
+            const uint32_t px = __funnelshift_r(__ldg(wp), __ldg(wp + 1), sh);
+            m10 = dp4a_s8u8(w.x, px, m10);
+            m01 += (row - HALF_PATCH) * (int)__dp4a((uint32_t)w.y, px, 0u);
         }
-        m10 = u * colsum;
     }
     m10 = __reduce_add_sync(0xffffffffu, m10);
     m01 = __reduce_add_sync(0xffffffffu, m01);

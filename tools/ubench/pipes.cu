@@ -31,6 +31,9 @@ __global__ void __launch_bounds__(256) k(uint32_t* out, uint32_t seed) {
             if (OP == 13) a[i] = __vminu2(__vmaxu2(a[i], b), c);
             if (OP == 14) { __half2 x = *reinterpret_cast<__half2*>(&a[i]); x = __hmin2(__hmax2(x, *reinterpret_cast<__half2*>(&b)), *reinterpret_cast<__half2*>(&c)); a[i] = *reinterpret_cast<uint32_t*>(&x); }
             if (OP == 15) { if (i < 4) a[i] = __vimin3_u16x2(a[i], b, c); else { __half2 x = *reinterpret_cast<__half2*>(&a[i]); x = __hmin2(__hmax2(x, *reinterpret_cast<__half2*>(&b)), *reinterpret_cast<__half2*>(&c)); a[i] = *reinterpret_cast<uint32_t*>(&x); } }
+            if (OP == 17) a[i] = __dp4a(a[i], b, c);
+            if (OP == 18) a[i] = __dp2a_lo(a[i], b, c);
+            if (OP == 19) a[i] = __vsadu4(a[i], b) + c;
             if (OP == 16) { if (i < 4) a[i] = a[i] * b + c; else a[i] = __vimin3_u16x2(a[i], b, c); }
         }
         if (OP == 5) {   // interleave with half2 max on a second set
@@ -62,5 +65,6 @@ void run(const char* name, int opsPerIter) {
 int main() {
     run<0>("vimax3_u16x2", 8); run<6>("vimin3_u16x2", 8); run<1>("vmaxu2 (2-input)", 8); run<2>("hmax2 on raw bits", 8);
     run<3>("prmt", 8); run<4>("imad", 8); run<5>("vimax3 + hmin2 interleaved", 16); run<7>("max3 u32", 8); run<8>("shf funnel", 8); run<9>("lop3 select", 8); run<10>("iadd", 8); run<11>("shr+lop3", 8); run<12>("vminu2", 8); run<13>("vmin(vmax) 2x2-input int", 16); run<14>("hmin(hmax) 2x2-input half", 16); run<15>("4 vimin3 + 4x2 half (indep)", 12); run<16>("4 imad + 4 vimin3 (indep)", 8);
+    run<17>("dp4a (IDP.4A)", 8); run<18>("dp2a_lo (IDP.2A)", 8); run<19>("vsadu4 + add", 8);
     return 0;
 }
