@@ -355,7 +355,7 @@ __global__ void k_quota(const LevelPlan* __restrict__ levels, const CellPlan* __
 // per cell: filter the candidate list to the threshold in force (order preserved), retainBest, append at the
 // cell's offset of the level buffer.  One warp per cell; the selection itself is sequential (lane 0).
 static const int RET_WARPS = 4;
-static const int RET_SMEM = 1536;   // entries per warp kept in shared memory
+static const int RET_SMEM = 768;    // entries per warp kept in shared memory (3 KB: 16 CTAs = 64 warps per SM)
 __global__ void __launch_bounds__(RET_WARPS * 32) k_cell_retain(const CellPlan* __restrict__ cells,
                                                                 const LevelPlan* __restrict__ levels, int nCellsTotal,
                                                                 uint32_t* __restrict__ cand, size_t frameCand,
