@@ -39,12 +39,14 @@ class TrackingFrontEnd:
         self.sample_scale = sample_scale_for(nfeatures, n_good, error_bound)
         z = lambda *s, dt=torch.float32: torch.zeros(s, dtype=dt, device=self.dev)
         self.images = z(B, height, width, dt=torch.uint8)
-        self.kps = z(B + 1, nf, 7)                       # slot 0 = halo (last frame of the previous batch)
-        self.desc = z(B + 1, nf, 32, dt=torch.uint8)
-        self.counts = z(B + 1, dt=torch.int32)
-        self.prev = z(B, nf, 2)
-        self.m12 = z(B, nf, dt=torch.int32)
-        self.nmatch = z(B, dt=torch.int32)
+        # keypoints / descriptors / matches are double-buffered over steps: the matcher of step t runs on its own stream
+        # while the main stream already extracts step t+1 into the other buffer
+        self.kps2 = [z(B + 1, nf, 7) for _ in range(2)]          # slot 0 = halo (last frame of the previous batch)
+        self.desc2 = [z(B + 1, nf, 32, dt=torch.uint8) for _ in range(2)]
+        self.counts2 = [z(B + 1, dt=torch.int32) for _ in range(2)]
+        self.prev2 = [z(B, nf, 2) for _ in range(2)]
+        self.m12_2 = [z(B, nf, dt=torch.int32) for _ in range(2)]
+        self.nmatch2 = [z(B, dt=torch.int32) for _ in range(2)]
         # synthetic matched map points of every keypoint slot (tools/simu_greedy.cc recipe, fixed per slot)
         world, _, score, _ = synth.landmark_cloud(nf, cloud_seed, visible_from=simu_visible_from(width, height))
         self.world_h, self.score_h = world, score
@@ -76,9 +78,12 @@ class TrackingFrontEnd:
         self.t = 0                          # steps issued
         self.images2 = [self.images, z(B, height, width, dt=torch.uint8)]
         self.seeds = torch.ones(B, dtype=torch.int32, device=self.dev)
-        self.F1 = Frames(self.kps[:B], self.desc[:B], self.counts[:B], width, height)
-        self.F2 = Frames(self.kps[1:], self.desc[1:], self.counts[1:], width, height)
-        self.kps_i32 = self.kps.view(torch.int32)
+        self.F1 = [Frames(self.kps2[i][:B], self.desc2[i][:B], self.counts2[i][:B], width, height) for i in range(2)]
+        self.F2 = [Frames(self.kps2[i][1:], self.desc2[i][1:], self.counts2[i][1:], width, height) for i in range(2)]
+        self.kps_i32 = [k.view(torch.int32) for k in self.kps2]
+        self.s_match = torch.cuda.Stream(device=self.dev) if overlap else None
+        self.ev_extract = [torch.cuda.Event() for _ in range(2)]
+        self.ev_match = [torch.cuda.Event() for _ in range(2)]
         self.launches_per_step = 0
         self.profile = False
         self._ev = []                       # (stage, start, end) torch events recorded while self.profile
@@ -111,6 +116,16 @@ class TrackingFrontEnd:
 
     # the buffers of the most recently issued step (valid after sync())
     @property
+    def kps(self): return self.kps2[(self.t - 1) & 1]
+    @property
+    def desc(self): return self.desc2[(self.t - 1) & 1]
+    @property
+    def counts(self): return self.counts2[(self.t - 1) & 1]
+    @property
+    def m12(self): return self.m12_2[(self.t - 1) & 1]
+    @property
+    def nmatch(self): return self.nmatch2[(self.t - 1) & 1]
+    @property
     def blocks(self): return self.blocks2[(self.t - 1) & 1]
     @property
     def obs_score(self): return self.obs_score2[(self.t - 1) & 1]
@@ -127,6 +142,8 @@ class TrackingFrontEnd:
         if self.s_sel is not None:
             for e in self.ev_sel:
                 cur.wait_event(e)
+        for e in self.ev_match:
+            cur.wait_event(e)
         cur.wait_event(self.ev_d2h)
         for e in self.ev_d2h_sel:
             cur.wait_event(e)
@@ -142,27 +159,39 @@ class TrackingFrontEnd:
         self._open = None
         self._mark("extract")
         # halo: the frame before this batch becomes slot 0
+        kps, desc, counts = self.kps2[p], self.desc2[p], self.counts2[p]
         src = self.halo_src if self.halo_src is not None else self
         if src is not self:
             main.wait_event(src.ev_extracted)
-        self.kps[0].copy_(src.kps[src.B]); self.desc[0].copy_(src.desc[src.B]); self.counts[0:1].copy_(src.counts[src.B:src.B + 1])
+        main.wait_event(self.ev_match[p])                                   # the matcher of step t-2 is done with buffer p
+        skps, sdesc, scounts = src.kps, src.desc, src.counts                # newest buffers of the halo source
+        kps[0].copy_(skps[src.B]); desc[0].copy_(sdesc[src.B]); counts[0:1].copy_(scounts[src.B:src.B + 1])
         if src is not self:
             self.ev_halo_read.record(main)
         if self.halo_reader is not None and self.halo_reader is not self:
-            main.wait_event(self.halo_reader.ev_halo_read)                  # slot B may be overwritten now
-        self.ex.extract_device(img, self.kps[1:], self.desc[1:], self.counts[1:], stream=st, sync=False)
+            main.wait_event(self.halo_reader.ev_halo_read)                  # the other lane has read its halo
+        self.ex.extract_device(img, kps[1:], desc[1:], counts[1:], stream=st, sync=False)
         self.ev_extracted.record(main)
         n = self.ex.last_launches()
         self._mark("match")
-        self.prev.copy_(self.kps[:B, :, 0:2])                               # vbPrevMatched[i] = F1.mvKeysUn[i].pt
-        self.matcher.SearchForInitialization(self.F1, self.F2, self.prev, self.window, matches12=self.m12,
-                                             nmatches=self.nmatch, stream=st, sync=False)
+        # frame-to-frame matching: on its own stream when overlapping (it is a latency-bound chain of three kernels that
+        # leaves the SMs almost empty; nothing downstream on the main stream consumes the matches)
+        ms = self.s_match if self.s_match is not None else main
+        if ms is not main:
+            self.ev_extract[p].record(main)
+            ms.wait_event(self.ev_extract[p])
+            ms.wait_event(self.ev_d2h)                                      # the host copies of older matches are done
+        with torch.cuda.stream(ms):
+            self.prev2[p].copy_(kps[:B, :, 0:2])                            # vbPrevMatched[i] = F1.mvKeysUn[i].pt
+            self.matcher.SearchForInitialization(self.F1[p], self.F2[p], self.prev2[p], self.window, matches12=self.m12_2[p],
+                                                 nmatches=self.nmatch2[p], stream=ms.cuda_stream, sync=False)
+            self.ev_match[p].record(ms)
         n += self.matcher.last_launches()
         self._mark("info")
         if self.s_sel is not None:
             main.wait_event(self.ev_sel[p])                                 # selection of step t-2 has released buffer p
-        self.octave.copy_(self.kps_i32[1:, :, 5])
-        self.cnt_sel2[p].copy_(self.counts[1:])
+        self.octave.copy_(self.kps_i32[p][1:, :, 5])
+        self.cnt_sel2[p].copy_(counts[1:])
         self.obs.build_info_frame(self.Xv, self.world, self.octave, self.score, self.valid, self.cnt_sel2[p], self.sigma2,
                                   blocks=self.blocks2[p], obs_score=self.obs_score2[p], stream=st, sync=False)
         n += self.obs.last_launches()
@@ -229,6 +258,7 @@ class TrackingFrontEnd:
         self.upload(q ^ 1)                     # frames of the next step
         self._uploaded = True
         self.s_copy.wait_event(self.ev_out)
+        self.s_copy.wait_event(self.ev_match[p])
         with torch.cuda.stream(self.s_copy):
             self.h_kps.copy_(self.kps[1:], non_blocking=True)
             self.h_desc.copy_(self.desc[1:], non_blocking=True)
