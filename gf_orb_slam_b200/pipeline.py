@@ -7,6 +7,8 @@ pick 100, eps 0.1).  All stages run in libgforb.so kernels on one CUDA stream; t
 Frame t-1 of the first frame of a batch is the last frame of the previous batch (1-frame halo)."""
 from __future__ import annotations
 
+import os
+
 import numpy as np
 import torch
 
@@ -73,7 +75,7 @@ class TrackingFrontEnd:
         self.ev_h2d = [torch.cuda.Event() for _ in range(2)]
         self.ev_ext = [torch.cuda.Event() for _ in range(2)]
         self.ev_out = torch.cuda.Event()
-        self.ev_d2h = torch.cuda.Event()
+        self.ev_d2h2 = [torch.cuda.Event() for _ in range(2)]   # host copies of buffer p's keypoints / matches are done
         self.ev_d2h_sel = [torch.cuda.Event() for _ in range(2)]
         self.t = 0                          # steps issued
         self.images2 = [self.images, z(B, height, width, dt=torch.uint8)]
@@ -144,7 +146,8 @@ class TrackingFrontEnd:
                 cur.wait_event(e)
         for e in self.ev_match:
             cur.wait_event(e)
-        cur.wait_event(self.ev_d2h)
+        for e in self.ev_d2h2:
+            cur.wait_event(e)
         for e in self.ev_d2h_sel:
             cur.wait_event(e)
 
@@ -180,7 +183,7 @@ class TrackingFrontEnd:
         if ms is not main:
             self.ev_extract[p].record(main)
             ms.wait_event(self.ev_extract[p])
-            ms.wait_event(self.ev_d2h)                                      # the host copies of older matches are done
+            ms.wait_event(self.ev_d2h2[p])                                  # the host copies of step t-2's matches are done
         with torch.cuda.stream(ms):
             self.prev2[p].copy_(kps[:B, :, 0:2])                            # vbPrevMatched[i] = F1.mvKeysUn[i].pt
             self.matcher.SearchForInitialization(self.F1[p], self.F2[p], self.prev2[p], self.window, matches12=self.m12_2[p],
@@ -250,7 +253,7 @@ class TrackingFrontEnd:
         if first or not self._uploaded:
             self.upload(q)
         main.wait_event(self.ev_h2d[q])
-        main.wait_event(self.ev_d2h)                                        # previous results left the output buffers
+        main.wait_event(self.ev_d2h2[q])                                    # step t-2's results left output buffer q
         self.step_device(self.images2[q])
         p = (self.t - 1) & 1
         self.ev_ext[q].record(main)            # (recorded after the whole main-stream part; extraction is its first stage)
@@ -265,7 +268,7 @@ class TrackingFrontEnd:
             self.h_counts.copy_(self.counts[1:], non_blocking=True)
             self.h_m12.copy_(self.m12, non_blocking=True)
             self.h_nmatch.copy_(self.nmatch, non_blocking=True)
-            self.ev_d2h.record(self.s_copy)
+            self.ev_d2h2[p].record(self.s_copy)
         if self.s_sel is not None:
             self.s_copy.wait_event(self.ev_sel[p])
         with torch.cuda.stream(self.s_copy):
@@ -296,7 +299,9 @@ class LanedFrontEnd:
         self.dev = torch.device("cuda", dev)
         torch.cuda.set_device(self.dev)
         self.lane = [TrackingFrontEnd(width, height, nfeatures, self.n, **kw) for _ in range(lanes)]
-        self.streams = [torch.cuda.Stream(device=self.dev) for _ in range(lanes)]
+        # the lane (extraction) streams are high priority: their short ALU-bound CTAs take freed SM slots before the
+        # long-lived CTAs of the selection / matching streams do (3.87 -> 3.68 ms per step on B200)
+        self.streams = [torch.cuda.Stream(device=self.dev, priority=int(os.environ.get("GFORB_MAIN_PRIORITY", "-3"))) for _ in range(lanes)]
         for j, fe in enumerate(self.lane):
             fe.halo_src = self.lane[(j - 1) % lanes]
             fe.halo_reader = self.lane[(j + 1) % lanes]
