@@ -100,12 +100,11 @@ __global__ void __launch_bounds__(256) k_border0(const uint8_t* __restrict__ img
 // level l = resize(level l-1, INTER_LINEAR) + reflect-101 ring (ComputePyramid :943, :982-983); cv::resize 8U fixed
 // point with 11-bit coefficients: out = ((b0 * (h0 >> 4) >> 16) + (b1 * (h1 >> 4) >> 16) + 2) >> 2,
 // h = s[sx] * a0 + s[sx + 1] * a1.  tabs: int2 {src index, a0 | a1 << 16} per destination column / row.
-// Thread = 4 adjacent bordered columns x a band of RS_BAND bordered rows: the column taps live in registers and every
-// horizontally interpolated source row is computed once and reused by the next output row (scale 1.2 -> ~1.3 source
-// rows per output row instead of 2).
+// Thread = 4 adjacent bordered columns x a band of RS_BAND bordered rows; the column taps live in registers.
 static const int RS_BAND = 8;
-__global__ void __launch_bounds__(256) k_resize(uint8_t* __restrict__ pyr, size_t framePyr, LevelPlan S, LevelPlan D,
-                                                const int2* __restrict__ tabs, int quadsPerRow, int nBands) {
+__global__ void __launch_bounds__(256) k_resize(const uint8_t* __restrict__ spyr, uint8_t* __restrict__ pyr, size_t framePyr,
+                                                LevelPlan S, LevelPlan D, const int2* __restrict__ tabs, int quadsPerRow,
+                                                int nBands) {
     const int t = blockIdx.x * 256 + threadIdx.x, b = blockIdx.y;
     if (t >= quadsPerRow * nBands) return;
     const int band = t / quadsPerRow, q = t - band * quadsPerRow;
@@ -119,33 +118,30 @@ __global__ void __launch_bounds__(256) k_resize(uint8_t* __restrict__ pyr, size_
         const int2 tx = __ldg(&xt[x]);
         sx[k] = tx.x; a0[k] = (short)(tx.y & 0xffff); a1[k] = (short)(tx.y >> 16);
     }
-    const uint8_t* sroi = pyr + (size_t)b * framePyr + S.off + (size_t)EDGE * S.pitch + EDGE;
-    uint8_t* dst = pyr + (size_t)b * framePyr + D.off + (q << 2);
-    int H0[4], H1[4], c0 = -0x40000000, c1 = -0x40000000;       // source rows held in H0 / H1
-    auto hrow = [&](int sy, int (&H)[4]) {
-        const uint8_t* r = sroi + (ptrdiff_t)sy * S.pitch;      // row sy+1 == S.h is the ring (b1 == 0 there)
+    const uint8_t* __restrict__ sroi = spyr + (size_t)b * framePyr + S.off + (size_t)EDGE * S.pitch + EDGE;
+    uint8_t* __restrict__ dst = pyr + (size_t)b * framePyr + D.off + (q << 2);
+    // The kernel is bound by the latency of its gathers, not by their number: every output row fetches its two source
+    // rows itself (no carried state, no branches), the band is fully unrolled and all table and pixel loads of the
+    // band are independent of each other.
+    const int Y0 = band * RS_BAND;
+    int2 ty[RS_BAND];
 #pragma unroll
-        for (int k = 0; k < 4; k++) H[k] = (r[sx[k]] * a0[k] + r[sx[k] + 1] * a1[k]) >> 4;
-    };
-    const int Yend = min((band + 1) * RS_BAND, D.rows);
-    for (int Y = band * RS_BAND; Y < Yend; Y++) {
-        const int y = reflect101(Y - EDGE, D.h);
-        const int2 ty = __ldg(&yt[y]);
-        const int b0 = (short)(ty.y & 0xffff), b1 = (short)(ty.y >> 16);
-        const int r0 = ty.x, r1 = ty.x + 1;
-        if (r0 == c1) {
+    for (int i = 0; i < RS_BAND; i++) ty[i] = __ldg(&yt[reflect101(min(Y0 + i, D.rows - 1) - EDGE, D.h)]);
 #pragma unroll
-            for (int k = 0; k < 4; k++) H0[k] = H1[k];
-            c0 = c1; c1 = -0x40000000;
-        } else if (r0 != c0) { hrow(r0, H0); c0 = r0; }
-        if (r1 != c1) { hrow(r1, H1); c1 = r1; }
+    for (int i = 0; i < RS_BAND; i++) {
+        const int Y = Y0 + i;
+        const int b0 = (short)(ty[i].y & 0xffff), b1 = (short)(ty[i].y >> 16);
+        const uint8_t* r0 = sroi + (ptrdiff_t)ty[i].x * S.pitch;     // row sy+1 == S.h is the ring (b1 == 0 there)
+        const uint8_t* r1 = r0 + S.pitch;
         uint32_t outv = 0;
 #pragma unroll
         for (int k = 0; k < 4; k++) {
-            const int v = (((b0 * H0[k]) >> 16) + ((b1 * H1[k]) >> 16) + 2) >> 2;
+            const int h0 = (__ldg(r0 + sx[k]) * a0[k] + __ldg(r0 + sx[k] + 1) * a1[k]) >> 4;
+            const int h1 = (__ldg(r1 + sx[k]) * a0[k] + __ldg(r1 + sx[k] + 1) * a1[k]) >> 4;
+            const int v = (((b0 * h0) >> 16) + ((b1 * h1) >> 16) + 2) >> 2;
             outv |= (uint32_t)min(max(v, 0), 255) << (8 * k);
         }
-        *reinterpret_cast<uint32_t*>(dst + (size_t)Y * D.pitch) = outv;
+        if (Y < D.rows) *reinterpret_cast<uint32_t*>(dst + (size_t)Y * D.pitch) = outv;
     }
 }
 
@@ -909,10 +905,11 @@ int gforb_extract(GforbExtractor* E, const uint8_t* images, int w, int h, int st
         const int tx = (L0.pitch >> 4) <= 32 ? 32 : 64, ty = 256 / tx;
         k_border0<<<dim3((L0.rows + ty - 1) / ty, batch), dim3(tx, ty), 0, st>>>(dimg, w, h, dstride, dfs, E->d_pyr, E->framePyr, L0); launches++;
     }
+    const uint8_t* spyr = E->d_pyr;     // source level l-1 and destination level l are disjoint planes of the same block
     for (int l = 1; l < nl; l++) {
         const LevelPlan& D = E->levels[l];
         const int quads = (D.w + 2 * EDGE + 3) >> 2, nBands = (D.rows + RS_BAND - 1) / RS_BAND;
-        k_resize<<<dim3((quads * nBands + 255) / 256, batch), 256, 0, st>>>(E->d_pyr, E->framePyr, E->levels[l - 1], D, E->d_tabs, quads, nBands); launches++;
+        k_resize<<<dim3((quads * nBands + 255) / 256, batch), 256, 0, st>>>(spyr, E->d_pyr, E->framePyr, E->levels[l - 1], D, E->d_tabs, quads, nBands); launches++;
     }
     end();
     begin("detect");
