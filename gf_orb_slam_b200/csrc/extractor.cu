@@ -414,6 +414,117 @@ __global__ void __launch_bounds__(128) k_level_retain(const LevelPlan* __restric
     }
 }
 
+// ------------------------------------------------------------------------------------------------ K3e HARRIS_SCORE
+// scoreType == HARRIS_SCORE (src/ORBextractor.cc:667-671): the FAST keypoints of a cell are re-scored with
+// HarrisResponses (:86-127: 7x7 block, Sobel-like integer gradients, float combination) before the quota loop, and both
+// retainBest passes then order by that float response.  The candidate lists stay as FAST wrote them; the retain kernels
+// of this mode work on 64-bit entries {response bits, packed FAST entry} in a global scratch list and keep the
+// response of every survivor in lvlResp (parallel to lvlKp), which k_orient copies into KeyPoint::response.
+struct HarrisGreater {
+    GF_HD bool operator()(uint64_t a, uint64_t b) const {
+        const uint32_t x = (uint32_t)(a >> 32), y = (uint32_t)(b >> 32);
+        float fa, fb;
+        memcpy(&fa, &x, 4); memcpy(&fb, &y, 4);
+        return fa > fb;
+    }
+};
+
+// p = the keypoint's pixel on the (unblurred) level plane
+__device__ float harris_response(const uint8_t* __restrict__ p, int step) {
+    int a = 0, b = 0, c = 0;
+    for (int i = -3; i <= 3; i++) {
+        const uint8_t* r = p + i * step;
+        for (int j = -3; j <= 3; j++) {
+            const uint8_t* q = r + j;
+            const int Ix = ((int)q[1] - (int)q[-1]) * 2 + ((int)q[-step + 1] - (int)q[-step - 1]) + ((int)q[step + 1] - (int)q[step - 1]);
+            const int Iy = ((int)q[step] - (int)q[-step]) * 2 + ((int)q[step - 1] - (int)q[-step - 1]) + ((int)q[step + 1] - (int)q[-step + 1]);
+            a += Ix * Ix; b += Iy * Iy; c += Ix * Iy;
+        }
+    }
+    float scale = __fmul_rn((float)((1 << 2) * 7), 255.0f);
+    scale = __fdiv_rn(1.0f, scale);
+    const float s4 = __fmul_rn(__fmul_rn(__fmul_rn(scale, scale), scale), scale);
+    const float fa = (float)a, fb = (float)b, fc = (float)c;
+    const float sum = __fadd_rn(fa, fb);
+    const float t = __fsub_rn(__fsub_rn(__fmul_rn(fa, fb), __fmul_rn(fc, fc)), __fmul_rn(__fmul_rn(0.04f, sum), sum));
+    return __fmul_rn(t, s4);
+}
+
+__global__ void __launch_bounds__(RET_WARPS * 32) k_cell_retain_harris(
+    const CellPlan* __restrict__ cells, const LevelPlan* __restrict__ levels, int nCellsTotal, const uint32_t* __restrict__ cand,
+    size_t frameCand, const int* __restrict__ cnt7, const int* __restrict__ nTotalArr, const int* __restrict__ nToRetainArr,
+    const int* __restrict__ cellOutOff, uint32_t* __restrict__ lvlKp, float* __restrict__ lvlResp, size_t frameKp, int iniTh,
+    int retainVariant, const uint8_t* __restrict__ pyr, size_t framePyr, uint64_t* __restrict__ work64, size_t frameWork) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int cellId = blockIdx.x * RET_WARPS + warp, b = blockIdx.y;
+    if (cellId >= nCellsTotal) return;
+    const CellPlan C = cells[cellId];
+    const LevelPlan L = levels[C.level];
+    const size_t ci = (size_t)b * nCellsTotal + cellId;
+    const int nKeep = nToRetainArr[ci];
+    if (nKeep <= 0) return;
+    const int enc = nTotalArr[ci];
+    const bool useIni = enc < 0;
+    const int nAll = cnt7[ci];
+    const uint32_t* list = cand + (size_t)b * frameCand + C.candBase;
+    uint64_t* work = work64 + (size_t)b * frameWork + C.candBase;
+    const uint8_t* roi = pyr + (size_t)b * framePyr + L.off + (size_t)EDGE * L.pitch + EDGE;
+    int outN = 0;
+    for (int i0 = 0; i0 < nAll; i0 += 32) {
+        const int i = i0 + lane;
+        const uint32_t v = (i < nAll) ? list[i] : 0u;
+        const bool keep = (i < nAll) && (!useIni || (int)(v >> 24) >= iniTh);
+        const uint32_t m = __ballot_sync(0xffffffffu, keep);
+        if (keep) {
+            const int x = v & 0xfff, y = (v >> 12) & 0xfff;
+            const float r = harris_response(roi + (size_t)y * L.pitch + x, L.pitch);
+            work[outN + __popc(m & ((1u << lane) - 1u))] = ((uint64_t)__float_as_uint(r) << 32) | v;
+        }
+        outN += __popc(m);
+    }
+    __syncwarp();
+    if (lane == 0 && outN > nKeep) retain_best_first_n(work, outN, nKeep, retainVariant, HarrisGreater());
+    __syncwarp();
+    const int dstOff = cellOutOff[ci];
+    if (dstOff + nKeep > L.kpCap) return;                     // overflow already flagged by k_quota
+    const size_t d0 = (size_t)b * frameKp + L.kpBase + dstOff;
+    for (int i = lane; i < nKeep; i += 32) {
+        const uint64_t e = work[i];
+        lvlKp[d0 + i] = (uint32_t)e;
+        lvlResp[d0 + i] = __uint_as_float((uint32_t)(e >> 32));
+    }
+}
+
+__global__ void __launch_bounds__(128) k_level_retain_harris(const LevelPlan* __restrict__ levels, int nLevels,
+                                                             uint32_t* __restrict__ lvlKp, float* __restrict__ lvlResp,
+                                                             size_t frameKp, const int* __restrict__ lvlPre,
+                                                             int* __restrict__ lvlCount, int batch, int retainVariant,
+                                                             uint64_t* __restrict__ work64, size_t frameWork) {
+    const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (gw >= batch * nLevels) return;
+    const int b = gw / nLevels, l = gw - b * nLevels;
+    const LevelPlan L = levels[l];
+    int n = lvlPre[gw];
+    if (n > L.kpCap) n = L.kpCap;
+    if (n > L.nDesired) {
+        const size_t k0 = (size_t)b * frameKp + L.kpBase;
+        uint64_t* w = work64 + (size_t)b * frameWork + L.kpBase;
+        for (int i = lane; i < n; i += 32) w[i] = ((uint64_t)__float_as_uint(lvlResp[k0 + i]) << 32) | lvlKp[k0 + i];
+        __syncwarp();
+        int m = n;
+        if (lane == 0) m = retain_best_first_n(w, n, L.nDesired, retainVariant, HarrisGreater());
+        m = __shfl_sync(0xffffffffu, m, 0);
+        __syncwarp();
+        for (int i = lane; i < m; i += 32) {
+            const uint64_t e = w[i];
+            lvlKp[k0 + i] = (uint32_t)e;
+            lvlResp[k0 + i] = __uint_as_float((uint32_t)(e >> 32));
+        }
+        n = m;
+    }
+    if (lane == 0) lvlCount[gw] = n;
+}
+
 // ------------------------------------------------------------------------------------------------ K4 orient
 // IC_Angle on the unblurred level (src/ORBextractor.cc:131-158) + KeyPoint emission (:738-745, :865-871).
 // One warp per keypoint slot.  The circular patch (31 rows, |u| <= umax[|v|]) is cut into 31 x 8 tasks of four
@@ -430,7 +541,8 @@ __global__ void __launch_bounds__(256) k_orient(const uint8_t* __restrict__ pyr,
                                                 const LevelPlan* __restrict__ levels, int nLevels,
                                                 const uint32_t* __restrict__ lvlKp, size_t frameKp, int kpCapTotal,
                                                 const int* __restrict__ lvlCount, GforbKeyPoint* __restrict__ kps,
-                                                int32_t* __restrict__ counts, int nfeatures) {
+                                                int32_t* __restrict__ counts, int nfeatures,
+                                                const float* __restrict__ lvlResp) {
     __shared__ int2 s_w[256];                 // task (row * 8 + chunk) -> {u weights (4 x s8), membership (4 x 0/1)}
     {
         const int row = threadIdx.x >> 3, c = threadIdx.x & 7, v = row - HALF_PATCH;
@@ -484,7 +596,7 @@ __global__ void __launch_bounds__(256) k_orient(const uint8_t* __restrict__ pyr,
         k.x = fx; k.y = fy;
         k.size = (float)L.scaledPatchSize;
         k.angle = fast_atan2_deg((float)m01, (float)m10);
-        k.response = (float)score;
+        k.response = lvlResp ? lvlResp[(size_t)b * frameKp + slot] : (float)score;   // HARRIS_SCORE : FAST_SCORE
         k.octave = l;
         k.class_id = -1;
         kps[(size_t)b * nfeatures + base + i] = k;
@@ -564,6 +676,9 @@ struct GforbExtractor {
     GforbKeyPoint* d_kps = nullptr;
     int32_t* d_counts = nullptr;
     uint32_t *d_cand = nullptr, *d_lvlKp = nullptr;
+    uint64_t* d_work64 = nullptr;       // HARRIS_SCORE only: 64-bit retain scratch and the survivors' responses
+    float* d_lvlResp = nullptr;
+    size_t frameWork = 0, capWork = 0, capResp = 0;
     int *d_cnt7 = nullptr, *d_cnt20 = nullptr, *d_nTotal = nullptr, *d_nToRetain = nullptr, *d_cellOff = nullptr;
     int *d_lvlPre = nullptr, *d_lvlCount = nullptr, *d_err = nullptr;
     LevelPlan* d_levels = nullptr;
@@ -718,6 +833,11 @@ static int build_plan(GforbExtractor* E, int w, int h) {
     { size_t cap2 = 0; uint8_t* old = E->d_blr; if (old) cudaFree(old); E->d_blr = nullptr; if ((rc = ensure(&E->d_blr, &cap2, E->framePyr * B))) return rc; }
     if ((rc = ensure(&E->d_cand, &E->capCand, E->frameCand * B))) return rc;
     if ((rc = ensure(&E->d_lvlKp, &E->capKp, E->frameKp * B))) return rc;
+    if (c.scoreType == 0) {
+        E->frameWork = std::max(E->frameCand, E->frameKp);
+        if ((rc = ensure(&E->d_work64, &E->capWork, E->frameWork * B))) return rc;
+        if ((rc = ensure(&E->d_lvlResp, &E->capResp, E->frameKp * B))) return rc;
+    }
     size_t nc = (size_t)E->nCellsTotal * B;
     if (nc > E->capCells) {
         for (int** p : {&E->d_cnt7, &E->d_cnt20, &E->d_nTotal, &E->d_nToRetain, &E->d_cellOff}) { if (*p) cudaFree(*p); *p = nullptr; }
@@ -752,7 +872,7 @@ int gforb_extractor_create(const GforbExtractorConfig* cfg, GforbExtractor** out
     if (!cfg || !out) return GFORB_ERR_ARG;
     *out = nullptr;
     if (cfg->nfeatures <= 0 || cfg->nlevels <= 0 || cfg->nlevels > MAX_LEVELS || !(cfg->scaleFactor > 1.0f) ||
-        cfg->scoreType != 1 || cfg->max_batch <= 0 || cfg->max_width <= 0 || cfg->max_height <= 0 ||
+        cfg->scoreType < 0 || cfg->scoreType > 1 || cfg->max_batch <= 0 || cfg->max_width <= 0 || cfg->max_height <= 0 ||
         cfg->blur_variant < 0 || cfg->blur_variant > 1 || cfg->retain_variant < 0 || cfg->retain_variant > 1 ||
         cfg->minThFAST < 1 || cfg->iniThFAST < cfg->minThFAST || cfg->iniThFAST > 254)
         return GFORB_ERR_ARG;
@@ -803,7 +923,7 @@ int gforb_extractor_destroy(GforbExtractor* E) {
     cudaSetDevice(E->device);
     void* ptrs[] = {E->d_img, E->d_pyr, E->d_blr, E->d_desc, E->d_kps, E->d_counts, E->d_cand, E->d_lvlKp, E->d_cnt7,
                     E->d_cnt20, E->d_nTotal, E->d_nToRetain, E->d_cellOff, E->d_lvlPre, E->d_lvlCount, E->d_err,
-                    E->d_levels, E->d_cells, E->d_tabs};
+                    E->d_levels, E->d_cells, E->d_tabs, E->d_work64, E->d_lvlResp};
     for (void* p : ptrs) if (p) cudaFree(p);
     for (auto& r : E->recs) { cudaEventDestroy(r.e0); cudaEventDestroy(r.e1); }
     for (auto& e : E->evPool) cudaEventDestroy(e);
@@ -928,15 +1048,27 @@ int gforb_extract(GforbExtractor* E, const uint8_t* images, int w, int h, int st
     begin("select");
     k_quota<<<(batch * nl + 127) / 128, 128, 0, st>>>(E->d_levels, E->d_cells, nl, E->nCellsTotal, E->d_cnt7, E->d_cnt20,
                                                      E->d_nTotal, E->d_nToRetain, E->d_cellOff, E->d_lvlPre, batch, E->d_err); launches++;
-    k_cell_retain<<<dim3((E->nCellsTotal + RET_WARPS - 1) / RET_WARPS, batch), RET_WARPS * 32, 0, st>>>(
-        E->d_cells, E->d_levels, E->nCellsTotal, E->d_cand, E->frameCand, E->d_cnt7, E->d_nTotal, E->d_nToRetain,
-        E->d_cellOff, E->d_lvlKp, E->frameKp, c.iniThFAST, c.retain_variant); launches++;
-    k_level_retain<<<(batch * nl * 32 + 127) / 128, 128, 0, st>>>(E->d_levels, nl, E->d_lvlKp, E->frameKp, E->d_lvlPre,
-                                                                  E->d_lvlCount, batch, c.retain_variant); launches++;
+    const bool harris = c.scoreType == 0;
+    if (!harris) {
+        k_cell_retain<<<dim3((E->nCellsTotal + RET_WARPS - 1) / RET_WARPS, batch), RET_WARPS * 32, 0, st>>>(
+            E->d_cells, E->d_levels, E->nCellsTotal, E->d_cand, E->frameCand, E->d_cnt7, E->d_nTotal, E->d_nToRetain,
+            E->d_cellOff, E->d_lvlKp, E->frameKp, c.iniThFAST, c.retain_variant); launches++;
+        k_level_retain<<<(batch * nl * 32 + 127) / 128, 128, 0, st>>>(E->d_levels, nl, E->d_lvlKp, E->frameKp, E->d_lvlPre,
+                                                                      E->d_lvlCount, batch, c.retain_variant); launches++;
+    } else {
+        k_cell_retain_harris<<<dim3((E->nCellsTotal + RET_WARPS - 1) / RET_WARPS, batch), RET_WARPS * 32, 0, st>>>(
+            E->d_cells, E->d_levels, E->nCellsTotal, E->d_cand, E->frameCand, E->d_cnt7, E->d_nTotal, E->d_nToRetain,
+            E->d_cellOff, E->d_lvlKp, E->d_lvlResp, E->frameKp, c.iniThFAST, c.retain_variant, E->d_pyr, E->framePyr,
+            E->d_work64, E->frameWork); launches++;
+        k_level_retain_harris<<<(batch * nl * 32 + 127) / 128, 128, 0, st>>>(
+            E->d_levels, nl, E->d_lvlKp, E->d_lvlResp, E->frameKp, E->d_lvlPre, E->d_lvlCount, batch, c.retain_variant,
+            E->d_work64, E->frameWork); launches++;
+    }
     end();
     begin("orient");
     k_orient<<<dim3((E->kpCapTotal + 7) / 8, batch), 256, 0, st>>>(E->d_pyr, E->framePyr, E->d_levels, nl, E->d_lvlKp,
-                                                                    E->frameKp, E->kpCapTotal, E->d_lvlCount, dk, dc, c.nfeatures); launches++;
+                                                                    E->frameKp, E->kpCapTotal, E->d_lvlCount, dk, dc, c.nfeatures,
+                                                                    harris ? E->d_lvlResp : nullptr); launches++;
     end();
     begin("blur");
     k_blur2<<<dim3((E->blTasks + BL2_WARPS - 1) / BL2_WARPS, batch), BL2_WARPS * 32, 0, st>>>(

@@ -51,7 +51,7 @@ typedef struct GforbExtractorConfig {
     int32_t nfeatures;        /* ctor arg nfeatures (1000) */
     float scaleFactor;        /* ctor arg scaleFactor (1.2f) */
     int32_t nlevels;          /* ctor arg nlevels (8) */
-    int32_t scoreType;        /* 1 = FAST_SCORE (only mode implemented; HARRIS_SCORE=0 -> GFORB_ERR_ARG) */
+    int32_t scoreType;        /* 1 = FAST_SCORE, 0 = HARRIS_SCORE (src/ORBextractor.cc:86-127, :667-671) */
     int32_t iniThFAST;        /* ctor arg fastTh (20) */
     int32_t minThFAST;        /* hard-coded 7 in the reference (src/ORBextractor.cc:627) */
     int32_t blur_variant;     /* 0 = OpenCV>=3.4 bit-exact Gaussian (cv2-4.13 verified), 1 = legacy 2.4 integer kernel */

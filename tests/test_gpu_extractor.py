@@ -37,6 +37,24 @@ def test_extract_matches_oracle(orc, w, h, nf):
     assert ex.last_launches() > 0
 
 
+@pytest.mark.parametrize("w,h,nf,variant", [(640, 480, 1000, 0), (752, 480, 500, 1), (200, 152, 300, 0)])
+def test_harris_score_matches_oracle(orc, w, h, nf, variant):
+    """scoreType = HARRIS_SCORE (src/ORBextractor.cc:86-127, :667-671): float responses drive both retainBest passes"""
+    from gf_orb_slam_b200 import HARRIS_SCORE, ORBextractor
+    B = 3
+    imgs = np.stack([synth.textured_frame(w, h, seed=40 + i, band=(i != 1)) for i in range(B)])
+    ex = ORBextractor(nf, 1.2, 8, HARRIS_SCORE, max_width=w, max_height=h, max_batch=B, retain_variant=variant)
+    kps, desc, counts = ex.extract_batch(imgs)
+    ex_cpu = orc.ORBextractor(nf, 1.2, 8, scoreType=0, retainVariant=variant)
+    for b in range(B):
+        _cmp_frame(orc, ex_cpu, imgs[b], b, kps, desc, counts)
+    k, _ = ex_cpu(imgs[0])
+    assert len(np.unique(k["response"])) > 200 and (k["response"] != np.round(k["response"])).any()   # really Harris floats
+    # and the FAST_SCORE keypoint set differs (the mode is not a no-op)
+    kf, _ = orc.ORBextractor(nf, 1.2, 8, scoreType=1, retainVariant=variant)(imgs[0])
+    assert len(kf) != len(k) or not (np.array_equal(kf["x"], k["x"]) and np.array_equal(kf["y"], k["y"]))
+
+
 def test_sequence_frames_and_single_call(orc):
     from gf_orb_slam_b200 import ORBextractor
     seq = synth.Sequence()
