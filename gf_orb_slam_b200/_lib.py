@@ -88,6 +88,7 @@ def lib() -> C.CDLL:
                                                         i32, vp, vp, vp, i32, vp]
         L.gforb_frame_is_in_frustum.argtypes = [vp, i32, vp, vp, vp, f32, f32, f32, f32, i32, i32, i32, i32, vp, vp, vp, vp, vp, i32,
                                                 f32, vp, vp, vp, vp, vp, i32, vp]
+        L.gforb_frame_undistort_keypoints.argtypes = [vp, i32, vp, vp, i32, f32, f32, f32, f32, vp, i32, vp, i32, vp]
         L.gforb_window_search.argtypes = [vp, FS, FS, i32, vp, i32, i32, i32, f32, i32, vp, vp, i32, vp]
         L.gforb_allpairs_top2.argtypes = [vp, vp, i32, vp, i64, i64, vp, i32, vp]
         L.gforb_top2_merge.argtypes = [vp, vp, i32, i32, vp, i32, vp]
@@ -119,7 +120,7 @@ gforb_search_for_initialization gforb_search_by_projection gforb_search_by_proje
 gforb_allpairs_top2 gforb_top2_merge gforb_obs_create gforb_obs_destroy gforb_obs_last_launches gforb_obs_set_state
 gforb_obs_get_state gforb_obs_update_pwls gforb_obs_predict_pwls gforb_obs_num_segments gforb_obs_get_segment
 gforb_obs_build_info_frame gforb_obs_build_info_map gforb_obs_logdet gforb_obs_rand_stream gforb_obs_select
-gforb_obs_active_match gforb_frame_is_in_frustum""".split()
+gforb_obs_active_match gforb_frame_is_in_frustum gforb_frame_undistort_keypoints""".split()
 
 
 def check(rc: int, what: str):

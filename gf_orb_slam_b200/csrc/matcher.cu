@@ -494,6 +494,43 @@ __global__ void __launch_bounds__(32) k_resolve(const RParams R) {
 namespace gforb {
 
 // ------------------------------------------------------------------------------------------------ Frame::isInFrustum
+// Frame::UndistortKeyPoints (src/Frame.cc:389-423) for the keypoints of `batch` frames: thread per keypoint.
+// cvUndistortPoints restated (double arithmetic on CV_32F inputs, 5 fixed-point iterations, R = I, P = K); the keypoint
+// is copied and its position replaced.  This TU is built with --fmad=false, so every operation rounds on its own.
+struct UndistortParams {
+    const GforbKeyPoint* keys;
+    GforbKeyPoint* keysUn;
+    const int32_t* counts;
+    int stride;
+    double fx, fy, cx, cy, k[8];
+    int identity;                          // mDistCoef[0] == 0: mvKeysUn = mvKeys
+};
+
+__global__ void __launch_bounds__(128) k_undistort(const UndistortParams P) {
+    const int b = blockIdx.y, i = blockIdx.x * 128 + threadIdx.x;
+    if (i >= P.stride || i >= P.counts[b]) return;
+    GforbKeyPoint kp = P.keys[(size_t)b * P.stride + i];
+    if (!P.identity) {
+        const double ifx = 1. / P.fx, ify = 1. / P.fy;
+        double x = ((double)kp.x - P.cx) * ifx, y = ((double)kp.y - P.cy) * ify;
+        const double x0 = x, y0 = y;
+        for (int j = 0; j < 5; j++) {
+            const double r2 = x * x + y * y;
+            const double icdist = (1 + ((P.k[7] * r2 + P.k[6]) * r2 + P.k[5]) * r2) / (1 + ((P.k[4] * r2 + P.k[1]) * r2 + P.k[0]) * r2);
+            const double deltaX = 2 * P.k[2] * x * y + P.k[3] * (r2 + 2 * x * x);
+            const double deltaY = P.k[2] * (r2 + 2 * y * y) + 2 * P.k[3] * x * y;
+            x = (x0 - deltaX) * icdist;
+            y = (y0 - deltaY) * icdist;
+        }
+        const double xx = P.fx * x + 0. * y + P.cx;
+        const double yy = 0. * x + P.fy * y + P.cy;
+        const double ww = 1. / (0. * x + 0. * y + 1.);
+        kp.x = (float)(xx * ww);
+        kp.y = (float)(yy * ww);
+    }
+    P.keysUn[(size_t)b * P.stride + i] = kp;
+}
+
 // src/Frame.cc:166-227 for every map point of `batch` frames: thread per point.  cv::Mat arithmetic restated: Rcw * P
 // accumulates each row in double and casts to float before + tcw; cv::norm / Mat::dot accumulate double products.
 struct FrustumParams {
@@ -1038,6 +1075,29 @@ int gforb_frame_is_in_frustum(GforbMatcher* M, int batch, const float* Rcw, cons
     F.viewCos = c.out(view_cos, nm, true); F.flags = c.out(mp_flags, nm, true);
     if (c.rc) return c.rc;
     k_is_in_frustum<<<dim3((mp_stride + 127) / 128, batch), 128, 0, c.st>>>(F);
+    M->lastLaunches++;
+    return end_call(M, c, flags);
+}
+
+int gforb_frame_undistort_keypoints(GforbMatcher* M, int batch, const GforbKeyPoint* keys, const int32_t* counts,
+                                    int kp_stride, float fx, float fy, float cx, float cy, const float* dist_coef,
+                                    int n_dist, GforbKeyPoint* keys_un, int flags, void* stream) {
+    Ctx c;
+    int rc = begin_call(M, batch, flags, stream, c);
+    if (rc) return rc;
+    if (!keys || !counts || !keys_un || kp_stride <= 0 || n_dist < 0 || n_dist > 8 || (n_dist > 0 && !dist_coef)) return GFORB_ERR_ARG;
+    if (kp_stride > M->cfg.max_keypoints) return GFORB_ERR_CAPACITY;
+    if (batch == 0) return GFORB_OK;
+    const size_t nk = (size_t)batch * kp_stride;
+    UndistortParams P;
+    memset(&P, 0, sizeof(P));
+    P.keys = c.in(keys, nk); P.counts = c.in(counts, (size_t)batch); P.keysUn = c.out(keys_un, nk, true);     // in/out: entries past counts[b] keep their contents
+    P.stride = kp_stride;
+    P.fx = fx; P.fy = fy; P.cx = cx; P.cy = cy;
+    for (int i = 0; i < n_dist; i++) P.k[i] = dist_coef[i];          // host array (Frame::mDistCoef, CV_32F)
+    P.identity = (n_dist == 0 || dist_coef[0] == 0.0f) ? 1 : 0;
+    if (c.rc) return c.rc;
+    k_undistort<<<dim3((kp_stride + 127) / 128, batch), 128, 0, c.st>>>(P);
     M->lastLaunches++;
     return end_call(M, c, flags);
 }

@@ -129,6 +129,26 @@ class ORBmatcher:
               "gforb_frame_is_in_frustum")
         return fl
 
+    # -- void Frame::UndistortKeyPoints(), batched over the keypoints of B frames
+    def UndistortKeyPoints(self, keys, counts, fx, fy, cx, cy, dist_coef, keys_un=None, *, stream=None, sync=True):
+        """src/Frame.cc:389-423.  keys (B, stride) KP_DTYPE records (numpy) or (B, stride, 7) float32 (torch, device);
+        dist_coef = Frame::mDistCoef (k1, k2, p1, p2[, k3]) on the host.  Returns mvKeysUn (same shape; entries past
+        counts[b] are left as allocated)."""
+        dev = is_device(keys)
+        B, stride = int(keys.shape[0]), int(keys.shape[1])
+        if keys_un is None:
+            if dev:
+                import torch
+                keys_un = torch.zeros_like(keys)
+            else:
+                keys_un = np.zeros_like(keys)
+        d = np.ascontiguousarray(dist_coef, np.float32).reshape(-1)
+        check(_lib.lib().gforb_frame_undistort_keypoints(self._h, B, ptr(keys), ptr(counts), stride, float(fx), float(fy),
+                                                         float(cx), float(cy), ptr(d), int(d.size), ptr(keys_un),
+                                                         self._flags(dev, is_device(keys_un), sync), C.c_void_p(stream or 0)),
+              "gforb_frame_undistort_keypoints")
+        return keys_un
+
     # -- int SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize=10)
     def SearchForInitialization(self, F1: Frames, F2: Frames, vbPrevMatched, windowSize=10, *, matches12=None,
                                 nmatches=None, stream=None, sync=True):

@@ -168,6 +168,14 @@ int gforb_frame_is_in_frustum(GforbMatcher* h, int batch, const float* Rcw, cons
                               const int32_t* counts, int mp_stride, float viewing_cos_limit, float* proj_x, float* proj_y,
                               int32_t* scale_level, float* view_cos, uint8_t* mp_flags, int flags, void* stream);
 
+/* Frame::UndistortKeyPoints() (src/Frame.cc:389-423) for the keypoints of `batch` frames: keys_un[i] = keys[i] with pt
+ * replaced by cv::undistortPoints(pt, K, dist_coef, R = I, P = K); dist_coef: HOST array of n_dist (0, 4, 5 or 8) floats
+ * = Frame::mDistCoef (k1, k2, p1, p2[, k3[, k4, k5, k6]]); dist_coef[0] == 0 copies the keypoints (the reference's early
+ * return).  Only the first counts[b] entries of every frame are written. */
+int gforb_frame_undistort_keypoints(GforbMatcher* h, int batch, const GforbKeyPoint* keys, const int32_t* counts,
+                                    int kp_stride, float fx, float fy, float cx, float cy, const float* dist_coef,
+                                    int n_dist, GforbKeyPoint* keys_un, int flags, void* stream);
+
 /* ORBmatcher::SearchByProjection(Frame& Current, const Frame& Last, th) (src/ORBmatcher.cc:2081-2202).
  * last_mappoints: batch x last.kp_stride ids (-1 = NULL); last_outlier: same shape or NULL; last_world: batch x
  * last.kp_stride x 3 (MapPoint::GetWorldPos of LastFrame.mvpMapPoints[i]); Tcw: batch x 16 row-major (Current.mTcw);

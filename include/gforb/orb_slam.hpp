@@ -264,6 +264,22 @@ public:
         return n;
     }
 
+    // Frame::UndistortKeyPoints() (src/Frame.cc:389-423): mvKeysUn = mvKeys with cv::undistortPoints(pt, K, mDistCoef,
+    // R = I, P = K); mDistCoef = (k1, k2, p1, p2[, k3]); mDistCoef[0] == 0 copies.
+    void UndistortKeyPoints(const Frame& F, const std::vector<gforb_cv::KeyPoint>& mvKeys, const std::vector<float>& mDistCoef,
+                            std::vector<gforb_cv::KeyPoint>& mvKeysUn) {
+        const int n = (int)mvKeys.size();
+        mvKeysUn.resize(mvKeys.size());
+        if (n == 0) return;
+        ensure(n, 1, F.mnScaleLevels, F.mfScaleFactor);
+        static_assert(sizeof(gforb_cv::KeyPoint) == sizeof(GforbKeyPoint), "KeyPoint layout");
+        int32_t cnt = n;
+        gforb_throw(gforb_frame_undistort_keypoints(h_, 1, reinterpret_cast<const GforbKeyPoint*>(mvKeys.data()), &cnt, n, F.fx, F.fy,
+                                                    F.cx, F.cy, mDistCoef.data(), (int)mDistCoef.size(),
+                                                    reinterpret_cast<GforbKeyPoint*>(mvKeysUn.data()), 0, nullptr),
+                    "UndistortKeyPoints");
+    }
+
     // Matching for the map initialisation / frame-to-frame tracking without a map
     // (include/ORBmatcher.h:79-80, src/ORBmatcher.cc:1172-1287).
     int SearchForInitialization(Frame& F1, Frame& F2, std::vector<gforb_cv::Point2f>& vbPrevMatched,

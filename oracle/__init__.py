@@ -268,6 +268,16 @@ def is_in_frustum(Rcw, tcw, Ow, fx, fy, cx, cy, bounds, world, normal, min_dist,
     return u, v, lvl, vc, fl
 
 
+def undistort_keypoints(xy, fx, fy, cx, cy, dist):
+    """Frame::UndistortKeyPoints (src/Frame.cc:389-423) on (N, 2) float32 keypoint positions -> (N, 2) float32"""
+    xy = np.ascontiguousarray(xy, np.float32).reshape(-1, 2)
+    dist = np.ascontiguousarray(dist, np.float32).reshape(-1)
+    out = np.empty_like(xy)
+    cf = C.c_float
+    lib().orc_undistort_keypoints(_p(xy), xy.shape[0], cf(fx), cf(fy), cf(cx), cf(cy), _p(dist), dist.size, _p(out))
+    return out
+
+
 # ---------------------------------------------------------------- observability
 class Observability:
     def __init__(self, *, f=None, fu=None, fv=None, nRows=480, nCols=752, Cx=0.0, Cy=0.0, k1=0.0, k2=0.0, dx=None, dy=None):

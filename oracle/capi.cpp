@@ -233,6 +233,13 @@ void orc_is_in_frustum(const float* Rcw, const float* tcw, const float* Ow, floa
     }
 }
 
+// Frame::UndistortKeyPoints (src/Frame.cc:389-423) on n x 2 positions; dist[0] == 0 -> copy (the early return)
+void orc_undistort_keypoints(const float* src, int n, float fx, float fy, float cx, float cy, const float* dist, int ndist,
+                             float* dst) {
+    if (ndist <= 0 || dist[0] == 0.0f) { for (int i = 0; i < 2 * n; i++) dst[i] = src[i]; return; }
+    undistortPoints(src, n, fx, fy, cx, cy, dist, ndist, dst);
+}
+
 // Observability::runActiveMapMatching (src/Observability.cc:1249-1524).  Map-point SoA as in orc_search_by_projection;
 // in_pool[i] = (updateAtFrameId == frame id); cur_mat (49) in: mBaseInfoMat, out: accumulated matrix; the frame's
 // mvpMapPoints / mvpMatchScore are updated in place; left_idx receives mLeftMapPoints, *left_n its size.

@@ -364,4 +364,36 @@ bool isInFrustum(const float* Rcw, const float* tcw, const float* Ow, float fx, 
     return true;
 }
 
+// Frame::UndistortKeyPoints (src/Frame.cc:389-423): cv::undistortPoints(mat, mat, mK, mDistCoef, cv::Mat(), mK) on the
+// N x 2 CV_32F keypoint positions.  OpenCV is not vendored; cvUndistortPoints (imgproc/src/undistort.cpp, 2.4.13 and
+// 3.4.1 agree for a k1,k2,p1,p2[,k3] model) restated: everything in double, K and the coefficients widened from
+// CV_32F, 5 fixed-point iterations, R = I, P = K (so RR = K and ww = 1), result narrowed to float.  The caller handles
+// the reference's early return (mDistCoef[0] == 0 -> mvKeysUn = mvKeys).
+void undistortPoints(const float* src, int n, float fxf, float fyf, float cxf, float cyf, const float* dist, int ndist,
+                     float* dst) {
+    double k[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int i = 0; i < ndist && i < 8; i++) k[i] = dist[i];
+    const double fx = fxf, fy = fyf, cx = cxf, cy = cyf;
+    const double ifx = 1. / fx, ify = 1. / fy;
+    for (int i = 0; i < n; i++) {
+        double x = src[2 * i], y = src[2 * i + 1];
+        x = (x - cx) * ifx;
+        y = (y - cy) * ify;
+        const double x0 = x, y0 = y;
+        for (int j = 0; j < 5; j++) {
+            const double r2 = x * x + y * y;
+            const double icdist = (1 + ((k[7] * r2 + k[6]) * r2 + k[5]) * r2) / (1 + ((k[4] * r2 + k[1]) * r2 + k[0]) * r2);
+            const double deltaX = 2 * k[2] * x * y + k[3] * (r2 + 2 * x * x);
+            const double deltaY = k[2] * (r2 + 2 * y * y) + 2 * k[3] * x * y;
+            x = (x0 - deltaX) * icdist;
+            y = (y0 - deltaY) * icdist;
+        }
+        const double xx = fx * x + 0. * y + cx;
+        const double yy = 0. * x + fy * y + cy;
+        const double ww = 1. / (0. * x + 0. * y + 1.);
+        dst[2 * i] = (float)(xx * ww);
+        dst[2 * i + 1] = (float)(yy * ww);
+    }
+}
+
 }  // namespace oracle

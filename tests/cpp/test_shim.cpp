@@ -243,6 +243,25 @@ int main() {
         CHECK(c3, "accumulated information matrix differs");
     }
 
+    // ---- Frame::UndistortKeyPoints through the shim vs the oracle's cv::undistortPoints restatement (EuRoC cam0 model)
+    {
+        const std::vector<float> dist = {-0.28340811f, 0.07395907f, 0.00019359f, 1.76187114e-05f};
+        Frame Fu = F1;
+        Fu.fx = 458.654f; Fu.fy = 457.296f; Fu.cx = 367.215f; Fu.cy = 248.375f;
+        std::vector<gforb_cv::KeyPoint> un;
+        m.UndistortKeyPoints(Fu, k1, dist, un);
+        std::vector<float> src(2 * k1.size()), dst(2 * k1.size());
+        for (size_t i = 0; i < k1.size(); i++) { src[2 * i] = k1[i].pt.x; src[2 * i + 1] = k1[i].pt.y; }
+        oracle::undistortPoints(src.data(), (int)k1.size(), Fu.fx, Fu.fy, Fu.cx, Fu.cy, dist.data(), 4, dst.data());
+        bool u1 = un.size() == k1.size(), moved = false;
+        for (size_t i = 0; u1 && i < k1.size(); i++) {
+            u1 = un[i].pt.x == dst[2 * i] && un[i].pt.y == dst[2 * i + 1] && un[i].octave == k1[i].octave && un[i].angle == k1[i].angle &&
+                 un[i].response == k1[i].response && un[i].size == k1[i].size;
+            moved = moved || std::fabs(un[i].pt.x - k1[i].pt.x) > 1.0f;
+        }
+        CHECK(u1 && moved, "UndistortKeyPoints differs from the oracle");
+    }
+
     printf("shim test: %zu/%zu keypoints, %d init matches, %d projection matches, %zu good features, %d active matches: %s\n", k1.size(),
            k2.size(), nm, np, good.size(), nActive, g_fail ? "FAILED" : "OK");
     return g_fail ? 1 : 0;

@@ -63,5 +63,5 @@ def test_no_device_means_error_not_fallback():
     else:
         assert rc == 0
         lib.gforb_extractor_destroy(h)
-    cfg.scoreType = 0          # HARRIS_SCORE is not implemented: argument error, never a silent substitute
+    cfg.scoreType = 2          # only HARRIS_SCORE (0) and FAST_SCORE (1) exist: argument error, never a silent substitute
     assert lib.gforb_extractor_create(ctypes.byref(cfg), ctypes.byref(h)) == -2

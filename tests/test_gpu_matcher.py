@@ -285,3 +285,37 @@ def test_is_in_frustum(orc):
         for got, exp in ((mps.a[0], eu), (mps.a[1], ev), (mps.a[2], el), (mps.a[3], ec)):
             assert np.array_equal(got[b, :n][k], exp[k]), b
     assert 200 < nin < B * M // 2
+
+
+def test_undistort_keypoints(orc):
+    """Frame::UndistortKeyPoints (src/Frame.cc:389-423) batched: positions bit-equal to the oracle and to the committed
+    cv2 4.13 vectors, every other KeyPoint field copied, entries past counts[b] untouched, k1 == 0 copies."""
+    import os
+    from gf_orb_slam_b200 import ORBmatcher
+    from gf_orb_slam_b200._lib import KP_DTYPE
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "cv413_undistort.npz"))
+    m = ORBmatcher(0.8, True, max_batch=3, max_keypoints=3000, max_queries=64)
+    rng = np.random.default_rng(3)
+    for name in ("euroc", "tum1", "k1only"):
+        K, D, xy, und = g[name + "_K"], g[name + "_D"], g[name + "_xy"], g[name + "_und"]
+        B, n = 3, xy.shape[0]
+        keys = np.zeros((B, n), KP_DTYPE)
+        for b in range(B):
+            p = np.roll(xy, 7 * b, axis=0)
+            keys[b]["x"], keys[b]["y"] = p[:, 0], p[:, 1]
+        keys["size"] = 31.0; keys["angle"] = rng.uniform(0, 360, (B, n)).astype(np.float32)
+        keys["response"] = rng.integers(7, 120, (B, n)); keys["octave"] = rng.integers(0, 8, (B, n)); keys["class_id"] = -1
+        counts = np.array([n, n - 100, 17], np.int32)
+        out = np.zeros((B, n), KP_DTYPE); out["class_id"] = 12345
+        m.UndistortKeyPoints(keys, counts, K[0, 0], K[1, 1], K[0, 2], K[1, 2], D, out)
+        for b in range(B):
+            c = int(counts[b])
+            exp = orc.undistort_keypoints(np.stack([keys[b]["x"][:c], keys[b]["y"][:c]], 1), K[0, 0], K[1, 1], K[0, 2], K[1, 2], D)
+            assert np.array_equal(out[b]["x"][:c], exp[:, 0]) and np.array_equal(out[b]["y"][:c], exp[:, 1]), (name, b)
+            if b == 0:
+                assert np.array_equal(exp, und)                                  # == cv2.undistortPoints
+            for f in ("size", "angle", "response", "octave", "class_id"):
+                assert np.array_equal(out[b][f][:c], keys[b][f][:c])
+            assert (out[b]["class_id"][c:] == 12345).all()
+        same = m.UndistortKeyPoints(keys, counts, K[0, 0], K[1, 1], K[0, 2], K[1, 2], [0.0, 0.2, 0.0, 0.0])
+        assert same[0].tobytes() == keys[0].tobytes()
