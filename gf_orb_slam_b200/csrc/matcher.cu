@@ -117,6 +117,9 @@ struct QParams {
     float window;                 // INIT / WINDOW
     int minScaleLevel, maxScaleLevel;   // WINDOW
     float th;                     // MAP / LAST
+    float thGood;                 // MAP / LAST, SearchByProjection_GoodFeature: window factor of the good features
+    int goodMode;                 // 1: good features (MAP: mpFlags bit2, LAST: srcGood) use thGood, the rest th (= th_rest)
+    const uint8_t* srcGood;       // LAST + goodMode: batch x src.stride
     const float *mpU, *mpV, *mpCos;     // MAP
     const int32_t* mpLevel;
     const uint8_t *mpFlags, *mpDesc;
@@ -238,7 +241,8 @@ __global__ void __launch_bounds__(128) k_candidates(const QParams P, const Frame
         int lvl = P.mpLevel[i];
         lvl = min(max(lvl, 0), P.nlevels - 1);
         float rr = (P.mpCos[i] > 0.998) ? 2.5f : 4.0f;    // RadiusByViewingCos (float vs double literal)
-        if (P.th != 1.0f) rr *= P.th;
+        if (P.goodMode && (fl & 4)) rr *= P.thGood;       // src/ORBmatcher.cc:73-80 (goodAtFrameId == F.mnId)
+        else if (P.th != 1.0f) rr *= P.th;
         x = P.mpU[i]; y = P.mpV[i];
         r = rr * P.scale[lvl];
         minL = P.mpLevel[i] - 1; maxL = P.mpLevel[i];
@@ -264,7 +268,7 @@ __global__ void __launch_bounds__(128) k_candidates(const QParams P, const Frame
             if (v < (float)G.iminY || v > (float)G.imaxY) active = false;
             const int oct = P.src.kps[i].octave;
             x = u; y = v;
-            r = P.th * P.scale[min(max(oct, 0), P.nlevels - 1)];
+            r = ((P.goodMode && P.srcGood[i]) ? P.thGood : P.th) * P.scale[min(max(oct, 0), P.nlevels - 1)];   // :46-53
             minL = oct - 1; maxL = oct + 1;
         }
         qdp = P.src.desc + i * 32;
@@ -952,15 +956,17 @@ int gforb_search_for_initialization(GforbMatcher* M, const GforbFrameSet* F1, co
     return end_call(M, c, flags);
 }
 
-int gforb_search_by_projection(GforbMatcher* M, const GforbFrameSet* F, const GforbMapPointSet* mps, int batch,
-                               float th, float nnratio, int32_t* frame_mappoints, int32_t* match_score,
-                               int32_t* nmatches, int flags, void* stream) {
+// shared body of SearchByProjection(F, MPs, th) and SearchByProjection_GoodFeature(F, MPs, th_good, th_rest); the latter
+// does not store match scores (match_score == nullptr -> the resolver writes into scratch)
+static int sbp_map(GforbMatcher* M, const GforbFrameSet* F, const GforbMapPointSet* mps, int batch, float th, float thGood,
+                   int goodMode, float nnratio, int32_t* frame_mappoints, int32_t* match_score, int32_t* nmatches, int flags,
+                   void* stream) {
     Ctx c;
     int rc = begin_call(M, batch, flags, stream, c);
     if (rc) return rc;
     if ((rc = check_frames(M, F))) return rc;
     if (!mps || !mps->proj_x || !mps->proj_y || !mps->scale_level || !mps->view_cos || !mps->flags || !mps->descriptors ||
-        !mps->counts || mps->mp_stride <= 0 || !frame_mappoints || !match_score || !nmatches)
+        !mps->counts || mps->mp_stride <= 0 || !frame_mappoints || (!match_score && !goodMode) || !nmatches)
         return GFORB_ERR_ARG;
     if (mps->mp_stride > M->cfg.max_queries) return GFORB_ERR_CAPACITY;
     if (batch == 0) return GFORB_OK;
@@ -973,8 +979,11 @@ int gforb_search_by_projection(GforbMatcher* M, const GforbFrameSet* F, const Gf
     P.mpU = c.in(mps->proj_x, nm); P.mpV = c.in(mps->proj_y, nm); P.mpCos = c.in(mps->view_cos, nm);
     P.mpLevel = c.in(mps->scale_level, nm); P.mpFlags = c.in(mps->flags, nm); P.mpDesc = c.in(mps->descriptors, nm * 32);
     P.mpCounts = c.in(mps->counts, (size_t)batch); P.mpStride = mps->mp_stride; P.th = th;
+    P.thGood = thGood; P.goodMode = goodMode;
     int32_t* dMp = c.out(frame_mappoints, (size_t)batch * F->kp_stride, true);
-    int32_t* dSc = c.out(match_score, (size_t)batch * F->kp_stride, true);
+    int32_t* dSc = match_score ? c.out(match_score, (size_t)batch * F->kp_stride, true)
+                               : (int32_t*)M->arena.take((size_t)batch * F->kp_stride * sizeof(int32_t));
+    if (!dSc) return GFORB_ERR_CAPACITY;
     int32_t* dN = c.out(nmatches, (size_t)batch, false);
     if (c.rc) return c.rc;
     build_grid(M, c, T, G, batch);
@@ -986,6 +995,18 @@ int gforb_search_by_projection(GforbMatcher* M, const GforbFrameSet* F, const Gf
     R.tgtMp = dMp; R.tgtScore = dSc; R.nmatches = dN; R.rotBinQ = M->d_rotBinQ;
     run_resolve<M_MAP>(M, c, R, batch);
     return end_call(M, c, flags);
+}
+
+int gforb_search_by_projection(GforbMatcher* M, const GforbFrameSet* F, const GforbMapPointSet* mps, int batch,
+                               float th, float nnratio, int32_t* frame_mappoints, int32_t* match_score,
+                               int32_t* nmatches, int flags, void* stream) {
+    return sbp_map(M, F, mps, batch, th, 0.0f, 0, nnratio, frame_mappoints, match_score, nmatches, flags, stream);
+}
+
+int gforb_search_by_projection_good_feature(GforbMatcher* M, const GforbFrameSet* F, const GforbMapPointSet* mps, int batch,
+                                            float th_good, float th_rest, float nnratio, int32_t* frame_mappoints,
+                                            int32_t* nmatches, int flags, void* stream) {
+    return sbp_map(M, F, mps, batch, th_rest, th_good, 1, nnratio, frame_mappoints, nullptr, nmatches, flags, stream);
 }
 
 int gforb_obs_active_match(GforbObs* O, GforbMatcher* M, const GforbFrameSet* F, const GforbMapPointSet* mps, int batch,
@@ -1102,16 +1123,18 @@ int gforb_frame_undistort_keypoints(GforbMatcher* M, int batch, const GforbKeyPo
     return end_call(M, c, flags);
 }
 
-int gforb_search_by_projection_frames(GforbMatcher* M, const GforbFrameSet* cur, const GforbFrameSet* last, int batch,
-                                      const int32_t* last_mappoints, const uint8_t* last_outlier,
-                                      const float* last_world, const float* Tcw, float fx, float fy, float cx, float cy,
-                                      float th, float nnratio, int check_orientation, int32_t* cur_mappoints,
-                                      int32_t* cur_score, int32_t* nmatches, int flags, void* stream) {
+// shared body of SearchByProjection(Cur, Last, th) and SearchByProjection_GoodFeature(Cur, Last, th_good, th_rest)
+static int sbp_last(GforbMatcher* M, const GforbFrameSet* cur, const GforbFrameSet* last, int batch,
+                    const int32_t* last_mappoints, const uint8_t* last_outlier, const uint8_t* last_good, const float* last_world,
+                    const float* Tcw, float fx, float fy, float cx, float cy, float th, float thGood, int goodMode, float nnratio,
+                    int check_orientation, int32_t* cur_mappoints, int32_t* cur_score, int32_t* nmatches, int flags,
+                    void* stream) {
     Ctx c;
     int rc = begin_call(M, batch, flags, stream, c);
     if (rc) return rc;
     if ((rc = check_frames(M, cur)) || (rc = check_frames(M, last))) return rc;
-    if (!last_mappoints || !last_world || !Tcw || !cur_mappoints || !cur_score || !nmatches) return GFORB_ERR_ARG;
+    if (!last_mappoints || !last_world || !Tcw || !cur_mappoints || (!cur_score && !goodMode) || (goodMode && !last_good) || !nmatches)
+        return GFORB_ERR_ARG;
     if (last->kp_stride > M->cfg.max_queries) return GFORB_ERR_CAPACITY;
     if (batch == 0) return GFORB_OK;
     FrameDev T = c.frame(cur, batch), S = c.frame(last, batch);
@@ -1123,8 +1146,11 @@ int gforb_search_by_projection_frames(GforbMatcher* M, const GforbFrameSet* cur,
     P.src = S; P.srcMp = c.in(last_mappoints, ns); P.srcOutlier = c.in(last_outlier, ns);
     P.srcWorld = c.in(last_world, ns * 3); P.Tcw = c.in(Tcw, (size_t)batch * 16);
     P.fx = fx; P.fy = fy; P.cx = cx; P.cy = cy; P.th = th;
+    P.thGood = thGood; P.goodMode = goodMode; P.srcGood = goodMode ? c.in(last_good, ns) : nullptr;
     int32_t* dMp = c.out(cur_mappoints, (size_t)batch * cur->kp_stride, true);
-    int32_t* dSc = c.out(cur_score, (size_t)batch * cur->kp_stride, true);
+    int32_t* dSc = cur_score ? c.out(cur_score, (size_t)batch * cur->kp_stride, true)
+                             : (int32_t*)M->arena.take((size_t)batch * cur->kp_stride * sizeof(int32_t));
+    if (!dSc) return GFORB_ERR_CAPACITY;
     int32_t* dN = c.out(nmatches, (size_t)batch, false);
     if (c.rc) return c.rc;
     build_grid(M, c, T, G, batch);
@@ -1136,6 +1162,25 @@ int gforb_search_by_projection_frames(GforbMatcher* M, const GforbFrameSet* cur,
     R.checkOri = check_orientation; R.tgtMp = dMp; R.tgtScore = dSc; R.nmatches = dN; R.rotBinQ = M->d_rotBinQ;
     run_resolve<M_LAST>(M, c, R, batch);
     return end_call(M, c, flags);
+}
+
+int gforb_search_by_projection_frames(GforbMatcher* M, const GforbFrameSet* cur, const GforbFrameSet* last, int batch,
+                                      const int32_t* last_mappoints, const uint8_t* last_outlier,
+                                      const float* last_world, const float* Tcw, float fx, float fy, float cx, float cy,
+                                      float th, float nnratio, int check_orientation, int32_t* cur_mappoints,
+                                      int32_t* cur_score, int32_t* nmatches, int flags, void* stream) {
+    return sbp_last(M, cur, last, batch, last_mappoints, last_outlier, nullptr, last_world, Tcw, fx, fy, cx, cy, th, 0.0f, 0, nnratio,
+                    check_orientation, cur_mappoints, cur_score, nmatches, flags, stream);
+}
+
+int gforb_search_by_projection_frames_good_feature(GforbMatcher* M, const GforbFrameSet* cur, const GforbFrameSet* last, int batch,
+                                                   const int32_t* last_mappoints, const uint8_t* last_outlier,
+                                                   const uint8_t* last_good, const float* last_world, const float* Tcw, float fx,
+                                                   float fy, float cx, float cy, float th_good, float th_rest, float nnratio,
+                                                   int check_orientation, int32_t* cur_mappoints, int32_t* nmatches, int flags,
+                                                   void* stream) {
+    return sbp_last(M, cur, last, batch, last_mappoints, last_outlier, last_good, last_world, Tcw, fx, fy, cx, cy, th_rest, th_good, 1,
+                    nnratio, check_orientation, cur_mappoints, nullptr, nmatches, flags, stream);
 }
 
 int gforb_window_search(GforbMatcher* M, const GforbFrameSet* F1, const GforbFrameSet* F2, int batch,

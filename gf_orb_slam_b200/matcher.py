@@ -205,6 +205,52 @@ class ORBmatcher:
             "gforb_search_by_projection_frames")
         return nmatches
 
+    # -- int SearchByProjection_GoodFeature(Frame &F, const vector<MapPoint*>&, th_good, th_rest)
+    def SearchByProjection_GoodFeature(self, F: Frames, mps: MapPoints, th_good, th_rest, mvpMapPoints, *, nmatches=None,
+                                       stream=None, sync=True):
+        """src/ORBmatcher.cc:51-140.  Bit2 of mps.flags marks the good features (goodAtFrameId == F.mnId); mvpMatchScore is
+        not written by this overload."""
+        out_dev = is_device(mvpMapPoints)
+        if nmatches is None:
+            if out_dev:
+                import torch
+                nmatches = torch.empty(F.batch, dtype=torch.int32, device=mvpMapPoints.device)
+            else:
+                nmatches = np.empty(F.batch, np.int32)
+        fs, ms = F.cstruct(), mps.cstruct()
+        check(_lib.lib().gforb_search_by_projection_good_feature(
+            self._h, C.byref(fs), C.byref(ms), F.batch, float(th_good), float(th_rest), self.mfNNratio, ptr(mvpMapPoints),
+            ptr(nmatches), self._flags(F.device, out_dev, sync), C.c_void_p(stream or 0)),
+            "gforb_search_by_projection_good_feature")
+        return nmatches
+
+    # -- int SearchByProjection_Budget(Frame &F, const vector<MapPoint*>&, th, time_constr)
+    def SearchByProjection_Budget(self, F: Frames, mps: MapPoints, th, time_constr, mvpMapPoints, mvpMatchScore, **kw):
+        """src/ORBmatcher.cc:276-379: nothing for a non-positive budget, else the plain search (budgets are unlimited here)."""
+        if time_constr <= 0:
+            return np.zeros(F.batch, np.int32)
+        return self.SearchByProjection(F, mps, th, mvpMapPoints, mvpMatchScore, **kw)
+
+    # -- int SearchByProjection_GoodFeature(Frame &CurrentFrame, const Frame &LastFrame, th_good, th_rest)
+    def SearchByProjectionFrames_GoodFeature(self, Cur: Frames, Last: Frames, last_mappoints, last_outlier, last_good, last_world,
+                                             Tcw, K, th_good, th_rest, cur_mappoints, *, nmatches=None, stream=None, sync=True):
+        """src/ORBmatcher.cc:143-274.  last_good (B, stride) uint8: goodAtFrameId == CurrentFrame.mnId per last-frame map point."""
+        out_dev = is_device(cur_mappoints)
+        if nmatches is None:
+            if out_dev:
+                import torch
+                nmatches = torch.empty(Cur.batch, dtype=torch.int32, device=cur_mappoints.device)
+            else:
+                nmatches = np.empty(Cur.batch, np.int32)
+        fx, fy, cx, cy = [float(v) for v in K]
+        c, l = Cur.cstruct(), Last.cstruct()
+        check(_lib.lib().gforb_search_by_projection_frames_good_feature(
+            self._h, C.byref(c), C.byref(l), Cur.batch, ptr(last_mappoints), ptr(last_outlier), ptr(last_good), ptr(last_world),
+            ptr(Tcw), fx, fy, cx, cy, float(th_good), float(th_rest), self.mfNNratio, int(self.mbCheckOrientation),
+            ptr(cur_mappoints), ptr(nmatches), self._flags(Cur.device, out_dev, sync), C.c_void_p(stream or 0)),
+            "gforb_search_by_projection_frames_good_feature")
+        return nmatches
+
     # -- int WindowSearch(F1, F2, windowSize, vpMapPointMatches2, minScaleLevel=-1, maxScaleLevel=INT_MAX)
     def WindowSearch(self, F1: Frames, F2: Frames, f1_mappoints, windowSize, minScaleLevel=-1, maxScaleLevel=0x7FFFFFFF,
                      *, stream=None, sync=True):

@@ -157,6 +157,16 @@ int gforb_search_by_projection(GforbMatcher* h, const GforbFrameSet* F, const Gf
                                float th, float nnratio, int32_t* frame_mappoints, int32_t* match_score,
                                int32_t* nmatches, int flags, void* stream);
 
+/* ORBmatcher::SearchByProjection_GoodFeature(Frame& F, const vector<MapPoint*>&, th_good, th_rest)
+ * (src/ORBmatcher.cc:51-140): as gforb_search_by_projection, but the search window of a map point with
+ * goodAtFrameId == F.mnId (bit2 of GforbMapPointSet::flags) is scaled by th_good and of the others by th_rest (when
+ * th_rest != 1); Frame::mvpMatchScore is not written by this overload.
+ * ORBmatcher::SearchByProjection_Budget(F, MPs, th, time_constr) (:276-379) is gforb_search_by_projection when
+ * time_constr > 0 and matches nothing otherwise (wall-clock budgets are unlimited on this path). */
+int gforb_search_by_projection_good_feature(GforbMatcher* h, const GforbFrameSet* F, const GforbMapPointSet* mps, int batch,
+                                            float th_good, float th_rest, float nnratio, int32_t* frame_mappoints,
+                                            int32_t* nmatches, int flags, void* stream);
+
 /* Frame::isInFrustum(MapPoint*, viewingCosLimit) (src/Frame.cc:166-227) for every map point of `batch` frames: the
  * pass that produces the GforbMapPointSet fields SearchByProjection reads.  Rcw / tcw / Ow: batch x 9 / 3 / 3 (Frame::mRcw
  * row-major, mtcw, mOw); world / normal: batch x mp_stride x 3 (MapPoint::GetWorldPos / GetNormal); min_distance /
@@ -185,6 +195,18 @@ int gforb_search_by_projection_frames(GforbMatcher* h, const GforbFrameSet* cur,
                                       const float* last_world, const float* Tcw, float fx, float fy, float cx, float cy,
                                       float th, float nnratio, int check_orientation, int32_t* cur_mappoints,
                                       int32_t* cur_score, int32_t* nmatches, int flags, void* stream);
+
+/* ORBmatcher::SearchByProjection_GoodFeature(Frame& Current, const Frame& Last, th_good, th_rest)
+ * (src/ORBmatcher.cc:143-274; the call Tracking::TrackWithMotionModel makes, src/Tracking.cc:1442): as
+ * gforb_search_by_projection_frames with the radius th_good * scale for last-frame map points with
+ * goodAtFrameId == Current.mnId (last_good: batch x last.kp_stride, non-zero = good) and th_rest * scale for the others;
+ * no match score is stored or reset. */
+int gforb_search_by_projection_frames_good_feature(GforbMatcher* h, const GforbFrameSet* cur, const GforbFrameSet* last, int batch,
+                                                   const int32_t* last_mappoints, const uint8_t* last_outlier,
+                                                   const uint8_t* last_good, const float* last_world, const float* Tcw, float fx,
+                                                   float fy, float cx, float cy, float th_good, float th_rest, float nnratio,
+                                                   int check_orientation, int32_t* cur_mappoints, int32_t* nmatches, int flags,
+                                                   void* stream);
 
 /* ORBmatcher::WindowSearch(F1, F2, windowSize, vpMapPointMatches2, minScaleLevel, maxScaleLevel)
  * (src/ORBmatcher.cc:979-1086).  f1_mappoints: batch x F1.kp_stride ids (>= 0: non-NULL, not bad);

@@ -148,6 +148,7 @@ struct MapPoint {
     double H_meas[14] = {0};                         // 2x7 row-major [H13 H47]
     double ObsMat[49] = {0};                         // 7x7 row-major
     long unsigned int updateAtFrameId = 0;
+    long unsigned int goodAtFrameId = 0;             // good-feature stamp read by SearchByProjection_GoodFeature
     bool isBad() const { return mbBad; }
     const uint8_t* GetDescriptor() const { return mDescriptor; }
 };
@@ -208,6 +209,22 @@ public:
     // Search matches between Frame keypoints and projected MapPoints; returns the number of matches
     // (include/ORBmatcher.h:48-50, src/ORBmatcher.cc:384-465).  F.mvpMapPoints / F.mvpMatchScore are updated in place.
     int SearchByProjection(Frame& F, const std::vector<MapPoint*>& vpMapPoints, const float th = 3) {
+        return searchMap(F, vpMapPoints, th, 0.f, false);
+    }
+    // include/ORBmatcher.h:52-53, src/ORBmatcher.cc:51-140: window x th_good for points with goodAtFrameId == F.mnId,
+    // x th_rest for the others; F.mvpMatchScore is left alone by this overload.
+    int SearchByProjection_GoodFeature(Frame& F, const std::vector<MapPoint*>& vpMapPoints, const float th_good, const float th_rest) {
+        return searchMap(F, vpMapPoints, th_rest, th_good, true);
+    }
+    // include/ORBmatcher.h:67-68, src/ORBmatcher.cc:276-379: a spent budget matches nothing; this path has no wall-clock
+    // cut-off inside the search, so a positive budget is the plain search.
+    int SearchByProjection_Budget(Frame& F, const std::vector<MapPoint*>& vpMapPoints, const float th, const double time_constr) {
+        if (time_constr <= 0) return 0;
+        return searchMap(F, vpMapPoints, th, 0.f, false);
+    }
+
+private:
+    int searchMap(Frame& F, const std::vector<MapPoint*>& vpMapPoints, float th, float thGood, bool goodMode) {
         const int M = (int)vpMapPoints.size();
         if (F.N == 0 || M == 0) return 0;
         ensure(F.N, M, F.mnScaleLevels, F.mfScaleFactor);
@@ -217,21 +234,27 @@ public:
         for (int i = 0; i < M; i++) {
             const MapPoint* p = vpMapPoints[i];
             u[i] = p->mTrackProjX; v[i] = p->mTrackProjY; vc[i] = p->mTrackViewCos; lvl[i] = p->mnTrackScaleLevel;
-            fl[i] = (uint8_t)((p->mbTrackInView ? 1 : 0) | (p->isBad() ? 2 : 0));
+            fl[i] = (uint8_t)((p->mbTrackInView ? 1 : 0) | (p->isBad() ? 2 : 0) | ((goodMode && p->goodAtFrameId == F.mnId) ? 4 : 0));
             std::memcpy(&desc[(size_t)i * 32], p->GetDescriptor(), 32);
         }
         FlatFrame ff(F);
         std::vector<int32_t> ids = ids_of(F, vpMapPoints), score(F.mvpMatchScore.begin(), F.mvpMatchScore.end());
         int32_t mcount = M, n = 0;
         GforbMapPointSet mp = {u.data(), v.data(), lvl.data(), vc.data(), fl.data(), desc.data(), &mcount, M};
-        gforb_throw(gforb_search_by_projection(h_, &ff.set, &mp, 1, th, mfNNratio, ids.data(), score.data(), &n, 0, nullptr),
-                    "SearchByProjection");
+        if (goodMode)
+            gforb_throw(gforb_search_by_projection_good_feature(h_, &ff.set, &mp, 1, thGood, th, mfNNratio, ids.data(), &n, 0, nullptr),
+                        "SearchByProjection_GoodFeature");
+        else
+            gforb_throw(gforb_search_by_projection(h_, &ff.set, &mp, 1, th, mfNNratio, ids.data(), score.data(), &n, 0, nullptr),
+                        "SearchByProjection");
         for (int i = 0; i < F.N; i++) {
             if (ids[i] >= 0 && ids[i] < M) F.mvpMapPoints[i] = vpMapPoints[ids[i]];
-            F.mvpMatchScore[i] = score[i];
+            if (!goodMode) F.mvpMatchScore[i] = score[i];
         }
         return n;
     }
+
+public:
 
     // Frame::isInFrustum(pMP, viewingCosLimit) (src/Frame.cc:166-227) for every point of vpMapPoints in one call
     // (Tracking::SearchReferencePointsInFrustum loops over the local map, src/Tracking.cc): sets mbTrackInView and,
@@ -305,34 +328,53 @@ public:
     // Project MapPoints tracked in the last frame into the current frame and search matches
     // (include/ORBmatcher.h:52-54, src/ORBmatcher.cc:2081-2202).
     int SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, float th) {
+        return searchLast(CurrentFrame, LastFrame, th, 0.f, false);
+    }
+    // include/ORBmatcher.h:55-56, src/ORBmatcher.cc:143-274 (the call of Tracking::TrackWithMotionModel, src/Tracking.cc:1442)
+    int SearchByProjection_GoodFeature(Frame& CurrentFrame, const Frame& LastFrame, const float th_good, const float th_rest) {
+        return searchLast(CurrentFrame, LastFrame, th_rest, th_good, true);
+    }
+
+private:
+    int searchLast(Frame& CurrentFrame, const Frame& LastFrame, float th, float thGood, bool goodMode) {
         if (CurrentFrame.N == 0 || LastFrame.N == 0) return 0;
         ensure(std::max(CurrentFrame.N, LastFrame.N), LastFrame.N, CurrentFrame.mnScaleLevels, CurrentFrame.mfScaleFactor);
         FlatFrame cur(CurrentFrame), last(LastFrame);
         const int NL = LastFrame.N;
         std::vector<int32_t> lastIds(NL, -1);
-        std::vector<uint8_t> outl(NL, 0);
+        std::vector<uint8_t> outl(NL, 0), good(NL, 0);
         std::vector<float> world((size_t)NL * 3, 0.f);
         for (int i = 0; i < NL; i++) {
             const MapPoint* p = LastFrame.mvpMapPoints[i];
             if (!p) continue;
             lastIds[i] = i; outl[i] = LastFrame.mvbOutlier[i] ? 1 : 0;
+            good[i] = p->goodAtFrameId == CurrentFrame.mnId ? 1 : 0;
             std::memcpy(&world[(size_t)i * 3], p->mWorldPos, 12);
         }
         std::vector<int32_t> ids(CurrentFrame.N, -1), score(CurrentFrame.mvpMatchScore.begin(), CurrentFrame.mvpMatchScore.end());
         for (int i = 0; i < CurrentFrame.N; i++) if (CurrentFrame.mvpMapPoints[i]) ids[i] = NL;   // already claimed
         int32_t n = 0;
-        gforb_throw(gforb_search_by_projection_frames(h_, &cur.set, &last.set, 1, lastIds.data(), outl.data(), world.data(),
-                                                      CurrentFrame.mTcw, CurrentFrame.fx, CurrentFrame.fy, CurrentFrame.cx,
-                                                      CurrentFrame.cy, th, mfNNratio, mbCheckOrientation ? 1 : 0, ids.data(),
-                                                      score.data(), &n, 0, nullptr),
-                    "SearchByProjection(Current, Last)");
+        if (goodMode)
+            gforb_throw(gforb_search_by_projection_frames_good_feature(
+                            h_, &cur.set, &last.set, 1, lastIds.data(), outl.data(), good.data(), world.data(), CurrentFrame.mTcw,
+                            CurrentFrame.fx, CurrentFrame.fy, CurrentFrame.cx, CurrentFrame.cy, thGood, th, mfNNratio,
+                            mbCheckOrientation ? 1 : 0, ids.data(), &n, 0, nullptr),
+                        "SearchByProjection_GoodFeature(Current, Last)");
+        else
+            gforb_throw(gforb_search_by_projection_frames(h_, &cur.set, &last.set, 1, lastIds.data(), outl.data(), world.data(),
+                                                          CurrentFrame.mTcw, CurrentFrame.fx, CurrentFrame.fy, CurrentFrame.cx,
+                                                          CurrentFrame.cy, th, mfNNratio, mbCheckOrientation ? 1 : 0, ids.data(),
+                                                          score.data(), &n, 0, nullptr),
+                        "SearchByProjection(Current, Last)");
         for (int i = 0; i < CurrentFrame.N; i++) {
             if (ids[i] >= 0 && ids[i] < NL) CurrentFrame.mvpMapPoints[i] = LastFrame.mvpMapPoints[ids[i]];
             else if (ids[i] < 0) CurrentFrame.mvpMapPoints[i] = nullptr;
-            CurrentFrame.mvpMatchScore[i] = score[i];
+            if (!goodMode) CurrentFrame.mvpMatchScore[i] = score[i];
         }
         return n;
     }
+
+public:
 
     // src/ORBmatcher.cc:979-1086
     int WindowSearch(Frame& F1, Frame& F2, int windowSize, std::vector<MapPoint*>& vpMapPointMatches2,

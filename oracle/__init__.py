@@ -223,6 +223,23 @@ def search_by_projection_frames(cur: Frame, last: Frame, last_world: np.ndarray,
     return lib().orc_search_by_projection_frames(cur.h, last.h, _p(lw), C.c_float(th), C.c_float(nnratio), int(checkOri))
 
 
+def search_by_projection_good_feature(F: Frame, u, v, level, viewCos, flags, desc, th_good: float, th_rest: float, nnratio: float) -> int:
+    """ORBmatcher::SearchByProjection_GoodFeature(F, MPs, th_good, th_rest) (src/ORBmatcher.cc:51-140); flags bit2 = good"""
+    u = np.ascontiguousarray(u, np.float32); v = np.ascontiguousarray(v, np.float32)
+    level = np.ascontiguousarray(level, np.int32); viewCos = np.ascontiguousarray(viewCos, np.float32)
+    flags = np.ascontiguousarray(flags, np.uint8); desc = np.ascontiguousarray(desc, np.uint8)
+    return lib().orc_search_by_projection_good(F.h, u.size, _p(u), _p(v), _p(level), _p(viewCos), _p(flags), _p(desc),
+                                               C.c_float(th_good), C.c_float(th_rest), C.c_float(nnratio))
+
+
+def search_by_projection_frames_good_feature(cur: Frame, last: Frame, last_world, good, th_good: float, th_rest: float,
+                                             nnratio=0.9, checkOri=True) -> int:
+    """ORBmatcher::SearchByProjection_GoodFeature(Cur, Last, th_good, th_rest) (src/ORBmatcher.cc:143-274)"""
+    lw = np.ascontiguousarray(last_world, np.float32); g = np.ascontiguousarray(good, np.uint8)
+    return lib().orc_search_by_projection_frames_good(cur.h, last.h, _p(lw), _p(g), C.c_float(th_good), C.c_float(th_rest),
+                                                      C.c_float(nnratio), int(checkOri))
+
+
 def search_for_initialization(F1: Frame, F2: Frame, prev_matched: np.ndarray, window: int, nnratio=0.9, checkOri=True):
     pm = np.ascontiguousarray(prev_matched, np.float32).copy()
     m12 = np.empty(F1.N, np.int32)

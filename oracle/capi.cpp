@@ -136,6 +136,25 @@ int orc_search_by_projection(void* fp, int M, const float* u, const float* v, co
     ORBmatcher m(nnratio, true);
     return m.SearchByProjection(*(Frame*)fp, mps, th);
 }
+// SearchByProjection_GoodFeature(F, MPs, th_good, th_rest): flags bit2 = goodAtFrameId == F.mnId
+int orc_search_by_projection_good(void* fp, int M, const float* u, const float* v, const int* level, const float* viewCos,
+                                  const uint8_t* flags, const uint8_t* desc, float th_good, float th_rest, float nnratio) {
+    std::vector<MapPointView> mps(M);
+    std::vector<uint8_t> good(M);
+    for (int i = 0; i < M; i++) {
+        mps[i].mTrackProjX = u[i]; mps[i].mTrackProjY = v[i]; mps[i].mnTrackScaleLevel = level[i];
+        mps[i].mTrackViewCos = viewCos[i]; mps[i].mbTrackInView = flags[i] & 1; mps[i].isBad = (flags[i] >> 1) & 1;
+        good[i] = (flags[i] >> 2) & 1;
+        memcpy(mps[i].desc, desc + (size_t)32 * i, 32);
+    }
+    ORBmatcher m(nnratio, true);
+    return m.SearchByProjection_GoodFeature(*(Frame*)fp, mps, good.data(), th_good, th_rest);
+}
+int orc_search_by_projection_frames_good(void* cur, void* last, const float* lastWorldPos, const uint8_t* good, float th_good,
+                                         float th_rest, float nnratio, int checkOri) {
+    ORBmatcher m(nnratio, checkOri != 0);
+    return m.SearchByProjection_GoodFeature(*(Frame*)cur, *(const Frame*)last, lastWorldPos, good, th_good, th_rest);
+}
 int orc_search_by_projection_frames(void* cur, void* last, const float* lastWorldPos, float th, float nnratio, int checkOri) {
     ORBmatcher m(nnratio, checkOri != 0);
     return m.SearchByProjection(*(Frame*)cur, *(const Frame*)last, lastWorldPos, th);

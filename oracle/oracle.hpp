@@ -123,6 +123,12 @@ public:
     static int DescriptorDistance(const uint8_t* a, const uint8_t* b);
     int SearchByProjection(Frame& F, const std::vector<MapPointView>& vpMapPoints, float th);
     int SearchByProjection_OnePoint(Frame& F, const MapPointView& mp, int mpId, float th);
+    // good[i] = (goodAtFrameId == F.mnId) of map point i / of LastFrame.mvpMapPoints[i]
+    int SearchByProjection_GoodFeature(Frame& F, const std::vector<MapPointView>& vpMapPoints, const uint8_t* good, float th_good,
+                                       float th_rest);
+    int SearchByProjection_GoodFeature(Frame& Cur, const Frame& Last, const float* lastWorldPos, const uint8_t* good,
+                                       float th_good, float th_rest);
+    int SearchByProjection_Budget(Frame& F, const std::vector<MapPointView>& vpMapPoints, float th, double time_constr);
     // last-frame variant: world positions of LastFrame's map points are given per keypoint (or id<0)
     int SearchByProjection(Frame& Cur, const Frame& Last, const float* lastWorldPos /*N x 3*/, float th);
     int SearchForInitialization(const Frame& F1, const Frame& F2, std::vector<float>& vbPrevMatched /*N1 x 2*/,

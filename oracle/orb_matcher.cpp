@@ -204,6 +204,113 @@ int ORBmatcher::SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, 
     return nmatches;
 }
 
+// src/ORBmatcher.cc:51-140: SearchByProjection(F, MPs, th) with the window of a good feature (goodAtFrameId == F.mnId)
+// scaled by th_good and of the rest by th_rest; F.mvpMatchScore is NOT written by this variant.
+int ORBmatcher::SearchByProjection_GoodFeature(Frame& F, const std::vector<MapPointView>& vpMapPoints, const uint8_t* good,
+                                               float th_good, float th_rest) {
+    int nmatches = 0;
+    const bool bFactor = th_rest != 1.0;
+    for (size_t iMP = 0; iMP < vpMapPoints.size(); iMP++) {
+        const MapPointView& mp = vpMapPoints[iMP];
+        if (!mp.mbTrackInView) continue;
+        if (mp.isBad) continue;
+        const int nPredictedLevel = mp.mnTrackScaleLevel;
+        float r = RadiusByViewingCos(mp.mTrackViewCos);
+        if (good[iMP]) r *= th_good;
+        else if (bFactor) r *= th_rest;
+        std::vector<size_t> vNearIndices = F.GetFeaturesInArea(mp.mTrackProjX, mp.mTrackProjY, r * F.mvScaleFactors[nPredictedLevel],
+                                                               nPredictedLevel - 1, nPredictedLevel);
+        if (vNearIndices.empty()) continue;
+        int bestDist = INT_MAX, bestLevel = -1, bestDist2 = INT_MAX, bestLevel2 = -1, bestIdx = -1;
+        for (size_t idx : vNearIndices) {
+            if (F.mvpMapPoints[idx] >= 0) continue;
+            const int dist = DescriptorDistance(mp.desc, &F.mDescriptors[idx * 32]);
+            if (dist < bestDist) {
+                bestDist2 = bestDist; bestDist = dist;
+                bestLevel2 = bestLevel; bestLevel = F.mvKeysUn[idx].octave;
+                bestIdx = idx;
+            } else if (dist < bestDist2) {
+                bestLevel2 = F.mvKeysUn[idx].octave;
+                bestDist2 = dist;
+            }
+        }
+        if (bestDist <= TH_HIGH) {
+            if (bestLevel == bestLevel2 && bestDist > mfNNratio * bestDist2) continue;
+            F.mvpMapPoints[bestIdx] = (int)iMP;
+            nmatches++;
+        }
+    }
+    return nmatches;
+}
+
+// src/ORBmatcher.cc:143-274: SearchByProjection(Cur, Last, th) with radius th_good / th_rest per last-frame map point;
+// no match score is stored or reset.
+int ORBmatcher::SearchByProjection_GoodFeature(Frame& CurrentFrame, const Frame& LastFrame, const float* lastWorldPos,
+                                               const uint8_t* good, float th_good, float th_rest) {
+    int nmatches = 0;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = 1.0f / HISTO_LENGTH;
+    const float* T = CurrentFrame.mTcw;
+    for (size_t i = 0; i < LastFrame.mvpMapPoints.size(); i++) {
+        if (LastFrame.mvpMapPoints[i] < 0) continue;
+        if (LastFrame.mvbOutlier[i]) continue;
+        const float* X = lastWorldPos + 3 * i;
+        float xc3[3];
+        for (int r = 0; r < 3; r++) {
+            double s = (double)T[r * 4 + 0] * X[0] + (double)T[r * 4 + 1] * X[1] + (double)T[r * 4 + 2] * X[2];
+            xc3[r] = (float)s + T[r * 4 + 3];
+        }
+        const float xc = xc3[0], yc = xc3[1];
+        const float invzc = 1.0 / xc3[2];
+        float u = CurrentFrame.fx * xc * invzc + CurrentFrame.cx;
+        float v = CurrentFrame.fy * yc * invzc + CurrentFrame.cy;
+        if (u < CurrentFrame.mnMinX || u > CurrentFrame.mnMaxX) continue;
+        if (v < CurrentFrame.mnMinY || v > CurrentFrame.mnMaxY) continue;
+        int nPredictedOctave = LastFrame.mvKeysUn[i].octave;
+        float radius;
+        if (good[i]) radius = th_good * CurrentFrame.mvScaleFactors[nPredictedOctave];
+        else radius = th_rest * CurrentFrame.mvScaleFactors[nPredictedOctave];
+        std::vector<size_t> vIndices2 = CurrentFrame.GetFeaturesInArea(u, v, radius, nPredictedOctave - 1, nPredictedOctave + 1);
+        if (vIndices2.empty()) continue;
+        const uint8_t* dMP = &LastFrame.mDescriptors[i * 32];
+        int bestDist = INT_MAX, bestIdx2 = -1;
+        for (size_t i2 : vIndices2) {
+            if (CurrentFrame.mvpMapPoints[i2] >= 0) continue;
+            int dist = DescriptorDistance(dMP, &CurrentFrame.mDescriptors[i2 * 32]);
+            if (dist < bestDist) { bestDist = dist; bestIdx2 = i2; }
+        }
+        if (bestDist <= TH_HIGH) {
+            CurrentFrame.mvpMapPoints[bestIdx2] = LastFrame.mvpMapPoints[i];
+            nmatches++;
+            if (mbCheckOrientation) {
+                float rot = LastFrame.mvKeysUn[i].angle - CurrentFrame.mvKeysUn[bestIdx2].angle;
+                if (rot < 0.0) rot += 360.0f;
+                int bin = std::round(rot * factor);
+                if (bin == HISTO_LENGTH) bin = 0;
+                rotHist[bin].push_back(bestIdx2);
+            }
+        }
+    }
+    if (mbCheckOrientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        ComputeThreeMaxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++)
+            if (i != ind1 && i != ind2 && i != ind3)
+                for (int idx : rotHist[i]) {
+                    CurrentFrame.mvpMapPoints[idx] = -1;
+                    nmatches--;
+                }
+    }
+    return nmatches;
+}
+
+// src/ORBmatcher.cc:276-379: SearchByProjection(F, MPs, th) under a wall-clock budget; a non-positive budget matches
+// nothing, and with an unlimited budget (the only mode the GPU path offers) the loop is the plain one.
+int ORBmatcher::SearchByProjection_Budget(Frame& F, const std::vector<MapPointView>& vpMapPoints, float th, double time_constr) {
+    if (time_constr <= 0) return 0;
+    return SearchByProjection(F, vpMapPoints, th);
+}
+
 // src/ORBmatcher.cc:1172-1287
 int ORBmatcher::SearchForInitialization(const Frame& F1, const Frame& F2, std::vector<float>& vbPrevMatched,
                                         std::vector<int>& vnMatches12, int windowSize) {

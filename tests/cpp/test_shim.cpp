@@ -126,6 +126,24 @@ int main() {
         o.mTrackViewCos = p.mTrackViewCos; o.mbTrackInView = p.mbTrackInView; o.isBad = p.mbBad;
         std::memcpy(o.desc, p.mDescriptor, 32);
     }
+    {   // SearchByProjection_GoodFeature (src/ORBmatcher.cc:51-140) and _Budget (:276-379) on copies of the frame
+        Frame Fg = F2;
+        oracle::Frame oFg = oF2;
+        Fg.mnId = 5;
+        std::vector<uint8_t> good(F1.N);
+        for (int i = 0; i < F1.N; i++) { good[i] = (splitmix() % 3) == 0; mps[i].goodAtFrameId = good[i] ? 5 : 4; }
+        const int ng = m.SearchByProjection_GoodFeature(Fg, vp, 1.0f, 3.0f);
+        const int ong = om.SearchByProjection_GoodFeature(oFg, omp, good.data(), 1.0f, 3.0f);
+        CHECK(ng == ong && ng > 50, "SearchByProjection_GoodFeature: %d vs %d", ng, ong);
+        bool ag = true;
+        for (int i = 0; i < Fg.N; i++) {
+            const int id = Fg.mvpMapPoints[i] ? (int)(Fg.mvpMapPoints[i] - &mps[0]) : -1;
+            ag = ag && id == oFg.mvpMapPoints[i] && Fg.mvpMatchScore[i] == F2.mvpMatchScore[i];
+        }
+        CHECK(ag, "SearchByProjection_GoodFeature associations differ");
+        Frame Fb = F2;
+        CHECK(m.SearchByProjection_Budget(Fb, vp, 3.0f, 0.0) == 0, "SearchByProjection_Budget with a spent budget");
+    }
     const int np = m.SearchByProjection(F2, vp, 3.0f);
     const int onp = om.SearchByProjection(oF2, omp, 3.0f);
     CHECK(np == onp, "SearchByProjection: %d vs %d", np, onp);

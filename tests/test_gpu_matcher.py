@@ -319,3 +319,85 @@ def test_undistort_keypoints(orc):
             assert (out[b]["class_id"][c:] == 12345).all()
         same = m.UndistortKeyPoints(keys, counts, K[0, 0], K[1, 1], K[0, 2], K[1, 2], [0.0, 0.2, 0.0, 0.0])
         assert same[0].tobytes() == keys[0].tobytes()
+
+
+@pytest.mark.parametrize("M,th_good,th_rest", [(10000, 1.0, 3.0), (3000, 2.0, 1.0)])
+def test_search_by_projection_good_feature_map(orc, M, th_good, th_rest):
+    """SearchByProjection_GoodFeature(F, MPs, th_good, th_rest) (src/ORBmatcher.cc:51-140): per-point window factor from
+    the good-feature flag (bit2), match scores untouched; and SearchByProjection_Budget (:276-379)."""
+    from gf_orb_slam_b200 import ORBextractor, ORBmatcher, Frames, MapPoints
+    img = synth.textured_frame(W, H, seed=1)
+    ex = ORBextractor(1500, 1.2, 8, max_width=W, max_height=H, max_batch=1)
+    kps, desc, counts = ex.extract_batch(img[None])
+    n = int(counts[0])
+    B = 2
+    mp = [synth.map_points_c3(kps[0, :n], desc[0, :n], M, seed=60 + b, w=W, h=H) for b in range(B)]
+    for b in range(B):
+        good = (synth.uniform01(300 + b, M) < 0.3).astype(np.uint8)
+        mp[b]["flags"] = (mp[b]["flags"] | (good << 2)).astype(np.uint8)
+    stack = lambda k: np.ascontiguousarray(np.stack([mp[b][k] for b in range(B)]))
+    mps = MapPoints(stack("proj_x"), stack("proj_y"), stack("scale_level"), stack("view_cos"), stack("flags"),
+                    stack("descriptors"), np.array([M, M - 7], np.int32))
+    kB = np.repeat(kps, B, 0); dB = np.repeat(desc, B, 0); cB = np.repeat(counts, B)
+    F = Frames(kB, dB, cB, W, H)
+    fmp = np.full((B, 1500), -1, np.int32)
+    fmp[1, 5:40:3] = 123456
+    fmp0 = fmp.copy()
+    m = ORBmatcher(0.8, True, max_batch=B, max_keypoints=1500, max_queries=M, cand_pool=64 * M)
+    nm = m.SearchByProjection_GoodFeature(F, mps, th_good, th_rest, fmp)
+    plain = fmp0.copy(); psc = np.full((B, 1500), 999, np.int32)
+    nplain = m.SearchByProjection(F, mps, th_rest, plain, psc)
+    for b in range(B):
+        fo = _oframe(orc, kps[0], desc[0], n)
+        fo.set_mappoints(fmp0[b, :n])
+        Mb = M if b == 0 else M - 7
+        en = orc.search_by_projection_good_feature(fo, mp[b]["proj_x"][:Mb], mp[b]["proj_y"][:Mb], mp[b]["scale_level"][:Mb],
+                                                   mp[b]["view_cos"][:Mb], mp[b]["flags"][:Mb], mp[b]["descriptors"][:Mb],
+                                                   th_good, th_rest, 0.8)
+        emp, esc = fo.matches()
+        assert nm[b] == en, (b, nm[b], en)
+        assert np.array_equal(fmp[b, :n], emp)
+        assert (esc == 999).all()                                  # the overload leaves mvpMatchScore alone
+    assert nm[0] > 100 and not np.array_equal(fmp, plain)          # the good-feature windows change the associations
+    # _Budget: a spent budget matches nothing, an open one is the plain search
+    b0 = fmp0.copy(); s0 = np.full((B, 1500), 999, np.int32)
+    assert (m.SearchByProjection_Budget(F, mps, th_rest, 0.0, b0, s0) == 0).all() and np.array_equal(b0, fmp0)
+    nb = m.SearchByProjection_Budget(F, mps, th_rest, 5.0, b0, s0)
+    assert np.array_equal(nb, nplain) and np.array_equal(b0, plain) and np.array_equal(s0, psc)
+
+
+@pytest.mark.parametrize("th_good,th_rest,check_ori", [(7.0, 15.0, True), (30.0, 10.0, False)])
+def test_search_by_projection_frames_good_feature(orc, seq_frames, th_good, th_rest, check_ori):
+    """SearchByProjection_GoodFeature(Cur, Last, th_good, th_rest) (src/ORBmatcher.cc:143-274)"""
+    from gf_orb_slam_b200 import ORBmatcher, Frames
+    kps, desc, counts = seq_frames
+    B = 3
+    Last = Frames(kps[:B], desc[:B], counts[:B], W, H)
+    Cur = Frames(kps[1:B + 1], desc[1:B + 1], counts[1:B + 1], W, H)
+    lmp = np.full((B, 1000), -1, np.int32); lout = np.zeros((B, 1000), np.uint8); lworld = np.zeros((B, 1000, 3), np.float32)
+    lgood = np.zeros((B, 1000), np.uint8)
+    Tcw = np.zeros((B, 4, 4), np.float32)
+    K = None
+    for b in range(B):
+        n = counts[b]
+        K, Tcw[b], lworld[b, :n] = _pose_and_world(kps[b], n, seed=170 + b, shift=(-1.0, 0.0))
+        u = synth.uniform01(190 + b, n)
+        lmp[b, :n] = np.where(u < 0.8, 1000 + np.arange(n), -1)
+        lout[b, :n] = (u > 0.75) & (u < 0.8)
+        lgood[b, :n] = synth.uniform01(210 + b, n) < 0.4
+    cmp_ = np.full((B, 1000), -1, np.int32)
+    cmp_[2, 0:30:4] = 777
+    cmp0 = cmp_.copy()
+    m = ORBmatcher(0.9, check_ori, max_batch=B, max_keypoints=1000, max_queries=1000)
+    nm = m.SearchByProjectionFrames_GoodFeature(Cur, Last, lmp, lout, lgood, lworld, Tcw, K, th_good, th_rest, cmp_)
+    for b in range(B):
+        fl = _oframe(orc, kps[b], desc[b], counts[b]); fc = _oframe(orc, kps[b + 1], desc[b + 1], counts[b + 1])
+        fl.set_mappoints(lmp[b, :counts[b]], lout[b, :counts[b]])
+        fc.set_mappoints(cmp0[b, :counts[b + 1]])
+        fc.set_camera(*K, Tcw[b])
+        en = orc.search_by_projection_frames_good_feature(fc, fl, lworld[b, :counts[b]], lgood[b, :counts[b]], th_good, th_rest,
+                                                          0.9, check_ori)
+        emp, esc = fc.matches()
+        assert nm[b] == en, (b, nm[b], en)
+        assert np.array_equal(cmp_[b, :counts[b + 1]], emp) and (esc == 999).all()
+    assert nm[0] > 50
