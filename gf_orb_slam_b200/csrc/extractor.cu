@@ -101,8 +101,8 @@ __global__ void __launch_bounds__(256) k_border0(const uint8_t* __restrict__ img
 // point with 11-bit coefficients: out = ((b0 * (h0 >> 4) >> 16) + (b1 * (h1 >> 4) >> 16) + 2) >> 2,
 // h = s[sx] * a0 + s[sx + 1] * a1.  tabs: int2 {src index, a0 | a1 << 16} per destination column / row.
 // Thread = 4 adjacent bordered columns x a band of RS_BAND bordered rows; the column taps live in registers.
-static const int RS_BAND = 8;
-__global__ void __launch_bounds__(256) k_resize(const uint8_t* __restrict__ spyr, uint8_t* __restrict__ pyr, size_t framePyr,
+static const int RS_BAND = 4;
+__global__ void __launch_bounds__(256, 6) k_resize(const uint8_t* __restrict__ spyr, uint8_t* __restrict__ pyr, size_t framePyr,
                                                 LevelPlan S, LevelPlan D, const int2* __restrict__ tabs, int quadsPerRow,
                                                 int nBands) {
     const int t = blockIdx.x * 256 + threadIdx.x, b = blockIdx.y;
