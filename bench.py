@@ -112,54 +112,17 @@ def cpu_leg(frames, threads, fe_consts):
     return frames.shape[0] / dt, dt
 
 
-def cv2_stage_leg(frames, threads):
-    """the OpenCV calls the reference's extractor makes (copyMakeBorder, the resize chain, FAST per cell
-    with the threshold fallback, GaussianBlur 7x7) issued through cv2 (SIMD, IPP), one frame per thread.  Orientation,
-    descriptors, matching and selection are the reference's own scalar C++ and are NOT in this figure: it bounds how
-    much the scalar oracle port understates the OpenCV-backed stages.  Returns (frames/s, seconds) or None without cv2."""
+def cv2_stage_leg(nframes, workers):
+    """tools/cv2_stage_baseline.py (the extractor's OpenCV calls through cv2, one frame per worker
+    process) run as a subprocess; returns its JSON dict or None."""
+    import subprocess
+    tool = os.path.join(os.path.dirname(os.path.abspath(__file__)), "tools", "cv2_stage_baseline.py")
     try:
-        import cv2
+        r = subprocess.run([sys.executable, tool, str(nframes), str(workers)], capture_output=True, text=True, timeout=240)
+        d = json.loads(r.stdout.strip().splitlines()[-1])
+        return d if "value" in d else None
     except Exception:
         return None
-    from concurrent.futures import ThreadPoolExecutor
-    from gf_orb_slam_b200.pipeline_consts import level_sizes
-    cv2.setNumThreads(1)
-    sizes = level_sizes(W_, H_)
-    nfeat = [217, 181, 151, 126, 105, 87, 73, 60]                     # features per level for 1000 (SURVEY 8, table)
-    det20 = cv2.FastFeatureDetector_create(20, True, cv2.FAST_FEATURE_DETECTOR_TYPE_9_16)
-    det7 = cv2.FastFeatureDetector_create(7, True, cv2.FAST_FEATURE_DETECTOR_TYPE_9_16)
-
-    def one(img):
-        lv = cv2.copyMakeBorder(img, 16, 16, 16, 16, cv2.BORDER_REFLECT_101)
-        n = 0
-        for l, (w, h) in enumerate(sizes):
-            if l:
-                roi = cv2.resize(lv[16:-16, 16:-16], (w, h), interpolation=cv2.INTER_LINEAR)
-                lv = cv2.copyMakeBorder(roi, 16, 16, 16, 16, cv2.BORDER_REFLECT_101)
-            Wb, Hb = w + 32 - 32, h + 32 - 32                         # maxBorder - minBorder (borders of 16 inside the ring)
-            cols = max(int(np.sqrt(np.float32(nfeat[l]) / np.float32(5.0 * Wb / Hb))), 1)
-            rows = max(int(np.float32(Wb / Hb) * cols), 1)
-            cw, ch = -(-Wb // cols), -(-Hb // rows)
-            for i in range(rows):
-                for j in range(cols):
-                    y0, x0 = 16 + i * ch - 3, 16 + j * cw - 3
-                    y1, x1 = min(y0 + ch + 6, 16 + Hb + 3), min(x0 + cw + 6, 16 + Wb + 3)
-                    if y1 <= y0 or x1 <= x0:
-                        continue
-                    cell = lv[y0:y1, x0:x1]
-                    k = det20.detect(cell)
-                    if len(k) <= 3:
-                        k = det7.detect(cell)
-                    n += len(k)
-            cv2.GaussianBlur(lv[16:-16, 16:-16], (7, 7), 2, 2, borderType=cv2.BORDER_REFLECT_101)
-        return n
-
-    one(frames[0])
-    t0 = time.perf_counter()
-    with ThreadPoolExecutor(threads) as ex:
-        list(ex.map(one, list(frames)))
-    dt = time.perf_counter() - t0
-    return frames.shape[0] / dt, dt
 
 
 def consts():
@@ -337,13 +300,13 @@ def run_ours(args):
         v, dt = cpu_leg(cf, cores, consts())
         out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                                "sample": f"{nfr} consecutive frames of the same sequence, oracle port (g++ -O2), {cores} threads, {dt:.1f} s wall"}
-        cvl = cv2_stage_leg(cf, cores)
+        cvl = cv2_stage_leg(nfr, cores)
         if cvl:
             out["cpu_baseline"]["opencv_stages"] = {
-                "value": cvl[0], "unit": UNIT, "cores": cores,
+                "value": cvl["value"], "unit": UNIT, "cores": cores,
                 "what": "only the OpenCV-backed stages of the extractor (copyMakeBorder, resize chain, per-cell FAST 20/7, "
-                        "GaussianBlur) through cv2 %s, one frame per thread; the reference's own scalar stages (orientation, "
-                        "descriptors, matching, selection) are not in it; includes the Python binding's KeyPoint-list construction" % __import__("cv2").__version__}
+                        "GaussianBlur) through cv2 %s, one frame per worker process, %d frames; the reference's own scalar stages "
+                        "(orientation, descriptors, matching, selection) are not in it" % (cvl["cv2"], cvl["frames"])}
     print(json.dumps(out))
     if world_size > 1:
         dist.destroy_process_group()

@@ -448,8 +448,10 @@ template <int ID, int N> __device__ __forceinline__ void bar_arrive_i() { asm vo
 template <int ID, int N> __device__ __forceinline__ void bar_sync2(int p) { if (p) bar_sync_i<ID + 1, N>(); else bar_sync_i<ID, N>(); }
 template <int ID, int N> __device__ __forceinline__ void bar_arrive2(int p) { if (p) bar_arrive_i<ID + 1, N>(); else bar_arrive_i<ID, N>(); }
 
-template <int T>
-__global__ void __launch_bounds__(T + 32, T == 256 ? 1 : (T == 128 ? 3 : 5)) k_select_ahead(const SelParams P) {
+// MINB = resident CTAs per SM the register budget is cut for: the evaluation wants ~170 registers (no spills of the two
+// 28-entry triangles), which fits two CTAs of 160 threads per SM; batches above two problems per SM trade that for a third CTA.
+template <int T, int MINB>
+__global__ void __launch_bounds__(T + 32, MINB) k_select_ahead(const SelParams P) {
     constexpr int NW = T / 32;                // evaluator warps; warp NW is the sampler
     constexpr int ALL = T + 32;
     enum { B_FULL = 1, B_EMPTY = 3, B_EVAL = 5 };
@@ -593,6 +595,14 @@ __global__ void __launch_bounds__(T + 32, T == 256 ? 1 : (T == 128 ? 3 : 5)) k_s
         const int cnt = dead ? 0 : s_cnt2[p];
         // ---- logDet(cur +- block) of every drawn column's pool entry; arg-max, first drawn wins ties (strict >)
         double bestV = -DBL_MAX; int bestT = INT_MAX;
+        // A round usually holds more candidates than evaluator threads (230 vs 128 in config C4): the packed blocks of this
+        // thread's later passes are pulled into L1 while the first pass computes (224 B = at most three 128-B lines).
+        for (int t = tid + T; t < cnt; t += T) {
+            const char* pf = reinterpret_cast<const char*>(pk + (size_t)idx[colp[t]] * 28);
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(pf));
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(pf + 112));
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(pf + 223));
+        }
         for (int t = tid; t < cnt; t += T) {
             const int q = idx[colp[t]];
             const double v = logdet_sum_packed(cur, pk + (size_t)q * 28, blk + (size_t)q * 49, sgn);
@@ -861,9 +871,10 @@ int gforb_obs_create(const GforbObsConfig* cfg, GforbObs** out) {
     GF_CUDA_OK(cudaFuncSetAttribute(k_select<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, selSmem));
     GF_CUDA_OK(cudaFuncSetAttribute(k_select<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, selSmem));
     const int aheadSmem = (int)ahead_smem(cfg->max_points);
-    GF_CUDA_OK(cudaFuncSetAttribute(k_select_ahead<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, aheadSmem));
-    GF_CUDA_OK(cudaFuncSetAttribute(k_select_ahead<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, aheadSmem));
-    GF_CUDA_OK(cudaFuncSetAttribute(k_select_ahead<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, aheadSmem));
+    GF_CUDA_OK(cudaFuncSetAttribute(k_select_ahead<64, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, aheadSmem));
+    GF_CUDA_OK(cudaFuncSetAttribute(k_select_ahead<128, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, aheadSmem));
+    GF_CUDA_OK(cudaFuncSetAttribute(k_select_ahead<128, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, aheadSmem));
+    GF_CUDA_OK(cudaFuncSetAttribute(k_select_ahead<256, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, aheadSmem));
     if (const char* e = getenv("GFORB_SELECT_THREADS")) O->selThreads = atoi(e);
     if (getenv("GFORB_SELECT_NO_AHEAD")) O->selAhead = 0;
     *out = O;
@@ -1073,9 +1084,14 @@ int gforb_obs_select(GforbObs* O, const double* blocks, const double* obs_score,
     O->lastLaunches = 1;
     if (P.split) {
         const size_t asm_ = ahead_smem(O->cfg.max_points);
-        if (T == 256) k_select_ahead<256><<<batch, 256 + 32, asm_, c.st>>>(P);
-        else if (T == 128) k_select_ahead<128><<<batch, 128 + 32, asm_, c.st>>>(P);
-        else k_select_ahead<64><<<batch, 64 + 32, asm_, c.st>>>(P);
+        const char* mb = getenv("GFORB_SELECT_MINB");
+        // waves of CTAs at 2 / 3 resident per SM; a 3-per-SM wave takes ~1.35x a 2-per-SM wave (measured, tools/bench_select.py)
+        const int w2 = (batch + 2 * O->numSMs - 1) / (2 * O->numSMs), w3 = (batch + 3 * O->numSMs - 1) / (3 * O->numSMs);
+        const bool three = mb ? atoi(mb) >= 3 : (w3 * 1.35 < w2);
+        if (T == 256) k_select_ahead<256, 1><<<batch, 256 + 32, asm_, c.st>>>(P);
+        else if (T == 128 && !three) k_select_ahead<128, 2><<<batch, 128 + 32, asm_, c.st>>>(P);
+        else if (T == 128) k_select_ahead<128, 3><<<batch, 128 + 32, asm_, c.st>>>(P);
+        else k_select_ahead<64, 5><<<batch, 64 + 32, asm_, c.st>>>(P);
         O->lastLaunches = 2;
     }
     if (wantProf) {

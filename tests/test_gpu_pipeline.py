@@ -98,37 +98,43 @@ def test_sampled_frames_match_oracle(orc, full):
         assert np.allclose(sld[:int(sn)], esl, rtol=1e-5, atol=0)        # north_star tolerance for log-det scores
 
 
-@pytest.mark.parametrize("mtd,k", [(2, 100), (5, 700), (3, 120)])
-def test_selection_variants_agree(mtd, k):
-    """threads per problem (64 / 128 / 256) and the sampler-ahead vs in-order kernels are launch choices only"""
+def _select_once(B, n, k, mtd):
     from gf_orb_slam_b200.observability import Observability
     from gf_orb_slam_b200.pipeline_consts import EUROC_CAM, SIMU_XV, level_sigma2, simu_visible_from
+    ob = Observability(**EUROC_CAM, max_batch=B, max_points=n)
+    ob.set_state(SIMU_XV); ob.predictPWLSVec(0.1, 1)
+    Xv = np.repeat(ob.kinematic(0)["Xv"][None], B, 0)
+    cl = [synth.landmark_cloud(n, 300 + b, visible_from=simu_visible_from(W, H)) for b in range(B)]
+    world = np.stack([c[0] for c in cl]); octave = np.stack([c[1] for c in cl]).astype(np.int32)
+    score = np.stack([c[2] for c in cl]).astype(np.int32)
+    valid = np.ones((B, n), np.uint8)
+    valid[B - 1, ::13] = 0                   # the last problem has invalid pool entries -> in-order kernel
+    counts = np.array([n, n - 5, n, n // 2, n, n], np.int32)
+    blocks, osc = ob.build_info_frame(Xv, world, octave, score, valid, counts, level_sigma2())
+    idx, ld, cnt = ob.select(blocks, osc, counts, k, mtd, 9.0, np.arange(1, B + 1, dtype=np.uint32))
+    return idx.copy(), ld.copy(), cnt.copy()
+
+
+@pytest.mark.parametrize("mtd,k", [(2, 100), (5, 700), (3, 120)])
+def test_selection_variants_agree(mtd, k):
+    """threads per problem (64 / 128 / 256), CTAs per SM and the sampler-ahead vs in-order kernels are launch choices only"""
     B, n = 6, 900
     outs = []
-    for env in ({"GFORB_SELECT_THREADS": "256"}, {"GFORB_SELECT_THREADS": "128"}, {"GFORB_SELECT_THREADS": "64"},
+    keys = ("GFORB_SELECT_THREADS", "GFORB_SELECT_NO_AHEAD", "GFORB_SELECT_MINB")
+    for env in ({"GFORB_SELECT_THREADS": "256"}, {"GFORB_SELECT_THREADS": "128", "GFORB_SELECT_MINB": "2"},
+                {"GFORB_SELECT_THREADS": "128", "GFORB_SELECT_MINB": "3"}, {"GFORB_SELECT_THREADS": "64"},
                 {"GFORB_SELECT_NO_AHEAD": "1"}):
-        old = {key: os.environ.get(key) for key in ("GFORB_SELECT_THREADS", "GFORB_SELECT_NO_AHEAD")}
-        for key in old:
+        old = {key: os.environ.get(key) for key in keys}
+        for key in keys:
             os.environ.pop(key, None)
         os.environ.update(env)
         try:
-            ob = Observability(**EUROC_CAM, max_batch=B, max_points=n)
+            outs.append(_select_once(B, n, k, mtd))
         finally:
             for key, v in old.items():
                 os.environ.pop(key, None)
                 if v is not None:
                     os.environ[key] = v
-        ob.set_state(SIMU_XV); ob.predictPWLSVec(0.1, 1)
-        Xv = np.repeat(ob.kinematic(0)["Xv"][None], B, 0)
-        cl = [synth.landmark_cloud(n, 300 + b, visible_from=simu_visible_from(W, H)) for b in range(B)]
-        world = np.stack([c[0] for c in cl]); octave = np.stack([c[1] for c in cl]).astype(np.int32)
-        score = np.stack([c[2] for c in cl]).astype(np.int32)
-        valid = np.ones((B, n), np.uint8)
-        valid[B - 1, ::13] = 0                   # the last problem has invalid pool entries -> in-order kernel
-        counts = np.array([n, n - 5, n, n // 2, n, n], np.int32)
-        blocks, osc = ob.build_info_frame(Xv, world, octave, score, valid, counts, level_sigma2())
-        idx, ld, cnt = ob.select(blocks, osc, counts, k, mtd, 9.0, np.arange(1, B + 1, dtype=np.uint32))
-        outs.append((idx.copy(), ld.copy(), cnt.copy()))
     for o in outs[1:]:
         assert np.array_equal(o[2], outs[0][2])
         for b in range(B):
