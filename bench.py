@@ -248,6 +248,21 @@ def run_ours(args):
         fe.step_host()
     ms_e2e = timed(fe.step_host, args.steps)
     clocks = sampler.stop() if rank == 0 else None
+    # the host link under the end-to-end number: one pinned host -> device copy of a step's input alone on the GPU
+    h2d_alone = None
+    if rank == 0:
+        hsrc = torch.empty(fe.h2d_bytes(), dtype=torch.uint8).pin_memory()
+        hdst = torch.empty(fe.h2d_bytes(), dtype=torch.uint8, device="cuda")
+        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        hdst.copy_(hsrc, non_blocking=True)
+        torch.cuda.synchronize()
+        c0.record()
+        for _ in range(5):
+            hdst.copy_(hsrc, non_blocking=True)
+        c1.record()
+        torch.cuda.synchronize()
+        h2d_alone = fe.h2d_bytes() * 5 / (c0.elapsed_time(c1) * 1e-3) / 1e9
+        del hsrc, hdst
     total_frames = B * args.steps * world_size
     value = total_frames / (ms * 1e-3)
     e2e = total_frames / (ms_e2e * 1e-3)
@@ -289,7 +304,10 @@ def run_ours(args):
                    "lanes_per_gpu": args.lanes, "ms_per_step_one_stream_no_overlap": round(ms_serial, 4)},
         "roofline": roof,
         "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": fe.h2d_bytes(), "d2h_bytes_per_step": fe.d2h_bytes(),
-                "ms_per_step": ms_e2e / args.steps},
+                "ms_per_step": ms_e2e / args.steps,
+                "h2d_GBps_in_step": fe.h2d_bytes() / (ms_e2e / args.steps * 1e-3) / 1e9, "h2d_GBps_copy_alone": h2d_alone,
+                "note": "h2d_GBps_in_step against h2d_GBps_copy_alone shows how much of the host link the step uses: the "
+                        "copies run on their own stream under the kernels, so the end-to-end rate is set by the kernels"},
         "gpu_launches": launches,
         "clocks": clocks,
     }
