@@ -659,6 +659,7 @@ struct GforbObs {
     GforbObsConfig cfg;
     int device = 0, lastLaunches = 0;
     int selThreads = 0, numSMs = 148, selAhead = 1;
+    int aheadPad = 0;        // same for k_select_ahead (GFORB_SELECT_AHEAD_PAD)
     int selPad = 0;          // extra dynamic smem of k_select (GFORB_SELECT_SMEM_PAD): caps its CTAs per SM when it shares the GPU
     double Xv[13];
     std::vector<KineSeg> kine;
@@ -870,7 +871,8 @@ int gforb_obs_create(const GforbObsConfig* cfg, GforbObs** out) {
     GF_CUDA_OK(cudaFuncSetAttribute(k_select<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, selSmem));
     GF_CUDA_OK(cudaFuncSetAttribute(k_select<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, selSmem));
     GF_CUDA_OK(cudaFuncSetAttribute(k_select<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, selSmem));
-    const int aheadSmem = (int)ahead_smem(cfg->max_points);
+    if (const char* e = getenv("GFORB_SELECT_AHEAD_PAD")) O->aheadPad = atoi(e);
+    const int aheadSmem = (int)ahead_smem(cfg->max_points) + O->aheadPad;
     GF_CUDA_OK(cudaFuncSetAttribute(k_select_ahead<64, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, aheadSmem));
     GF_CUDA_OK(cudaFuncSetAttribute(k_select_ahead<128, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, aheadSmem));
     GF_CUDA_OK(cudaFuncSetAttribute(k_select_ahead<128, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, aheadSmem));
@@ -1083,7 +1085,7 @@ int gforb_obs_select(GforbObs* O, const double* blocks, const double* obs_score,
     else k_select<64><<<batch, 64, smem, c.st>>>(P);
     O->lastLaunches = 1;
     if (P.split) {
-        const size_t asm_ = ahead_smem(O->cfg.max_points);
+        const size_t asm_ = ahead_smem(O->cfg.max_points) + O->aheadPad;
         const char* mb = getenv("GFORB_SELECT_MINB");
         // waves of CTAs at 2 / 3 resident per SM; a 3-per-SM wave takes ~1.35x a 2-per-SM wave (measured, tools/bench_select.py)
         const int w2 = (batch + 2 * O->numSMs - 1) / (2 * O->numSMs), w3 = (batch + 3 * O->numSMs - 1) / (3 * O->numSMs);
