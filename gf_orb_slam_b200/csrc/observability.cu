@@ -659,6 +659,7 @@ struct GforbObs {
     GforbObsConfig cfg;
     int device = 0, lastLaunches = 0;
     int selThreads = 0, numSMs = 148, selAhead = 1;
+    int selResidency = 0;    // gforb_obs_set_select_residency: 0 = by waves, 2 / 3 = register budget of k_select_ahead<128, .>
     int aheadPad = 0;        // same for k_select_ahead (GFORB_SELECT_AHEAD_PAD)
     int selPad = 0;          // extra dynamic smem of k_select (GFORB_SELECT_SMEM_PAD): caps its CTAs per SM when it shares the GPU
     double Xv[13];
@@ -894,6 +895,12 @@ int gforb_obs_destroy(GforbObs* O) {
 
 int gforb_obs_last_launches(const GforbObs* O) { return O ? O->lastLaunches : GFORB_ERR_ARG; }
 
+int gforb_obs_set_select_residency(GforbObs* O, int ctas_per_sm) {
+    if (!O || (ctas_per_sm != 0 && ctas_per_sm != 2 && ctas_per_sm != 3)) return GFORB_ERR_ARG;
+    O->selResidency = ctas_per_sm;
+    return GFORB_OK;
+}
+
 int gforb_obs_set_state(GforbObs* O, const double* Xv13) {
     if (!O || !Xv13) return GFORB_ERR_ARG;
     memcpy(O->Xv, Xv13, sizeof(O->Xv));
@@ -1089,7 +1096,7 @@ int gforb_obs_select(GforbObs* O, const double* blocks, const double* obs_score,
         const char* mb = getenv("GFORB_SELECT_MINB");
         // waves of CTAs at 2 / 3 resident per SM; a 3-per-SM wave takes ~1.35x a 2-per-SM wave (measured, tools/bench_select.py)
         const int w2 = (batch + 2 * O->numSMs - 1) / (2 * O->numSMs), w3 = (batch + 3 * O->numSMs - 1) / (3 * O->numSMs);
-        const bool three = mb ? atoi(mb) >= 3 : (w3 * 1.35 < w2);
+        const bool three = mb ? atoi(mb) >= 3 : (O->selResidency ? O->selResidency == 3 : (w3 * 1.35 < w2));
         if (T == 256) k_select_ahead<256, 1><<<batch, 256 + 32, asm_, c.st>>>(P);
         else if (T == 128 && !three) k_select_ahead<128, 2><<<batch, 128 + 32, asm_, c.st>>>(P);
         else if (T == 128) k_select_ahead<128, 3><<<batch, 128 + 32, asm_, c.st>>>(P);

@@ -50,6 +50,10 @@ class Observability:
     def last_launches(self) -> int:
         return _lib.lib().gforb_obs_last_launches(self._h)
 
+    def set_select_residency(self, ctas_per_sm: int):
+        """register budget of the lazier-greedy kernel: 2 or 3 resident CTAs per SM, 0 = from the batch size (scheduling only)"""
+        check(_lib.lib().gforb_obs_set_select_residency(self._h, int(ctas_per_sm)), "gforb_obs_set_select_residency")
+
     # ---- kinematics (host)
     def set_state(self, Xv):
         Xv = np.ascontiguousarray(Xv, np.float64)

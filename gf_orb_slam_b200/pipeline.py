@@ -35,6 +35,8 @@ class TrackingFrontEnd:
         cam = dict(EUROC_CAM); cam["nRows"], cam["nCols"] = height, width
         self.obs = Observability(**cam, max_batch=batch, max_points=nfeatures, device=device)
         self.obs_sel = Observability(**cam, max_batch=batch, max_points=nfeatures, device=device)   # handle used on s_sel
+        if overlap:
+            self.obs_sel.set_select_residency(3)    # it shares the SMs with the next step's extraction: smaller register footprint
         self.obs.set_state(SIMU_XV)
         self.obs.predictPWLSVec(0.1, 1)
         xv = self.obs.kinematic(0)["Xv"]
@@ -69,7 +71,8 @@ class TrackingFrontEnd:
         self.sel_n2 = [z(B, dt=torch.int32) for _ in range(2)]
         self.overlap = overlap
         self.s_sel = torch.cuda.Stream(device=self.dev) if overlap else None
-        self.s_copy = torch.cuda.Stream(device=self.dev)
+        self.s_copy = torch.cuda.Stream(device=self.dev)        # device -> host results
+        self.s_up = torch.cuda.Stream(device=self.dev)          # host -> device frames (its own copy engine and queue)
         self.ev_info = [torch.cuda.Event() for _ in range(2)]
         self.ev_sel = [torch.cuda.Event() for _ in range(2)]
         self.ev_h2d = [torch.cuda.Event() for _ in range(2)]
@@ -238,14 +241,14 @@ class TrackingFrontEnd:
         return {"per_stage": per, "extract_frame": sum(per.values()), "traffic": {}}
 
     # ---- the same step through host buffers: H2D of the frames, D2H of every result a Tracking caller consumes.
-    # Copies run on s_copy: the frames of step t+1 upload while step t computes (two device image buffers), results
+    # Copies run on s_up / s_copy: the frames of step t+1 upload while step t computes (two device image buffers), results
     # download while the selection runs.
     def upload(self, q):
         """enqueue the H2D copy of self.h_images into device image buffer q on the copy stream"""
-        self.s_copy.wait_event(self.ev_ext[q])                              # the extraction that last read buffer q is done
-        with torch.cuda.stream(self.s_copy):
+        self.s_up.wait_event(self.ev_ext[q])                                # the extraction that last read buffer q is done
+        with torch.cuda.stream(self.s_up):
             self.images2[q].copy_(self.h_images, non_blocking=True)
-            self.ev_h2d[q].record(self.s_copy)
+            self.ev_h2d[q].record(self.s_up)
 
     def step_host(self, first=False):
         main = torch.cuda.current_stream()

@@ -242,6 +242,10 @@ typedef struct GforbObs GforbObs;
 int gforb_obs_create(const GforbObsConfig* cfg, GforbObs** out);
 int gforb_obs_destroy(GforbObs* h);
 int gforb_obs_last_launches(const GforbObs* h);
+/* Scheduling hint for gforb_obs_select's lazier-greedy kernel: register budget for 2 resident CTAs per SM (168 registers, no
+ * spills: fastest when the selection has the GPU to itself), for 3 (128 registers: a third less of the register file, better
+ * when it runs beside other kernels on another stream), or 0 = chosen from the batch size.  Results do not depend on it. */
+int gforb_obs_set_select_residency(GforbObs* h, int ctas_per_sm);
 
 /* Observability::Xv (13-state [r(3) q(4) v(3) w(3)]), updatePWLSVec (include/Observability.h:222-259) and
  * predictPWLSVec (:261-295); matrices are 4x4 row-major float like the reference's cv::Mat.  Host-side. */
