@@ -141,7 +141,7 @@ def run_reference(args):
     from gf_orb_slam_b200 import synth
     cores = host_cores()
     seq = synth.Sequence(W_, H_)
-    nfr = args.ref_frames
+    nfr = args.ref_frames if args.ref_frames > 0 else 8 * cores     # several frames per thread: no idle tail
     frames = seq.frames(0, nfr)
     c = consts()
     for _ in range(args.warmup):
@@ -339,7 +339,7 @@ def main():
     ap.add_argument("--batch", type=int, default=256, help="frames per step per GPU")
     ap.add_argument("--distinct", type=int, default=256, help="distinct synthetic frames generated per GPU (tiled to --batch)")
     ap.add_argument("--cpu-frames", type=int, default=128, help="frames of the cpu_baseline sample")
-    ap.add_argument("--ref-frames", type=int, default=32, help="frames per step of the --impl reference arm")
+    ap.add_argument("--ref-frames", type=int, default=0, help="frames per step of the --impl reference arm (0: 8 per host thread)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-overlap", action="store_true", help="run the good-feature selection on the main stream")
     ap.add_argument("--lanes", type=int, default=1, help="independent half-batch pipelines (CUDA streams) per GPU")
