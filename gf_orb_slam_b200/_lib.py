@@ -89,6 +89,7 @@ def lib() -> C.CDLL:
         L.gforb_search_by_projection_good_feature.argtypes = [vp, FS, MS, i32, f32, f32, f32, vp, vp, i32, vp]
         L.gforb_search_by_projection_frames_good_feature.argtypes = [vp, FS, FS, i32, vp, vp, vp, vp, vp, f32, f32, f32, f32, f32,
                                                                      f32, f32, i32, vp, vp, i32, vp]
+        L.gforb_mappoint_distinctive_descriptors.argtypes = [vp, i32, vp, vp, vp, vp, i32, vp]
         L.gforb_frame_is_in_frustum.argtypes = [vp, i32, vp, vp, vp, f32, f32, f32, f32, i32, i32, i32, i32, vp, vp, vp, vp, vp, i32,
                                                 f32, vp, vp, vp, vp, vp, i32, vp]
         L.gforb_frame_undistort_keypoints.argtypes = [vp, i32, vp, vp, i32, f32, f32, f32, f32, vp, i32, vp, i32, vp]
@@ -125,7 +126,8 @@ gforb_allpairs_top2 gforb_top2_merge gforb_obs_create gforb_obs_destroy gforb_ob
 gforb_obs_get_state gforb_obs_update_pwls gforb_obs_predict_pwls gforb_obs_num_segments gforb_obs_get_segment
 gforb_obs_build_info_frame gforb_obs_build_info_map gforb_obs_logdet gforb_obs_rand_stream gforb_obs_select
 gforb_obs_active_match gforb_frame_is_in_frustum gforb_frame_undistort_keypoints
-gforb_search_by_projection_good_feature gforb_search_by_projection_frames_good_feature""".split()
+gforb_search_by_projection_good_feature gforb_search_by_projection_frames_good_feature
+gforb_mappoint_distinctive_descriptors""".split()
 
 
 def check(rc: int, what: str):

@@ -593,6 +593,59 @@ __global__ void __launch_bounds__(128) k_is_in_frustum(const FrustumParams F) {
     F.flags[p] = fl;
 }
 
+// ------------------------------------------------------------------------------------------------ distinctive descriptor
+// MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:196-262) for many map points: the observation descriptor with
+// the least median Hamming distance to the others (median = sorted row [int(0.5 (N - 1))], the row's own 0 included; the
+// first row with the smallest median wins).  CTA of 4 warps per map point, a warp per row: distances go into a 257-bin
+// histogram (they are integers 0..256) and the median is the bin where the running count passes the rank.
+static const int DD_WARPS = 4;
+__global__ void __launch_bounds__(DD_WARPS * 32) k_distinctive(const uint8_t* __restrict__ desc, const int32_t* __restrict__ offsets,
+                                                              int nPoints, int32_t* __restrict__ bestIdx,
+                                                              uint8_t* __restrict__ outDesc) {
+    __shared__ int hist[DD_WARPS][264];
+    __shared__ unsigned long long s_best[DD_WARPS];
+    const int mp = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (mp >= nPoints) return;
+    const int o0 = offsets[mp], N = offsets[mp + 1] - o0;
+    if (N <= 0) {
+        if (threadIdx.x == 0) bestIdx[mp] = -1;          // no observation: the reference returns and keeps mDescriptor
+        return;
+    }
+    const uint4* D = reinterpret_cast<const uint4*>(desc + (size_t)o0 * 32);
+    const int rank = (int)(0.5 * (N - 1));
+    unsigned long long best = ~0ull;                      // (median << 32 | row), smallest wins
+    for (int i = warp; i < N; i += DD_WARPS) {
+        for (int q = lane; q < 264; q += 32) hist[warp][q] = 0;
+        __syncwarp();
+        const uint4 a0 = __ldg(D + 2 * i), a1 = __ldg(D + 2 * i + 1);
+        for (int j = lane; j < N; j += 32) atomicAdd(&hist[warp][popc256(a0, a1, __ldg(D + 2 * j), __ldg(D + 2 * j + 1))], 1);
+        __syncwarp();
+        // lane l owns bins [9 l, 9 l + 9) (32 x 9 = 288 >= 257): inclusive scan of the lane sums, then walk the own bins
+        int c[9], sum = 0;
+#pragma unroll
+        for (int q = 0; q < 9; q++) { const int bin = 9 * lane + q; c[q] = bin < 257 ? hist[warp][bin] : 0; sum += c[q]; }
+        int incl = sum;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += t; }
+        int before = incl - sum, med = 1 << 30;
+#pragma unroll
+        for (int q = 0; q < 9; q++) { if (med == (1 << 30) && before + c[q] > rank && before <= rank) med = 9 * lane + q; before += c[q]; }
+        med = __reduce_min_sync(0xffffffffu, med);
+        const unsigned long long key = ((unsigned long long)(unsigned)med << 32) | (unsigned)i;
+        if (key < best) best = key;
+        __syncwarp();
+    }
+    if (lane == 0) s_best[warp] = best;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        unsigned long long b = s_best[0];
+        for (int w = 1; w < DD_WARPS; w++) b = s_best[w] < b ? s_best[w] : b;
+        const int row = (int)(b & 0xffffffffu);
+        if (lane == 0) bestIdx[mp] = row;
+        if (outDesc && lane < 2) reinterpret_cast<uint4*>(outDesc + (size_t)mp * 32)[lane] = __ldg(D + 2 * row + lane);
+    }
+}
+
 // ------------------------------------------------------------------------------------------------ B1 distance
 __global__ void __launch_bounds__(256) k_distance(const uint4* __restrict__ a, const uint4* __restrict__ b, int n,
                                                   int32_t* __restrict__ out) {
@@ -865,6 +918,31 @@ int gforb_matcher_destroy(GforbMatcher* M) {
 }
 
 int gforb_matcher_last_launches(const GforbMatcher* M) { return M ? M->lastLaunches : GFORB_ERR_ARG; }
+
+int gforb_mappoint_distinctive_descriptors(GforbMatcher* M, int n_points, const uint8_t* descriptors, const int32_t* offsets,
+                                           int32_t* best_idx, uint8_t* out_desc, int flags, void* stream) {
+    Ctx c;
+    int rc = begin_call(M, 0, flags, stream, c);
+    if (rc) return rc;
+    if (n_points == 0) return GFORB_OK;
+    if (n_points < 0 || !offsets || !best_idx) return GFORB_ERR_ARG;
+    // the total number of observation descriptors is offsets[n_points]: host-visible for host inputs; for device inputs
+    // it is read back (one int) because the staging size is not needed then
+    size_t total = 0;
+    if (!(flags & GFORB_IN_DEVICE)) {
+        total = (size_t)offsets[n_points];
+        for (int i = 0; i < n_points; i++) if (offsets[i + 1] < offsets[i]) return GFORB_ERR_ARG;
+        if (total > 0 && !descriptors) return GFORB_ERR_ARG;
+    }
+    const uint8_t* dd = (flags & GFORB_IN_DEVICE) ? descriptors : c.in(descriptors, total * 32);
+    const int32_t* doff = c.in(offsets, (size_t)n_points + 1);
+    int32_t* dbest = c.out(best_idx, (size_t)n_points, false);
+    uint8_t* dout = out_desc ? c.out(out_desc, (size_t)n_points * 32, true) : nullptr;
+    if (c.rc) return c.rc;
+    k_distinctive<<<n_points, DD_WARPS * 32, 0, c.st>>>(dd, doff, n_points, dbest, dout);
+    M->lastLaunches++;
+    return end_call(M, c, flags);
+}
 
 int gforb_descriptor_distance(GforbMatcher* M, const uint8_t* a, const uint8_t* b, int n, int32_t* out, int flags, void* stream) {
     Ctx c;

@@ -129,6 +129,24 @@ class ORBmatcher:
               "gforb_frame_is_in_frustum")
         return fl
 
+    # -- void MapPoint::ComputeDistinctiveDescriptors(), batched over map points
+    def ComputeDistinctiveDescriptors(self, descriptors, offsets, out_desc=None, *, stream=None, sync=True):
+        """src/MapPoint.cc:196-262.  descriptors (total, 32) uint8 = the observation descriptors of all points concatenated,
+        offsets (n_points + 1) int32.  Returns (best row per point or -1, the representative descriptors (n_points, 32))."""
+        dev = is_device(descriptors)
+        n = int(offsets.shape[0]) - 1
+        if dev:
+            import torch
+            best = torch.empty(n, dtype=torch.int32, device=descriptors.device)
+            out = torch.zeros((n, 32), dtype=torch.uint8, device=descriptors.device) if out_desc is None else out_desc
+        else:
+            best = np.empty(n, np.int32)
+            out = np.zeros((n, 32), np.uint8) if out_desc is None else out_desc
+        check(_lib.lib().gforb_mappoint_distinctive_descriptors(self._h, n, ptr(descriptors), ptr(offsets), ptr(best), ptr(out),
+                                                                self._flags(dev, dev, sync), C.c_void_p(stream or 0)),
+              "gforb_mappoint_distinctive_descriptors")
+        return best, out
+
     # -- void Frame::UndistortKeyPoints(), batched over the keypoints of B frames
     def UndistortKeyPoints(self, keys, counts, fx, fy, cx, cy, dist_coef, keys_un=None, *, stream=None, sync=True):
         """src/Frame.cc:389-423.  keys (B, stride) KP_DTYPE records (numpy) or (B, stride, 7) float32 (torch, device);

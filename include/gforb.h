@@ -167,6 +167,15 @@ int gforb_search_by_projection_good_feature(GforbMatcher* h, const GforbFrameSet
                                             float th_good, float th_rest, float nnratio, int32_t* frame_mappoints,
                                             int32_t* nmatches, int flags, void* stream);
 
+/* MapPoint::ComputeDistinctiveDescriptors() (src/MapPoint.cc:196-262) for n_points map points: descriptors = the
+ * observation descriptors (KeyFrame::GetDescriptor of every non-bad observing keyframe) of all points concatenated,
+ * offsets[i] .. offsets[i+1] = the rows of point i (n_points + 1 entries).  best_idx[i] = the row (relative to
+ * offsets[i]) with the least median Hamming distance to the point's other observations, -1 for a point without
+ * observations (the reference returns and keeps mDescriptor); out_desc (n_points x 32, may be NULL) receives that
+ * descriptor (= the new MapPoint::mDescriptor; rows of empty points are left as they are). */
+int gforb_mappoint_distinctive_descriptors(GforbMatcher* h, int n_points, const uint8_t* descriptors, const int32_t* offsets,
+                                           int32_t* best_idx, uint8_t* out_desc, int flags, void* stream);
+
 /* Frame::isInFrustum(MapPoint*, viewingCosLimit) (src/Frame.cc:166-227) for every map point of `batch` frames: the
  * pass that produces the GforbMapPointSet fields SearchByProjection reads.  Rcw / tcw / Ow: batch x 9 / 3 / 3 (Frame::mRcw
  * row-major, mtcw, mOw); world / normal: batch x mp_stride x 3 (MapPoint::GetWorldPos / GetNormal); min_distance /

@@ -287,6 +287,25 @@ public:
         return n;
     }
 
+    // MapPoint::ComputeDistinctiveDescriptors() (src/MapPoint.cc:196-262) for a set of map points at once:
+    // vObservationDescriptors[i] = the descriptors of point i's non-bad observations (32 bytes each, concatenated);
+    // the representative descriptor is written to vpMapPoints[i]->mDescriptor (points without observations keep theirs).
+    void ComputeDistinctiveDescriptors(const std::vector<MapPoint*>& vpMapPoints,
+                                       const std::vector<std::vector<uint8_t>>& vObservationDescriptors) {
+        const int n = (int)vpMapPoints.size();
+        if (n == 0) return;
+        ensure(1, 1, nlevels_ > 0 ? nlevels_ : 8, sf_ > 0 ? sf_ : 1.2f);
+        std::vector<int32_t> off(n + 1, 0), best(n, -1);
+        for (int i = 0; i < n; i++) off[i + 1] = off[i] + (int32_t)(vObservationDescriptors[i].size() / 32);
+        std::vector<uint8_t> all((size_t)off[n] * 32), out((size_t)n * 32);
+        for (int i = 0; i < n; i++)
+            if (off[i + 1] > off[i]) std::memcpy(&all[(size_t)off[i] * 32], vObservationDescriptors[i].data(), (size_t)(off[i + 1] - off[i]) * 32);
+        gforb_throw(gforb_mappoint_distinctive_descriptors(h_, n, all.data(), off.data(), best.data(), out.data(), 0, nullptr),
+                    "ComputeDistinctiveDescriptors");
+        for (int i = 0; i < n; i++)
+            if (best[i] >= 0) std::memcpy(vpMapPoints[i]->mDescriptor, &out[(size_t)i * 32], 32);
+    }
+
     // Frame::UndistortKeyPoints() (src/Frame.cc:389-423): mvKeysUn = mvKeys with cv::undistortPoints(pt, K, mDistCoef,
     // R = I, P = K); mDistCoef = (k1, k2, p1, p2[, k3]); mDistCoef[0] == 0 copies.
     void UndistortKeyPoints(const Frame& F, const std::vector<gforb_cv::KeyPoint>& mvKeys, const std::vector<float>& mDistCoef,

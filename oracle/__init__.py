@@ -285,6 +285,15 @@ def is_in_frustum(Rcw, tcw, Ow, fx, fy, cx, cy, bounds, world, normal, min_dist,
     return u, v, lvl, vc, fl
 
 
+def distinctive_descriptors(descriptors, offsets):
+    """MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:196-262) per map point -> best row index (or -1)"""
+    d = np.ascontiguousarray(descriptors, np.uint8).reshape(-1, 32)
+    off = np.ascontiguousarray(offsets, np.int32)
+    out = np.empty(off.size - 1, np.int32)
+    lib().orc_distinctive_descriptors(off.size - 1, _p(d), _p(off), _p(out))
+    return out
+
+
 def undistort_keypoints(xy, fx, fy, cx, cy, dist):
     """Frame::UndistortKeyPoints (src/Frame.cc:389-423) on (N, 2) float32 keypoint positions -> (N, 2) float32"""
     xy = np.ascontiguousarray(xy, np.float32).reshape(-1, 2)

@@ -252,6 +252,12 @@ void orc_is_in_frustum(const float* Rcw, const float* tcw, const float* Ow, floa
     }
 }
 
+// MapPoint::ComputeDistinctiveDescriptors for n_points map points (concatenated observation descriptors + offsets)
+void orc_distinctive_descriptors(int n_points, const uint8_t* descriptors, const int* offsets, int* best_idx) {
+    for (int i = 0; i < n_points; i++)
+        best_idx[i] = distinctiveDescriptor(descriptors + (size_t)32 * offsets[i], offsets[i + 1] - offsets[i]);
+}
+
 // Frame::UndistortKeyPoints (src/Frame.cc:389-423) on n x 2 positions; dist[0] == 0 -> copy (the early return)
 void orc_undistort_keypoints(const float* src, int n, float fx, float fy, float cx, float cy, const float* dist, int ndist,
                              float* dst) {

@@ -113,6 +113,8 @@ bool isInFrustum(const float* Rcw, const float* tcw, const float* Ow, float fx, 
                  int mnMaxX, int mnMinY, int mnMaxY, const std::vector<float>& mvScaleFactors, const float* P,
                  const float* Pn, float minDistance, float maxDistance, float viewingCosLimit, float& u, float& v,
                  int& level, float& viewCos);
+// MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:196-262): index of the representative descriptor among N
+int distinctiveDescriptor(const uint8_t* descriptors, int N);
 // Frame::UndistortKeyPoints' cv::undistortPoints call (src/Frame.cc:389-423), src / dst: n x 2 floats
 void undistortPoints(const float* src, int n, float fx, float fy, float cx, float cy, const float* dist, int ndist, float* dst);
 

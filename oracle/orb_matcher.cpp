@@ -471,6 +471,33 @@ bool isInFrustum(const float* Rcw, const float* tcw, const float* Ow, float fx, 
     return true;
 }
 
+// MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:196-262) on the N observation descriptors of one map point:
+// returns BestIdx (-1 when there is no observation: the reference returns early and keeps mDescriptor).
+int distinctiveDescriptor(const uint8_t* descriptors, int N) {
+    if (N <= 0) return -1;
+    std::vector<float> Distances((size_t)N * N);
+    for (int i = 0; i < N; i++) {
+        Distances[(size_t)i * N + i] = 0;
+        for (int j = i + 1; j < N; j++) {
+            int distij = ORBmatcher::DescriptorDistance(descriptors + (size_t)32 * i, descriptors + (size_t)32 * j);
+            Distances[(size_t)i * N + j] = distij;
+            Distances[(size_t)j * N + i] = distij;
+        }
+    }
+    int BestMedian = INT_MAX;
+    int BestIdx = 0;
+    for (int i = 0; i < N; i++) {
+        std::vector<int> vDists(Distances.begin() + (size_t)i * N, Distances.begin() + (size_t)(i + 1) * N);
+        std::sort(vDists.begin(), vDists.end());
+        int median = vDists[0.5 * (N - 1)];
+        if (median < BestMedian) {
+            BestMedian = median;
+            BestIdx = i;
+        }
+    }
+    return BestIdx;
+}
+
 // Frame::UndistortKeyPoints (src/Frame.cc:389-423): cv::undistortPoints(mat, mat, mK, mDistCoef, cv::Mat(), mK) on the
 // N x 2 CV_32F keypoint positions.  OpenCV is not vendored; cvUndistortPoints (imgproc/src/undistort.cpp, 2.4.13 and
 // 3.4.1 agree for a k1,k2,p1,p2[,k3] model) restated: everything in double, K and the coefficients widened from

@@ -280,6 +280,35 @@ int main() {
         CHECK(u1 && moved, "UndistortKeyPoints differs from the oracle");
     }
 
+    // ---- MapPoint::ComputeDistinctiveDescriptors through the shim vs the oracle (observations = jittered copies)
+    {
+        const int nmp = 40;
+        std::vector<MapPoint> dmp(nmp);
+        std::vector<MapPoint*> dvp(nmp);
+        std::vector<std::vector<uint8_t>> obsd(nmp);
+        sm_state = 4242;
+        for (int i = 0; i < nmp; i++) {
+            dvp[i] = &dmp[i];
+            std::memset(dmp[i].mDescriptor, 0x5a, 32);
+            const int nobs = i % 9;                                   // 0 .. 8 observations
+            obsd[i].resize((size_t)nobs * 32);
+            for (int r = 0; r < nobs; r++) {
+                std::memcpy(&obsd[i][(size_t)r * 32], d1.ptr(i), 32);
+                const int flips = (int)(splitmix() % 40);
+                for (int f = 0; f < flips; f++) { const int b = (int)(splitmix() % 256); obsd[i][(size_t)r * 32 + (b >> 3)] ^= (uint8_t)(1u << (b & 7)); }
+            }
+        }
+        m.ComputeDistinctiveDescriptors(dvp, obsd);
+        bool dd = true;
+        for (int i = 0; i < nmp; i++) {
+            const int nobs = i % 9;
+            const int ob = oracle::distinctiveDescriptor(obsd[i].data(), nobs);
+            if (ob < 0) { for (int q = 0; q < 32; q++) dd = dd && dmp[i].mDescriptor[q] == 0x5a; }
+            else dd = dd && std::memcmp(dmp[i].mDescriptor, &obsd[i][(size_t)ob * 32], 32) == 0;
+        }
+        CHECK(dd, "ComputeDistinctiveDescriptors differs from the oracle");
+    }
+
     printf("shim test: %zu/%zu keypoints, %d init matches, %d projection matches, %zu good features, %d active matches: %s\n", k1.size(),
            k2.size(), nm, np, good.size(), nActive, g_fail ? "FAILED" : "OK");
     return g_fail ? 1 : 0;

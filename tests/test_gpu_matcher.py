@@ -401,3 +401,39 @@ def test_search_by_projection_frames_good_feature(orc, seq_frames, th_good, th_r
         assert nm[b] == en, (b, nm[b], en)
         assert np.array_equal(cmp_[b, :counts[b + 1]], emp) and (esc == 999).all()
     assert nm[0] > 50
+
+
+def test_compute_distinctive_descriptors(orc):
+    """MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:196-262) batched: least-median row per map point, ties to
+    the first row, empty points -> -1 and an untouched descriptor; host and device inputs."""
+    import torch
+    from gf_orb_slam_b200 import ORBmatcher
+    rng = np.random.default_rng(11)
+    sizes = [0, 1, 2, 3, 4, 7, 33, 50, 64, 129, 300, 0, 5] + list(rng.integers(1, 40, 200))
+    descs = []
+    for n in sizes:
+        base = rng.integers(0, 256, 32, dtype=np.uint8)
+        d = np.repeat(base[None], n, 0)
+        for r in range(n):                                        # observations = a base descriptor with a few flipped bits
+            k = int(rng.integers(0, 60)) if r % 5 != 2 else 0      # every fifth is an exact copy -> ties between rows
+            bits = rng.choice(256, k, replace=False)
+            for b in bits:
+                d[r, b >> 3] ^= np.uint8(1 << (b & 7))
+        descs.append(d)
+    allD = np.concatenate(descs).astype(np.uint8)
+    off = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+    exp = orc.distinctive_descriptors(allD, off)
+    m = ORBmatcher(0.8, True, max_batch=1, max_keypoints=4096, max_queries=4096)
+    out0 = np.full((len(sizes), 32), 0xAB, np.uint8)
+    best, out = m.ComputeDistinctiveDescriptors(allD, off, out0)
+    assert np.array_equal(best, exp)
+    for i, n in enumerate(sizes):
+        if n == 0:
+            assert exp[i] == -1 and (out[i] == 0xAB).all()
+        else:
+            assert np.array_equal(out[i], descs[i][exp[i]])
+    assert len(set(exp[np.array(sizes) > 4].tolist())) > 3          # the winner is not a fixed row
+    bd, od = m.ComputeDistinctiveDescriptors(torch.from_numpy(allD).cuda(), torch.from_numpy(off).cuda())
+    assert np.array_equal(bd.cpu().numpy(), exp)
+    nz = np.array(sizes) > 0
+    assert np.array_equal(od.cpu().numpy()[nz], out[nz])
