@@ -626,7 +626,12 @@ __global__ void __launch_bounds__(T + 32, MINB) k_select_ahead(const SelParams P
         if (pick < 0) dead = true;
         if (!dead) {
             // ---- update the running matrix, record the pick, erase its column (order preserved)
-            if (tid < 49) cur[tid] = cur[tid] + sgn * blk[(size_t)pick * 49 + tid];
+            // the winner's packed triangle was read by its evaluator a moment ago (L1 / L2 hot); blocks are exactly
+            // symmetric (H^T H with commutative products), so entry (i, j) is the packed entry (max, min)
+            if (tid < 49) {
+                const int ui = tid / 7, uj = tid - ui * 7;
+                cur[tid] = cur[tid] + sgn * pk[(size_t)pick * 28 + LT(max(ui, uj), min(ui, uj))];
+            }
             if (tid == 0 && !deletion && i < P.outStride) { outIdx[i] = pick; if (outLd) outLd[i] = winV; }
             if (!deletion) nOut = i + 1;
             // lmkIdx stays ascending (identity minus erased columns): every entry >= pick moves one column left
