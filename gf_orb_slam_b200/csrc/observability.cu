@@ -608,11 +608,18 @@ __global__ void __launch_bounds__(T + 32, MINB) k_select_ahead(const SelParams P
             const double v = logdet_sum_packed(cur, pk + (size_t)q * 28, blk + (size_t)q * 49, sgn);
             if (v > bestV) { bestV = v; bestT = t; }
         }
-#pragma unroll
-        for (int d = 16; d >= 1; d >>= 1) {
-            const double ov = __shfl_xor_sync(full, bestV, d);
-            const int ot = __shfl_xor_sync(full, bestT, d);
-            if (ov > bestV || (ov == bestV && ot < bestT)) { bestV = ov; bestT = ot; }
+        {   // warp arg-max (largest value, then smallest draw number) with three redux ops on an order-preserving integer
+            // image of the double instead of five rounds of 64-bit shuffles
+            const long long bits = __double_as_longlong(bestV);
+            const unsigned long long key = bits < 0 ? ~(unsigned long long)bits : ((unsigned long long)bits | 0x8000000000000000ull);
+            const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
+            const unsigned mhi = __reduce_max_sync(full, hi);
+            const unsigned mlo = __reduce_max_sync(full, hi == mhi ? lo : 0u);
+            const bool top = hi == mhi && lo == mlo;
+            const int mt = __reduce_min_sync(full, top ? bestT : INT_MAX);
+            const int src = __ffs(__ballot_sync(full, top && bestT == mt)) - 1;
+            bestV = __shfl_sync(full, bestV, src);
+            bestT = mt;
         }
         if (lane == 0) { redV[i & 1][warp] = bestV; redT[i & 1][warp] = bestT; }
         bar_sync_i<B_EVAL, T>();
