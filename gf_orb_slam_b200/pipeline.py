@@ -70,7 +70,7 @@ class TrackingFrontEnd:
         self.sel_ld2 = [z(B, n_good, dt=torch.float64) for _ in range(2)]
         self.sel_n2 = [z(B, dt=torch.int32) for _ in range(2)]
         self.overlap = overlap
-        self.s_sel = torch.cuda.Stream(device=self.dev) if overlap else None
+        self.s_sel = torch.cuda.Stream(device=self.dev, priority=int(os.environ.get("GFORB_SEL_PRIORITY", "0"))) if overlap else None
         self.s_copy = torch.cuda.Stream(device=self.dev)        # device -> host results
         self.s_up = torch.cuda.Stream(device=self.dev)          # host -> device frames (its own copy engine and queue)
         self.ev_info = [torch.cuda.Event() for _ in range(2)]
@@ -86,11 +86,12 @@ class TrackingFrontEnd:
         self.F1 = [Frames(self.kps2[i][:B], self.desc2[i][:B], self.counts2[i][:B], width, height) for i in range(2)]
         self.F2 = [Frames(self.kps2[i][1:], self.desc2[i][1:], self.counts2[i][1:], width, height) for i in range(2)]
         self.kps_i32 = [k.view(torch.int32) for k in self.kps2]
-        self.s_match = torch.cuda.Stream(device=self.dev) if overlap else None
+        self.s_match = torch.cuda.Stream(device=self.dev, priority=int(os.environ.get("GFORB_MATCH_PRIORITY", "0"))) if overlap else None
         self.ev_extract = [torch.cuda.Event() for _ in range(2)]
         self.ev_match = [torch.cuda.Event() for _ in range(2)]
         self.launches_per_step = 0
         self.profile = False
+        self.timeline = None                # list of (name, step, event) when tools/timeline.py asks for one
         self._ev = []                       # (stage, start, end) torch events recorded while self.profile
         # pinned host staging for the end-to-end path
         self.h_images = torch.zeros((B, height, width), dtype=torch.uint8).pin_memory()
@@ -154,6 +155,12 @@ class TrackingFrontEnd:
         for e in self.ev_d2h_sel:
             cur.wait_event(e)
 
+    def _tl(self, name, stream):
+        if self.timeline is not None:
+            e = torch.cuda.Event(enable_timing=True)
+            e.record(stream)
+            self.timeline.append((name, self.t, e))
+
     def step_device(self, images: torch.Tensor | None = None):
         """extract -> match -> info on the current stream; the good-feature selection of this step on s_sel, where it
         overlaps the extraction of the next step (it is a latency-bound kernel that leaves the ALU pipe idle)"""
@@ -176,7 +183,9 @@ class TrackingFrontEnd:
             self.ev_halo_read.record(main)
         if self.halo_reader is not None and self.halo_reader is not self:
             main.wait_event(self.halo_reader.ev_halo_read)                  # the other lane has read its halo
+        self._tl("extract_begin", main)
         self.ex.extract_device(img, kps[1:], desc[1:], counts[1:], stream=st, sync=False)
+        self._tl("extract_end", main)
         self.ev_extracted.record(main)
         n = self.ex.last_launches()
         self._mark("match")
@@ -187,11 +196,13 @@ class TrackingFrontEnd:
             self.ev_extract[p].record(main)
             ms.wait_event(self.ev_extract[p])
             ms.wait_event(self.ev_d2h2[p])                                  # the host copies of step t-2's matches are done
+        self._tl("match_begin", ms)
         with torch.cuda.stream(ms):
             self.prev2[p].copy_(kps[:B, :, 0:2])                            # vbPrevMatched[i] = F1.mvKeysUn[i].pt
             self.matcher.SearchForInitialization(self.F1[p], self.F2[p], self.prev2[p], self.window, matches12=self.m12_2[p],
                                                  nmatches=self.nmatch2[p], stream=ms.cuda_stream, sync=False)
             self.ev_match[p].record(ms)
+        self._tl("match_end", ms)
         n += self.matcher.last_launches()
         self._mark("info")
         if self.s_sel is not None:
@@ -210,8 +221,11 @@ class TrackingFrontEnd:
         else:
             main.wait_event(self.ev_d2h_sel[p])
             obs, sst = self.obs, st
+        self._tl("info_end", main)
+        self._tl("select_begin", self.s_sel if self.s_sel is not None else main)
         obs.select(self.blocks2[p], self.obs_score2[p], self.cnt_sel2[p], self.k, LAZIER_GREEDY, self.sample_scale, self.seeds,
                    out_idx=self.sel_idx2[p], out_logdet=self.sel_ld2[p], out_n=self.sel_n2[p], stream=sst, sync=False)
+        self._tl("select_end", self.s_sel if self.s_sel is not None else main)
         n += obs.last_launches()
         if self.s_sel is not None:
             self.ev_sel[p].record(self.s_sel)
