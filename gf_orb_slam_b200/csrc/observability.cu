@@ -590,7 +590,7 @@ __global__ void __launch_bounds__(T + 32, MINB) k_select_ahead(const SelParams P
     for (int i = 0; i < rounds; i++) {
         const int p = i & 1;
         const int* colp = p ? col1 : col0;
-        bar_sync2<B_FULL, ALL>(p);
+        if (i == 0) bar_sync2<B_FULL, ALL>(p);            // later lists are waited for at the end of the previous round
         SEL_MARK(0)
         const int cnt = dead ? 0 : s_cnt2[p];
         // ---- logDet(cur +- block) of every drawn column's pool entry; arg-max, first drawn wins ties (strict >)
@@ -631,6 +631,21 @@ __global__ void __launch_bounds__(T + 32, MINB) k_select_ahead(const SelParams P
         SEL_MARK(1)
         if (i + 2 < rounds) bar_arrive2<B_EMPTY, ALL>(p);     // this thread's last read of list p is behind it
         if (pick < 0) dead = true;
+        if (i + 1 < rounds) {
+            // The next round's list is there already (the sampler runs ahead) and its columns map to pool entries through
+            // this round's index array and pick, before the erase below: pull this thread's first block of the next round
+            // into L1 now, so that the L2 round trip overlaps the update, the erase and the barrier.
+            bar_sync2<B_FULL, ALL>(p ^ 1);
+            if (!dead && tid < s_cnt2[p ^ 1]) {
+                const int c = (p ? col0 : col1)[tid];
+                const int e0 = idx[c];
+                const int qn = (e0 >= pick) ? idx[c + 1] : e0;
+                const char* pf = reinterpret_cast<const char*>(pk + (size_t)qn * 28);
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(pf));
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(pf + 112));
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(pf + 223));
+            }
+        }
         if (!dead) {
             // ---- update the running matrix, record the pick, erase its column (order preserved)
             // the winner's packed triangle was read by its evaluator a moment ago (L1 / L2 hot); blocks are exactly
