@@ -50,14 +50,46 @@ def ncu_facts():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    """SM clock and clock-event (throttle) reasons sampled while the timed region runs: NVML every 10 ms (a timed region
+    is only tens of milliseconds long), `nvidia-smi -lms 200` when pynvml is missing."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    BITS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
 
     def __init__(self, index: int):
         self.index, self.proc, self.lines = index, None, []
+        self.nv, self.samples, self.stop_flag, self.mx = None, [], False, None
+
+    def _poll(self):
+        nv, h = self.nv
+        while not self.stop_flag:
+            try:
+                clk = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+                try:
+                    rs = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+                except Exception:
+                    rs = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                self.samples.append((clk, rs))
+            except Exception:
+                pass
+            time.sleep(0.01)
 
     def start(self):
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            # NVML enumerates physical devices: honour CUDA_VISIBLE_DEVICES when it lists indices
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+            ids = [int(x) for x in vis.split(",") if x.strip().isdigit()]
+            phys = ids[self.index] if self.index < len(ids) else self.index
+            h = nv.nvmlDeviceGetHandleByIndex(phys)
+            self.mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            self.nv = (nv, h)
+            self.th = threading.Thread(target=self._poll, daemon=True)
+            self.th.start()
+            return
+        except Exception:
+            self.nv = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
                                           "-lms", "200"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
@@ -71,6 +103,17 @@ class ClockSampler:
             self.lines.append(ln.strip())
 
     def stop(self):
+        if self.nv is not None:
+            self.stop_flag = True
+            self.th.join(timeout=1)
+            sm = [c for c, _ in self.samples]
+            reasons = set()
+            for _, rs in self.samples:
+                for bit, nm in self.BITS.items():
+                    if rs & bit:
+                        reasons.add(nm)
+            return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": float(self.mx) if self.mx else None,
+                    "reasons": sorted(reasons), "samples": len(sm), "source": "nvml, 10 ms"}
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
@@ -92,7 +135,7 @@ class ClockSampler:
                 if v.lower().startswith("active"):
                     reasons.add(nm)
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm), "source": "nvidia-smi -lms 200"}
 
 
 def host_cores() -> int:
