@@ -265,7 +265,7 @@ def run_ours(args):
     fe.profile = False
     stages = fe.extract_stage_times()
     pipe_stages = fe.stage_times()
-    launches = fe.launches_per_step * args.steps
+    launches = fe.launches_per_step * args.steps * world_size        # whole job, like `value`
     # the same stage events with the selection on the main stream (no co-running kernel): per-kernel durations that are
     # not inflated by the selection kernel of the previous step sharing the SMs
     ser = LanedFrontEnd(W_, H_, NFEAT, B, lanes=1, n_good=NGOOD, device=local, overlap=False)
