@@ -214,6 +214,16 @@ def run_ours(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device -- the B200 path has no CPU fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
+    if world_size > 1 and os.environ.get("GFORB_NO_CPU_AFFINITY") is None:
+        # one process per GPU on a multi-socket host: run (and first-touch the pinned staging buffers) on the CPUs NVML
+        # reports as local to this GPU, so that the H2D / D2H traffic of the end-to-end leg does not cross sockets
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            vis = [int(x) for x in os.environ.get("CUDA_VISIBLE_DEVICES", "").split(",") if x.strip().isdigit()]
+            nv.nvmlDeviceSetCpuAffinity(nv.nvmlDeviceGetHandleByIndex(vis[local] if local < len(vis) else local))
+        except Exception:
+            pass
     if world_size > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
