@@ -1,10 +1,12 @@
 // Shared device code of the good-feature kernels: logDet (include/Util.hpp:714-731) as a register-resident 7x7
 // Cholesky with the LU fallback, and the warp-parallel glibc TYPE_3 rand() stream the selection loops draw from.
 // Included by observability.cu (k_select, k_logdet) and matcher.cu (k_active_match); both TUs are built with
-// --fmad=false so every double operation rounds like the scalar CPU sequence.
+// --fmad=false so every double operation rounds like the scalar CPU sequence, and log() is glibc's (glibc_log.h): the
+// log-dets are bit-identical to the host's, ties in the greedy arg-max included.
 #pragma once
 #include <cstdint>
 #include <cmath>
+#include "glibc_log.h"
 
 namespace gforb {
 
@@ -50,7 +52,7 @@ static __device__ __noinline__ double lu7_logabsdet(const double* __restrict__ c
         for (int i = k + 1; i < 7; i++) if (fabs(A[i * 7 + k]) > fabs(A[p * 7 + k])) p = i;
         if (p != k) for (int c = 0; c < 7; c++) { double t = A[k * 7 + c]; A[k * 7 + c] = A[p * 7 + c]; A[p * 7 + c] = t; }
         const double piv = A[k * 7 + k];
-        ld += log(fabs(piv));
+        ld += glibc_log(fabs(piv));
         if (piv == 0) continue;
         for (int i = k + 1; i < 7; i++) {
             const double f = A[i * 7 + k] / piv;
@@ -68,7 +70,7 @@ __device__ __forceinline__ double logdet_sum(const double* __restrict__ cur, con
 #pragma unroll
         for (int j = 0; j < 7; j++) if (j <= i) A[LT(i, j)] = cur[i * 7 + j] + sgn * blk[i * 7 + j];
     double p;
-    if (chol7_prod(A, p)) return 2 * log(p);
+    if (chol7_prod(A, p)) return 2 * glibc_log(p);
     return lu7_logabsdet(cur, blk, sgn);
 }
 
@@ -96,7 +98,7 @@ __device__ __forceinline__ double logdet_sum_packed(const double* __restrict__ c
 #pragma unroll
         for (int j = 0; j < 7; j++) if (j <= i) A[LT(i, j)] = cur[i * 7 + j] + sgn * B[LT(i, j)];
     double p;
-    if (chol7_prod(A, p)) return 2 * log(p);
+    if (chol7_prod(A, p)) return 2 * glibc_log(p);
     return lu7_logabsdet(cur, blkRow, sgn);
 }
 

@@ -401,62 +401,3 @@ def _sum_stage_times(per_lane):
         for k, t in st:
             acc[k] = acc.get(k, 0.0) + t
     return list(acc.items())
-
-
-def cpu_front_end(oracle, frames: np.ndarray, prev_kd, world, score, xv, sigma2, k, sample_scale, window=100, nnratio=0.9,
-                  cam=None):
-    """The same per-frame chain on the CPU oracle (checker / cpu_baseline only).  prev_kd = (kps, desc) of the frame
-    before frames[0] or None.  Returns per frame (kps, desc, matches12 or None, nmatches, sel_idx, sel_logdet)."""
-    h, w = frames.shape[1:]
-    ex = oracle.ORBextractor(1000 if world is None else world.shape[0], 1.2, 8)
-    cam = dict(EUROC_CAM) if cam is None else cam
-    ob = oracle.Observability(**cam)
-    out = []
-    for t in range(frames.shape[0]):
-        kps, desc = ex(frames[t])
-        m12, nm = None, 0
-        if prev_kd is not None:
-            f1 = oracle.Frame(prev_kd[0], prev_kd[1], w, h); f2 = oracle.Frame(kps, desc, w, h)
-            pm = np.stack([prev_kd[0]["x"], prev_kd[0]["y"]], -1).astype(np.float32)
-            nm, m12, _ = oracle.search_for_initialization(f1, f2, pm, window, nnratio, True)
-        n = len(kps)
-        ob.set_xv(xv); ob.predict(0.1, 1)
-        blocks, obs, _ = ob.build_frame(world[:n], kps["octave"], score[:n], np.ones(n, np.uint8), sigma2)
-        si, sl = oracle.select(blocks, k, 2, sample_scale, 1, scores=obs) if n > 0 else (np.zeros(0, np.int32), np.zeros(0))
-        out.append((kps, desc, m12, nm, si, sl))
-        prev_kd = (kps, desc)
-    return out
-
-
-def smoke_check(oracle, device=0, batch=3):
-    """One small batch through the CUDA front end, checked bit-exactly against the CPU oracle."""
-    seq = synth.Sequence()
-    frames = seq.frames(0, 2 * batch)
-    fe = TrackingFrontEnd(batch=batch, device=device)
-    res = []
-    for s in range(2):
-        fe.images.copy_(torch.from_numpy(frames[s * batch:(s + 1) * batch]))
-        fe.step_device()
-        fe.sync()
-        torch.cuda.synchronize()
-        res.append([t.cpu().numpy().copy() for t in (fe.kps[1:], fe.desc[1:], fe.counts[1:], fe.m12, fe.nmatch, fe.sel_idx,
-                                                      fe.sel_ld, fe.sel_n)])
-    exp = cpu_front_end(oracle, frames, None, fe.world_h, fe.score_h, fe.xv_h, fe.sigma2_h, fe.k, fe.sample_scale)
-    from ._lib import KP_DTYPE
-    nmatched = 0
-    for s in range(2):
-        kps, desc, counts, m12, nmatch, sidx, sld, sn = res[s]
-        for b in range(batch):
-            t = s * batch + b
-            ek, ed, em12, enm, esi, esl = exp[t]
-            n = counts[b]
-            assert n == len(ek), ("keypoint count", t, n, len(ek))
-            gk = kps[b, :n].copy().view(KP_DTYPE).reshape(-1)
-            assert gk.tobytes() == ek.tobytes(), ("keypoints", t)
-            assert np.array_equal(desc[b, :n], ed), ("descriptors", t)
-            if t > 0:
-                assert nmatch[b] == enm and np.array_equal(m12[b, :len(em12)], em12), ("matches", t)
-                nmatched += int(enm)
-            assert sn[b] == len(esi) and np.array_equal(sidx[b, :sn[b]], esi), ("good-feature subset", t)
-            assert np.allclose(sld[b, :sn[b]], esl, rtol=1e-5), ("log-det", t)
-    return dict(frames=2 * batch, launches_per_step=fe.launches_per_step, matches=nmatched, selected=int(res[1][7].sum()))

@@ -18,11 +18,30 @@ KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4
                      ("octave", "<i4"), ("class_id", "<i4")])
 
 
+def host_signature() -> str:
+    """the CPU feature flags of this host: liboracle.so is built -O3 -march=native (the reference's own flags,
+    CMakeLists.txt:13-31), so a copy built on another machine must be rebuilt here before it is loaded"""
+    import hashlib
+    try:
+        for ln in open("/proc/cpuinfo"):
+            if ln.startswith("flags"):
+                return hashlib.sha1(" ".join(sorted(ln.split(":", 1)[1].split())).encode()).hexdigest()
+    except OSError:
+        pass
+    return "unknown"
+
+
 def build(force: bool = False) -> str:
     so = os.path.join(_HERE, "liboracle.so")
-    srcs = [os.path.join(_HERE, f) for f in os.listdir(_HERE) if f.endswith((".cpp", ".hpp"))]
-    if force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
+    tag = so + ".host"
+    srcs = [os.path.join(_HERE, f) for f in os.listdir(_HERE) if f.endswith((".cpp", ".hpp")) or f == "Makefile"]
+    sig = host_signature()
+    stale = not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs)
+    foreign = not os.path.exists(tag) or open(tag).read().strip() != sig
+    if force or stale or foreign:
         subprocess.check_call(["make", "-C", _HERE, "-B", "liboracle.so"], stdout=subprocess.DEVNULL)
+        with open(tag, "w") as f:
+            f.write(sig + "\n")
     return so
 
 

@@ -34,6 +34,8 @@ __global__ void __launch_bounds__(256) k(uint32_t* out, uint32_t seed) {
             if (OP == 17) a[i] = __dp4a(a[i], b, c);
             if (OP == 18) a[i] = __dp2a_lo(a[i], b, c);
             if (OP == 19) a[i] = __vsadu4(a[i], b) + c;
+            if (OP == 20) a[i] = __popc(a[i] ^ b) + c;           // LOP3 + POPC + IADD: POPC-bound if POPC is the slow pipe
+            if (OP == 21) a[i] = __popc(a[i]) ^ b;              // POPC + LOP3
             if (OP == 16) { if (i < 4) a[i] = a[i] * b + c; else a[i] = __vimin3_u16x2(a[i], b, c); }
         }
         if (OP == 5) {   // interleave with half2 max on a second set
@@ -59,12 +61,13 @@ void run(const char* name, int opsPerIter) {
     float ms; cudaEventElapsedTime(&ms, e0, e1);
     double ops = 148.0 * 8 * 256 * (double)ITERS * opsPerIter;
     int clk; cudaDeviceGetAttribute(&clk, cudaDevAttrClockRate, 0);
-    printf("%-28s %8.3f ms  %7.2f Tops/s  %6.1f lane-ops/clk/SM (at %d MHz)\n", name, ms, ops / ms / 1e9, ops / (ms * 1e-3) / 148 / (clk * 1e3), clk / 1000);
+    printf("{\"op\": \"%s\", \"ms\": %.3f, \"tera_ops_per_s\": %.2f, \"lane_ops_per_clk_per_sm\": %.1f, \"clock_mhz\": %d}\n", name, ms, ops / ms / 1e9, ops / (ms * 1e-3) / 148 / (clk * 1e3), clk / 1000);
     cudaFree(d);
 }
 int main() {
     run<0>("vimax3_u16x2", 8); run<6>("vimin3_u16x2", 8); run<1>("vmaxu2 (2-input)", 8); run<2>("hmax2 on raw bits", 8);
     run<3>("prmt", 8); run<4>("imad", 8); run<5>("vimax3 + hmin2 interleaved", 16); run<7>("max3 u32", 8); run<8>("shf funnel", 8); run<9>("lop3 select", 8); run<10>("iadd", 8); run<11>("shr+lop3", 8); run<12>("vminu2", 8); run<13>("vmin(vmax) 2x2-input int", 16); run<14>("hmin(hmax) 2x2-input half", 16); run<15>("4 vimin3 + 4x2 half (indep)", 12); run<16>("4 imad + 4 vimin3 (indep)", 8);
+    run<20>("popc(xor)+add (1 POPC counted)", 8); run<21>("popc^b (1 POPC counted)", 8);
     run<17>("dp4a (IDP.4A)", 8); run<18>("dp2a_lo (IDP.2A)", 8); run<19>("vsadu4 + add", 8);
     return 0;
 }
