@@ -52,6 +52,20 @@ class ExtractorConfig(C.Structure):
                 ("max_batch", C.c_int32), ("device", C.c_int32)]
 
 
+class FrontEndConfig(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("nfeatures", C.c_int32), ("nlevels", C.c_int32),
+                ("scaleFactor", C.c_float), ("iniThFAST", C.c_int32), ("minThFAST", C.c_int32), ("max_batch", C.c_int32),
+                ("window_size", C.c_int32), ("nnratio", C.c_float), ("check_orientation", C.c_int32), ("n_good", C.c_int32),
+                ("sample_scale", C.c_double), ("fu", C.c_double), ("fv", C.c_double), ("Cx", C.c_double), ("Cy", C.c_double),
+                ("k1", C.c_double), ("k2", C.c_double), ("dx", C.c_double), ("dy", C.c_double), ("overlap", C.c_int32),
+                ("device", C.c_int32)]
+
+
+class FrontEndOutputs(C.Structure):
+    _fields_ = [("keypoints", C.c_void_p), ("descriptors", C.c_void_p), ("counts", C.c_void_p), ("matches12", C.c_void_p),
+                ("nmatches", C.c_void_p), ("good_idx", C.c_void_p), ("good_logdet", C.c_void_p), ("good_n", C.c_void_p)]
+
+
 _lib = None
 
 
@@ -96,6 +110,21 @@ def lib() -> C.CDLL:
         L.gforb_window_search.argtypes = [vp, FS, FS, i32, vp, i32, i32, i32, f32, i32, vp, vp, i32, vp]
         L.gforb_allpairs_top2.argtypes = [vp, vp, i32, vp, i64, i64, vp, i32, vp]
         L.gforb_top2_merge.argtypes = [vp, vp, i32, i32, vp, i32, vp]
+        L.gforb_matcher_poll_error.argtypes = [vp, vp]
+        L.gforb_extractor_poll_error.argtypes = [vp, vp]
+        L.gforb_obs_poll_error.argtypes = [vp, vp]
+        FO = C.POINTER(FrontEndOutputs)
+        L.gforb_frontend_create.argtypes = [C.POINTER(FrontEndConfig), C.POINTER(vp)]
+        L.gforb_frontend_destroy.argtypes = [vp]
+        L.gforb_frontend_set_map.argtypes = [vp, vp, vp, vp, vp]
+        L.gforb_frontend_step_device.argtypes = [vp, vp, i32]
+        L.gforb_frontend_step_host.argtypes = [vp, vp, i32, FO]
+        L.gforb_frontend_sync.argtypes = [vp]
+        L.gforb_frontend_wait_results.argtypes = [vp, i32]
+        L.gforb_frontend_results.argtypes = [vp, FO]
+        L.gforb_frontend_launches_per_step.argtypes = [vp]
+        L.gforb_frontend_set_profiling.argtypes = [vp, i32]
+        L.gforb_frontend_stage_time.argtypes = [vp, i32, C.POINTER(C.c_char_p), C.POINTER(C.c_float)]
         L.gforb_obs_create.argtypes = [C.POINTER(ObsConfig), C.POINTER(vp)]
         L.gforb_obs_destroy.argtypes = [vp]
         L.gforb_obs_last_launches.argtypes = [vp]
@@ -127,7 +156,10 @@ gforb_obs_get_state gforb_obs_update_pwls gforb_obs_predict_pwls gforb_obs_num_s
 gforb_obs_build_info_frame gforb_obs_build_info_map gforb_obs_logdet gforb_obs_rand_stream gforb_obs_select
 gforb_obs_active_match gforb_frame_is_in_frustum gforb_frame_undistort_keypoints
 gforb_search_by_projection_good_feature gforb_search_by_projection_frames_good_feature
-gforb_mappoint_distinctive_descriptors""".split()
+gforb_mappoint_distinctive_descriptors gforb_matcher_poll_error gforb_extractor_poll_error gforb_obs_poll_error
+gforb_frontend_create gforb_frontend_destroy gforb_frontend_set_map gforb_frontend_step_device gforb_frontend_step_host
+gforb_frontend_sync gforb_frontend_wait_results gforb_frontend_results gforb_frontend_launches_per_step gforb_frontend_set_profiling
+gforb_frontend_stage_time""".split()
 
 
 def check(rc: int, what: str):

@@ -1096,6 +1096,17 @@ int gforb_extract(GforbExtractor* E, const uint8_t* images, int w, int h, int st
     return GFORB_OK;
 }
 
+// error word of GFORB_ASYNC calls (cell-list overflow): synchronises `stream`, returns and clears the recorded error
+int gforb_extractor_poll_error(GforbExtractor* E, void* stream) {
+    if (!E) return GFORB_ERR_ARG;
+    GF_CUDA_OK(cudaSetDevice(E->device));
+    GF_CUDA_OK(cudaStreamSynchronize((cudaStream_t)stream));
+    int err = 0;
+    GF_CUDA_OK(cudaMemcpy(&err, E->d_err, sizeof(int), cudaMemcpyDeviceToHost));
+    if (err) { cudaMemset(E->d_err, 0, sizeof(int)); return err; }
+    return GFORB_OK;
+}
+
 int gforb_extractor_debug_level(GforbExtractor* E, int b, int level, int which, uint8_t* dst, size_t dst_bytes, int* w,
                                 int* hgt, int* pitch) {
     if (!E || level < 0 || level >= E->cfg.nlevels || b < 0 || b >= E->lastBatch) return GFORB_ERR_ARG;

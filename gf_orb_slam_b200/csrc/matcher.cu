@@ -495,6 +495,7 @@ __global__ void __launch_bounds__(32) k_resolve(const RParams R) {
 
 }  // namespace gforb
 #include "active.cuh"
+#include "allpairs_tc.cuh"
 namespace gforb {
 
 // ------------------------------------------------------------------------------------------------ Frame::isInFrustum
@@ -1301,27 +1302,74 @@ int gforb_allpairs_top2(GforbMatcher* M, const uint8_t* queries, int n_q, const 
     GF_CUDA_OK(cudaSetDevice(M->device));
     cudaStream_t st = (cudaStream_t)stream;
     M->lastLaunches = 0;
-    const int qTiles = (n_q + AP_THREADS * AP_R - 1) / (AP_THREADS * AP_R);
-    // chunk the shard so that the grid covers every SM several times; chunk rows <= 2^22 (packed key)
-    long long targetBlocks = (long long)M->numSMs * 8;
-    long long chunks = std::max<long long>(1, targetBlocks / qTiles);
-    long long chunkRows = (n_db + chunks - 1) / std::max<long long>(chunks, 1);
-    chunkRows = std::max<long long>(AP_TILE, ((chunkRows + AP_TILE - 1) / AP_TILE) * AP_TILE);
-    chunkRows = std::min<long long>(chunkRows, 1 << 22);
-    const int nChunks = (int)std::max<long long>(1, (n_db + chunkRows - 1) / chunkRows);
-    const size_t need = (size_t)nChunks * n_q * 2;
-    if (need > M->capPartial) {
-        if (M->d_partial) cudaFree(M->d_partial);
-        M->d_partial = nullptr;
-        GF_CUDA_OK(cudaMalloc((void**)&M->d_partial, need * sizeof(uint64_t)));
-        M->capPartial = need;
+    // GFORB_ALLPAIRS = "popc": the integer-pipe kernel (parity reference, A/B partner); default: tcgen05 kind::i8 kernel
+    const char* sel = getenv("GFORB_ALLPAIRS");
+    const bool usePopc = n_db == 0 || (sel && !strcmp(sel, "popc"));
+    int nChunks;
+    if (!usePopc) {
+        const int qTiles = (n_q + tc::TC_QTILE - 1) / tc::TC_QTILE;
+        const long long nTiles = (n_db + tc::TC_TILE - 1) / tc::TC_TILE;
+        long long splits = std::max<long long>(1, M->numSMs / qTiles);             // one wave of (splits x qTiles) CTAs
+        if (const char* e = getenv("GFORB_ALLPAIRS_SPLITS")) splits = std::max(1, atoi(e));
+        long long tilesPer = std::min<long long>((nTiles + splits - 1) / splits, (1 << 21) / tc::TC_TILE);   // packed key: 2^21 rows
+        tilesPer = std::max<long long>(tilesPer, 1);
+        nChunks = (int)((nTiles + tilesPer - 1) / tilesPer);
+        const size_t need = (size_t)nChunks * n_q * 2;
+        if (need > M->capPartial) {
+            if (M->d_partial) cudaFree(M->d_partial);
+            M->d_partial = nullptr; M->capPartial = 0;
+            GF_CUDA_OK(cudaMalloc((void**)&M->d_partial, need * sizeof(uint64_t)));
+            M->capPartial = need;
+        }
+        static bool attrSet[64] = {};
+        if (!attrSet[M->device & 63]) {
+            GF_CUDA_OK(cudaFuncSetAttribute(tc::k_allpairs_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::TC_SMEM_BYTES));
+            attrSet[M->device & 63] = true;
+        }
+        tc::TcParams P;
+        P.q = (const uint4*)queries; P.nq = n_q; P.db = (const uint4*)db; P.nDb = n_db; P.tilesPerSplit = (int)tilesPer;
+        P.idxBase = idx_base; P.partial = M->d_partial; P.err = M->d_err;
+        tc::k_allpairs_tc<<<dim3(nChunks, qTiles), tc::TC_THREADS, tc::TC_SMEM_BYTES, st>>>(P);
+    } else {
+        const int qTiles = (n_q + AP_THREADS * AP_R - 1) / (AP_THREADS * AP_R);
+        // chunk the shard so that the grid covers every SM several times; chunk rows <= 2^22 (packed key)
+        long long targetBlocks = (long long)M->numSMs * 8;
+        long long chunks = std::max<long long>(1, targetBlocks / qTiles);
+        long long chunkRows = (n_db + chunks - 1) / std::max<long long>(chunks, 1);
+        chunkRows = std::max<long long>(AP_TILE, ((chunkRows + AP_TILE - 1) / AP_TILE) * AP_TILE);
+        chunkRows = std::min<long long>(chunkRows, 1 << 22);
+        nChunks = (int)std::max<long long>(1, (n_db + chunkRows - 1) / chunkRows);
+        const size_t need = (size_t)nChunks * n_q * 2;
+        if (need > M->capPartial) {
+            if (M->d_partial) cudaFree(M->d_partial);
+            M->d_partial = nullptr; M->capPartial = 0;
+            GF_CUDA_OK(cudaMalloc((void**)&M->d_partial, need * sizeof(uint64_t)));
+            M->capPartial = need;
+        }
+        k_allpairs<<<dim3(qTiles, nChunks), AP_THREADS, 0, st>>>((const uint4*)queries, n_q, (const uint4*)db, n_db,
+                                                                 (int)chunkRows, idx_base, M->d_partial);
     }
-    k_allpairs<<<dim3(qTiles, nChunks), AP_THREADS, 0, st>>>((const uint4*)queries, n_q, (const uint4*)db, n_db,
-                                                             (int)chunkRows, idx_base, M->d_partial);
     k_top2_merge<<<(n_q + 255) / 256, 256, 0, st>>>(M->d_partial, nChunks, n_q, out_keys);
     M->lastLaunches = 2;
     GF_CUDA_OK(cudaGetLastError());
-    if (!(flags & GFORB_ASYNC)) GF_CUDA_OK(cudaStreamSynchronize(st));
+    if (!(flags & GFORB_ASYNC)) {
+        GF_CUDA_OK(cudaStreamSynchronize(st));
+        int err = 0;
+        GF_CUDA_OK(cudaMemcpy(&err, M->d_err, sizeof(int), cudaMemcpyDeviceToHost));
+        if (err) { cudaMemset(M->d_err, 0, sizeof(int)); return err > 0 ? GFORB_ERR_CUDA : err; }
+    }
+    return GFORB_OK;
+}
+
+// error word of the asynchronous calls (GFORB_ASYNC): internal overflow / protocol errors raised by kernels since the last poll.
+// Synchronises `stream`; returns GFORB_OK or the recorded GFORB_ERR_* and clears it.
+int gforb_matcher_poll_error(GforbMatcher* M, void* stream) {
+    if (!M) return GFORB_ERR_ARG;
+    GF_CUDA_OK(cudaSetDevice(M->device));
+    GF_CUDA_OK(cudaStreamSynchronize((cudaStream_t)stream));
+    int err = 0;
+    GF_CUDA_OK(cudaMemcpy(&err, M->d_err, sizeof(int), cudaMemcpyDeviceToHost));
+    if (err) { cudaMemset(M->d_err, 0, sizeof(int)); return err > 0 ? GFORB_ERR_CUDA : err; }
     return GFORB_OK;
 }
 

@@ -920,6 +920,16 @@ int gforb_obs_destroy(GforbObs* O) {
     return GFORB_OK;
 }
 
+int gforb_obs_poll_error(GforbObs* O, void* stream) {
+    if (!O) return GFORB_ERR_ARG;
+    GF_CUDA_OK(cudaSetDevice(O->device));
+    GF_CUDA_OK(cudaStreamSynchronize((cudaStream_t)stream));
+    int err = 0;
+    GF_CUDA_OK(cudaMemcpy(&err, O->d_err, sizeof(int), cudaMemcpyDeviceToHost));
+    if (err) { cudaMemset(O->d_err, 0, sizeof(int)); return err; }
+    return GFORB_OK;
+}
+
 int gforb_obs_last_launches(const GforbObs* O) { return O ? O->lastLaunches : GFORB_ERR_ARG; }
 
 int gforb_obs_set_select_residency(GforbObs* O, int ctas_per_sm) {

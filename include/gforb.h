@@ -234,6 +234,13 @@ int gforb_allpairs_top2(GforbMatcher* h, const uint8_t* queries, int n_q, const 
                         int64_t idx_base, uint64_t* out_keys, int flags, void* stream);
 int gforb_top2_merge(GforbMatcher* h, const uint64_t* gathered /* n_shards x n_q x 2 */, int n_shards, int n_q,
                      uint64_t* out_keys /* n_q x 2 */, int flags, void* stream);
+/* gforb_allpairs_top2 runs on the tensor cores (tcgen05.mma kind::i8 on +-1 / 0-1 expanded descriptors, exact); the
+ * environment variable GFORB_ALLPAIRS=popc selects the integer-pipe (LOP3/POPC) kernel, the parity reference. */
+
+/* Calls made with GFORB_ASYNC do not read the handle's device error word (candidate-pool overflow etc. -- the reference
+ * has no such limit, so an overflow would silently change results).  gforb_matcher_poll_error synchronises `stream` and
+ * returns GFORB_OK or the first GFORB_ERR_* recorded since the last poll (and clears it). */
+int gforb_matcher_poll_error(GforbMatcher* h, void* stream);
 
 /* ------------------------------------------------------------------------------------------------ good features
  * Replaces ORB_SLAM::Observability (include/Observability.h:113-770, include/Util.hpp, src/Observability.cc) for
@@ -315,6 +322,72 @@ int gforb_obs_active_match(GforbObs* obs, GforbMatcher* matcher, const GforbFram
                            float nnratio, int num_to_match, const uint32_t* seeds, int32_t* frame_mappoints,
                            int32_t* match_score, int32_t* nmatched, int32_t* left_idx, int32_t* left_n,
                            double* out_info, int flags, void* stream);
+
+/* ------------------------------------------------------------------------------------------------ pipelined front end
+ * The per-frame chain of Tracking::GrabImage (src/Tracking.cc:461-917) for a batch of consecutive frames, scheduled
+ * below the ABI in C++ (CUDA streams / events; double-buffered so that step t+1's upload and extraction overlap step t's
+ * matching, selection and result download):
+ *   Frame ctor:  ORBextractor::operator()                                  (src/Frame.cc:59)
+ *   tracking:    ORBmatcher::SearchForInitialization(frame t-1, frame t)    (src/Tracking.cc:1008,1097; the map-free matcher)
+ *   good feats:  Observability::runMatrixBuilding(FRAME_INFO_MATRIX) + maxVolSelection_LazierGreedy, which -- as in the
+ *                reference, where they work on the frame's matched map points -- start only after the matcher has finished.
+ * Frame t-1 of a step's first frame is the last frame of the previous step (1-frame halo; the very first frame of a
+ * stream is matched against an empty frame).  Every call is asynchronous; gforb_frontend_sync() joins all streams and
+ * returns the first error any kernel recorded (the device error words of the three operators are polled there). */
+typedef struct GforbFrontEndConfig {
+    int32_t width, height;            /* frame size (8-bit, tightly packed rows) */
+    int32_t nfeatures, nlevels;       /* ORBextractor ctor */
+    float scaleFactor;
+    int32_t iniThFAST, minThFAST;
+    int32_t max_batch;                /* frames per step */
+    int32_t window_size;              /* SearchForInitialization windowSize (100) */
+    float nnratio;                    /* ORBmatcher ctor (0.9) */
+    int32_t check_orientation;
+    int32_t n_good;                   /* k of the good-feature subset (100) */
+    double sample_scale;              /* lazier-greedy sampleScale (setSelction_Number :826) */
+    double fu, fv, Cx, Cy, k1, k2, dx, dy;   /* Observability / PinHoleCamera */
+    int32_t overlap;                  /* 1: matcher and selection on their own streams; 0: everything on one stream */
+    int32_t device;
+} GforbFrontEndConfig;
+
+typedef struct GforbFrontEndOutputs {  /* per step; host pointers (pinned recommended) for step_host, device pointers from results() */
+    GforbKeyPoint* keypoints;         /* batch x nfeatures */
+    uint8_t* descriptors;             /* batch x nfeatures x 32 */
+    int32_t* counts;                  /* batch */
+    int32_t* matches12;               /* batch x nfeatures: vnMatches12 of (frame t-1 -> frame t) */
+    int32_t* nmatches;                /* batch */
+    int32_t* good_idx;                /* batch x n_good: selected keypoint indices, selection order */
+    double* good_logdet;              /* batch x n_good or NULL */
+    int32_t* good_n;                  /* batch */
+} GforbFrontEndOutputs;
+
+typedef struct GforbFrontEnd GforbFrontEnd;
+int gforb_frontend_create(const GforbFrontEndConfig* cfg, GforbFrontEnd** out);
+int gforb_frontend_destroy(GforbFrontEnd* h);
+/* The matched map points the information blocks are built from, one per keypoint slot (MapPoint::GetWorldPos,
+ * Frame::mvpMatchScore), the 13-state Xv of the predicted segment and Frame::mvLevelSigma2; host arrays. */
+int gforb_frontend_set_map(GforbFrontEnd* h, const float* world /* nfeatures x 3 */, const int32_t* match_score /* nfeatures */,
+                           const double* Xv13, const float* level_sigma2 /* nlevels */);
+/* One step over `batch` frames resident in HBM (device pointer, batch x height x width). */
+int gforb_frontend_step_device(GforbFrontEnd* h, const uint8_t* d_images, int batch);
+/* One step over `batch` frames in host memory: H2D of the frames, the step, D2H of every output into *out (all inside
+ * the call's stream work; out's arrays must stay valid until gforb_frontend_sync). */
+int gforb_frontend_step_host(GforbFrontEnd* h, const uint8_t* images, int batch, const GforbFrontEndOutputs* out);
+int gforb_frontend_sync(GforbFrontEnd* h);
+/* Host-side wait for one gforb_frontend_step_host call only: the most recent one (steps_back = 0) or the one before it (1)
+ * has read its host frames and delivered its host outputs (a caller cycling through two sets of staging buffers waits
+ * with steps_back = 1 before refilling a set).  Does not poll the error words. */
+int gforb_frontend_wait_results(GforbFrontEnd* h, int steps_back);
+/* device pointers of the most recently issued step's results (valid after gforb_frontend_sync) */
+int gforb_frontend_results(GforbFrontEnd* h, GforbFrontEndOutputs* device_out);
+int gforb_frontend_launches_per_step(const GforbFrontEnd* h);
+/* profiling: CUDA-event time of stage i ("extract", "match", "info+select", then the extractor's own stages) averaged over
+ * the steps since profiling was switched on; returns the number of stages */
+int gforb_frontend_set_profiling(GforbFrontEnd* h, int on);
+int gforb_frontend_stage_time(GforbFrontEnd* h, int i, const char** name, float* ms);
+/* error words of asynchronous calls on the other handles (see gforb_matcher_poll_error) */
+int gforb_extractor_poll_error(GforbExtractor* h, void* stream);
+int gforb_obs_poll_error(GforbObs* h, void* stream);
 
 #ifdef __cplusplus
 }

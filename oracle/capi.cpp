@@ -13,6 +13,7 @@ extern "C" {
 
 // ------------------------------------------------------------------ primitives
 int orc_cvround(double v) { return cvRound(v); }
+void orc_set_fast_scalar(int on) { oracle::g_fast_scalar_only = on != 0; }
 void orc_fastatan2(const float* y, const float* x, float* out, int n) { for (int i = 0; i < n; i++) out[i] = fastAtan2(y[i], x[i]); }
 void orc_resize(const uint8_t* src, int sw, int sh, int sstep, uint8_t* dst, int dw, int dh, int dstep) { resizeLinear8u(src, sw, sh, sstep, dst, dw, dh, dstep); }
 void orc_border101(const uint8_t* src, int w, int h, int sstep, uint8_t* dst, int dstep, int b) { copyMakeBorder101(src, w, h, sstep, dst, dstep, b); }

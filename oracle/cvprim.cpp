@@ -5,6 +5,9 @@
 // CMakeLists.txt:42-49 / build_dep.sh:37-45); what is restated is its published algorithm, cross-checked
 // against cv2 4.13 in tests/test_oracle_cv.py.
 #include "oracle.hpp"
+#if defined(__SSE2__)
+#include <emmintrin.h>
+#endif
 #include <algorithm>
 #include <cfloat>
 #include <cmath>
@@ -105,29 +108,51 @@ void copyMakeBorder101(const uint8_t* src, int w, int h, int sstep, uint8_t* dst
 // Variant 1 (legacy 2.4.x integer path): kernel cvRound(k*256) = {18,34,49,55,49,34,18}, saturated.
 static const int kGauss[2][7] = {{18, 34, 48, 56, 48, 34, 18}, {18, 34, 49, 55, 49, 34, 18}};
 
-template <class Fetch>
-static void blurCore(Fetch fetch, int w, int h, uint8_t* dst, int dstep, int variant) {
+// Separable pass over rows that are directly addressable with a 3-pixel margin on every side (a reflect-101 padded copy,
+// or the ROI of a bordered pyramid plane): a ring of 7 horizontally filtered int32 rows, then the vertical taps.  Same
+// integer arithmetic as the textbook double loop ((sum_y k_y sum_x k_x p + 2^15) >> 16); written with plain pointer loops so
+// that -O3 -march=native vectorises it like OpenCV's SIMD path.
+static void blurRows(const uint8_t* src, ptrdiff_t sstep, int w, int h, uint8_t* dst, ptrdiff_t dstep, int variant) {
     const int* k = kGauss[variant];
-    std::vector<int> rows((size_t)(h + 6) * w);
-    for (int y = -3; y < h + 3; y++)
+    std::vector<int> ring((size_t)7 * w);
+    auto hrow = [&](int y) {
+        const uint8_t* __restrict p = src + (ptrdiff_t)y * sstep - 3;
+        int* __restrict r = ring.data() + (size_t)((y + 3) % 7) * w;
+        const int k0 = k[0], k1 = k[1], k2 = k[2], k3 = k[3], k4 = k[4], k5 = k[5], k6 = k[6];
+        for (int x = 0; x < w; x++)
+            r[x] = k0 * p[x] + k1 * p[x + 1] + k2 * p[x + 2] + k3 * p[x + 3] + k4 * p[x + 4] + k5 * p[x + 5] + k6 * p[x + 6];
+    };
+    for (int y = -3; y < 3; y++) hrow(y);
+    for (int y = 0; y < h; y++) {
+        hrow(y + 3);
+        const int* __restrict r0 = ring.data() + (size_t)((y + 0) % 7) * w;       // row y - 3 lives in slot (y - 3 + 3) % 7
+        const int* __restrict r1 = ring.data() + (size_t)((y + 1) % 7) * w;
+        const int* __restrict r2 = ring.data() + (size_t)((y + 2) % 7) * w;
+        const int* __restrict r3 = ring.data() + (size_t)((y + 3) % 7) * w;
+        const int* __restrict r4 = ring.data() + (size_t)((y + 4) % 7) * w;
+        const int* __restrict r5 = ring.data() + (size_t)((y + 5) % 7) * w;
+        const int* __restrict r6 = ring.data() + (size_t)((y + 6) % 7) * w;
+        uint8_t* __restrict d = dst + (ptrdiff_t)y * dstep;
+        const int k0 = k[0], k1 = k[1], k2 = k[2], k3 = k[3], k4 = k[4], k5 = k[5], k6 = k[6];
         for (int x = 0; x < w; x++) {
-            int s = 0;
-            for (int i = 0; i < 7; i++) s += k[i] * fetch(x + i - 3, y);
-            rows[(size_t)(y + 3) * w + x] = s;
+            const int sum = k0 * r0[x] + k1 * r1[x] + k2 * r2[x] + k3 * r3[x] + k4 * r4[x] + k5 * r5[x] + k6 * r6[x];
+            const int v = (sum + 32768) >> 16;
+            d[x] = (uint8_t)std::min(std::max(v, 0), 255);
         }
-    for (int y = 0; y < h; y++)
-        for (int x = 0; x < w; x++) {
-            int s = 0;
-            for (int i = 0; i < 7; i++) s += k[i] * rows[(size_t)(y + i) * w + x];
-            int v = (s + 32768) >> 16;
-            dst[(size_t)y * dstep + x] = (uint8_t)std::min(std::max(v, 0), 255);
-        }
+    }
 }
 
 void gaussianBlur7x7(const uint8_t* src, int w, int h, int sstep, uint8_t* dst, int dstep, int variant) {
+    // reflect-101 padded copy (3 pixels), then the shared row kernel; dst may alias src
+    const int pw = w + 6;
+    std::vector<uint8_t> pad((size_t)pw * (h + 6));
+    for (int y = -3; y < h + 3; y++) {
+        const uint8_t* srow = src + (size_t)reflect101(y, h) * sstep;
+        uint8_t* prow = pad.data() + (size_t)(y + 3) * pw;
+        for (int x = -3; x < w + 3; x++) prow[x + 3] = srow[reflect101(x, w)];
+    }
     std::vector<uint8_t> tmp((size_t)w * h);
-    blurCore([&](int x, int y) { return (int)src[(size_t)reflect101(y, h) * sstep + reflect101(x, w)]; }, w, h,
-             tmp.data(), w, variant);
+    blurRows(pad.data() + (size_t)3 * pw + 3, pw, w, h, tmp.data(), w, variant);
     for (int y = 0; y < h; y++) memcpy(dst + (size_t)y * dstep, tmp.data() + (size_t)y * w, w);
 }
 
@@ -135,7 +160,7 @@ void gaussianBlur7x7InPlace(uint8_t* roi, int w, int h, int step, int variant) {
     // The ROI sits inside a bordered plane, so (without BORDER_ISOLATED) OpenCV reads the ring pixels, which
     // hold the reflect-101 copy of the unblurred level (src/ORBextractor.cc:982-983) => same as isolated blur.
     std::vector<uint8_t> tmp((size_t)w * h);
-    blurCore([&](int x, int y) { return (int)roi[(ptrdiff_t)y * step + x]; }, w, h, tmp.data(), w, variant);
+    blurRows(roi, step, w, h, tmp.data(), w, variant);
     for (int y = 0; y < h; y++) memcpy(roi + (size_t)y * step, tmp.data() + (size_t)y * w, w);
 }
 
@@ -143,6 +168,8 @@ void gaussianBlur7x7InPlace(uint8_t* roi, int w, int h, int step, int variant) {
 // cv::FAST TYPE_9_16 with non-max suppression.
 static const int kCircle[16][2] = {{0, 3},  {1, 3},   {2, 2},   {3, 1},   {3, 0},  {3, -1}, {2, -2}, {1, -3},
                                    {0, -3}, {-1, -3}, {-2, -2}, {-3, -1}, {-3, 0}, {-3, 1}, {-2, 2}, {-1, 3}};
+
+bool g_fast_scalar_only = false;      // tests: force the scalar FAST path (orc_set_fast_scalar)
 
 static bool isCorner9(const uint8_t* p, const int* ofs, int t) {
     int v = p[0];
@@ -184,6 +211,36 @@ static int cornerScore9(const uint8_t* p, const int* ofs, int threshold) {
     return -b0 - 1;
 }
 
+#if defined(__SSE2__)
+// The same score with 16-bit lanes, one lane per arc start (the structure of OpenCV's SIMD cornerScore<16>): per lane k
+// a = min(d[k+1..k+8]), b = max(d[k+1..k+8]); A = max_k max(min(a, d[k]), min(a, d[k+9])), B likewise with min/max swapped;
+// result max(A, -B) - 1.  For a pixel that IS a corner at `threshold` this equals cornerScore9 (whose running maximum
+// merely starts at the threshold).
+static int cornerScore9_simd(const uint8_t* p, const int* ofs) {
+    alignas(16) short d[32];
+    const int v = p[0];
+    for (int k = 0; k < 25; k++) d[k] = (short)(v - p[ofs[k & 15]]);
+    __m128i q0 = _mm_set1_epi16(-1000), q1 = _mm_set1_epi16(1000);
+    for (int k = 0; k < 16; k += 8) {
+        __m128i v0 = _mm_loadu_si128((const __m128i*)(d + k + 1)), v1 = _mm_loadu_si128((const __m128i*)(d + k + 2));
+        __m128i a = _mm_min_epi16(v0, v1), b = _mm_max_epi16(v0, v1);
+        for (int t = 3; t <= 8; t++) {
+            v0 = _mm_loadu_si128((const __m128i*)(d + k + t));
+            a = _mm_min_epi16(a, v0); b = _mm_max_epi16(b, v0);
+        }
+        v0 = _mm_loadu_si128((const __m128i*)(d + k));
+        q0 = _mm_max_epi16(q0, _mm_min_epi16(a, v0)); q1 = _mm_min_epi16(q1, _mm_max_epi16(b, v0));
+        v0 = _mm_loadu_si128((const __m128i*)(d + k + 9));
+        q0 = _mm_max_epi16(q0, _mm_min_epi16(a, v0)); q1 = _mm_min_epi16(q1, _mm_max_epi16(b, v0));
+    }
+    q0 = _mm_max_epi16(q0, _mm_sub_epi16(_mm_setzero_si128(), q1));
+    q0 = _mm_max_epi16(q0, _mm_srli_si128(q0, 8));
+    q0 = _mm_max_epi16(q0, _mm_srli_si128(q0, 4));
+    q0 = _mm_max_epi16(q0, _mm_srli_si128(q0, 2));
+    return (short)_mm_cvtsi128_si32(q0) - 1;
+}
+#endif
+
 void FAST9_16(const uint8_t* img, int w, int h, int step, int threshold, bool nonmax, std::vector<KeyPoint>& out) {
     out.clear();
     if (w < 7 || h < 7) return;
@@ -199,7 +256,51 @@ void FAST9_16(const uint8_t* img, int w, int h, int step, int threshold, bool no
         memset(curr, 0, w);
         int ncorners = 0;
         if (i < h - 3) {
-            for (int j = 3; j < w - 3; j++) {
+            int j = 3;
+#if defined(__SSE2__)
+            if (!g_fast_scalar_only)
+            // 16 pixels per step, the structure of OpenCV's own SIMD FAST: signed-domain compares against v +- t
+            // (saturating), block-wide early out on the four compass points, then per-lane run-length counters over
+            // the wrapped circle.  Decides exactly what isCorner9 decides (a run of > 8 brighter or darker pixels).
+            {
+                const __m128i delta = _mm_set1_epi8((char)-128), tt = _mm_set1_epi8((char)threshold), K8 = _mm_set1_epi8(8);
+                for (; j < w - 18; j += 16) {
+                    const uint8_t* q = ptr + j;
+                    const __m128i v = _mm_loadu_si128((const __m128i*)q);
+                    const __m128i v0 = _mm_xor_si128(_mm_adds_epu8(v, tt), delta), v1 = _mm_xor_si128(_mm_subs_epu8(v, tt), delta);
+                    __m128i x0 = _mm_xor_si128(_mm_loadu_si128((const __m128i*)(q + ofs[0])), delta);
+                    __m128i x1 = _mm_xor_si128(_mm_loadu_si128((const __m128i*)(q + ofs[4])), delta);
+                    __m128i x2 = _mm_xor_si128(_mm_loadu_si128((const __m128i*)(q + ofs[8])), delta);
+                    __m128i x3 = _mm_xor_si128(_mm_loadu_si128((const __m128i*)(q + ofs[12])), delta);
+                    __m128i m0 = _mm_and_si128(_mm_cmpgt_epi8(x0, v0), _mm_cmpgt_epi8(x1, v0));
+                    __m128i m1 = _mm_and_si128(_mm_cmpgt_epi8(v1, x0), _mm_cmpgt_epi8(v1, x1));
+                    m0 = _mm_or_si128(m0, _mm_and_si128(_mm_cmpgt_epi8(x1, v0), _mm_cmpgt_epi8(x2, v0)));
+                    m1 = _mm_or_si128(m1, _mm_and_si128(_mm_cmpgt_epi8(v1, x1), _mm_cmpgt_epi8(v1, x2)));
+                    m0 = _mm_or_si128(m0, _mm_and_si128(_mm_cmpgt_epi8(x2, v0), _mm_cmpgt_epi8(x3, v0)));
+                    m1 = _mm_or_si128(m1, _mm_and_si128(_mm_cmpgt_epi8(v1, x2), _mm_cmpgt_epi8(v1, x3)));
+                    m0 = _mm_or_si128(m0, _mm_and_si128(_mm_cmpgt_epi8(x3, v0), _mm_cmpgt_epi8(x0, v0)));
+                    m1 = _mm_or_si128(m1, _mm_and_si128(_mm_cmpgt_epi8(v1, x3), _mm_cmpgt_epi8(v1, x0)));
+                    if (_mm_movemask_epi8(_mm_or_si128(m0, m1)) == 0) continue;      // no 9-arc can exist in these 16 pixels
+                    __m128i c0 = _mm_setzero_si128(), c1 = c0, max0 = c0, max1 = c0;
+                    for (int k = 0; k < 25; k++) {
+                        const __m128i x = _mm_xor_si128(_mm_loadu_si128((const __m128i*)(q + ofs[k & 15])), delta);
+                        m0 = _mm_cmpgt_epi8(x, v0);
+                        m1 = _mm_cmpgt_epi8(v1, x);
+                        c0 = _mm_and_si128(_mm_sub_epi8(c0, m0), m0);
+                        c1 = _mm_and_si128(_mm_sub_epi8(c1, m1), m1);
+                        max0 = _mm_max_epu8(max0, c0);
+                        max1 = _mm_max_epu8(max1, c1);
+                    }
+                    int m = _mm_movemask_epi8(_mm_cmpgt_epi8(_mm_max_epu8(max0, max1), K8));
+                    for (int l = 0; m; l++, m >>= 1)
+                        if (m & 1) {
+                            cornerpos[ncorners++] = j + l;
+                            if (nonmax) curr[j + l] = (uint8_t)cornerScore9_simd(q + l, ofs);
+                        }
+                }
+            }
+#endif
+            for (; j < w - 3; j++) {
                 if (isCorner9(ptr + j, ofs, threshold)) {
                     cornerpos[ncorners++] = j;
                     if (nonmax) curr[j] = (uint8_t)cornerScore9(ptr + j, ofs, threshold);

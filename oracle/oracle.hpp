@@ -46,6 +46,7 @@ void gaussianBlur7x7InPlace(uint8_t* roi, int w, int h, int step, int variant);
 // Isolated blur with computed reflect-101 border (used to validate the in-place claim).
 void gaussianBlur7x7(const uint8_t* src, int w, int h, int sstep, uint8_t* dst, int dstep, int variant);
 // cv::FAST(img, kps, threshold, nonmax=true), TYPE_9_16
+extern bool g_fast_scalar_only;
 void FAST9_16(const uint8_t* img, int w, int h, int step, int threshold, bool nonmax, std::vector<KeyPoint>& out);
 // cv::KeyPointsFilter::retainBest
 void retainBest(std::vector<KeyPoint>& kps, int n, int variant);

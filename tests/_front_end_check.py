@@ -46,12 +46,10 @@ def smoke_check(oracle, device=0, batch=3):
     fe = TrackingFrontEnd(batch=batch, device=device)
     res = []
     for s in range(2):
-        fe.images.copy_(torch.from_numpy(frames[s * batch:(s + 1) * batch]))
+        fe.load_host_frames(frames[s * batch:(s + 1) * batch])
         fe.step_device()
         fe.sync()
-        torch.cuda.synchronize()
-        res.append([t.cpu().numpy().copy() for t in (fe.kps[1:], fe.desc[1:], fe.counts[1:], fe.m12, fe.nmatch, fe.sel_idx,
-                                                      fe.sel_ld, fe.sel_n)])
+        res.append([t.cpu().numpy().copy() for t in (fe.kps, fe.desc, fe.counts, fe.m12, fe.nmatch, fe.sel_idx, fe.sel_ld, fe.sel_n)])
     exp = cpu_front_end(oracle, frames, None, fe.world_h, fe.score_h, fe.xv_h, fe.sigma2_h, fe.k, fe.sample_scale)
     from gf_orb_slam_b200._lib import KP_DTYPE
     nmatched = 0

@@ -218,29 +218,50 @@ def test_empty_and_ragged(orc, seq_frames):
     assert np.array_equal(m.SearchByProjection(F2, mps, 1.0, fmp, fsc), [0, 0, 0]) and (fmp == -1).all()
 
 
-def test_allpairs_top2():
+def _allpairs_ref(q, db, base):
+    lut = np.array([bin(i).count("1") for i in range(256)], np.int32)
+    out = np.full((len(q), 2), -1, np.int64)                    # ~0ull = "no such row"
+    for s in range(0, len(q), 64):
+        d = lut[q[s:s + 64, None, :] ^ db[None, :, :]].sum(-1)
+        key = d.astype(np.int64) * (1 << 32) + (np.arange(len(db), dtype=np.int64) + base)[None, :]
+        part = np.sort(key, axis=1)[:, :2]
+        out[s:s + 64, :part.shape[1]] = part
+    return out
+
+
+@pytest.mark.parametrize("kernel,nq,ndb,splits", [("tc", 777, 20011, None), ("popc", 777, 20011, None), ("tc", 777, 20011, 1),
+                                                  ("tc", 1, 1, None), ("tc", 3, 2, None), ("tc", 130, 255, None),
+                                                  ("tc", 128, 256, None), ("tc", 129, 257, 2), ("tc", 2000, 70013, None),
+                                                  ("tc", 300, 9000, 3)])
+def test_allpairs_top2(kernel, nq, ndb, splits, monkeypatch):
+    """config 5 brute force: tensor-core kernel (tcgen05 kind::i8, default) and integer-pipe kernel (GFORB_ALLPAIRS=popc)
+    against numpy, packed (dist << 32 | row) keys bit for bit incl. ties (lower row wins), ragged tails, tiny inputs,
+    one CTA walking many tiles (splits = 1: every pipeline stage wraps) and the shard merge"""
     import torch
     from gf_orb_slam_b200 import ORBmatcher
-    rng = np.random.default_rng(9)
-    nq, ndb = 777, 20011
+    monkeypatch.setenv("GFORB_ALLPAIRS", kernel)
+    if splits:
+        monkeypatch.setenv("GFORB_ALLPAIRS_SPLITS", str(splits))
+    rng = np.random.default_rng(9 + nq)
     q = rng.integers(0, 256, (nq, 32), dtype=np.uint8)
     db = rng.integers(0, 256, (ndb, 32), dtype=np.uint8)
-    db[100] = q[5]; db[9000] = q[5]; db[20010] = q[776]        # exact hits + a tie (lower index must win)
+    if ndb > 9000:
+        db[100] = q[5]; db[9000] = q[5]; db[ndb - 1] = q[nq - 1]        # exact hits + a tie (lower index must win)
+        db[300] = ~q[7]                                                  # distance 256
+    if ndb > 600:
+        db[512:520] = db[40]                                             # eight equal rows across a tile boundary region
     m = ORBmatcher(max_batch=1)
-    keys = m.AllPairsTop2(torch.from_numpy(q).cuda(), torch.from_numpy(db).cuda(), idx_base=1000).cpu().numpy()
-    lut = np.array([bin(i).count("1") for i in range(256)], np.int32)
-    for s in range(0, nq, 64):
-        d = lut[q[s:s + 64, None, :] ^ db[None, :, :]].sum(-1)
-        key = d.astype(np.int64) * (1 << 32) + (np.arange(ndb, dtype=np.int64) + 1000)[None, :]
-        part = np.sort(key, axis=1)[:, :2]
-        assert np.array_equal(keys[s:s + 64], part), s
-    assert keys[5, 0] == 1100 and keys[5, 1] == 10000 and keys[776, 0] == 21010
-    # shard merge: two half-shards merged == the full result
-    h = ndb // 2
     qd, dd = torch.from_numpy(q).cuda(), torch.from_numpy(db).cuda()
-    k0 = m.AllPairsTop2(qd, dd[:h], idx_base=1000).clone(); k1 = m.AllPairsTop2(qd, dd[h:], idx_base=1000 + h).clone()
-    merged = m.Top2Merge(torch.stack([k0, k1])).cpu().numpy()
-    assert np.array_equal(merged, keys)
+    keys = m.AllPairsTop2(qd, dd, idx_base=1000).cpu().numpy().astype(np.int64)
+    exp = _allpairs_ref(q, db, 1000)
+    assert np.array_equal(keys, exp)
+    if ndb > 9000:
+        assert keys[5, 0] == 1100 and keys[5, 1] == 10000 and keys[nq - 1, 0] == 1000 + ndb - 1
+    if ndb >= 4:
+        h = ndb // 2                                                     # shard merge: two half-shards == the full result
+        k0 = m.AllPairsTop2(qd, dd[:h], idx_base=1000).clone(); k1 = m.AllPairsTop2(qd, dd[h:], idx_base=1000 + h).clone()
+        merged = m.Top2Merge(torch.stack([k0, k1])).cpu().numpy().astype(np.int64)
+        assert np.array_equal(merged, exp)
 
 
 def test_is_in_frustum(orc):

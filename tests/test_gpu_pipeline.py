@@ -14,23 +14,28 @@ pytestmark = pytest.mark.gpu
 W, H, NF, K = 752, 480, 1000, 100
 
 
-def _run(frames, batch, lanes=1):
-    """all frames through the front end in steps of `batch`; returns per-frame numpy results"""
+def _run(frames, batch, host=False):
+    """all frames through the front end in steps of `batch`; returns per-frame numpy results.  host=True: through
+    gforb_frontend_step_host (pinned host frames in, results copied out by the library) instead of device-resident frames"""
     import torch
-    from gf_orb_slam_b200.pipeline import LanedFrontEnd
-    fe = LanedFrontEnd(W, H, NF, batch, lanes=lanes, n_good=K)
-    n = batch // lanes
+    from gf_orb_slam_b200.pipeline import TrackingFrontEnd
+    fe = TrackingFrontEnd(W, H, NF, batch, n_good=K)
     out = []
     for s in range(0, frames.shape[0], batch):
-        fe.load_host_frames(frames[s:s + batch])
-        fe.step_device()
-        fe.sync()
-        torch.cuda.synchronize()
-        for j, ln in enumerate(fe.lane):
-            res = [t.cpu().numpy().copy() for t in (ln.kps[1:], ln.desc[1:], ln.counts[1:], ln.m12, ln.nmatch, ln.sel_idx,
-                                                    ln.sel_ld, ln.sel_n)]
-            for b in range(n):
-                out.append(tuple(r[b] for r in res))
+        if host:
+            fe.h_images.copy_(torch.from_numpy(frames[s:s + batch]))
+            fe.step_host()
+            fe.sync()
+            res = [t.numpy().copy() for t in (fe.h_kps, fe.h_desc, fe.h_counts, fe.h_m12, fe.h_nmatch, fe.h_sel_idx, fe.h_sel_ld,
+                                              fe.h_sel_n)]
+        else:
+            fe.load_host_frames(frames[s:s + batch])
+            fe.step_device()
+            fe.sync()
+            res = [t.cpu().numpy().copy() for t in (fe.kps, fe.desc, fe.counts, fe.m12, fe.nmatch, fe.sel_idx, fe.sel_ld, fe.sel_n)]
+        for b in range(batch):
+            out.append(tuple(r[b] for r in res))
+    fe.close()
     return out
 
 
@@ -72,12 +77,13 @@ def test_full_size_invariants(full):
             assert (np.diff(sld[:int(sn)]) >= 0).all()                                    # log det grows with every pick
 
 
-def test_batch_size_and_lanes_do_not_change_results(full):
-    """the same 256 frames in 4 steps of 64 (1-frame halo between steps) and in 2 lanes give the same bytes"""
+def test_batch_size_and_host_path_do_not_change_results(full):
+    """the same 256 frames in 4 steps of 64 (1-frame halo between steps) and through the host-buffer entry point
+    (gforb_frontend_step_host: H2D / D2H inside the library, steps pipelined) give the same bytes"""
     frames, res = full
     ref = _sha(res)
     assert _sha(_run(frames, 64)) == ref
-    assert _sha(_run(frames, 256, lanes=2)) == ref
+    assert _sha(_run(frames, 64, host=True)) == ref
     assert _sha(_run(frames, 256)) == ref                                                 # and the run is deterministic
 
 
@@ -145,3 +151,52 @@ def test_selection_variants_agree(mtd, k):
         for b in range(B):
             c = int(o[2][b])
             assert np.array_equal(o[0][b, :c], outs[0][0][b, :c]) and np.array_equal(o[1][b, :c], outs[0][1][b, :c])
+
+
+def test_cpp_caller_through_the_c_abi(tmp_path):
+    """tests/cpp/frontend_cli.cpp -- a plain C++ program over include/gforb.h (cudaHostAlloc'ed frames in, host results
+    out, two staging sets, steps enqueued back to back) -- delivers the same bytes as the Python-driven front end."""
+    import json
+    import subprocess
+    import torch
+    from gf_orb_slam_b200._lib import KP_DTYPE
+    from gf_orb_slam_b200.pipeline import TrackingFrontEnd
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = os.path.join(root, "tests", "cpp", "frontend_cli.bin")
+    assert os.path.exists(exe), "run __graft_entry__.build()"
+    B, steps = 32, 3
+    frames = synth.Sequence(W, H).frames(0, 2 * B)
+    fe = TrackingFrontEnd(W, H, NF, B, n_good=K)
+    (tmp_path / "frames.bin").write_bytes(frames.tobytes())
+    (tmp_path / "map.bin").write_bytes(fe.world_h.tobytes() + fe.score_h.tobytes() + np.ascontiguousarray(fe.xv_h, np.float64).tobytes()
+                                       + np.ascontiguousarray(fe.sigma2_h, np.float32).tobytes())
+    r = subprocess.run([exe, str(tmp_path / "frames.bin"), str(tmp_path / "map.bin"), str(W), str(H), str(NF), str(B), str(K),
+                        repr(fe.sample_scale), str(steps), str(tmp_path / "out.bin")], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    info = json.loads(r.stdout.strip().splitlines()[-1])
+    assert info["frames_per_s"] > 0 and info["keypoints_last_step"] > 0
+    for s in range(steps + 1):                                   # the same step sequence (warm-up step 0 + `steps`)
+        idx = [(s * B + b) % (2 * B) for b in range(B)]
+        fe.h_images.copy_(torch.from_numpy(frames[idx]))
+        fe.step_host()
+        fe.sync()
+    raw = (tmp_path / "out.bin").read_bytes()
+    off = 0
+
+    def take(dtype, shape):
+        nonlocal off
+        n = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        a = np.frombuffer(raw, dtype, int(np.prod(shape)), off).reshape(shape)
+        off += n
+        return a
+    kps = take(KP_DTYPE, (B, NF)); desc = take(np.uint8, (B, NF, 32)); cnt = take(np.int32, (B,)); m12 = take(np.int32, (B, NF))
+    nm = take(np.int32, (B,)); gi = take(np.int32, (B, K)); gl = take(np.float64, (B, K)); gn = take(np.int32, (B,))
+    assert off == len(raw)
+    assert np.array_equal(cnt, fe.h_counts.numpy()) and np.array_equal(nm, fe.h_nmatch.numpy()) and np.array_equal(gn, fe.h_sel_n.numpy())
+    hk = fe.h_kps.numpy().view(np.int32)
+    for b in range(B):
+        c = int(cnt[b])
+        assert kps[b, :c].tobytes() == hk[b, :c].tobytes() and np.array_equal(desc[b, :c], fe.h_desc.numpy()[b, :c])
+        assert np.array_equal(m12[b], fe.h_m12.numpy()[b])
+        assert np.array_equal(gi[b, :gn[b]], fe.h_sel_idx.numpy()[b, :gn[b]]) and np.array_equal(gl[b, :gn[b]], fe.h_sel_ld.numpy()[b, :gn[b]])
+    fe.close()
