@@ -27,7 +27,7 @@ namespace gforb {
 
 static const int GRID_COLS = 64, GRID_ROWS = 48, GRID_CELLS = GRID_COLS * GRID_ROWS;
 static const int TH_HIGH = 100, TH_LOW = 50, HISTO_LENGTH = 30;
-enum { M_INIT = 0, M_WINDOW = 1, M_MAP = 2, M_LAST = 3, M_AREA = 4 };
+enum { M_INIT = 0, M_WINDOW = 1, M_MAP = 2, M_LAST = 3, M_AREA = 4, M_PROJ2 = 5 };
 
 struct FrameDev {
     const GforbKeyPoint* kps;
@@ -120,6 +120,7 @@ struct QParams {
     float thGood;                 // MAP / LAST, SearchByProjection_GoodFeature: window factor of the good features
     int goodMode;                 // 1: good features (MAP: mpFlags bit2, LAST: srcGood) use thGood, the rest th (= th_rest)
     const uint8_t* srcGood;       // LAST + goodMode: batch x src.stride
+    const int32_t* tgtMp0;        // PROJ2: F2.mvpMapPoints (batch x T.stride) = spMapPointsAlreadyFound
     const float *mpU, *mpV, *mpCos;     // MAP
     const int32_t* mpLevel;
     const uint8_t *mpFlags, *mpDesc;
@@ -272,6 +273,36 @@ __global__ void __launch_bounds__(128) k_candidates(const QParams P, const Frame
             minL = oct - 1; maxL = oct + 1;
         }
         qdp = P.src.desc + i * 32;
+    } else if (MODE == M_PROJ2) {
+        // SearchByProjection(F1, F2, windowSize, ...) (src/ORBmatcher.cc:1089-1168): F1 map points not yet in F2, projected
+        // with F2's pose; no bounds / depth test; fixed pixel window, same level
+        const size_t i = (size_t)b * P.src.stride + q;
+        const int id = P.srcMp[i];
+        if (id < 0) active = false;
+        if (active) {                                     // spMapPointsAlreadyFound.count(pMP1) (:1092, :1106)
+            const int n2 = min(T.counts[b], T.stride);
+            bool found = false;
+            for (int t = lane; t < n2; t += 32) found |= P.tgtMp0[(size_t)b * T.stride + t] == id;
+            if (__any_sync(0xffffffffu, found)) active = false;
+        }
+        if (active) {
+            const float* X = P.srcWorld + i * 3;
+            const float* Tm = P.Tcw + (size_t)b * 16;
+            float xc3[3];
+#pragma unroll
+            for (int rw = 0; rw < 3; rw++) {
+                double s = (double)Tm[rw * 4 + 0] * (double)X[0] + (double)Tm[rw * 4 + 1] * (double)X[1] +
+                           (double)Tm[rw * 4 + 2] * (double)X[2];
+                xc3[rw] = (float)s + Tm[rw * 4 + 3];
+            }
+            const float invzc = (float)(1.0 / (double)xc3[2]);
+            x = P.fx * xc3[0] * invzc + P.cx;
+            y = P.fy * xc3[1] * invzc + P.cy;
+            r = P.window;
+            minL = maxL = P.src.kps[i].octave;
+            if (!(x == x) || !(y == y) || fabsf(x) > 1e30f || fabsf(y) > 1e30f) active = false;   // z = 0: no cell range exists
+        }
+        qdp = P.src.desc + i * 32;
     } else {
         x = P.ax[q]; y = P.ay[q]; r = P.ar[q]; minL = P.aMin[q]; maxL = P.aMax[q];
     }
@@ -342,7 +373,7 @@ __global__ void __launch_bounds__(32) k_resolve(const RParams R) {
     const int Q = min(R.qCounts[b], R.maxQ);
     const size_t tOff = (size_t)b * R.tgt.stride, sOff = (size_t)b * R.src.stride;
     for (int i = lane; i < N2; i += 32) {
-        if (MODE == M_MAP || MODE == M_LAST) state[i] = R.tgtMp[tOff + i];
+        if (MODE == M_MAP || MODE == M_LAST || MODE == M_PROJ2) state[i] = R.tgtMp[tOff + i];
         else if (MODE == M_WINDOW) state[i] = -1;
         else state[i] = INT_MAX;
         owner[i] = -1;
@@ -384,7 +415,7 @@ __global__ void __launch_bounds__(32) k_resolve(const RParams R) {
                     }
                 }
                 if (MODE == M_INIT) acc = best <= TH_LOW && (float)best < (float)best2 * R.nnratio;
-                else if (MODE == M_WINDOW) acc = (float)best <= (float)best2 * R.nnratio && best <= TH_HIGH;
+                else if (MODE == M_WINDOW || MODE == M_PROJ2) acc = (float)best <= (float)best2 * R.nnratio && best <= TH_HIGH;
                 else if (MODE == M_LAST) acc = best <= TH_HIGH;
                 else acc = best <= TH_HIGH && !(bl == bl2 && (float)best > R.nnratio * (float)best2);
                 if (bi < 0) acc = false;
@@ -408,6 +439,11 @@ __global__ void __launch_bounds__(32) k_resolve(const RParams R) {
                         state[bi] = q;
                         R.tgtMp[tOff + bi] = q;
                         R.tgtScore[tOff + bi] = best;
+                    } else if (MODE == M_PROJ2) {
+                        const int id = R.srcMp[sOff + q];
+                        state[bi] = id;
+                        R.tgtMp[tOff + bi] = id;                                 // vpMapPointMatches2[bestIdx2] = pMP1
+                        R.tgtScore[tOff + bi] = best;                            // F2.mvpMatchScore[bestIdx2] (:1158)
                     } else if (MODE == M_LAST) {
                         const int id = R.srcMp[sOff + q];
                         state[bi] = id;
@@ -473,7 +509,7 @@ __global__ void __launch_bounds__(32) k_resolve(const RParams R) {
             }
         }
         total = __reduce_add_sync(full, total);
-    } else if (MODE == M_MAP) {
+    } else if (MODE == M_MAP || MODE == M_PROJ2) {
         total = __reduce_add_sync(full, accepted);
     } else {
         int removed = 0;
@@ -1291,6 +1327,42 @@ int gforb_window_search(GforbMatcher* M, const GforbFrameSet* F1, const GforbFra
     R.maxKp = M->cfg.max_keypoints; R.qCounts = S.counts; R.srcMp = P.srcMp; R.nnratio = nnratio;
     R.checkOri = check_orientation; R.tgtMp = dM2; R.nmatches = dN; R.rotBinQ = M->d_rotBinQ;
     run_resolve<M_WINDOW>(M, c, R, batch);
+    return end_call(M, c, flags);
+}
+
+int gforb_search_by_projection_window(GforbMatcher* M, const GforbFrameSet* F1, const GforbFrameSet* F2, int batch,
+                                      const int32_t* f1_mappoints, const float* f1_world, const float* Tcw2, float fx, float fy,
+                                      float cx, float cy, int window_size, float nnratio, int32_t* matches2, int32_t* f2_score,
+                                      int32_t* nmatches, int flags, void* stream) {
+    Ctx c;
+    int rc = begin_call(M, batch, flags, stream, c);
+    if (rc) return rc;
+    if ((rc = check_frames(M, F1)) || (rc = check_frames(M, F2))) return rc;
+    if (!f1_mappoints || !f1_world || !Tcw2 || !matches2 || !f2_score || !nmatches) return GFORB_ERR_ARG;
+    if (F1->kp_stride > M->cfg.max_queries) return GFORB_ERR_CAPACITY;
+    if (batch == 0) return GFORB_OK;
+    FrameDev S = c.frame(F1, batch), T = c.frame(F2, batch);
+    GridGeom G = geom_of(F2);
+    QParams P;
+    memset(&P, 0, sizeof(P));
+    fill_scale(M, P);
+    P.src = S; P.srcMp = c.in(f1_mappoints, (size_t)batch * F1->kp_stride);
+    P.srcWorld = c.in(f1_world, (size_t)batch * F1->kp_stride * 3);
+    P.Tcw = c.in(Tcw2, (size_t)batch * 16);
+    P.fx = fx; P.fy = fy; P.cx = cx; P.cy = cy; P.window = (float)window_size;
+    int32_t* dM2 = c.out(matches2, (size_t)batch * F2->kp_stride, true);       // in: F2.mvpMapPoints
+    int32_t* dSc = c.out(f2_score, (size_t)batch * F2->kp_stride, true);
+    int32_t* dN = c.out(nmatches, (size_t)batch, false);
+    if (c.rc) return c.rc;
+    P.tgtMp0 = dM2;            // read by k_candidates before k_resolve (same stream) starts to write it
+    build_grid(M, c, T, G, batch);
+    run_candidates<M_PROJ2>(M, c, P, T, G, batch, F1->kp_stride);
+    RParams R;
+    memset(&R, 0, sizeof(R));
+    R.src = S; R.tgt = T; R.pool = M->d_pool; R.poolCap = M->poolCap; R.qMeta = M->d_qMeta; R.maxQ = M->cfg.max_queries;
+    R.maxKp = M->cfg.max_keypoints; R.qCounts = S.counts; R.srcMp = P.srcMp; R.nnratio = nnratio;
+    R.tgtMp = dM2; R.tgtScore = dSc; R.nmatches = dN; R.rotBinQ = M->d_rotBinQ;
+    run_resolve<M_PROJ2>(M, c, R, batch);
     return end_call(M, c, flags);
 }
 

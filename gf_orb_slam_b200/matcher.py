@@ -286,6 +286,26 @@ class ORBmatcher:
                                              C.c_void_p(stream or 0)), "gforb_window_search")
         return nm, m2
 
+    # -- int SearchByProjection(Frame &F1, Frame &F2, int windowSize, vector<MapPoint*> &vpMapPointMatches2)
+    def SearchByProjectionWindow(self, F1: Frames, F2: Frames, f1_mappoints, f1_world, Tcw2, K, windowSize, matches2, f2_score, *,
+                                 nmatches=None, stream=None, sync=True):
+        """src/ORBmatcher.cc:1089-1168.  matches2 (B, F2.stride) int32: in = F2.mvpMapPoints, out = vpMapPointMatches2;
+        f2_score: F2.mvpMatchScore, updated in place."""
+        out_dev = is_device(matches2)
+        if nmatches is None:
+            if out_dev:
+                import torch
+                nmatches = torch.empty(F2.batch, dtype=torch.int32, device=matches2.device)
+            else:
+                nmatches = np.empty(F2.batch, np.int32)
+        fx, fy, cx, cy = [float(v) for v in K]
+        a, b = F1.cstruct(), F2.cstruct()
+        check(_lib.lib().gforb_search_by_projection_window(
+            self._h, C.byref(a), C.byref(b), F1.batch, ptr(f1_mappoints), ptr(f1_world), ptr(Tcw2), fx, fy, cx, cy, int(windowSize),
+            self.mfNNratio, ptr(matches2), ptr(f2_score), ptr(nmatches), self._flags(F1.device, out_dev, sync),
+            C.c_void_p(stream or 0)), "gforb_search_by_projection_window")
+        return nmatches
+
     # -- all-pairs top-2 against a database shard resident in HBM (torch CUDA uint8 tensors)
     def AllPairsTop2(self, queries, db, idx_base=0, *, out=None, stream=None, sync=True):
         import torch

@@ -225,6 +225,17 @@ int gforb_window_search(GforbMatcher* h, const GforbFrameSet* F1, const GforbFra
                         float nnratio, int check_orientation, int32_t* matches2, int32_t* nmatches, int flags,
                         void* stream);
 
+/* ORBmatcher::SearchByProjection(Frame& F1, Frame& F2, int windowSize, vector<MapPoint*>& vpMapPointMatches2)
+ * (src/ORBmatcher.cc:1089-1168; Tracking::TrackPreviousFrame, src/Tracking.cc:1373-1376): F1 map points that F2 does not
+ * hold yet, projected with F2's pose into a fixed pixel window on the same pyramid level; ratio test
+ * best <= second * nnratio and best <= TH_HIGH.  f1_mappoints: batch x F1.kp_stride ids (>= 0: non-NULL, not bad);
+ * f1_world: batch x F1.kp_stride x 3 (MapPoint::GetWorldPos); Tcw2: batch x 16 row-major (F2.mTcw);
+ * matches2: in/out, batch x F2.kp_stride, in = F2.mvpMapPoints, out = vpMapPointMatches2; f2_score: in/out F2.mvpMatchScore. */
+int gforb_search_by_projection_window(GforbMatcher* h, const GforbFrameSet* F1, const GforbFrameSet* F2, int batch,
+                                      const int32_t* f1_mappoints, const float* f1_world, const float* Tcw2, float fx, float fy,
+                                      float cx, float cy, int window_size, float nnratio, int32_t* matches2, int32_t* f2_score,
+                                      int32_t* nmatches, int flags, void* stream);
+
 /* Batched all-pairs Hamming top-2 of n_q query descriptors against one database shard of n_db descriptors
  * (BASELINE.json config 5; the reference's brute-force analogue is the DescriptorDistance loop of
  * MapPoint::ComputeDistinctiveDescriptors, src/MapPoint.cc:225-250).  out: n_q x 2 packed keys

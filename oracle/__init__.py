@@ -266,6 +266,16 @@ def search_for_initialization(F1: Frame, F2: Frame, prev_matched: np.ndarray, wi
     return n, m12, pm
 
 
+def search_by_projection_window(F1: Frame, F2: Frame, f1_world: np.ndarray, window: int, nnratio=0.9):
+    """ORBmatcher::SearchByProjection(F1, F2, windowSize, vpMapPointMatches2) (src/ORBmatcher.cc:1089-1168); F1 / F2 carry
+    their map-point ids (set_mappoints), F2 its camera and pose (set_camera).  Returns (nmatches, matches2); F2's match
+    scores are updated in place (F2.matches())."""
+    w = np.ascontiguousarray(f1_world, np.float32)
+    m2 = np.full(F2.N, -1, np.int32)
+    n = lib().orc_search_by_projection_window(F1.h, F2.h, _p(w), int(window), _p(m2), C.c_float(nnratio))
+    return n, m2
+
+
 def window_search(F1: Frame, F2: Frame, window: int, minL=-1, maxL=0x7FFFFFFF, nnratio=0.9, checkOri=True):
     m2 = np.empty(F2.N, np.int32)
     n = lib().orc_window_search(F1.h, F2.h, window, _p(m2), minL, maxL, C.c_float(nnratio), int(checkOri))

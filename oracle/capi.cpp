@@ -9,6 +9,20 @@
 
 using namespace oracle;
 
+// rand() of a seeded selection is a thread-local random_r (the same glibc TYPE_3 generator): callers may run selections on
+// several threads (tests, front_end_batch) without racing on the process-global rand() state.
+#include <stdlib.h>
+namespace {
+thread_local struct random_data tl_rd;
+thread_local char tl_state[128];
+thread_local bool tl_init = false;
+int tl_rand() { int32_t r; random_r(&tl_rd, &r); return (int)r; }
+void tl_srand(unsigned seed) {
+    if (!tl_init) { memset(&tl_rd, 0, sizeof(tl_rd)); initstate_r(seed, tl_state, sizeof(tl_state), &tl_rd); tl_init = true; }
+    srandom_r(seed, &tl_rd);
+}
+}  // namespace
+
 extern "C" {
 
 // ------------------------------------------------------------------ primitives
@@ -170,6 +184,13 @@ int orc_search_for_initialization(void* f1, void* f2, float* prevMatched, int* m
     memcpy(matches12, m12.data(), sizeof(int) * m12.size());
     return n;
 }
+int orc_search_by_projection_window(void* f1, void* f2, const float* f1World, int windowSize, int* matches2, float nnratio) {
+    ORBmatcher m(nnratio, true);
+    std::vector<int> m2;
+    int n = m.SearchByProjection(*(const Frame*)f1, *(Frame*)f2, f1World, windowSize, m2);
+    memcpy(matches2, m2.data(), sizeof(int) * m2.size());
+    return n;
+}
 int orc_window_search(void* f1, void* f2, int windowSize, int* matches2, int minLevel, int maxLevel, float nnratio, int checkOri) {
     ORBmatcher m(nnratio, checkOri != 0);
     std::vector<int> m2;
@@ -228,7 +249,7 @@ int orc_obs_select(const double* blocks, const double* obsScore, int n, int k, i
         g.idx = i; g.obs_score = obsScore ? obsScore[i] : 1.0; g.selected = false; g.upper_bound = 0;
         memcpy(g.obs_block, blocks + (size_t)49 * i, sizeof(g.obs_block));
     }
-    if (seed >= 0) srand((unsigned)seed);
+    if (seed >= 0) { tl_srand((unsigned)seed); ob.rand_fn = &tl_rand; }      // seed < 0: the process-global rand() as it stands
     std::vector<GoodPoint> sub;
     if (mtd == 1) ob.maxVolSelection_BaselineGreedy(&sub, k);
     else if (mtd == 2) ob.maxVolSelection_LazierGreedy(0, n, &sub, k, sampleScale, 1e30);
@@ -295,17 +316,6 @@ int orc_active_match(void* fp, int M, const float* u, const float* v, const int*
 // frames split into contiguous chunks over `threads` std::threads (one extractor per thread, 1-frame halo per chunk:
 // the reference extractor/matcher are single-threaded per frame).  rand() is replaced by a thread-local random_r
 // (same glibc TYPE_3 generator, seed 1 per frame) so threads neither race nor contend on glibc's lock.
-#include <stdlib.h>
-namespace {
-thread_local struct random_data tl_rd;
-thread_local char tl_state[128];
-thread_local bool tl_init = false;
-int tl_rand() { int32_t r; random_r(&tl_rd, &r); return (int)r; }
-void tl_srand(unsigned seed) {
-    if (!tl_init) { memset(&tl_rd, 0, sizeof(tl_rd)); initstate_r(seed, tl_state, sizeof(tl_state), &tl_rd); tl_init = true; }
-    srandom_r(seed, &tl_rd);
-}
-}  // namespace
 
 extern "C" int orc_front_end_batch(const uint8_t* imgs, int w, int ht, int nframes, int threads, int nfeatures,
                                    const float* world, const int* score, const double* xv13, const float* sigma2, int k,

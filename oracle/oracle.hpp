@@ -136,6 +136,7 @@ public:
     int SearchByProjection(Frame& Cur, const Frame& Last, const float* lastWorldPos /*N x 3*/, float th);
     int SearchForInitialization(const Frame& F1, const Frame& F2, std::vector<float>& vbPrevMatched /*N1 x 2*/,
                                 std::vector<int>& vnMatches12, int windowSize);
+    int SearchByProjection(const Frame& F1, Frame& F2, const float* f1World /*N1 x 3*/, int windowSize, std::vector<int>& vpMapPointMatches2);
     int WindowSearch(const Frame& F1, const Frame& F2, int windowSize, std::vector<int>& vpMapPointMatches2,
                      int minScaleLevel = -1, int maxScaleLevel = 0x7fffffff);
     static void ComputeThreeMaxima(const std::vector<int>* histo, int L, int& ind1, int& ind2, int& ind3);

@@ -3,6 +3,7 @@
 // 979-1086, 1172-1287, 2081-2202, 2338-2400; include/ORBmatcher.h:71-145).
 // MapPoint* / NULL is flattened to an int id / -1.
 #include "oracle.hpp"
+#include <set>
 #include <algorithm>
 #include <climits>
 #include <cmath>
@@ -419,6 +420,48 @@ int ORBmatcher::WindowSearch(const Frame& F1, const Frame& F2, int windowSize, s
                     vnMatches21[idx] = -1;
                     nmatches--;
                 }
+    }
+    return nmatches;
+}
+
+// src/ORBmatcher.cc:1089-1168: SearchByProjection(Frame& F1, Frame& F2, int windowSize, vector<MapPoint*>& vpMapPointMatches2)
+// (TrackPreviousFrame, src/Tracking.cc:1373-1376).  f1World = MapPoint::GetWorldPos of F1.mvpMapPoints[i1]; ids >= 0 are
+// non-NULL, non-bad map points.  F2.mvpMapPoints is only read; F2.mvpMatchScore is written.
+int ORBmatcher::SearchByProjection(const Frame& F1, Frame& F2, const float* f1World, int windowSize, std::vector<int>& vpMapPointMatches2) {
+    vpMapPointMatches2 = F2.mvpMapPoints;
+    std::set<int> spMapPointsAlreadyFound(vpMapPointMatches2.begin(), vpMapPointMatches2.end());
+    int nmatches = 0;
+    const float* T = F2.mTcw;
+    for (size_t i1 = 0; i1 < F1.mvpMapPoints.size(); i1++) {
+        const int pMP1 = F1.mvpMapPoints[i1];
+        if (pMP1 < 0) continue;
+        if (spMapPointsAlreadyFound.count(pMP1)) continue;
+        const int level1 = F1.mvKeysUn[i1].octave;
+        const float* X = f1World + 3 * i1;
+        float xc3[3];                                    // Rc2w*x3Dw+tc2w: see SearchByProjection(Cur, Last) above
+        for (int r = 0; r < 3; r++) {
+            double s = (double)T[r * 4 + 0] * X[0] + (double)T[r * 4 + 1] * X[1] + (double)T[r * 4 + 2] * X[2];
+            xc3[r] = (float)s + T[r * 4 + 3];
+        }
+        const float xc2 = xc3[0], yc2 = xc3[1];
+        const float invzc2 = 1.0 / xc3[2];
+        float u2 = F2.fx * xc2 * invzc2 + F2.cx;
+        float v2 = F2.fy * yc2 * invzc2 + F2.cy;
+        std::vector<size_t> vIndices2 = F2.GetFeaturesInArea(u2, v2, windowSize, level1, level1);
+        if (vIndices2.empty()) continue;
+        const uint8_t* d1 = &F1.mDescriptors[i1 * 32];
+        int bestDist = INT_MAX, bestDist2 = INT_MAX, bestIdx2 = -1;
+        for (size_t i2 : vIndices2) {
+            if (vpMapPointMatches2[i2] >= 0) continue;
+            int dist = DescriptorDistance(d1, &F2.mDescriptors[i2 * 32]);
+            if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestIdx2 = i2; }
+            else if (dist < bestDist2) bestDist2 = dist;
+        }
+        if (static_cast<float>(bestDist) <= static_cast<float>(bestDist2) * mfNNratio && bestDist <= TH_HIGH) {
+            vpMapPointMatches2[bestIdx2] = pMP1;
+            F2.mvpMatchScore[bestIdx2] = bestDist;
+            nmatches++;
+        }
     }
     return nmatches;
 }

@@ -195,6 +195,43 @@ def test_window_search(orc, seq_frames, window, minL, maxL):
     assert nm[0] > 50
 
 
+@pytest.mark.parametrize("window,nnratio", [(15, 0.9), (50, 0.7)])
+def test_search_by_projection_window(orc, seq_frames, window, nnratio):
+    """ORBmatcher::SearchByProjection(F1, F2, windowSize, vpMapPointMatches2) (src/ORBmatcher.cc:1089-1168, TrackPreviousFrame):
+    F2 arrives with map points of its own (claimed keypoints, ids F1 must skip), matches and F2's match scores bit-exact"""
+    from gf_orb_slam_b200 import ORBmatcher, Frames
+    kps, desc, counts = seq_frames
+    B = 3
+    F1 = Frames(kps[:B], desc[:B], counts[:B], W, H)
+    F2 = Frames(kps[1:B + 1], desc[1:B + 1], counts[1:B + 1], W, H)
+    K = None
+    f1mp = np.full((B, 1000), -1, np.int32); world = np.zeros((B, 1000, 3), np.float32); Tcw = np.zeros((B, 16), np.float32)
+    m2 = np.full((B, 1000), -1, np.int32); sc = np.full((B, 1000), 999, np.int32)
+    for b in range(B):
+        n1, n2 = int(counts[b]), int(counts[b + 1])
+        u = synth.uniform01(133 + b, n1)
+        f1mp[b, :n1] = np.where(u < 0.85, 7000 + np.arange(n1), -1)
+        K, T, w = _pose_and_world(kps[b], n1, seed=70 + b, shift=(float(b) + 1.0, -2.0))
+        world[b, :n1] = w; Tcw[b] = T.reshape(16)
+        pre = synth.uniform01(233 + b, n2)
+        m2[b, :n2] = np.where(pre < 0.10, 7000 + 3 * np.arange(n2), -1)      # F2 already holds some points, some shared with F1
+    m20 = m2.copy()
+    m = ORBmatcher(nnratio, True, max_batch=B, max_keypoints=1000, max_queries=1000)
+    nm = m.SearchByProjectionWindow(F1, F2, f1mp, world, Tcw, K, window, m2, sc)
+    tot = 0
+    for b in range(B):
+        n1, n2 = int(counts[b]), int(counts[b + 1])
+        f1 = _oframe(orc, kps[b], desc[b], n1); f2 = _oframe(orc, kps[b + 1], desc[b + 1], n2)
+        f1.set_mappoints(f1mp[b, :n1]); f2.set_mappoints(m20[b, :n2])
+        f2.set_camera(*K, Tcw[b].reshape(4, 4))
+        en, e2 = orc.search_by_projection_window(f1, f2, world[b, :n1], window, nnratio)
+        _, esc = f2.matches()
+        assert nm[b] == en, (b, nm[b], en)
+        assert np.array_equal(m2[b, :n2], e2) and np.array_equal(sc[b, :n2], esc)
+        tot += en
+    assert tot > 100
+
+
 def test_empty_and_ragged(orc, seq_frames):
     """frames with zero keypoints and different counts in one batch; zero map points"""
     from gf_orb_slam_b200 import ORBmatcher, Frames, MapPoints
