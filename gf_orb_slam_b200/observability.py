@@ -139,6 +139,34 @@ class Observability:
                                           out_stride, flags, C.c_void_p(stream or 0)), "gforb_obs_select")
         return out_idx, out_logdet, out_n
 
+    def select_map_mtd3(self, blocks, obs_score, k, seed=1, num_threads=8):
+        """Selection stage of setSelction_Number(k, 3, T, vector<MapPoint*>*, out) (src/Observability.cc:1085-1163) over ONE
+        pool (n x 49 numpy blocks whose entries all have ObsScore >= 0): sample scale 6.0; pools of >= 2000 points that
+        exceed 1.2 k by more than 10 are cut into min(round(n / 1000), num_threads) ranges selected in one batched call
+        (range i draws from rand() stream seed + 1 + i), their picks are merged and the final k picked with stream `seed`."""
+        n = int(blocks.shape[0])
+        blocks = np.ascontiguousarray(blocks, np.float64).reshape(n, 49)
+        sc = np.ones(n) if obs_score is None else np.ascontiguousarray(obs_score, np.float64)
+        thread_needed = 1
+        if not (n - 1.2 * float(np.float32(k)) <= 10 or n < 2000):
+            thread_needed = min(int(np.round(np.float32(n) / np.float32(1000))), int(num_threads))
+        if thread_needed <= 1:
+            idx, _, cnt = self.select(blocks[None], sc[None], np.array([n], np.int32), k, AUTOMATIC_LAZIER, 6.0, np.array([seed], np.uint32))
+            return idx[0, :cnt[0]].copy()
+        sub = int(np.ceil(np.float32(k) / np.float32(thread_needed) * 1.2))
+        per = int(np.ceil(np.float32(n) / np.float32(thread_needed)))
+        pb = np.zeros((thread_needed, per, 49)); ps = np.full((thread_needed, per), -1.0); cnts = np.zeros(thread_needed, np.int32)
+        for i in range(thread_needed):
+            st, ed = i * per, min((i + 1) * per, n)
+            pb[i, :ed - st] = blocks[st:ed]; ps[i, :ed - st] = sc[st:ed]; cnts[i] = max(ed - st, 0)
+        seeds = (seed + 1 + np.arange(thread_needed)).astype(np.uint32)
+        idx, _, cnt = self.select(pb, ps, cnts, sub, AUTOMATIC_LAZIER, 6.0, seeds)
+        merged = np.concatenate([i * per + idx[i, :cnt[i]] for i in range(thread_needed)]).astype(np.int64)
+        m = len(merged)
+        idx2, _, cnt2 = self.select(blocks[merged][None], sc[merged][None], np.array([m], np.int32), k, AUTOMATIC_LAZIER, 6.0,
+                                    np.array([seed], np.uint32))
+        return merged[idx2[0, :cnt2[0]]].astype(np.int32)
+
     # ---- int runActiveMapMatching(Frame*, mat_type, mBaseInfoMat, th, ORBmatcher&, num_to_match, time_for_match)
     def runActiveMapMatching(self, F, mps, mat_type, base_info, th, matcher, num_to_match, *, obs_score, obs_mat, H_meas,
                              level_sigma2, frame_mappoints, match_score, seeds=None, stream=None, sync=True):

@@ -615,6 +615,54 @@ public:
         if (!runMatrixBuilding(FRAME_INFO_MATRIX, time_for_select / 2, true, false)) return false;
         return select_pool(num_good_inlier, greedy_mtd, sampleScale, mpVec, pF);
     }
+    // src/Observability.cc:1021-1247: the local-map variant.  mKineIdx = 1, runMatrixBuilding(MAP_INFO_MATRIX, check_viz),
+    // pool = map points with ObsScore >= 0 in index order (GoodPoint::idx = index into *mapPoints), fixed
+    // random_sample_scale = 6.0 (:1035).  greedy_mtd 3 with a pool of >= 2 * Greedy_Paral_TrigSz (1000) points that exceeds
+    // Greedy_Paral_RelFac (1.2) * k by more than 10 is cut into threadNeeded = min(round(pool / 1000), mNumThreads) ranges
+    // (:1085-1163): every range picks ceil(k / threadNeeded * 1.2) points by the automatic lazier greedy, the picks are
+    // concatenated and the final k are picked from them.  In the reference those ranges run on std::threads that all draw
+    // from the process-global rand() (a data race: its result depends on thread timing); here range i draws from its own
+    // stream rng_seed + 1 + i and the final pass from rng_seed -- one GPU call for all ranges, one for the final pass.
+    size_t mNumThreads = 8;                           // std::thread::hardware_concurrency() in the reference (include/Observability.h:138)
+    bool setSelction_Number(const size_t num_good_inlier, const int greedy_mtd, const double time_for_select,
+                            std::vector<MapPoint*>* mapPoints, std::vector<GoodPoint>* mpVec) {
+        if (!mapPoints || !mpVec || time_for_select <= 0) return false;   // :1026-1027
+        mKineIdx = 1;
+        mMapPoints = mapPoints;
+        const double sampleScale = 6.0;                                   // :1035
+        if (!runMatrixBuilding(MAP_INFO_MATRIX, time_for_select / 2.0, true, true)) return false;
+        std::vector<int> pool;
+        for (int i = 0; i < n_; i++) if ((*mapPoints)[i] && (*mapPoints)[i]->ObsScore >= 0) pool.push_back(i);   // :1046-1058
+        mpVec->clear();
+        const size_t np = pool.size();
+        if (np == 0) return true;
+        size_t threadNeeded = 1;
+        if (greedy_mtd == 3 && !((double)np - 1.2 * (float)num_good_inlier <= 10 || np < 2 * 1000)) {             // :1085-1092
+            threadNeeded = (size_t)std::round((float)np / 1000.f);
+            if (threadNeeded > mNumThreads) threadNeeded = mNumThreads;
+        }
+        if (threadNeeded <= 1) return select_indices(pool, num_good_inlier, greedy_mtd, sampleScale, rng_seed, mpVec);
+        const size_t numSubsetParal = (size_t)std::ceil((float)num_good_inlier / (float)threadNeeded * 1.2);      // :1110
+        const size_t numPoolParal = (size_t)std::ceil((float)np / (float)threadNeeded);                           // :1111
+        // all ranges in ONE batched call: range i = pool entries [i * numPoolParal, min((i + 1) * numPoolParal, np))
+        std::vector<double> pb(threadNeeded * numPoolParal * 49, 0.0), ps(threadNeeded * numPoolParal, -1.0);
+        std::vector<int32_t> cnt(threadNeeded), idx(threadNeeded * numPoolParal), nsel(threadNeeded);
+        std::vector<uint32_t> seeds(threadNeeded);
+        for (size_t t = 0; t < np; t++) { std::memcpy(&pb[t * 49], &blocks_[(size_t)pool[t] * 49], 49 * sizeof(double)); ps[t] = score_[pool[t]]; }
+        for (size_t i = 0; i < threadNeeded; i++) {
+            const size_t st = i * numPoolParal, ed = std::min((i + 1) * numPoolParal, np);
+            cnt[i] = (int32_t)(ed > st ? ed - st : 0);
+            seeds[i] = rng_seed + 1 + (uint32_t)i;
+        }
+        if (gforb_obs_select(h_, pb.data(), ps.data(), cnt.data(), (int)numPoolParal, (int)threadNeeded, (int)numSubsetParal, 3,
+                             sampleScale, seeds.data(), idx.data(), nullptr, nsel.data(), (int)numPoolParal, 0, nullptr) != GFORB_OK)
+            return false;
+        std::vector<int> merged;                                          // :1147-1153, parVec order
+        for (size_t i = 0; i < threadNeeded; i++)
+            for (int t = 0; t < nsel[i]; t++) merged.push_back(pool[i * numPoolParal + (size_t)idx[i * numPoolParal + t]]);
+        return select_indices(merged, num_good_inlier, 3, sampleScale, rng_seed, mpVec);
+    }
+
     // src/Observability.cc:2815-3029 on the pool built by the last runMatrixBuilding
     bool maxVolSelection_LazierGreedy(const size_t /*stIdx*/, const size_t /*edIdx*/, std::vector<GoodPoint>* subVec,
                                       const size_t mpLimit, const double sampleScale, const double /*max_time*/) {
@@ -631,6 +679,23 @@ private:
         c.fu = fu; c.fv = fv; c.nRows = nRows; c.nCols = nCols; c.Cx = Cx; c.Cy = Cy; c.k1 = k1; c.k2 = k2; c.dx = dx; c.dy = dy;
         c.max_batch = 1; c.max_points = maxPoints_; c.device = device;
         gforb_throw(gforb_obs_create(&c, &h_), "Observability: create");
+    }
+    // one selection over the pool entries `pool` (indices into the arrays of the last runMatrixBuilding), appended to *out
+    bool select_indices(const std::vector<int>& pool, size_t k, int mtd, double sampleScale, uint32_t seed, std::vector<GoodPoint>* out) {
+        const int np = (int)pool.size();
+        if (np == 0) return true;
+        if (np > maxPoints_) return false;
+        std::vector<double> pb((size_t)np * 49), ps(np), ld(std::max<size_t>(k, 1) + np);
+        for (int t = 0; t < np; t++) { std::memcpy(&pb[(size_t)t * 49], &blocks_[(size_t)pool[t] * 49], 49 * sizeof(double)); ps[t] = score_[pool[t]]; }
+        std::vector<int32_t> idx(np);
+        int32_t cnt = np, nsel = 0;
+        if (gforb_obs_select(h_, pb.data(), ps.data(), &cnt, np, 1, (int)k, mtd, sampleScale, &seed, idx.data(), ld.data(), &nsel, np, 0,
+                             nullptr) != GFORB_OK) return false;
+        for (int t = 0; t < nsel; t++) {
+            GoodPoint g; g.idx = (size_t)pool[idx[t]]; g.obs_score = ps[idx[t]]; g.selected = true; g.upper_bound = ld[t];
+            out->push_back(g);
+        }
+        return true;
     }
     bool select_pool(size_t k, int mtd, double sampleScale, std::vector<GoodPoint>* out, Frame* F) {
         if (n_ <= 0 || !out) return false;

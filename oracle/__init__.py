@@ -414,6 +414,16 @@ def select(blocks: np.ndarray, k: int, mtd: int = 2, sample_scale: float = 23.0,
     return idx[:m].copy(), ld[:m].copy()
 
 
+def select_map_mtd3(blocks: np.ndarray, k: int, seed: int = 1, num_threads: int = 8, scores=None):
+    """selection stage of the local-map setSelction_Number, greedy_mtd 3 incl. the partitioned pool (src/Observability.cc:1085-1163)"""
+    blocks = np.ascontiguousarray(blocks, np.float64)
+    n = blocks.shape[0]
+    sc = None if scores is None else np.ascontiguousarray(scores, np.float64)
+    idx = np.empty(n, np.int32)
+    m = lib().orc_obs_select_map_mtd3(_p(blocks), _p(sc), n, k, C.c_long(seed), num_threads, _p(idx))
+    return idx[:m].copy()
+
+
 def front_end_batch(imgs: np.ndarray, threads: int, world, score, xv, sigma2, k: int, sample_scale: float, window=100,
                     nnratio=0.9, cam=None):
     """extract + SearchForInitialization(prev, cur) + info blocks + lazier-greedy selection for every frame, frames

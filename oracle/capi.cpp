@@ -260,6 +260,50 @@ int orc_obs_select(const double* blocks, const double* obsScore, int n, int k, i
     return (int)sub.size();
 }
 
+// Selection stage of the local-map setSelction_Number with greedy_mtd 3 (src/Observability.cc:1085-1163): pool of n entries
+// (all with ObsScore >= 0), Greedy_Paral_TrigSz 1000, Greedy_Paral_RelFac 1.2, random_sample_scale 6.0, numThreads =
+// mNumThreads.  The reference runs the ranges on std::threads sharing the global rand() (timing dependent); this
+// restatement -- like the product -- gives range i the stream seed + 1 + i and the final pass the stream `seed`.
+int orc_obs_select_map_mtd3(const double* blocks, const double* obsScore, int n, int k, long seed, int numThreads, int* out_idx) {
+    Observability ob(1.0, 1.0, 480, 640, 320, 240, 0, 0);
+    ob.lmkSelectPool.resize(n);
+    for (int i = 0; i < n; i++) {
+        GoodPoint& g = ob.lmkSelectPool[i];
+        g.idx = i; g.obs_score = obsScore ? obsScore[i] : 1.0; g.selected = false; g.upper_bound = 0;
+        memcpy(g.obs_block, blocks + (size_t)49 * i, sizeof(g.obs_block));
+    }
+    ob.rand_fn = &tl_rand;
+    const double random_sample_scale = 6.0;
+    const size_t num_good_inlier = (size_t)k;
+    std::vector<GoodPoint> mpVec;
+    size_t threadNeeded = 1;
+    if (ob.lmkSelectPool.size() - 1.2 * float(num_good_inlier) <= 10 || ob.lmkSelectPool.size() < 2 * 1000) threadNeeded = 1;
+    else {
+        threadNeeded = static_cast<size_t>(round(float(ob.lmkSelectPool.size()) / float(1000)));
+        if (threadNeeded > (size_t)numThreads) threadNeeded = (size_t)numThreads;
+    }
+    if (threadNeeded == 1) {
+        tl_srand((unsigned)seed);
+        ob.maxVolAutomatic_LazierGreedy(0, ob.lmkSelectPool.size(), &mpVec, num_good_inlier, random_sample_scale, 1e30);
+    } else {
+        size_t numSubsetParal = static_cast<size_t>(ceil(float(num_good_inlier) / float(threadNeeded) * 1.2));
+        size_t numPoolParal = static_cast<size_t>(ceil(float(ob.lmkSelectPool.size()) / float(threadNeeded)));
+        std::vector<std::vector<GoodPoint>> parVec(threadNeeded);
+        for (size_t i = 0; i < threadNeeded; i++) {
+            tl_srand((unsigned)(seed + 1 + (long)i));
+            const size_t st = i * numPoolParal, ed = (i + 1 < threadNeeded) ? (i + 1) * numPoolParal : ob.lmkSelectPool.size();
+            ob.maxVolAutomatic_LazierGreedy(st, ed, &parVec[i], numSubsetParal, random_sample_scale, 1e30);
+        }
+        ob.lmkSelectPool.clear();
+        for (size_t i = 0; i < threadNeeded; i++)
+            for (size_t j = 0; j < parVec[i].size(); ++j) { parVec[i][j].selected = false; ob.lmkSelectPool.push_back(parVec[i][j]); }
+        tl_srand((unsigned)seed);
+        ob.maxVolAutomatic_LazierGreedy(0, ob.lmkSelectPool.size(), &mpVec, num_good_inlier, random_sample_scale, 1e30);
+    }
+    for (size_t i = 0; i < mpVec.size(); i++) out_idx[i] = (int)mpVec[i].idx;
+    return (int)mpVec.size();
+}
+
 // Frame::isInFrustum for M map points (src/Frame.cc:166-227); flags[i] bit0 <- mbTrackInView
 void orc_is_in_frustum(const float* Rcw, const float* tcw, const float* Ow, float fx, float fy, float cx, float cy, int minX,
                        int maxX, int minY, int maxY, int nlevels, float scaleFactor, int M, const float* world,

@@ -162,3 +162,21 @@ def test_selection_matches_oracle(orc, n, k, mtd, scale):
             assert np.array_equal(ld[b, :cnt[b]], el)      # north_star asks 1e-5 relative; the running log-dets are bit-equal
     if n == 1000:
         assert Observability.sample_scale_for(1000, 100, 0.1) == 23.0
+
+
+@pytest.mark.parametrize("n,k,threads", [(2600, 120, 8), (3100, 100, 2), (1500, 100, 8), (2010, 1700, 8)])
+def test_map_variant_partitioned_selection(orc, n, k, threads):
+    """setSelction_Number(k, 3, T, vector<MapPoint*>*, out) (src/Observability.cc:1021-1247): sample scale 6.0, pools of
+    >= 2 * Greedy_Paral_TrigSz points are partitioned (:1085-1163), all ranges in one batched GPU call; deletion mode
+    inside the ranges / the final pass when 2 k exceeds the pool"""
+    from gf_orb_slam_b200 import Observability
+    oo = orc.Observability(**EUROC)
+    oo.set_xv(XV); oo.predict(0.1, 1)
+    world, octave, score = _cloud(n, 77)
+    blocks, obs, _ = oo.build_map(world, np.ones(n, np.uint8), 0, (0, 752, 0, 480))
+    assert (obs == 1.0).all()
+    ob = Observability(**EUROC, max_batch=8, max_points=n)
+    got = ob.select_map_mtd3(blocks.reshape(n, 49), obs, k, seed=1, num_threads=threads)
+    exp = orc.select_map_mtd3(blocks.reshape(n, 7, 7), k, 1, threads, scores=obs)
+    assert len(exp) == min(k, n)
+    assert np.array_equal(got, exp)
