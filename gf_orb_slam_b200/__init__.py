@@ -7,3 +7,4 @@ from ._lib import KP_DTYPE, GforbError, LIB_PATH  # noqa: F401
 from .extractor import ORBextractor, FAST_SCORE, HARRIS_SCORE  # noqa: F401
 from .matcher import ORBmatcher, Frames, MapPoints  # noqa: F401
 from .observability import Observability  # noqa: F401
+from .optimizer import Optimizer  # noqa: F401

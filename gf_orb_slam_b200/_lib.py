@@ -112,6 +112,9 @@ def lib() -> C.CDLL:
         L.gforb_allpairs_top2.argtypes = [vp, vp, i32, vp, i64, i64, vp, i32, vp]
         L.gforb_top2_merge.argtypes = [vp, vp, i32, i32, vp, i32, vp]
         L.gforb_matcher_poll_error.argtypes = [vp, vp]
+        L.gforb_poseopt_create.argtypes = [i32, i32, i32, C.POINTER(vp)]
+        L.gforb_poseopt_destroy.argtypes = [vp]
+        L.gforb_pose_optimization.argtypes = [vp, vp, vp, vp, vp, vp, i32, i32, vp, i32, f32, f32, f32, f32, vp, vp, i32, vp]
         L.gforb_extractor_poll_error.argtypes = [vp, vp]
         L.gforb_obs_poll_error.argtypes = [vp, vp]
         FO = C.POINTER(FrontEndOutputs)
@@ -158,6 +161,7 @@ gforb_obs_build_info_frame gforb_obs_build_info_map gforb_obs_logdet gforb_obs_r
 gforb_obs_active_match gforb_frame_is_in_frustum gforb_frame_undistort_keypoints
 gforb_search_by_projection_good_feature gforb_search_by_projection_frames_good_feature
 gforb_mappoint_distinctive_descriptors gforb_matcher_poll_error gforb_extractor_poll_error gforb_obs_poll_error
+gforb_poseopt_create gforb_poseopt_destroy gforb_pose_optimization
 gforb_frontend_create gforb_frontend_destroy gforb_frontend_set_map gforb_frontend_step_device gforb_frontend_step_host
 gforb_frontend_sync gforb_frontend_wait_results gforb_frontend_results gforb_frontend_launches_per_step gforb_frontend_set_profiling
 gforb_frontend_stage_time""".split()

@@ -146,7 +146,7 @@ template <bool MASK>
 __device__ __forceinline__ void top2_chunk(const uint32_t (&r)[32], uint32_t invBase, int validCols, uint32_t& k1, uint32_t& k2, int& thr) {
     int m = (int)r[31];
 #pragma unroll
-    for (int j = 0; j < 31; j += 2) m = max(m, max((int)r[j], (int)r[j + 1]));
+    for (int j = 0; j < 31; j += 2) m = __vimax3_s32(m, (int)r[j], (int)r[j + 1]);      // VIMNMX3: two accumulators per issue slot
     if (MASK || m > thr) {
 #pragma unroll
         for (int j = 0; j < 32; j++) {

@@ -148,13 +148,13 @@ class Observability:
         blocks = np.ascontiguousarray(blocks, np.float64).reshape(n, 49)
         sc = np.ones(n) if obs_score is None else np.ascontiguousarray(obs_score, np.float64)
         thread_needed = 1
-        if not (n - 1.2 * float(np.float32(k)) <= 10 or n < 2000):
+        if not (n - 1.2 * float(np.float32(k)) <= 10 or n < 2000):        # (size_t - double * float) as written at :1086
             thread_needed = min(int(np.round(np.float32(n) / np.float32(1000))), int(num_threads))
         if thread_needed <= 1:
             idx, _, cnt = self.select(blocks[None], sc[None], np.array([n], np.int32), k, AUTOMATIC_LAZIER, 6.0, np.array([seed], np.uint32))
             return idx[0, :cnt[0]].copy()
-        sub = int(np.ceil(np.float32(k) / np.float32(thread_needed) * 1.2))
-        per = int(np.ceil(np.float32(n) / np.float32(thread_needed)))
+        sub = int(np.ceil(float(np.float32(k) / np.float32(thread_needed)) * 1.2))       # float division, double product (:1110)
+        per = int(np.ceil(float(np.float32(n) / np.float32(thread_needed))))
         pb = np.zeros((thread_needed, per, 49)); ps = np.full((thread_needed, per), -1.0); cnts = np.zeros(thread_needed, np.int32)
         for i in range(thread_needed):
             st, ed = i * per, min((i + 1) * per, n)

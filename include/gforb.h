@@ -334,6 +334,23 @@ int gforb_obs_active_match(GforbObs* obs, GforbMatcher* matcher, const GforbFram
                            int32_t* match_score, int32_t* nmatched, int32_t* left_idx, int32_t* left_n,
                            double* out_info, int flags, void* stream);
 
+/* ------------------------------------------------------------------------------------------------ pose optimisation
+ * Optimizer::PoseOptimization(Frame*) (src/Optimizer.cc:279-413; the step right after the matchers of this path:
+ * TrackWithMotionModel :1596, TrackLocalMap :2776) for `batch` frames: g2o Levenberg-Marquardt on one SE3 vertex per
+ * frame, EdgeSE3ProjectXYZ edges with Huber delta sqrt(5.991), information mvInvLevelSigma2[octave], 4 rounds of
+ * {10,10,7,5} iterations with the chi2 outlier re-test {9.210, 7.378, 5.991, 5.991}.
+ * Tcw: in/out, batch x 16 row-major float (Frame::mTcw); keys_un: batch x stride (Frame::mvKeysUn: pt and octave are read);
+ * map_points: batch x stride ids (>= 0: Frame::mvpMapPoints[i] != NULL); world: batch x stride x 3 (MapPoint::GetWorldPos);
+ * inv_level_sigma2: HOST array of nlevels floats (Frame::mvInvLevelSigma2); outlier: in/out batch x stride
+ * (Frame::mvbOutlier; only entries with a map point are written); n_inliers: batch (the return value).
+ * GFORB_IN_DEVICE covers keys_un / map_points / world / counts, GFORB_OUT_DEVICE covers Tcw / outlier / n_inliers. */
+typedef struct GforbPoseOpt GforbPoseOpt;
+int gforb_poseopt_create(int max_batch, int max_points, int device, GforbPoseOpt** out);
+int gforb_poseopt_destroy(GforbPoseOpt* h);
+int gforb_pose_optimization(GforbPoseOpt* h, float* Tcw, const GforbKeyPoint* keys_un, const int32_t* map_points, const float* world,
+                            const int32_t* counts, int stride, int batch, const float* inv_level_sigma2, int nlevels, float fx,
+                            float fy, float cx, float cy, uint8_t* outlier, int32_t* n_inliers, int flags, void* stream);
+
 /* ------------------------------------------------------------------------------------------------ pipelined front end
  * The per-frame chain of Tracking::GrabImage (src/Tracking.cc:461-917) for a batch of consecutive frames, scheduled
  * below the ABI in C++ (CUDA streams / events; double-buffered so that step t+1's upload and extraction overlap step t's

@@ -424,6 +424,18 @@ def select_map_mtd3(blocks: np.ndarray, k: int, seed: int = 1, num_threads: int 
     return idx[:m].copy()
 
 
+def pose_optimization(Tcw, kp_xy, octave, map_point, world, inv_level_sigma2, K):
+    """Optimizer::PoseOptimization (src/Optimizer.cc:279-413).  Returns (n_inliers, Tcw_out (4x4 f32), outlier (N u8))."""
+    T = np.ascontiguousarray(Tcw, np.float32).reshape(4, 4).copy()
+    xy = np.ascontiguousarray(kp_xy, np.float32); oc = np.ascontiguousarray(octave, np.int32)
+    mp = np.ascontiguousarray(map_point, np.int32); w = np.ascontiguousarray(world, np.float32)
+    s2 = np.ascontiguousarray(inv_level_sigma2, np.float32)
+    out = np.zeros(len(mp), np.uint8)
+    fx, fy, cx, cy = [C.c_float(v) for v in K]
+    n = lib().orc_pose_optimization(_p(T), len(mp), _p(xy), _p(oc), _p(mp), _p(w), _p(s2), fx, fy, cx, cy, _p(out))
+    return n, T, out
+
+
 def front_end_batch(imgs: np.ndarray, threads: int, world, score, xv, sigma2, k: int, sample_scale: float, window=100,
                     nnratio=0.9, cam=None):
     """extract + SearchForInitialization(prev, cur) + info blocks + lazier-greedy selection for every frame, frames

@@ -304,6 +304,11 @@ int orc_obs_select_map_mtd3(const double* blocks, const double* obsScore, int n,
     return (int)mpVec.size();
 }
 
+int orc_pose_optimization(float* Tcw, int N, const float* kpXY, const int* octave, const int* mapPoint, const float* world,
+                          const float* invLevelSigma2, float fx, float fy, float cx, float cy, uint8_t* outlier) {
+    return PoseOptimization(Tcw, N, kpXY, octave, mapPoint, world, invLevelSigma2, fx, fy, cx, cy, outlier);
+}
+
 // Frame::isInFrustum for M map points (src/Frame.cc:166-227); flags[i] bit0 <- mbTrackInView
 void orc_is_in_frustum(const float* Rcw, const float* tcw, const float* Ow, float fx, float fy, float cx, float cy, int minX,
                        int maxX, int minY, int maxY, int nlevels, float scaleFactor, int M, const float* world,

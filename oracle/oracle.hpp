@@ -210,4 +210,8 @@ int runActiveMapMatching(Frame& F, const std::vector<MapPointView>& mps, const u
                          const double* H_meas, double* curMat, float th, ORBmatcher& matcher, int num_to_match,
                          std::vector<int>& left, int (*rand_fn)() = nullptr);
 
+// Optimizer::PoseOptimization (src/Optimizer.cc:279-413), pose_optimizer.cpp
+int PoseOptimization(float* Tcw, int N, const float* kpXY, const int* octave, const int* mapPoint, const float* world,
+                     const float* invLevelSigma2, float fx, float fy, float cx, float cy, uint8_t* outlier);
+
 }  // namespace oracle
