@@ -276,16 +276,17 @@ def run_ours(args):
         for b0, b1 in batches:
             fe.step_device(dev_frames[b0:b1], b1 - b0)
 
-    outs = _staging_sets(fe, 2)
+    NSETS = 4
+    outs = _staging_sets(fe, NSETS)
     issued = [0]
 
     def step_e2e():
-        # frames of a step are in pinned host memory; results land in two rotating sets of pinned buffers, a set is
+        # frames of a step are in pinned host memory; results land in four rotating sets of pinned buffers, a set is
         # handed back to the library only after the step that last used it has delivered (gforb_frontend_wait_results)
         for b0, b1 in batches:
-            if issued[0] >= 2:
-                L.check(L.lib.gforb_frontend_wait_results(fe._h, 1), "gforb_frontend_wait_results")
-            L.check(L.lib.gforb_frontend_step_host(fe._h, L.vp(host[b0:b1].data_ptr()), b1 - b0, L.byref(outs[issued[0] & 1][0])),
+            if issued[0] >= NSETS:
+                L.check(L.lib.gforb_frontend_wait_results(fe._h, NSETS - 1), "gforb_frontend_wait_results")
+            L.check(L.lib.gforb_frontend_step_host(fe._h, L.vp(host[b0:b1].data_ptr()), b1 - b0, L.byref(outs[issued[0] % NSETS][0])),
                     "gforb_frontend_step_host")
             issued[0] += 1
 

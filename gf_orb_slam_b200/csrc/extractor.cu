@@ -145,6 +145,73 @@ __global__ void __launch_bounds__(256, 6) k_resize(const uint8_t* __restrict__ s
     }
 }
 
+// K1b, TMA variant (A/B partner of k_resize, GFORB_RESIZE=tma): CTA = RT_ROWS bordered output rows x the whole width.  The
+// source rows those output rows read (<= ceil(RT_ROWS * scale) + 3 consecutive rows of level l-1, contiguous in the bordered
+// plane) arrive in shared memory through ONE cp.async.bulk (TMA bulk copy, mbarrier complete_tx); the byte gathers of the
+// bilinear taps then hit shared memory instead of L1/L2.  Same arithmetic, same output bytes.
+static const int RT_ROWS = 8, RT_MAXSRC = 14;
+__global__ void __launch_bounds__(256) k_resize_tma(const uint8_t* __restrict__ spyr, uint8_t* __restrict__ pyr, size_t framePyr,
+                                                    LevelPlan S, LevelPlan D, const int2* __restrict__ tabs, int quadsPerRow) {
+    extern __shared__ __align__(128) uint8_t rsm[];
+    __shared__ uint64_t bar;
+    __shared__ int s_sy0;
+    const int tid = threadIdx.x, b = blockIdx.y;
+    const int Y0 = blockIdx.x * RT_ROWS;
+    const int2* __restrict__ xt = tabs + D.xtab;
+    const int2* __restrict__ yt = tabs + D.ytab;
+    if (tid == 0) {
+        int lo = INT_MAX, hi = -1;
+        for (int i = 0; i < RT_ROWS; i++) {
+            const int sy = __ldg(&yt[reflect101(min(Y0 + i, D.rows - 1) - EDGE, D.h)]).x;
+            lo = min(lo, sy); hi = max(hi, sy + 1);
+        }
+        const int nrows = min(hi - lo + 1, RT_MAXSRC);
+        s_sy0 = lo;
+        const uint32_t bytes = (uint32_t)nrows * (uint32_t)S.pitch;
+        const uint8_t* src = spyr + (size_t)b * framePyr + S.off + (size_t)(EDGE + lo) * S.pitch;
+        const uint32_t barA = (uint32_t)__cvta_generic_to_shared(&bar), dstA = (uint32_t)__cvta_generic_to_shared(rsm);
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(barA));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(barA), "r"(bytes) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(dstA), "l"(src), "r"(bytes), "r"(barA) : "memory");
+    }
+    __syncthreads();
+    {
+        const uint32_t barA = (uint32_t)__cvta_generic_to_shared(&bar);
+        uint32_t ok = 0;
+        while (!ok)
+            asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                         : "=r"(ok) : "r"(barA) : "memory");
+    }
+    const int sy0 = s_sy0;
+    const uint8_t* __restrict__ sroi = rsm + EDGE;                      // ROI column 0 of source row sy0
+    uint8_t* __restrict__ dplane = pyr + (size_t)b * framePyr + D.off;
+    const int items = RT_ROWS * quadsPerRow;
+    for (int it = tid; it < items; it += 256) {
+        const int r = it / quadsPerRow, q = it - r * quadsPerRow;
+        const int Y = Y0 + r;
+        if (Y >= D.rows) break;
+        const int2 ty = __ldg(&yt[reflect101(Y - EDGE, D.h)]);
+        const int b0 = (short)(ty.y & 0xffff), b1 = (short)(ty.y >> 16);
+        const uint8_t* r0 = sroi + (ptrdiff_t)(ty.x - sy0) * S.pitch;
+        const uint8_t* r1 = r0 + S.pitch;
+        uint32_t outv = 0;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const int X = (q << 2) + k;
+            const int x = reflect101(min(X, D.w + 2 * EDGE - 1) - EDGE, D.w);
+            const int2 tx = __ldg(&xt[x]);
+            const int sx = tx.x, a0 = (short)(tx.y & 0xffff), a1 = (short)(tx.y >> 16);
+            const int h0 = (r0[sx] * a0 + r0[sx + 1] * a1) >> 4;
+            const int h1 = (r1[sx] * a0 + r1[sx + 1] * a1) >> 4;
+            const int v = (((b0 * h0) >> 16) + ((b1 * h1) >> 16) + 2) >> 2;
+            outv |= (uint32_t)min(max(v, 0), 255) << (8 * k);
+        }
+        *reinterpret_cast<uint32_t*>(dplane + (size_t)Y * D.pitch + (q << 2)) = outv;
+    }
+}
+
 // ------------------------------------------------------------------------------------------------ K2 detect
 // FAST-9/16 corner score in the pixel domain: with M1 = min over the 16 arcs of (max of the arc's 9 pixels) and
 // M2 = max over arcs of (min of the arc), cornerScore = max(v - M1, M2 - v) - 1 and corner(t) <=> score >= t
@@ -671,6 +738,7 @@ struct GforbExtractor {
     int kpCapTotal = 0, nCellsTotal = 0, detSmem = 0, detPixPitch = 0, fnTasks = 0, blTasks = 0;
     bool tiled = true;
     int detectVersion = 2;              // GFORB_DETECT=1 selects the first-generation per-cell kernel (A/B tool)
+    int resizeTma = 0;                  // GFORB_RESIZE=tma / direct: source rows staged by cp.async.bulk (k_resize_tma) or gathered from L1 (k_resize)
     // device buffers
     uint8_t *d_img = nullptr, *d_pyr = nullptr, *d_blr = nullptr, *d_desc = nullptr;
     GforbKeyPoint* d_kps = nullptr;
@@ -889,6 +957,8 @@ int gforb_extractor_create(const GforbExtractorConfig* cfg, GforbExtractor** out
     cudaDeviceGetAttribute(&E->numSMs, cudaDevAttrMultiProcessorCount, cfg->device);
     build_ctor_tables(E);
     if (const char* dv = getenv("GFORB_DETECT")) E->detectVersion = atoi(dv);
+    if (const char* rv = getenv("GFORB_RESIZE")) E->resizeTma = !strcmp(rv, "tma") ? 1 : 0;
+
     GF_CUDA_OK(cudaMemcpyToSymbol(g_pattern, h_pattern, sizeof(h_pattern)));
     {   // umax (src/ORBextractor.cc:500-517)
         int umax[16];
@@ -1029,7 +1099,12 @@ int gforb_extract(GforbExtractor* E, const uint8_t* images, int w, int h, int st
     for (int l = 1; l < nl; l++) {
         const LevelPlan& D = E->levels[l];
         const int quads = (D.w + 2 * EDGE + 3) >> 2, nBands = (D.rows + RS_BAND - 1) / RS_BAND;
-        k_resize<<<dim3((quads * nBands + 255) / 256, batch), 256, 0, st>>>(spyr, E->d_pyr, E->framePyr, E->levels[l - 1], D, E->d_tabs, quads, nBands); launches++;
+        if (E->resizeTma && (size_t)RT_MAXSRC * E->levels[l - 1].pitch <= 48 * 1024)
+            k_resize_tma<<<dim3((D.rows + RT_ROWS - 1) / RT_ROWS, batch), 256, (size_t)RT_MAXSRC * E->levels[l - 1].pitch, st>>>(
+                spyr, E->d_pyr, E->framePyr, E->levels[l - 1], D, E->d_tabs, quads);
+        else
+            k_resize<<<dim3((quads * nBands + 255) / 256, batch), 256, 0, st>>>(spyr, E->d_pyr, E->framePyr, E->levels[l - 1], D, E->d_tabs, quads, nBands);
+        launches++;
     }
     end();
     begin("detect");

@@ -64,6 +64,7 @@ struct GforbFrontEnd {
     bool mapSet = false;
     cudaStream_t sMain = nullptr, sMatch = nullptr, sSel = nullptr, sUp = nullptr, sDown = nullptr;
     cudaEvent_t evExtract[2], evMatch[2], evSel[2], evH2D[2], evImgFree[2], evD2H[2];
+    cudaEvent_t evHostDone[8];             // ring: step t's host frames consumed and host outputs delivered (gforb_frontend_wait_results)
     std::vector<void*> allocs;
     // profiling
     bool prof = false;
@@ -103,6 +104,7 @@ int gforb_frontend_destroy(GforbFrontEnd* F) {
         cudaEventDestroy(F->evExtract[i]); cudaEventDestroy(F->evMatch[i]); cudaEventDestroy(F->evSel[i]);
         cudaEventDestroy(F->evH2D[i]); cudaEventDestroy(F->evImgFree[i]); cudaEventDestroy(F->evD2H[i]);
     }
+    for (int i = 0; i < 8; i++) cudaEventDestroy(F->evHostDone[i]);
     for (auto& r : F->recs) { cudaEventDestroy(r.e0); cudaEventDestroy(r.e1); }
     for (auto e : F->evPool) cudaEventDestroy(e);
     if (F->sMatch && F->sMatch != F->sMain) cudaStreamDestroy(F->sMatch);
@@ -128,6 +130,7 @@ int gforb_frontend_create(const GforbFrontEndConfig* cfg, GforbFrontEnd** out) {
         cudaEventCreateWithFlags(&F->evSel[i], cudaEventDisableTiming); cudaEventCreateWithFlags(&F->evH2D[i], cudaEventDisableTiming);
         cudaEventCreateWithFlags(&F->evImgFree[i], cudaEventDisableTiming); cudaEventCreateWithFlags(&F->evD2H[i], cudaEventDisableTiming);
     }
+    for (int i = 0; i < 8; i++) cudaEventCreateWithFlags(&F->evHostDone[i], cudaEventDisableTiming);
     int rc = GFORB_OK;
     auto fail = [&](int code) { gforb_frontend_destroy(F); return code; };
     // extraction on a high-priority stream: its short ALU-bound CTAs take freed SM slots before the long-lived CTAs of the
@@ -332,6 +335,7 @@ int gforb_frontend_step_host(GforbFrontEnd* F, const uint8_t* images, int batch,
         GF_CUDA_OK(cudaMemcpyAsync(out->good_logdet, F->d_selLd[p], (size_t)batch * k * sizeof(double), cudaMemcpyDeviceToHost, F->sDown));
     GF_CUDA_OK(cudaMemcpyAsync(out->good_n, F->d_selN[p], (size_t)batch * sizeof(int32_t), cudaMemcpyDeviceToHost, F->sDown));
     GF_CUDA_OK(cudaEventRecord(F->evD2H[p], F->sDown));
+    GF_CUDA_OK(cudaEventRecord(F->evHostDone[(F->t - 1) & 7], F->sDown));     // sDown waited for this step's upload via evExtract
     return GFORB_OK;
 }
 
@@ -349,14 +353,13 @@ int gforb_frontend_sync(GforbFrontEnd* F) {
     return rc;
 }
 
-// host-side wait for ONE step_host call: the most recent (steps_back = 0) or the one before it (1) has consumed its host
-// frames and delivered its host outputs -- what a caller cycling through two sets of staging buffers needs; no error poll.
+// host-side wait for ONE step_host call: the one issued `steps_back` (0 .. 6) calls before the most recent has consumed its host
+// frames and delivered its host outputs -- what a caller cycling through S sets of staging buffers needs (steps_back = S - 1
+// before refilling a set); no error poll.
 int gforb_frontend_wait_results(GforbFrontEnd* F, int steps_back) {
-    if (!F || steps_back < 0 || steps_back > 1 || F->t <= steps_back) return GFORB_ERR_ARG;
-    const int p = (int)((F->t - 1 - steps_back) & 1);
+    if (!F || steps_back < 0 || steps_back > 6 || F->t <= steps_back) return GFORB_ERR_ARG;
     GF_CUDA_OK(cudaSetDevice(F->device));
-    GF_CUDA_OK(cudaEventSynchronize(F->evH2D[p]));
-    GF_CUDA_OK(cudaEventSynchronize(F->evD2H[p]));
+    GF_CUDA_OK(cudaEventSynchronize(F->evHostDone[(F->t - 1 - steps_back) & 7]));
     return GFORB_OK;
 }
 

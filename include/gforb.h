@@ -402,9 +402,9 @@ int gforb_frontend_step_device(GforbFrontEnd* h, const uint8_t* d_images, int ba
  * the call's stream work; out's arrays must stay valid until gforb_frontend_sync). */
 int gforb_frontend_step_host(GforbFrontEnd* h, const uint8_t* images, int batch, const GforbFrontEndOutputs* out);
 int gforb_frontend_sync(GforbFrontEnd* h);
-/* Host-side wait for one gforb_frontend_step_host call only: the most recent one (steps_back = 0) or the one before it (1)
- * has read its host frames and delivered its host outputs (a caller cycling through two sets of staging buffers waits
- * with steps_back = 1 before refilling a set).  Does not poll the error words. */
+/* Host-side wait for one gforb_frontend_step_host call only: the call issued `steps_back` (0 .. 6) calls before the most
+ * recent one has read its host frames and delivered its host outputs (a caller cycling through S sets of staging buffers
+ * waits with steps_back = S - 1 before refilling a set).  Does not poll the error words. */
 int gforb_frontend_wait_results(GforbFrontEnd* h, int steps_back);
 /* device pointers of the most recently issued step's results (valid after gforb_frontend_sync) */
 int gforb_frontend_results(GforbFrontEnd* h, GforbFrontEndOutputs* device_out);

@@ -411,6 +411,40 @@ public:
         return n;
     }
 
+    // src/ORBmatcher.cc:1089-1168 (Tracking::TrackPreviousFrame): F1's map points that F2 does not hold yet, projected with
+    // F2.mTcw into a window of windowSize pixels on the same level.  vpMapPointMatches2 starts as F2.mvpMapPoints;
+    // F2.mvpMatchScore is updated.
+    int SearchByProjection(Frame& F1, Frame& F2, int windowSize, std::vector<MapPoint*>& vpMapPointMatches2) {
+        vpMapPointMatches2 = F2.mvpMapPoints;
+        if (F1.N == 0 || F2.N == 0) return 0;
+        ensure(std::max(F1.N, F2.N), F1.N, F2.mnScaleLevels, F2.mfScaleFactor);
+        FlatFrame a(F1), b(F2);
+        // MapPoint* identity -> ids: a point of F1 is its F1 index; a point only F2 holds gets F1.N + its F2 index
+        std::vector<int32_t> ids1(F1.N, -1), m2(F2.N, -1), sc(F2.mvpMatchScore.begin(), F2.mvpMatchScore.end());
+        std::vector<float> world((size_t)F1.N * 3, 0.f);
+        for (int i = 0; i < F1.N; i++) {
+            MapPoint* p = F1.mvpMapPoints[i];
+            if (!p || p->isBad()) continue;
+            ids1[i] = i;
+            std::memcpy(&world[(size_t)i * 3], p->mWorldPos, 12);
+        }
+        for (int j = 0; j < F2.N; j++) {
+            MapPoint* p = F2.mvpMapPoints[j];
+            if (!p) continue;
+            m2[j] = F1.N + j;
+            for (int i = 0; i < F1.N; i++) if (F1.mvpMapPoints[i] == p) { m2[j] = i; break; }
+        }
+        int32_t n = 0;
+        gforb_throw(gforb_search_by_projection_window(h_, &a.set, &b.set, 1, ids1.data(), world.data(), F2.mTcw, F2.fx, F2.fy, F2.cx,
+                                                      F2.cy, windowSize, mfNNratio, m2.data(), sc.data(), &n, 0, nullptr),
+                    "SearchByProjection(F1, F2, windowSize)");
+        for (int j = 0; j < F2.N; j++) {
+            if (m2[j] >= 0 && m2[j] < F1.N) vpMapPointMatches2[j] = F1.mvpMapPoints[m2[j]];
+            F2.mvpMatchScore[j] = sc[j];
+        }
+        return n;
+    }
+
     float mfNNratio;
     bool mbCheckOrientation;
 
@@ -721,6 +755,39 @@ private:
     GforbObs* h_ = nullptr;
     int maxPoints_ = 8192, n_ = 0;
     std::vector<double> blocks_, score_;
+};
+
+// ------------------------------------------------------------------------------------------------ Optimizer
+// Optimizer::PoseOptimization(Frame*) (include/Optimizer.h, src/Optimizer.cc:279-413): motion-only bundle adjustment on the
+// frame's matched map points; pFrame->mTcw and pFrame->mvbOutlier are updated, returns nInitialCorrespondences - nBad.
+class Optimizer {
+public:
+    static int PoseOptimization(Frame* pFrame, int device = 0) {
+        if (!pFrame) return 0;
+        Frame& F = *pFrame;
+        const int N = (int)F.mvpMapPoints.size();
+        if (N == 0) return 0;
+        GforbPoseOpt* h = nullptr;
+        gforb_throw(gforb_poseopt_create(1, N, device, &h), "PoseOptimization: create");
+        std::vector<GforbKeyPoint> kps(N);
+        std::vector<int32_t> mp(N);
+        std::vector<float> world((size_t)N * 3, 0.f), inv(F.mvLevelSigma2.size());
+        std::vector<uint8_t> out(N);
+        for (int i = 0; i < N; i++) {
+            std::memcpy(&kps[i], &F.mvKeysUn[i], sizeof(GforbKeyPoint));
+            mp[i] = F.mvpMapPoints[i] ? i : -1;
+            if (F.mvpMapPoints[i]) std::memcpy(&world[(size_t)i * 3], F.mvpMapPoints[i]->mWorldPos, 12);
+            out[i] = F.mvbOutlier[i] ? 1 : 0;
+        }
+        for (size_t l = 0; l < inv.size(); l++) inv[l] = 1.0f / F.mvLevelSigma2[l];            // Frame::mvInvLevelSigma2 (src/Frame.cc:109-112)
+        int32_t cnt = N, ninl = 0;
+        const int rc = gforb_pose_optimization(h, F.mTcw, kps.data(), mp.data(), world.data(), &cnt, N, 1, inv.data(), (int)inv.size(),
+                                               F.fx, F.fy, F.cx, F.cy, out.data(), &ninl, 0, nullptr);
+        gforb_poseopt_destroy(h);
+        gforb_throw(rc, "PoseOptimization");
+        for (int i = 0; i < N; i++) if (F.mvpMapPoints[i]) F.mvbOutlier[i] = out[i] != 0;
+        return ninl;
+    }
 };
 
 }  // namespace ORB_SLAM

@@ -309,6 +309,80 @@ int main() {
         CHECK(dd, "ComputeDistinctiveDescriptors differs from the oracle");
     }
 
+    // ---- ORBmatcher::SearchByProjection(F1, F2, windowSize, out) (TrackPreviousFrame) and Optimizer::PoseOptimization through the
+    //      shim vs the oracle: frame-1 keypoints become map points that project near their frame-2 positions
+    int nPrev = 0, nInl = 0;
+    {
+        const float fx = 458.0f, fy = 457.0f, cx = 376.0f, cy = 240.0f;
+        std::vector<MapPoint> wp(F1.N);
+        std::vector<float> world((size_t)F1.N * 3);
+        sm_state = 909;
+        for (int i = 0; i < F1.N; i++) {
+            const float z = 2.0f + (float)(splitmix() % 600) * 0.01f;
+            const float u = k1[i].pt.x - 3.0f + (float)(splitmix() % 3) - 1.0f, v = k1[i].pt.y - 1.0f + (float)(splitmix() % 3) - 1.0f;
+            wp[i].mWorldPos[0] = (u - cx) / fx * z; wp[i].mWorldPos[1] = (v - cy) / fy * z; wp[i].mWorldPos[2] = z;
+            wp[i].mbBad = (splitmix() % 25) == 0;
+            std::memcpy(&world[(size_t)i * 3], wp[i].mWorldPos, 12);
+        }
+        Frame Fa = F1, Fb = F2;
+        oracle::Frame oFa = oF1, oFb = oF2;
+        for (int i = 0; i < Fa.N; i++) {
+            const bool has = (splitmix() % 7) != 0;
+            Fa.mvpMapPoints[i] = has ? &wp[i] : nullptr;
+            oFa.mvpMapPoints[i] = (has && !wp[i].mbBad) ? i : -1;
+        }
+        for (int j = 0; j < Fb.N; j++) {                       // F2 arrives holding a few points already (some shared with F1)
+            Fb.mvpMapPoints[j] = nullptr; oFb.mvpMapPoints[j] = -1; Fb.mvpMatchScore[j] = 999; oFb.mvpMatchScore[j] = 999;
+            if ((splitmix() % 12) == 0) { const int i = (int)(splitmix() % (uint64_t)Fa.N); Fb.mvpMapPoints[j] = &wp[i]; oFb.mvpMapPoints[j] = i; }
+        }
+        // the product maps pointer identity to ids itself; the oracle ids above use the F1 index of the shared point only when F1
+        // holds it -- align the oracle with the shim's convention (a point only F2 holds: F1.N + j)
+        for (int j = 0; j < Fb.N; j++)
+            if (Fb.mvpMapPoints[j]) {
+                const int i = (int)(Fb.mvpMapPoints[j] - &wp[0]);
+                oFb.mvpMapPoints[j] = (Fa.mvpMapPoints[i] == Fb.mvpMapPoints[j]) ? i : Fa.N + j;
+            }
+        Fb.fx = fx; Fb.fy = fy; Fb.cx = cx; Fb.cy = cy; oFb.fx = fx; oFb.fy = fy; oFb.cx = cx; oFb.cy = cy;
+        ORBmatcher mp(0.9f, true);
+        oracle::ORBmatcher omp2(0.9f, true);
+        std::vector<MapPoint*> out2;
+        std::vector<int> oout2;
+        nPrev = mp.SearchByProjection(Fa, Fb, 15, out2);
+        const int onPrev = omp2.SearchByProjection(oFa, oFb, world.data(), 15, oout2);
+        CHECK(nPrev == onPrev && nPrev > 50, "SearchByProjection(F1, F2, window): %d vs %d", nPrev, onPrev);
+        bool pa = out2.size() == oout2.size();
+        for (size_t j = 0; pa && j < out2.size(); j++) {
+            int id = -1;
+            if (out2[j]) { const int i = (int)(out2[j] - &wp[0]); id = (Fa.mvpMapPoints[i] == out2[j]) ? i : Fa.N + (int)j; }
+            pa = id == oout2[j] && Fb.mvpMatchScore[j] == oFb.mvpMatchScore[j];
+        }
+        CHECK(pa, "SearchByProjection(F1, F2, window) associations / scores differ");
+        // PoseOptimization on the matched frame from a perturbed pose
+        Frame Fp = Fb;
+        Fp.mvpMapPoints = out2;
+        Fp.mTcw[3] = 0.02f; Fp.mTcw[7] = -0.01f; Fp.mTcw[11] = 0.03f;
+        std::vector<float> xy((size_t)Fp.N * 2), wpos((size_t)Fp.N * 3, 0.f), inv(Fp.mvLevelSigma2.size());
+        std::vector<int> oct(Fp.N), ids(Fp.N);
+        std::vector<uint8_t> oflag(Fp.N, 0);
+        for (int j = 0; j < Fp.N; j++) {
+            xy[2 * j] = Fp.mvKeysUn[j].pt.x; xy[2 * j + 1] = Fp.mvKeysUn[j].pt.y; oct[j] = Fp.mvKeysUn[j].octave;
+            ids[j] = out2[j] ? j : -1;
+            if (out2[j]) std::memcpy(&wpos[(size_t)j * 3], out2[j]->mWorldPos, 12);
+        }
+        for (size_t l = 0; l < inv.size(); l++) inv[l] = 1.0f / Fp.mvLevelSigma2[l];
+        float oT[16];
+        std::memcpy(oT, Fp.mTcw, sizeof(oT));
+        const int onInl = oracle::PoseOptimization(oT, Fp.N, xy.data(), oct.data(), ids.data(), wpos.data(), inv.data(), fx, fy, cx, cy, oflag.data());
+        nInl = Optimizer::PoseOptimization(&Fp);
+        CHECK(nInl == onInl && nInl > 30, "PoseOptimization inliers: %d vs %d", nInl, onInl);
+        bool fl = true, ps = true;
+        for (int j = 0; j < Fp.N; j++) if (out2[j]) fl = fl && (Fp.mvbOutlier[j] ? 1 : 0) == oflag[j];
+        for (int e = 0; e < 16; e++) ps = ps && std::fabs(Fp.mTcw[e] - oT[e]) <= 1e-5f * std::fabs(oT[e]) + 1e-6f;
+        CHECK(fl, "PoseOptimization outlier flags differ");
+        CHECK(ps, "PoseOptimization pose differs by more than 1e-5 relative");
+    }
+
+    printf("TrackPreviousFrame leg: %d window-projection matches, %d pose inliers\n", nPrev, nInl);
     printf("shim test: %zu/%zu keypoints, %d init matches, %d projection matches, %zu good features, %d active matches: %s\n", k1.size(),
            k2.size(), nm, np, good.size(), nActive, g_fail ? "FAILED" : "OK");
     return g_fail ? 1 : 0;

@@ -95,3 +95,20 @@ def test_variants(orc, blur_variant, retain_variant):
     kps, desc, counts = ex.extract_batch(img[None])
     ex_cpu = orc.ORBextractor(1000, 1.2, 8, blurVariant=blur_variant, retainVariant=retain_variant)
     _cmp_frame(orc, ex_cpu, img, 0, kps, desc, counts)
+
+
+def test_resize_variants_agree(monkeypatch):
+    """the pyramid resize with source rows staged by cp.async.bulk (GFORB_RESIZE=tma, the A/B partner recorded in
+    profiles/r2_ncu_summary.txt) writes the same pyramid bytes and the same keypoints / descriptors as the default kernel"""
+    from gf_orb_slam_b200 import ORBextractor
+    imgs = np.stack([synth.textured_frame(1241, 376, seed=40 + i) for i in range(2)])
+    res = []
+    for v in ("direct", "tma"):
+        monkeypatch.setenv("GFORB_RESIZE", v)
+        ex = ORBextractor(2000, 1.2, 8, max_width=1241, max_height=376, max_batch=2)
+        kps, desc, counts = ex.extract_batch(imgs)
+        res.append((kps.copy(), desc.copy(), counts.copy(), [ex.debug_level(1, l, 0).copy() for l in range(8)]))
+    a, b = res
+    assert np.array_equal(a[2], b[2]) and a[0].tobytes() == b[0].tobytes() and np.array_equal(a[1], b[1])
+    for l in range(8):
+        assert np.array_equal(a[3][l], b[3][l]), l
