@@ -738,6 +738,8 @@ struct GforbExtractor {
     int kpCapTotal = 0, nCellsTotal = 0, detSmem = 0, detPixPitch = 0, fnTasks = 0, blTasks = 0;
     bool tiled = true;
     int detectVersion = 2;              // GFORB_DETECT=1 selects the first-generation per-cell kernel (A/B tool)
+    int blurFork = 1;                   // the blur of a call runs on ownStream beside the quota / retainBest / orientation kernels (gforb_extractor_set_concurrency)
+    cudaEvent_t evFork = nullptr, evJoin = nullptr;
     int resizeTma = 0;                  // GFORB_RESIZE=tma / direct: source rows staged by cp.async.bulk (k_resize_tma) or gathered from L1 (k_resize)
     // device buffers
     uint8_t *d_img = nullptr, *d_pyr = nullptr, *d_blr = nullptr, *d_desc = nullptr;
@@ -954,6 +956,9 @@ int gforb_extractor_create(const GforbExtractorConfig* cfg, GforbExtractor** out
     E->cfg = *cfg;
     E->device = cfg->device;
     GF_CUDA_OK(cudaStreamCreateWithFlags(&E->ownStream, cudaStreamNonBlocking));
+    GF_CUDA_OK(cudaEventCreateWithFlags(&E->evFork, cudaEventDisableTiming));
+    GF_CUDA_OK(cudaEventCreateWithFlags(&E->evJoin, cudaEventDisableTiming));
+    if (const char* bf = getenv("GFORB_BLUR_FORK")) E->blurFork = atoi(bf);
     cudaDeviceGetAttribute(&E->numSMs, cudaDevAttrMultiProcessorCount, cfg->device);
     build_ctor_tables(E);
     if (const char* dv = getenv("GFORB_DETECT")) E->detectVersion = atoi(dv);
@@ -998,6 +1003,8 @@ int gforb_extractor_destroy(GforbExtractor* E) {
     for (auto& r : E->recs) { cudaEventDestroy(r.e0); cudaEventDestroy(r.e1); }
     for (auto& e : E->evPool) cudaEventDestroy(e);
     if (E->ownStream) cudaStreamDestroy(E->ownStream);
+    if (E->evFork) cudaEventDestroy(E->evFork);
+    if (E->evJoin) cudaEventDestroy(E->evJoin);
     delete E;
     return GFORB_OK;
 }
@@ -1079,15 +1086,16 @@ int gforb_extract(GforbExtractor* E, const uint8_t* images, int w, int h, int st
         return e;
     };
     const bool prof = E->profiling && E->recs.size() < 65536;
+    cudaStream_t stageStream = st;
     auto begin = [&](const char* name) {
         if (!prof) return;
         if (si >= E->stages.size()) { Stage s; s.name = name; s.ms = 0; s.e0 = s.e1 = nullptr; E->stages.push_back(s); }
         E->stages[si].name = name;
         StageRec r; r.stage = (int)si; r.e0 = getEv(); r.e1 = getEv();
         E->recs.push_back(r);
-        cudaEventRecord(r.e0, st);
+        cudaEventRecord(r.e0, stageStream);
     };
-    auto end = [&]() { if (!prof) return; cudaEventRecord(E->recs.back().e1, st); si++; };
+    auto end = [&]() { if (!prof) return; cudaEventRecord(E->recs.back().e1, stageStream); si++; };
 
     begin("pyramid");
     {
@@ -1120,6 +1128,21 @@ int gforb_extract(GforbExtractor* E, const uint8_t* images, int w, int h, int st
             c.iniThFAST, c.minThFAST, E->detPixPitch, E->d_err); launches++;
     }
     end();
+    // The blur needs only the pyramid and the score map's storage (free once k_cell_emit has read it); the quota / retainBest /
+    // orientation kernels are latency-bound and leave the SMs almost empty: the blur runs beside them on the handle's own stream
+    // and joins before the descriptors (issued first, so its blocks fill the SMs the short kernels leave idle).
+    const bool fork = E->blurFork && st != E->ownStream;
+    if (fork) {
+        GF_CUDA_OK(cudaEventRecord(E->evFork, st));
+        GF_CUDA_OK(cudaStreamWaitEvent(E->ownStream, E->evFork, 0));
+    }
+    if (fork) stageStream = E->ownStream;
+    begin("blur");
+    k_blur2<<<dim3((E->blTasks + BL2_WARPS - 1) / BL2_WARPS, batch), BL2_WARPS * 32, 0, fork ? E->ownStream : st>>>(
+        E->d_pyr, E->d_blr, E->framePyr, E->d_levels, nl, E->blTasks, c.blur_variant); launches++;
+    end();
+    stageStream = st;
+    if (fork) GF_CUDA_OK(cudaEventRecord(E->evJoin, E->ownStream));
     begin("select");
     k_quota<<<(batch * nl + 127) / 128, 128, 0, st>>>(E->d_levels, E->d_cells, nl, E->nCellsTotal, E->d_cnt7, E->d_cnt20,
                                                      E->d_nTotal, E->d_nToRetain, E->d_cellOff, E->d_lvlPre, batch, E->d_err); launches++;
@@ -1145,10 +1168,7 @@ int gforb_extract(GforbExtractor* E, const uint8_t* images, int w, int h, int st
                                                                     E->frameKp, E->kpCapTotal, E->d_lvlCount, dk, dc, c.nfeatures,
                                                                     harris ? E->d_lvlResp : nullptr); launches++;
     end();
-    begin("blur");
-    k_blur2<<<dim3((E->blTasks + BL2_WARPS - 1) / BL2_WARPS, batch), BL2_WARPS * 32, 0, st>>>(
-        E->d_pyr, E->d_blr, E->framePyr, E->d_levels, nl, E->blTasks, c.blur_variant); launches++;
-    end();
+    if (fork) GF_CUDA_OK(cudaStreamWaitEvent(st, E->evJoin, 0));
     begin("describe");
     k_describe<<<dim3((E->kpCapTotal + 7) / 8, batch), 256, 0, st>>>(E->d_pyr, E->d_blr, E->framePyr, E->d_levels, nl, E->d_lvlKp,
                                                                       E->frameKp, E->kpCapTotal, E->d_lvlCount, dk, dd, c.nfeatures); launches++;
@@ -1179,6 +1199,14 @@ int gforb_extractor_poll_error(GforbExtractor* E, void* stream) {
     int err = 0;
     GF_CUDA_OK(cudaMemcpy(&err, E->d_err, sizeof(int), cudaMemcpyDeviceToHost));
     if (err) { cudaMemset(E->d_err, 0, sizeof(int)); return err; }
+    return GFORB_OK;
+}
+
+// 1 (default): the Gaussian blur of a call runs on the handle's own stream beside the quota / retainBest / orientation
+// kernels; 0: every kernel of a call on the caller's stream, one after the other (serial per-kernel timing)
+int gforb_extractor_set_concurrency(GforbExtractor* E, int on) {
+    if (!E) return GFORB_ERR_ARG;
+    E->blurFork = on != 0;
     return GFORB_OK;
 }
 

@@ -154,6 +154,7 @@ int gforb_frontend_create(const GforbFrontEndConfig* cfg, GforbFrontEnd** out) {
     ec.iniThFAST = cfg->iniThFAST; ec.minThFAST = cfg->minThFAST; ec.max_width = cfg->width; ec.max_height = cfg->height;
     ec.max_batch = cfg->max_batch; ec.device = cfg->device;
     if ((rc = gforb_extractor_create(&ec, &F->ex))) return fail(rc);
+    if (!cfg->overlap) gforb_extractor_set_concurrency(F->ex, 0);      // serial reference timing: one kernel after the other
     GforbMatcherConfig mc;
     memset(&mc, 0, sizeof(mc));
     mc.max_batch = cfg->max_batch; mc.max_keypoints = cfg->nfeatures; mc.max_queries = cfg->nfeatures; mc.cand_pool = 48 * cfg->nfeatures;

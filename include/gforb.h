@@ -89,6 +89,9 @@ int gforb_extractor_last_launches(const GforbExtractor* h);
  * number of stages.  Profiling is enabled with gforb_extractor_set_profiling(h, 1). */
 int gforb_extractor_set_profiling(GforbExtractor* h, int on);
 int gforb_extractor_stage_time(const GforbExtractor* h, int i, const char** name, float* ms);
+/* 1 (default): within a call the Gaussian blur runs on the handle's own stream beside the latency-bound quota / retainBest /
+ * orientation kernels and joins before the descriptors; 0: all kernels of a call in sequence on the caller's stream. */
+int gforb_extractor_set_concurrency(GforbExtractor* h, int on);
 
 /* ------------------------------------------------------------------------------------------------ matching
  * Replaces ORB_SLAM::ORBmatcher (include/ORBmatcher.h:39-294, src/ORBmatcher.cc) for the per-frame tracking
