@@ -64,35 +64,45 @@ __device__ __forceinline__ int reflect101(int p, int len) {
 }
 
 // ------------------------------------------------------------------------------------------------ K1a
-// level 0 = copyMakeBorder(image, 16, BORDER_REFLECT_101) (ComputePyramid :990-991).  Thread = one 16-byte chunk of a
-// bordered row; grid (row blocks, frames).
+// level 0 = copyMakeBorder(image, 16, BORDER_REFLECT_101) (ComputePyramid :990-991).  Task = one 16-byte chunk of a
+// bordered row; a CTA owns B0_ROWS bordered rows and runs the chunks in two groups so that warps do not diverge: the interior
+// chunks (one aligned 128-bit load each) first, then the few chunks per row that touch the reflected ring or the pitch padding.
+static const int B0_ROWS = 16;
 __global__ void __launch_bounds__(256) k_border0(const uint8_t* __restrict__ img, int w, int h, int stride,
                                                  size_t frameStride, uint8_t* __restrict__ pyr, size_t framePyr,
                                                  LevelPlan L) {
-    const int Y = blockIdx.x * blockDim.y + threadIdx.y, b = blockIdx.y;
-    if (Y >= L.rows) return;
-    const uint8_t* srow = img + (size_t)b * frameStride + (size_t)reflect101(Y - EDGE, h) * stride;
-    for (int X0 = threadIdx.x << 4; X0 < L.pitch; X0 += blockDim.x << 4) {
-        uint4 out;
-        const uint8_t* sp = srow + (X0 - EDGE);
-        if (X0 >= EDGE && X0 + 15 < EDGE + w && ((reinterpret_cast<uintptr_t>(sp) & 15) == 0)) {
-            out = ldg_nc_u4(sp);
-        } else {
-            uint32_t wv[4];
+    const int Y0 = blockIdx.x * B0_ROWS, b = blockIdx.y, tid = threadIdx.x;
+    const int nRows = min(B0_ROWS, L.rows - Y0);
+    const uint8_t* src = img + (size_t)b * frameStride;
+    uint8_t* dst = pyr + (size_t)b * framePyr + L.off;
+    const int nC = L.pitch >> 4;
+    // chunk c (bytes 16c .. 16c + 15 of the bordered row) lies inside the image iff 1 <= c <= w / 16
+    const bool aligned = (((reinterpret_cast<uintptr_t>(src)) | (uintptr_t)stride) & 15) == 0;
+    const int cLo = aligned ? 1 : nC, cHi = aligned ? min(w / 16 + 1, nC) : nC;
+    const int nFast = max(cHi - cLo, 0), nSlow = nC - nFast;
+    for (int t = tid; t < nFast * nRows; t += 256) {
+        const int r = t / nFast, c = cLo + (t - r * nFast), Y = Y0 + r;
+        const uint8_t* srow = src + (size_t)reflect101(Y - EDGE, h) * stride;
+        *reinterpret_cast<uint4*>(dst + (size_t)Y * L.pitch + (c << 4)) = ldg_nc_u4(srow + ((c << 4) - EDGE));
+    }
+    for (int t = tid; t < nSlow * nRows; t += 256) {
+        const int r = t / nSlow, k = t - r * nSlow, Y = Y0 + r;
+        const int c = (nFast > 0 && k >= cLo) ? k + nFast : k;
+        const int X0 = c << 4;
+        const uint8_t* srow = src + (size_t)reflect101(Y - EDGE, h) * stride;
+        uint32_t wv[4];
 #pragma unroll
-            for (int q = 0; q < 4; q++) {
-                uint32_t v = 0;
+        for (int q = 0; q < 4; q++) {
+            uint32_t v = 0;
 #pragma unroll
-                for (int k = 0; k < 4; k++) {
-                    const int X = X0 + q * 4 + k;
-                    const uint32_t px = (X < w + 2 * EDGE) ? srow[reflect101(X - EDGE, w)] : 0u;
-                    v |= px << (8 * k);
-                }
-                wv[q] = v;
+            for (int j = 0; j < 4; j++) {
+                const int X = X0 + q * 4 + j;
+                const uint32_t px = (X < w + 2 * EDGE) ? srow[reflect101(X - EDGE, w)] : 0u;
+                v |= px << (8 * j);
             }
-            out = make_uint4(wv[0], wv[1], wv[2], wv[3]);
+            wv[q] = v;
         }
-        *reinterpret_cast<uint4*>(pyr + (size_t)b * framePyr + L.off + (size_t)Y * L.pitch + X0) = out;
+        *reinterpret_cast<uint4*>(dst + (size_t)Y * L.pitch + X0) = make_uint4(wv[0], wv[1], wv[2], wv[3]);
     }
 }
 
@@ -1100,8 +1110,7 @@ int gforb_extract(GforbExtractor* E, const uint8_t* images, int w, int h, int st
     begin("pyramid");
     {
         const LevelPlan& L0 = E->levels[0];
-        const int tx = (L0.pitch >> 4) <= 32 ? 32 : 64, ty = 256 / tx;
-        k_border0<<<dim3((L0.rows + ty - 1) / ty, batch), dim3(tx, ty), 0, st>>>(dimg, w, h, dstride, dfs, E->d_pyr, E->framePyr, L0); launches++;
+        k_border0<<<dim3((L0.rows + B0_ROWS - 1) / B0_ROWS, batch), 256, 0, st>>>(dimg, w, h, dstride, dfs, E->d_pyr, E->framePyr, L0); launches++;
     }
     const uint8_t* spyr = E->d_pyr;     // source level l-1 and destination level l are disjoint planes of the same block
     for (int l = 1; l < nl; l++) {
