@@ -21,6 +21,7 @@
 #include <type_traits>
 #include <vector>
 #include "common.cuh"
+#include "host_util.h"
 
 namespace gforb {
 
@@ -933,7 +934,7 @@ static int build_plan(GforbExtractor* E, int w, int h) {
     GF_CUDA_OK(cudaMemcpy(E->d_levels, E->levels.data(), sizeof(LevelPlan) * nl, cudaMemcpyHostToDevice));
     GF_CUDA_OK(cudaMemcpy(E->d_cells, E->cells.data(), sizeof(CellPlan) * E->cells.size(), cudaMemcpyHostToDevice));
     if (!tabs.empty()) GF_CUDA_OK(cudaMemcpy(E->d_tabs, tabs.data(), sizeof(int2) * tabs.size(), cudaMemcpyHostToDevice));
-    GF_CUDA_OK(cudaFuncSetAttribute(k_detect, cudaFuncAttributeMaxDynamicSharedMemorySize, E->detSmem));
+    GF_CUDA_OK(raise_dyn_smem(k_detect, E->detSmem, E->device));
     E->planW = w; E->planH = h;
     return GFORB_OK;
 }
@@ -963,6 +964,7 @@ int gforb_extractor_create(const GforbExtractorConfig* cfg, GforbExtractor** out
     }
     GF_CUDA_OK(cudaSetDevice(cfg->device));
     GforbExtractor* E = new GforbExtractor();
+    const auto init = [&]() -> int {
     E->cfg = *cfg;
     E->device = cfg->device;
     GF_CUDA_OK(cudaStreamCreateWithFlags(&E->ownStream, cudaStreamNonBlocking));
@@ -997,8 +999,10 @@ int gforb_extractor_create(const GforbExtractorConfig* cfg, GforbExtractor** out
     GF_CUDA_OK(cudaMemset(E->d_err, 0, sizeof(int)));
     E->capImg = (size_t)cfg->max_width * cfg->max_height * B;
     GF_CUDA_OK(cudaMalloc((void**)&E->d_img, E->capImg));
-    int rc = build_plan(E, cfg->max_width, cfg->max_height);
-    if (rc != GFORB_OK) { gforb_extractor_destroy(E); return rc; }
+    if (const int rc = build_plan(E, cfg->max_width, cfg->max_height)) return rc;
+        return GFORB_OK;
+    };
+    if (const int rc = init()) { gforb_extractor_destroy(E); return rc; }   // a failure part-way frees what was allocated
     *out = E;
     return GFORB_OK;
 }

@@ -4,6 +4,9 @@
 #include <cuda_runtime.h>
 #include <stddef.h>
 #include <stdint.h>
+#include <map>
+#include <mutex>
+#include <utility>
 #include <vector>
 
 namespace gforb {
@@ -24,6 +27,20 @@ struct Arena {
         return base + a;
     }
 };
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize is one value per (function, device) shared by every handle of the process:
+// only ever raise it, so that creating a small handle after a large one cannot starve the large one's launches.
+template <class F>
+inline cudaError_t raise_dyn_smem(F func, int bytes, int device) {
+    static std::mutex mu;
+    static std::map<std::pair<const void*, int>, int> granted;
+    std::lock_guard<std::mutex> g(mu);
+    int& cur = granted[std::make_pair(reinterpret_cast<const void*>(func), device)];
+    if (bytes <= cur) return cudaSuccess;
+    const cudaError_t e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e == cudaSuccess) cur = bytes;
+    return e;
+}
 
 // deferred device -> host copies of a call's outputs
 struct OutCopy { void* host; const void* dev; size_t bytes; };

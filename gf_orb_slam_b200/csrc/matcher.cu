@@ -915,6 +915,7 @@ int gforb_matcher_create(const GforbMatcherConfig* cfg, GforbMatcher** out) {
     }
     GF_CUDA_OK(cudaSetDevice(cfg->device));
     GforbMatcher* M = new GforbMatcher();
+    const auto init = [&]() -> int {
     M->cfg = *cfg;
     M->device = cfg->device;
     cudaDeviceGetAttribute(&M->numSMs, cudaDevAttrMultiProcessorCount, cfg->device);
@@ -935,10 +936,14 @@ int gforb_matcher_create(const GforbMatcherConfig* cfg, GforbMatcher** out) {
     const size_t arenaBytes = B * (K * 2 * (28 + 32 + 16) + Qn * (64 + 32)) + (4u << 20);
     GF_CUDA_OK(M->arena.init(arenaBytes));
     const int smem = 3 * cfg->max_keypoints * (int)sizeof(int);
-    GF_CUDA_OK(cudaFuncSetAttribute(k_resolve<M_INIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    GF_CUDA_OK(cudaFuncSetAttribute(k_resolve<M_WINDOW>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    GF_CUDA_OK(cudaFuncSetAttribute(k_resolve<M_MAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    GF_CUDA_OK(cudaFuncSetAttribute(k_resolve<M_LAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    GF_CUDA_OK(raise_dyn_smem(k_resolve<M_INIT>, smem, cfg->device));
+    GF_CUDA_OK(raise_dyn_smem(k_resolve<M_WINDOW>, smem, cfg->device));
+    GF_CUDA_OK(raise_dyn_smem(k_resolve<M_MAP>, smem, cfg->device));
+    GF_CUDA_OK(raise_dyn_smem(k_resolve<M_LAST>, smem, cfg->device));
+    GF_CUDA_OK(raise_dyn_smem(k_resolve<M_PROJ2>, smem, cfg->device));
+        return GFORB_OK;
+    };
+    if (const int rc = init()) { gforb_matcher_destroy(M); return rc; }   // a failure part-way frees what was allocated
     *out = M;
     return GFORB_OK;
 }
@@ -1393,11 +1398,7 @@ int gforb_allpairs_top2(GforbMatcher* M, const uint8_t* queries, int n_q, const 
             GF_CUDA_OK(cudaMalloc((void**)&M->d_partial, need * sizeof(uint64_t)));
             M->capPartial = need;
         }
-        static bool attrSet[64] = {};
-        if (!attrSet[M->device & 63]) {
-            GF_CUDA_OK(cudaFuncSetAttribute(tc::k_allpairs_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::TC_SMEM_BYTES));
-            attrSet[M->device & 63] = true;
-        }
+        GF_CUDA_OK(raise_dyn_smem(tc::k_allpairs_tc, tc::TC_SMEM_BYTES, M->device));
         tc::TcParams P;
         P.q = (const uint4*)queries; P.nq = n_q; P.db = (const uint4*)db; P.nDb = n_db; P.tilesPerSplit = (int)tilesPer;
         P.idxBase = idx_base; P.partial = M->d_partial; P.err = M->d_err;

@@ -886,6 +886,7 @@ int gforb_obs_create(const GforbObsConfig* cfg, GforbObs** out) {
     }
     GF_CUDA_OK(cudaSetDevice(cfg->device));
     GforbObs* O = new GforbObs();
+    const auto init = [&]() -> int {
     O->cfg = *cfg;
     O->device = cfg->device;
     for (int i = 0; i < 13; i++) O->Xv[i] = 0;
@@ -896,17 +897,20 @@ int gforb_obs_create(const GforbObsConfig* cfg, GforbObs** out) {
     if (const char* e = getenv("GFORB_SELECT_SMEM_PAD")) O->selPad = atoi(e);
     cudaDeviceGetAttribute(&O->numSMs, cudaDevAttrMultiProcessorCount, cfg->device);
     const int selSmem = (int)select_smem(cfg->max_points) + O->selPad;
-    GF_CUDA_OK(cudaFuncSetAttribute(k_select<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, selSmem));
-    GF_CUDA_OK(cudaFuncSetAttribute(k_select<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, selSmem));
-    GF_CUDA_OK(cudaFuncSetAttribute(k_select<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, selSmem));
+    GF_CUDA_OK(raise_dyn_smem(k_select<64>, selSmem, cfg->device));
+    GF_CUDA_OK(raise_dyn_smem(k_select<128>, selSmem, cfg->device));
+    GF_CUDA_OK(raise_dyn_smem(k_select<256>, selSmem, cfg->device));
     if (const char* e = getenv("GFORB_SELECT_AHEAD_PAD")) O->aheadPad = atoi(e);
     const int aheadSmem = (int)ahead_smem(cfg->max_points) + O->aheadPad;
-    GF_CUDA_OK(cudaFuncSetAttribute(k_select_ahead<64, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, aheadSmem));
-    GF_CUDA_OK(cudaFuncSetAttribute(k_select_ahead<128, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, aheadSmem));
-    GF_CUDA_OK(cudaFuncSetAttribute(k_select_ahead<128, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, aheadSmem));
-    GF_CUDA_OK(cudaFuncSetAttribute(k_select_ahead<256, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, aheadSmem));
+    GF_CUDA_OK(raise_dyn_smem(k_select_ahead<64, 5>, aheadSmem, cfg->device));
+    GF_CUDA_OK(raise_dyn_smem(k_select_ahead<128, 2>, aheadSmem, cfg->device));
+    GF_CUDA_OK(raise_dyn_smem(k_select_ahead<128, 3>, aheadSmem, cfg->device));
+    GF_CUDA_OK(raise_dyn_smem(k_select_ahead<256, 1>, aheadSmem, cfg->device));
     if (const char* e = getenv("GFORB_SELECT_THREADS")) O->selThreads = atoi(e);
     if (getenv("GFORB_SELECT_NO_AHEAD")) O->selAhead = 0;
+        return GFORB_OK;
+    };
+    if (const int rc = init()) { gforb_obs_destroy(O); return rc; }   // a failure part-way frees what was allocated
     *out = O;
     return GFORB_OK;
 }
