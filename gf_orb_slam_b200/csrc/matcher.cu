@@ -27,7 +27,7 @@ namespace gforb {
 
 static const int GRID_COLS = 64, GRID_ROWS = 48, GRID_CELLS = GRID_COLS * GRID_ROWS;
 static const int TH_HIGH = 100, TH_LOW = 50, HISTO_LENGTH = 30;
-enum { M_INIT = 0, M_WINDOW = 1, M_MAP = 2, M_LAST = 3, M_AREA = 4, M_PROJ2 = 5 };
+enum { M_INIT = 0, M_WINDOW = 1, M_MAP = 2, M_LAST = 3, M_AREA = 4, M_PROJ2 = 5, M_BOW = 6, M_KF = 7 };
 
 struct FrameDev {
     const GforbKeyPoint* kps;
@@ -121,6 +121,10 @@ struct QParams {
     int goodMode;                 // 1: good features (MAP: mpFlags bit2, LAST: srcGood) use thGood, the rest th (= th_rest)
     const uint8_t* srcGood;       // LAST + goodMode: batch x src.stride
     const int32_t* tgtMp0;        // PROJ2: F2.mvpMapPoints (batch x T.stride) = spMapPointsAlreadyFound
+    const int32_t *srcNode, *tgtNode;   // BOW: DBoW2 FeatureVector node of every KF / F feature (-1 = none)
+    int32_t* order;               // BOW out: batch x maxQ, the queries in (node, index) order = the reference's walk
+    const float* srcMinDist;      // KF: MapPoint::GetMinDistanceInvariance per KF keypoint
+    const uint8_t* qDesc;         // KF: MapPoint::GetDescriptor per KF keypoint (batch x src.stride x 32)
     const float *mpU, *mpV, *mpCos;     // MAP
     const int32_t* mpLevel;
     const uint8_t *mpFlags, *mpDesc;
@@ -198,6 +202,29 @@ __device__ __forceinline__ int enum_candidates(const int* __restrict__ cs, const
             }
             total += __popc(m);
         }
+    }
+    return total;
+}
+
+// SearchByBoW: the features of the target frame that sit in the query's vocabulary node, in index order (vIndicesF)
+template <bool WRITE>
+__device__ __forceinline__ int enum_node(const int32_t* __restrict__ tnode, const GforbKeyPoint* __restrict__ tkps,
+                                         const uint8_t* __restrict__ tdesc, int N2, int node, const uint32_t (&qd)[8],
+                                         uint32_t* __restrict__ out, int lane) {
+    const unsigned full = 0xffffffffu;
+    int total = 0;
+    for (int t0 = 0; t0 < N2; t0 += 32) {
+        const int t = t0 + lane;
+        const bool valid = t < N2 && tnode[t] == node;
+        const unsigned m = __ballot_sync(full, valid);
+        if (WRITE && valid) {
+            const uint4* dp = reinterpret_cast<const uint4*>(tdesc + (size_t)t * 32);
+            const uint4 d0 = __ldg(dp), d1 = __ldg(dp + 1);
+            const int dist = __popc(qd[0] ^ d0.x) + __popc(qd[1] ^ d0.y) + __popc(qd[2] ^ d0.z) + __popc(qd[3] ^ d0.w) +
+                             __popc(qd[4] ^ d1.x) + __popc(qd[5] ^ d1.y) + __popc(qd[6] ^ d1.z) + __popc(qd[7] ^ d1.w);
+            out[total + __popc(m & ((1u << lane) - 1u))] = ((uint32_t)dist << 20) | ((uint32_t)(tkps[t].octave & 15) << 16) | (uint32_t)t;
+        }
+        total += __popc(m);
     }
     return total;
 }
@@ -303,8 +330,63 @@ __global__ void __launch_bounds__(128) k_candidates(const QParams P, const Frame
             if (!(x == x) || !(y == y) || fabsf(x) > 1e30f || fabsf(y) > 1e30f) active = false;   // z = 0: no cell range exists
         }
         qdp = P.src.desc + i * 32;
+    } else if (MODE == M_KF) {
+        // SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist) (src/ORBmatcher.cc:2204-2336): the keyframe's map
+        // points projected with the current pose, level predicted from the distance to the camera centre
+        const size_t i = (size_t)b * P.src.stride + q;
+        if (P.srcMp[i] < 0) active = false;
+        if (P.srcOutlier && P.srcOutlier[i]) active = false;      // isBad() || sAlreadyFound.count(pMP)
+        if (active) {
+            const float* X = P.srcWorld + i * 3;
+            const float* Tm = P.Tcw + (size_t)b * 16;
+            float xc3[3], Ow[3];
+#pragma unroll
+            for (int rw = 0; rw < 3; rw++) {
+                double s = (double)Tm[rw * 4 + 0] * (double)X[0] + (double)Tm[rw * 4 + 1] * (double)X[1] +
+                           (double)Tm[rw * 4 + 2] * (double)X[2];
+                xc3[rw] = (float)s + Tm[rw * 4 + 3];
+                // Ow = -Rcw.t()*tcw: cv::gemm(alpha = -1, GEMM_1_T) on CV_32F, double accumulation over k = 0, 1, 2
+                double o = 0.0;
+                o = o + (double)Tm[0 * 4 + rw] * (double)Tm[0 * 4 + 3];
+                o = o + (double)Tm[1 * 4 + rw] * (double)Tm[1 * 4 + 3];
+                o = o + (double)Tm[2 * 4 + rw] * (double)Tm[2 * 4 + 3];
+                Ow[rw] = (float)(o * -1.0);
+            }
+            const float invzc = (float)(1.0 / (double)xc3[2]);
+            const float u = P.fx * xc3[0] * invzc + P.cx;
+            const float v = P.fy * xc3[1] * invzc + P.cy;
+            if (u < (float)G.iminX || u > (float)G.imaxX) active = false;
+            if (v < (float)G.iminY || v > (float)G.imaxY) active = false;
+            const float PO0 = X[0] - Ow[0], PO1 = X[1] - Ow[1], PO2 = X[2] - Ow[2];
+            const double n2 = (double)PO0 * (double)PO0 + (double)PO1 * (double)PO1 + (double)PO2 * (double)PO2;
+            const float dist3D = (float)sqrt(n2);
+            const float ratio = dist3D / P.srcMinDist[i];
+            int lvl = 0;                                          // std::lower_bound(mvScaleFactors, ratio)
+            while (lvl < P.nlevels && P.scale[lvl] < ratio) lvl++;
+            if (lvl >= P.nlevels) lvl = P.nlevels - 1;
+            x = u; y = v;
+            r = P.th * P.scale[lvl];
+            minL = lvl - 1; maxL = lvl + 1;
+        }
+        qdp = P.qDesc + i * 32;
+    } else if (MODE == M_BOW) {
+        const size_t i = (size_t)b * P.src.stride + q;
+        if (P.srcMp[i] < 0 || P.srcNode[i] < 0) active = false;
+        qdp = P.src.desc + i * 32;
     } else {
         x = P.ax[q]; y = P.ay[q]; r = P.ar[q]; minL = P.aMin[q]; maxL = P.aMax[q];
+    }
+    if (MODE == M_BOW) {
+        // position of this query in the reference's walk: FeatureVector nodes ascending, features of a node in index order
+        const size_t so = (size_t)b * P.src.stride;
+        const int myNode = P.srcNode[so + q];
+        int rank = 0;
+        for (int t = lane; t < Q; t += 32) {
+            const int nd = P.srcNode[so + t];
+            rank += (nd < myNode || (nd == myNode && t < q)) ? 1 : 0;
+        }
+        rank = __reduce_add_sync(0xffffffffu, rank);
+        if (lane == 0) P.order[(size_t)b * maxQ + rank] = q;
     }
     int2 meta = make_int2(0, 0);
     if (active) {
@@ -316,7 +398,11 @@ __global__ void __launch_bounds__(128) k_candidates(const QParams P, const Frame
         const int* cs = Gd.cellStart + (size_t)tb * (GRID_CELLS + 1);
         const int4* ent = Gd.entries + (size_t)tb * Gd.maxKp;
         const uint8_t* tdesc = T.desc + (size_t)tb * T.stride * 32;
-        int cnt = enum_candidates<false>(cs, ent, tdesc, G, x, y, r, minL, maxL, qd, nullptr, lane);
+        const int N2 = min(T.counts[tb], T.stride);
+        const int32_t* tnode = (MODE == M_BOW) ? P.tgtNode + (size_t)tb * T.stride : nullptr;
+        const int myNode = (MODE == M_BOW) ? P.srcNode[(size_t)b * P.src.stride + q] : 0;
+        int cnt = (MODE == M_BOW) ? enum_node<false>(tnode, T.kps + (size_t)tb * T.stride, tdesc, N2, myNode, qd, nullptr, lane)
+                                  : enum_candidates<false>(cs, ent, tdesc, G, x, y, r, minL, maxL, qd, nullptr, lane);
         if (cnt > 0) {
             int off = 0;
             if (lane == 0) off = atomicAdd(&poolCount[b], cnt);
@@ -324,7 +410,8 @@ __global__ void __launch_bounds__(128) k_candidates(const QParams P, const Frame
             if (off + cnt > poolCap) {
                 if (lane == 0) atomicExch(err, GFORB_ERR_OVERFLOW);
             } else {
-                enum_candidates<true>(cs, ent, tdesc, G, x, y, r, minL, maxL, qd, pool + (size_t)b * poolCap + off, lane);
+                if (MODE == M_BOW) enum_node<true>(tnode, T.kps + (size_t)tb * T.stride, tdesc, N2, myNode, qd, pool + (size_t)b * poolCap + off, lane);
+                else enum_candidates<true>(cs, ent, tdesc, G, x, y, r, minL, maxL, qd, pool + (size_t)b * poolCap + off, lane);
                 meta = make_int2(off, cnt);
             }
         }
@@ -349,6 +436,8 @@ struct RParams {
     float* prevMatched;   // INIT
     int32_t* nmatches;
     int* rotBinQ;         // INIT scratch: batch x maxQ
+    const int32_t* order; // BOW: batch x maxQ, query index per position of the walk
+    int thHigh;           // LAST / KF: acceptance threshold (TH_HIGH; ORBdist for the keyframe overload)
 };
 
 __device__ __forceinline__ int rot_bin(float a1, float a2) {
@@ -374,7 +463,7 @@ __global__ void __launch_bounds__(32) k_resolve(const RParams R) {
     const size_t tOff = (size_t)b * R.tgt.stride, sOff = (size_t)b * R.src.stride;
     for (int i = lane; i < N2; i += 32) {
         if (MODE == M_MAP || MODE == M_LAST || MODE == M_PROJ2) state[i] = R.tgtMp[tOff + i];
-        else if (MODE == M_WINDOW) state[i] = -1;
+        else if (MODE == M_WINDOW || MODE == M_BOW) state[i] = -1;
         else state[i] = INT_MAX;
         owner[i] = -1;
         rnd[i] = 0xffffffffu;
@@ -388,9 +477,10 @@ __global__ void __launch_bounds__(32) k_resolve(const RParams R) {
     __syncwarp();
     int accepted = 0;
     for (int qb = 0; qb < Q; qb += 32) {
-        const int q = qb + lane;
+        int q = qb + lane;
+        if (MODE == M_BOW && q < Q) q = R.order[(size_t)b * R.maxQ + q];       // (node, index) order of the reference's walk
         int2 meta = make_int2(0, 0);
-        if (q < Q) meta = R.qMeta[(size_t)b * R.maxQ + q];
+        if (qb + lane < Q) meta = R.qMeta[(size_t)b * R.maxQ + q];
         const uint32_t* list = R.pool + (size_t)b * R.poolCap + meta.x;
         const int cnt = meta.y;
         bool done = cnt <= 0;
@@ -414,9 +504,9 @@ __global__ void __launch_bounds__(32) k_resolve(const RParams R) {
                         else if (dist < best2) { bl2 = oct; best2 = dist; bi2 = i2; }
                     }
                 }
-                if (MODE == M_INIT) acc = best <= TH_LOW && (float)best < (float)best2 * R.nnratio;
+                if (MODE == M_INIT || MODE == M_BOW) acc = best <= TH_LOW && (float)best < (float)best2 * R.nnratio;   // :1219-1221, :790-792
                 else if (MODE == M_WINDOW || MODE == M_PROJ2) acc = (float)best <= (float)best2 * R.nnratio && best <= TH_HIGH;
-                else if (MODE == M_LAST) acc = best <= TH_HIGH;
+                else if (MODE == M_LAST) acc = best <= R.thHigh;
                 else acc = best <= TH_HIGH && !(bl == bl2 && (float)best > R.nnratio * (float)best2);
                 if (bi < 0) acc = false;
             }
@@ -454,11 +544,13 @@ __global__ void __launch_bounds__(32) k_resolve(const RParams R) {
                             owner[bi] = bin;
                             atomicAdd(&hist[bin], 1);
                         }
-                    } else if (MODE == M_WINDOW) {
+                    } else if (MODE == M_WINDOW || MODE == M_BOW) {
                         state[bi] = R.srcMp[sOff + q];
-                        const int bin = rot_bin(R.src.kps[sOff + q].angle, R.tgt.kps[tOff + bi].angle);
-                        owner[bi] = bin;
-                        atomicAdd(&hist[bin], 1);
+                        if (MODE == M_WINDOW || R.checkOri) {                    // :1064 pushes always, :796 under mbCheckOrientation
+                            const int bin = rot_bin(R.src.kps[sOff + q].angle, R.tgt.kps[tOff + bi].angle);
+                            owner[bi] = bin;
+                            atomicAdd(&hist[bin], 1);
+                        }
                     } else {
                         const int prev = owner[bi];
                         if (prev >= 0) R.matches12[sOff + prev] = -1;           // steal (:1230-1234)
@@ -522,7 +614,7 @@ __global__ void __launch_bounds__(32) k_resolve(const RParams R) {
                     if (MODE == M_LAST) { R.tgtMp[tOff + i] = -1; R.tgtScore[tOff + i] = 999; }
                 }
             }
-        if (MODE == M_WINDOW)
+        if (MODE == M_WINDOW || MODE == M_BOW)
             for (int i = lane; i < R.tgt.stride; i += 32) R.tgtMp[tOff + i] = (i < N2) ? state[i] : -1;
         total = __reduce_add_sync(full, accepted - removed);
     }
@@ -941,6 +1033,7 @@ int gforb_matcher_create(const GforbMatcherConfig* cfg, GforbMatcher** out) {
     GF_CUDA_OK(raise_dyn_smem(k_resolve<M_MAP>, smem, cfg->device));
     GF_CUDA_OK(raise_dyn_smem(k_resolve<M_LAST>, smem, cfg->device));
     GF_CUDA_OK(raise_dyn_smem(k_resolve<M_PROJ2>, smem, cfg->device));
+    GF_CUDA_OK(raise_dyn_smem(k_resolve<M_BOW>, smem, cfg->device));
         return GFORB_OK;
     };
     if (const int rc = init()) { gforb_matcher_destroy(M); return rc; }   // a failure part-way frees what was allocated
@@ -1280,6 +1373,7 @@ static int sbp_last(GforbMatcher* M, const GforbFrameSet* cur, const GforbFrameS
     R.src = S; R.tgt = T; R.pool = M->d_pool; R.poolCap = M->poolCap; R.qMeta = M->d_qMeta; R.maxQ = M->cfg.max_queries;
     R.maxKp = M->cfg.max_keypoints; R.qCounts = S.counts; R.srcMp = P.srcMp; R.nnratio = nnratio;
     R.checkOri = check_orientation; R.tgtMp = dMp; R.tgtScore = dSc; R.nmatches = dN; R.rotBinQ = M->d_rotBinQ;
+    R.thHigh = TH_HIGH;
     run_resolve<M_LAST>(M, c, R, batch);
     return end_call(M, c, flags);
 }
@@ -1368,6 +1462,77 @@ int gforb_search_by_projection_window(GforbMatcher* M, const GforbFrameSet* F1, 
     R.maxKp = M->cfg.max_keypoints; R.qCounts = S.counts; R.srcMp = P.srcMp; R.nnratio = nnratio;
     R.tgtMp = dM2; R.tgtScore = dSc; R.nmatches = dN; R.rotBinQ = M->d_rotBinQ;
     run_resolve<M_PROJ2>(M, c, R, batch);
+    return end_call(M, c, flags);
+}
+
+int gforb_search_by_bow(GforbMatcher* M, const GforbFrameSet* KF, const int32_t* kf_mappoints, const int32_t* kf_nodes,
+                        const GforbFrameSet* F, const int32_t* f_nodes, int batch, float nnratio, int check_orientation,
+                        int32_t* matches, int32_t* nmatches, int flags, void* stream) {
+    Ctx c;
+    int rc = begin_call(M, batch, flags, stream, c);
+    if (rc) return rc;
+    if ((rc = check_frames(M, KF)) || (rc = check_frames(M, F))) return rc;
+    if (!kf_mappoints || !kf_nodes || !f_nodes || !matches || !nmatches) return GFORB_ERR_ARG;
+    if (KF->kp_stride > M->cfg.max_queries) return GFORB_ERR_CAPACITY;
+    if (batch == 0) return GFORB_OK;
+    FrameDev S = c.frame(KF, batch), T = c.frame(F, batch);
+    GridGeom G = geom_of(F);
+    QParams P;
+    memset(&P, 0, sizeof(P));
+    fill_scale(M, P);
+    P.src = S; P.srcMp = c.in(kf_mappoints, (size_t)batch * KF->kp_stride);
+    P.srcNode = c.in(kf_nodes, (size_t)batch * KF->kp_stride);
+    P.tgtNode = c.in(f_nodes, (size_t)batch * F->kp_stride);
+    P.order = M->d_rotBinQ;                        // the INIT scratch doubles as the walk order of this call
+    int32_t* dM = c.out(matches, (size_t)batch * F->kp_stride, false);
+    int32_t* dN = c.out(nmatches, (size_t)batch, false);
+    if (c.rc) return c.rc;
+    run_candidates<M_BOW>(M, c, P, T, G, batch, KF->kp_stride);     // no grid: candidates come from the node lists
+    RParams R;
+    memset(&R, 0, sizeof(R));
+    R.src = S; R.tgt = T; R.pool = M->d_pool; R.poolCap = M->poolCap; R.qMeta = M->d_qMeta; R.maxQ = M->cfg.max_queries;
+    R.maxKp = M->cfg.max_keypoints; R.qCounts = S.counts; R.srcMp = P.srcMp; R.nnratio = nnratio;
+    R.checkOri = check_orientation; R.tgtMp = dM; R.nmatches = dN; R.rotBinQ = M->d_rotBinQ; R.order = M->d_rotBinQ;
+    run_resolve<M_BOW>(M, c, R, batch);
+    return end_call(M, c, flags);
+}
+
+int gforb_search_by_projection_keyframe(GforbMatcher* M, const GforbFrameSet* cur, const GforbFrameSet* KF, int batch,
+                                        const int32_t* kf_mappoints, const uint8_t* kf_skip, const float* kf_world,
+                                        const float* kf_min_distance, const uint8_t* kf_mp_descriptors, const float* Tcw,
+                                        float fx, float fy, float cx, float cy, float th, int orb_dist, int check_orientation,
+                                        int32_t* cur_mappoints, int32_t* cur_score, int32_t* nmatches, int flags, void* stream) {
+    Ctx c;
+    int rc = begin_call(M, batch, flags, stream, c);
+    if (rc) return rc;
+    if ((rc = check_frames(M, cur)) || (rc = check_frames(M, KF))) return rc;
+    if (!kf_mappoints || !kf_world || !kf_min_distance || !kf_mp_descriptors || !Tcw || !cur_mappoints || !cur_score || !nmatches)
+        return GFORB_ERR_ARG;
+    if (KF->kp_stride > M->cfg.max_queries) return GFORB_ERR_CAPACITY;
+    if (batch == 0) return GFORB_OK;
+    FrameDev T = c.frame(cur, batch), S = c.frame(KF, batch);
+    GridGeom G = geom_of(cur);
+    QParams P;
+    memset(&P, 0, sizeof(P));
+    fill_scale(M, P);
+    const size_t ns = (size_t)batch * KF->kp_stride;
+    P.src = S; P.srcMp = c.in(kf_mappoints, ns); P.srcOutlier = c.in(kf_skip, ns);
+    P.srcWorld = c.in(kf_world, ns * 3); P.srcMinDist = c.in(kf_min_distance, ns); P.qDesc = c.in(kf_mp_descriptors, ns * 32);
+    P.Tcw = c.in(Tcw, (size_t)batch * 16);
+    P.fx = fx; P.fy = fy; P.cx = cx; P.cy = cy; P.th = th;
+    int32_t* dMp = c.out(cur_mappoints, (size_t)batch * cur->kp_stride, true);
+    int32_t* dSc = c.out(cur_score, (size_t)batch * cur->kp_stride, true);
+    int32_t* dN = c.out(nmatches, (size_t)batch, false);
+    if (c.rc) return c.rc;
+    build_grid(M, c, T, G, batch);
+    run_candidates<M_KF>(M, c, P, T, G, batch, KF->kp_stride);
+    RParams R;                                     // the walk, the claims and the rotation histogram are those of (Cur, Last)
+    memset(&R, 0, sizeof(R));
+    R.src = S; R.tgt = T; R.pool = M->d_pool; R.poolCap = M->poolCap; R.qMeta = M->d_qMeta; R.maxQ = M->cfg.max_queries;
+    R.maxKp = M->cfg.max_keypoints; R.qCounts = S.counts; R.srcMp = P.srcMp; R.nnratio = 0.0f;
+    R.checkOri = check_orientation; R.tgtMp = dMp; R.tgtScore = dSc; R.nmatches = dN; R.rotBinQ = M->d_rotBinQ;
+    R.thHigh = orb_dist;
+    run_resolve<M_LAST>(M, c, R, batch);
     return end_call(M, c, flags);
 }
 

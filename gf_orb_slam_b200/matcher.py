@@ -306,6 +306,40 @@ class ORBmatcher:
             C.c_void_p(stream or 0)), "gforb_search_by_projection_window")
         return nmatches
 
+    def _nm(self, n, like, out_dev):
+        if out_dev:
+            import torch
+            return torch.empty(n, dtype=torch.int32, device=like.device)
+        return np.empty(n, np.int32)
+
+    def SearchByBoW(self, KF: Frames, kf_mappoints, kf_nodes, F: Frames, f_nodes, matches, *, nmatches=None, stream=None, sync=True):
+        """ORBmatcher::SearchByBoW(KeyFrame*, Frame&, vpMapPointMatches) (src/ORBmatcher.cc:724-853).  *_nodes: DBoW2
+        FeatureVector node per feature (-1 = none); matches (B, F.stride) int32 out."""
+        out_dev = is_device(matches)
+        if nmatches is None:
+            nmatches = self._nm(F.batch, matches, out_dev)
+        a, b = KF.cstruct(), F.cstruct()
+        check(_lib.lib().gforb_search_by_bow(self._h, C.byref(a), ptr(kf_mappoints), ptr(kf_nodes), C.byref(b), ptr(f_nodes), F.batch,
+                                             self.mfNNratio, int(self.mbCheckOrientation), ptr(matches), ptr(nmatches),
+                                             self._flags(F.device, out_dev, sync), C.c_void_p(stream or 0)), "gforb_search_by_bow")
+        return nmatches
+
+    def SearchByProjectionKeyFrame(self, Cur: Frames, KF: Frames, kf_mappoints, kf_skip, kf_world, kf_min_distance, kf_mp_desc, Tcw, K,
+                                   th, ORBdist, cur_mappoints, cur_score, *, nmatches=None, stream=None, sync=True):
+        """ORBmatcher::SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist) (src/ORBmatcher.cc:2204-2336);
+        kf_skip non-zero = isBad() or in sAlreadyFound; cur_mappoints / cur_score are updated in place."""
+        out_dev = is_device(cur_mappoints)
+        if nmatches is None:
+            nmatches = self._nm(Cur.batch, cur_mappoints, out_dev)
+        fx, fy, cx, cy = [float(v) for v in K]
+        a, b = Cur.cstruct(), KF.cstruct()
+        check(_lib.lib().gforb_search_by_projection_keyframe(
+            self._h, C.byref(a), C.byref(b), Cur.batch, ptr(kf_mappoints), ptr(kf_skip), ptr(kf_world), ptr(kf_min_distance),
+            ptr(kf_mp_desc), ptr(Tcw), fx, fy, cx, cy, float(th), int(ORBdist), int(self.mbCheckOrientation), ptr(cur_mappoints),
+            ptr(cur_score), ptr(nmatches), self._flags(Cur.device, out_dev, sync), C.c_void_p(stream or 0)),
+            "gforb_search_by_projection_keyframe")
+        return nmatches
+
     # -- all-pairs top-2 against a database shard resident in HBM (torch CUDA uint8 tensors)
     def AllPairsTop2(self, queries, db, idx_base=0, *, out=None, stream=None, sync=True):
         import torch

@@ -239,6 +239,30 @@ int gforb_search_by_projection_window(GforbMatcher* h, const GforbFrameSet* F1, 
                                       float cx, float cy, int window_size, float nnratio, int32_t* matches2, int32_t* f2_score,
                                       int32_t* nmatches, int flags, void* stream);
 
+/* ORBmatcher::SearchByBoW(KeyFrame* pKF, Frame& F, vector<MapPoint*>& vpMapPointMatches) (src/ORBmatcher.cc:724-853;
+ * Tracking::TrackReferenceKeyFrame and Relocalization).  The vocabulary transform is the caller's (DBoW2): kf_nodes /
+ * f_nodes = the FeatureVector node id of every keyframe / frame feature (batch x kp_stride, -1 = in no node).  The walk is
+ * the reference's: nodes ascending, keyframe features of a node in index order, every frame feature of the same node that
+ * is still unmatched as candidate, best <= TH_LOW and best < nnratio * second, rotation histogram under check_orientation.
+ * kf_mappoints: batch x KF.kp_stride ids of pKF->GetMapPointMatches() (-1 = NULL or isBad()); KF->keypoints = the
+ * keyframe's undistorted keys (angle), KF->descriptors its descriptors.  matches: out, batch x F.kp_stride (id or -1). */
+int gforb_search_by_bow(GforbMatcher* h, const GforbFrameSet* KF, const int32_t* kf_mappoints, const int32_t* kf_nodes,
+                        const GforbFrameSet* F, const int32_t* f_nodes, int batch, float nnratio, int check_orientation,
+                        int32_t* matches, int32_t* nmatches, int flags, void* stream);
+
+/* ORBmatcher::SearchByProjection(Frame& CurrentFrame, KeyFrame* pKF, const set<MapPoint*>& sAlreadyFound, float th,
+ * int ORBdist) (src/ORBmatcher.cc:2204-2336; Tracking::Relocalization).  Per keyframe keypoint (batch x KF.kp_stride):
+ * kf_mappoints = id of pKF->GetMapPointMatches()[i] (-1 = NULL), kf_skip (may be NULL) non-zero = isBad() or in
+ * sAlreadyFound, kf_world (x 3) / kf_min_distance / kf_mp_descriptors (x 32) = GetWorldPos / GetMinDistanceInvariance /
+ * GetDescriptor of that map point; KF->keypoints = the keyframe's undistorted keys (angle).  Tcw: batch x 16 (Current.mTcw);
+ * the level is predicted from |x3Dw - Ow| / minDistance, the window is th * scale[level] over levels level-1 .. level+1,
+ * the best unclaimed candidate is taken if its distance is <= orb_dist.  cur_mappoints / cur_score: in/out. */
+int gforb_search_by_projection_keyframe(GforbMatcher* h, const GforbFrameSet* cur, const GforbFrameSet* KF, int batch,
+                                        const int32_t* kf_mappoints, const uint8_t* kf_skip, const float* kf_world,
+                                        const float* kf_min_distance, const uint8_t* kf_mp_descriptors, const float* Tcw,
+                                        float fx, float fy, float cx, float cy, float th, int orb_dist, int check_orientation,
+                                        int32_t* cur_mappoints, int32_t* cur_score, int32_t* nmatches, int flags, void* stream);
+
 /* Batched all-pairs Hamming top-2 of n_q query descriptors against one database shard of n_db descriptors
  * (BASELINE.json config 5; the reference's brute-force analogue is the DescriptorDistance loop of
  * MapPoint::ComputeDistinctiveDescriptors, src/MapPoint.cc:225-250).  out: n_q x 2 packed keys

@@ -21,6 +21,8 @@
 #include <cstring>
 #include <stdexcept>
 #include <string>
+#include <map>
+#include <set>
 #include <vector>
 
 #include "../gforb.h"
@@ -170,6 +172,7 @@ struct Frame {
     float mTcw[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
     float mRcw[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}, mtcw[3] = {0, 0, 0}, mOw[3] = {0, 0, 0};   // Frame::UpdatePoseMatrices
     float fx = 0, fy = 0, cx = 0, cy = 0;
+    std::map<unsigned, std::vector<unsigned>> mFeatVec;   // DBoW2::FeatureVector (node id -> feature indices), filled by the caller's ComputeBoW
 
     Frame() {}
     // what Frame::Frame does for this path after extraction (src/Frame.cc:40-131; no distortion -> mvKeysUn = mvKeys)
@@ -183,6 +186,24 @@ struct Frame {
         float s = 1.0f;
         for (int i = 1; i < nlevels; i++) { s = s * scaleFactor; mvLevelSigma2[i] = s * s; }
     }
+};
+
+// The KeyFrame fields the Tracking-side matcher overloads read (include/KeyFrame.h): GetMapPointMatches(), GetFeatureVector(),
+// GetDescriptor(i), GetKeyPointUn(i).  Built from a Frame like the reference's KeyFrame::KeyFrame(Frame&, Map*, KeyFrameDatabase*).
+struct KeyFrame {
+    int N = 0;
+    std::vector<gforb_cv::KeyPoint> mvKeysUn;
+    gforb_cv::Mat mDescriptors;
+    std::vector<MapPoint*> mvpMapPoints;
+    std::map<unsigned, std::vector<unsigned>> mFeatVec;
+    int mnMinX = 0, mnMaxX = 0, mnMinY = 0, mnMaxY = 0;
+    KeyFrame() {}
+    explicit KeyFrame(const Frame& F)
+        : N(F.N), mvKeysUn(F.mvKeysUn), mDescriptors(F.mDescriptors), mvpMapPoints(F.mvpMapPoints), mFeatVec(F.mFeatVec),
+          mnMinX(F.mnMinX), mnMaxX(F.mnMaxX), mnMinY(F.mnMinY), mnMaxY(F.mnMaxY) {}
+    std::vector<MapPoint*> GetMapPointMatches() const { return mvpMapPoints; }
+    const std::map<unsigned, std::vector<unsigned>>& GetFeatureVector() const { return mFeatVec; }
+    gforb_cv::KeyPoint GetKeyPointUn(size_t i) const { return mvKeysUn[i]; }
 };
 
 // ------------------------------------------------------------------------------------------------ ORBmatcher
@@ -445,6 +466,60 @@ public:
         return n;
     }
 
+    // src/ORBmatcher.cc:724-853 (Tracking::TrackReferenceKeyFrame, Relocalization): matches between the keyframe's map points
+    // and the frame's keypoints over the features that share a vocabulary node.  The FeatureVectors are the caller's
+    // (DBoW2 transform); a feature listed under several nodes keeps the last one, as DBoW2 never does that.
+    int SearchByBoW(KeyFrame* pKF, Frame& F, std::vector<MapPoint*>& vpMapPointMatches) {
+        vpMapPointMatches = std::vector<MapPoint*>(F.mvpMapPoints.size(), static_cast<MapPoint*>(nullptr));
+        if (!pKF || pKF->N == 0 || F.N == 0) return 0;
+        ensure(std::max(pKF->N, F.N), pKF->N, F.mnScaleLevels, F.mfScaleFactor);
+        FlatFrame a(*pKF), b(F);
+        std::vector<int32_t> ids(pKF->N, -1), kn(pKF->N, -1), fn(F.N, -1), m(F.N, -1);
+        for (int i = 0; i < pKF->N; i++) if (pKF->mvpMapPoints[i] && !pKF->mvpMapPoints[i]->isBad()) ids[i] = i;
+        for (const auto& nd : pKF->mFeatVec) for (unsigned i : nd.second) if ((int)i < pKF->N) kn[i] = (int32_t)nd.first;
+        for (const auto& nd : F.mFeatVec) for (unsigned i : nd.second) if ((int)i < F.N) fn[i] = (int32_t)nd.first;
+        int32_t n = 0;
+        gforb_throw(gforb_search_by_bow(h_, &a.set, ids.data(), kn.data(), &b.set, fn.data(), 1, mfNNratio, mbCheckOrientation ? 1 : 0,
+                                        m.data(), &n, 0, nullptr), "SearchByBoW(KeyFrame, Frame)");
+        for (int j = 0; j < F.N; j++) if (m[j] >= 0) vpMapPointMatches[j] = pKF->mvpMapPoints[m[j]];
+        return n;
+    }
+
+    // src/ORBmatcher.cc:2204-2336 (Tracking::Relocalization): project the keyframe's map points that were not found yet with
+    // the current pose; CurrentFrame.mvpMapPoints / mvpMatchScore are updated in place.
+    int SearchByProjection(Frame& CurrentFrame, KeyFrame* pKF, const std::set<MapPoint*>& sAlreadyFound, const float th, const int ORBdist) {
+        if (!pKF || pKF->N == 0 || CurrentFrame.N == 0) return 0;
+        ensure(std::max(pKF->N, CurrentFrame.N), pKF->N, CurrentFrame.mnScaleLevels, CurrentFrame.mfScaleFactor);
+        FlatFrame cur(CurrentFrame), kf(*pKF);
+        const int NK = pKF->N;
+        std::vector<int32_t> ids(NK, -1);
+        std::vector<uint8_t> skip(NK, 0), mpd((size_t)NK * 32, 0);
+        std::vector<float> world((size_t)NK * 3, 0.f), mind(NK, 1.f);
+        for (int i = 0; i < NK; i++) {
+            MapPoint* p = pKF->mvpMapPoints[i];
+            if (!p) continue;
+            ids[i] = i;
+            skip[i] = (p->isBad() || sAlreadyFound.count(p)) ? 1 : 0;
+            std::memcpy(&world[(size_t)i * 3], p->mWorldPos, 12);
+            mind[i] = p->mfMinDistance;
+            std::memcpy(&mpd[(size_t)i * 32], p->mDescriptor, 32);
+        }
+        std::vector<int32_t> cids(CurrentFrame.N, -1), score(CurrentFrame.mvpMatchScore.begin(), CurrentFrame.mvpMatchScore.end());
+        for (int j = 0; j < CurrentFrame.N; j++) if (CurrentFrame.mvpMapPoints[j]) cids[j] = NK;   // already claimed
+        int32_t n = 0;
+        gforb_throw(gforb_search_by_projection_keyframe(h_, &cur.set, &kf.set, 1, ids.data(), skip.data(), world.data(), mind.data(),
+                                                        mpd.data(), CurrentFrame.mTcw, CurrentFrame.fx, CurrentFrame.fy, CurrentFrame.cx,
+                                                        CurrentFrame.cy, th, ORBdist, mbCheckOrientation ? 1 : 0, cids.data(),
+                                                        score.data(), &n, 0, nullptr),
+                    "SearchByProjection(Current, KeyFrame)");
+        for (int j = 0; j < CurrentFrame.N; j++) {
+            if (cids[j] >= 0 && cids[j] < NK) CurrentFrame.mvpMapPoints[j] = pKF->mvpMapPoints[cids[j]];
+            else if (cids[j] < 0) CurrentFrame.mvpMapPoints[j] = nullptr;
+            CurrentFrame.mvpMatchScore[j] = score[j];
+        }
+        return n;
+    }
+
     float mfNNratio;
     bool mbCheckOrientation;
 
@@ -454,7 +529,8 @@ private:
         std::vector<uint8_t> desc;
         int32_t count;
         GforbFrameSet set;
-        explicit FlatFrame(const Frame& F) : desc((size_t)F.N * 32), count(F.N) {
+        template <class FrameLike>
+        explicit FlatFrame(const FrameLike& F) : desc((size_t)F.N * 32), count(F.N) {
             for (int i = 0; i < F.N; i++) std::memcpy(&desc[(size_t)i * 32], F.mDescriptors.ptr(i), 32);
             set.keypoints = reinterpret_cast<const GforbKeyPoint*>(F.mvKeysUn.data());
             set.descriptors = desc.data(); set.counts = &count; set.kp_stride = F.N;

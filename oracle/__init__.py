@@ -276,6 +276,26 @@ def search_by_projection_window(F1: Frame, F2: Frame, f1_world: np.ndarray, wind
     return n, m2
 
 
+def search_by_bow(KF: Frame, kf_nodes, F: Frame, f_nodes, nnratio=0.7, checkOri=True):
+    """ORBmatcher::SearchByBoW(KeyFrame*, Frame&, vpMapPointMatches) (src/ORBmatcher.cc:724-853); KF carries the keyframe's
+    map-point ids (set_mappoints, bad points as -1); *_nodes = DBoW2 FeatureVector node id per feature (-1 = none).
+    Returns (nmatches, matches per F keypoint)."""
+    kn = np.ascontiguousarray(kf_nodes, np.int32); fn = np.ascontiguousarray(f_nodes, np.int32)
+    m = np.full(F.N, -1, np.int32)
+    n = lib().orc_search_by_bow(KF.h, _p(kn), F.h, _p(fn), _p(m), C.c_float(nnratio), int(checkOri))
+    return n, m
+
+
+def search_by_projection_keyframe(Cur: Frame, KF: Frame, kf_skip, kf_world, kf_min_dist, kf_mp_desc, th: float, orb_dist: int,
+                                  checkOri=True):
+    """ORBmatcher::SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist) (src/ORBmatcher.cc:2204-2336); Cur carries
+    camera + pose (set_camera) and its map points; updated in place (Cur.matches()).  Returns nmatches."""
+    sk = np.ascontiguousarray(kf_skip, np.uint8); w = np.ascontiguousarray(kf_world, np.float32)
+    md = np.ascontiguousarray(kf_min_dist, np.float32); d = np.ascontiguousarray(kf_mp_desc, np.uint8)
+    return lib().orc_search_by_projection_keyframe(Cur.h, KF.h, _p(sk), _p(w), _p(md), _p(d), C.c_float(th), int(orb_dist),
+                                                   C.c_float(0.9), int(checkOri))
+
+
 def window_search(F1: Frame, F2: Frame, window: int, minL=-1, maxL=0x7FFFFFFF, nnratio=0.9, checkOri=True):
     m2 = np.empty(F2.N, np.int32)
     n = lib().orc_window_search(F1.h, F2.h, window, _p(m2), minL, maxL, C.c_float(nnratio), int(checkOri))

@@ -191,6 +191,18 @@ int orc_search_by_projection_window(void* f1, void* f2, const float* f1World, in
     memcpy(matches2, m2.data(), sizeof(int) * m2.size());
     return n;
 }
+int orc_search_by_bow(void* kf, const int* kfNode, void* f, const int* fNode, int* matches, float nnratio, int checkOri) {
+    ORBmatcher m(nnratio, checkOri != 0);
+    std::vector<int> mm;
+    int n = m.SearchByBoW(*(const Frame*)kf, kfNode, *(const Frame*)f, fNode, mm);
+    memcpy(matches, mm.data(), sizeof(int) * mm.size());
+    return n;
+}
+int orc_search_by_projection_keyframe(void* cur, void* kf, const uint8_t* kfSkip, const float* kfWorld, const float* kfMinDist,
+                                      const uint8_t* kfMpDesc, float th, int ORBdist, float nnratio, int checkOri) {
+    ORBmatcher m(nnratio, checkOri != 0);
+    return m.SearchByProjection(*(Frame*)cur, *(const Frame*)kf, kfSkip, kfWorld, kfMinDist, kfMpDesc, th, ORBdist);
+}
 int orc_window_search(void* f1, void* f2, int windowSize, int* matches2, int minLevel, int maxLevel, float nnratio, int checkOri) {
     ORBmatcher m(nnratio, checkOri != 0);
     std::vector<int> m2;

@@ -137,6 +137,10 @@ public:
     int SearchForInitialization(const Frame& F1, const Frame& F2, std::vector<float>& vbPrevMatched /*N1 x 2*/,
                                 std::vector<int>& vnMatches12, int windowSize);
     int SearchByProjection(const Frame& F1, Frame& F2, const float* f1World /*N1 x 3*/, int windowSize, std::vector<int>& vpMapPointMatches2);
+    // :724-853 (TrackReferenceKeyFrame / Relocalization) and :2204-2336 (Relocalization)
+    int SearchByBoW(const Frame& KF, const int* kfNode, const Frame& F, const int* fNode, std::vector<int>& vpMapPointMatches);
+    int SearchByProjection(Frame& CurrentFrame, const Frame& KF, const uint8_t* kfSkip, const float* kfWorld, const float* kfMinDist,
+                           const uint8_t* kfMpDesc, float th, int ORBdist);
     int WindowSearch(const Frame& F1, const Frame& F2, int windowSize, std::vector<int>& vpMapPointMatches2,
                      int minScaleLevel = -1, int maxScaleLevel = 0x7fffffff);
     static void ComputeThreeMaxima(const std::vector<int>* histo, int L, int& ind1, int& ind2, int& ind3);

@@ -5,6 +5,7 @@
 #include "oracle.hpp"
 #include <set>
 #include <algorithm>
+#include <map>
 #include <climits>
 #include <cmath>
 #include <cstring>
@@ -477,6 +478,149 @@ void ORBmatcher::ComputeThreeMaxima(const std::vector<int>* histo, int L, int& i
     }
     if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
     else if (max3 < 0.1f * (float)max1) ind3 = -1;
+}
+
+// src/ORBmatcher.cc:724-853: SearchByBoW(KeyFrame* pKF, Frame& F, vector<MapPoint*>& vpMapPointMatches).  The DBoW2
+// FeatureVector (std::map<NodeId, vector<unsigned>>, filled feature by feature in index order by
+// Thirdparty/DBoW2/DBoW2/FeatureVector.cpp:addFeature) is rebuilt from the node id of every feature; a negative node id
+// leaves the feature out.  KF.mvpMapPoints = pKF->GetMapPointMatches() with bad points as -1.
+int ORBmatcher::SearchByBoW(const Frame& KF, const int* kfNode, const Frame& F, const int* fNode, std::vector<int>& vpMapPointMatches) {
+    const std::vector<int>& vpMapPointsKF = KF.mvpMapPoints;
+    vpMapPointMatches.assign(F.mvpMapPoints.size(), -1);
+    std::map<int, std::vector<unsigned>> vFeatVecKF, vFeatVecF;
+    for (int i = 0; i < KF.N; i++) if (kfNode[i] >= 0) vFeatVecKF[kfNode[i]].push_back((unsigned)i);
+    for (int i = 0; i < F.N; i++) if (fNode[i] >= 0) vFeatVecF[fNode[i]].push_back((unsigned)i);
+    int nmatches = 0;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = 1.0f / HISTO_LENGTH;
+    auto KFit = vFeatVecKF.begin(), KFend = vFeatVecKF.end();
+    auto Fit = vFeatVecF.begin(), Fend = vFeatVecF.end();
+    while (KFit != KFend && Fit != Fend) {
+        if (KFit->first == Fit->first) {
+            const std::vector<unsigned>& vIndicesKF = KFit->second;
+            const std::vector<unsigned>& vIndicesF = Fit->second;
+            for (size_t iKF = 0; iKF < vIndicesKF.size(); iKF++) {
+                const unsigned realIdxKF = vIndicesKF[iKF];
+                const int pMP = vpMapPointsKF[realIdxKF];
+                if (pMP < 0) continue;                                   // NULL or isBad()
+                const uint8_t* dKF = &KF.mDescriptors[(size_t)realIdxKF * 32];
+                int bestDist1 = INT_MAX, bestIdxF = -1, bestDist2 = INT_MAX;
+                for (size_t iF = 0; iF < vIndicesF.size(); iF++) {
+                    const unsigned realIdxF = vIndicesF[iF];
+                    if (vpMapPointMatches[realIdxF] >= 0) continue;
+                    const int dist = DescriptorDistance(dKF, &F.mDescriptors[(size_t)realIdxF * 32]);
+                    if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdxF = (int)realIdxF; }
+                    else if (dist < bestDist2) bestDist2 = dist;
+                }
+                if (bestDist1 <= TH_LOW) {
+                    if ((float)bestDist1 < mfNNratio * (float)bestDist2) {
+                        vpMapPointMatches[bestIdxF] = pMP;
+                        if (mbCheckOrientation) {
+                            float rot = KF.mvKeysUn[realIdxKF].angle - F.mvKeysUn[bestIdxF].angle;
+                            if (rot < 0.0) rot += 360.0f;
+                            int bin = std::round(rot * factor);
+                            if (bin == HISTO_LENGTH) bin = 0;
+                            rotHist[bin].push_back(bestIdxF);
+                        }
+                        nmatches++;
+                    }
+                }
+            }
+            KFit++;
+            Fit++;
+        } else if (KFit->first < Fit->first) {
+            KFit = vFeatVecKF.lower_bound(Fit->first);
+        } else {
+            Fit = vFeatVecF.lower_bound(KFit->first);
+        }
+    }
+    if (mbCheckOrientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        ComputeThreeMaxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (int idx : rotHist[i]) { vpMapPointMatches[idx] = -1; nmatches--; }
+        }
+    }
+    return nmatches;
+}
+
+// src/ORBmatcher.cc:2204-2336: SearchByProjection(Frame& CurrentFrame, KeyFrame* pKF, const set<MapPoint*>& sAlreadyFound,
+// float th, int ORBdist) (Tracking::Relocalization).  KF.mvpMapPoints = pKF->GetMapPointMatches(), kfSkip[i] != 0 stands
+// for pMP->isBad() || sAlreadyFound.count(pMP); kfWorld / kfMinDist / kfMpDesc = GetWorldPos / GetMinDistanceInvariance /
+// GetDescriptor of that map point; KF.mvKeysUn[i].angle = pKF->GetKeyPointUn(i).angle.
+int ORBmatcher::SearchByProjection(Frame& CurrentFrame, const Frame& KF, const uint8_t* kfSkip, const float* kfWorld,
+                                   const float* kfMinDist, const uint8_t* kfMpDesc, float th, int ORBdist) {
+    int nmatches = 0;
+    const float* T = CurrentFrame.mTcw;
+    // const cv::Mat Ow = -Rcw.t()*tcw: cv::gemm(Rcw, tcw, -1, GEMM_1_T) on CV_32F accumulates every output in double over
+    // k = 0, 1, 2, scales by alpha and casts (GEMMSingleMul<float,double>; pinned against cv2 4.13 in tests/test_oracle_cv.py)
+    float Ow[3];
+    for (int i = 0; i < 3; i++) {
+        double s = 0;
+        for (int k = 0; k < 3; k++) s += (double)T[k * 4 + i] * (double)T[k * 4 + 3];
+        Ow[i] = (float)(s * -1.0);
+    }
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = 1.0f / HISTO_LENGTH;
+    for (size_t i = 0; i < KF.mvpMapPoints.size(); i++) {
+        const int pMP = KF.mvpMapPoints[i];
+        if (pMP < 0) continue;
+        if (kfSkip && kfSkip[i]) continue;
+        const float* X = kfWorld + 3 * i;
+        float xc3[3];                                    // Rcw*x3Dw+tcw: see SearchByProjection(Cur, Last) above
+        for (int r = 0; r < 3; r++) {
+            double s = (double)T[r * 4 + 0] * X[0] + (double)T[r * 4 + 1] * X[1] + (double)T[r * 4 + 2] * X[2];
+            xc3[r] = (float)s + T[r * 4 + 3];
+        }
+        const float xc = xc3[0], yc = xc3[1];
+        const float invzc = 1.0 / xc3[2];
+        float u = CurrentFrame.fx * xc * invzc + CurrentFrame.cx;
+        float v = CurrentFrame.fy * yc * invzc + CurrentFrame.cy;
+        if (u < CurrentFrame.mnMinX || u > CurrentFrame.mnMaxX) continue;
+        if (v < CurrentFrame.mnMinY || v > CurrentFrame.mnMaxY) continue;
+        // predicted scale level: cv::norm(x3Dw - Ow) (double accumulation, as in isInFrustum below)
+        const float minDistance = kfMinDist[i];
+        const float PO[3] = {X[0] - Ow[0], X[1] - Ow[1], X[2] - Ow[2]};
+        float dist3D = (float)std::sqrt((double)PO[0] * PO[0] + (double)PO[1] * PO[1] + (double)PO[2] * PO[2]);
+        float ratio = dist3D / minDistance;
+        auto it = std::lower_bound(CurrentFrame.mvScaleFactors.begin(), CurrentFrame.mvScaleFactors.end(), ratio);
+        const int nPredictedLevel = std::min((int)(it - CurrentFrame.mvScaleFactors.begin()), (int)CurrentFrame.mvScaleFactors.size() - 1);
+        float radius = th * CurrentFrame.mvScaleFactors[nPredictedLevel];
+        std::vector<size_t> vIndices2 = CurrentFrame.GetFeaturesInArea(u, v, radius, nPredictedLevel - 1, nPredictedLevel + 1);
+        if (vIndices2.empty()) continue;
+        const uint8_t* dMP = kfMpDesc + 32 * i;
+        int bestDist = INT_MAX, bestIdx2 = -1;
+        for (size_t i2 : vIndices2) {
+            if (CurrentFrame.mvpMapPoints[i2] >= 0) continue;
+            int dist = DescriptorDistance(dMP, &CurrentFrame.mDescriptors[i2 * 32]);
+            if (dist < bestDist) { bestDist = dist; bestIdx2 = i2; }
+        }
+        if (bestDist <= ORBdist) {
+            CurrentFrame.mvpMapPoints[bestIdx2] = pMP;
+            CurrentFrame.mvpMatchScore[bestIdx2] = bestDist;
+            nmatches++;
+            if (mbCheckOrientation) {
+                float rot = KF.mvKeysUn[i].angle - CurrentFrame.mvKeysUn[bestIdx2].angle;
+                if (rot < 0.0) rot += 360.0f;
+                int bin = std::round(rot * factor);
+                if (bin == HISTO_LENGTH) bin = 0;
+                rotHist[bin].push_back(bestIdx2);
+            }
+        }
+    }
+    if (mbCheckOrientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        ComputeThreeMaxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++)
+            if (i != ind1 && i != ind2 && i != ind3)
+                for (int idx : rotHist[i]) {
+                    CurrentFrame.mvpMapPoints[idx] = -1;
+                    CurrentFrame.mvpMatchScore[idx] = 999;
+                    nmatches--;
+                }
+    }
+    return nmatches;
 }
 
 // src/Frame.cc:166-227.  cv::Mat arithmetic restated: Rcw*P accumulates each row in double and casts to float before

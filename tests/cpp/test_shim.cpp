@@ -8,6 +8,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <set>
 #include <vector>
 
 #include "gforb/orb_slam.hpp"
@@ -381,6 +382,75 @@ int main() {
         CHECK(fl, "PoseOptimization outlier flags differ");
         CHECK(ps, "PoseOptimization pose differs by more than 1e-5 relative");
     }
+
+    // ---- the Tracking-side keyframe overloads through the shim vs the oracle (TrackReferenceKeyFrame / Relocalization):
+    //      ORBmatcher::SearchByBoW(KeyFrame*, Frame&, out) and SearchByProjection(CurrentFrame, KeyFrame*, sAlreadyFound, th, ORBdist)
+    int nBow = 0, nKf = 0;
+    {
+        const float fx = 458.0f, fy = 457.0f, cx = 376.0f, cy = 240.0f;
+        std::vector<MapPoint> wp(F1.N);
+        std::vector<float> world((size_t)F1.N * 3), mind(F1.N);
+        std::vector<uint8_t> mpd((size_t)F1.N * 32), skip(F1.N, 0);
+        std::set<MapPoint*> found;
+        sm_state = 4242;
+        Frame Fk = F1, Fc = F2;
+        oracle::Frame oK = oF1, oC = oF2;
+        float sc[8]; sc[0] = 1.0f; for (int l = 1; l < 8; l++) sc[l] = sc[l - 1] * 1.2f;
+        for (int i = 0; i < F1.N; i++) {
+            const float z = 2.0f + (float)(splitmix() % 600) * 0.01f;
+            const float u = k1[i].pt.x - 3.0f, v = k1[i].pt.y - 1.0f;        // frame 2 is frame 1 shifted by (3, 1)
+            wp[i].mWorldPos[0] = (u - cx) / fx * z; wp[i].mWorldPos[1] = (v - cy) / fy * z; wp[i].mWorldPos[2] = z;
+            const float d3 = std::sqrt(wp[i].mWorldPos[0] * wp[i].mWorldPos[0] + wp[i].mWorldPos[1] * wp[i].mWorldPos[1] + z * z);
+            wp[i].mfMinDistance = d3 / (sc[k1[i].octave] * (0.95f + 0.01f * (float)(splitmix() % 10)));
+            std::memcpy(wp[i].mDescriptor, F1.mDescriptors.ptr(i), 32);
+            if ((splitmix() % 5) == 0) wp[i].mDescriptor[splitmix() % 32] ^= 0x22;
+            wp[i].mbBad = (splitmix() % 30) == 0;
+            const bool has = (splitmix() % 8) != 0;
+            Fk.mvpMapPoints[i] = has ? &wp[i] : nullptr;
+            if (has && (splitmix() % 9) == 0) found.insert(&wp[i]);
+            oK.mvpMapPoints[i] = has ? i : -1;
+            skip[i] = (has && (wp[i].mbBad || found.count(&wp[i]))) ? 1 : 0;
+            std::memcpy(&world[(size_t)i * 3], wp[i].mWorldPos, 12);
+            mind[i] = wp[i].mfMinDistance;
+            std::memcpy(&mpd[(size_t)i * 32], wp[i].mDescriptor, 32);
+        }
+        // vocabulary stand-in: node = leading descriptor bits
+        std::vector<int> kn(F1.N), fn(F2.N);
+        for (int i = 0; i < F1.N; i++) { kn[i] = 40 + (F1.mDescriptors.ptr(i)[0] & 0x1f); Fk.mFeatVec[(unsigned)kn[i]].push_back((unsigned)i); }
+        for (int j = 0; j < F2.N; j++) { fn[j] = 40 + (F2.mDescriptors.ptr(j)[0] & 0x1f); Fc.mFeatVec[(unsigned)fn[j]].push_back((unsigned)j); }
+        KeyFrame KF(Fk);
+        ORBmatcher mb(0.7f, true);
+        oracle::ORBmatcher omb(0.7f, true);
+        std::vector<MapPoint*> vm;
+        std::vector<int> ovm;
+        oracle::Frame oKb = oK;
+        for (int i = 0; i < F1.N; i++) if (oKb.mvpMapPoints[i] >= 0 && wp[i].mbBad) oKb.mvpMapPoints[i] = -1;   // isBad() -> skipped
+        nBow = mb.SearchByBoW(&KF, Fc, vm);
+        const int onBow = omb.SearchByBoW(oKb, kn.data(), oC, fn.data(), ovm);
+        CHECK(nBow == onBow && nBow > 50, "SearchByBoW: %d vs %d", nBow, onBow);
+        bool okb = vm.size() == ovm.size();
+        for (size_t j = 0; okb && j < vm.size(); j++) okb = (vm[j] ? (int)(vm[j] - &wp[0]) : -1) == ovm[j];
+        CHECK(okb, "SearchByBoW associations differ");
+        // relocalisation-style projection search: the current frame already holds a few points
+        for (int j = 0; j < Fc.N; j++) {
+            Fc.mvpMapPoints[j] = nullptr; oC.mvpMapPoints[j] = -1; Fc.mvpMatchScore[j] = 999; oC.mvpMatchScore[j] = 999;
+            if ((splitmix() % 11) == 0) { Fc.mvpMapPoints[j] = &wp[0]; oC.mvpMapPoints[j] = F1.N; }
+        }
+        Fc.fx = fx; Fc.fy = fy; Fc.cx = cx; Fc.cy = cy; oC.fx = fx; oC.fy = fy; oC.cx = cx; oC.cy = cy;
+        ORBmatcher mk(0.9f, true);
+        oracle::ORBmatcher omk(0.9f, true);
+        nKf = mk.SearchByProjection(Fc, &KF, found, 10.0f, 100);
+        const int onKf = omk.SearchByProjection(oC, oK, skip.data(), world.data(), mind.data(), mpd.data(), 10.0f, 100);
+        CHECK(nKf == onKf && nKf > 50, "SearchByProjection(Current, KeyFrame): %d vs %d", nKf, onKf);
+        bool okk = true;
+        for (int j = 0; okk && j < Fc.N; j++) {
+            int id = -1;
+            if (Fc.mvpMapPoints[j]) { const int i = (int)(Fc.mvpMapPoints[j] - &wp[0]); id = (oC.mvpMapPoints[j] == F1.N) ? F1.N : i; }
+            okk = id == oC.mvpMapPoints[j] && Fc.mvpMatchScore[j] == oC.mvpMatchScore[j];
+        }
+        CHECK(okk, "SearchByProjection(Current, KeyFrame) associations / scores differ");
+    }
+    printf("keyframe leg: %d BoW matches, %d keyframe-projection matches\n", nBow, nKf);
 
     printf("TrackPreviousFrame leg: %d window-projection matches, %d pose inliers\n", nPrev, nInl);
     printf("shim test: %zu/%zu keypoints, %d init matches, %d projection matches, %zu good features, %d active matches: %s\n", k1.size(),

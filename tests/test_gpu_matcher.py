@@ -495,3 +495,86 @@ def test_compute_distinctive_descriptors(orc):
     assert np.array_equal(bd.cpu().numpy(), exp)
     nz = np.array(sizes) > 0
     assert np.array_equal(od.cpu().numpy()[nz], out[nz])
+
+
+def _bow_nodes(desc, n, seed):
+    """a stand-in for the DBoW2 transform: features with the same leading descriptor bits share a node; a few have none"""
+    node = 300 + 7 * (desc[:n, 0].astype(np.int32) & 0x3F)
+    node[synth.uniform01(seed, n) < 0.03] = -1
+    return node
+
+
+@pytest.mark.parametrize("nnratio,check_ori", [(0.7, True), (0.9, False)])
+def test_search_by_bow(orc, seq_frames, nnratio, check_ori):
+    """ORBmatcher::SearchByBoW(KeyFrame*, Frame&, vpMapPointMatches) (src/ORBmatcher.cc:724-853): walk in (node, index) order,
+    claims, ratio test, rotation histogram -- matches per frame keypoint bit-exact"""
+    from gf_orb_slam_b200 import ORBmatcher, Frames
+    kps, desc, counts = seq_frames
+    B = 3
+    KF = Frames(kps[:B], desc[:B], counts[:B], W, H)
+    F = Frames(kps[1:B + 1], desc[1:B + 1], counts[1:B + 1], W, H)
+    kfmp = np.full((B, 1000), -1, np.int32); kn = np.full((B, 1000), -1, np.int32); fn = np.full((B, 1000), -1, np.int32)
+    for b in range(B):
+        n1, n2 = int(counts[b]), int(counts[b + 1])
+        kfmp[b, :n1] = np.where(synth.uniform01(433 + b, n1) < 0.85, 9000 + np.arange(n1), -1)
+        kn[b, :n1] = _bow_nodes(desc[b], n1, 533 + b); fn[b, :n2] = _bow_nodes(desc[b + 1], n2, 633 + b)
+    out = np.full((B, 1000), -7, np.int32)
+    m = ORBmatcher(nnratio, check_ori, max_batch=B, max_keypoints=1000, max_queries=1000)
+    nm = m.SearchByBoW(KF, kfmp, kn, F, fn, out)
+    tot = 0
+    for b in range(B):
+        n1, n2 = int(counts[b]), int(counts[b + 1])
+        kf = _oframe(orc, kps[b], desc[b], n1); f = _oframe(orc, kps[b + 1], desc[b + 1], n2)
+        kf.set_mappoints(kfmp[b, :n1])
+        en, em = orc.search_by_bow(kf, kn[b, :n1], f, fn[b, :n2], nnratio, check_ori)
+        assert nm[b] == en, (b, nm[b], en)
+        assert np.array_equal(out[b, :n2], em) and (out[b, n2:] == -1).all()
+        tot += en
+    assert tot > 100
+
+
+@pytest.mark.parametrize("th,orb_dist,check_ori", [(10.0, 100, True), (3.0, 64, False)])
+def test_search_by_projection_keyframe(orc, seq_frames, th, orb_dist, check_ori):
+    """ORBmatcher::SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist) (src/ORBmatcher.cc:2204-2336): level
+    predicted from the distance to the camera centre, map-point descriptors, skip flags, pre-claimed keypoints"""
+    from gf_orb_slam_b200 import ORBmatcher, Frames
+    kps, desc, counts = seq_frames
+    B = 3
+    KF = Frames(kps[:B], desc[:B], counts[:B], W, H)
+    Cur = Frames(kps[1:B + 1], desc[1:B + 1], counts[1:B + 1], W, H)
+    S = 1000
+    kfmp = np.full((B, S), -1, np.int32); skip = np.zeros((B, S), np.uint8); world = np.zeros((B, S, 3), np.float32)
+    mind = np.ones((B, S), np.float32); mpd = np.zeros((B, S, 32), np.uint8); Tcw = np.zeros((B, 16), np.float32)
+    cmp_ = np.full((B, S), -1, np.int32); csc = np.full((B, S), 999, np.int32)
+    K = None
+    scale = (np.float32(1.2) ** np.arange(8)).astype(np.float32)
+    for b in range(B):
+        n1, n2 = int(counts[b]), int(counts[b + 1])
+        kfmp[b, :n1] = np.where(synth.uniform01(733 + b, n1) < 0.9, 5000 + np.arange(n1), -1)
+        skip[b, :n1] = synth.uniform01(833 + b, n1) < 0.1
+        K, T, w = _pose_and_world(kps[b], n1, seed=170 + b, shift=(1.0 + b, 1.5))
+        world[b, :n1] = w; Tcw[b] = T.reshape(16)
+        Ow = -(T[:3, :3].T.astype(np.float64) @ T[:3, 3].astype(np.float64))
+        d3 = np.linalg.norm(w.astype(np.float64) - Ow, axis=1)
+        jitter = 0.93 + 0.14 * synth.uniform01(933 + b, n1)               # puts the predicted level at the octave or next to it
+        mind[b, :n1] = (d3 / (scale[np.clip(kps["octave"][b, :n1], 0, 7)] * jitter)).astype(np.float32)
+        d = desc[b, :n1].copy()
+        flip = synth.uniform01(1033 + b, n1 * 32).reshape(n1, 32) < 0.04   # the map point's descriptor differs by a few bits
+        d[flip] ^= 0x10
+        mpd[b, :n1] = d
+        cmp_[b, :n2] = np.where(synth.uniform01(1133 + b, n2) < 0.1, 100 + np.arange(n2), -1)
+    cmp0 = cmp_.copy()
+    m = ORBmatcher(0.9, check_ori, max_batch=B, max_keypoints=S, max_queries=S)
+    nm = m.SearchByProjectionKeyFrame(Cur, KF, kfmp, skip, world, mind, mpd, Tcw, K, th, orb_dist, cmp_, csc)
+    tot = 0
+    for b in range(B):
+        n1, n2 = int(counts[b]), int(counts[b + 1])
+        kf = _oframe(orc, kps[b], desc[b], n1); cur = _oframe(orc, kps[b + 1], desc[b + 1], n2)
+        kf.set_mappoints(kfmp[b, :n1]); cur.set_mappoints(cmp0[b, :n2])
+        cur.set_camera(*K, Tcw[b].reshape(4, 4))
+        en = orc.search_by_projection_keyframe(cur, kf, skip[b, :n1], world[b, :n1], mind[b, :n1], mpd[b, :n1], th, orb_dist, check_ori)
+        emp, esc = cur.matches()
+        assert nm[b] == en, (b, nm[b], en)
+        assert np.array_equal(cmp_[b, :n2], emp) and np.array_equal(csc[b, :n2], esc)
+        tot += en
+    assert tot > 100
