@@ -204,9 +204,9 @@ def run_reference(args):
     val = nfr * args.steps / dt
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "frames_per_step": nfr},
+        "config": {"workload": WORKLOAD, "frames_per_step": args.seq_frames, "sample_frames_per_step": nfr},
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port",
                          "sample": f"{nfr} consecutive frames per step x {args.steps} steps, oracle port (g++ -O3 -march=native), {cores} threads"},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -324,6 +324,16 @@ def run_ours(args):
     fe.sync()
     ms_e2e = timed(step_e2e, args.steps)
     clocks = sampler.stop() if rank == 0 else None
+    # where the end-to-end step spends its time: CUDA events around the upload, the bulk download and the three compute stages of
+    # a few more (untimed) steps, every rank at once
+    barrier()
+    fe.set_profiling(True)
+    for _ in range(3):
+        step_e2e()
+    fe.sync()
+    e2e_stages = {n: round(t, 4) for n, t in fe.stage_times()}
+    fe.set_profiling(False)
+    barrier()
     # weak-scaling companion (secondary): every rank walks a whole SEQ-frame schedule of its own (its chunk repeated)
     ms_weak = None
     if world_size > 1 and not args.no_weak:
@@ -428,7 +438,7 @@ def run_ours(args):
                 "ms_per_step": ms_e2e / args.steps,
                 "path": "gforb_frontend_step_host: plain host pointers (pinned), cudaMemcpyAsync up / down inside the library",
                 "h2d_GBps_in_step": nloc * W_ * H_ / (ms_e2e / args.steps * 1e-3) / 1e9, "h2d_GBps_copy_alone": h2d_alone,
-                "h2d_GBps_per_rank_all_ranks_copying": h2d_all},
+                "h2d_GBps_per_rank_all_ranks_copying": h2d_all, "stage_ms_per_batch_rank0": e2e_stages},
         "gpu_launches": launches,
         "clocks": clocks,
     }

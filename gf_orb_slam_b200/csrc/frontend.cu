@@ -315,7 +315,10 @@ int gforb_frontend_step_host(GforbFrontEnd* F, const uint8_t* images, int batch,
     // upload on its own stream (its own copy engine and queue): it may start as soon as the extraction that last read image
     // buffer q (step t-2) is done, i.e. while step t-1 is still computing
     GF_CUDA_OK(cudaStreamWaitEvent(F->sUp, F->evImgFree[q], 0));
-    GF_CUDA_OK(cudaMemcpyAsync(F->d_img[q], images, (size_t)batch * px, cudaMemcpyHostToDevice, F->sUp));
+    {
+        ProfScope ps(F, 3, "h2d", F->sUp);
+        GF_CUDA_OK(cudaMemcpyAsync(F->d_img[q], images, (size_t)batch * px, cudaMemcpyHostToDevice, F->sUp));
+    }
     GF_CUDA_OK(cudaEventRecord(F->evH2D[q], F->sUp));
     GF_CUDA_OK(cudaStreamWaitEvent(F->sMain, F->evH2D[q], 0));
     int rc = step_common(F, F->d_img[q], batch);
@@ -324,9 +327,12 @@ int gforb_frontend_step_host(GforbFrontEnd* F, const uint8_t* images, int batch,
     GF_CUDA_OK(cudaEventRecord(F->evImgFree[q], F->sMain));             // (sMain has only issued this step's extraction since)
     // results: keypoints as soon as the extraction is done, matches after the matcher, the subset after the selection
     GF_CUDA_OK(cudaStreamWaitEvent(F->sDown, F->evExtract[p], 0));
+    {
+    ProfScope psd(F, 4, "d2h keypoints+descriptors", F->sDown);
     GF_CUDA_OK(cudaMemcpyAsync(out->keypoints, F->d_kps[p] + nf, (size_t)batch * nf * sizeof(GforbKeyPoint), cudaMemcpyDeviceToHost, F->sDown));
     GF_CUDA_OK(cudaMemcpyAsync(out->descriptors, F->d_desc[p] + (size_t)nf * 32, (size_t)batch * nf * 32, cudaMemcpyDeviceToHost, F->sDown));
     GF_CUDA_OK(cudaMemcpyAsync(out->counts, F->d_counts[p] + 1, (size_t)batch * sizeof(int32_t), cudaMemcpyDeviceToHost, F->sDown));
+    }
     GF_CUDA_OK(cudaStreamWaitEvent(F->sDown, F->evMatch[p], 0));
     GF_CUDA_OK(cudaMemcpyAsync(out->matches12, F->d_m12[p], (size_t)batch * nf * sizeof(int32_t), cudaMemcpyDeviceToHost, F->sDown));
     GF_CUDA_OK(cudaMemcpyAsync(out->nmatches, F->d_nmatch[p], (size_t)batch * sizeof(int32_t), cudaMemcpyDeviceToHost, F->sDown));
@@ -384,7 +390,8 @@ int gforb_frontend_set_profiling(GforbFrontEnd* F, int on) {
     return gforb_extractor_set_profiling(F->ex, on);
 }
 
-// stages 0..2: extract / match / info+select (CUDA events on the stage's own stream), then the extractor's own stages
+// stages 0..2: extract / match / info+select (CUDA events on the stage's own stream), 3..4 after a profiled step_host: the
+// frame upload and the keypoint + descriptor download; then the extractor's own stages (the first is "pyramid")
 int gforb_frontend_stage_time(GforbFrontEnd* F, int i, const char** name, float* ms) {
     if (!F) return GFORB_ERR_ARG;
     GF_CUDA_OK(cudaSetDevice(F->device));

@@ -146,13 +146,18 @@ class TrackingFrontEnd:
             out.append((name.value.decode() if name.value else "?", float(ms.value)))
         return out
 
+    def _split(self):
+        st = self._stages()
+        own = next((i for i, (n, _) in enumerate(st) if n == "pyramid"), len(st))
+        return st[:own], st[own:]
+
     def stage_times(self):
-        """[(stage, ms)]: extract / match / info+select of the pipeline"""
-        return self._stages()[:3]
+        """[(stage, ms)]: extract / match / info+select of the pipeline (+ h2d and d2h after a profiled step_host)"""
+        return [x for x in self._split()[0] if x[0]]
 
     def extract_stage_times(self):
         """[(stage, ms)]: the extractor's own stages (pyramid, detect, select, orient, blur, describe)"""
-        return self._stages()[3:]
+        return self._split()[1]
 
     # ---- sizes
     def pyramid_bytes(self) -> int:
