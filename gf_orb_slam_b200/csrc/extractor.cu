@@ -425,6 +425,81 @@ __global__ void k_quota(const LevelPlan* __restrict__ levels, const CellPlan* __
     if (off > L.kpCap) atomicExch(errflag, GFORB_ERR_OVERFLOW);
 }
 
+// ------------------------------------------------------------------------------------------------ warp-parallel nth_element
+// The permutation of nth_element_libstdcxx (introselect.h), every Hoare partition pass done by the 32 lanes of a warp.
+// __unguarded_partition swaps the k-th element from the left that is not "before" the pivot (a left stop: !comp(a, p)) with
+// the k-th from the right that is not "after" it (a right stop: !comp(p, a)) while the left one lies left of the right one.
+// Both pointers only ever see unmodified elements before they meet, so the pairs follow from the ORIGINAL array:
+//   left stop i (rank = left stops before i) is swapped  iff  right stops after i  > rank,
+//   right stop j (rank = right stops after j) is swapped  iff  left stops before j  > rank,
+// and the returned cut is min(first unswapped left stop, last swapped right stop) -- the place where the scanning pointer
+// is halted by an element the previous swap put there.  tmp: size / 2 entries, info: size entries of scratch.
+template <class T, class C>
+__device__ void nth_element_warp(T* a, int size, int nthIdx, C comp, T* tmp, uint16_t* info, int lane) {
+    const unsigned full = 0xffffffffu;
+    if (size <= 0 || nthIdx >= size) return;
+    const unsigned lt = (1u << lane) - 1u, le = lt | (1u << lane);
+    int first = 0, last = size;
+    int depth = 2 * (31 - __clz(size));
+    while (last - first > 3) {
+        if (depth == 0) {                                  // introsort's heap-select fallback: sequential (never seen on images)
+            if (lane == 0) { is_heap_select(a + first, a + nthIdx + 1, a + last, comp); gf_swap(a[first], a[nthIdx]); }
+            __syncwarp();
+            return;
+        }
+        --depth;
+        if (lane == 0) is_move_median_to_first(a + first, a + first + 1, a + first + (last - first) / 2, a + last - 1, comp);
+        __syncwarp();
+        const T p = a[first];
+        const int lo = first + 1, hi = last;
+        int totalR = 0;
+        for (int c0 = lo; c0 < hi; c0 += 32) {
+            const int i = c0 + lane;
+            const bool isR = i < hi && !comp(p, a[i]);
+            totalR += __popc(__ballot_sync(full, isR));
+        }
+        int baseL = 0, baseR = 0, cut = INT_MAX;
+        for (int c0 = lo; c0 < hi; c0 += 32) {
+            const int i = c0 + lane;
+            const bool in = i < hi;
+            const T v = in ? a[i] : p;
+            const bool isL = in && !comp(v, p), isR = in && !comp(p, v);
+            const unsigned mL = __ballot_sync(full, isL), mR = __ballot_sync(full, isR);
+            const int prefL = baseL + __popc(mL & lt);                    // left stops before i
+            const int sufR = totalR - (baseR + __popc(mR & le));          // right stops after i
+            const bool swL = isL && sufR > prefL, swR = isR && prefL > sufR;
+            if (swR) tmp[sufR] = v;
+            if (in) info[i] = swL ? (uint16_t)(0x8000 | prefL) : swR ? (uint16_t)(0x4000 | sufR) : (uint16_t)0;
+            if ((isL && !swL) || swR) cut = min(cut, i);
+            baseL += __popc(mL); baseR += __popc(mR);
+        }
+        __syncwarp();
+        for (int i = lo + lane; i < hi; i += 32) {
+            const uint16_t f = info[i];
+            if (f & 0x8000) { const int k = f & 0x3fff; const T v = tmp[k]; tmp[k] = a[i]; a[i] = v; }
+        }
+        __syncwarp();
+        for (int i = lo + lane; i < hi; i += 32) {
+            const uint16_t f = info[i];
+            if (f & 0x4000) a[i] = tmp[f & 0x3fff];
+        }
+        __syncwarp();
+        cut = __reduce_min_sync(full, cut);
+        if (cut <= nthIdx) first = cut; else last = cut;
+    }
+    if (lane == 0) is_insertion_sort(a + first, a + last, comp);
+    __syncwarp();
+}
+
+// retain_best_first_n (introselect.h) with the warp-parallel nth_element; all 32 lanes call it
+template <class T, class C>
+__device__ int retain_best_first_n_warp(T* v, int size, int n, int variant, C comp, T* tmp, uint16_t* info, int lane) {
+    if (n < 0 || size <= n) return size;
+    if (n == 0) return 0;
+    nth_element_warp(v, size, variant ? n - 1 : n, comp, tmp, info, lane);
+    return n;
+}
+
 // ------------------------------------------------------------------------------------------------ K3c
 // per cell: filter the candidate list to the threshold in force (order preserved), retainBest, append at the
 // cell's offset of the level buffer.  One warp per cell; the selection itself is sequential (lane 0).
@@ -440,6 +515,8 @@ __global__ void __launch_bounds__(RET_WARPS * 32) k_cell_retain(const CellPlan* 
                                                                 uint32_t* __restrict__ lvlKp, size_t frameKp, int iniTh,
                                                                 int retainVariant) {
     __shared__ uint32_t s_buf[RET_WARPS][RET_SMEM];
+    __shared__ uint32_t s_tmp[RET_WARPS][RET_SMEM / 2];      // scratch of the warp-parallel selection
+    __shared__ uint16_t s_info[RET_WARPS][RET_SMEM];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int cellId = blockIdx.x * RET_WARPS + warp, b = blockIdx.y;
     if (cellId >= nCellsTotal) return;
@@ -466,7 +543,10 @@ __global__ void __launch_bounds__(RET_WARPS * 32) k_cell_retain(const CellPlan* 
         __syncwarp();
     }
     __syncwarp();
-    if (lane == 0 && outN > nKeep) retain_best_first_n(work, outN, nKeep, retainVariant, ScoreGreater());
+    if (outN > nKeep) {
+        if (outN <= RET_SMEM && !(retainVariant & 2)) retain_best_first_n_warp(work, outN, nKeep, retainVariant & 1, ScoreGreater(), s_tmp[warp], s_info[warp], lane);
+        else if (lane == 0) retain_best_first_n(work, outN, nKeep, retainVariant & 1, ScoreGreater());    // huge lists / probe switch: sequential
+    }
     __syncwarp();
     const int dstOff = cellOutOff[ci];
     if (dstOff + nKeep > levels[C.level].kpCap) return;      // overflow already flagged by k_quota
@@ -478,18 +558,26 @@ __global__ void __launch_bounds__(RET_WARPS * 32) k_cell_retain(const CellPlan* 
 __global__ void __launch_bounds__(128) k_level_retain(const LevelPlan* __restrict__ levels, int nLevels,
                                                       uint32_t* __restrict__ lvlKp, size_t frameKp,
                                                       const int* __restrict__ lvlPre, int* __restrict__ lvlCount,
-                                                      int batch, int retainVariant) {
-    const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+                                                      int batch, int retainVariant, int scratchCap) {
+    extern __shared__ __align__(16) unsigned char lr_smem[];        // per warp: scratchCap / 2 u32 + scratchCap u16 (0: sequential)
+    const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (gw >= batch * nLevels) return;
     const int b = gw / nLevels, l = gw - b * nLevels;
     const LevelPlan L = levels[l];
     int n = lvlPre[gw];
     if (n > L.kpCap) n = L.kpCap;
-    if (lane == 0) {
-        uint32_t* v = lvlKp + (size_t)b * frameKp + L.kpBase;
-        if (n > L.nDesired) n = retain_best_first_n(v, n, L.nDesired, retainVariant, ScoreGreater());
-        lvlCount[gw] = n;
+    uint32_t* v = lvlKp + (size_t)b * frameKp + L.kpBase;
+    if (n > L.nDesired) {
+        if (n <= scratchCap && !(retainVariant & 2)) {
+            uint32_t* tmp = reinterpret_cast<uint32_t*>(lr_smem + (size_t)warp * scratchCap * 4);
+            uint16_t* info = reinterpret_cast<uint16_t*>(tmp + scratchCap / 2);
+            n = retain_best_first_n_warp(v, n, L.nDesired, retainVariant & 1, ScoreGreater(), tmp, info, lane);
+        } else {
+            if (lane == 0) retain_best_first_n(v, n, L.nDesired, retainVariant & 1, ScoreGreater());
+            n = L.nDesired;
+        }
     }
+    if (lane == 0) lvlCount[gw] = n;
 }
 
 // ------------------------------------------------------------------------------------------------ K3e HARRIS_SCORE
@@ -751,6 +839,7 @@ struct GforbExtractor {
     int detectVersion = 2;              // GFORB_DETECT=1 selects the first-generation per-cell kernel (A/B tool)
     int blurFork = 1;                   // the blur of a call runs on ownStream beside the quota / retainBest / orientation kernels (gforb_extractor_set_concurrency)
     cudaEvent_t evFork = nullptr, evJoin = nullptr;
+    int retainSeq = 0;                  // GFORB_RETAIN=seq: retainBest's nth_element on one lane (the first-generation path)
     int resizeTma = 0;                  // GFORB_RESIZE=tma / direct: source rows staged by cp.async.bulk (k_resize_tma) or gathered from L1 (k_resize)
     // device buffers
     uint8_t *d_img = nullptr, *d_pyr = nullptr, *d_blr = nullptr, *d_desc = nullptr;
@@ -971,6 +1060,7 @@ int gforb_extractor_create(const GforbExtractorConfig* cfg, GforbExtractor** out
     GF_CUDA_OK(cudaEventCreateWithFlags(&E->evFork, cudaEventDisableTiming));
     GF_CUDA_OK(cudaEventCreateWithFlags(&E->evJoin, cudaEventDisableTiming));
     if (const char* bf = getenv("GFORB_BLUR_FORK")) E->blurFork = atoi(bf);
+    if (const char* rs = getenv("GFORB_RETAIN")) E->retainSeq = strcmp(rs, "seq") == 0;
     cudaDeviceGetAttribute(&E->numSMs, cudaDevAttrMultiProcessorCount, cfg->device);
     build_ctor_tables(E);
     if (const char* dv = getenv("GFORB_DETECT")) E->detectVersion = atoi(dv);
@@ -1163,9 +1253,14 @@ int gforb_extract(GforbExtractor* E, const uint8_t* images, int w, int h, int st
     if (!harris) {
         k_cell_retain<<<dim3((E->nCellsTotal + RET_WARPS - 1) / RET_WARPS, batch), RET_WARPS * 32, 0, st>>>(
             E->d_cells, E->d_levels, E->nCellsTotal, E->d_cand, E->frameCand, E->d_cnt7, E->d_nTotal, E->d_nToRetain,
-            E->d_cellOff, E->d_lvlKp, E->frameKp, c.iniThFAST, c.retain_variant); launches++;
-        k_level_retain<<<(batch * nl * 32 + 127) / 128, 128, 0, st>>>(E->d_levels, nl, E->d_lvlKp, E->frameKp, E->d_lvlPre,
-                                                                      E->d_lvlCount, batch, c.retain_variant); launches++;
+            E->d_cellOff, E->d_lvlKp, E->frameKp, c.iniThFAST, c.retain_variant | (E->retainSeq ? 2 : 0)); launches++;
+        // scratch of the warp-parallel selection: 4 bytes per level-buffer entry and warp (sequential when it would not fit)
+        int cap = 0;
+        for (int l = 0; l < nl; l++) cap = std::max(cap, E->levels[l].kpCap);
+        cap = (cap + 7) & ~7;
+        if ((size_t)cap * 16 > 48 * 1024 || cap > 0x3fff) cap = 0;
+        k_level_retain<<<(batch * nl * 32 + 127) / 128, 128, (size_t)cap * 16, st>>>(E->d_levels, nl, E->d_lvlKp, E->frameKp, E->d_lvlPre,
+                                                                                     E->d_lvlCount, batch, c.retain_variant | (E->retainSeq ? 2 : 0), cap); launches++;
     } else {
         k_cell_retain_harris<<<dim3((E->nCellsTotal + RET_WARPS - 1) / RET_WARPS, batch), RET_WARPS * 32, 0, st>>>(
             E->d_cells, E->d_levels, E->nCellsTotal, E->d_cand, E->frameCand, E->d_cnt7, E->d_nTotal, E->d_nToRetain,

@@ -112,3 +112,22 @@ def test_resize_variants_agree(monkeypatch):
     assert np.array_equal(a[2], b[2]) and a[0].tobytes() == b[0].tobytes() and np.array_equal(a[1], b[1])
     for l in range(8):
         assert np.array_equal(a[3][l], b[3][l]), l
+
+
+@pytest.mark.parametrize("size,nf,variant", [((752, 480), 1000, 0), ((1241, 376), 2000, 1), ((640, 480), 300, 0)])
+def test_retain_variants_agree(monkeypatch, size, nf, variant):
+    """retainBest's nth_element replayed by the 32 lanes of a warp (default) gives the permutation of the sequential replay
+    (GFORB_RETAIN=seq, the libstdc++ introselect of csrc/introselect.h): same keypoints in the same order, same descriptors.
+    Small nfeatures make every cell and level overflow its quota, so the selection runs everywhere."""
+    from gf_orb_slam_b200 import ORBextractor
+    w, h = size
+    imgs = np.stack([synth.textured_frame(w, h, seed=60 + i) for i in range(3)])
+    res = []
+    for v in ("seq", "warp"):
+        monkeypatch.setenv("GFORB_RETAIN", v)
+        ex = ORBextractor(nf, 1.2, 8, max_width=w, max_height=h, max_batch=3, retain_variant=variant)
+        kps, desc, counts = ex.extract_batch(imgs)
+        res.append((kps.copy(), desc.copy(), counts.copy()))
+    a, b = res
+    assert np.array_equal(a[2], b[2]) and a[0].tobytes() == b[0].tobytes() and np.array_equal(a[1], b[1])
+    assert a[2].min() > nf // 2
