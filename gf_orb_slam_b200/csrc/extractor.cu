@@ -385,22 +385,24 @@ __global__ void __launch_bounds__(DET_THREADS) k_detect(const uint8_t* __restric
 }
 
 // ------------------------------------------------------------------------------------------------ K3b quota
-// src/ORBextractor.cc:621-628 (threshold fallback), :673-721 (quota redistribution).  One thread per (frame, level).
-__global__ void k_quota(const LevelPlan* __restrict__ levels, const CellPlan* __restrict__ cells, int nLevels,
+// src/ORBextractor.cc:621-628 (threshold fallback), :673-721 (quota redistribution).  One warp per (frame, level): the cells of
+// the level are spread over the lanes, the loop-carried totals (all integers) are warp reductions, the output offsets a warp scan.
+__global__ void __launch_bounds__(128) k_quota(const LevelPlan* __restrict__ levels, const CellPlan* __restrict__ cells, int nLevels,
                         int nCellsTotal, const int* __restrict__ cnt7, const int* __restrict__ cnt20,
                         int* __restrict__ nTotalOut, int* __restrict__ nToRetainOut, int* __restrict__ cellOutOff,
                         int* __restrict__ lvlPre, int batch, int* __restrict__ errflag) {
-    int gi = blockIdx.x * blockDim.x + threadIdx.x;
+    const unsigned full = 0xffffffffu;
+    const int gi = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (gi >= batch * nLevels) return;
     const int b = gi / nLevels, l = gi - b * nLevels;
     const LevelPlan L = levels[l];
     const size_t cb = (size_t)b * nCellsTotal + L.cellBase;
     int* nTotal = nTotalOut + cb;
     int* nToRetain = nToRetainOut + cb;
-    // bNoMore is kept in the sign bit of cellOutOff during the loop (scratch), rewritten as offsets at the end
+    // bNoMore is kept in cellOutOff during the loop (scratch), rewritten as offsets at the end
     int* noMore = cellOutOff + cb;
     int nNoMore = 0, nToDistribute = 0;
-    for (int c = 0; c < L.nCells; c++) {
+    for (int c = lane; c < L.nCells; c += 32) {
         if (cells[L.cellBase + c].skipped) { nTotal[c] = 0; nToRetain[c] = 0; noMore[c] = 0; continue; }
         int n20 = cnt20[cb + c], n7 = cnt7[cb + c];
         int nKeys = (n20 <= 3) ? n7 : n20;          // "if size()<=3 -> clear; FAST(cell, 7)"
@@ -408,21 +410,35 @@ __global__ void k_quota(const LevelPlan* __restrict__ levels, const CellPlan* __
         if (nKeys > L.nfeaturesCell) { nToRetain[c] = L.nfeaturesCell; noMore[c] = 0; }
         else { nToRetain[c] = nKeys; nToDistribute += L.nfeaturesCell - nKeys; noMore[c] = 1; nNoMore++; }
     }
+    nNoMore = __reduce_add_sync(full, nNoMore);
+    nToDistribute = __reduce_add_sync(full, nToDistribute);
     while (nToDistribute > 0 && nNoMore < L.nCells) {
-        int nNew = L.nfeaturesCell + (int)ceilf(__fdiv_rn((float)nToDistribute, (float)(L.nCells - nNoMore)));
-        nToDistribute = 0;
-        for (int c = 0; c < L.nCells; c++) {
+        const int nNew = L.nfeaturesCell + (int)ceilf(__fdiv_rn((float)nToDistribute, (float)(L.nCells - nNoMore)));
+        int dist = 0, more = 0;
+        for (int c = lane; c < L.nCells; c += 32) {
             if (!noMore[c]) {
                 int tot = nTotal[c] >= 0 ? nTotal[c] : -nTotal[c] - 1;
                 if (tot > nNew) { nToRetain[c] = nNew; }
-                else { nToRetain[c] = tot; nToDistribute += nNew - tot; noMore[c] = 1; nNoMore++; }
+                else { nToRetain[c] = tot; dist += nNew - tot; noMore[c] = 1; more++; }
             }
         }
+        nToDistribute = __reduce_add_sync(full, dist);
+        nNoMore += __reduce_add_sync(full, more);
     }
     int off = 0;
-    for (int c = 0; c < L.nCells; c++) { noMore[c] = off; off += nToRetain[c]; }
-    lvlPre[(size_t)b * nLevels + l] = off;
-    if (off > L.kpCap) atomicExch(errflag, GFORB_ERR_OVERFLOW);
+    for (int c0 = 0; c0 < L.nCells; c0 += 32) {
+        const int c = c0 + lane;
+        const int r = c < L.nCells ? nToRetain[c] : 0;
+        int inc = r;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const int t = __shfl_up_sync(full, inc, d); if (lane >= d) inc += t; }
+        if (c < L.nCells) noMore[c] = off + inc - r;
+        off += __shfl_sync(full, inc, 31);
+    }
+    if (lane == 0) {
+        lvlPre[(size_t)b * nLevels + l] = off;
+        if (off > L.kpCap) atomicExch(errflag, GFORB_ERR_OVERFLOW);
+    }
 }
 
 // ------------------------------------------------------------------------------------------------ warp-parallel nth_element
@@ -1247,7 +1263,7 @@ int gforb_extract(GforbExtractor* E, const uint8_t* images, int w, int h, int st
     stageStream = st;
     if (fork) GF_CUDA_OK(cudaEventRecord(E->evJoin, E->ownStream));
     begin("select");
-    k_quota<<<(batch * nl + 127) / 128, 128, 0, st>>>(E->d_levels, E->d_cells, nl, E->nCellsTotal, E->d_cnt7, E->d_cnt20,
+    k_quota<<<(batch * nl * 32 + 127) / 128, 128, 0, st>>>(E->d_levels, E->d_cells, nl, E->nCellsTotal, E->d_cnt7, E->d_cnt20,
                                                      E->d_nTotal, E->d_nToRetain, E->d_cellOff, E->d_lvlPre, batch, E->d_err); launches++;
     const bool harris = c.scoreType == 0;
     if (!harris) {
