@@ -438,6 +438,7 @@ struct RParams {
     int* rotBinQ;         // INIT scratch: batch x maxQ
     const int32_t* order; // BOW: batch x maxQ, query index per position of the walk
     int thHigh;           // LAST / KF: acceptance threshold (TH_HIGH; ORBdist for the keyframe overload)
+    int laneParallel;     // INIT: queries one after the other, the candidates of a query over the lanes (0: speculative rounds)
 };
 
 __device__ __forceinline__ int rot_bin(float a1, float a2) {
@@ -448,6 +449,7 @@ __device__ __forceinline__ int rot_bin(float a1, float a2) {
     return min(max(bin, 0), HISTO_LENGTH - 1);
 }
 
+static const int RS_STAGE = 4096;
 template <int MODE>
 __global__ void __launch_bounds__(32) k_resolve(const RParams R) {
     extern __shared__ int sm[];
@@ -456,6 +458,7 @@ __global__ void __launch_bounds__(32) k_resolve(const RParams R) {
     int* state = sm;                          // MAP/LAST/WINDOW: id held by target keypoint (-1 free); INIT: vMatchedDistance
     int* owner = sm + R.maxKp;                // INIT: vnMatches21;  LAST/WINDOW: rotation bin of a claimed keypoint
     unsigned* rnd = reinterpret_cast<unsigned*>(sm + 2 * R.maxKp);
+    __shared__ uint32_t stage[MODE == M_INIT ? RS_STAGE : 1];   // INIT, lane-parallel walk: the candidate lists of 32 queries
     __shared__ int hist[32];
     __shared__ int top3[3];
     const int N2 = min(R.tgt.counts[b], R.maxKp);
@@ -476,6 +479,99 @@ __global__ void __launch_bounds__(32) k_resolve(const RParams R) {
         }
     __syncwarp();
     int accepted = 0;
+    if (MODE == M_INIT && R.laneParallel) {
+        // SearchForInitialization has few active queries (level-0 keypoints only) with long candidate lists (a 100-pixel
+        // window): the queries are taken strictly in order and the 32 lanes share the candidate walk of one query.  The
+        // sequential scan's outcome is the minimum of (dist, list position) and the second order statistic of dist over the
+        // eligible candidates (vMatchedDistance > dist), which two warp reductions reproduce.
+        const uint32_t* poolB = R.pool + (size_t)b * R.poolCap;
+        for (int qb = 0; qb < Q; qb += 32) {
+            int2 meta = make_int2(0, 0);
+            if (qb + lane < Q) meta = R.qMeta[(size_t)b * R.maxQ + qb + lane];
+            unsigned act = __ballot_sync(full, meta.y > 0);
+            if (!act) continue;
+            // the candidate lists of this block of 32 queries go to shared memory with every copy in flight at once
+            // (cp.async, 4 bytes per element): one L2 round trip per block instead of one or two per query
+            int inc = meta.y;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { const int t = __shfl_up_sync(full, inc, d); if (lane >= d) inc += t; }
+            const int soff = inc - meta.y;
+            const bool fits = inc <= RS_STAGE;
+            for (unsigned m = act; m; m &= m - 1) {
+                const int src = __ffs(m) - 1;
+                const int c = __shfl_sync(full, meta.y, src), o = __shfl_sync(full, soff, src), g = __shfl_sync(full, meta.x, src);
+                if (__shfl_sync(full, (int)fits, src))
+                    for (int k = lane; k < c; k += 32) {
+                        const unsigned sa = (unsigned)__cvta_generic_to_shared(&stage[o + k]);
+                        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa), "l"(poolB + g + k) : "memory");
+                    }
+            }
+            asm volatile("cp.async.commit_group;" ::: "memory");
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+            __syncwarp();
+            for (; act; act &= act - 1) {
+                const int src = __ffs(act) - 1, q = qb + src;
+                const int cnt = __shfl_sync(full, meta.y, src);
+                const bool st = __shfl_sync(full, (int)fits, src) != 0;
+                const uint32_t* lst = st ? stage + __shfl_sync(full, soff, src) : poolB + __shfl_sync(full, meta.x, src);
+                // local best / second over this lane's candidates (list positions lane, lane + 32, ...)
+                unsigned k1 = 0xffffffffu, d2 = 0x7fffffffu;      // k1 = dist << 16 | list position
+                int myBi = -1;
+                {   // the first two chunks (lists of up to 64 candidates) with both loads in flight
+                    const bool h0 = lane < cnt, h1 = lane + 32 < cnt;
+                    const uint32_t ea = h0 ? lst[lane] : 0u, eb = h1 ? lst[lane + 32] : 0u;
+                    const int ia = ea & 0xffff, ib = eb & 0xffff, da = (int)(ea >> 20), db = (int)(eb >> 20);
+                    const bool oka = h0 && state[ia] > da, okb = h1 && state[ib] > db;         // :1211
+                    if (oka) { k1 = ((unsigned)da << 16) | (unsigned)lane; myBi = ia; }
+                    if (okb) {
+                        const unsigned key = ((unsigned)db << 16) | (unsigned)(lane + 32);
+                        if (key < k1) { if (oka) d2 = (unsigned)da; k1 = key; myBi = ib; }
+                        else d2 = (unsigned)db;
+                    }
+                }
+                for (int c = lane + 64; c < cnt; c += 32) {
+                    const uint32_t e = lst[c];
+                    const int i2 = e & 0xffff, dist = (int)(e >> 20);
+                    if (state[i2] <= dist) continue;                             // :1211
+                    const unsigned key = ((unsigned)dist << 16) | (unsigned)c;
+                    if (key < k1) { if (k1 != 0xffffffffu) d2 = min(d2, k1 >> 16); k1 = key; myBi = i2; }
+                    else d2 = min(d2, (unsigned)dist);
+                }
+                const unsigned kb = __reduce_min_sync(full, k1);
+                if (kb != 0xffffffffu) {
+                    const unsigned other = (k1 == kb) ? d2 : (k1 == 0xffffffffu ? 0x7fffffffu : (k1 >> 16));
+                    const int best2 = (int)__reduce_min_sync(full, other);
+                    const int best = (int)(kb >> 16);
+                    const int bi = __shfl_sync(full, myBi, (int)(kb & 31u));     // list position c sits on lane c & 31
+                    if (best <= TH_LOW && (float)best < (float)best2 * R.nnratio) {     // :1219-1221
+                        if (lane == 0) {
+                            const int prev = owner[bi];
+                            if (prev >= 0) R.matches12[sOff + prev] = -1;       // steal (:1230-1234)
+                            R.matches12[sOff + q] = bi;
+                            owner[bi] = q;
+                            state[bi] = best;
+                            // the rotation bin depends only on (q, bi): it is filled in after the walk; stale entries of
+                            // stolen matches stay and count, as in the reference (:1249)
+                            if (R.checkOri) R.rotBinQ[(size_t)b * R.maxQ + q] = bi;
+                        }
+                        __syncwarp();
+                    }
+                }
+            }
+            __syncwarp();
+        }
+        __threadfence_block();
+        __syncwarp();
+        if (R.checkOri)
+            for (int q = lane; q < Q; q += 32) {
+                const int bi = __ldcg(&R.rotBinQ[(size_t)b * R.maxQ + q]);
+                if (bi >= 0) {
+                    const int bin = rot_bin(R.src.kps[sOff + q].angle, R.tgt.kps[tOff + bi].angle);
+                    R.rotBinQ[(size_t)b * R.maxQ + q] = bin;
+                    atomicAdd(&hist[bin], 1);
+                }
+            }
+    } else
     for (int qb = 0; qb < Q; qb += 32) {
         int q = qb + lane;
         if (MODE == M_BOW && q < Q) q = R.order[(size_t)b * R.maxQ + q];       // (node, index) order of the reference's walk
@@ -878,6 +974,7 @@ struct GforbMatcher {
     int* d_poolCount = nullptr;      // max_batch
     int2* d_qMeta = nullptr;         // max_batch x max_queries
     int* d_rotBinQ = nullptr;        // max_batch x max_queries
+    int initLaneParallel = 1;        // GFORB_RESOLVE=spec: SearchForInitialization through the speculative rounds of the other modes
     int* d_err = nullptr;
     uint64_t* d_partial = nullptr;
     size_t capPartial = 0;
@@ -1011,6 +1108,7 @@ int gforb_matcher_create(const GforbMatcherConfig* cfg, GforbMatcher** out) {
     M->cfg = *cfg;
     M->device = cfg->device;
     cudaDeviceGetAttribute(&M->numSMs, cudaDevAttrMultiProcessorCount, cfg->device);
+    if (const char* e = getenv("GFORB_RESOLVE")) M->initLaneParallel = strcmp(e, "spec") != 0;
     // Frame::mvScaleFactors (src/Frame.cc:62-75): mvScaleFactors[i] = mvScaleFactors[i-1] * mfScaleFactor (float)
     M->scale[0] = 1.0f;
     for (int i = 1; i < MAX_LEVELS; i++) M->scale[i] = M->scale[i - 1] * cfg->scaleFactor;
@@ -1165,6 +1263,7 @@ int gforb_search_for_initialization(GforbMatcher* M, const GforbFrameSet* F1, co
     R.src = S; R.tgt = T; R.pool = M->d_pool; R.poolCap = M->poolCap; R.qMeta = M->d_qMeta; R.maxQ = M->cfg.max_queries;
     R.maxKp = M->cfg.max_keypoints; R.qCounts = S.counts; R.nnratio = nnratio; R.checkOri = check_orientation;
     R.matches12 = dM12; R.prevMatched = dPrev; R.nmatches = dN; R.rotBinQ = M->d_rotBinQ;
+    R.laneParallel = M->initLaneParallel;
     run_resolve<M_INIT>(M, c, R, batch);
     return end_call(M, c, flags);
 }

@@ -578,3 +578,24 @@ def test_search_by_projection_keyframe(orc, seq_frames, th, orb_dist, check_ori)
         assert np.array_equal(cmp_[b, :n2], emp) and np.array_equal(csc[b, :n2], esc)
         tot += en
     assert tot > 100
+
+
+def test_init_resolve_variants_agree(monkeypatch, seq_frames):
+    """SearchForInitialization resolved query by query with the candidates over the lanes (default) == the speculative
+    32-queries-per-round resolver of the other modes (GFORB_RESOLVE=spec), incl. a repeated call on the updated vbPrevMatched"""
+    from gf_orb_slam_b200 import ORBmatcher, Frames
+    kps, desc, counts = seq_frames
+    B = 4
+    F1 = Frames(kps[:B], desc[:B], counts[:B], W, H); F2 = Frames(kps[1:B + 1], desc[1:B + 1], counts[1:B + 1], W, H)
+    res = []
+    for v in ("spec", "lanes"):
+        monkeypatch.setenv("GFORB_RESOLVE", v)
+        m = ORBmatcher(0.9, True, max_batch=B, max_keypoints=1000, max_queries=1000)
+        prev = np.stack([kps["x"][:B], kps["y"][:B]], axis=-1).astype(np.float32).copy()
+        na, m12a = m.SearchForInitialization(F1, F2, prev, 100)
+        m12a = np.array(m12a).copy(); na = np.array(na).copy(); p1 = prev.copy()
+        nb, m12b = m.SearchForInitialization(F1, F2, prev, 30)
+        res.append((m12a, na, p1, np.array(m12b).copy(), np.array(nb).copy(), prev.copy()))
+    for x, y in zip(*res):
+        assert np.array_equal(x, y)
+    assert res[0][1].sum() > 300
