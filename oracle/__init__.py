@@ -55,6 +55,7 @@ def lib():
         L.orc_extractor_create.restype = C.c_void_p
         L.orc_frame_create.restype = C.c_void_p
         L.orc_logdet.restype = C.c_double
+        L.orc_ic_angle_at.restype = C.c_float
     return _LIB
 
 
@@ -120,6 +121,20 @@ def rand_stream(seed: int, n: int) -> np.ndarray:
     out = np.empty(n, np.int32)
     lib().orc_rand_stream(C.c_uint(seed), n, _p(out))
     return out
+
+
+def ic_angle_at(img: np.ndarray, x: float, y: float) -> float:
+    """IC_Angle (src/ORBextractor.cc:131-158) of the keypoint at (x, y) of `img` (needs 15 pixels around it)"""
+    img = np.ascontiguousarray(img, np.uint8)
+    return float(lib().orc_ic_angle_at(_p(img), img.shape[1], C.c_float(x), C.c_float(y)))
+
+
+def describe_at(img: np.ndarray, x: float, y: float, angle_deg: float) -> np.ndarray:
+    """computeOrbDescriptor (src/ORBextractor.cc:161-201) of the keypoint at (x, y) with the given angle on `img`"""
+    img = np.ascontiguousarray(img, np.uint8)
+    d = np.zeros(32, np.uint8)
+    lib().orc_describe_at(_p(img), img.shape[1], C.c_float(x), C.c_float(y), C.c_float(angle_deg), _p(d))
+    return d
 
 
 def descriptor_distance(a: np.ndarray, b: np.ndarray) -> int:

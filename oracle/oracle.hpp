@@ -108,6 +108,10 @@ struct MapPointView {   // the MapPoint fields SearchByProjection reads (include
     uint8_t desc[32];
 };
 
+// single-keypoint entry points for known-answer tests (IC_Angle :131-158, computeOrbDescriptor :161-201)
+float ic_angle_at(const uint8_t* img, int step, float x, float y);
+void describe_at(const uint8_t* img, int step, float x, float y, float angleDeg, uint8_t* desc);
+
 // Frame::isInFrustum (src/Frame.cc:166-227) on the fields it reads: Rcw (3x3 row-major), tcw, Ow, intrinsics, image
 // bounds and mvScaleFactors.  Returns mbTrackInView and, when true, fills u, v, level, viewCos.
 bool isInFrustum(const float* Rcw, const float* tcw, const float* Ow, float fx, float fy, float cx, float cy, int mnMinX,

@@ -133,6 +133,18 @@ static void computeOrbDescriptor(const KeyPoint& kpt, const uint8_t* roi, int st
     }
 }
 
+// single-keypoint entry points for the known-answer tests (tests/test_oracle_kat.py): the orientation and the descriptor of
+// a keypoint at (x, y) on a plane the caller supplies
+float ic_angle_at(const uint8_t* img, int step, float x, float y) {
+    ORBextractor ex(100, 1.2f, 1);
+    return IC_Angle(img, step, x, y, ex.umax);
+}
+void describe_at(const uint8_t* img, int step, float x, float y, float angleDeg, uint8_t* desc) {
+    KeyPoint kp{};
+    kp.x = x; kp.y = y; kp.angle = angleDeg;
+    computeOrbDescriptor(kp, img, step, desc);
+}
+
 // src/ORBextractor.cc:535-758.  Returns <0 where the reference would hit UB / a cv::Exception.
 int ORBextractor::ComputeKeyPoints(std::vector<std::vector<KeyPoint>>& allKeypoints) {
     allKeypoints.assign(nlevels, {});
