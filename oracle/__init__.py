@@ -178,6 +178,10 @@ class ORBextractor:
                                       _p(kps), _p(desc), _p(counts), cap)
         return kps, desc, counts
 
+    def set_distribution(self, mode: int):
+        """0: the reference's cell-quota distribution, 1: ORB-SLAM2's quadtree (oracle/orb_quadtree.cpp)"""
+        lib().orc_extractor_set_distribution(self.h, int(mode))
+
     def pyramid(self, img: np.ndarray):
         img = np.ascontiguousarray(img, np.uint8)
         lib().orc_extractor_pyramid(self.h, _p(img), img.shape[1], img.shape[0], img.shape[1])

@@ -191,6 +191,7 @@ int orc_search_by_projection_window(void* f1, void* f2, const float* f1World, in
     memcpy(matches2, m2.data(), sizeof(int) * m2.size());
     return n;
 }
+void orc_extractor_set_distribution(void* e, int mode) { ((ORBextractor*)e)->distribution = mode; }
 float orc_ic_angle_at(const uint8_t* img, int step, float x, float y) { return ic_angle_at(img, step, x, y); }
 void orc_describe_at(const uint8_t* img, int step, float x, float y, float angleDeg, uint8_t* desc) { describe_at(img, step, x, y, angleDeg, desc); }
 int orc_search_by_bow(void* kf, const int* kfNode, void* f, const int* fNode, int* matches, float nnratio, int checkOri) {

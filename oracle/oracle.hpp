@@ -72,6 +72,8 @@ public:
     std::vector<std::vector<KeyPoint>> lastAllKeypoints;  // per level, level coordinates, with angle
     void ComputePyramid(const uint8_t* image, int w, int h, int step);
     int ComputeKeyPoints(std::vector<std::vector<KeyPoint>>& all);
+    int ComputeKeyPointsOctTree(std::vector<std::vector<KeyPoint>>& all);   // orb_quadtree.cpp: ORB-SLAM2's quadtree mode (non-default)
+    int distribution = 0;                                                    // 0: the reference's cell quota, 1: quadtree
 
     int nfeatures;
     double scaleFactor;

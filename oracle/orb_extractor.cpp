@@ -136,8 +136,8 @@ static void computeOrbDescriptor(const KeyPoint& kpt, const uint8_t* roi, int st
 // single-keypoint entry points for the known-answer tests (tests/test_oracle_kat.py): the orientation and the descriptor of
 // a keypoint at (x, y) on a plane the caller supplies
 float ic_angle_at(const uint8_t* img, int step, float x, float y) {
-    ORBextractor ex(100, 1.2f, 1);
-    return IC_Angle(img, step, x, y, ex.umax);
+    static const std::vector<int> umax = ORBextractor(100, 1.2f, 1).umax;
+    return IC_Angle(img, step, x, y, umax);
 }
 void describe_at(const uint8_t* img, int step, float x, float y, float angleDeg, uint8_t* desc) {
     KeyPoint kp{};
@@ -250,7 +250,7 @@ int ORBextractor::operator()(const uint8_t* image, int w, int h, int step, std::
     if (image == nullptr || w <= 0 || h <= 0) return 0;   // _image.empty() -> silent return
     ComputePyramid(image, w, h, step);
     std::vector<std::vector<KeyPoint>> allKeypoints;
-    int rc = ComputeKeyPoints(allKeypoints);
+    int rc = distribution == 1 ? ComputeKeyPointsOctTree(allKeypoints) : ComputeKeyPoints(allKeypoints);
     if (rc < 0) return rc;
     int nkeypoints = 0;
     for (int level = 0; level < nlevels; ++level) nkeypoints += (int)allKeypoints[level].size();
