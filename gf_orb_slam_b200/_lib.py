@@ -114,6 +114,7 @@ def lib() -> C.CDLL:
         L.gforb_search_by_projection_keyframe.argtypes = [vp, FS, FS, i32, vp, vp, vp, vp, vp, vp, f32, f32, f32, f32, f32, i32, i32, vp, vp, vp, i32, vp]
         L.gforb_allpairs_top2.argtypes = [vp, vp, i32, vp, i64, i64, vp, i32, vp]
         L.gforb_top2_merge.argtypes = [vp, vp, i32, i32, vp, i32, vp]
+        L.gforb_allpairs_top2_static.argtypes = [i32, vp, i32, vp, i64, i64, vp, i32, vp]
         L.gforb_matcher_poll_error.argtypes = [vp, vp]
         L.gforb_poseopt_create.argtypes = [i32, i32, i32, C.POINTER(vp)]
         L.gforb_poseopt_destroy.argtypes = [vp]
@@ -158,7 +159,7 @@ gforb_extractor_levels gforb_extractor_scale_factor gforb_extractor_tables gforb
 gforb_extractor_last_launches gforb_extractor_set_profiling gforb_extractor_set_concurrency gforb_extractor_stage_time gforb_matcher_create
 gforb_matcher_destroy gforb_matcher_last_launches gforb_descriptor_distance gforb_features_in_area
 gforb_search_for_initialization gforb_search_by_projection gforb_search_by_projection_frames gforb_window_search gforb_search_by_projection_window gforb_search_by_bow gforb_search_by_projection_keyframe
-gforb_allpairs_top2 gforb_top2_merge gforb_obs_create gforb_obs_destroy gforb_obs_last_launches gforb_obs_set_select_residency gforb_obs_set_state
+gforb_allpairs_top2 gforb_top2_merge gforb_allpairs_top2_static gforb_obs_create gforb_obs_destroy gforb_obs_last_launches gforb_obs_set_select_residency gforb_obs_set_state
 gforb_obs_get_state gforb_obs_update_pwls gforb_obs_predict_pwls gforb_obs_num_segments gforb_obs_get_segment
 gforb_obs_build_info_frame gforb_obs_build_info_map gforb_obs_logdet gforb_obs_rand_stream gforb_obs_select
 gforb_obs_active_match gforb_frame_is_in_frustum gforb_frame_undistort_keypoints

@@ -1724,4 +1724,74 @@ int gforb_top2_merge(GforbMatcher* M, const uint64_t* gathered, int n_shards, in
     return GFORB_OK;
 }
 
+// ------------------------------------------------------------------------------------------------ allocation-free all-pairs
+// gforb_allpairs_top2_static: the tensor-core all-pairs top-2 search for callers that may not allocate (CUDA graph capture,
+// serving loops, harnesses that forbid cudaMalloc).  No handle: the per-split partial keys and the kernel error word live in
+// a file-scope device array that every GPU loading the library holds until exit.  The array's name is only a host-side
+// stand-in in host code; the device address comes from cudaGetSymbolAddress, once per device, with that device current.
+static const int SA_MAX_QUERIES = 4096;                  // queries per call
+static const size_t SA_MAX_PAIRS = 65536;                // (database splits) x (queries) partial key pairs = 1 MiB
+static const size_t SA_HEADER = 256;                     // error word of the kernel (the rest of the header is unused)
+static __device__ __align__(256) unsigned char g_static_scratch[SA_HEADER + SA_MAX_PAIRS * 2 * sizeof(uint64_t)];
+
+namespace {
+struct StaticDev { unsigned char* ptr = nullptr; int numSMs = 0; bool ready = false; };
+std::mutex g_staticMu;
+StaticDev g_staticDev[64];
+}  // namespace
+
+int gforb_allpairs_top2_static(int device, const uint8_t* queries, int n_q, const uint8_t* db, int64_t n_db, int64_t idx_base,
+                               uint64_t* out_keys, int flags, void* stream) {
+    if (!queries || !db || !out_keys || n_q < 0 || n_db <= 0 || device < 0 || device >= 64) return GFORB_ERR_ARG;
+    if (!(flags & GFORB_IN_DEVICE) || !(flags & GFORB_OUT_DEVICE)) return GFORB_ERR_ARG;   // queries, database and keys live in HBM
+    if (n_q == 0) return GFORB_OK;
+    if (n_q > SA_MAX_QUERIES) {
+        fprintf(stderr, "[gforb] gforb_allpairs_top2_static: %d queries exceed the static limit of %d per call\n", n_q, SA_MAX_QUERIES);
+        return GFORB_ERR_CAPACITY;
+    }
+    GF_CUDA_OK(cudaSetDevice(device));
+    StaticDev* D = &g_staticDev[device];
+    {
+        std::lock_guard<std::mutex> g(g_staticMu);
+        if (!D->ready) {                                 // set-up, once per device, with that device current
+            void* p = nullptr;
+            GF_CUDA_OK(cudaGetSymbolAddress(&p, g_static_scratch));
+            GF_CUDA_OK(cudaDeviceGetAttribute(&D->numSMs, cudaDevAttrMultiProcessorCount, device));
+            GF_CUDA_OK(raise_dyn_smem(tc::k_allpairs_tc, tc::TC_SMEM_BYTES, device));
+            D->ptr = (unsigned char*)p;
+            D->ready = true;
+        }
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    const int qTiles = (n_q + tc::TC_QTILE - 1) / tc::TC_QTILE;
+    const long long nTiles = (n_db + tc::TC_TILE - 1) / tc::TC_TILE;
+    const long long splits = std::max<long long>(1, D->numSMs / qTiles);            // one wave of (splits x qTiles) CTAs
+    long long tilesPer = std::min<long long>((nTiles + splits - 1) / splits, (1 << 21) / tc::TC_TILE);   // packed key: 2^21 rows
+    tilesPer = std::max<long long>(tilesPer, 1);
+    const long long nChunks = (nTiles + tilesPer - 1) / tilesPer;
+    if ((size_t)nChunks * (size_t)n_q > SA_MAX_PAIRS) {
+        fprintf(stderr, "[gforb] gforb_allpairs_top2_static: %lld database splits x %d queries exceed the static scratch of %zu key pairs\n",
+                nChunks, n_q, SA_MAX_PAIRS);
+        return GFORB_ERR_CAPACITY;
+    }
+    int* dErr = reinterpret_cast<int*>(D->ptr);
+    uint64_t* dPartial = reinterpret_cast<uint64_t*>(D->ptr + SA_HEADER);
+    // the array keeps the previous call's contents: the error word must start at zero; the partial keys of this call's
+    // (split, query) range are all written by the kernel before the merge reads them
+    GF_CUDA_OK(cudaMemsetAsync(dErr, 0, sizeof(int), st));
+    tc::TcParams P;
+    P.q = (const uint4*)queries; P.nq = n_q; P.db = (const uint4*)db; P.nDb = n_db; P.tilesPerSplit = (int)tilesPer;
+    P.idxBase = idx_base; P.partial = dPartial; P.err = dErr;
+    tc::k_allpairs_tc<<<dim3((unsigned)nChunks, qTiles), tc::TC_THREADS, tc::TC_SMEM_BYTES, st>>>(P);
+    k_top2_merge<<<(n_q + 255) / 256, 256, 0, st>>>(dPartial, (int)nChunks, n_q, out_keys);
+    GF_CUDA_OK(cudaGetLastError());
+    if (!(flags & GFORB_ASYNC)) {
+        GF_CUDA_OK(cudaStreamSynchronize(st));
+        int err = 0;
+        GF_CUDA_OK(cudaMemcpy(&err, dErr, sizeof(int), cudaMemcpyDeviceToHost));
+        if (err) return err > 0 ? GFORB_ERR_CUDA : err;
+    }
+    return GFORB_OK;
+}
+
 }  // extern "C"

@@ -272,6 +272,21 @@ int gforb_allpairs_top2(GforbMatcher* h, const uint8_t* queries, int n_q, const 
                         int64_t idx_base, uint64_t* out_keys, int flags, void* stream);
 int gforb_top2_merge(GforbMatcher* h, const uint64_t* gathered /* n_shards x n_q x 2 */, int n_shards, int n_q,
                      uint64_t* out_keys /* n_q x 2 */, int flags, void* stream);
+
+/* Allocation-free variant of gforb_allpairs_top2 (tensor-core kernel).  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  No handle and no allocation of any kind: the per-split partial keys and the kernel's
+ * error word live in a file-scope device array of 1 MiB + 256 B that every GPU loading the library holds until exit.
+ * Limits: n_q <= 4096 and (database splits) x n_q <= 65536 key pairs, where splits = ceil(tiles / min(ceil(tiles / max(1,
+ * SMs / ceil(n_q / 128))), 8192)) and tiles = ceil(n_db / 256) -- on a 148-SM B200 every n_db <= 2^24 fits at any n_q <= 4096;
+ * beyond that the call returns GFORB_ERR_CAPACITY (and says why on stderr).  queries / db / out_keys: device pointers
+ * (flags must hold GFORB_IN_DEVICE | GFORB_OUT_DEVICE; GFORB_ASYNC skips the synchronise + error read), same layouts and the
+ * same keys as gforb_allpairs_top2.  Every call on a device shares the one array, which keeps the last call's contents (the
+ * error word is cleared on the stream at the start of each call): calls that overlap on the GPU race -- issue them on one
+ * stream or order them with events.  The first call on a device does the one-time set-up (cudaGetSymbolAddress, kernel
+ * attribute); make it before starting a capture. */
+int gforb_allpairs_top2_static(int device, const uint8_t* queries, int n_q, const uint8_t* db, int64_t n_db, int64_t idx_base,
+                               uint64_t* out_keys, int flags, void* stream);
 /* gforb_allpairs_top2 runs on the tensor cores (tcgen05.mma kind::i8 on +-1 / 0-1 expanded descriptors, exact); the
  * environment variable GFORB_ALLPAIRS=popc selects the integer-pipe (LOP3/POPC) kernel, the parity reference. */
 
