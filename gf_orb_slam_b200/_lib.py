@@ -89,6 +89,7 @@ def lib() -> C.CDLL:
         L.gforb_extractor_last_launches.argtypes = [vp]
         L.gforb_extractor_set_profiling.argtypes = [vp, i32]
         L.gforb_extractor_set_concurrency.argtypes = [vp, i32]
+        L.gforb_extractor_set_distribution.argtypes = [vp, i32]
         L.gforb_extractor_stage_time.argtypes = [vp, i32, C.POINTER(C.c_char_p), C.POINTER(C.c_float)]
         f32, f64, i64, u32 = C.c_float, C.c_double, C.c_int64, C.c_uint32
         FS, MS = C.POINTER(FrameSet), C.POINTER(MapPointSet)
@@ -156,7 +157,7 @@ def lib() -> C.CDLL:
 # every symbol include/gforb.h declares (checked by tests/test_abi.py against the header and the built library)
 EXPORTS = """gforb_version gforb_device_count gforb_extractor_create gforb_extractor_destroy gforb_extract
 gforb_extractor_levels gforb_extractor_scale_factor gforb_extractor_tables gforb_extractor_debug_level
-gforb_extractor_last_launches gforb_extractor_set_profiling gforb_extractor_set_concurrency gforb_extractor_stage_time gforb_matcher_create
+gforb_extractor_last_launches gforb_extractor_set_profiling gforb_extractor_set_concurrency gforb_extractor_set_distribution gforb_extractor_stage_time gforb_matcher_create
 gforb_matcher_destroy gforb_matcher_last_launches gforb_descriptor_distance gforb_features_in_area
 gforb_search_for_initialization gforb_search_by_projection gforb_search_by_projection_frames gforb_window_search gforb_search_by_projection_window gforb_search_by_bow gforb_search_by_projection_keyframe
 gforb_allpairs_top2 gforb_top2_merge gforb_allpairs_top2_static gforb_obs_create gforb_obs_destroy gforb_obs_last_launches gforb_obs_set_select_residency gforb_obs_set_state

@@ -46,6 +46,7 @@ struct CellPlan {
 }  // namespace gforb
 #include "detect.cuh"
 #include "blur.cuh"
+#include "quadtree.cuh"
 namespace gforb {
 
 // bit_pattern_31_ (src/ORBextractor.cc:204-462) as 256 x {x0, y0, x1, y1}; lane j of k_describe reads its 32 bytes with
@@ -855,6 +856,13 @@ struct GforbExtractor {
     int detectVersion = 2;              // GFORB_DETECT=1 selects the first-generation per-cell kernel (A/B tool)
     int blurFork = 1;                   // the blur of a call runs on ownStream beside the quota / retainBest / orientation kernels (gforb_extractor_set_concurrency)
     cudaEvent_t evFork = nullptr, evJoin = nullptr;
+    int distribution = 0;               // 0: the reference's cell quota; 1: ORB-SLAM2 quadtree (quadtree.cuh, gforb_extractor_set_distribution)
+    std::vector<QtLevel> qlevels;
+    QtLevel* d_qlv = nullptr;
+    uint32_t *d_qtKeys = nullptr, *d_qtTmp = nullptr;
+    QtNode* d_qtNodes = nullptr;
+    int2* d_qtVsz = nullptr;
+    size_t frameQtKeys = 0, frameQtNodes = 0, capQtKeys = 0, capQtTmp = 0, capQtNodes = 0, capQtVsz = 0;
     int retainSeq = 0;                  // GFORB_RETAIN=seq: retainBest's nth_element on one lane (the first-generation path)
     int resizeTma = 0;                  // GFORB_RESIZE=tma / direct: source rows staged by cp.async.bulk (k_resize_tma) or gathered from L1 (k_resize)
     // device buffers
@@ -933,6 +941,9 @@ static int build_plan(GforbExtractor* E, int w, int h) {
     std::vector<int2> tabs;
     size_t off = 0;
     int kpBase = 0, candBase = 0, maxCellW = 0, fnTasks = 0, blTasks = 0;
+    const bool qt = E->distribution == 1;
+    E->qlevels.assign(nl, QtLevel());
+    int qtKeyBase = 0, qtNodeBase = 0;
     bool tiled = true;      // cell interiors tile [16, w-16) x [16, h-16) (k_fast_nms precondition)
     const float imageRatio = (float)w / h;
     for (int l = 0; l < nl; l++) {
@@ -950,11 +961,22 @@ static int build_plan(GforbExtractor* E, int w, int h) {
         L.nDesired = E->featPerLevel[l];
         L.levelCols = (int)sqrtf((float)L.nDesired / (5 * imageRatio));
         L.levelRows = (int)(imageRatio * L.levelCols);
-        if (L.levelCols <= 0 || L.levelRows <= 0) return GFORB_ERR_GEOMETRY;
         const int minB = EDGE, maxBX = L.w - EDGE, maxBY = L.h - EDGE;
         const int W = maxBX - minB, H = maxBY - minB;
-        L.cellW = (int)ceilf((float)W / L.levelCols);
-        L.cellH = (int)ceilf((float)H / L.levelRows);
+        if (qt) {
+            // ORB-SLAM2 ComputeKeyPointsOctTree: cells of ~30 px over [13, w - 13) x [13, h - 13); a cell image is its interior
+            // + 3 px on every side, so the interiors tile [16, w - 16) x [16, h - 16) with period (wCell, hCell)
+            const float width = (float)(L.w - 2 * QT_MIN_BORDER), height = (float)(L.h - 2 * QT_MIN_BORDER);
+            L.levelCols = (int)(width / 30.f);
+            L.levelRows = (int)(height / 30.f);
+            if (L.levelCols <= 0 || L.levelRows <= 0) return GFORB_ERR_GEOMETRY;
+            L.cellW = (int)ceilf(width / L.levelCols);
+            L.cellH = (int)ceilf(height / L.levelRows);
+        } else {
+            if (L.levelCols <= 0 || L.levelRows <= 0) return GFORB_ERR_GEOMETRY;
+            L.cellW = (int)ceilf((float)W / L.levelCols);
+            L.cellH = (int)ceilf((float)H / L.levelRows);
+        }
         L.nCells = L.levelRows * L.levelCols;
         L.nfeaturesCell = (int)ceilf((float)L.nDesired / L.nCells);
         L.cellBase = (int)E->cells.size();
@@ -986,7 +1008,12 @@ static int build_plan(GforbExtractor* E, int w, int h) {
                 CellPlan C;
                 C.level = l; C.skipped = skipped ? 1 : 0;
                 C.x0 = C.y0 = C.x1 = C.y1 = 0;
-                if (!skipped) {
+                if (qt) {
+                    C.x0 = EDGE + j * L.cellW; C.x1 = std::min(C.x0 + L.cellW, maxBX);
+                    C.y0 = EDGE + i * L.cellH; C.y1 = std::min(C.y0 + L.cellH, maxBY);
+                    C.skipped = (C.x1 <= C.x0 || C.y1 <= C.y0) ? 1 : 0;      // "iniX >= maxBorderX - 6" / a cell image too low for FAST
+                    if (C.skipped) C.x0 = C.y0 = C.x1 = C.y1 = 0;
+                } else if (!skipped) {
                     int x1 = iniX + (int)hX, y1 = iniY + (int)hY;            // cell image = [iniX,x1) x [iniY,y1)
                     if (iniX < 0 || iniY < 0 || x1 > L.w || y1 > L.h) return GFORB_ERR_GEOMETRY;  // cv::Mat range assert
                     C.x0 = iniX + 3; C.y0 = iniY + 3; C.x1 = x1 - 3; C.y1 = y1 - 3;                // FAST's 3-px margin
@@ -1001,6 +1028,26 @@ static int build_plan(GforbExtractor* E, int w, int h) {
                 E->cells.push_back(C);
             }
         }
+    }
+    if (qt) {
+        for (int l = 0; l < nl; l++) {
+            const LevelPlan& L = E->levels[l];
+            QtLevel& Q = E->qlevels[l];
+            Q.rootW = L.w - 2 * QT_MIN_BORDER; Q.rootH = L.h - 2 * QT_MIN_BORDER;
+            Q.nIni = (int)roundf((float)Q.rootW / (float)Q.rootH);
+            if (Q.nIni <= 0 || Q.nIni > 4) return GFORB_ERR_GEOMETRY;         // aspect ratios beyond 4.5 : 1 (or portrait below 1 : 2)
+            Q.hX = (float)Q.rootW / Q.nIni;
+            for (int i = 0; i <= Q.nIni; i++) Q.iniUL[i] = (int)(Q.hX * (float)i);
+            Q.N = L.nDesired;
+            long long sum = 0;
+            for (int cI = 0; cI < L.nCells; cI++) sum += E->cells[L.cellBase + cI].candCap;
+            Q.keyBase = qtKeyBase; Q.keyCap = (int)std::min<long long>(sum, 32768);
+            qtKeyBase += (Q.keyCap + 63) & ~63;
+            Q.nodeBase = qtNodeBase; Q.nodeCap = 8 * Q.N + 64;
+            if (Q.nodeCap > 32767) return GFORB_ERR_CAPACITY;
+            qtNodeBase += Q.nodeCap;
+        }
+        E->frameQtKeys = (size_t)qtKeyBase; E->frameQtNodes = (size_t)qtNodeBase;
     }
     E->framePyr = off;
     E->frameCand = (size_t)candBase + 4;
@@ -1023,6 +1070,16 @@ static int build_plan(GforbExtractor* E, int w, int h) {
         E->frameWork = std::max(E->frameCand, E->frameKp);
         if ((rc = ensure(&E->d_work64, &E->capWork, E->frameWork * B))) return rc;
         if ((rc = ensure(&E->d_lvlResp, &E->capResp, E->frameKp * B))) return rc;
+    }
+    if (qt) {
+        if ((rc = ensure(&E->d_qtKeys, &E->capQtKeys, E->frameQtKeys * B))) return rc;
+        if ((rc = ensure(&E->d_qtTmp, &E->capQtTmp, E->frameQtKeys * B))) return rc;
+        if ((rc = ensure(&E->d_qtNodes, &E->capQtNodes, E->frameQtNodes * B))) return rc;
+        if ((rc = ensure(&E->d_qtVsz, &E->capQtVsz, E->frameQtNodes * B * 2))) return rc;
+        if (E->d_qlv) cudaFree(E->d_qlv);
+        E->d_qlv = nullptr;
+        GF_CUDA_OK(cudaMalloc((void**)&E->d_qlv, sizeof(QtLevel) * nl));
+        GF_CUDA_OK(cudaMemcpy(E->d_qlv, E->qlevels.data(), sizeof(QtLevel) * nl, cudaMemcpyHostToDevice));
     }
     size_t nc = (size_t)E->nCellsTotal * B;
     if (nc > E->capCells) {
@@ -1118,7 +1175,8 @@ int gforb_extractor_destroy(GforbExtractor* E) {
     cudaSetDevice(E->device);
     void* ptrs[] = {E->d_img, E->d_pyr, E->d_blr, E->d_desc, E->d_kps, E->d_counts, E->d_cand, E->d_lvlKp, E->d_cnt7,
                     E->d_cnt20, E->d_nTotal, E->d_nToRetain, E->d_cellOff, E->d_lvlPre, E->d_lvlCount, E->d_err,
-                    E->d_levels, E->d_cells, E->d_tabs, E->d_work64, E->d_lvlResp};
+                    E->d_levels, E->d_cells, E->d_tabs, E->d_work64, E->d_lvlResp, E->d_qlv, E->d_qtKeys, E->d_qtTmp, E->d_qtNodes,
+                    E->d_qtVsz};
     for (void* p : ptrs) if (p) cudaFree(p);
     for (auto& r : E->recs) { cudaEventDestroy(r.e0); cudaEventDestroy(r.e1); }
     for (auto& e : E->evPool) cudaEventDestroy(e);
@@ -1263,9 +1321,14 @@ int gforb_extract(GforbExtractor* E, const uint8_t* images, int w, int h, int st
     stageStream = st;
     if (fork) GF_CUDA_OK(cudaEventRecord(E->evJoin, E->ownStream));
     begin("select");
+    const bool harris = c.scoreType == 0;
+    if (E->distribution == 1) {
+        k_quadtree<<<batch, 256, 0, st>>>(E->d_levels, E->d_qlv, nl, E->d_cells, E->nCellsTotal, E->d_cand, E->frameCand, E->d_cnt7,
+                                          E->d_cnt20, c.iniThFAST, E->d_qtKeys, E->d_qtTmp, E->frameQtKeys, E->d_qtNodes, E->d_qtVsz,
+                                          E->frameQtNodes, E->d_lvlKp, E->frameKp, E->d_lvlCount, c.nfeatures, E->d_err); launches++;
+    } else {
     k_quota<<<(batch * nl * 32 + 127) / 128, 128, 0, st>>>(E->d_levels, E->d_cells, nl, E->nCellsTotal, E->d_cnt7, E->d_cnt20,
                                                      E->d_nTotal, E->d_nToRetain, E->d_cellOff, E->d_lvlPre, batch, E->d_err); launches++;
-    const bool harris = c.scoreType == 0;
     if (!harris) {
         k_cell_retain<<<dim3((E->nCellsTotal + RET_WARPS - 1) / RET_WARPS, batch), RET_WARPS * 32, 0, st>>>(
             E->d_cells, E->d_levels, E->nCellsTotal, E->d_cand, E->frameCand, E->d_cnt7, E->d_nTotal, E->d_nToRetain,
@@ -1285,6 +1348,7 @@ int gforb_extract(GforbExtractor* E, const uint8_t* images, int w, int h, int st
         k_level_retain_harris<<<(batch * nl * 32 + 127) / 128, 128, 0, st>>>(
             E->d_levels, nl, E->d_lvlKp, E->d_lvlResp, E->frameKp, E->d_lvlPre, E->d_lvlCount, batch, c.retain_variant,
             E->d_work64, E->frameWork); launches++;
+    }
     }
     end();
     begin("orient");
@@ -1332,6 +1396,21 @@ int gforb_extractor_set_concurrency(GforbExtractor* E, int on) {
     if (!E) return GFORB_ERR_ARG;
     E->blurFork = on != 0;
     return GFORB_OK;
+}
+
+// 0 (default): the reference's cell-quota distribution (ComputeKeyPoints, src/ORBextractor.cc:535-758); 1: ORB-SLAM2's
+// quadtree (quadtree.cuh).  Re-plans the cell grid for the sizes given at create().
+int gforb_extractor_set_distribution(GforbExtractor* E, int mode) {
+    if (!E || (mode != 0 && mode != 1)) return GFORB_ERR_ARG;
+    if (mode == 1 && E->cfg.scoreType == 0) return GFORB_ERR_ARG;          // the quadtree mode ranks by the FAST score
+    if (mode == E->distribution) return GFORB_OK;
+    GF_CUDA_OK(cudaSetDevice(E->device));
+    GF_CUDA_OK(cudaDeviceSynchronize());
+    E->distribution = mode;
+    const int w = E->planW > 0 ? E->planW : E->cfg.max_width, h = E->planH > 0 ? E->planH : E->cfg.max_height;
+    const int rc = build_plan(E, w, h);
+    if (rc != GFORB_OK) { E->planW = E->planH = -1; }
+    return rc;
 }
 
 int gforb_extractor_debug_level(GforbExtractor* E, int b, int level, int which, uint8_t* dst, size_t dst_bytes, int* w,

@@ -86,6 +86,10 @@ class ORBextractor:
     def last_launches(self) -> int:
         return _lib.lib().gforb_extractor_last_launches(self._h)
 
+    def set_distribution(self, mode: int):
+        """0: the reference's cell-quota keypoint distribution (default); 1: ORB-SLAM2's quadtree (non-default mode)"""
+        check(_lib.lib().gforb_extractor_set_distribution(self._h, int(mode)), "gforb_extractor_set_distribution")
+
     def set_profiling(self, on=True):
         _lib.lib().gforb_extractor_set_profiling(self._h, int(on))
 

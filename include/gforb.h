@@ -92,6 +92,12 @@ int gforb_extractor_stage_time(const GforbExtractor* h, int i, const char** name
 /* 1 (default): within a call the Gaussian blur runs on the handle's own stream beside the latency-bound quota / retainBest /
  * orientation kernels and joins before the descriptors; 0: all kernels of a call in sequence on the caller's stream. */
 int gforb_extractor_set_concurrency(GforbExtractor* h, int on);
+/* Keypoint distribution: 0 (default) = the reference's cell quota (ComputeKeyPoints, src/ORBextractor.cc:535-758); 1 = the
+ * quadtree of ORB-SLAM2 (ComputeKeyPointsOctTree / DistributeOctTree: FAST on ~30-px cells with "empty at iniThFAST ->
+ * minThFAST", nodes split until mnFeaturesPerLevel, the best response of every node) -- the mode north_star names; the
+ * GF-ORB-SLAM reference itself has no such code, so this mode is checked against the restatement in oracle/orb_quadtree.cpp
+ * only (size-sort ties by node creation order, rows beyond nfeatures dropped).  FAST_SCORE only; re-plans the cell grid. */
+int gforb_extractor_set_distribution(GforbExtractor* h, int mode);
 
 /* ------------------------------------------------------------------------------------------------ matching
  * Replaces ORB_SLAM::ORBmatcher (include/ORBmatcher.h:39-294, src/ORBmatcher.cc) for the per-frame tracking

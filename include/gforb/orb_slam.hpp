@@ -112,6 +112,12 @@ public:
     }
     int GetLevels() { return nlevels_; }
     float GetScaleFactor() { return scaleFactor_; }
+    // Not in the reference: 0 = its cell-quota keypoint distribution (default), 1 = ORB-SLAM2's quadtree distribution
+    // (gforb_extractor_set_distribution); applies to the next operator() call.
+    void SetKeypointDistribution(int mode) {
+        distribution_ = mode;
+        if (h_) gforb_throw(gforb_extractor_set_distribution(h_, mode), "ORBextractor::SetKeypointDistribution");
+    }
 
 private:
     void ensure(int w, int h) {
@@ -123,11 +129,12 @@ private:
         c.iniThFAST = fastTh_; c.minThFAST = 7; c.blur_variant = 0; c.retain_variant = 0;
         c.max_width = w; c.max_height = h; c.max_batch = 1; c.device = device_;
         gforb_throw(gforb_extractor_create(&c, &h_), "ORBextractor: create");
+        if (distribution_) gforb_throw(gforb_extractor_set_distribution(h_, distribution_), "ORBextractor: distribution");
         maxW_ = w; maxH_ = h;
     }
     int nfeatures_; float scaleFactor_; int nlevels_, scoreType_, fastTh_, device_;
     GforbExtractor* h_ = nullptr;
-    int maxW_ = 0, maxH_ = 0;
+    int maxW_ = 0, maxH_ = 0, distribution_ = 0;
     std::vector<GforbKeyPoint> kp_;
     std::vector<uint8_t> desc_;
 };

@@ -131,3 +131,43 @@ def test_retain_variants_agree(monkeypatch, size, nf, variant):
     a, b = res
     assert np.array_equal(a[2], b[2]) and a[0].tobytes() == b[0].tobytes() and np.array_equal(a[1], b[1])
     assert a[2].min() > nf // 2
+
+
+@pytest.mark.parametrize("w,h,nf", [(752, 480, 1000), (640, 480, 1000), (1241, 376, 2000), (320, 240, 500)])
+def test_quadtree_distribution_matches_oracle(orc, w, h, nf):
+    """the non-default ORB-SLAM2 quadtree distribution (gforb_extractor_set_distribution(h, 1)) against the restatement in
+    oracle/orb_quadtree.cpp: keypoints (order included), angles and descriptors bit-exact; the mode differs from the default;
+    switching back gives the default mode's result again"""
+    from gf_orb_slam_b200 import ORBextractor
+    B = 3
+    imgs = np.stack([synth.textured_frame(w, h, seed=80 + i, band=(i != 1)) for i in range(B)])
+    imgs[2, :, : w // 2] = 90                                             # a frame with a flat half: few keys, early termination
+    ex = ORBextractor(nf, 1.2, 8, max_width=w, max_height=h, max_batch=B)
+    k0, d0, c0 = [a.copy() for a in ex.extract_batch(imgs)]
+    ex.set_distribution(1)
+    kps, desc, counts = [a.copy() for a in ex.extract_batch(imgs)]
+    ex_cpu = orc.ORBextractor(nf, 1.2, 8)
+    ex_cpu.set_distribution(1)
+    for b in range(B):
+        _cmp_frame(orc, ex_cpu, imgs[b], b, kps, desc, counts)
+    assert counts[0] > nf // 2 and counts.max() <= nf
+    assert not (np.array_equal(counts, c0) and kps[0, :c0[0]].tobytes() == k0[0, :c0[0]].tobytes())
+    ex.set_distribution(0)
+    k1, d1, c1 = ex.extract_batch(imgs)
+    assert np.array_equal(c1, c0)
+    for b in range(B):                                                    # rows past counts[b] are not written
+        assert k1[b, :c0[b]].tobytes() == k0[b, :c0[b]].tobytes() and np.array_equal(d1[b, :c0[b]], d0[b, :c0[b]])
+
+
+def test_quadtree_distribution_rejects_degenerate_grids():
+    """a pyramid whose top level is lower than one 30-px cell: the published code divides by zero there (the oracle returns an
+    error), the product answers GFORB_ERR_GEOMETRY and stays usable in the default mode"""
+    from gf_orb_slam_b200 import ORBextractor
+    from gf_orb_slam_b200._lib import GforbError
+    ex = ORBextractor(300, 1.2, 8, max_width=200, max_height=152, max_batch=1)
+    with pytest.raises(GforbError):
+        ex.set_distribution(1)
+    ex.set_distribution(0)
+    img = synth.textured_frame(200, 152, seed=3)
+    kps, desc, counts = ex.extract_batch(img[None])
+    assert counts[0] > 100

@@ -110,3 +110,24 @@ def test_hand_checkable_frame(orc):
     pts = {(int(p["x"]), int(p["y"])) for p in raw}
     assert {(22, 22), (22, 41), (41, 22), (41, 41)} <= pts and (32, 32) not in pts and (22, 32) not in pts
     assert len(orc.fast(sq, 20, True)) == 0
+
+
+def test_quadtree_oracle_properties(orc):
+    """oracle/orb_quadtree.cpp (ORB-SLAM2's distribution, the non-default mode; the reference holds no such code and no vectors):
+    every level returns at most mnFeaturesPerLevel + 3 keypoints, the frame at most nfeatures, no pixel twice, and on a
+    frame whose right half is flat every keypoint comes from the textured half -- while a frame with a single corner returns it"""
+    from gf_orb_slam_b200 import synth
+    img = synth.textured_frame(752, 480, seed=11)
+    ex = orc.ORBextractor(1000, 1.2, 8)
+    ex.set_distribution(1)
+    k, d = ex(img)
+    per = np.bincount(k["octave"], minlength=8)
+    fpl = np.array(ex.features_per_level())
+    assert len(k) <= 1000 and (per <= fpl + 3).all() and per[0] >= fpl[0]
+    assert len({(float(a), float(b), int(o)) for a, b, o in zip(k["x"], k["y"], k["octave"])}) == len(k)
+    half = img.copy(); half[:, 376:] = 77
+    kh, _ = ex(half)
+    assert len(kh) > 200 and (kh["x"] < 376 + 4 * 1.2 ** kh["octave"]).all()
+    one = np.full((480, 752), 30, np.uint8); one[200, 300] = 220
+    k1, _ = ex(one)
+    assert len(k1) >= 1 and (k1["x"][0], k1["y"][0], k1["octave"][0]) == (300.0, 200.0, 0)
