@@ -5,6 +5,6 @@ mirror of ORB_SLAM::ORBextractor / ORBmatcher / Observability used by the tests 
 fallback: without the built library and a CUDA device the operators raise."""
 from ._lib import KP_DTYPE, GforbError, LIB_PATH  # noqa: F401
 from .extractor import ORBextractor, FAST_SCORE, HARRIS_SCORE  # noqa: F401
-from .matcher import ORBmatcher, Frames, MapPoints  # noqa: F401
+from .matcher import ORBmatcher, Frames, MapPoints, WorldPoints  # noqa: F401
 from .observability import Observability  # noqa: F401
 from .optimizer import Optimizer  # noqa: F401

@@ -34,6 +34,11 @@ class MapPointSet(C.Structure):
                 ("flags", C.c_void_p), ("descriptors", C.c_void_p), ("counts", C.c_void_p), ("mp_stride", C.c_int32)]
 
 
+class WorldPointSet(C.Structure):
+    _fields_ = [("world", C.c_void_p), ("normal", C.c_void_p), ("min_distance", C.c_void_p), ("max_distance", C.c_void_p),
+                ("descriptors", C.c_void_p), ("skip", C.c_void_p), ("counts", C.c_void_p), ("mp_stride", C.c_int32)]
+
+
 class MatcherConfig(C.Structure):
     _fields_ = [("max_batch", C.c_int32), ("max_keypoints", C.c_int32), ("max_queries", C.c_int32),
                 ("cand_pool", C.c_int32), ("nlevels", C.c_int32), ("scaleFactor", C.c_float), ("device", C.c_int32)]
@@ -113,6 +118,12 @@ def lib() -> C.CDLL:
         L.gforb_search_by_projection_window.argtypes = [vp, FS, FS, i32, vp, vp, vp, f32, f32, f32, f32, i32, f32, vp, vp, vp, i32, vp]
         L.gforb_search_by_bow.argtypes = [vp, FS, vp, vp, FS, vp, i32, f32, i32, vp, vp, i32, vp]
         L.gforb_search_by_projection_keyframe.argtypes = [vp, FS, FS, i32, vp, vp, vp, vp, vp, vp, f32, f32, f32, f32, f32, i32, i32, vp, vp, vp, i32, vp]
+        WS = C.POINTER(WorldPointSet)
+        L.gforb_search_by_bow_keyframes.argtypes = [vp, FS, vp, vp, FS, vp, vp, i32, f32, i32, vp, vp, i32, vp]
+        L.gforb_search_for_triangulation.argtypes = [vp, FS, vp, vp, FS, vp, vp, i32, vp, i32, vp, vp, i32, vp]
+        L.gforb_fuse.argtypes = [vp, FS, i32, vp, i32, f32, f32, f32, f32, WS, f32, vp, vp, vp, i32, vp]
+        L.gforb_search_by_projection_sim3.argtypes = [vp, FS, i32, vp, f32, f32, f32, f32, WS, vp, f32, vp, vp, i32, vp]
+        L.gforb_search_by_sim3.argtypes = [vp, FS, FS, i32, WS, WS, vp, vp, vp, vp, vp, vp, f32, f32, f32, f32, f32, vp, vp, i32, vp]
         L.gforb_allpairs_top2.argtypes = [vp, vp, i32, vp, i64, i64, vp, i32, vp]
         L.gforb_top2_merge.argtypes = [vp, vp, i32, i32, vp, i32, vp]
         L.gforb_allpairs_top2_static.argtypes = [i32, vp, i32, vp, i64, i64, vp, i32, vp]
@@ -160,6 +171,7 @@ gforb_extractor_levels gforb_extractor_scale_factor gforb_extractor_tables gforb
 gforb_extractor_last_launches gforb_extractor_set_profiling gforb_extractor_set_concurrency gforb_extractor_set_distribution gforb_extractor_stage_time gforb_matcher_create
 gforb_matcher_destroy gforb_matcher_last_launches gforb_descriptor_distance gforb_features_in_area
 gforb_search_for_initialization gforb_search_by_projection gforb_search_by_projection_frames gforb_window_search gforb_search_by_projection_window gforb_search_by_bow gforb_search_by_projection_keyframe
+gforb_search_by_bow_keyframes gforb_search_for_triangulation gforb_fuse gforb_search_by_projection_sim3 gforb_search_by_sim3
 gforb_allpairs_top2 gforb_top2_merge gforb_allpairs_top2_static gforb_obs_create gforb_obs_destroy gforb_obs_last_launches gforb_obs_set_select_residency gforb_obs_set_state
 gforb_obs_get_state gforb_obs_update_pwls gforb_obs_predict_pwls gforb_obs_num_segments gforb_obs_get_segment
 gforb_obs_build_info_frame gforb_obs_build_info_map gforb_obs_logdet gforb_obs_rand_stream gforb_obs_select

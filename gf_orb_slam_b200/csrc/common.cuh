@@ -52,6 +52,21 @@ __device__ __forceinline__ int popc256(const uint4 a0, const uint4 a1, const uin
            __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
 }
 
+// cv::Mat arithmetic of the matchers on CV_32F 3x3 / 3x1 operands (restated from OpenCV's matop.cpp / matmul.cpp; pinned
+// against cv2 4.13 in tests/golden/cv413_gemm_small.npz).  `R*x + t` is ONE cv::gemm(R, x, 1, t, 1) (MatOp_GEMM::add folds the
+// sum in); with no transpose flag and len = 3 cv::gemm takes its small-matrix path: the row's dot product accumulates in
+// float, left to right, and d = (float)(t0*alpha + c*beta) is evaluated in double.
+__device__ __forceinline__ float cv_gemm_row(float a0, float a1, float a2, float x0, float x1, float x2, float c) {
+    const float t0 = __fadd_rn(__fadd_rn(__fmul_rn(a0, x0), __fmul_rn(a1, x1)), __fmul_rn(a2, x2));
+    return (float)((double)t0 * 1.0 + (double)c * 1.0);
+}
+// one entry of `-R.t()*t`: the MatExpr materialises the transpose, scales it by -1 and multiplies: cv::gemm(Rt, t, -1), the
+// same small-matrix path with c = 0.  a0..a2 = column i of R.
+__device__ __forceinline__ float cv_neg_rt_t_row(float a0, float a1, float a2, float t0, float t1, float t2) {
+    const float s = __fadd_rn(__fadd_rn(__fmul_rn(a0, t0), __fmul_rn(a1, t1)), __fmul_rn(a2, t2));
+    return (float)((double)s * -1.0 + 0.0);
+}
+
 __device__ __forceinline__ uint4 ldg_nc_u4(const void* p) {
     uint4 r;
     asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));

@@ -27,7 +27,11 @@ namespace gforb {
 
 static const int GRID_COLS = 64, GRID_ROWS = 48, GRID_CELLS = GRID_COLS * GRID_ROWS;
 static const int TH_HIGH = 100, TH_LOW = 50, HISTO_LENGTH = 30;
-enum { M_INIT = 0, M_WINDOW = 1, M_MAP = 2, M_LAST = 3, M_AREA = 4, M_PROJ2 = 5, M_BOW = 6, M_KF = 7 };
+enum { M_INIT = 0, M_WINDOW = 1, M_MAP = 2, M_LAST = 3, M_AREA = 4, M_PROJ2 = 5, M_BOW = 6, M_KF = 7,
+       M_BOW2 = 8,      // SearchByBoW(KeyFrame, KeyFrame)
+       M_TRI = 9,       // SearchForTriangulation
+       M_PKF = 10 };    // map points projected into a keyframe: Fuse (both), SearchByProjection(KF, Scw, ..), SearchBySim3
+#define GF_IS_BOW(M) ((M) == M_BOW || (M) == M_BOW2 || (M) == M_TRI)
 
 struct FrameDev {
     const GforbKeyPoint* kps;
@@ -130,6 +134,12 @@ struct QParams {
     const uint8_t *mpFlags, *mpDesc;
     const int32_t* mpCounts;
     int mpStride;
+    const int32_t* tgtMp;         // BOW2 / TRI: pKF2->GetMapPointMatches() as ids (batch x T.stride)
+    const float* F12;             // TRI: batch x 9
+    const float *pWorld, *pNormal, *pMinD, *pMaxD;   // PKF: batch x mpStride (x 3); pNormal == nullptr: no viewing-angle gate
+    const uint8_t* pSkip;         // PKF
+    int pkfMode;                  // PKF: 0 pose = Tcw, 1 pose = Scw (decomposed), 2 / 3 SearchBySim3 direction 1 -> 2 / 2 -> 1
+    const float *s12, *R12, *t12; // PKF, SearchBySim3: batch, batch x 9, batch x 3
     const float *ax, *ay, *ar;    // AREA
     const int32_t *aMin, *aMax;
     int aCount, aFrame;
@@ -206,23 +216,51 @@ __device__ __forceinline__ int enum_candidates(const int* __restrict__ cs, const
     return total;
 }
 
-// SearchByBoW: the features of the target frame that sit in the query's vocabulary node, in index order (vIndicesF)
-template <bool WRITE>
+// SearchByBoW / SearchForTriangulation: the features of the target frame that sit in the query's vocabulary node, in index
+// order (vIndicesF / f2it->second).  FILT 0: every feature (SearchByBoW(KF, F): claims are the resolver's business);
+// FILT 1: features that hold a map point (SearchByBoW(KF1, KF2), :1341-1347); FILT 2: SearchForTriangulation -- features without
+// a map point whose distance is <= TH_LOW (:1485-1493); bit 31 of the entry = CheckDistEpipolarLine(kp1, kp2, F12) (:705-722).
+template <bool WRITE, int FILT>
 __device__ __forceinline__ int enum_node(const int32_t* __restrict__ tnode, const GforbKeyPoint* __restrict__ tkps,
                                          const uint8_t* __restrict__ tdesc, int N2, int node, const uint32_t (&qd)[8],
-                                         uint32_t* __restrict__ out, int lane) {
+                                         uint32_t* __restrict__ out, int lane, const int32_t* __restrict__ tmp = nullptr,
+                                         float k1x = 0.f, float k1y = 0.f, const float* __restrict__ F12 = nullptr,
+                                         const float* scale = nullptr) {
     const unsigned full = 0xffffffffu;
     int total = 0;
     for (int t0 = 0; t0 < N2; t0 += 32) {
         const int t = t0 + lane;
-        const bool valid = t < N2 && tnode[t] == node;
-        const unsigned m = __ballot_sync(full, valid);
-        if (WRITE && valid) {
+        bool valid = t < N2 && tnode[t] == node;
+        if (FILT == 1 && valid) valid = tmp[t] >= 0;
+        if (FILT == 2 && valid) valid = tmp[t] < 0;
+        int dist = 0;
+        if ((WRITE || FILT == 2) && valid) {
             const uint4* dp = reinterpret_cast<const uint4*>(tdesc + (size_t)t * 32);
             const uint4 d0 = __ldg(dp), d1 = __ldg(dp + 1);
-            const int dist = __popc(qd[0] ^ d0.x) + __popc(qd[1] ^ d0.y) + __popc(qd[2] ^ d0.z) + __popc(qd[3] ^ d0.w) +
-                             __popc(qd[4] ^ d1.x) + __popc(qd[5] ^ d1.y) + __popc(qd[6] ^ d1.z) + __popc(qd[7] ^ d1.w);
-            out[total + __popc(m & ((1u << lane) - 1u))] = ((uint32_t)dist << 20) | ((uint32_t)(tkps[t].octave & 15) << 16) | (uint32_t)t;
+            dist = __popc(qd[0] ^ d0.x) + __popc(qd[1] ^ d0.y) + __popc(qd[2] ^ d0.z) + __popc(qd[3] ^ d0.w) +
+                   __popc(qd[4] ^ d1.x) + __popc(qd[5] ^ d1.y) + __popc(qd[6] ^ d1.z) + __popc(qd[7] ^ d1.w);
+            if (FILT == 2 && dist > TH_LOW) valid = false;
+        }
+        const unsigned m = __ballot_sync(full, valid);
+        if (WRITE && valid) {
+            const int oct = tkps[t].octave;
+            uint32_t e = ((uint32_t)dist << 20) | ((uint32_t)(oct & 15) << 16) | (uint32_t)t;
+            if (FILT == 2) {
+                const float k2x = tkps[t].x, k2y = tkps[t].y;
+                const float a = __fadd_rn(__fadd_rn(__fmul_rn(k1x, F12[0]), __fmul_rn(k1y, F12[3])), F12[6]);
+                const float b = __fadd_rn(__fadd_rn(__fmul_rn(k1x, F12[1]), __fmul_rn(k1y, F12[4])), F12[7]);
+                const float c = __fadd_rn(__fadd_rn(__fmul_rn(k1x, F12[2]), __fmul_rn(k1y, F12[5])), F12[8]);
+                const float num = __fadd_rn(__fadd_rn(__fmul_rn(a, k2x), __fmul_rn(b, k2y)), c);
+                const float den = __fadd_rn(__fmul_rn(a, a), __fmul_rn(b, b));
+                bool ok = false;
+                if (den != 0.0f) {
+                    const float dsqr = __fdiv_rn(__fmul_rn(num, num), den);
+                    const float sc = scale[min(max(oct, 0), MAX_LEVELS - 1)];
+                    ok = (double)dsqr < 3.84 * (double)__fmul_rn(sc, sc);              // mvLevelSigma2[i] = scale[i]^2 (src/Frame.cc:110)
+                }
+                if (ok) e |= 0x80000000u;
+            }
+            out[total + __popc(m & ((1u << lane) - 1u))] = e;
         }
         total += __popc(m);
     }
@@ -237,7 +275,7 @@ __global__ void __launch_bounds__(128) k_candidates(const QParams P, const Frame
     const int q = blockIdx.x * 4 + warp, b = blockIdx.y;
     const int tb = (MODE == M_AREA) ? P.aFrame : b;      // target frame
     int Q;
-    if (MODE == M_MAP) Q = P.mpCounts[b];
+    if (MODE == M_MAP || MODE == M_PKF) Q = P.mpCounts[b];
     else if (MODE == M_AREA) Q = P.aCount;
     else Q = P.src.counts[b];
     Q = min(Q, maxQ);
@@ -282,13 +320,9 @@ __global__ void __launch_bounds__(128) k_candidates(const QParams P, const Frame
         if (active) {
             const float* X = P.srcWorld + i * 3;
             const float* Tm = P.Tcw + (size_t)b * 16;
-            float xc3[3];
+            float xc3[3];                                   // Rcw*x3Dw+tcw (common.cuh: cv_gemm_row)
 #pragma unroll
-            for (int rw = 0; rw < 3; rw++) {
-                double s = (double)Tm[rw * 4 + 0] * (double)X[0] + (double)Tm[rw * 4 + 1] * (double)X[1] +
-                           (double)Tm[rw * 4 + 2] * (double)X[2];
-                xc3[rw] = (float)s + Tm[rw * 4 + 3];
-            }
+            for (int rw = 0; rw < 3; rw++) xc3[rw] = cv_gemm_row(Tm[rw * 4], Tm[rw * 4 + 1], Tm[rw * 4 + 2], X[0], X[1], X[2], Tm[rw * 4 + 3]);
             const float invzc = (float)(1.0 / (double)xc3[2]);
             const float u = P.fx * xc3[0] * invzc + P.cx;
             const float v = P.fy * xc3[1] * invzc + P.cy;
@@ -315,13 +349,9 @@ __global__ void __launch_bounds__(128) k_candidates(const QParams P, const Frame
         if (active) {
             const float* X = P.srcWorld + i * 3;
             const float* Tm = P.Tcw + (size_t)b * 16;
-            float xc3[3];
+            float xc3[3];                                   // Rcw*x3Dw+tcw (common.cuh: cv_gemm_row)
 #pragma unroll
-            for (int rw = 0; rw < 3; rw++) {
-                double s = (double)Tm[rw * 4 + 0] * (double)X[0] + (double)Tm[rw * 4 + 1] * (double)X[1] +
-                           (double)Tm[rw * 4 + 2] * (double)X[2];
-                xc3[rw] = (float)s + Tm[rw * 4 + 3];
-            }
+            for (int rw = 0; rw < 3; rw++) xc3[rw] = cv_gemm_row(Tm[rw * 4], Tm[rw * 4 + 1], Tm[rw * 4 + 2], X[0], X[1], X[2], Tm[rw * 4 + 3]);
             const float invzc = (float)(1.0 / (double)xc3[2]);
             x = P.fx * xc3[0] * invzc + P.cx;
             y = P.fy * xc3[1] * invzc + P.cy;
@@ -342,15 +372,8 @@ __global__ void __launch_bounds__(128) k_candidates(const QParams P, const Frame
             float xc3[3], Ow[3];
 #pragma unroll
             for (int rw = 0; rw < 3; rw++) {
-                double s = (double)Tm[rw * 4 + 0] * (double)X[0] + (double)Tm[rw * 4 + 1] * (double)X[1] +
-                           (double)Tm[rw * 4 + 2] * (double)X[2];
-                xc3[rw] = (float)s + Tm[rw * 4 + 3];
-                // Ow = -Rcw.t()*tcw: cv::gemm(alpha = -1, GEMM_1_T) on CV_32F, double accumulation over k = 0, 1, 2
-                double o = 0.0;
-                o = o + (double)Tm[0 * 4 + rw] * (double)Tm[0 * 4 + 3];
-                o = o + (double)Tm[1 * 4 + rw] * (double)Tm[1 * 4 + 3];
-                o = o + (double)Tm[2 * 4 + rw] * (double)Tm[2 * 4 + 3];
-                Ow[rw] = (float)(o * -1.0);
+                xc3[rw] = cv_gemm_row(Tm[rw * 4], Tm[rw * 4 + 1], Tm[rw * 4 + 2], X[0], X[1], X[2], Tm[rw * 4 + 3]);
+                Ow[rw] = cv_neg_rt_t_row(Tm[rw], Tm[4 + rw], Tm[8 + rw], Tm[3], Tm[7], Tm[11]);    // Ow = -Rcw.t()*tcw (:2210)
             }
             const float invzc = (float)(1.0 / (double)xc3[2]);
             const float u = P.fx * xc3[0] * invzc + P.cx;
@@ -369,14 +392,101 @@ __global__ void __launch_bounds__(128) k_candidates(const QParams P, const Frame
             minL = lvl - 1; maxL = lvl + 1;
         }
         qdp = P.qDesc + i * 32;
-    } else if (MODE == M_BOW) {
+    } else if (MODE == M_BOW || MODE == M_BOW2) {
         const size_t i = (size_t)b * P.src.stride + q;
         if (P.srcMp[i] < 0 || P.srcNode[i] < 0) active = false;
         qdp = P.src.desc + i * 32;
+    } else if (MODE == M_TRI) {
+        const size_t i = (size_t)b * P.src.stride + q;
+        if (P.srcMp[i] >= 0 || P.srcNode[i] < 0) active = false;     // "if there is already a MapPoint skip" (:1468-1470)
+        x = P.src.kps[i].x; y = P.src.kps[i].y;                       // kp1 of the epipolar test
+        qdp = P.src.desc + i * 32;
+    } else if (MODE == M_PKF) {
+        // the projection block of Fuse (:1617-1659, :1743-1788), SearchByProjection(pKF, Scw, ..) (:889-934) and one direction
+        // of SearchBySim3 (:1903-1939, :1986-2024); every lane computes it (a few dozen operations)
+        const size_t i = (size_t)b * P.mpStride + q;
+        if (P.pSkip && P.pSkip[i]) active = false;
+        if (active) {
+            const float* S = P.Tcw + (size_t)b * 16;
+            float R[9], t[3];
+            if (P.pkfMode == 1) {
+                // scw = sqrt(sRcw.row(0).dot(sRcw.row(0))) (Mat::dot: double products), Rcw = sRcw/scw, tcw = Scw.col(3)/scw:
+                // the MatExpr scale converts with alpha = 1./scw -> every entry times (float)alpha
+                const double d = (double)S[0] * (double)S[0] + (double)S[1] * (double)S[1] + (double)S[2] * (double)S[2];
+                const float scw = (float)sqrt(d);
+                const float al = (float)(1.0 / (double)scw);
+#pragma unroll
+                for (int rw = 0; rw < 3; rw++) {
+#pragma unroll
+                    for (int c = 0; c < 3; c++) R[rw * 3 + c] = __fadd_rn(__fmul_rn(S[rw * 4 + c], al), 0.0f);
+                    t[rw] = __fadd_rn(__fmul_rn(S[rw * 4 + 3], al), 0.0f);
+                }
+            } else {
+#pragma unroll
+                for (int rw = 0; rw < 3; rw++) { R[rw * 3] = S[rw * 4]; R[rw * 3 + 1] = S[rw * 4 + 1]; R[rw * 3 + 2] = S[rw * 4 + 2]; t[rw] = S[rw * 4 + 3]; }
+            }
+            const float* X = P.pWorld + i * 3;
+            float pc[3];
+#pragma unroll
+            for (int rw = 0; rw < 3; rw++) pc[rw] = cv_gemm_row(R[rw * 3], R[rw * 3 + 1], R[rw * 3 + 2], X[0], X[1], X[2], t[rw]);
+            float dist3D;
+            if (P.pkfMode >= 2) {
+                // SearchBySim3: sR12 = s12*R12; sR21 = (1.0/s12)*R12.t(); t21 = -sR21*t12 (:1858-1860), then sR*p3Dc + t
+                const float s12 = P.s12[b];
+                const float* R12 = P.R12 + (size_t)b * 9;
+                const float* t12 = P.t12 + (size_t)b * 3;
+                float Qm[9], tq[3];
+                if (P.pkfMode == 3) {
+                    const float al = (float)(double)s12;
+#pragma unroll
+                    for (int k = 0; k < 9; k++) Qm[k] = __fadd_rn(__fmul_rn(R12[k], al), 0.0f);
+                    tq[0] = t12[0]; tq[1] = t12[1]; tq[2] = t12[2];
+                } else {
+                    const float al = (float)(1.0 / (double)s12);
+#pragma unroll
+                    for (int rw = 0; rw < 3; rw++)
+#pragma unroll
+                        for (int c = 0; c < 3; c++) Qm[rw * 3 + c] = __fadd_rn(__fmul_rn(R12[c * 3 + rw], al), 0.0f);
+#pragma unroll
+                    for (int rw = 0; rw < 3; rw++) tq[rw] = cv_neg_rt_t_row(Qm[rw * 3], Qm[rw * 3 + 1], Qm[rw * 3 + 2], t12[0], t12[1], t12[2]);
+                }
+                float pd[3];
+#pragma unroll
+                for (int rw = 0; rw < 3; rw++) pd[rw] = cv_gemm_row(Qm[rw * 3], Qm[rw * 3 + 1], Qm[rw * 3 + 2], pc[0], pc[1], pc[2], tq[rw]);
+                pc[0] = pd[0]; pc[1] = pd[1]; pc[2] = pd[2];
+                dist3D = (float)sqrt((double)pc[0] * (double)pc[0] + (double)pc[1] * (double)pc[1] + (double)pc[2] * (double)pc[2]);   // cv::norm(p3Dc2)
+            } else {
+                float PO[3];
+#pragma unroll
+                for (int rw = 0; rw < 3; rw++) PO[rw] = X[rw] - cv_neg_rt_t_row(R[rw], R[3 + rw], R[6 + rw], t[0], t[1], t[2]);      // p3Dw - Ow
+                dist3D = (float)sqrt((double)PO[0] * (double)PO[0] + (double)PO[1] * (double)PO[1] + (double)PO[2] * (double)PO[2]);
+                if (P.pNormal) {                           // PO.dot(Pn) < 0.5*dist3D: viewing angle above 60 degrees
+                    const float* Pn = P.pNormal + i * 3;
+                    const double dot = (double)PO[0] * (double)Pn[0] + (double)PO[1] * (double)Pn[1] + (double)PO[2] * (double)Pn[2];
+                    if (dot < 0.5 * (double)dist3D) active = false;
+                }
+            }
+            if (pc[2] < 0.0f) active = false;              // depth must be positive
+            const float invz = (float)(1.0 / (double)pc[2]);
+            const float xn = __fmul_rn(pc[0], invz), yn = __fmul_rn(pc[1], invz);
+            const float u = __fadd_rn(__fmul_rn(P.fx, xn), P.cx), v = __fadd_rn(__fmul_rn(P.fy, yn), P.cy);
+            // KeyFrame::IsInImage (src/KeyFrame.cc:654-657); a NaN projection fails it
+            if (!(u >= (float)G.iminX && u < (float)G.imaxX && v >= (float)G.iminY && v < (float)G.imaxY)) active = false;
+            const float minD = P.pMinD[i];
+            if (dist3D < minD || dist3D > P.pMaxD[i]) active = false;
+            const float ratio = __fdiv_rn(dist3D, minD);
+            int lvl = 0;                                   // std::lower_bound(vfScaleFactors, ratio), capped at nMaxLevel
+            while (lvl < P.nlevels && P.scale[lvl] < ratio) lvl++;
+            if (lvl >= P.nlevels) lvl = P.nlevels - 1;
+            x = u; y = v;
+            r = __fmul_rn(P.th, P.scale[lvl]);
+            minL = lvl - 1; maxL = lvl;
+        }
+        qdp = P.mpDesc + i * 32;
     } else {
         x = P.ax[q]; y = P.ay[q]; r = P.ar[q]; minL = P.aMin[q]; maxL = P.aMax[q];
     }
-    if (MODE == M_BOW) {
+    if (GF_IS_BOW(MODE)) {
         // position of this query in the reference's walk: FeatureVector nodes ascending, features of a node in index order
         const size_t so = (size_t)b * P.src.stride;
         const int myNode = P.srcNode[so + q];
@@ -399,9 +509,12 @@ __global__ void __launch_bounds__(128) k_candidates(const QParams P, const Frame
         const int4* ent = Gd.entries + (size_t)tb * Gd.maxKp;
         const uint8_t* tdesc = T.desc + (size_t)tb * T.stride * 32;
         const int N2 = min(T.counts[tb], T.stride);
-        const int32_t* tnode = (MODE == M_BOW) ? P.tgtNode + (size_t)tb * T.stride : nullptr;
-        const int myNode = (MODE == M_BOW) ? P.srcNode[(size_t)b * P.src.stride + q] : 0;
-        int cnt = (MODE == M_BOW) ? enum_node<false>(tnode, T.kps + (size_t)tb * T.stride, tdesc, N2, myNode, qd, nullptr, lane)
+        const int32_t* tnode = GF_IS_BOW(MODE) ? P.tgtNode + (size_t)tb * T.stride : nullptr;
+        const int myNode = GF_IS_BOW(MODE) ? P.srcNode[(size_t)b * P.src.stride + q] : 0;
+        const int32_t* tmp = (MODE == M_BOW2 || MODE == M_TRI) ? P.tgtMp + (size_t)tb * T.stride : nullptr;
+        const float* F12 = (MODE == M_TRI) ? P.F12 + (size_t)b * 9 : nullptr;
+        constexpr int FILT = MODE == M_BOW2 ? 1 : (MODE == M_TRI ? 2 : 0);
+        int cnt = GF_IS_BOW(MODE) ? enum_node<false, FILT>(tnode, T.kps + (size_t)tb * T.stride, tdesc, N2, myNode, qd, nullptr, lane, tmp, x, y, F12, P.scale)
                                   : enum_candidates<false>(cs, ent, tdesc, G, x, y, r, minL, maxL, qd, nullptr, lane);
         if (cnt > 0) {
             int off = 0;
@@ -410,7 +523,7 @@ __global__ void __launch_bounds__(128) k_candidates(const QParams P, const Frame
             if (off + cnt > poolCap) {
                 if (lane == 0) atomicExch(err, GFORB_ERR_OVERFLOW);
             } else {
-                if (MODE == M_BOW) enum_node<true>(tnode, T.kps + (size_t)tb * T.stride, tdesc, N2, myNode, qd, pool + (size_t)b * poolCap + off, lane);
+                if (GF_IS_BOW(MODE)) enum_node<true, FILT>(tnode, T.kps + (size_t)tb * T.stride, tdesc, N2, myNode, qd, pool + (size_t)b * poolCap + off, lane, tmp, x, y, F12, P.scale);
                 else enum_candidates<true>(cs, ent, tdesc, G, x, y, r, minL, maxL, qd, pool + (size_t)b * poolCap + off, lane);
                 meta = make_int2(off, cnt);
             }
@@ -436,7 +549,8 @@ struct RParams {
     float* prevMatched;   // INIT
     int32_t* nmatches;
     int* rotBinQ;         // INIT scratch: batch x maxQ
-    const int32_t* order; // BOW: batch x maxQ, query index per position of the walk
+    const int32_t* order; // BOW / BOW2 / TRI: batch x maxQ, query index per position of the walk
+    const int32_t* tgtMpIds;   // BOW2: pKF2->GetMapPointMatches() as ids (the value written to matches12)
     int thHigh;           // LAST / KF: acceptance threshold (TH_HIGH; ORBdist for the keyframe overload)
     int laneParallel;     // INIT: queries one after the other, the candidates of a query over the lanes (0: speculative rounds)
 };
@@ -466,7 +580,7 @@ __global__ void __launch_bounds__(32) k_resolve(const RParams R) {
     const size_t tOff = (size_t)b * R.tgt.stride, sOff = (size_t)b * R.src.stride;
     for (int i = lane; i < N2; i += 32) {
         if (MODE == M_MAP || MODE == M_LAST || MODE == M_PROJ2) state[i] = R.tgtMp[tOff + i];
-        else if (MODE == M_WINDOW || MODE == M_BOW) state[i] = -1;
+        else if (MODE == M_WINDOW || GF_IS_BOW(MODE)) state[i] = -1;
         else state[i] = INT_MAX;
         owner[i] = -1;
         rnd[i] = 0xffffffffu;
@@ -477,6 +591,8 @@ __global__ void __launch_bounds__(32) k_resolve(const RParams R) {
             R.matches12[sOff + i] = -1;
             if (i < R.maxQ) R.rotBinQ[(size_t)b * R.maxQ + i] = -1;
         }
+    if (MODE == M_BOW2 || MODE == M_TRI)
+        for (int i = lane; i < R.src.stride; i += 32) R.matches12[sOff + i] = -1;
     __syncwarp();
     int accepted = 0;
     if (MODE == M_INIT && R.laneParallel) {
@@ -574,7 +690,7 @@ __global__ void __launch_bounds__(32) k_resolve(const RParams R) {
     } else
     for (int qb = 0; qb < Q; qb += 32) {
         int q = qb + lane;
-        if (MODE == M_BOW && q < Q) q = R.order[(size_t)b * R.maxQ + q];       // (node, index) order of the reference's walk
+        if (GF_IS_BOW(MODE) && q < Q) q = R.order[(size_t)b * R.maxQ + q];     // (node, index) order of the reference's walk
         int2 meta = make_int2(0, 0);
         if (qb + lane < Q) meta = R.qMeta[(size_t)b * R.maxQ + q];
         const uint32_t* list = R.pool + (size_t)b * R.poolCap + meta.x;
@@ -583,7 +699,30 @@ __global__ void __launch_bounds__(32) k_resolve(const RParams R) {
         while (__any_sync(full, !done)) {
             bool acc = false;
             int bi = -1, bi2 = -1, best = INT_MAX;     // bi2 = the candidate that defines the second-best distance
-            if (!done) {
+            if (MODE == M_TRI && !done) {
+                // SearchForTriangulation (:1476-1533): the unmatched candidates sorted by (distance, index); the first one with
+                // distance <= 2 * best that passes the epipolar test (bit 31, set by k_candidates) is taken.  bi2 = the entry
+                // that defines `best`, bi = the chosen one: the outcome depends on the claim state only through these two.
+                unsigned kmin = 0xffffffffu, kch = 0xffffffffu;
+                for (int c = 0; c < cnt; c++) {
+                    const uint32_t e = list[c];
+                    const int i2 = e & 0xffff;
+                    if (state[i2] >= 0) continue;                               // vbMatched2 (:1485)
+                    kmin = min(kmin, (((e >> 20) & 0x1ffu) << 16) | (unsigned)i2);
+                }
+                if (kmin != 0xffffffffu) {
+                    bi2 = (int)(kmin & 0xffffu);
+                    const unsigned distTh = 2u * (kmin >> 16);                  // round(2*BestDist)
+                    for (int c = 0; c < cnt; c++) {
+                        const uint32_t e = list[c];
+                        const int i2 = e & 0xffff;
+                        const unsigned dist = (e >> 20) & 0x1ffu;
+                        if (!(e >> 31) || dist > distTh || state[i2] >= 0) continue;
+                        kch = min(kch, (dist << 16) | (unsigned)i2);
+                    }
+                    if (kch != 0xffffffffu) { bi = (int)(kch & 0xffffu); best = (int)(kch >> 16); acc = true; }
+                }
+            } else if (!done) {
                 int best2 = INT_MAX, bl = -1, bl2 = -1;
                 for (int c = 0; c < cnt; c++) {
                     const uint32_t e = list[c];
@@ -601,6 +740,7 @@ __global__ void __launch_bounds__(32) k_resolve(const RParams R) {
                     }
                 }
                 if (MODE == M_INIT || MODE == M_BOW) acc = best <= TH_LOW && (float)best < (float)best2 * R.nnratio;   // :1219-1221, :790-792
+                else if (MODE == M_BOW2) acc = best < TH_LOW && (float)best < R.nnratio * (float)best2;                // :1365-1367
                 else if (MODE == M_WINDOW || MODE == M_PROJ2) acc = (float)best <= (float)best2 * R.nnratio && best <= TH_HIGH;
                 else if (MODE == M_LAST) acc = best <= R.thHigh;
                 else acc = best <= TH_HIGH && !(bl == bl2 && (float)best > R.nnratio * (float)best2);
@@ -635,6 +775,14 @@ __global__ void __launch_bounds__(32) k_resolve(const RParams R) {
                         state[bi] = id;
                         R.tgtMp[tOff + bi] = id;
                         R.tgtScore[tOff + bi] = best;
+                        if (R.checkOri) {
+                            const int bin = rot_bin(R.src.kps[sOff + q].angle, R.tgt.kps[tOff + bi].angle);
+                            owner[bi] = bin;
+                            atomicAdd(&hist[bin], 1);
+                        }
+                    } else if (MODE == M_BOW2 || MODE == M_TRI) {
+                        state[bi] = q;                                           // vbMatched2[bestIdx2] = true, by whom
+                        R.matches12[sOff + q] = (MODE == M_BOW2) ? R.tgtMpIds[tOff + bi] : bi;   // :1369 / :1515
                         if (R.checkOri) {
                             const int bin = rot_bin(R.src.kps[sOff + q].angle, R.tgt.kps[tOff + bi].angle);
                             owner[bi] = bin;
@@ -699,6 +847,14 @@ __global__ void __launch_bounds__(32) k_resolve(const RParams R) {
         total = __reduce_add_sync(full, total);
     } else if (MODE == M_MAP || MODE == M_PROJ2) {
         total = __reduce_add_sync(full, accepted);
+    } else if (MODE == M_BOW2 || MODE == M_TRI) {
+        int removed = 0;
+        if (R.checkOri)
+            for (int i = lane; i < N2; i += 32) {
+                const int bin = owner[i];
+                if (bin >= 0 && bin != i1 && bin != i2m && bin != i3) { removed++; R.matches12[sOff + state[i]] = -1; }   // :1409-1419
+            }
+        total = __reduce_add_sync(full, accepted - removed);
     } else {
         int removed = 0;
         if (R.checkOri)
@@ -715,6 +871,51 @@ __global__ void __launch_bounds__(32) k_resolve(const RParams R) {
         total = __reduce_add_sync(full, accepted - removed);
     }
     if (lane == 0) R.nmatches[b] = total;
+}
+
+// Claim-free overloads (Fuse, the two directions of SearchBySim3): the best candidate of every query, first occurrence of the
+// smallest distance (strict `<` over the list in the reference's order).  outIdx = the keypoint when dist <= thrIdx, else -1.
+__global__ void __launch_bounds__(128) k_pick_best(const uint32_t* __restrict__ pool, int poolCap, const int2* __restrict__ qMeta,
+                                                   int maxQ, const int32_t* __restrict__ qCounts, int outStride, int thrIdx,
+                                                   int thrCount, int32_t* __restrict__ outIdx, int32_t* __restrict__ outDist,
+                                                   int32_t* __restrict__ nAccepted) {
+    const int b = blockIdx.y, q = blockIdx.x * 128 + threadIdx.x;
+    const int Q = min(qCounts[b], maxQ);
+    int bestDist = INT_MAX, bestIdx = -1;
+    if (q < Q) {
+        const int2 meta = qMeta[(size_t)b * maxQ + q];
+        const uint32_t* list = pool + (size_t)b * poolCap + meta.x;
+        for (int c = 0; c < meta.y; c++) {
+            const uint32_t e = list[c];
+            const int dist = (int)(e >> 20);
+            if (dist < bestDist) { bestDist = dist; bestIdx = (int)(e & 0xffff); }
+        }
+    }
+    if (q < outStride) {
+        outIdx[(size_t)b * outStride + q] = (q < Q && bestDist <= thrIdx) ? bestIdx : -1;
+        if (outDist) outDist[(size_t)b * outStride + q] = (q < Q) ? bestDist : INT_MAX;
+    }
+    if (nAccepted) {
+        const unsigned m = __ballot_sync(0xffffffffu, q < Q && bestDist <= thrCount);
+        if ((threadIdx.x & 31) == 0 && m) atomicAdd(&nAccepted[b], __popc(m));
+    }
+}
+
+// SearchBySim3, "check agreement" (:2060-2076)
+__global__ void __launch_bounds__(128) k_sim3_agree(const int32_t* __restrict__ vnMatch1, int stride1, const int32_t* __restrict__ vnMatch2,
+                                                    int stride2, const int32_t* __restrict__ n1, const int32_t* __restrict__ mp2,
+                                                    int32_t* __restrict__ matches12, int32_t* __restrict__ nFound) {
+    const int b = blockIdx.y, i1 = blockIdx.x * 128 + threadIdx.x;
+    bool ok = false;
+    if (i1 < min(n1[b], stride1)) {
+        const int idx2 = vnMatch1[(size_t)b * stride1 + i1];
+        if (idx2 >= 0 && idx2 < stride2 && vnMatch2[(size_t)b * stride2 + idx2] == i1) {
+            matches12[(size_t)b * stride1 + i1] = mp2[(size_t)b * stride2 + idx2];
+            ok = true;
+        }
+    }
+    const unsigned m = __ballot_sync(0xffffffffu, ok);
+    if ((threadIdx.x & 31) == 0 && m) atomicAdd(&nFound[b], __popc(m));
 }
 
 }  // namespace gforb
@@ -760,8 +961,8 @@ __global__ void __launch_bounds__(128) k_undistort(const UndistortParams P) {
     P.keysUn[(size_t)b * P.stride + i] = kp;
 }
 
-// src/Frame.cc:166-227 for every map point of `batch` frames: thread per point.  cv::Mat arithmetic restated: Rcw * P
-// accumulates each row in double and casts to float before + tcw; cv::norm / Mat::dot accumulate double products.
+// src/Frame.cc:166-227 for every map point of `batch` frames: thread per point.  cv::Mat arithmetic restated: Rcw * P + tcw
+// is one small-matrix cv::gemm (common.cuh: cv_gemm_row); cv::norm / Mat::dot accumulate double products.
 struct FrustumParams {
     const float *Rcw, *tcw, *Ow;          // batch x 9 / 3 / 3
     float fx, fy, cx, cy;
@@ -789,10 +990,7 @@ __global__ void __launch_bounds__(128) k_is_in_frustum(const FrustumParams F) {
     bool in = true;
     float Pc[3];
 #pragma unroll
-    for (int r = 0; r < 3; r++) {
-        const double s = (double)R[r * 3 + 0] * (double)P0 + (double)R[r * 3 + 1] * (double)P1 + (double)R[r * 3 + 2] * (double)P2;
-        Pc[r] = (float)s + t[r];
-    }
+    for (int r = 0; r < 3; r++) Pc[r] = cv_gemm_row(R[r * 3], R[r * 3 + 1], R[r * 3 + 2], P0, P1, P2, t[r]);   // mRcw*P+mtcw
     if (Pc[2] < 0.0f) in = false;
     const float invz = (float)(1.0 / (double)Pc[2]);
     const float u = F.fx * Pc[0] * invz + F.cx;
@@ -1132,6 +1330,8 @@ int gforb_matcher_create(const GforbMatcherConfig* cfg, GforbMatcher** out) {
     GF_CUDA_OK(raise_dyn_smem(k_resolve<M_LAST>, smem, cfg->device));
     GF_CUDA_OK(raise_dyn_smem(k_resolve<M_PROJ2>, smem, cfg->device));
     GF_CUDA_OK(raise_dyn_smem(k_resolve<M_BOW>, smem, cfg->device));
+    GF_CUDA_OK(raise_dyn_smem(k_resolve<M_BOW2>, smem, cfg->device));
+    GF_CUDA_OK(raise_dyn_smem(k_resolve<M_TRI>, smem, cfg->device));
         return GFORB_OK;
     };
     if (const int rc = init()) { gforb_matcher_destroy(M); return rc; }   // a failure part-way frees what was allocated
@@ -1632,6 +1832,202 @@ int gforb_search_by_projection_keyframe(GforbMatcher* M, const GforbFrameSet* cu
     R.checkOri = check_orientation; R.tgtMp = dMp; R.tgtScore = dSc; R.nmatches = dN; R.rotBinQ = M->d_rotBinQ;
     R.thHigh = orb_dist;
     run_resolve<M_LAST>(M, c, R, batch);
+    return end_call(M, c, flags);
+}
+
+}  // extern "C"
+
+// ---- the overloads of the mapping / loop-closing threads
+// shared body of SearchByBoW(pKF1, pKF2, vpMatches12) and SearchForTriangulation: the walk of gforb_search_by_bow with the
+// keyframe-pair filters and outputs per KF1 feature
+template <int MODE>
+static int bow_pair(GforbMatcher* M, const GforbFrameSet* KF1, const int32_t* kf1_mappoints, const int32_t* kf1_nodes,
+                    const GforbFrameSet* KF2, const int32_t* kf2_mappoints, const int32_t* kf2_nodes, int batch, const float* F12,
+                    float nnratio, int check_orientation, int32_t* matches12, int32_t* nmatches, int flags, void* stream) {
+    Ctx c;
+    int rc = begin_call(M, batch, flags, stream, c);
+    if (rc) return rc;
+    if ((rc = check_frames(M, KF1)) || (rc = check_frames(M, KF2))) return rc;
+    if (!kf1_mappoints || !kf1_nodes || !kf2_mappoints || !kf2_nodes || !matches12 || !nmatches || (MODE == M_TRI && !F12))
+        return GFORB_ERR_ARG;
+    if (KF1->kp_stride > M->cfg.max_queries) return GFORB_ERR_CAPACITY;
+    if (batch == 0) return GFORB_OK;
+    FrameDev S = c.frame(KF1, batch), T = c.frame(KF2, batch);
+    GridGeom G = geom_of(KF2);
+    QParams P;
+    memset(&P, 0, sizeof(P));
+    fill_scale(M, P);
+    P.src = S; P.srcMp = c.in(kf1_mappoints, (size_t)batch * KF1->kp_stride);
+    P.srcNode = c.in(kf1_nodes, (size_t)batch * KF1->kp_stride);
+    P.tgtNode = c.in(kf2_nodes, (size_t)batch * KF2->kp_stride);
+    P.tgtMp = c.in(kf2_mappoints, (size_t)batch * KF2->kp_stride);
+    P.F12 = (MODE == M_TRI) ? c.in(F12, (size_t)batch * 9) : nullptr;
+    P.order = M->d_rotBinQ;
+    int32_t* dM = c.out(matches12, (size_t)batch * KF1->kp_stride, false);
+    int32_t* dN = c.out(nmatches, (size_t)batch, false);
+    if (c.rc) return c.rc;
+    run_candidates<MODE>(M, c, P, T, G, batch, KF1->kp_stride);
+    RParams R;
+    memset(&R, 0, sizeof(R));
+    R.src = S; R.tgt = T; R.pool = M->d_pool; R.poolCap = M->poolCap; R.qMeta = M->d_qMeta; R.maxQ = M->cfg.max_queries;
+    R.maxKp = M->cfg.max_keypoints; R.qCounts = S.counts; R.srcMp = P.srcMp; R.nnratio = nnratio;
+    R.checkOri = check_orientation; R.matches12 = dM; R.nmatches = dN; R.rotBinQ = M->d_rotBinQ; R.order = M->d_rotBinQ;
+    R.tgtMpIds = P.tgtMp;
+    run_resolve<MODE>(M, c, R, batch);
+    return end_call(M, c, flags);
+}
+
+extern "C" {
+
+int gforb_search_by_bow_keyframes(GforbMatcher* M, const GforbFrameSet* KF1, const int32_t* kf1_mappoints, const int32_t* kf1_nodes,
+                                  const GforbFrameSet* KF2, const int32_t* kf2_mappoints, const int32_t* kf2_nodes, int batch,
+                                  float nnratio, int check_orientation, int32_t* matches12, int32_t* nmatches, int flags,
+                                  void* stream) {
+    return bow_pair<M_BOW2>(M, KF1, kf1_mappoints, kf1_nodes, KF2, kf2_mappoints, kf2_nodes, batch, nullptr, nnratio, check_orientation,
+                            matches12, nmatches, flags, stream);
+}
+
+int gforb_search_for_triangulation(GforbMatcher* M, const GforbFrameSet* KF1, const int32_t* kf1_mappoints, const int32_t* kf1_nodes,
+                                   const GforbFrameSet* KF2, const int32_t* kf2_mappoints, const int32_t* kf2_nodes, int batch,
+                                   const float* F12, int check_orientation, int32_t* matches12, int32_t* nmatches, int flags,
+                                   void* stream) {
+    return bow_pair<M_TRI>(M, KF1, kf1_mappoints, kf1_nodes, KF2, kf2_mappoints, kf2_nodes, batch, F12, 0.0f, check_orientation,
+                           matches12, nmatches, flags, stream);
+}
+
+namespace {
+int check_points(GforbMatcher* M, const GforbWorldPointSet* p, bool needNormal) {
+    if (!p || !p->world || !p->min_distance || !p->max_distance || !p->descriptors || !p->counts || p->mp_stride <= 0) return GFORB_ERR_ARG;
+    if (needNormal && !p->normal) return GFORB_ERR_ARG;
+    if (p->mp_stride > M->cfg.max_queries) return GFORB_ERR_CAPACITY;
+    return GFORB_OK;
+}
+void stage_points(Ctx& c, QParams& P, const GforbWorldPointSet* p, int batch, bool withNormal) {
+    const size_t nm = (size_t)batch * p->mp_stride;
+    P.pWorld = c.in(p->world, nm * 3);
+    P.pNormal = withNormal ? c.in(p->normal, nm * 3) : nullptr;
+    P.pMinD = c.in(p->min_distance, nm); P.pMaxD = c.in(p->max_distance, nm);
+    P.mpDesc = c.in(p->descriptors, nm * 32);
+    P.pSkip = c.in(p->skip, nm);
+    P.mpCounts = c.in(p->counts, (size_t)batch); P.mpStride = p->mp_stride;
+}
+void run_pick(GforbMatcher* M, Ctx& c, const int32_t* qCounts, int batch, int outStride, int thrIdx, int thrCount, int32_t* outIdx,
+              int32_t* outDist, int32_t* nAccepted) {
+    k_pick_best<<<dim3((outStride + 127) / 128, batch), 128, 0, c.st>>>(M->d_pool, M->poolCap, M->d_qMeta, M->cfg.max_queries, qCounts,
+                                                                         outStride, thrIdx, thrCount, outIdx, outDist, nAccepted);
+    M->lastLaunches++;
+}
+}  // namespace
+
+int gforb_fuse(GforbMatcher* M, const GforbFrameSet* KF, int batch, const float* pose, int is_sim3, float fx, float fy, float cx,
+               float cy, const GforbWorldPointSet* points, float th, int32_t* best_idx, int32_t* best_dist, int32_t* nfused,
+               int flags, void* stream) {
+    Ctx c;
+    int rc = begin_call(M, batch, flags, stream, c);
+    if (rc) return rc;
+    if ((rc = check_frames(M, KF)) || (rc = check_points(M, points, true))) return rc;
+    if (!pose || !best_idx || !best_dist || !nfused) return GFORB_ERR_ARG;
+    if (batch == 0) return GFORB_OK;
+    FrameDev T = c.frame(KF, batch);
+    GridGeom G = geom_of(KF);
+    QParams P;
+    memset(&P, 0, sizeof(P));
+    fill_scale(M, P);
+    stage_points(c, P, points, batch, true);
+    P.Tcw = c.in(pose, (size_t)batch * 16); P.pkfMode = is_sim3 ? 1 : 0;
+    P.fx = fx; P.fy = fy; P.cx = cx; P.cy = cy; P.th = th;
+    const size_t nm = (size_t)batch * points->mp_stride;
+    int32_t* dIdx = c.out(best_idx, nm, false);
+    int32_t* dDist = c.out(best_dist, nm, false);
+    int32_t* dN = c.out(nfused, (size_t)batch, false);
+    if (c.rc) return c.rc;
+    GF_CUDA_OK(cudaMemsetAsync(dN, 0, sizeof(int32_t) * batch, c.st));
+    build_grid(M, c, T, G, batch);
+    run_candidates<M_PKF>(M, c, P, T, G, batch, points->mp_stride);
+    run_pick(M, c, P.mpCounts, batch, points->mp_stride, INT_MAX - 1, TH_LOW, dIdx, dDist, dN);
+    return end_call(M, c, flags);
+}
+
+int gforb_search_by_projection_sim3(GforbMatcher* M, const GforbFrameSet* KF, int batch, const float* Scw, float fx, float fy,
+                                    float cx, float cy, const GforbWorldPointSet* points, const int32_t* point_ids, float th,
+                                    int32_t* matched, int32_t* nmatches, int flags, void* stream) {
+    Ctx c;
+    int rc = begin_call(M, batch, flags, stream, c);
+    if (rc) return rc;
+    if ((rc = check_frames(M, KF)) || (rc = check_points(M, points, true))) return rc;
+    if (!Scw || !point_ids || !matched || !nmatches) return GFORB_ERR_ARG;
+    if (batch == 0) return GFORB_OK;
+    FrameDev T = c.frame(KF, batch);
+    GridGeom G = geom_of(KF);
+    QParams P;
+    memset(&P, 0, sizeof(P));
+    fill_scale(M, P);
+    stage_points(c, P, points, batch, true);
+    P.Tcw = c.in(Scw, (size_t)batch * 16); P.pkfMode = 1;
+    P.fx = fx; P.fy = fy; P.cx = cx; P.cy = cy; P.th = th;
+    const int32_t* dIds = c.in(point_ids, (size_t)batch * points->mp_stride);
+    int32_t* dM = c.out(matched, (size_t)batch * KF->kp_stride, true);
+    int32_t* dSc = (int32_t*)M->arena.take((size_t)batch * KF->kp_stride * sizeof(int32_t));     // distances of the claims (not returned)
+    if (!dSc) return GFORB_ERR_CAPACITY;
+    int32_t* dN = c.out(nmatches, (size_t)batch, false);
+    if (c.rc) return c.rc;
+    build_grid(M, c, T, G, batch);
+    run_candidates<M_PKF>(M, c, P, T, G, batch, points->mp_stride);
+    RParams R;                                     // claims as in (Cur, Last): best unclaimed candidate, threshold TH_LOW, no histogram
+    memset(&R, 0, sizeof(R));
+    R.src = T; R.src.stride = points->mp_stride; R.tgt = T; R.pool = M->d_pool; R.poolCap = M->poolCap; R.qMeta = M->d_qMeta;
+    R.maxQ = M->cfg.max_queries; R.maxKp = M->cfg.max_keypoints; R.qCounts = P.mpCounts; R.srcMp = dIds; R.checkOri = 0;
+    R.tgtMp = dM; R.tgtScore = dSc; R.nmatches = dN; R.rotBinQ = M->d_rotBinQ; R.thHigh = TH_LOW;
+    run_resolve<M_LAST>(M, c, R, batch);
+    return end_call(M, c, flags);
+}
+
+int gforb_search_by_sim3(GforbMatcher* M, const GforbFrameSet* KF1, const GforbFrameSet* KF2, int batch,
+                         const GforbWorldPointSet* points1, const GforbWorldPointSet* points2, const int32_t* kf2_mappoints,
+                         const float* T1w, const float* T2w, const float* s12, const float* R12, const float* t12, float fx, float fy,
+                         float cx, float cy, float th, int32_t* matches12, int32_t* nfound, int flags, void* stream) {
+    Ctx c;
+    int rc = begin_call(M, batch, flags, stream, c);
+    if (rc) return rc;
+    if ((rc = check_frames(M, KF1)) || (rc = check_frames(M, KF2)) || (rc = check_points(M, points1, false)) ||
+        (rc = check_points(M, points2, false)))
+        return rc;
+    if (!kf2_mappoints || !T1w || !T2w || !s12 || !R12 || !t12 || !matches12 || !nfound) return GFORB_ERR_ARG;
+    if (points1->mp_stride != KF1->kp_stride || points2->mp_stride != KF2->kp_stride) return GFORB_ERR_ARG;
+    if (batch == 0) return GFORB_OK;
+    FrameDev F1 = c.frame(KF1, batch), F2 = c.frame(KF2, batch);
+    const float* dT1 = c.in(T1w, (size_t)batch * 16);
+    const float* dT2 = c.in(T2w, (size_t)batch * 16);
+    const float* dS = c.in(s12, (size_t)batch);
+    const float* dR = c.in(R12, (size_t)batch * 9);
+    const float* dt = c.in(t12, (size_t)batch * 3);
+    const int32_t* dMp2 = c.in(kf2_mappoints, (size_t)batch * KF2->kp_stride);
+    int32_t* dM12 = c.out(matches12, (size_t)batch * KF1->kp_stride, true);
+    int32_t* dN = c.out(nfound, (size_t)batch, false);
+    int32_t* vn1 = (int32_t*)M->arena.take((size_t)batch * KF1->kp_stride * sizeof(int32_t));
+    int32_t* vn2 = (int32_t*)M->arena.take((size_t)batch * KF2->kp_stride * sizeof(int32_t));
+    if (!vn1 || !vn2) return GFORB_ERR_CAPACITY;
+    QParams P1, P2;
+    memset(&P1, 0, sizeof(P1)); memset(&P2, 0, sizeof(P2));
+    fill_scale(M, P1); fill_scale(M, P2);
+    stage_points(c, P1, points1, batch, false);
+    stage_points(c, P2, points2, batch, false);
+    if (c.rc) return c.rc;
+    P1.Tcw = dT1; P1.pkfMode = 2; P2.Tcw = dT2; P2.pkfMode = 3;
+    for (QParams* P : {&P1, &P2}) { P->s12 = dS; P->R12 = dR; P->t12 = dt; P->fx = fx; P->fy = fy; P->cx = cx; P->cy = cy; P->th = th; }
+    GF_CUDA_OK(cudaMemsetAsync(dN, 0, sizeof(int32_t) * batch, c.st));
+    // KF1's map points into KF2 (:1893-1973), then KF2's into KF1 (:1976-2058): the grid, pool and query scratch are reused
+    // one direction after the other on the stream
+    const GridGeom G2 = geom_of(KF2), G1 = geom_of(KF1);
+    build_grid(M, c, F2, G2, batch);
+    run_candidates<M_PKF>(M, c, P1, F2, G2, batch, KF1->kp_stride);
+    run_pick(M, c, P1.mpCounts, batch, KF1->kp_stride, TH_HIGH, INT_MIN, vn1, nullptr, nullptr);
+    build_grid(M, c, F1, G1, batch);
+    run_candidates<M_PKF>(M, c, P2, F1, G1, batch, KF2->kp_stride);
+    run_pick(M, c, P2.mpCounts, batch, KF2->kp_stride, TH_HIGH, INT_MIN, vn2, nullptr, nullptr);
+    k_sim3_agree<<<dim3((KF1->kp_stride + 127) / 128, batch), 128, 0, c.st>>>(vn1, KF1->kp_stride, vn2, KF2->kp_stride, P1.mpCounts, dMp2,
+                                                                              dM12, dN);
+    M->lastLaunches++;
     return end_call(M, c, flags);
 }
 

@@ -8,7 +8,7 @@ import ctypes as C
 import numpy as np
 
 from . import _lib
-from ._lib import KP_DTYPE, FrameSet, MapPointSet, MatcherConfig, check, is_device, ptr
+from ._lib import KP_DTYPE, FrameSet, MapPointSet, MatcherConfig, WorldPointSet, check, is_device, ptr
 
 TH_LOW, TH_HIGH, HISTO_LENGTH = 50, 100, 30      # src/ORBmatcher.cc:40-42
 
@@ -53,6 +53,19 @@ class MapPoints:
 
     def cstruct(self) -> MapPointSet:
         return MapPointSet(*[_raw(x) for x in self.a], self.stride)
+
+
+class WorldPoints:
+    """SoA of the MapPoint fields the mapping / loop-closing overloads read (GforbWorldPointSet); arrays (B, stride[, 3 | 32]).
+    skip non-zero = the reference `continue`s before projecting (NULL, isBad(), already found / in the keyframe)."""
+
+    def __init__(self, world, normal, min_distance, max_distance, descriptors, skip, counts):
+        self.a = (world, normal, min_distance, max_distance, descriptors, skip, counts)
+        self.batch, self.stride = int(world.shape[0]), int(world.shape[1])
+        self.device = is_device(world)
+
+    def cstruct(self) -> WorldPointSet:
+        return WorldPointSet(*[_raw(x) for x in self.a], self.stride)
 
 
 class ORBmatcher:
@@ -339,6 +352,78 @@ class ORBmatcher:
             ptr(cur_score), ptr(nmatches), self._flags(Cur.device, out_dev, sync), C.c_void_p(stream or 0)),
             "gforb_search_by_projection_keyframe")
         return nmatches
+
+    # -- the overloads of the LocalMapping / LoopClosing threads
+    def SearchByBoWKeyFrames(self, KF1: Frames, kf1_mappoints, kf1_nodes, KF2: Frames, kf2_mappoints, kf2_nodes, matches12, *,
+                             nmatches=None, stream=None, sync=True):
+        """ORBmatcher::SearchByBoW(KeyFrame*, KeyFrame*, vpMatches12) (src/ORBmatcher.cc:1289-1424); matches12 (B, KF1.stride)
+        int32 out = id of the matched KF2 map point or -1."""
+        out_dev = is_device(matches12)
+        if nmatches is None:
+            nmatches = self._nm(KF1.batch, matches12, out_dev)
+        a, b = KF1.cstruct(), KF2.cstruct()
+        check(_lib.lib().gforb_search_by_bow_keyframes(
+            self._h, C.byref(a), ptr(kf1_mappoints), ptr(kf1_nodes), C.byref(b), ptr(kf2_mappoints), ptr(kf2_nodes), KF1.batch,
+            self.mfNNratio, int(self.mbCheckOrientation), ptr(matches12), ptr(nmatches), self._flags(KF1.device, out_dev, sync),
+            C.c_void_p(stream or 0)), "gforb_search_by_bow_keyframes")
+        return nmatches
+
+    def SearchForTriangulation(self, KF1: Frames, kf1_mappoints, kf1_nodes, KF2: Frames, kf2_mappoints, kf2_nodes, F12, matches12, *,
+                               nmatches=None, stream=None, sync=True):
+        """ORBmatcher::SearchForTriangulation (src/ORBmatcher.cc:1426-1588); F12 (B, 9); matches12 (B, KF1.stride) out = index
+        into KF2 or -1 (vMatchedPairs = the pairs (i, matches12[i]) in ascending i)."""
+        out_dev = is_device(matches12)
+        if nmatches is None:
+            nmatches = self._nm(KF1.batch, matches12, out_dev)
+        a, b = KF1.cstruct(), KF2.cstruct()
+        check(_lib.lib().gforb_search_for_triangulation(
+            self._h, C.byref(a), ptr(kf1_mappoints), ptr(kf1_nodes), C.byref(b), ptr(kf2_mappoints), ptr(kf2_nodes), KF1.batch,
+            ptr(F12), int(self.mbCheckOrientation), ptr(matches12), ptr(nmatches), self._flags(KF1.device, out_dev, sync),
+            C.c_void_p(stream or 0)), "gforb_search_for_triangulation")
+        return nmatches
+
+    def Fuse(self, KF: Frames, pose, K, points: WorldPoints, th, best_idx, best_dist, *, sim3=False, nfused=None, stream=None, sync=True):
+        """The matching loop of ORBmatcher::Fuse(pKF, vpMapPoints, th) (pose = Tcw, src/ORBmatcher.cc:1590-1708) or, with
+        sim3=True, Fuse(pKF, Scw, vpPoints, th) (:1710-1839): best keypoint and distance per list entry; the caller applies
+        Replace / AddObservation in list order."""
+        out_dev = is_device(best_idx)
+        if nfused is None:
+            nfused = self._nm(KF.batch, best_idx, out_dev)
+        fx, fy, cx, cy = [float(v) for v in K]
+        a, w = KF.cstruct(), points.cstruct()
+        check(_lib.lib().gforb_fuse(self._h, C.byref(a), KF.batch, ptr(pose), int(sim3), fx, fy, cx, cy, C.byref(w), float(th),
+                                    ptr(best_idx), ptr(best_dist), ptr(nfused), self._flags(KF.device, out_dev, sync),
+                                    C.c_void_p(stream or 0)), "gforb_fuse")
+        return nfused
+
+    def SearchByProjectionSim3(self, KF: Frames, Scw, K, points: WorldPoints, point_ids, th, matched, *, nmatches=None, stream=None,
+                               sync=True):
+        """ORBmatcher::SearchByProjection(pKF, Scw, vpPoints, vpMatched, th) (src/ORBmatcher.cc:855-977); matched (B, KF.stride)
+        in/out ids."""
+        out_dev = is_device(matched)
+        if nmatches is None:
+            nmatches = self._nm(KF.batch, matched, out_dev)
+        fx, fy, cx, cy = [float(v) for v in K]
+        a, w = KF.cstruct(), points.cstruct()
+        check(_lib.lib().gforb_search_by_projection_sim3(self._h, C.byref(a), KF.batch, ptr(Scw), fx, fy, cx, cy, C.byref(w),
+                                                         ptr(point_ids), float(th), ptr(matched), ptr(nmatches),
+                                                         self._flags(KF.device, out_dev, sync), C.c_void_p(stream or 0)),
+              "gforb_search_by_projection_sim3")
+        return nmatches
+
+    def SearchBySim3(self, KF1: Frames, KF2: Frames, points1: WorldPoints, points2: WorldPoints, kf2_mappoints, T1w, T2w, s12, R12, t12,
+                     K, th, matches12, *, nfound=None, stream=None, sync=True):
+        """ORBmatcher::SearchBySim3 (src/ORBmatcher.cc:1841-2079); matches12 (B, KF1.stride) in/out ids."""
+        out_dev = is_device(matches12)
+        if nfound is None:
+            nfound = self._nm(KF1.batch, matches12, out_dev)
+        fx, fy, cx, cy = [float(v) for v in K]
+        a, b, w1, w2 = KF1.cstruct(), KF2.cstruct(), points1.cstruct(), points2.cstruct()
+        check(_lib.lib().gforb_search_by_sim3(self._h, C.byref(a), C.byref(b), KF1.batch, C.byref(w1), C.byref(w2), ptr(kf2_mappoints),
+                                              ptr(T1w), ptr(T2w), ptr(s12), ptr(R12), ptr(t12), fx, fy, cx, cy, float(th),
+                                              ptr(matches12), ptr(nfound), self._flags(KF1.device, out_dev, sync),
+                                              C.c_void_p(stream or 0)), "gforb_search_by_sim3")
+        return nfound
 
     # -- all-pairs top-2 against a database shard resident in HBM (torch CUDA uint8 tensors)
     def AllPairsTop2(self, queries, db, idx_base=0, *, out=None, stream=None, sync=True):

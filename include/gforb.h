@@ -269,6 +269,74 @@ int gforb_search_by_projection_keyframe(GforbMatcher* h, const GforbFrameSet* cu
                                         float fx, float fy, float cx, float cy, float th, int orb_dist, int check_orientation,
                                         int32_t* cur_mappoints, int32_t* cur_score, int32_t* nmatches, int flags, void* stream);
 
+/* ---- the ORBmatcher overloads of the LocalMapping / LoopClosing threads: same Hamming core, candidate
+ * order and claim rules as above.  Map mutations (MapPoint::Replace, AddObservation, KeyFrame::AddMapPoint) stay with the
+ * caller: the calls return what the reference's matching loop decides, the caller applies it to its map. */
+
+/* ORBmatcher::SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, vector<MapPoint*>& vpMatches12) (src/ORBmatcher.cc:1289-1424;
+ * LoopClosing::ComputeSim3).  kf*_mappoints: batch x kp_stride ids of GetMapPointMatches() (-1 = NULL or isBad());
+ * kf*_nodes: DBoW2 FeatureVector node of every feature (-1 = none).  Walk as in gforb_search_by_bow; candidates are the
+ * KF2 features of the node that hold a map point and are not matched yet; best < TH_LOW (strict) and best < nnratio *
+ * second.  matches12: out, batch x KF1.kp_stride = the id vpMapPoints2[bestIdx2] (or -1). */
+int gforb_search_by_bow_keyframes(GforbMatcher* h, const GforbFrameSet* KF1, const int32_t* kf1_mappoints, const int32_t* kf1_nodes,
+                                  const GforbFrameSet* KF2, const int32_t* kf2_mappoints, const int32_t* kf2_nodes, int batch,
+                                  float nnratio, int check_orientation, int32_t* matches12, int32_t* nmatches, int flags,
+                                  void* stream);
+
+/* ORBmatcher::SearchForTriangulation(pKF1, pKF2, F12, vMatchedKeys1, vMatchedKeys2, vMatchedPairs) (src/ORBmatcher.cc:1426-1588;
+ * LocalMapping::CreateNewMapPoints) with CheckDistEpipolarLine (:705-722).  Queries: KF1 features WITHOUT a map point
+ * (kf1_mappoints < 0); candidates: KF2 features of the same node without a map point, not matched yet, distance <= TH_LOW,
+ * visited in (distance, index) order while distance <= 2 * best; the first one within 3.84 sigma2(octave) of the epipolar
+ * line of F12 (batch x 9, row-major) is taken.  matches12: out, batch x KF1.kp_stride = index into KF2 or -1 (the
+ * reference's vMatchedPairs are the pairs (i, matches12[i]) in ascending i). */
+int gforb_search_for_triangulation(GforbMatcher* h, const GforbFrameSet* KF1, const int32_t* kf1_mappoints, const int32_t* kf1_nodes,
+                                   const GforbFrameSet* KF2, const int32_t* kf2_mappoints, const int32_t* kf2_nodes, int batch,
+                                   const float* F12, int check_orientation, int32_t* matches12, int32_t* nmatches, int flags,
+                                   void* stream);
+
+typedef struct GforbWorldPointSet {   /* MapPoint fields the projection overloads below read; arrays are batch x mp_stride */
+    const float* world;               /* x 3: GetWorldPos() */
+    const float* normal;              /* x 3: GetNormal() (not read by gforb_search_by_sim3; may be NULL there) */
+    const float* min_distance;        /* GetMinDistanceInvariance() */
+    const float* max_distance;        /* GetMaxDistanceInvariance() */
+    const uint8_t* descriptors;       /* x 32: GetDescriptor() */
+    const uint8_t* skip;              /* non-zero: the reference `continue`s before projecting (NULL, isBad(), IsInKeyFrame /
+                                         already found / already matched) */
+    const int32_t* counts;            /* batch: list length */
+    int32_t mp_stride;
+} GforbWorldPointSet;
+
+/* The matching loop of ORBmatcher::Fuse(KeyFrame* pKF, vector<MapPoint*>& vpMapPoints, float th) (src/ORBmatcher.cc:1590-1708,
+ * is_sim3 = 0, pose = Tcw, batch x 16 row-major; Ow = -Rcw.t()*tcw as KeyFrame::SetPose computes it) and of
+ * Fuse(KeyFrame* pKF, cv::Mat Scw, const vector<MapPoint*>& vpPoints, float th) (:1710-1839, is_sim3 = 1, pose = Scw,
+ * decomposed as :1718-1723).  Per list entry: projection, KeyFrame::IsInImage, distance / viewing-angle gates, predicted level,
+ * GetFeaturesInArea(u, v, th * scale[level]), levels level-1 .. level, first smallest distance (no claims).  best_idx /
+ * best_dist: out, batch x mp_stride (-1 / INT_MAX where the point was skipped or had no candidate); nfused: out, batch =
+ * entries with best_dist <= TH_LOW.  The caller walks the list in order and applies Replace / AddObservation (a point that
+ * an earlier entry made bad or added to the keyframe is skipped there, as in the reference). */
+int gforb_fuse(GforbMatcher* h, const GforbFrameSet* KF, int batch, const float* pose, int is_sim3, float fx, float fy, float cx,
+               float cy, const GforbWorldPointSet* points, float th, int32_t* best_idx, int32_t* best_dist, int32_t* nfused,
+               int flags, void* stream);
+
+/* ORBmatcher::SearchByProjection(KeyFrame* pKF, cv::Mat Scw, const vector<MapPoint*>& vpPoints, vector<MapPoint*>& vpMatched,
+ * int th) (src/ORBmatcher.cc:855-977; LoopClosing::ComputeSim3 / CorrectLoop).  points->skip = isBad() or in vpMatched at
+ * entry; point_ids: batch x mp_stride, the id written for a match; matched: in/out, batch x KF.kp_stride (vpMatched as ids,
+ * -1 = NULL): keypoints that hold an id are skipped, best <= TH_LOW claims the keypoint. */
+int gforb_search_by_projection_sim3(GforbMatcher* h, const GforbFrameSet* KF, int batch, const float* Scw, float fx, float fy,
+                                    float cx, float cy, const GforbWorldPointSet* points, const int32_t* point_ids, float th,
+                                    int32_t* matched, int32_t* nmatches, int flags, void* stream);
+
+/* ORBmatcher::SearchBySim3(pKF1, pKF2, vpMatches12, s12, R12, t12, th) (src/ORBmatcher.cc:1841-2079; LoopClosing::ComputeSim3).
+ * points1 / points2: the map points of KF1 / KF2 per keypoint (mp_stride = kp_stride; skip = NULL, isBad() or
+ * vbAlreadyMatched1/2); T1w / T2w: batch x 16 (pKF->GetRotation / GetTranslation); s12: batch; R12: batch x 9; t12: batch x 3;
+ * fx.. = pKF1's intrinsics (the reference uses them for both directions).  Both directions are searched without claims
+ * (best <= TH_HIGH), a pair is kept when the two agree.  kf2_mappoints: ids of KF2's map points; matches12: in/out, batch x
+ * KF1.kp_stride (agreeing pairs receive kf2_mappoints[idx2]); nfound: out, batch. */
+int gforb_search_by_sim3(GforbMatcher* h, const GforbFrameSet* KF1, const GforbFrameSet* KF2, int batch,
+                         const GforbWorldPointSet* points1, const GforbWorldPointSet* points2, const int32_t* kf2_mappoints,
+                         const float* T1w, const float* T2w, const float* s12, const float* R12, const float* t12, float fx, float fy,
+                         float cx, float cy, float th, int32_t* matches12, int32_t* nfound, int flags, void* stream);
+
 /* Batched all-pairs Hamming top-2 of n_q query descriptors against one database shard of n_db descriptors
  * (BASELINE.json config 5; the reference's brute-force analogue is the DescriptorDistance loop of
  * MapPoint::ComputeDistinctiveDescriptors, src/MapPoint.cc:225-250).  out: n_q x 2 packed keys

@@ -315,6 +315,92 @@ def search_by_projection_keyframe(Cur: Frame, KF: Frame, kf_skip, kf_world, kf_m
                                                    C.c_float(0.9), int(checkOri))
 
 
+def cv_rx_plus_t(R, x, t):
+    """cv::Mat R*x + t on CV_32F (3x3, 3x1, 3x1) as the matchers evaluate it (oracle.hpp: cvGemmRxPlusT)"""
+    R = np.ascontiguousarray(R, np.float32); x = np.ascontiguousarray(x, np.float32); t = np.ascontiguousarray(t, np.float32)
+    y = np.empty(3, np.float32)
+    lib().orc_cv_rx_plus_t(_p(R), _p(x), _p(t), _p(y))
+    return y
+
+
+def cv_neg_rt_t(R, t):
+    """cv::Mat -R.t()*t on CV_32F (oracle.hpp: cvNegRtTimesT)"""
+    R = np.ascontiguousarray(R, np.float32); t = np.ascontiguousarray(t, np.float32)
+    y = np.empty(3, np.float32)
+    lib().orc_cv_neg_rt_t(_p(R), _p(t), _p(y))
+    return y
+
+
+def sim3_decompose(Scw):
+    """Scw -> (Rcw, tcw, Ow) as src/ORBmatcher.cc:866-871 computes them"""
+    S = np.ascontiguousarray(Scw, np.float32)
+    R = np.empty((3, 3), np.float32); t = np.empty(3, np.float32); Ow = np.empty(3, np.float32)
+    lib().orc_sim3_decompose(_p(S), _p(R), _p(t), _p(Ow))
+    return R, t, Ow
+
+
+def search_by_bow_keyframes(KF1: Frame, nodes1, KF2: Frame, nodes2, nnratio=0.8, checkOri=True):
+    """ORBmatcher::SearchByBoW(KeyFrame*, KeyFrame*, vpMatches12) (src/ORBmatcher.cc:1289-1424); both keyframes carry their
+    map-point ids (set_mappoints; NULL / bad = -1).  Returns (nmatches, vpMatches12 as ids of KF2's map points)."""
+    n1 = np.ascontiguousarray(nodes1, np.int32); n2 = np.ascontiguousarray(nodes2, np.int32)
+    m = np.full(KF1.N, -1, np.int32)
+    n = lib().orc_search_by_bow_kf(KF1.h, _p(n1), KF2.h, _p(n2), _p(m), C.c_float(nnratio), int(checkOri))
+    return n, m
+
+
+def search_for_triangulation(KF1: Frame, nodes1, KF2: Frame, nodes2, F12, checkOri=True):
+    """ORBmatcher::SearchForTriangulation (src/ORBmatcher.cc:1426-1588).  Returns (nmatches, vMatches12 = index into KF2 or -1)."""
+    n1 = np.ascontiguousarray(nodes1, np.int32); n2 = np.ascontiguousarray(nodes2, np.int32)
+    F = np.ascontiguousarray(F12, np.float32)
+    m = np.full(KF1.N, -1, np.int32)
+    n = lib().orc_search_for_triangulation(KF1.h, _p(n1), KF2.h, _p(n2), _p(F), _p(m), int(checkOri))
+    return n, m
+
+
+def _geom(world, normal, min_dist, max_dist, desc):
+    w = np.ascontiguousarray(world, np.float32)
+    nr = None if normal is None else np.ascontiguousarray(normal, np.float32)
+    return (w, nr, np.ascontiguousarray(min_dist, np.float32), np.ascontiguousarray(max_dist, np.float32),
+            np.ascontiguousarray(desc, np.uint8))
+
+
+def fuse(KF: Frame, Scw, points, world, normal, min_dist, max_dist, desc, th, kf_slot, bad, idx_in_kf):
+    """ORBmatcher::Fuse(pKF, vpMapPoints, th) (Scw None; src/ORBmatcher.cc:1590-1708) / Fuse(pKF, Scw, vpPoints, th) (:1710-1839).
+    points: ids (-1 = NULL); geometry arrays indexed by id; kf_slot (KF.N), bad / idx_in_kf (per id) are the map state, returned
+    updated.  Returns (nFused, bestIdx, bestDist per list position, kf_slot, bad, idx_in_kf)."""
+    pts = np.ascontiguousarray(points, np.int32)
+    w, nr, mn, mx, d = _geom(world, normal, min_dist, max_dist, desc)
+    slot = np.ascontiguousarray(kf_slot, np.int32).copy(); b = np.ascontiguousarray(bad, np.uint8).copy()
+    ik = np.ascontiguousarray(idx_in_kf, np.int32).copy()
+    bi = np.empty(pts.size, np.int32); bd = np.empty(pts.size, np.int32)
+    S = None if Scw is None else np.ascontiguousarray(Scw, np.float32)
+    n = lib().orc_fuse(KF.h, _p(S), _p(pts), pts.size, mn.size, _p(w), _p(nr), _p(mn), _p(mx), _p(d), C.c_float(th), _p(slot), _p(b),
+                       _p(ik), _p(bi), _p(bd))
+    return n, bi, bd, slot, b, ik
+
+
+def search_by_projection_sim3(KF: Frame, Scw, points, world, normal, min_dist, max_dist, desc, bad, matched, th: int):
+    """ORBmatcher::SearchByProjection(pKF, Scw, vpPoints, vpMatched, th) (src/ORBmatcher.cc:855-977).  Returns (nmatches, vpMatched)."""
+    pts = np.ascontiguousarray(points, np.int32)
+    w, nr, mn, mx, d = _geom(world, normal, min_dist, max_dist, desc)
+    b = np.ascontiguousarray(bad, np.uint8); mt = np.ascontiguousarray(matched, np.int32).copy()
+    S = np.ascontiguousarray(Scw, np.float32)
+    n = lib().orc_search_by_projection_sim3(KF.h, _p(S), _p(pts), pts.size, mn.size, _p(w), _p(nr), _p(mn), _p(mx), _p(d), _p(b), _p(mt), int(th))
+    return n, mt
+
+
+def search_by_sim3(KF1: Frame, KF2: Frame, matches12, idx2_in_kf2, world, min_dist, max_dist, desc, bad, s12, R12, t12, th):
+    """ORBmatcher::SearchBySim3 (src/ORBmatcher.cc:1841-2079); KF1 / KF2 carry map-point ids, cameras and poses.  Returns
+    (nFound, vpMatches12 as ids)."""
+    w, _, mn, mx, d = _geom(world, None, min_dist, max_dist, desc)
+    b = np.ascontiguousarray(bad, np.uint8); m = np.ascontiguousarray(matches12, np.int32).copy()
+    i2 = np.ascontiguousarray(idx2_in_kf2, np.int32)
+    R = np.ascontiguousarray(R12, np.float32); t = np.ascontiguousarray(t12, np.float32)
+    n = lib().orc_search_by_sim3(KF1.h, KF2.h, _p(m), _p(i2), mn.size, _p(w), _p(mn), _p(mx), _p(d), _p(b), C.c_float(s12), _p(R), _p(t),
+                                 C.c_float(th))
+    return n, m
+
+
 def window_search(F1: Frame, F2: Frame, window: int, minL=-1, maxL=0x7FFFFFFF, nnratio=0.9, checkOri=True):
     m2 = np.empty(F2.N, np.int32)
     n = lib().orc_window_search(F1.h, F2.h, window, _p(m2), minL, maxL, C.c_float(nnratio), int(checkOri))

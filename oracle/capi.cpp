@@ -206,6 +206,74 @@ int orc_search_by_projection_keyframe(void* cur, void* kf, const uint8_t* kfSkip
     ORBmatcher m(nnratio, checkOri != 0);
     return m.SearchByProjection(*(Frame*)cur, *(const Frame*)kf, kfSkip, kfWorld, kfMinDist, kfMpDesc, th, ORBdist);
 }
+// ---- mapping / loop-closing overloads (orb_matcher_kf.cpp).  Map-point geometry as SoA arrays indexed by id.
+static std::vector<MapPointGeom> geom_of(int nIds, const float* world, const float* normal, const float* minDist, const float* maxDist,
+                                         const uint8_t* desc) {
+    std::vector<MapPointGeom> g(nIds);
+    for (int i = 0; i < nIds; i++) {
+        memcpy(g[i].world, world + 3 * (size_t)i, 12);
+        if (normal) memcpy(g[i].normal, normal + 3 * (size_t)i, 12); else g[i].normal[0] = g[i].normal[1] = g[i].normal[2] = 0;
+        g[i].minDist = minDist[i]; g[i].maxDist = maxDist[i];
+        memcpy(g[i].desc, desc + 32 * (size_t)i, 32);
+    }
+    return g;
+}
+void orc_cv_rx_plus_t(const float* R9, const float* x3, const float* t3, float* y3) { cvGemmRxPlusT(R9, 3, x3, t3, 1, y3); }
+void orc_cv_neg_rt_t(const float* R9, const float* t3, float* Ow3) { cvNegRtTimesT(R9, 3, t3, 1, Ow3); }
+void orc_sim3_decompose(const float* Scw16, float* R9, float* t3, float* Ow3) {
+    const Sim3Rt S = decomposeSim3(Scw16);
+    memcpy(R9, S.R, 36); memcpy(t3, S.t, 12); memcpy(Ow3, S.Ow, 12);
+}
+int orc_search_by_bow_kf(void* kf1, const int* node1, void* kf2, const int* node2, int* matches12, float nnratio, int checkOri) {
+    ORBmatcher m(nnratio, checkOri != 0);
+    std::vector<int> mm;
+    const int n = m.SearchByBoW_KeyFrames(*(const Frame*)kf1, node1, *(const Frame*)kf2, node2, mm);
+    memcpy(matches12, mm.data(), sizeof(int) * mm.size());
+    return n;
+}
+int orc_search_for_triangulation(void* kf1, const int* node1, void* kf2, const int* node2, const float* F12, int* matches12, int checkOri) {
+    ORBmatcher m(0.6f, checkOri != 0);
+    std::vector<int> mm;
+    const int n = m.SearchForTriangulation(*(const Frame*)kf1, node1, *(const Frame*)kf2, node2, F12, mm);
+    memcpy(matches12, mm.data(), sizeof(int) * mm.size());
+    return n;
+}
+// Scw == nullptr: Fuse(pKF, vpMapPoints, th) with the pose in the frame (orc_frame_set_camera); else Fuse(pKF, Scw, vpPoints, th)
+int orc_fuse(void* kf, const float* Scw, const int* points, int nPoints, int nIds, const float* world, const float* normal,
+             const float* minDist, const float* maxDist, const uint8_t* desc, float th, int* kfSlot, uint8_t* bad, int* idxInKF,
+             int* bestIdx, int* bestDist) {
+    const Frame& KF = *(const Frame*)kf;
+    const std::vector<MapPointGeom> g = geom_of(nIds, world, normal, minDist, maxDist, desc);
+    std::vector<int> pts(points, points + nPoints), slot(kfSlot, kfSlot + KF.N), inKF(idxInKF, idxInKF + nIds), bi, bd;
+    std::vector<uint8_t> b(bad, bad + nIds);
+    ORBmatcher m;
+    const int n = Scw ? m.Fuse(KF, Scw, pts, g.data(), th, slot, b, inKF, bi, bd) : m.Fuse(KF, pts, g.data(), th, slot, b, inKF, bi, bd);
+    memcpy(kfSlot, slot.data(), sizeof(int) * slot.size()); memcpy(bad, b.data(), b.size()); memcpy(idxInKF, inKF.data(), sizeof(int) * inKF.size());
+    memcpy(bestIdx, bi.data(), sizeof(int) * bi.size()); memcpy(bestDist, bd.data(), sizeof(int) * bd.size());
+    return n;
+}
+int orc_search_by_projection_sim3(void* kf, const float* Scw, const int* points, int nPoints, int nIds, const float* world,
+                                  const float* normal, const float* minDist, const float* maxDist, const uint8_t* desc,
+                                  const uint8_t* bad, int* matched, int th) {
+    const Frame& KF = *(const Frame*)kf;
+    const std::vector<MapPointGeom> g = geom_of(nIds, world, normal, minDist, maxDist, desc);
+    std::vector<int> pts(points, points + nPoints), mt(matched, matched + KF.N);
+    ORBmatcher m;
+    const int n = m.SearchByProjection(KF, Scw, pts, g.data(), bad, mt, th);
+    memcpy(matched, mt.data(), sizeof(int) * mt.size());
+    return n;
+}
+int orc_search_by_sim3(void* kf1, void* kf2, int* matches12, const int* idx2InKF2, int nIds, const float* world, const float* minDist,
+                       const float* maxDist, const uint8_t* desc, const uint8_t* bad, float s12, const float* R12, const float* t12,
+                       float th) {
+    const Frame& KF1 = *(const Frame*)kf1;
+    const std::vector<MapPointGeom> g = geom_of(nIds, world, nullptr, minDist, maxDist, desc);
+    std::vector<int> m12(matches12, matches12 + KF1.N);
+    ORBmatcher m;
+    const int n = m.SearchBySim3(KF1, *(const Frame*)kf2, m12, idx2InKF2, g.data(), bad, s12, R12, t12, th);
+    memcpy(matches12, m12.data(), sizeof(int) * m12.size());
+    return n;
+}
 int orc_window_search(void* f1, void* f2, int windowSize, int* matches2, int minLevel, int maxLevel, float nnratio, int checkOri) {
     ORBmatcher m(nnratio, checkOri != 0);
     std::vector<int> m2;

@@ -102,6 +102,38 @@ struct Frame {
     std::vector<size_t> GetFeaturesInArea(float x, float y, float r, int minLevel = -1, int maxLevel = -1) const;
 };
 
+// ---- cv::Mat (CV_32F) arithmetic of the matchers, restated from OpenCV's matop.cpp / matmul.cpp (2.4.13, 3.4.1 and 4.13 agree)
+// y = R*x + t (3x3 * 3x1 + 3x1): MatOp_GEMM::add folds the sum into one cv::gemm(R, x, 1, t, 1); with no transpose flag and
+// len = 3, cv::gemm takes its small-matrix path ("case 3" of the 2 <= len <= 4 switch): every row's dot product is accumulated
+// in *float*, left to right, and d = (float)(t0*alpha + c*beta) is evaluated in double.  Pinned against cv2 4.13
+// (tests/golden/cv413_gemm_small.npz).  rstep / tstep: element strides of the rows of R and of the entries of t.
+inline void cvGemmRxPlusT(const float* R, int rstep, const float* x, const float* t, int tstep, float* y) {
+    for (int r = 0; r < 3; r++) {
+        const float* a = R + r * rstep;
+        const float t0 = a[0] * x[0] + a[1] * x[1] + a[2] * x[2];
+        y[r] = (float)((double)t0 * 1.0 + (double)t[r * tstep] * 1.0);
+    }
+}
+// Ow = -R.t()*t: operator-(MatExpr) materialises the transpose (MatOp::subtract(Scalar, expr)) and scales it by -1; MatOp::matmul
+// turns the scaled operand into cv::gemm(Rt, t, -1) with no transpose flag -> the same small-matrix path, c = 0
+inline void cvNegRtTimesT(const float* R, int rstep, const float* t, int tstep, float* Ow) {
+    for (int i = 0; i < 3; i++) {
+        const float t0 = R[0 * rstep + i] * t[0] + R[1 * rstep + i] * t[tstep] + R[2 * rstep + i] * t[2 * tstep];
+        Ow[i] = (float)((double)t0 * -1.0 + 0.0);
+    }
+}
+// dst = src * alpha for a MatExpr scale (Mat / double, double * Mat): Mat::convertTo(CV_32F, alpha) multiplies by (float)alpha
+inline float cvScale32f(float v, double alpha) { return v * (float)alpha + 0.0f; }
+
+struct MapPointGeom {   // the MapPoint fields the mapping / loop-closing matchers read (include/MapPoint.h)
+    float world[3], normal[3];       // GetWorldPos(), GetNormal()
+    float minDist, maxDist;          // GetMinDistanceInvariance(), GetMaxDistanceInvariance()
+    uint8_t desc[32];                // GetDescriptor()
+};
+struct Sim3Rt { float R[9], t[3], Ow[3]; };
+// Scw (4x4 row-major) -> Rcw = sRcw/scw, tcw = Scw.col(3)/scw, Ow = -Rcw.t()*tcw (src/ORBmatcher.cc:866-871, :1718-1723)
+Sim3Rt decomposeSim3(const float* Scw);
+
 struct MapPointView {   // the MapPoint fields SearchByProjection reads (include/MapPoint.h)
     float mTrackProjX, mTrackProjY;
     int mnTrackScaleLevel;
@@ -147,6 +179,25 @@ public:
     int SearchByBoW(const Frame& KF, const int* kfNode, const Frame& F, const int* fNode, std::vector<int>& vpMapPointMatches);
     int SearchByProjection(Frame& CurrentFrame, const Frame& KF, const uint8_t* kfSkip, const float* kfWorld, const float* kfMinDist,
                            const uint8_t* kfMpDesc, float th, int ORBdist);
+    // orb_matcher_kf.cpp: the overloads of the mapping / loop-closing threads.  Map points are ids (>= 0) in
+    // Frame::mvpMapPoints (-1 = NULL); `bad` / geometry arrays are indexed by id.
+    int SearchByBoW_KeyFrames(const Frame& KF1, const int* node1, const Frame& KF2, const int* node2, std::vector<int>& vpMatches12);   // SearchByBoW(pKF1, pKF2, ..) :1289-1424
+    int SearchForTriangulation(const Frame& KF1, const int* node1, const Frame& KF2, const int* node2, const float* F12 /*3x3*/,
+                               std::vector<int>& vMatches12);                                                                    // :1426-1588
+    // Fuse: `points` = vpMapPoints as ids (-1 = NULL); state (in/out): kfSlot = pKF->mvpMapPoints as ids, bad[id], idxInKF[id]
+    // (-1: pKF does not observe the point).  bestIdx / bestDist per list position (-1 / INT_MAX where the point was skipped).
+    int Fuse(const Frame& KF, const std::vector<int>& points, const MapPointGeom* geom, float th, std::vector<int>& kfSlot,
+             std::vector<uint8_t>& bad, std::vector<int>& idxInKF, std::vector<int>& bestIdx, std::vector<int>& bestDist);       // :1590-1708
+    int Fuse(const Frame& KF, const float* Scw, const std::vector<int>& points, const MapPointGeom* geom, float th,
+             std::vector<int>& kfSlot, std::vector<uint8_t>& bad, std::vector<int>& idxInKF, std::vector<int>& bestIdx,
+             std::vector<int>& bestDist);                                                                                        // :1710-1839
+    int SearchByProjection(const Frame& KF, const float* Scw, const std::vector<int>& points, const MapPointGeom* geom,
+                           const uint8_t* bad, std::vector<int>& vpMatched, int th);                                             // :855-977
+    // vpMatches12 (in/out, per KF1 keypoint): in: id or -1; out: newly found pairs hold vpMapPoints2[idx2].  idx2InKF2[i1] =
+    // pMP->GetIndexInKeyFrame(pKF2) of vpMatches12[i1].  geom / bad are indexed by map-point id.
+    int SearchBySim3(const Frame& KF1, const Frame& KF2, std::vector<int>& vpMatches12, const int* idx2InKF2, const MapPointGeom* geom,
+                     const uint8_t* bad, float s12, const float* R12, const float* t12, float th);                               // :1841-2079
+    static bool CheckDistEpipolarLine(const KeyPoint& kp1, const KeyPoint& kp2, const float* F12, float sigma2kp2);              // :705-722
     int WindowSearch(const Frame& F1, const Frame& F2, int windowSize, std::vector<int>& vpMapPointMatches2,
                      int minScaleLevel = -1, int maxScaleLevel = 0x7fffffff);
     static void ComputeThreeMaxima(const std::vector<int>* histo, int L, int& ind1, int& ind2, int& ind3);

@@ -155,13 +155,9 @@ int ORBmatcher::SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, 
         if (LastFrame.mvpMapPoints[i] < 0) continue;
         if (LastFrame.mvbOutlier[i]) continue;
         const float* X = lastWorldPos + 3 * i;
-        // cv::Mat x3Dc = Rcw*x3Dw+tcw: CV_32F gemm accumulates each row dot product in double, then casts to
-        // float (cv::gemm's small-matrix path for 32F uses double accumulators), then adds tcw in float.
+        // cv::Mat x3Dc = Rcw*x3Dw+tcw: one cv::gemm(Rcw, x3Dw, 1, tcw, 1), small-matrix path (cvGemmRxPlusT, oracle.hpp)
         float xc3[3];
-        for (int r = 0; r < 3; r++) {
-            double s = (double)T[r * 4 + 0] * X[0] + (double)T[r * 4 + 1] * X[1] + (double)T[r * 4 + 2] * X[2];
-            xc3[r] = (float)s + T[r * 4 + 3];
-        }
+        cvGemmRxPlusT(T, 4, X, T + 3, 4, xc3);
         const float xc = xc3[0], yc = xc3[1];
         const float invzc = 1.0 / xc3[2];
         float u = CurrentFrame.fx * xc * invzc + CurrentFrame.cx;
@@ -258,10 +254,7 @@ int ORBmatcher::SearchByProjection_GoodFeature(Frame& CurrentFrame, const Frame&
         if (LastFrame.mvbOutlier[i]) continue;
         const float* X = lastWorldPos + 3 * i;
         float xc3[3];
-        for (int r = 0; r < 3; r++) {
-            double s = (double)T[r * 4 + 0] * X[0] + (double)T[r * 4 + 1] * X[1] + (double)T[r * 4 + 2] * X[2];
-            xc3[r] = (float)s + T[r * 4 + 3];
-        }
+        cvGemmRxPlusT(T, 4, X, T + 3, 4, xc3);
         const float xc = xc3[0], yc = xc3[1];
         const float invzc = 1.0 / xc3[2];
         float u = CurrentFrame.fx * xc * invzc + CurrentFrame.cx;
@@ -440,10 +433,7 @@ int ORBmatcher::SearchByProjection(const Frame& F1, Frame& F2, const float* f1Wo
         const int level1 = F1.mvKeysUn[i1].octave;
         const float* X = f1World + 3 * i1;
         float xc3[3];                                    // Rc2w*x3Dw+tc2w: see SearchByProjection(Cur, Last) above
-        for (int r = 0; r < 3; r++) {
-            double s = (double)T[r * 4 + 0] * X[0] + (double)T[r * 4 + 1] * X[1] + (double)T[r * 4 + 2] * X[2];
-            xc3[r] = (float)s + T[r * 4 + 3];
-        }
+        cvGemmRxPlusT(T, 4, X, T + 3, 4, xc3);
         const float xc2 = xc3[0], yc2 = xc3[1];
         const float invzc2 = 1.0 / xc3[2];
         float u2 = F2.fx * xc2 * invzc2 + F2.cx;
@@ -553,14 +543,9 @@ int ORBmatcher::SearchByProjection(Frame& CurrentFrame, const Frame& KF, const u
                                    const float* kfMinDist, const uint8_t* kfMpDesc, float th, int ORBdist) {
     int nmatches = 0;
     const float* T = CurrentFrame.mTcw;
-    // const cv::Mat Ow = -Rcw.t()*tcw: cv::gemm(Rcw, tcw, -1, GEMM_1_T) on CV_32F accumulates every output in double over
-    // k = 0, 1, 2, scales by alpha and casts (GEMMSingleMul<float,double>; pinned against cv2 4.13 in tests/test_oracle_cv.py)
+    // const cv::Mat Ow = -Rcw.t()*tcw (:2210): cvNegRtTimesT (oracle.hpp)
     float Ow[3];
-    for (int i = 0; i < 3; i++) {
-        double s = 0;
-        for (int k = 0; k < 3; k++) s += (double)T[k * 4 + i] * (double)T[k * 4 + 3];
-        Ow[i] = (float)(s * -1.0);
-    }
+    cvNegRtTimesT(T, 4, T + 3, 4, Ow);
     std::vector<int> rotHist[HISTO_LENGTH];
     const float factor = 1.0f / HISTO_LENGTH;
     for (size_t i = 0; i < KF.mvpMapPoints.size(); i++) {
@@ -569,10 +554,7 @@ int ORBmatcher::SearchByProjection(Frame& CurrentFrame, const Frame& KF, const u
         if (kfSkip && kfSkip[i]) continue;
         const float* X = kfWorld + 3 * i;
         float xc3[3];                                    // Rcw*x3Dw+tcw: see SearchByProjection(Cur, Last) above
-        for (int r = 0; r < 3; r++) {
-            double s = (double)T[r * 4 + 0] * X[0] + (double)T[r * 4 + 1] * X[1] + (double)T[r * 4 + 2] * X[2];
-            xc3[r] = (float)s + T[r * 4 + 3];
-        }
+        cvGemmRxPlusT(T, 4, X, T + 3, 4, xc3);
         const float xc = xc3[0], yc = xc3[1];
         const float invzc = 1.0 / xc3[2];
         float u = CurrentFrame.fx * xc * invzc + CurrentFrame.cx;
@@ -623,17 +605,14 @@ int ORBmatcher::SearchByProjection(Frame& CurrentFrame, const Frame& KF, const u
     return nmatches;
 }
 
-// src/Frame.cc:166-227.  cv::Mat arithmetic restated: Rcw*P accumulates each row in double and casts to float before
-// + tcw (cv::gemm, CV_32F); cv::norm and Mat::dot of CV_32F vectors accumulate double products and return double.
+// src/Frame.cc:166-227.  cv::Mat arithmetic restated: Rcw*P+tcw is one small-matrix cv::gemm (cvGemmRxPlusT, oracle.hpp);
+// cv::norm and Mat::dot of CV_32F vectors accumulate double products and return double.
 bool isInFrustum(const float* Rcw, const float* tcw, const float* Ow, float fx, float fy, float cx, float cy, int mnMinX,
                  int mnMaxX, int mnMinY, int mnMaxY, const std::vector<float>& mvScaleFactors, const float* P,
                  const float* Pn, float minDistance, float maxDistance, float viewingCosLimit, float& u, float& v,
                  int& level, float& viewCos) {
     float Pc[3];
-    for (int r = 0; r < 3; r++) {
-        double s = (double)Rcw[r * 3 + 0] * P[0] + (double)Rcw[r * 3 + 1] * P[1] + (double)Rcw[r * 3 + 2] * P[2];
-        Pc[r] = (float)s + tcw[r];
-    }
+    cvGemmRxPlusT(Rcw, 3, P, tcw, 1, Pc);           // const cv::Mat Pc = mRcw*P+mtcw (:174)
     const float PcX = Pc[0], PcY = Pc[1], PcZ = Pc[2];
     if (PcZ < 0.0) return false;
     const float invz = 1.0 / PcZ;

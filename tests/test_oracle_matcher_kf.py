@@ -96,11 +96,23 @@ def test_search_by_bow_matches_python_walk(orc, ratio, ori):
     assert n > 20
 
 
-def test_gemm_transposed_restatement_matches_cv2_golden():
-    """Ow = -Rcw.t()*tcw (src/ORBmatcher.cc:2210): double accumulation over k, times alpha, cast -- the form the oracle and
-    k_candidates<M_KF> use"""
+def test_small_gemm_restatements_match_cv2_golden(orc):
+    """`Rcw*x3Dw+tcw` and `-Rcw.t()*tcw` as cv::MatExpr evaluates them (one cv::gemm each, small-matrix path: float accumulation,
+    alpha / beta applied in double) -- the forms the oracle (oracle.hpp: cvGemmRxPlusT, cvNegRtTimesT) and the kernels use,
+    bit-for-bit against cv2 4.13 (tests/golden/cv413_gemm_small.npz, generator make_gemm_golden.py)"""
+    g = np.load(os.path.join(HERE, "golden", "cv413_gemm_small.npz"))
+    R, x, t, y, Ow = g["R"], g["x"], g["t"], g["y"], g["Ow"]
+    for i in range(R.shape[0]):
+        assert np.array_equal(orc.cv_rx_plus_t(R[i], x[i], t[i]), y[i]), i
+        assert np.array_equal(orc.cv_neg_rt_t(R[i], t[i]), Ow[i]), i
+
+
+def test_general_gemm_path_differs_from_the_small_path(orc):
+    """cv::gemm with a transpose flag takes the general path (double accumulators): its results (cv413_gemm_t.npz) are not
+    what `-Rcw.t()*tcw` evaluates to -- the MatExpr materialises the transpose first.  Guards against mixing the two up."""
     g = np.load(os.path.join(HERE, "golden", "cv413_gemm_t.npz"))
-    R, t, exp = g["R"], g["t"], g["Ow"]
+    R, t, general = g["R"], g["t"], g["Ow"]
+    diff = 0
     for i in range(R.shape[0]):
         got = np.zeros(3, np.float32)
         for c in range(3):
@@ -108,4 +120,6 @@ def test_gemm_transposed_restatement_matches_cv2_golden():
             for k in range(3):
                 s += float(R[i, k, c]) * float(t[i, k])
             got[c] = np.float32(s * -1.0)
-        assert np.array_equal(got, exp[i])
+        assert np.array_equal(got, general[i])
+        diff += not np.array_equal(orc.cv_neg_rt_t(R[i], t[i]), general[i])
+    assert diff > 0
