@@ -142,6 +142,7 @@ private:
 // ------------------------------------------------------------------------------------------------ Frame / MapPoint views
 // The MapPoint fields the tracking matchers read (include/MapPoint.h): projection cache written by Frame::isInFrustum,
 // the representative descriptor and the world position.
+struct KeyFrame;
 struct MapPoint {
     float mTrackProjX = 0, mTrackProjY = 0;
     int mnTrackScaleLevel = 0;
@@ -160,6 +161,15 @@ struct MapPoint {
     long unsigned int goodAtFrameId = 0;             // good-feature stamp read by SearchByProjection_GoodFeature
     bool isBad() const { return mbBad; }
     const uint8_t* GetDescriptor() const { return mDescriptor; }
+    // observations (src/MapPoint.cc:77-81, :270-283, :136-170): what the Fuse overloads and SearchBySim3 read and write
+    std::map<KeyFrame*, size_t> mObservations;
+    void AddObservation(KeyFrame* pKF, size_t idx) { mObservations[pKF] = idx; }
+    bool IsInKeyFrame(KeyFrame* pKF) const { return mObservations.count(pKF) != 0; }
+    int GetIndexInKeyFrame(KeyFrame* pKF) const {
+        auto it = mObservations.find(pKF);
+        return it == mObservations.end() ? -1 : (int)it->second;
+    }
+    inline void Replace(MapPoint* pMP);                // defined after KeyFrame
 };
 
 // The Frame fields this path touches (include/Frame.h): undistorted keypoints, descriptors, per-keypoint map-point
@@ -204,14 +214,47 @@ struct KeyFrame {
     std::vector<MapPoint*> mvpMapPoints;
     std::map<unsigned, std::vector<unsigned>> mFeatVec;
     int mnMinX = 0, mnMaxX = 0, mnMinY = 0, mnMaxY = 0;
+    int mnScaleLevels = 8;
+    float mfScaleFactor = 1.2f;
+    float Tcw[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};   // GetPose(): GetRotation() / GetTranslation() are its blocks
+    float fx = 0, fy = 0, cx = 0, cy = 0;
     KeyFrame() {}
     explicit KeyFrame(const Frame& F)
         : N(F.N), mvKeysUn(F.mvKeysUn), mDescriptors(F.mDescriptors), mvpMapPoints(F.mvpMapPoints), mFeatVec(F.mFeatVec),
-          mnMinX(F.mnMinX), mnMaxX(F.mnMaxX), mnMinY(F.mnMinY), mnMaxY(F.mnMaxY) {}
+          mnMinX(F.mnMinX), mnMaxX(F.mnMaxX), mnMinY(F.mnMinY), mnMaxY(F.mnMaxY), mnScaleLevels(F.mnScaleLevels),
+          mfScaleFactor(F.mfScaleFactor), fx(F.fx), fy(F.fy), cx(F.cx), cy(F.cy) { std::memcpy(Tcw, F.mTcw, sizeof(Tcw)); }
     std::vector<MapPoint*> GetMapPointMatches() const { return mvpMapPoints; }
     const std::map<unsigned, std::vector<unsigned>>& GetFeatureVector() const { return mFeatVec; }
     gforb_cv::KeyPoint GetKeyPointUn(size_t i) const { return mvKeysUn[i]; }
+    // src/KeyFrame.cc:205-251
+    void AddMapPoint(MapPoint* pMP, size_t idx) { mvpMapPoints[idx] = pMP; }
+    void EraseMapPointMatch(size_t idx) { mvpMapPoints[idx] = nullptr; }
+    void ReplaceMapPointMatch(size_t idx, MapPoint* pMP) { mvpMapPoints[idx] = pMP; }
+    MapPoint* GetMapPoint(size_t idx) const { return mvpMapPoints[idx]; }
+    std::set<MapPoint*> GetMapPoints() const {
+        std::set<MapPoint*> s;
+        for (MapPoint* p : mvpMapPoints) if (p && !p->isBad()) s.insert(p);
+        return s;
+    }
 };
+
+// src/MapPoint.cc:136-170 without the map bookkeeping that is not on this path (ComputeDistinctiveDescriptors is
+// ORBmatcher::ComputeDistinctiveDescriptors below; Map::EraseMapPoint is the caller's)
+inline void MapPoint::Replace(MapPoint* pMP) {
+    if (pMP == this) return;
+    std::map<KeyFrame*, size_t> obs = mObservations;
+    mObservations.clear();
+    mbBad = true;
+    for (auto& o : obs) {
+        KeyFrame* pKF = o.first;
+        if (!pMP->IsInKeyFrame(pKF)) {
+            pKF->ReplaceMapPointMatch(o.second, pMP);
+            pMP->AddObservation(pKF, o.second);
+        } else {
+            pKF->EraseMapPointMatch(o.second);
+        }
+    }
+}
 
 // ------------------------------------------------------------------------------------------------ ORBmatcher
 class ORBmatcher {
@@ -527,11 +570,197 @@ public:
         return n;
     }
 
+    // ---- the overloads of the LocalMapping / LoopClosing threads
+    // src/ORBmatcher.cc:1289-1424 (LoopClosing::ComputeSim3)
+    int SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<MapPoint*>& vpMatches12) {
+        vpMatches12 = std::vector<MapPoint*>(pKF1->mvpMapPoints.size(), static_cast<MapPoint*>(nullptr));
+        if (pKF1->N == 0 || pKF2->N == 0) return 0;
+        ensure(std::max(pKF1->N, pKF2->N), pKF1->N, pKF2->mnScaleLevels, pKF2->mfScaleFactor);
+        FlatFrame a(*pKF1), b(*pKF2);
+        std::vector<int32_t> id1, id2, n1, n2, m(pKF1->N, -1);
+        pair_inputs(*pKF1, id1, n1, true); pair_inputs(*pKF2, id2, n2, true);
+        int32_t n = 0;
+        gforb_throw(gforb_search_by_bow_keyframes(h_, &a.set, id1.data(), n1.data(), &b.set, id2.data(), n2.data(), 1, mfNNratio,
+                                                  mbCheckOrientation ? 1 : 0, m.data(), &n, 0, nullptr), "SearchByBoW(KeyFrame, KeyFrame)");
+        for (int i = 0; i < pKF1->N; i++) if (m[i] >= 0) vpMatches12[i] = pKF2->mvpMapPoints[m[i]];
+        return n;
+    }
+
+    // src/ORBmatcher.cc:1426-1588 (LocalMapping::CreateNewMapPoints); F12: 3x3 CV_32F
+    int SearchForTriangulation(KeyFrame* pKF1, KeyFrame* pKF2, const gforb_cv::Mat& F12, std::vector<gforb_cv::KeyPoint>& vMatchedKeys1,
+                               std::vector<gforb_cv::KeyPoint>& vMatchedKeys2, std::vector<std::pair<size_t, size_t>>& vMatchedPairs) {
+        vMatchedKeys1.clear(); vMatchedKeys2.clear(); vMatchedPairs.clear();
+        if (pKF1->N == 0 || pKF2->N == 0) return 0;
+        ensure(std::max(pKF1->N, pKF2->N), pKF1->N, pKF2->mnScaleLevels, pKF2->mfScaleFactor);
+        FlatFrame a(*pKF1), b(*pKF2);
+        std::vector<int32_t> id1, id2, n1, n2, m(pKF1->N, -1);
+        pair_inputs(*pKF1, id1, n1, false); pair_inputs(*pKF2, id2, n2, false);     // "there is already a MapPoint": any non-NULL
+        float F[9];
+        for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) F[r * 3 + c] = F12.at<float>(r, c);
+        int32_t n = 0;
+        gforb_throw(gforb_search_for_triangulation(h_, &a.set, id1.data(), n1.data(), &b.set, id2.data(), n2.data(), 1, F,
+                                                   mbCheckOrientation ? 1 : 0, m.data(), &n, 0, nullptr), "SearchForTriangulation");
+        for (int i = 0; i < pKF1->N; i++) {
+            if (m[i] < 0) continue;
+            vMatchedKeys1.push_back(pKF1->mvKeysUn[i]);
+            vMatchedKeys2.push_back(pKF2->mvKeysUn[m[i]]);
+            vMatchedPairs.push_back(std::make_pair((size_t)i, (size_t)m[i]));
+        }
+        return n;
+    }
+
+    // src/ORBmatcher.cc:1590-1708 (LocalMapping::SearchInNeighbors): the matching loop runs on the GPU for the whole list, the
+    // map mutations are applied here in list order (a point an earlier entry made bad or added to pKF is skipped, :1614)
+    int Fuse(KeyFrame* pKF, std::vector<MapPoint*>& vpMapPoints, float th) {
+        std::vector<int32_t> bi, bd;
+        std::vector<uint8_t> skip(vpMapPoints.size(), 0);
+        for (size_t i = 0; i < vpMapPoints.size(); i++) {
+            MapPoint* p = vpMapPoints[i];
+            skip[i] = (!p || p->isBad() || p->IsInKeyFrame(pKF)) ? 1 : 0;
+        }
+        if (!fuse_match(pKF, pKF->Tcw, 0, vpMapPoints, skip, th, bi, bd)) return 0;
+        int nFused = 0;
+        for (size_t i = 0; i < vpMapPoints.size(); i++) {
+            MapPoint* pMP = vpMapPoints[i];
+            if (!pMP) continue;
+            if (pMP->isBad() || pMP->IsInKeyFrame(pKF)) continue;
+            if (bi[i] < 0 || bd[i] > TH_LOW) continue;
+            MapPoint* pMPinKF = pKF->GetMapPoint(bi[i]);
+            if (pMPinKF) {
+                if (!pMPinKF->isBad()) pMP->Replace(pMPinKF);
+            } else {
+                pMP->AddObservation(pKF, bi[i]);
+                pKF->AddMapPoint(pMP, bi[i]);
+            }
+            nFused++;
+        }
+        return nFused;
+    }
+
+    // src/ORBmatcher.cc:1710-1839 (LoopClosing::SearchAndFuse); Scw: 4x4 CV_32F
+    int Fuse(KeyFrame* pKF, const gforb_cv::Mat& Scw, const std::vector<MapPoint*>& vpPoints, float th) {
+        float S[16];
+        for (int r = 0; r < 4; r++) for (int c = 0; c < 4; c++) S[r * 4 + c] = Scw.at<float>(r, c);
+        const std::set<MapPoint*> spAlreadyFound = pKF->GetMapPoints();
+        std::vector<int32_t> bi, bd;
+        std::vector<uint8_t> skip(vpPoints.size(), 0);
+        for (size_t i = 0; i < vpPoints.size(); i++) skip[i] = (vpPoints[i]->isBad() || spAlreadyFound.count(vpPoints[i])) ? 1 : 0;
+        if (!fuse_match(pKF, S, 1, vpPoints, skip, th, bi, bd)) return 0;
+        int nFused = 0;
+        for (size_t i = 0; i < vpPoints.size(); i++) {
+            MapPoint* pMP = vpPoints[i];
+            if (pMP->isBad() || spAlreadyFound.count(pMP)) continue;
+            if (bi[i] < 0 || bd[i] > TH_LOW) continue;
+            MapPoint* pMPinKF = pKF->GetMapPoint(bi[i]);
+            if (pMPinKF) {
+                if (!pMPinKF->isBad()) pMPinKF->Replace(pMP);
+            } else {
+                pMP->AddObservation(pKF, bi[i]);
+                pKF->AddMapPoint(pMP, bi[i]);
+            }
+            nFused++;
+        }
+        return nFused;
+    }
+
+    // src/ORBmatcher.cc:855-977 (LoopClosing::ComputeSim3 / DetectLoop); Scw: 4x4 CV_32F
+    int SearchByProjection(KeyFrame* pKF, const gforb_cv::Mat& Scw, const std::vector<MapPoint*>& vpPoints,
+                           std::vector<MapPoint*>& vpMatched, int th) {
+        if (pKF->N == 0 || vpPoints.empty()) return 0;
+        ensure(pKF->N, (int)vpPoints.size(), pKF->mnScaleLevels, pKF->mfScaleFactor);
+        float S[16];
+        for (int r = 0; r < 4; r++) for (int c = 0; c < 4; c++) S[r * 4 + c] = Scw.at<float>(r, c);
+        std::set<MapPoint*> spAlreadyFound(vpMatched.begin(), vpMatched.end());
+        spAlreadyFound.erase(static_cast<MapPoint*>(nullptr));
+        const int L = (int)vpPoints.size();
+        FlatFrame kf(*pKF);
+        FlatPoints P(vpPoints);
+        std::vector<int32_t> ids(L), matched(pKF->N, -1);
+        for (int i = 0; i < L; i++) { ids[i] = i; P.skip[i] = (vpPoints[i]->isBad() || spAlreadyFound.count(vpPoints[i])) ? 1 : 0; }
+        for (int j = 0; j < pKF->N; j++) if (vpMatched[j]) matched[j] = L;          // held by an earlier match
+        int32_t n = 0;
+        gforb_throw(gforb_search_by_projection_sim3(h_, &kf.set, 1, S, pKF->fx, pKF->fy, pKF->cx, pKF->cy, &P.set, ids.data(), (float)th,
+                                                    matched.data(), &n, 0, nullptr), "SearchByProjection(KeyFrame, Scw)");
+        for (int j = 0; j < pKF->N; j++) if (matched[j] >= 0 && matched[j] < L) vpMatched[j] = vpPoints[matched[j]];
+        return n;
+    }
+
+    // src/ORBmatcher.cc:1841-2079 (LoopClosing::ComputeSim3); R12: 3x3, t12: 3x1 CV_32F
+    int SearchBySim3(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<MapPoint*>& vpMatches12, const float& s12, const gforb_cv::Mat& R12,
+                     const gforb_cv::Mat& t12, float th) {
+        if (pKF1->N == 0 || pKF2->N == 0) return 0;
+        ensure(std::max(pKF1->N, pKF2->N), std::max(pKF1->N, pKF2->N), pKF2->mnScaleLevels, pKF2->mfScaleFactor);
+        const int N1 = pKF1->N, N2 = pKF2->N;
+        std::vector<bool> vbAlreadyMatched1(N1, false), vbAlreadyMatched2(N2, false);
+        for (int i = 0; i < N1; i++) {
+            MapPoint* pMP = vpMatches12[i];
+            if (pMP) {
+                vbAlreadyMatched1[i] = true;
+                const int idx2 = pMP->GetIndexInKeyFrame(pKF2);
+                if (idx2 >= 0 && idx2 < N2) vbAlreadyMatched2[idx2] = true;
+            }
+        }
+        FlatFrame a(*pKF1), b(*pKF2);
+        FlatPoints P1(pKF1->mvpMapPoints), P2(pKF2->mvpMapPoints);
+        for (int i = 0; i < N1; i++) if (vbAlreadyMatched1[i]) P1.skip[i] = 1;
+        for (int j = 0; j < N2; j++) if (vbAlreadyMatched2[j]) P2.skip[j] = 1;
+        std::vector<int32_t> id2(N2, -1), m12(N1, -1);
+        for (int j = 0; j < N2; j++) if (pKF2->mvpMapPoints[j]) id2[j] = j;
+        float R[9], t[3];
+        for (int r = 0; r < 3; r++) { for (int c = 0; c < 3; c++) R[r * 3 + c] = R12.at<float>(r, c); t[r] = t12.at<float>(r, 0); }
+        int32_t n = 0;
+        gforb_throw(gforb_search_by_sim3(h_, &a.set, &b.set, 1, &P1.set, &P2.set, id2.data(), pKF1->Tcw, pKF2->Tcw, &s12, R, t, pKF1->fx,
+                                         pKF1->fy, pKF1->cx, pKF1->cy, th, m12.data(), &n, 0, nullptr), "SearchBySim3");
+        for (int i = 0; i < N1; i++) if (m12[i] >= 0) vpMatches12[i] = pKF2->mvpMapPoints[m12[i]];
+        return n;
+    }
+
     float mfNNratio;
     bool mbCheckOrientation;
 
 private:
-    friend class Observability;                       // runActiveMapMatching drives the one-point matcher of this handle
+    friend class Observability;
+    // a list of MapPoint* -> GforbWorldPointSet (one problem); NULL and bad points are flagged in `skip`
+    struct FlatPoints {
+        std::vector<float> world, normal, mind, maxd;
+        std::vector<uint8_t> desc, skip;
+        int32_t count;
+        GforbWorldPointSet set;
+        explicit FlatPoints(const std::vector<MapPoint*>& v)
+            : world(v.size() * 3, 0.f), normal(v.size() * 3, 0.f), mind(v.size(), 1.f), maxd(v.size(), 1.f), desc(v.size() * 32, 0),
+              skip(v.size(), 0), count((int32_t)v.size()) {
+            for (size_t i = 0; i < v.size(); i++) {
+                const MapPoint* p = v[i];
+                if (!p || p->isBad()) { skip[i] = 1; if (!p) continue; }
+                std::memcpy(&world[i * 3], p->mWorldPos, 12); std::memcpy(&normal[i * 3], p->mNormalVector, 12);
+                mind[i] = p->mfMinDistance; maxd[i] = p->mfMaxDistance;
+                std::memcpy(&desc[i * 32], p->mDescriptor, 32);
+            }
+            set.world = world.data(); set.normal = normal.data(); set.min_distance = mind.data(); set.max_distance = maxd.data();
+            set.descriptors = desc.data(); set.skip = skip.data(); set.counts = &count; set.mp_stride = (int32_t)std::max<size_t>(v.size(), 1);
+        }
+    };
+    // ids (index of the keypoint when it holds a usable map point) and FeatureVector nodes of a keyframe pair member
+    static void pair_inputs(const KeyFrame& KF, std::vector<int32_t>& ids, std::vector<int32_t>& nodes, bool dropBad) {
+        ids.assign(KF.N, -1); nodes.assign(KF.N, -1);
+        for (int i = 0; i < KF.N; i++) if (KF.mvpMapPoints[i] && !(dropBad && KF.mvpMapPoints[i]->isBad())) ids[i] = i;
+        for (const auto& nd : KF.mFeatVec) for (unsigned i : nd.second) if ((int)i < KF.N) nodes[i] = (int32_t)nd.first;
+    }
+    template <class Vec>
+    bool fuse_match(KeyFrame* pKF, const float* pose, int sim3, const Vec& pts, const std::vector<uint8_t>& skip, float th,
+                    std::vector<int32_t>& bi, std::vector<int32_t>& bd) {
+        const int L = (int)pts.size();
+        bi.assign(L, -1); bd.assign(L, 0x7fffffff);
+        if (pKF->N == 0 || L == 0) return false;
+        ensure(pKF->N, L, pKF->mnScaleLevels, pKF->mfScaleFactor);
+        FlatFrame kf(*pKF);
+        FlatPoints P(std::vector<MapPoint*>(pts.begin(), pts.end()));
+        for (int i = 0; i < L; i++) if (skip[i]) P.skip[i] = 1;
+        int32_t n = 0;
+        gforb_throw(gforb_fuse(h_, &kf.set, 1, pose, sim3, pKF->fx, pKF->fy, pKF->cx, pKF->cy, &P.set, th, bi.data(), bd.data(), &n, 0,
+                               nullptr), "Fuse");
+        return true;
+    }                       // runActiveMapMatching drives the one-point matcher of this handle
     struct FlatFrame {          // Frame -> GforbFrameSet (one frame); keeps the staging alive for the call
         std::vector<uint8_t> desc;
         int32_t count;

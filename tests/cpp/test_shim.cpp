@@ -452,6 +452,165 @@ int main() {
     }
     printf("keyframe leg: %d BoW matches, %d keyframe-projection matches\n", nBow, nKf);
 
+    // ---- the overloads of the LocalMapping / LoopClosing threads through the shim vs the oracle (oracle/orb_matcher_kf.cpp):
+    //      SearchByBoW(KF, KF), SearchForTriangulation, SearchByProjection(KF, Scw, ..), SearchBySim3, Fuse(KF, Scw, ..), Fuse(KF, ..)
+    int nBow2 = 0, nTri = 0, nSbp = 0, nSim3 = 0, nFuseS = 0, nFuse = 0;
+    {
+        const float fx = 458.0f, fy = 457.0f, cx = 320.0f, cy = 240.0f;
+        const int N1 = F1.N, N2 = F2.N;
+        sm_state = 9191;
+        float sc[8]; sc[0] = 1.0f; for (int l = 1; l < 8; l++) sc[l] = sc[l - 1] * 1.2f;
+        Frame Fa = F1, Fb = F2;
+        for (Frame* f : {&Fa, &Fb}) { f->fx = fx; f->fy = fy; f->cx = cx; f->cy = cy; f->mFeatVec.clear(); }
+        std::vector<int> nd1(N1), nd2(N2);
+        for (int i = 0; i < N1; i++) { nd1[i] = 40 + (F1.mDescriptors.ptr(i)[0] & 0x1f); Fa.mFeatVec[(unsigned)nd1[i]].push_back((unsigned)i); }
+        for (int j = 0; j < N2; j++) { nd2[j] = 40 + (F2.mDescriptors.ptr(j)[0] & 0x1f); Fb.mFeatVec[(unsigned)nd2[j]].push_back((unsigned)j); }
+        KeyFrame KF1(Fa), KF2(Fb);
+        const float eye[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
+        std::memcpy(KF1.Tcw, eye, sizeof(eye)); std::memcpy(KF2.Tcw, eye, sizeof(eye));
+        // map points: ids 0 .. N1-1 sit on KF1's keypoints and project (identity poses) onto the matching KF2 keypoints,
+        // ids N1 .. N1+N2-1 sit on KF2's keypoints and project onto KF1's
+        std::vector<MapPoint> pts((size_t)N1 + N2);
+        std::vector<oracle::MapPointGeom> geom(pts.size());
+        auto make = [&](int id, const gforb_cv::KeyPoint& kp, float du, float dv, const uint8_t* d) {
+            MapPoint& p = pts[id];
+            const float z = 2.0f + (float)(splitmix() % 600) * 0.01f;
+            const float u = kp.pt.x + du, v = kp.pt.y + dv;
+            p.mWorldPos[0] = (u - cx) / fx * z; p.mWorldPos[1] = (v - cy) / fy * z; p.mWorldPos[2] = z;
+            const float d3 = std::sqrt(p.mWorldPos[0] * p.mWorldPos[0] + p.mWorldPos[1] * p.mWorldPos[1] + z * z);
+            p.mfMinDistance = d3 / (sc[kp.octave] * (0.95f + 0.01f * (float)(splitmix() % 10)));
+            p.mfMaxDistance = p.mfMinDistance * 3.58f * ((splitmix() % 25) == 0 ? 0.2f : 1.3f);
+            p.mNormalVector[0] = 0; p.mNormalVector[1] = 0; p.mNormalVector[2] = ((splitmix() % 20) == 0) ? -1.0f : 1.0f;
+            std::memcpy(p.mDescriptor, d, 32);
+            if ((splitmix() % 5) == 0) p.mDescriptor[splitmix() % 32] ^= 0x22;
+            p.mbBad = (splitmix() % 30) == 0;
+        };
+        for (int i = 0; i < N1; i++) make(i, k1[i], -3.0f, -1.0f, F1.mDescriptors.ptr(i));
+        for (int j = 0; j < N2; j++) make(N1 + j, k2[j], 3.0f, 1.0f, F2.mDescriptors.ptr(j));
+        for (size_t id = 0; id < pts.size(); id++) {
+            std::memcpy(geom[id].world, pts[id].mWorldPos, 12); std::memcpy(geom[id].normal, pts[id].mNormalVector, 12);
+            geom[id].minDist = pts[id].mfMinDistance; geom[id].maxDist = pts[id].mfMaxDistance;
+            std::memcpy(geom[id].desc, pts[id].mDescriptor, 32);
+        }
+        for (int i = 0; i < N1; i++) { const bool has = (splitmix() % 2) != 0; KF1.mvpMapPoints[i] = has ? &pts[i] : nullptr; if (has) pts[i].AddObservation(&KF1, i); }
+        for (int j = 0; j < N2; j++) { const bool has = (splitmix() % 2) != 0; KF2.mvpMapPoints[j] = has ? &pts[N1 + j] : nullptr; if (has) pts[N1 + j].AddObservation(&KF2, j); }
+        auto idOf = [&](const MapPoint* p) { return p ? (int)(p - &pts[0]) : -1; };
+        auto oracleKF = [&](const oracle::Frame& base, const KeyFrame& KF, bool dropBad) {
+            oracle::Frame o = base;
+            o.fx = fx; o.fy = fy; o.cx = cx; o.cy = cy;
+            std::memcpy(o.mTcw, eye, sizeof(eye));
+            for (int i = 0; i < KF.N; i++) {
+                const MapPoint* p = KF.mvpMapPoints[i];
+                o.mvpMapPoints[i] = (p && !(dropBad && p->isBad())) ? idOf(p) : -1;
+            }
+            return o;
+        };
+        auto badVec = [&]() { std::vector<uint8_t> b(pts.size()); for (size_t i = 0; i < pts.size(); i++) b[i] = pts[i].isBad() ? 1 : 0; return b; };
+
+        {   // SearchByBoW(pKF1, pKF2, vpMatches12)
+            ORBmatcher mb(0.8f, true);
+            oracle::ORBmatcher omb(0.8f, true);
+            std::vector<MapPoint*> vm;
+            std::vector<int> ovm;
+            nBow2 = mb.SearchByBoW(&KF1, &KF2, vm);
+            const int on = omb.SearchByBoW_KeyFrames(oracleKF(oF1, KF1, true), nd1.data(), oracleKF(oF2, KF2, true), nd2.data(), ovm);
+            bool ok = vm.size() == ovm.size();
+            for (size_t i = 0; ok && i < vm.size(); i++) ok = idOf(vm[i]) == ovm[i];
+            CHECK(nBow2 == on && nBow2 > 20 && ok, "SearchByBoW(KF, KF): %d vs %d", nBow2, on);
+        }
+        {   // SearchForTriangulation: frame 2 is frame 1 shifted by (3, 1): epipolar lines y2 = y1 (one row off passes the gate)
+            gforb_cv::Mat F12; F12.create(3, 3, 4);
+            const float Fv[9] = {0, 1e-5f, 0, -1e-5f, 0, -1, 2e-5f, 1, 0.25f};
+            for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) F12.at<float>(r, c) = Fv[r * 3 + c];
+            ORBmatcher mt(0.6f, true);
+            oracle::ORBmatcher omt(0.6f, true);
+            std::vector<gforb_cv::KeyPoint> mk1, mk2;
+            std::vector<std::pair<size_t, size_t>> pairs;
+            std::vector<int> ovm;
+            nTri = mt.SearchForTriangulation(&KF1, &KF2, F12, mk1, mk2, pairs);
+            const int on = omt.SearchForTriangulation(oracleKF(oF1, KF1, false), nd1.data(), oracleKF(oF2, KF2, false), nd2.data(), Fv, ovm);
+            size_t k = 0; bool ok = true;
+            for (int i = 0; i < N1; i++) if (ovm[i] >= 0) { ok = ok && k < pairs.size() && pairs[k].first == (size_t)i && pairs[k].second == (size_t)ovm[i]; k++; }
+            ok = ok && k == pairs.size() && mk1.size() == k && mk2.size() == k;
+            CHECK(nTri == on && nTri > 20 && ok, "SearchForTriangulation: %d vs %d", nTri, on);
+        }
+        gforb_cv::Mat Scw; Scw.create(4, 4, 4);
+        float Sv[16] = {0};
+        {
+            const float s = 1.3f, a = 0.001f;
+            const float Rz[9] = {std::cos(a), -std::sin(a), 0, std::sin(a), std::cos(a), 0, 0, 0, 1};
+            for (int r = 0; r < 3; r++) { for (int c = 0; c < 3; c++) Sv[r * 4 + c] = s * Rz[r * 3 + c]; }
+            Sv[3] = s * 0.002f; Sv[7] = s * -0.001f; Sv[11] = s * 0.003f; Sv[15] = 1.0f;
+            for (int r = 0; r < 4; r++) for (int c = 0; c < 4; c++) Scw.at<float>(r, c) = Sv[r * 4 + c];
+        }
+        {   // SearchByProjection(pKF2, Scw, vpPoints, vpMatched, th): KF1's points (with repeats) into KF2
+            std::vector<MapPoint*> list, vpMatched(N2, nullptr);
+            std::vector<int> olist, omatched(N2, -1);
+            for (int i = 0; i < N1; i++) { list.push_back(&pts[i]); if ((splitmix() % 9) == 0) list.push_back(&pts[splitmix() % N1]); }
+            for (int j = 0; j < N2; j++) if ((splitmix() % 8) == 0) vpMatched[j] = &pts[splitmix() % N1];
+            for (MapPoint* p : list) olist.push_back(idOf(p));
+            for (int j = 0; j < N2; j++) omatched[j] = idOf(vpMatched[j]);
+            ORBmatcher ms(0.6f, true);
+            oracle::ORBmatcher oms(0.6f, true);
+            nSbp = ms.SearchByProjection(&KF2, Scw, list, vpMatched, 10);
+            const std::vector<uint8_t> bad = badVec();
+            const int on = oms.SearchByProjection(oracleKF(oF2, KF2, false), Sv, olist, geom.data(), bad.data(), omatched, 10);
+            bool ok = true;
+            for (int j = 0; j < N2; j++) ok = ok && idOf(vpMatched[j]) == omatched[j];
+            CHECK(nSbp == on && nSbp > 50 && ok, "SearchByProjection(KF, Scw): %d vs %d", nSbp, on);
+        }
+        {   // SearchBySim3: a similarity close to the identity between the two (identity-pose) keyframes
+            gforb_cv::Mat R12, t12; R12.create(3, 3, 4); t12.create(3, 1, 4);
+            const float a = 0.0015f, s12 = 1.004f;
+            const float Rv[9] = {std::cos(a), -std::sin(a), 0, std::sin(a), std::cos(a), 0, 0, 0, 1}, tv[3] = {0.003f, -0.002f, 0.004f};
+            for (int r = 0; r < 3; r++) { for (int c = 0; c < 3; c++) R12.at<float>(r, c) = Rv[r * 3 + c]; t12.at<float>(r, 0) = tv[r]; }
+            std::vector<MapPoint*> vm(N1, nullptr);
+            std::vector<int> ovm(N1, -1), idx2(N1, -1);
+            for (int i = 0; i < N1; i++)
+                if (KF1.mvpMapPoints[i] && (splitmix() % 12) == 0) {
+                    const int j = (int)(splitmix() % N2);
+                    if (KF2.mvpMapPoints[j]) { vm[i] = KF2.mvpMapPoints[j]; ovm[i] = idOf(vm[i]); idx2[i] = vm[i]->GetIndexInKeyFrame(&KF2); }
+                }
+            ORBmatcher m3(0.6f, true);
+            oracle::ORBmatcher om3(0.6f, true);
+            nSim3 = m3.SearchBySim3(&KF1, &KF2, vm, s12, R12, t12, 7.5f);
+            const std::vector<uint8_t> bad = badVec();
+            const int on = om3.SearchBySim3(oracleKF(oF1, KF1, false), oracleKF(oF2, KF2, false), ovm, idx2.data(), geom.data(), bad.data(), s12, Rv, tv, 7.5f);
+            bool ok = true;
+            for (int i = 0; i < N1; i++) ok = ok && idOf(vm[i]) == ovm[i];
+            CHECK(nSim3 == on && nSim3 > 30 && ok, "SearchBySim3: %d vs %d", nSim3, on);
+        }
+        // the Fuse overloads change the map: the oracle's model of the keyframe (slots, bad flags, observation index) is taken
+        // from the shim's state before each call and compared after it
+        auto fuseCase = [&](KeyFrame& KF, const oracle::Frame& obase, int firstId, int nIds, bool sim3, int& nOut) {
+            std::vector<MapPoint*> list;
+            for (int i = 0; i < nIds; i++) {
+                list.push_back(&pts[firstId + i]);
+                if ((splitmix() % 10) == 0) list.push_back(&pts[firstId + (int)(splitmix() % nIds)]);     // repeated entries
+                if (!sim3 && (splitmix() % 25) == 0) list.push_back(nullptr);
+            }
+            std::vector<int> olist, slot(KF.N), inKF(pts.size(), -1), obi, obd;
+            for (MapPoint* p : list) olist.push_back(idOf(p));
+            for (int j = 0; j < KF.N; j++) slot[j] = idOf(KF.mvpMapPoints[j]);
+            for (size_t id = 0; id < pts.size(); id++) inKF[id] = pts[id].GetIndexInKeyFrame(&KF);
+            std::vector<uint8_t> bad = badVec();
+            ORBmatcher mf(0.6f, true);
+            oracle::ORBmatcher omf(0.6f, true);
+            const oracle::Frame okf = oracleKF(obase, KF, false);
+            int on;
+            if (sim3) { nOut = mf.Fuse(&KF, Scw, list, 4.0f); on = omf.Fuse(okf, Sv, olist, geom.data(), 4.0f, slot, bad, inKF, obi, obd); }
+            else { nOut = mf.Fuse(&KF, list, 3.0f); on = omf.Fuse(okf, olist, geom.data(), 3.0f, slot, bad, inKF, obi, obd); }
+            bool ok = true;
+            for (int j = 0; j < KF.N; j++) ok = ok && idOf(KF.mvpMapPoints[j]) == slot[j];
+            for (size_t id = 0; id < pts.size(); id++) ok = ok && (pts[id].isBad() ? 1 : 0) == bad[id] && pts[id].GetIndexInKeyFrame(&KF) == inKF[id];
+            CHECK(nOut == on && nOut > 30 && ok, "Fuse(%s): %d vs %d fused, map state %s", sim3 ? "KF, Scw" : "KF", nOut, on, ok ? "equal" : "differs");
+        };
+        fuseCase(KF1, oF1, N1, N2, true, nFuseS);          // KF2's points fused into KF1 through Scw
+        fuseCase(KF2, oF2, 0, N1, false, nFuse);           // KF1's points fused into KF2 with its own pose
+    }
+    printf("mapping / loop-closing leg: %d BoW(KF, KF), %d triangulation, %d projection(Scw), %d Sim3, %d + %d fused\n", nBow2, nTri, nSbp,
+           nSim3, nFuseS, nFuse);
+
     printf("TrackPreviousFrame leg: %d window-projection matches, %d pose inliers\n", nPrev, nInl);
     printf("shim test: %zu/%zu keypoints, %d init matches, %d projection matches, %zu good features, %d active matches: %s\n", k1.size(),
            k2.size(), nm, np, good.size(), nActive, g_fail ? "FAILED" : "OK");

@@ -123,3 +123,125 @@ def test_general_gemm_path_differs_from_the_small_path(orc):
         assert np.array_equal(got, general[i])
         diff += not np.array_equal(orc.cv_neg_rt_t(R[i], t[i]), general[i])
     assert diff > 0
+
+
+# ---------------------------------------------------------------- mapping / loop-closing overloads (oracle/orb_matcher_kf.cpp)
+POP = np.array([bin(i).count("1") for i in range(256)], np.int32)
+
+
+def _py_triangulation(k1, d1, mp1, n1, k2, d2, mp2, n2, F, sigma2):
+    """independent walk of src/ORBmatcher.cc:1426-1547 without the rotation histogram: (node, index) order, unmatched
+    candidates without a map point at distance <= 50, sorted by (distance, index), first within twice the best that passes the
+    epipolar test"""
+    out = np.full(len(k1), -1, np.int32)
+    taken = np.zeros(len(k2), bool)
+    F = F.astype(np.float32).reshape(3, 3)
+    order = sorted([i for i in range(len(k1)) if n1[i] >= 0], key=lambda i: (n1[i], i))
+    for i in order:
+        if mp1[i] >= 0:
+            continue
+        cand = []
+        for j in range(len(k2)):
+            if n2[j] != n1[i] or taken[j] or mp2[j] >= 0:
+                continue
+            d = int(POP[d1[i] ^ d2[j]].sum())
+            if d <= 50:
+                cand.append((d, j))
+        if not cand:
+            continue
+        cand.sort()
+        x1, y1 = np.float32(k1["x"][i]), np.float32(k1["y"][i])
+        a = np.float32(np.float32(x1 * F[0, 0]) + np.float32(y1 * F[1, 0])) + F[2, 0]
+        b = np.float32(np.float32(x1 * F[0, 1]) + np.float32(y1 * F[1, 1])) + F[2, 1]
+        c = np.float32(np.float32(x1 * F[0, 2]) + np.float32(y1 * F[1, 2])) + F[2, 2]
+        for d, j in cand:
+            if d > 2 * cand[0][0]:
+                break
+            x2, y2 = np.float32(k2["x"][j]), np.float32(k2["y"][j])
+            num = np.float32(np.float32(a * x2) + np.float32(b * y2)) + c
+            den = np.float32(a * a) + np.float32(b * b)
+            if den == 0:
+                continue
+            dsqr = np.float32(np.float32(num * num) / den)
+            if float(dsqr) < 3.84 * float(sigma2[k2["octave"][j]]):
+                taken[j] = True; out[i] = j
+                break
+    return int((out >= 0).sum()), out
+
+
+def test_search_for_triangulation_matches_python_walk(orc):
+    n1, n2 = 170, 160
+    k1, d1, F1 = _frame(orc, n1, 111)
+    k2, d2, F2 = _frame(orc, n2, 121, base=(k1, d1))
+    k2["x"][:n2] = k1["x"][:n2] + 2.0; k2["y"][:n2] = k1["y"][:n2] + np.where(synth.uniform01(5, n2) < 0.3, 4.0, 0.5)
+    F2 = orc.Frame(k2, d2, 752, 480)
+    mp1 = np.where(synth.uniform01(131, n1) < 0.3, 10 + np.arange(n1), -1).astype(np.int32)
+    mp2 = np.where(synth.uniform01(141, n2) < 0.3, 900 + np.arange(n2), -1).astype(np.int32)
+    nd1 = (50 + 3 * (d1[:, 0] & 3)).astype(np.int32); nd1[::17] = -1
+    nd2 = (50 + 3 * (d2[:, 0] & 3)).astype(np.int32); nd2[5::19] = -1
+    F1.set_mappoints(mp1); F2.set_mappoints(mp2)
+    F = np.array([0, 2e-5, 0, -1e-5, 0, -1, 1e-5, 1, 0.1], np.float32)
+    n, m = orc.search_for_triangulation(F1, nd1, F2, nd2, F, checkOri=False)
+    sigma2 = (np.float32(1.2) ** np.arange(8)).astype(np.float32) ** 2
+    s = np.ones(8, np.float32)
+    for i in range(1, 8):
+        s[i] = np.float32(s[i - 1] * np.float32(1.2))
+    en, em = _py_triangulation(k1, d1, mp1, nd1, k2, d2, mp2, nd2, F, (s * s).astype(np.float32))
+    assert n == en and np.array_equal(m, em)
+    assert 20 < n < (mp1 < 0).sum()
+    # with the rotation histogram the result is a subset of it
+    n_o, m_o = orc.search_for_triangulation(F1, nd1, F2, nd2, F, checkOri=True)
+    assert n_o <= n and np.all((m_o == m) | (m_o == -1))
+
+
+def test_search_by_bow_keyframes_properties(orc):
+    """SearchByBoW(KF1, KF2): every match joins features of one node, both with a map point, distance < 50, no KF2 point twice"""
+    n1, n2 = 200, 190
+    k1, d1, F1 = _frame(orc, n1, 211)
+    k2, d2, F2 = _frame(orc, n2, 221, base=(k1, d1))
+    mp1 = np.where(synth.uniform01(231, n1) < 0.8, 10 + np.arange(n1), -1).astype(np.int32)
+    mp2 = np.where(synth.uniform01(241, n2) < 0.8, 900 + np.arange(n2), -1).astype(np.int32)
+    nd1 = (50 + 3 * (d1[:, 0] & 7)).astype(np.int32); nd2 = (50 + 3 * (d2[:, 0] & 7)).astype(np.int32)
+    F1.set_mappoints(mp1); F2.set_mappoints(mp2)
+    n, m = orc.search_by_bow_keyframes(F1, nd1, F2, nd2, 0.9, False)
+    assert n == (m >= 0).sum() and n > 40
+    used = m[m >= 0]
+    assert len(set(used.tolist())) == len(used)
+    for i in np.nonzero(m >= 0)[0]:
+        j = int(m[i]) - 900
+        assert mp1[i] >= 0 and mp2[j] >= 0 and nd1[i] == nd2[j] and int(POP[d1[i] ^ d2[j]].sum()) < 50
+
+
+def test_sim3_decomposition_and_projection_properties(orc):
+    """decomposeSim3 recovers (R, t, Ow) of Scw = s [R | t] to float accuracy; Fuse through Scw = s Tcw finds what Fuse with Tcw finds
+    when the scale is a power of two (every product then scales exactly)"""
+    a = 0.3
+    R = np.array([[np.cos(a), -np.sin(a), 0], [np.sin(a), np.cos(a), 0], [0, 0, 1]], np.float32)
+    t = np.array([0.3, -0.2, 0.5], np.float32)
+    S = np.eye(4, dtype=np.float32); S[:3, :3] = 1.75 * R; S[:3, 3] = 1.75 * t
+    Rd, td, Ow = orc.sim3_decompose(S)
+    assert np.allclose(Rd, R, atol=2e-7) and np.allclose(td, t, atol=2e-7)
+    assert np.allclose(Ow, -(R.T.astype(np.float64) @ t), atol=1e-6)
+    n = 300
+    k, d, F = _frame(orc, n, 311)
+    fx = fy = 458.0; cx, cy = 376.0, 240.0
+    z = (2 + 4 * synth.uniform01(312, n)).astype(np.float32)
+    Xc = np.stack([(k["x"] + 1.0 - cx) / fx * z, (k["y"] - 1.0 - cy) / fy * z, z], 1).astype(np.float32)
+    Xw = ((Xc - t) @ R).astype(np.float32)
+    T = np.eye(4, dtype=np.float32); T[:3, :3] = R; T[:3, 3] = t
+    Owd = -(R.T.astype(np.float64) @ t)
+    d3 = np.linalg.norm(Xw - Owd, axis=1)
+    scale = (np.float32(1.2) ** np.arange(8))
+    mind = (d3 / (scale[k["octave"]] * 0.99)).astype(np.float32); maxd = (mind * 5).astype(np.float32)
+    nrm = ((Xw - Owd) / d3[:, None]).astype(np.float32)
+    F.set_camera(fx, fy, cx, cy, T)
+    pts = np.arange(n, dtype=np.int32)
+    slot = np.full(n, -1, np.int32); bad = np.zeros(n, np.uint8); ik = np.full(n, -1, np.int32)
+    n1, bi1, bd1, s1, b1, i1 = orc.fuse(F, None, pts, Xw, nrm, mind, maxd, d, 3.0, slot, bad, ik)
+    S2 = T.copy(); S2[:3, :] *= 2.0
+    n2, bi2, bd2, s2, b2, i2 = orc.fuse(F, S2, pts, Xw, nrm, mind, maxd, d, 3.0, slot, bad, ik)
+    assert n1 == n2 and n1 > 200
+    assert np.array_equal(bi1, bi2) and np.array_equal(bd1, bd2) and np.array_equal(s1, s2)
+    # every fused point took the keypoint it was generated from (descriptor distance 0) and now sits in that slot
+    fused = bd1 <= 50
+    assert np.array_equal(bi1[fused], pts[fused]) and (bd1[fused] == 0).all() and np.array_equal(s1[fused], pts[fused])
