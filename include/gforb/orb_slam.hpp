@@ -804,6 +804,9 @@ private:
 // ------------------------------------------------------------------------------------------------ Observability
 // Good-feature selection (DIMENSION_OF_STATE_MODEL = 7).  GoodPoint mirrors include/Util.hpp:64-92 (idx, obs_score,
 // selected, upper_bound); the 7x7 block itself stays in HBM.
+// include/Observability.h:94-102: namespace-scope constants, as the call sites name them (ORB_SLAM::FRAME_INFO_MATRIX)
+enum { MAP_INFO_MATRIX = 0, FRAME_INFO_MATRIX = 1, MAP_HYBRID_MATRIX = 2, FRAME_HYBRID_MATRIX = 3, FRAME_STRIP_OBS_MATRIX = 4 };
+
 struct GoodPoint {
     size_t idx = 0;
     double obs_score = -1, upper_bound = 0;
@@ -812,7 +815,6 @@ struct GoodPoint {
 
 class Observability {
 public:
-    enum { MAP_INFO_MATRIX = 0, FRAME_INFO_MATRIX = 1, MAP_HYBRID_MATRIX = 2, FRAME_HYBRID_MATRIX = 3 };   // include/Observability.h:94-102
     // used by Tracking (src/Tracking.cc:146; k1 = k2 = 0)
     Observability(double fu, double fv, int nRows, int nCols, double Cx, double Cy, double k1, double k2, int device = 0) {
         init(fu, fv, nRows, nCols, Cx, Cy, k1, k2, 1.0, 1.0, device);

@@ -225,7 +225,7 @@ int main() {
             tv[i] = p.mbTrackInView;
         }
         ob.pFrame = &F3; ob.mMapPoints = &vp; ob.mnFrameId = F3.mnId;
-        CHECK(ob.runMatrixBuilding(Observability::MAP_INFO_MATRIX, 1.0, true, false), "runMatrixBuilding(MAP) failed");
+        CHECK(ob.runMatrixBuilding(ORB_SLAM::MAP_INFO_MATRIX, 1.0, true, false), "runMatrixBuilding(MAP) failed");
         std::vector<double> mb((size_t)M * 49), ms(M), mh((size_t)M * 14);
         oob.batchInfoMat_Map(mw.data(), tv.data(), M, false, 0, W, 0, H, mb.data(), ms.data(), nullptr, mh.data());
         std::vector<uint8_t> inPool(M);
@@ -242,7 +242,7 @@ int main() {
         std::memcpy(ocur, base, sizeof(base));
         ORBmatcher m3(0.8f, true);
         oracle::ORBmatcher om3(0.8f, true);
-        nActive = ob.runActiveMapMatching(&F3, Observability::MAP_INFO_MATRIX, base, 3.0f, m3, 60, 1e30, 1, cur);
+        nActive = ob.runActiveMapMatching(&F3, ORB_SLAM::MAP_INFO_MATRIX, base, 3.0f, m3, 60, 1e30, 1, cur);
         std::vector<int> oleft;
         srand(1);
         const int onActive = oracle::runActiveMapMatching(oF3, omp, inPool.data(), mb.data(), mh.data(), ocur, 3.0f, om3, 60, oleft);

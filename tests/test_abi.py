@@ -49,6 +49,20 @@ def test_header_is_plain_c_and_shim_is_cxx17(tmp_path):
     subprocess.check_call(["g++", "-std=c++17", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"), "-c", str(cc), "-o", str(tmp_path / "s.o")])
 
 
+def test_shim_opencv_branch_compiles_against_the_opencv_interface(tmp_path):
+    """include/gforb/orb_slam.hpp with -DGFORB_WITH_OPENCV (the branch a maintainer of the reference builds): every class
+    instantiated and every member the reference's call sites use named with cv::Mat / cv::KeyPoint / cv::Point2f arguments,
+    compiled against a stand-in for the OpenCV headers (tests/cpp/opencv_stub; OpenCV's C++ headers are not in this image) and
+    linked against libgforb.so, so that every C-ABI symbol the branch references resolves."""
+    src = os.path.join(ROOT, "tests", "cpp", "shim_opencv_branch.cpp")
+    out = tmp_path / "shim_cv"
+    subprocess.check_call(["g++", "-std=c++17", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"),
+                           "-I", os.path.join(ROOT, "tests", "cpp", "opencv_stub"), src, "-o", str(out),
+                           "-L", os.path.join(ROOT, "gf_orb_slam_b200"), "-lgforb", "-L/usr/local/cuda/lib64",
+                           "-Wl,-rpath," + os.path.join(ROOT, "gf_orb_slam_b200"), "-Wl,-rpath,/usr/local/cuda/lib64"])
+    subprocess.check_call([str(out)])          # main() touches nothing that needs a device
+
+
 def test_no_device_means_error_not_fallback():
     """Without a CUDA device every create() must fail loudly (GFORB_ERR_CUDA); bad arguments are rejected first."""
     from gf_orb_slam_b200 import _lib
