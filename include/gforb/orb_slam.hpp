@@ -270,10 +270,13 @@ public:
 
     // Hamming distance of two 32-byte descriptors (src/ORBmatcher.cc:2384-2400).  The reference calls this scalar helper
     // from host loops; here it goes through gforb_descriptor_distance like every batched caller (n = 1).
-    int DescriptorDistance(const gforb_cv::Mat& a, const gforb_cv::Mat& b) {
-        ensure(1, 1, 8, 1.2f);
+    // `static` like the reference (call sites write ORBmatcher::DescriptorDistance(a, b)): the call borrows a process-wide
+    // matcher handle on device 0, created on first use.
+    static int DescriptorDistance(const gforb_cv::Mat& a, const gforb_cv::Mat& b) {
+        static ORBmatcher shared(0.6f, true, 0);
+        shared.ensure(1, 1, 8, 1.2f);
         int32_t d = 0;
-        gforb_throw(gforb_descriptor_distance(h_, a.ptr(0), b.ptr(0), 1, &d, 0, nullptr), "DescriptorDistance");
+        gforb_throw(gforb_descriptor_distance(shared.h_, a.ptr(0), b.ptr(0), 1, &d, 0, nullptr), "DescriptorDistance");
         return d;
     }
 
@@ -611,7 +614,7 @@ public:
 
     // src/ORBmatcher.cc:1590-1708 (LocalMapping::SearchInNeighbors): the matching loop runs on the GPU for the whole list, the
     // map mutations are applied here in list order (a point an earlier entry made bad or added to pKF is skipped, :1614)
-    int Fuse(KeyFrame* pKF, std::vector<MapPoint*>& vpMapPoints, float th) {
+    int Fuse(KeyFrame* pKF, std::vector<MapPoint*>& vpMapPoints, float th = 2.5) {
         std::vector<int32_t> bi, bd;
         std::vector<uint8_t> skip(vpMapPoints.size(), 0);
         for (size_t i = 0; i < vpMapPoints.size(); i++) {
@@ -638,7 +641,7 @@ public:
     }
 
     // src/ORBmatcher.cc:1710-1839 (LoopClosing::SearchAndFuse); Scw: 4x4 CV_32F
-    int Fuse(KeyFrame* pKF, const gforb_cv::Mat& Scw, const std::vector<MapPoint*>& vpPoints, float th) {
+    int Fuse(KeyFrame* pKF, const gforb_cv::Mat& Scw, const std::vector<MapPoint*>& vpPoints, float th = 2.5) {
         float S[16];
         for (int r = 0; r < 4; r++) for (int c = 0; c < 4; c++) S[r * 4 + c] = Scw.at<float>(r, c);
         const std::set<MapPoint*> spAlreadyFound = pKF->GetMapPoints();

@@ -21,7 +21,7 @@ int touch_everything(bool run) {
     n += m.SearchByProjection(F2, F1, 15.0f);
     n += m.WindowSearch(F1, F2, 200, out, 0, 7);
     n += m.SearchByProjection(F1, F2, 15, out);
-    n += m.DescriptorDistance(desc.row(0), desc.row(0));
+    n += ORBmatcher::DescriptorDistance(desc.row(0), desc.row(0));
     KeyFrame K1(F1), K2(F2);
     std::set<MapPoint*> found;
     n += m.SearchByBoW(&K1, F2, out);

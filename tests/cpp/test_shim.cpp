@@ -105,7 +105,7 @@ int main() {
     bool prevSame = true;
     for (int i = 0; i < F1.N; i++) prevSame = prevSame && prev[i].x == oprev[2 * i] && prev[i].y == oprev[2 * i + 1];
     CHECK(prevSame, "vbPrevMatched differs");
-    CHECK(m.DescriptorDistance(d1.row(0), d2.row(0)) == oracle::ORBmatcher::DescriptorDistance(&od1[0], &od2[0]), "DescriptorDistance");
+    CHECK(ORBmatcher::DescriptorDistance(d1.row(0), d2.row(0)) == oracle::ORBmatcher::DescriptorDistance(&od1[0], &od2[0]), "DescriptorDistance");
 
     // SearchByProjection(F, map points): project frame-1 keypoints (jittered) into frame 2
     std::vector<MapPoint> mps(F1.N);
