@@ -275,7 +275,7 @@ __global__ void __launch_bounds__(128) k_candidates(const QParams P, const Frame
     const int q = blockIdx.x * 4 + warp, b = blockIdx.y;
     const int tb = (MODE == M_AREA) ? P.aFrame : b;      // target frame
     int Q;
-    if (MODE == M_MAP || MODE == M_PKF) Q = P.mpCounts[b];
+    if (MODE == M_MAP || MODE == M_PKF) Q = min(P.mpCounts[b], P.mpStride);
     else if (MODE == M_AREA) Q = P.aCount;
     else Q = P.src.counts[b];
     Q = min(Q, maxQ);

@@ -326,3 +326,46 @@ def test_search_by_sim3(orc, seq_frames, th):
         assert np.array_equal(m12[b, :n1], em)
         tot += en
     assert tot > 300
+
+
+def test_edge_cases(orc, seq_frames):
+    """empty keyframes, lists of skipped points only, features without vocabulary nodes, a batch of zero problems: no match,
+    every output written, no error"""
+    from gf_orb_slam_b200 import ORBmatcher, Frames, WorldPoints
+    kps, desc, counts = seq_frames
+    B = 2
+    c0 = counts[:B].astype(np.int32).copy(); c0[1] = 0                      # the second keyframe is empty
+    KF1 = Frames(kps[:B], desc[:B], c0, W, H); KF2 = Frames(kps[1:B + 1], desc[1:B + 1], counts[1:B + 1].astype(np.int32).copy(), W, H)
+    m = ORBmatcher(0.8, True, max_batch=B, max_keypoints=S, max_queries=S)
+    mp = np.arange(B * S, dtype=np.int32).reshape(B, S); none = np.full((B, S), -1, np.int32)
+    out = np.full((B, S), -7, np.int32)
+    nm = m.SearchByBoWKeyFrames(KF1, mp, none, KF2, mp, none, out)          # no feature sits in a node
+    assert (np.asarray(nm) == 0).all() and (out == -1).all()
+    out[:] = -7
+    nodes = np.full((B, S), 5, np.int32)
+    nm = m.SearchForTriangulation(KF1, mp, nodes, KF2, mp, nodes, np.zeros((B, 9), np.float32), out)   # every feature holds a map point
+    assert (np.asarray(nm) == 0).all() and (out == -1).all()
+    L = 64
+    z = np.zeros((B, L, 3), np.float32)
+    pts = WorldPoints(z, z, np.ones((B, L), np.float32), np.ones((B, L), np.float32), np.zeros((B, L, 32), np.uint8),
+                      np.ones((B, L), np.uint8), np.full(B, L, np.int32))   # every entry skipped
+    bi = np.full((B, L), -9, np.int32); bd = np.full((B, L), -9, np.int32)
+    T = np.tile(np.eye(4, dtype=np.float32).reshape(16), (B, 1))
+    nf = m.Fuse(KF1, T, (458.0, 458.0, 376.0, 240.0), pts, 3.0, bi, bd)
+    assert (np.asarray(nf) == 0).all() and (bi == -1).all() and (bd == INT_MAX).all()
+    # points that are not skipped but lie behind the camera / project outside the image / at z = 0
+    w = np.zeros((B, L, 3), np.float32); w[:, :, 2] = -1.0; w[:, 1::3, 2] = 0.0; w[:, 2::3] = (1e6, 1e6, 1.0)
+    pts = WorldPoints(w, z, np.ones((B, L), np.float32), np.full((B, L), 1e9, np.float32), np.zeros((B, L, 32), np.uint8),
+                      np.zeros((B, L), np.uint8), np.full(B, L, np.int32))
+    nf = m.Fuse(KF1, T, (458.0, 458.0, 376.0, 240.0), pts, 3.0, bi, bd, sim3=True)
+    assert (np.asarray(nf) == 0).all() and (bi == -1).all()
+    matched = np.full((B, S), -1, np.int32)
+    nm = m.SearchByProjectionSim3(KF1, T, (458.0, 458.0, 376.0, 240.0), pts, np.zeros((B, L), np.int32), 10, matched)
+    assert (np.asarray(nm) == 0).all() and (matched == -1).all()
+    m0 = ORBmatcher(0.8, True, max_batch=1, max_keypoints=S, max_queries=S)
+    E = Frames(kps[:0], desc[:0], counts[:0].astype(np.int32), W, H)
+    from gf_orb_slam_b200 import _lib
+    import ctypes as C
+    a = E.cstruct()
+    rc = _lib.lib().gforb_search_by_bow_keyframes(m0._h, C.byref(a), None, None, C.byref(a), None, None, 0, 0.8, 1, None, None, 0, None)
+    assert rc in (0, -2)                                                     # zero problems: nothing to do (or rejected arguments)
