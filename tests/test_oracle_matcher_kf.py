@@ -245,3 +245,18 @@ def test_sim3_decomposition_and_projection_properties(orc):
     # every fused point took the keypoint it was generated from (descriptor distance 0) and now sits in that slot
     fused = bd1 <= 50
     assert np.array_equal(bi1[fused], pts[fused]) and (bd1[fused] == 0).all() and np.array_equal(s1[fused], pts[fused])
+
+
+@pytest.mark.parametrize("dy,octave,expect", [(0.0, 0, 1), (1.9, 0, 1), (2.0, 0, 0), (3.0, 0, 0), (3.0, 3, 1), (3.4, 3, 0), (-3.0, 3, 1)])
+def test_epipolar_gate_known_answers(orc, dy, octave, expect):
+    """CheckDistEpipolarLine (src/ORBmatcher.cc:705-722) by hand: with F12 = [t]x for a translation along x the line of (x1, y1) is
+    y = y1, the squared distance of (x2, y1 + dy) is dy^2, and the gate is dy^2 < 3.84 * sigma2(octave of kp2) with
+    sigma2 = 1.2^(2 octave): 3.84 at octave 0 (|dy| < 1.96), 11.47 at octave 3 (|dy| < 3.39)"""
+    k1 = np.zeros(1, KP); k2 = np.zeros(1, KP)
+    k1["x"] = 100.0; k1["y"] = 50.0; k2["x"] = 80.0; k2["y"] = 50.0 + dy; k2["octave"] = octave
+    d = np.arange(32, dtype=np.uint8).reshape(1, 32)
+    F1 = orc.Frame(k1, d, 752, 480); F2 = orc.Frame(k2, d, 752, 480)
+    F1.set_mappoints(np.array([-1], np.int32)); F2.set_mappoints(np.array([-1], np.int32))
+    F = np.array([0, 0, 0, 0, 0, -1, 0, 1, 0], np.float32)
+    n, m = orc.search_for_triangulation(F1, np.array([7], np.int32), F2, np.array([7], np.int32), F, checkOri=False)
+    assert n == expect and m[0] == (0 if expect else -1)
