@@ -35,35 +35,41 @@ __global__ void __launch_bounds__(256) k_fe_prep(const GforbKeyPoint* __restrict
 
 using namespace gforb;
 
+// buffer sets in flight: step t's extraction may start when the matcher, the selection and the download of step t - FE_NB are
+// done.  With two sets the extraction of step t waited ~0.26 ms per batch for the selection of step t - 2 (extraction 3.09 ms,
+// matcher + selection 3.05 ms behind it when they co-run); a third set removes the wait.
+// GFORB_FE_NB (2 .. 4) overrides the default of 3 (A/B tool).
+#define FE_NB 4                 /* array size; the number of sets in use is GforbFrontEnd::nb */
 struct FeStage { std::string name; double ms = 0; int n = 0; };
 struct FeRec { int stage; cudaEvent_t e0, e1; };
 
 struct GforbFrontEnd {
+    int nb = 3;                            // buffer sets in flight
     GforbFrontEndConfig cfg;
     int device = 0, B = 0, nf = 0, k = 0, launches = 0, lastBatch = 0;
     long long t = 0;                      // steps issued
     GforbExtractor* ex = nullptr;
     GforbMatcher* mt = nullptr;
     GforbObs* obs = nullptr;
-    uint8_t* d_img[2] = {nullptr, nullptr};
-    GforbKeyPoint* d_kps[2] = {nullptr, nullptr};      // (B + 1) x nf, slot 0 = halo
-    uint8_t* d_desc[2] = {nullptr, nullptr};
-    int32_t* d_counts[2] = {nullptr, nullptr};
-    float* d_prev[2] = {nullptr, nullptr};
-    int32_t* d_m12[2] = {nullptr, nullptr};
-    int32_t* d_nmatch[2] = {nullptr, nullptr};
-    int32_t* d_octave[2] = {nullptr, nullptr};
-    int32_t* d_cntSel[2] = {nullptr, nullptr};
-    double* d_blocks[2] = {nullptr, nullptr};
-    double* d_obsScore[2] = {nullptr, nullptr};
-    int32_t* d_selIdx[2] = {nullptr, nullptr};
-    double* d_selLd[2] = {nullptr, nullptr};
-    int32_t* d_selN[2] = {nullptr, nullptr};
+    uint8_t* d_img[FE_NB] = {};
+    GforbKeyPoint* d_kps[FE_NB] = {};      // (B + 1) x nf, slot 0 = halo
+    uint8_t* d_desc[FE_NB] = {};
+    int32_t* d_counts[FE_NB] = {};
+    float* d_prev[FE_NB] = {};
+    int32_t* d_m12[FE_NB] = {};
+    int32_t* d_nmatch[FE_NB] = {};
+    int32_t* d_octave[FE_NB] = {};
+    int32_t* d_cntSel[FE_NB] = {};
+    double* d_blocks[FE_NB] = {};
+    double* d_obsScore[FE_NB] = {};
+    int32_t* d_selIdx[FE_NB] = {};
+    double* d_selLd[FE_NB] = {};
+    int32_t* d_selN[FE_NB] = {};
     float* d_world = nullptr; int32_t* d_score = nullptr; uint8_t* d_valid = nullptr; double* d_Xv = nullptr; float* d_sigma2 = nullptr;
     uint32_t* d_seeds = nullptr;
     bool mapSet = false;
     cudaStream_t sMain = nullptr, sMatch = nullptr, sSel = nullptr, sUp = nullptr, sDown = nullptr;
-    cudaEvent_t evExtract[2], evMatch[2], evSel[2], evH2D[2], evImgFree[2], evD2H[2];
+    cudaEvent_t evExtract[FE_NB], evMatch[FE_NB], evSel[FE_NB], evH2D[FE_NB], evImgFree[FE_NB], evD2H[FE_NB];
     cudaEvent_t evHostDone[8];             // ring: step t's host frames consumed and host outputs delivered (gforb_frontend_wait_results)
     std::vector<void*> allocs;
     // profiling
@@ -100,7 +106,7 @@ int gforb_frontend_destroy(GforbFrontEnd* F) {
     if (F->mt) gforb_matcher_destroy(F->mt);
     if (F->obs) gforb_obs_destroy(F->obs);
     for (void* p : F->allocs) cudaFree(p);
-    for (int i = 0; i < 2; i++) {
+    for (int i = 0; i < FE_NB; i++) {
         cudaEventDestroy(F->evExtract[i]); cudaEventDestroy(F->evMatch[i]); cudaEventDestroy(F->evSel[i]);
         cudaEventDestroy(F->evH2D[i]); cudaEventDestroy(F->evImgFree[i]); cudaEventDestroy(F->evD2H[i]);
     }
@@ -125,7 +131,8 @@ int gforb_frontend_create(const GforbFrontEndConfig* cfg, GforbFrontEnd** out) {
     GF_CUDA_OK(cudaSetDevice(cfg->device));
     GforbFrontEnd* F = new GforbFrontEnd();
     F->cfg = *cfg; F->device = cfg->device; F->B = cfg->max_batch; F->nf = cfg->nfeatures; F->k = cfg->n_good;
-    for (int i = 0; i < 2; i++) {
+    F->nb = std::min(FE_NB, std::max(2, env_int("GFORB_FE_NB", 3)));
+    for (int i = 0; i < FE_NB; i++) {
         cudaEventCreateWithFlags(&F->evExtract[i], cudaEventDisableTiming); cudaEventCreateWithFlags(&F->evMatch[i], cudaEventDisableTiming);
         cudaEventCreateWithFlags(&F->evSel[i], cudaEventDisableTiming); cudaEventCreateWithFlags(&F->evH2D[i], cudaEventDisableTiming);
         cudaEventCreateWithFlags(&F->evImgFree[i], cudaEventDisableTiming); cudaEventCreateWithFlags(&F->evD2H[i], cudaEventDisableTiming);
@@ -168,7 +175,7 @@ int gforb_frontend_create(const GforbFrontEndConfig* cfg, GforbFrontEnd** out) {
     if (cfg->overlap) gforb_obs_set_select_residency(F->obs, 3);      // it shares the SMs with the next step's extraction
 
     const size_t B = F->B, nf = F->nf, k = F->k, px = (size_t)cfg->width * cfg->height;
-    for (int i = 0; i < 2 && !rc; i++) {
+    for (int i = 0; i < F->nb && !rc; i++) {
         rc = dalloc(F, &F->d_img[i], B * px);
         if (!rc) rc = dalloc(F, &F->d_kps[i], (B + 1) * nf);
         if (!rc) rc = dalloc(F, &F->d_desc[i], (B + 1) * nf * 32);
@@ -236,9 +243,9 @@ struct ProfScope {
 // one step on frames resident at dimg; the caller has made sMain wait for whatever produces dimg
 int step_common(GforbFrontEnd* F, const uint8_t* dimg, int batch) {
     const GforbFrontEndConfig& c = F->cfg;
-    const int p = (int)(F->t & 1), nf = F->nf;
+    const int p = (int)(F->t % F->nb), nf = F->nf;
     const size_t px = (size_t)c.width * c.height;
-    // buffer set p was last used by step t-2: its matcher, selection and result download must be done
+    // buffer set p was last used by step t - FE_NB: its matcher, selection and result download must be done
     GF_CUDA_OK(cudaStreamWaitEvent(F->sMain, F->evMatch[p], 0));
     GF_CUDA_OK(cudaStreamWaitEvent(F->sMain, F->evSel[p], 0));
     GF_CUDA_OK(cudaStreamWaitEvent(F->sMain, F->evD2H[p], 0));
@@ -246,7 +253,7 @@ int step_common(GforbFrontEnd* F, const uint8_t* dimg, int batch) {
     {
         ProfScope ps(F, 0, "extract", F->sMain);
         if (F->t > 0) {                                               // halo: the newest frame of the previous step -> slot 0
-            const int o = p ^ 1, s = F->lastBatch;
+            const int o = (p + F->nb - 1) % F->nb, s = F->lastBatch;
             GF_CUDA_OK(cudaMemcpyAsync(F->d_kps[p], F->d_kps[o] + (size_t)s * nf, (size_t)nf * sizeof(GforbKeyPoint), cudaMemcpyDeviceToDevice, F->sMain));
             GF_CUDA_OK(cudaMemcpyAsync(F->d_desc[p], F->d_desc[o] + (size_t)s * nf * 32, (size_t)nf * 32, cudaMemcpyDeviceToDevice, F->sMain));
             GF_CUDA_OK(cudaMemcpyAsync(F->d_counts[p], F->d_counts[o] + s, sizeof(int32_t), cudaMemcpyDeviceToDevice, F->sMain));
@@ -310,7 +317,7 @@ int gforb_frontend_step_host(GforbFrontEnd* F, const uint8_t* images, int batch,
         return GFORB_ERR_ARG;
     if (batch > F->B) return GFORB_ERR_CAPACITY;
     GF_CUDA_OK(cudaSetDevice(F->device));
-    const int q = (int)(F->t & 1), nf = F->nf, k = F->k;
+    const int q = (int)(F->t % F->nb), nf = F->nf, k = F->k;
     const size_t px = (size_t)F->cfg.width * F->cfg.height;
     // upload on its own stream (its own copy engine and queue): it may start as soon as the extraction that last read image
     // buffer q (step t-2) is done, i.e. while step t-1 is still computing
@@ -372,7 +379,7 @@ int gforb_frontend_wait_results(GforbFrontEnd* F, int steps_back) {
 
 int gforb_frontend_results(GforbFrontEnd* F, GforbFrontEndOutputs* o) {
     if (!F || !o || F->t == 0) return GFORB_ERR_ARG;
-    const int p = (int)((F->t - 1) & 1), nf = F->nf;
+    const int p = (int)((F->t - 1) % F->nb), nf = F->nf;
     o->keypoints = F->d_kps[p] + nf; o->descriptors = F->d_desc[p] + (size_t)nf * 32; o->counts = F->d_counts[p] + 1;
     o->matches12 = F->d_m12[p]; o->nmatches = F->d_nmatch[p];
     o->good_idx = F->d_selIdx[p]; o->good_logdet = F->d_selLd[p]; o->good_n = F->d_selN[p];
