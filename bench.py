@@ -590,8 +590,63 @@ def extras(torch, local, world_size, rank):
                 "ms_per_256_calls": msb, "calls_per_s": Bc / (msb * 1e-3), "map_points_per_s": Bc * M / (msb * 1e-3),
                 "matches_per_call": float(nm.float().mean().item()), "launches": m.last_launches()}
 
+    def lc():
+        # the loop-closing / mapping overloads: 256 batched ORBmatcher::Fuse matching loops, 1000 map points projected into
+        # a 1000-keypoint keyframe each, device-resident; the oracle's Fuse on one thread beside it
+        from gf_orb_slam_b200 import Frames, ORBextractor, ORBmatcher, WorldPoints
+        import numpy as _np
+        import oracle
+        Bc, L = 256, 1000
+        img = synth.textured_frame(W_, H_, seed=1)
+        ex = ORBextractor(1000, 1.2, 8, max_width=W_, max_height=H_, max_batch=1, device=local)
+        kps, desc, counts = ex.extract_batch(img[None])
+        n = int(counts[0])
+        fx = fy = 458.0; cx, cy = W_ / 2.0, H_ / 2.0
+        u01 = synth.uniform01(77, 2 * L).reshape(L, 2)
+        pick = _np.minimum((u01[:, 0] * n).astype(_np.int64), n - 1)
+        z = (2.0 + 6.0 * u01[:, 1]).astype(_np.float32)
+        world = _np.stack([(kps["x"][0, pick] + 1.0 - cx) / fx * z, (kps["y"][0, pick] - 1.0 - cy) / fy * z, z], 1).astype(_np.float32)
+        d3 = _np.linalg.norm(world.astype(_np.float64), axis=1)
+        scale = (_np.float32(1.2) ** _np.arange(8)).astype(_np.float32)
+        mind = (d3 / (scale[_np.clip(kps["octave"][0, pick], 0, 7)] * 0.99)).astype(_np.float32); maxd = (mind * 5).astype(_np.float32)
+        nrm = (world / d3[:, None]).astype(_np.float32)
+        mpd = desc[0, pick].copy()
+        rep = lambda a: torch.from_numpy(_np.ascontiguousarray(_np.repeat(a[None], Bc, 0))).cuda()
+        pts = WorldPoints(rep(world), rep(nrm), rep(mind), rep(maxd), rep(mpd), torch.zeros((Bc, L), dtype=torch.uint8).cuda(),
+                          torch.full((Bc,), L, dtype=torch.int32).cuda())
+        kview = torch.from_numpy(_np.repeat(kps.view(_np.float32).reshape(1, 1000, 7), Bc, 0)).cuda()
+        KF = Frames(kview, torch.from_numpy(_np.repeat(desc, Bc, 0)).cuda(), torch.from_numpy(_np.repeat(counts, Bc)).cuda(), W_, H_)
+        T = torch.eye(4, dtype=torch.float32).reshape(1, 16).repeat(Bc, 1).cuda()
+        m = ORBmatcher(0.6, True, max_batch=Bc, max_keypoints=1000, max_queries=L, device=local)
+        bi = torch.empty((Bc, L), dtype=torch.int32).cuda(); bd = torch.empty((Bc, L), dtype=torch.int32).cuda()
+        nf = torch.zeros(Bc, dtype=torch.int32).cuda()
+        st = torch.cuda.current_stream().cuda_stream
+        for _ in range(2):
+            m.Fuse(KF, T, (fx, fy, cx, cy), pts, 3.0, bi, bd, nfused=nf, stream=st, sync=False)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        it = 10
+        e0.record()
+        for _ in range(it):
+            m.Fuse(KF, T, (fx, fy, cx, cy), pts, 3.0, bi, bd, nfused=nf, stream=st, sync=False)
+        e1.record()
+        torch.cuda.synchronize()
+        msb = e0.elapsed_time(e1) / it
+        okf = oracle.Frame(kps[0, :n], desc[0, :n], W_, H_)
+        okf.set_camera(fx, fy, cx, cy, _np.eye(4, dtype=_np.float32))
+        slot = _np.full(n, -1, _np.int32); bad = _np.zeros(L, _np.uint8); ik = _np.full(L, -1, _np.int32)
+        t0 = _t.perf_counter()
+        for _ in range(3):
+            en, ebi, ebd, _, _, _ = oracle.fuse(okf, None, _np.arange(L, dtype=_np.int32), world, nrm, mind, maxd, mpd, 3.0, slot, bad, ik)
+        oms = (_t.perf_counter() - t0) / 3 * 1e3
+        same = bool((bi[0].cpu().numpy() == ebi).all() and (bd[0].cpu().numpy() == ebd).all())
+        return {"what": "256 batched matching loops of ORBmatcher::Fuse(pKF, vpMapPoints, th=3): 1000 map points into a 1000-keypoint keyframe each, device-resident",
+                "ms_per_256_calls": msb, "calls_per_s": Bc / (msb * 1e-3), "fused_per_call": float(nf.float().mean().item()),
+                "launches": m.last_launches(), "oracle_ms_per_call_1_thread": oms, "bit_exact_vs_oracle": same}
+
     out["C1"] = _guard(c1)
     out["C3"] = _guard(c3)
+    out["LC_fuse"] = _guard(lc)
     return out
 
 
