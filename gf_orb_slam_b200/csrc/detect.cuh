@@ -7,7 +7,7 @@
 // score >= iniThFAST.  The cell interiors tile [16, w-16) x [16, h-16) exactly, so one dense pass over the level with
 // per-column / per-row "cell edge" masks reproduces every per-cell NMS at once.
 //
-// k_fast_nms: one warp per strip of 120 output columns x up to 64 output rows.  Lane l owns the 4 pixels
+// k_fast_nms: one warp per strip of 120 output columns x up to 64 (small batches) or 128 output rows.  Lane l owns the 4 pixels
 // x = X0 - 4 + 4 l .. +3 (two u16x2 pairs A, B); lanes 0 and 31 only provide the horizontal NMS halo.  Each input row is
 // read ONCE per strip (one coalesced 32-bit load per lane, neighbours' words by shuffle), expanded ONCE into its nine
 // zero-extended u16x2 pixel pairs and kept in a 7-row register window that rolls down the strip; the FAST ring pairs are
@@ -18,7 +18,7 @@
 namespace gforb {
 
 static const int FN_OUTW = 120;          // output columns per strip (lanes 1..30)
-static const int FN_ROWS = 64;           // output rows per strip
+static const int FN_ROWS[2] = {64, 128};  // most output rows per strip: variant 0 / variant 1 (LevelPlan::fnRows holds the per-level value)
 static const int FN_WARPS = 4;           // warps (strips) per CTA
 #ifndef FN_QD
 #define FN_QD 1                          // prefetch depth in rows (1 or 7: must divide the 7-phase unroll)
@@ -96,18 +96,19 @@ struct FnNms {                            // packed NMS state of pairs A and B f
 
 __global__ void __launch_bounds__(FN_WARPS * 32, FN_MINB) k_fast_nms(const uint8_t* __restrict__ pyr, uint8_t* __restrict__ smap,
                                                             size_t framePyr, const LevelPlan* __restrict__ levels,
-                                                            int nLevels, int tasksPerFrame, int minTh) {
+                                                            int nLevels, int tasksPerFrame, int minTh, int fv) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     int task = blockIdx.x * FN_WARPS + warp;
     const int b = blockIdx.y;
     if (task >= tasksPerFrame) return;
     int l = 0;
-    while (l + 1 < nLevels && task >= levels[l + 1].fnTaskBase) l++;
+    while (l + 1 < nLevels && task >= (fv ? levels[l + 1].fnTaskBase[1] : levels[l + 1].fnTaskBase[0])) l++;
     const LevelPlan L = levels[l];
-    task -= L.fnTaskBase;
+    task -= fv ? L.fnTaskBase[1] : L.fnTaskBase[0];
+    const int stripRows = fv ? L.fnRows[1] : L.fnRows[0];
     const int sy = task / L.fnStripsX, sx = task - sy * L.fnStripsX;
     const int X0 = EDGE + FN_OUTW * sx;                     // first output column (ROI coordinates)
-    const int Y0 = EDGE + FN_ROWS * sy, Y1 = min(Y0 + FN_ROWS, L.h - EDGE);
+    const int Y0 = EDGE + stripRows * sy, Y1 = min(Y0 + stripRows, L.h - EDGE);
     const int xl = X0 - 4 + 4 * lane;                      // first of this lane's 4 pixels
     const uint8_t* roi = pyr + (size_t)b * framePyr + L.off + (size_t)EDGE * L.pitch + EDGE;
     uint8_t* oroi = smap + (size_t)b * framePyr + L.off + (size_t)EDGE * L.pitch + EDGE;

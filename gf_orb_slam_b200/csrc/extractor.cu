@@ -34,8 +34,8 @@ struct LevelPlan {
     int xtab, ytab;               // offsets (in int2 units) of the resize tables for l-1 -> l
     int scaledPatchSize;
     float scale;
-    int fnStripsX, fnStripsY, fnTaskBase;   // k_fast_nms strips (detect.cuh)
-    int blStripsX, blTaskBase;              // k_blur2 strips (blur.cuh)
+    int fnStripsX, fnRows[2], fnTaskBase[2];   // k_fast_nms strips (detect.cuh): [0] rows <= 64 per strip (small batches), [1] <= 128
+    int blStripsX, blRows[2], blTaskBase[2];   // k_blur2 strips (blur.cuh), same two strip heights
 };
 struct CellPlan {
     int level, x0, y0, x1, y1;    // interior rectangle in level ROI coordinates [x0,x1) x [y0,y1) (may be empty)
@@ -53,6 +53,10 @@ namespace gforb {
 // two 128-bit loads (a per-lane index into __constant__ memory would serialise on the ADU pipe: ncu r1_v1, adu=97%)
 __device__ __align__(16) signed char g_pattern[256 * 4];
 __constant__ int c_umax[16];
+// second-generation keypoint kernels (k_orient2 / k_describe2): the pattern as floats (no I2F on the XU pipe) and the
+// IC_Angle task weights of k_orient's shared table, built once on the host
+__device__ __align__(16) float g_patternF[256 * 4];
+__device__ __align__(8) int2 g_orientW[256];
 __constant__ int c_gauss[2][7] = {{18, 34, 48, 56, 48, 34, 18}, {18, 34, 49, 55, 49, 34, 18}};
 
 static const signed char h_pattern[256][4] = {
@@ -790,19 +794,31 @@ __global__ void __launch_bounds__(256) k_orient(const uint8_t* __restrict__ pyr,
 // src/ORBextractor.cc:161-201.  Warp per keypoint, lane j builds descriptor byte j (8 tests, 16 taps).  Taps inside
 // the level ROI read the blurred plane, taps in the 16-px ring read the unblurred reflect-101 ring (the reference
 // blurs the ROI in place and leaves the ring untouched).
+// ROWMAP (default): warp per output row j < nfeatures (kp_row_to_slot); otherwise warp per slot of the per-level lists
+// (kpCapTotal slots, ~3.5 x nfeatures, most of which exit right after the level search: GFORB_KP=v1).
+__device__ __forceinline__ bool kp_row_to_slot(int j, int b, int nLevels, const int* __restrict__ lvlCount, int& l, int& i);
+template <bool ROWMAP>
 __global__ void __launch_bounds__(256) k_describe(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ blr,
                                                   size_t framePyr, const LevelPlan* __restrict__ levels, int nLevels,
                                                   const uint32_t* __restrict__ lvlKp, size_t frameKp, int kpCapTotal,
                                                   const int* __restrict__ lvlCount,
                                                   const GforbKeyPoint* __restrict__ kps, uint8_t* __restrict__ desc,
                                                   int nfeatures) {
-    const int slot = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), b = blockIdx.y, lane = threadIdx.x & 31;
-    if (slot >= kpCapTotal) return;
-    int l = 0, base = 0;
-    while (l + 1 < nLevels && slot >= levels[l + 1].kpBase) { base += lvlCount[b * nLevels + l]; l++; }
+    const int slot0 = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), b = blockIdx.y, lane = threadIdx.x & 31;
+    int l = 0, base = 0, i, slot = slot0;
+    if (ROWMAP) {
+        if (slot0 >= nfeatures || !kp_row_to_slot(slot0, b, nLevels, lvlCount, l, i)) return;
+        base = slot0 - i;
+    } else {
+        if (slot >= kpCapTotal) return;
+        while (l + 1 < nLevels && slot >= levels[l + 1].kpBase) { base += lvlCount[b * nLevels + l]; l++; }
+    }
     const LevelPlan L = levels[l];
-    const int i = slot - L.kpBase;
-    if (i >= lvlCount[b * nLevels + l]) return;
+    if (ROWMAP) slot = L.kpBase + i;
+    else {
+        i = slot - L.kpBase;
+        if (i >= lvlCount[b * nLevels + l]) return;
+    }
     const uint32_t e = lvlKp[(size_t)b * frameKp + slot];
     const int cx = e & 0xfff, cy = (e >> 12) & 0xfff;
     const size_t oi = (size_t)b * nfeatures + base + i;
@@ -831,6 +847,163 @@ __global__ void __launch_bounds__(256) k_describe(const uint8_t* __restrict__ py
     desc[oi * 32 + lane] = (uint8_t)val;
 }
 
+// ------------------------------------------------------------------------------------------------ K4b / K6b
+// Second generation of the two keypoint kernels.  Both take one warp per OUTPUT row j < nfeatures (the level and the slot
+// follow from the per-level counts) instead of one warp per slot of the over-provisioned per-level lists (kpCapTotal ~ 3.5 x
+// nfeatures at the reference's defaults).  k_orient2 is the default (GFORB_KP=v1: k_orient + slot-mapped k_describe);
+// k_describe2 is an A/B LOSER kept selectable (GFORB_DESCRIBE=smem) -- see its comment.
+__device__ __forceinline__ bool kp_row_to_slot(int j, int b, int nLevels, const int* __restrict__ lvlCount, int& l, int& i) {
+    int base = 0;
+    for (l = 0; l < nLevels; l++) {
+        const int n = lvlCount[b * nLevels + l];
+        if (j < base + n) { i = j - base; return true; }
+        base += n;
+    }
+    return false;
+}
+
+// IC_Angle as in k_orient; the task weights come from g_orientW (coalesced 8-byte loads into registers) instead of a
+// table that every CTA rebuilt in shared memory through divergent __constant__ reads.
+__global__ void __launch_bounds__(256) k_orient2(const uint8_t* __restrict__ pyr, size_t framePyr,
+                                                 const LevelPlan* __restrict__ levels, int nLevels,
+                                                 const uint32_t* __restrict__ lvlKp, size_t frameKp,
+                                                 const int* __restrict__ lvlCount, GforbKeyPoint* __restrict__ kps,
+                                                 int32_t* __restrict__ counts, int nfeatures,
+                                                 const float* __restrict__ lvlResp) {
+    const int j = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), b = blockIdx.y, lane = threadIdx.x & 31;
+    if (j >= nfeatures) return;
+    if (j == 0 && lane == 0) {
+        int tot = 0;
+        for (int q = 0; q < nLevels; q++) tot += lvlCount[b * nLevels + q];
+        counts[b] = tot;
+    }
+    int l, i;
+    if (!kp_row_to_slot(j, b, nLevels, lvlCount, l, i)) return;
+    const LevelPlan L = levels[l];
+    const int slot = L.kpBase + i;
+    const uint32_t e = lvlKp[(size_t)b * frameKp + slot];
+    const int x = e & 0xfff, y = (e >> 12) & 0xfff, score = e >> 24;
+    const uint32_t* w00 = reinterpret_cast<const uint32_t*>(pyr + (size_t)b * framePyr + L.off + (size_t)(EDGE + y - HALF_PATCH) * L.pitch) +
+                          (x >> 2) + (lane & 7);
+    const int sh = (x & 3) * 8, pw = L.pitch >> 2;
+    int m10 = 0, m01 = 0;
+#pragma unroll
+    for (int it = 0; it < 8; it++) {
+        const int row = it * 4 + (lane >> 3);                     // 0..31, row 31 has empty weights
+        const int2 w = g_orientW[it * 32 + lane];
+        if (row < 2 * HALF_PATCH + 1) {
+            const uint32_t* wp = w00 + row * pw;
+            const uint32_t px = __funnelshift_r(__ldg(wp), __ldg(wp + 1), sh);
+            m10 = dp4a_s8u8(w.x, px, m10);
+            m01 += (row - HALF_PATCH) * (int)__dp4a((uint32_t)w.y, px, 0u);
+        }
+    }
+    m10 = __reduce_add_sync(0xffffffffu, m10);
+    m01 = __reduce_add_sync(0xffffffffu, m01);
+    if (lane == 0) {
+        GforbKeyPoint k;
+        float fx = (float)x, fy = (float)y;
+        if (l != 0) { fx = __fmul_rn(fx, L.scale); fy = __fmul_rn(fy, L.scale); }
+        k.x = fx; k.y = fy;
+        k.size = (float)L.scaledPatchSize;
+        k.angle = fast_atan2_deg((float)m01, (float)m10);
+        k.response = lvlResp ? lvlResp[(size_t)b * frameKp + slot] : (float)score;   // HARRIS_SCORE : FAST_SCORE
+        k.octave = l;
+        k.class_id = -1;
+        kps[(size_t)b * nfeatures + j] = k;
+    }
+}
+
+// A/B loser (B200: 0.369 ms per 250 frames against 0.2375 ms for k_describe; ncu: L1 data-pipe wavefronts 399 per keypoint
+// against 186 -- the 128-bit staging and float-pattern loads cost one data-stage wavefront per 32-byte sector, 317 per
+// keypoint, where a 32-lane byte gather costs ~9; shared-memory gathers add 49 + 31 for the stores).
+// computeOrbDescriptor with the keypoint's 37 x 37 tap window staged in shared memory.  The rotated pattern reaches
+// |ix|, |iy| <= 18 (largest pattern radius 18.38), so the window is plane rows cy - 2 .. cy + 34 and the 16-byte chunks
+// that cover plane columns cx - 2 .. cx + 34 (3 or 4 per row): ~120 coalesced 128-bit loads per warp replace 512
+// byte gathers that each touched up to 32 cache lines (the L1 tag stage was the limiter of k_describe: ncu l1 71 %).
+// A chunk inside the level ROI comes from the blurred plane, one in the 16-px ring from the unblurred pyramid plane,
+// a chunk that straddles the ROI edge is merged byte by byte -- the same source rule as k_describe, tap for tap.
+// cvRound of the rotated coordinates is taken by adding 1.5 * 2^23 (round-to-nearest-even in the float add, the
+// integer sits in the mantissa), which keeps the conversions off the XU pipe; identical to __float2int_rn for |v| < 2^22.
+static const int DS_ROWS = 37, DS_PITCH = 80, DS_R = 18;
+__global__ void __launch_bounds__(256) k_describe2(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ blr,
+                                                   size_t framePyr, const LevelPlan* __restrict__ levels, int nLevels,
+                                                   const uint32_t* __restrict__ lvlKp, size_t frameKp,
+                                                   const int* __restrict__ lvlCount,
+                                                   const GforbKeyPoint* __restrict__ kps, uint8_t* __restrict__ desc,
+                                                   int nfeatures) {
+    __shared__ __align__(16) uint8_t s_patch[8][DS_ROWS * DS_PITCH];
+    const int j = blockIdx.x * 8 + (threadIdx.x >> 5), b = blockIdx.y, lane = threadIdx.x & 31;
+    if (j >= nfeatures) return;
+    int l, i;
+    if (!kp_row_to_slot(j, b, nLevels, lvlCount, l, i)) return;
+    const LevelPlan L = levels[l];
+    const uint32_t e = lvlKp[(size_t)b * frameKp + L.kpBase + i];
+    const int cx = e & 0xfff, cy = (e >> 12) & 0xfff;
+    const size_t oi = (size_t)b * nfeatures + j;
+    uint8_t* sp = s_patch[threadIdx.x >> 5];
+    // ---- stage the window (plane coordinates = ROI coordinates + EDGE)
+    const int X0 = cx + EDGE - DS_R, Y0 = cy + EDGE - DS_R;
+    const int a0 = X0 & ~15, o = X0 - a0;
+    const int nch = o + 2 * DS_R >= 48 ? 4 : 3;
+    const uint8_t* Pp = pyr + (size_t)b * framePyr + L.off;
+    const uint8_t* Bp = blr + (size_t)b * framePyr + L.off;
+    const int planeH = L.h + 2 * EDGE;
+    for (int t = lane; t < DS_ROWS * nch; t += 32) {
+        const int r = nch == 4 ? t >> 2 : t / 3, c = t - r * nch;
+        const int Y = Y0 + r, X = a0 + 16 * c;
+        uint4 v = make_uint4(0, 0, 0, 0);
+        if ((unsigned)Y < (unsigned)planeH && X >= 0 && X + 16 <= L.pitch) {
+            const size_t off = (size_t)Y * L.pitch + X;
+            const bool rowIn = Y >= EDGE && Y < EDGE + L.h;
+            if (rowIn && X >= EDGE && X + 16 <= EDGE + L.w) {
+                v = __ldg(reinterpret_cast<const uint4*>(Bp + off));
+            } else {
+                v = __ldg(reinterpret_cast<const uint4*>(Pp + off));
+                if (rowIn && X + 16 > EDGE && X < EDGE + L.w) {          // straddles the left or right ROI edge
+                    const uint4 q = __ldg(reinterpret_cast<const uint4*>(Bp + off));
+                    uint32_t pv[4] = {v.x, v.y, v.z, v.w};
+                    const uint32_t qv[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+                    for (int k = 0; k < 16; k++) {
+                        const int xx = X + k;
+                        if (xx >= EDGE && xx < EDGE + L.w) {
+                            const uint32_t m = 0xffu << (8 * (k & 3));
+                            pv[k >> 2] = (pv[k >> 2] & ~m) | (qv[k >> 2] & m);
+                        }
+                    }
+                    v = make_uint4(pv[0], pv[1], pv[2], pv[3]);
+                }
+            }
+        }
+        *reinterpret_cast<uint4*>(sp + r * DS_PITCH + 16 * c) = v;
+    }
+    const float factorPI = (float)(3.14159265358979323846 / 180.f);
+    const float angle = __fmul_rn(kps[oi].angle, factorPI);
+    const float a = glibc_cosf(angle), bb = glibc_sinf(angle);
+    __syncwarp();
+    // ---- 8 tests of this lane's descriptor byte
+    const float MAGIC = 12582912.f;                               // 1.5 * 2^23; its bit image is 0x4B400000
+    const uint32_t bias = (uint32_t)(DS_R * DS_PITCH + DS_R + o) - 0x4B400000u * (uint32_t)(DS_PITCH + 1);   // mod 2^32
+    const float4* pf = reinterpret_cast<const float4*>(g_patternF) + lane * 8;
+    int val = 0;
+#pragma unroll
+    for (int t = 0; t < 8; t++) {
+        const float4 p4 = __ldg(pf + t);
+        const float pxs[2] = {p4.x, p4.z}, pys[2] = {p4.y, p4.w};
+        int tv[2];
+#pragma unroll
+        for (int q = 0; q < 2; q++) {
+            const float fy = __fadd_rn(__fmul_rn(pxs[q], bb), __fmul_rn(pys[q], a));
+            const float fx = __fsub_rn(__fmul_rn(pxs[q], a), __fmul_rn(pys[q], bb));
+            const int iy = __float_as_int(__fadd_rn(fy, MAGIC)), ix = __float_as_int(__fadd_rn(fx, MAGIC));
+            tv[q] = sp[(uint32_t)iy * DS_PITCH + (uint32_t)ix + bias];
+        }
+        val |= (tv[0] < tv[1]) << t;
+    }
+    desc[oi * 32 + lane] = (uint8_t)val;
+}
+
 // ================================================================================================ host side
 struct Stage { const char* name; cudaEvent_t e0, e1; float ms; };
 struct StageRec { int stage; cudaEvent_t e0, e1; };   // one (stage, call) pair recorded while profiling is on
@@ -851,7 +1024,9 @@ struct GforbExtractor {
     std::vector<LevelPlan> levels;
     std::vector<CellPlan> cells;
     size_t framePyr = 0, frameCand = 0, frameKp = 0;
-    int kpCapTotal = 0, nCellsTotal = 0, detSmem = 0, detPixPitch = 0, fnTasks = 0, blTasks = 0;
+    int kpCapTotal = 0, nCellsTotal = 0, detSmem = 0, detPixPitch = 0, fnTasks[2] = {0, 0}, blTasks[2] = {0, 0};
+    int blurV2 = 0;                     // GFORB_BLUR=v2: second-generation blur (vertical pass on unpacked 32-bit lane-ops) instead of k_blur3 (IDP.2A row pairs)
+    int fnTall = -1;                    // GFORB_FN_TALL=0/1 pins the strip height of k_fast_nms; -1: tall strips once the batch fills the GPU several times
     bool tiled = true;
     int detectVersion = 2;              // GFORB_DETECT=1 selects the first-generation per-cell kernel (A/B tool)
     int blurFork = 1;                   // the blur of a call runs on ownStream beside the quota / retainBest / orientation kernels (gforb_extractor_set_concurrency)
@@ -864,6 +1039,8 @@ struct GforbExtractor {
     int2* d_qtVsz = nullptr;
     size_t frameQtKeys = 0, frameQtNodes = 0, capQtKeys = 0, capQtTmp = 0, capQtNodes = 0, capQtVsz = 0;
     int retainSeq = 0;                  // GFORB_RETAIN=seq: retainBest's nth_element on one lane (the first-generation path)
+    int describeSmem = 0;               // GFORB_DESCRIBE=smem: k_describe2 (tap window staged in shared memory; A/B loser)
+    int kpV1 = 0;                       // GFORB_KP=v1: first-generation k_orient / k_describe (warp per list slot, byte gathers from L1)
     int resizeTma = 0;                  // GFORB_RESIZE=tma / direct: source rows staged by cp.async.bulk (k_resize_tma) or gathered from L1 (k_resize)
     // device buffers
     uint8_t *d_img = nullptr, *d_pyr = nullptr, *d_blr = nullptr, *d_desc = nullptr;
@@ -940,7 +1117,7 @@ static int build_plan(GforbExtractor* E, int w, int h) {
     E->cells.clear();
     std::vector<int2> tabs;
     size_t off = 0;
-    int kpBase = 0, candBase = 0, maxCellW = 0, fnTasks = 0, blTasks = 0;
+    int kpBase = 0, candBase = 0, maxCellW = 0, fnTasks[2] = {0, 0}, blTasks[2] = {0, 0};
     const bool qt = E->distribution == 1;
     E->qlevels.assign(nl, QtLevel());
     int qtKeyBase = 0, qtNodeBase = 0;
@@ -981,12 +1158,19 @@ static int build_plan(GforbExtractor* E, int w, int h) {
         L.nfeaturesCell = (int)ceilf((float)L.nDesired / L.nCells);
         L.cellBase = (int)E->cells.size();
         L.fnStripsX = (W + FN_OUTW - 1) / FN_OUTW;
-        L.fnStripsY = (H + FN_ROWS - 1) / FN_ROWS;
-        L.fnTaskBase = fnTasks;
-        fnTasks += L.fnStripsX * L.fnStripsY;
+        for (int v = 0; v < 2; v++) {                        // equal strips per level: no ragged last strip
+            const int sy = (H + FN_ROWS[v] - 1) / FN_ROWS[v];
+            L.fnRows[v] = (H + sy - 1) / sy;
+            L.fnTaskBase[v] = fnTasks[v];
+            fnTasks[v] += L.fnStripsX * sy;
+        }
         L.blStripsX = (L.w + 127) / 128;
-        L.blTaskBase = blTasks;
-        blTasks += L.blStripsX * ((L.h + BL2_ROWS - 1) / BL2_ROWS);
+        for (int v = 0; v < 2; v++) {
+            const int sy = (L.h + BL2_ROWS[v] - 1) / BL2_ROWS[v];
+            L.blRows[v] = (L.h + sy - 1) / sy;
+            L.blTaskBase[v] = blTasks[v];
+            blTasks[v] += L.blStripsX * sy;
+        }
         if ((long long)L.cellW * (L.levelCols - 1) >= W || (long long)L.cellH * (L.levelRows - 1) >= H) tiled = false;
         L.kpBase = kpBase;
         L.kpCap = 2 * L.nDesired + L.nCells + 64;
@@ -1054,8 +1238,8 @@ static int build_plan(GforbExtractor* E, int w, int h) {
     E->frameKp = (size_t)kpBase;
     E->kpCapTotal = kpBase;
     E->nCellsTotal = (int)E->cells.size();
-    E->fnTasks = fnTasks;
-    E->blTasks = blTasks;
+    E->fnTasks[0] = fnTasks[0]; E->fnTasks[1] = fnTasks[1];
+    E->blTasks[0] = blTasks[0]; E->blTasks[1] = blTasks[1];
     E->tiled = tiled;
     E->detPixPitch = (maxCellW + 16 + 3) & ~3;
     E->detSmem = (DET_BAND + 8) * E->detPixPitch + (DET_BAND + 2) * E->detPixPitch + DET_BAND * ((maxCellW + 31) / 32) * 4 + 16;
@@ -1138,6 +1322,10 @@ int gforb_extractor_create(const GforbExtractorConfig* cfg, GforbExtractor** out
     build_ctor_tables(E);
     if (const char* dv = getenv("GFORB_DETECT")) E->detectVersion = atoi(dv);
     if (const char* rv = getenv("GFORB_RESIZE")) E->resizeTma = !strcmp(rv, "tma") ? 1 : 0;
+    if (const char* kv = getenv("GFORB_KP")) E->kpV1 = !strcmp(kv, "v1") ? 1 : 0;
+    if (const char* dv2 = getenv("GFORB_DESCRIBE")) E->describeSmem = !strcmp(dv2, "smem") ? 1 : 0;
+    if (const char* tv = getenv("GFORB_FN_TALL")) E->fnTall = atoi(tv) ? 1 : 0;
+    if (const char* bv2 = getenv("GFORB_BLUR")) E->blurV2 = !strcmp(bv2, "v2") ? 1 : 0;
 
     GF_CUDA_OK(cudaMemcpyToSymbol(g_pattern, h_pattern, sizeof(h_pattern)));
     {   // umax (src/ORBextractor.cc:500-517)
@@ -1151,6 +1339,21 @@ int gforb_extractor_create(const GforbExtractorConfig* cfg, GforbExtractor** out
             ++v0;
         }
         GF_CUDA_OK(cudaMemcpyToSymbol(c_umax, umax, sizeof(umax)));
+        int2 ow[256];                                            // k_orient2's task table: (row * 8 + chunk) -> {u weights, membership}
+        for (int t = 0; t < 256; t++) {
+            const int row = t >> 3, c = t & 7, vv = row - HALF_PATCH;
+            const int d = row < 2 * HALF_PATCH + 1 ? umax[vv < 0 ? -vv : vv] : -1;
+            uint32_t wu = 0, w1 = 0;
+            for (int k = 0; k < 4; k++) {
+                const int u = -16 + 4 * c + k;
+                if ((u < 0 ? -u : u) <= d) { wu |= (uint32_t)(u & 0xff) << (8 * k); w1 |= 1u << (8 * k); }
+            }
+            ow[t] = make_int2((int)wu, (int)w1);
+        }
+        GF_CUDA_OK(cudaMemcpyToSymbol(g_orientW, ow, sizeof(ow)));
+        float pf[1024];
+        for (int t = 0; t < 1024; t++) pf[t] = (float)h_pattern[t >> 2][t & 3];
+        GF_CUDA_OK(cudaMemcpyToSymbol(g_patternF, pf, sizeof(pf)));
     }
     size_t B = cfg->max_batch;
     GF_CUDA_OK(cudaMalloc((void**)&E->d_kps, B * cfg->nfeatures * sizeof(GforbKeyPoint)));
@@ -1294,8 +1497,11 @@ int gforb_extract(GforbExtractor* E, const uint8_t* images, int w, int h, int st
     end();
     begin("detect");
     if (E->detectVersion == 2 && E->tiled) {
-        k_fast_nms<<<dim3((E->fnTasks + FN_WARPS - 1) / FN_WARPS, batch), FN_WARPS * 32, 0, st>>>(
-            E->d_pyr, E->d_blr, E->framePyr, E->d_levels, nl, E->fnTasks, c.minThFAST); launches++;
+        // strip height: every strip re-reads 7 rows of run-in, so tall strips (<= 128 rows) do ~6 % less work; short ones (<= 64)
+        // keep the latency of a small batch low.  Tall once the short tasks of the batch would fill the resident warps 4 times over.
+        const int fv = E->fnTall >= 0 ? E->fnTall : ((long long)E->fnTasks[0] * batch >= 4LL * E->numSMs * 16 ? 1 : 0);
+        k_fast_nms<<<dim3((E->fnTasks[fv] + FN_WARPS - 1) / FN_WARPS, batch), FN_WARPS * 32, 0, st>>>(
+            E->d_pyr, E->d_blr, E->framePyr, E->d_levels, nl, E->fnTasks[fv], c.minThFAST, fv); launches++;
         k_cell_emit<<<dim3((E->nCellsTotal + EM_WARPS - 1) / EM_WARPS, batch), EM_WARPS * 32, 0, st>>>(
             E->d_blr, E->framePyr, E->d_levels, E->d_cells, E->nCellsTotal, E->d_cand, E->frameCand, E->d_cnt7, E->d_cnt20,
             c.iniThFAST, E->d_err); launches++;
@@ -1315,8 +1521,14 @@ int gforb_extract(GforbExtractor* E, const uint8_t* images, int w, int h, int st
     }
     if (fork) stageStream = E->ownStream;
     begin("blur");
-    k_blur2<<<dim3((E->blTasks + BL2_WARPS - 1) / BL2_WARPS, batch), BL2_WARPS * 32, 0, fork ? E->ownStream : st>>>(
-        E->d_pyr, E->d_blr, E->framePyr, E->d_levels, nl, E->blTasks, c.blur_variant); launches++;
+    const int bv = E->fnTall >= 0 ? E->fnTall : ((long long)E->blTasks[0] * batch >= 4LL * E->numSMs * 16 ? 1 : 0);
+    if (E->blurV2)
+        k_blur2<<<dim3((E->blTasks[bv] + BL2_WARPS - 1) / BL2_WARPS, batch), BL2_WARPS * 32, 0, fork ? E->ownStream : st>>>(
+            E->d_pyr, E->d_blr, E->framePyr, E->d_levels, nl, E->blTasks[bv], c.blur_variant, bv);
+    else
+        k_blur3<<<dim3((E->blTasks[bv] + BL2_WARPS - 1) / BL2_WARPS, batch), BL2_WARPS * 32, 0, fork ? E->ownStream : st>>>(
+            E->d_pyr, E->d_blr, E->framePyr, E->d_levels, nl, E->blTasks[bv], c.blur_variant, bv);
+    launches++;
     end();
     stageStream = st;
     if (fork) GF_CUDA_OK(cudaEventRecord(E->evJoin, E->ownStream));
@@ -1352,14 +1564,28 @@ int gforb_extract(GforbExtractor* E, const uint8_t* images, int w, int h, int st
     }
     end();
     begin("orient");
-    k_orient<<<dim3((E->kpCapTotal + 7) / 8, batch), 256, 0, st>>>(E->d_pyr, E->framePyr, E->d_levels, nl, E->d_lvlKp,
-                                                                    E->frameKp, E->kpCapTotal, E->d_lvlCount, dk, dc, c.nfeatures,
-                                                                    harris ? E->d_lvlResp : nullptr); launches++;
+    if (E->kpV1)
+        k_orient<<<dim3((E->kpCapTotal + 7) / 8, batch), 256, 0, st>>>(E->d_pyr, E->framePyr, E->d_levels, nl, E->d_lvlKp,
+                                                                        E->frameKp, E->kpCapTotal, E->d_lvlCount, dk, dc, c.nfeatures,
+                                                                        harris ? E->d_lvlResp : nullptr);
+    else
+        k_orient2<<<dim3((c.nfeatures + 7) / 8, batch), 256, 0, st>>>(E->d_pyr, E->framePyr, E->d_levels, nl, E->d_lvlKp,
+                                                                       E->frameKp, E->d_lvlCount, dk, dc, c.nfeatures,
+                                                                       harris ? E->d_lvlResp : nullptr);
+    launches++;
     end();
     if (fork) GF_CUDA_OK(cudaStreamWaitEvent(st, E->evJoin, 0));
     begin("describe");
-    k_describe<<<dim3((E->kpCapTotal + 7) / 8, batch), 256, 0, st>>>(E->d_pyr, E->d_blr, E->framePyr, E->d_levels, nl, E->d_lvlKp,
-                                                                      E->frameKp, E->kpCapTotal, E->d_lvlCount, dk, dd, c.nfeatures); launches++;
+    if (E->kpV1)
+        k_describe<false><<<dim3((E->kpCapTotal + 7) / 8, batch), 256, 0, st>>>(E->d_pyr, E->d_blr, E->framePyr, E->d_levels, nl, E->d_lvlKp,
+                                                                                 E->frameKp, E->kpCapTotal, E->d_lvlCount, dk, dd, c.nfeatures);
+    else if (!E->describeSmem)
+        k_describe<true><<<dim3((c.nfeatures + 7) / 8, batch), 256, 0, st>>>(E->d_pyr, E->d_blr, E->framePyr, E->d_levels, nl, E->d_lvlKp,
+                                                                              E->frameKp, E->kpCapTotal, E->d_lvlCount, dk, dd, c.nfeatures);
+    else
+        k_describe2<<<dim3((c.nfeatures + 7) / 8, batch), 256, 0, st>>>(E->d_pyr, E->d_blr, E->framePyr, E->d_levels, nl, E->d_lvlKp,
+                                                                         E->frameKp, E->d_lvlCount, dk, dd, c.nfeatures);
+    launches++;
     end();
     GF_CUDA_OK(cudaGetLastError());
     E->lastLaunches = launches;

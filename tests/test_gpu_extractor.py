@@ -114,6 +114,34 @@ def test_resize_variants_agree(monkeypatch):
         assert np.array_equal(a[3][l], b[3][l]), l
 
 
+@pytest.mark.parametrize("size,nf", [((752, 480), 1000), ((1241, 376), 2000), ((200, 152), 1500)])
+@pytest.mark.parametrize("knob", ["GFORB_KP=v1", "GFORB_DESCRIBE=smem", "GFORB_BLUR=v2", "GFORB_FN_TALL=0", "GFORB_FN_TALL=1"])
+def test_kernel_generations_agree(monkeypatch, knob, size, nf):
+    """A/B partners of the extractor kernels against the default build, byte for byte (keypoints incl. angles, descriptors,
+    counts, blurred planes): GFORB_KP=v1 (first-generation k_orient / slot-mapped k_describe instead of k_orient2 and the
+    row-mapped k_describe), GFORB_DESCRIBE=smem (k_describe2: tap window staged in shared memory, cvRound by the 1.5 * 2^23
+    add; the A/B loser), GFORB_BLUR=v2 (vertical blur pass on unpacked lane-ops instead of k_blur3's IDP.2A row pairs),
+    GFORB_FN_TALL=0/1 (strips of <= 64 / <= 128 rows in k_fast_nms and the blur; the default picks by batch size).
+    The small frame puts most keypoints within 18 px of the ROI edge, so k_describe2's blurred / unblurred-ring merge runs."""
+    from gf_orb_slam_b200 import ORBextractor
+    w, h = size
+    imgs = np.stack([synth.textured_frame(w, h, seed=70 + i) for i in range(3)])
+    res = []
+    for v in (None, knob):
+        for k in ("GFORB_KP", "GFORB_DESCRIBE", "GFORB_BLUR", "GFORB_FN_TALL"):
+            monkeypatch.delenv(k, raising=False)
+        if v:
+            monkeypatch.setenv(*v.split("="))
+        ex = ORBextractor(nf, 1.2, 8, max_width=w, max_height=h, max_batch=3)
+        kps, desc, counts = ex.extract_batch(imgs)
+        res.append((kps.copy(), desc.copy(), counts.copy(), [ex.debug_level(2, l, 1)[16:-16, 16:-16].copy() for l in range(8)]))
+    a, b = res
+    assert np.array_equal(a[2], b[2]) and a[0].tobytes() == b[0].tobytes() and np.array_equal(a[1], b[1])
+    for l in range(8):
+        assert np.array_equal(a[3][l], b[3][l]), l
+    assert a[2].min() > 50
+
+
 @pytest.mark.parametrize("size,nf,variant", [((752, 480), 1000, 0), ((1241, 376), 2000, 1), ((640, 480), 300, 0)])
 def test_retain_variants_agree(monkeypatch, size, nf, variant):
     """retainBest's nth_element replayed by the 32 lanes of a warp (default) gives the permutation of the sequential replay
