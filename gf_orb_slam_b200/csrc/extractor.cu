@@ -32,6 +32,7 @@ struct LevelPlan {
     int nDesired, levelCols, levelRows, cellW, cellH, nCells, cellBase, nfeaturesCell;
     int kpBase, kpCap;            // slice of the per-frame level-keypoint buffer
     int xtab, ytab;               // offsets (in int2 units) of the resize tables for l-1 -> l
+    int qtab, ybtab;              // k_resize2: per column quad {base, selA | selB << 16, 4 weight pairs} (4 int2), per bordered row {src row, b0 | b1 << 16}
     int scaledPatchSize;
     float scale;
     int fnStripsX, fnRows[2], fnTaskBase[2];   // k_fast_nms strips (detect.cuh): [0] rows <= 64 per strip (small batches), [1] <= 128
@@ -156,6 +157,71 @@ __global__ void __launch_bounds__(256, 6) k_resize(const uint8_t* __restrict__ s
             const int h1 = (__ldg(r1 + sx[k]) * a0[k] + __ldg(r1 + sx[k] + 1) * a1[k]) >> 4;
             const int v = (((b0 * h0) >> 16) + ((b1 * h1) >> 16) + 2) >> 2;
             outv |= (uint32_t)min(max(v, 0), 255) << (8 * k);
+        }
+        if (Y < D.rows) *reinterpret_cast<uint32_t*>(dst + (size_t)Y * D.pitch) = outv;
+    }
+}
+
+// K1b, word-load variant (GFORB_RESIZE=words): same thread / band layout and the same fixed-point arithmetic as k_resize, but
+// the 8 byte gathers per source row (two taps x four columns, each warp-wide gather = 2-3 L1 wavefronts) become three aligned
+// 32-bit loads: the four columns of a thread read source bytes base .. base + 6 (base = their smallest tap; adjacent
+// destination columns -- reflected ring columns included -- lie <= scale apart, the host checks the span), two funnel shifts
+// bring bytes base .. base + 7 into a register pair, one PRMT per column pair picks {s[sx], s[sx+1]} of both columns with a
+// per-thread selector, and the horizontal pass of a column is ONE dp2a (16-bit weights x 8-bit pixels) instead of two IMAD.
+__device__ __forceinline__ int dp2a_lo_su(uint32_t w, uint32_t px) {
+    int d;
+    asm("dp2a.lo.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(w), "r"(px), "r"(0));
+    return d;
+}
+__device__ __forceinline__ int dp2a_hi_su(uint32_t w, uint32_t px) {
+    int d;
+    asm("dp2a.hi.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(w), "r"(px), "r"(0));
+    return d;
+}
+// Everything that depends only on the column quad (smallest tap, the two PRMT selectors, the four weight pairs) and on the
+// bordered output row (source row, weight pair; reflect-101 already applied) comes from host-built tables (LevelPlan::qtab,
+// ybtab): the per-thread prologue of k_resize (four reflect-101 loops + table lookups per axis) was 40 % of its instructions.
+// The saturation of cv::resize is dropped: (b0 h0 >> 16) + (b1 h1 >> 16) <= 32656 * 2049 / 65536 < 1021, so the result
+// (.. + 2) >> 2 lies in [0, 255] for every input.
+template <int BAND>
+__global__ void __launch_bounds__(256, 6) k_resize2(const uint8_t* __restrict__ spyr, uint8_t* __restrict__ pyr, size_t framePyr,
+                                                 LevelPlan S, LevelPlan D, const int2* __restrict__ tabs, int quadsPerRow,
+                                                 int nBands) {
+    const int t = blockIdx.x * 256 + threadIdx.x, b = blockIdx.y;
+    if (t >= quadsPerRow * nBands) return;
+    const int band = t / quadsPerRow, q = t - band * quadsPerRow;
+    const int4* __restrict__ qt = reinterpret_cast<const int4*>(tabs + D.qtab) + 2 * q;
+    const int2* __restrict__ ybt = tabs + D.ybtab;
+    const int4 qa = __ldg(qt), qb = __ldg(qt + 1);
+    const int base = qa.x;
+    const uint32_t selA = (uint32_t)qa.y & 0xffffu, selB = (uint32_t)qa.y >> 16;
+    const uint32_t wg0 = (uint32_t)qa.z, wg1 = (uint32_t)qa.w, wg2 = (uint32_t)qb.x, wg3 = (uint32_t)qb.y;
+    const int sh = (base & 3) * 8;
+    const uint8_t* __restrict__ sroi = spyr + (size_t)b * framePyr + S.off + (size_t)EDGE * S.pitch + EDGE + (base & ~3);
+    uint8_t* __restrict__ dst = pyr + (size_t)b * framePyr + D.off + (q << 2);
+    const int Y0 = band * BAND, spw = S.pitch >> 2;
+    int2 ty[BAND];
+#pragma unroll
+    for (int i = 0; i < BAND; i++) ty[i] = __ldg(&ybt[min(Y0 + i, D.rows - 1)]);
+#pragma unroll
+    for (int i = 0; i < BAND; i++) {
+        const int Y = Y0 + i;
+        const int b0 = ty[i].y & 0xffff, b1 = (int)((uint32_t)ty[i].y >> 16);
+        const uint32_t* r0 = reinterpret_cast<const uint32_t*>(sroi + (ptrdiff_t)ty[i].x * S.pitch);   // row sy+1 == S.h is the ring (b1 == 0 there)
+        const uint32_t* r1 = r0 + spw;
+        const uint32_t u0 = __ldg(r0), u1 = __ldg(r0 + 1), u2 = __ldg(r0 + 2);
+        const uint32_t v0 = __ldg(r1), v1 = __ldg(r1 + 1), v2 = __ldg(r1 + 2);
+        const uint32_t U0 = __funnelshift_r(u0, u1, sh), U1 = __funnelshift_r(u1, u2, sh);
+        const uint32_t V0 = __funnelshift_r(v0, v1, sh), V1 = __funnelshift_r(v1, v2, sh);
+        const uint32_t uA = __byte_perm(U0, U1, selA), uB = __byte_perm(U0, U1, selB);
+        const uint32_t vA = __byte_perm(V0, V1, selA), vB = __byte_perm(V0, V1, selB);
+        const int h0[4] = {dp2a_lo_su(wg0, uA) >> 4, dp2a_hi_su(wg1, uA) >> 4, dp2a_lo_su(wg2, uB) >> 4, dp2a_hi_su(wg3, uB) >> 4};
+        const int h1[4] = {dp2a_lo_su(wg0, vA) >> 4, dp2a_hi_su(wg1, vA) >> 4, dp2a_lo_su(wg2, vB) >> 4, dp2a_hi_su(wg3, vB) >> 4};
+        uint32_t outv = 0;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const int v = (((b0 * h0[k]) >> 16) + ((b1 * h1[k]) >> 16) + 2) >> 2;
+            outv |= (uint32_t)v << (8 * k);
         }
         if (Y < D.rows) *reinterpret_cast<uint32_t*>(dst + (size_t)Y * D.pitch) = outv;
     }
@@ -1041,6 +1107,9 @@ struct GforbExtractor {
     int retainSeq = 0;                  // GFORB_RETAIN=seq: retainBest's nth_element on one lane (the first-generation path)
     int describeSmem = 0;               // GFORB_DESCRIBE=smem: k_describe2 (tap window staged in shared memory; A/B loser)
     int kpV1 = 0;                       // GFORB_KP=v1: first-generation k_orient / k_describe (warp per list slot, byte gathers from L1)
+    int resizeWords = 2;                // k_resize2 (aligned word loads + dp2a) with 8-row bands (default; GFORB_RESIZE=words: 4-row bands, =direct: the byte-gather k_resize);
+                                        // needs every quad's tap span <= 6 (resizeWordsOk, true up to scaleFactor 2), else k_resize runs
+    bool resizeWordsOk = true;
     int resizeTma = 0;                  // GFORB_RESIZE=tma / direct: source rows staged by cp.async.bulk (k_resize_tma) or gathered from L1 (k_resize)
     // device buffers
     uint8_t *d_img = nullptr, *d_pyr = nullptr, *d_blr = nullptr, *d_desc = nullptr;
@@ -1121,6 +1190,7 @@ static int build_plan(GforbExtractor* E, int w, int h) {
     const bool qt = E->distribution == 1;
     E->qlevels.assign(nl, QtLevel());
     int qtKeyBase = 0, qtNodeBase = 0;
+    bool wordsOk = true;    // k_resize2 precondition (tap span of every column quad)
     bool tiled = true;      // cell interiors tile [16, w-16) x [16, h-16) (k_fast_nms precondition)
     const float imageRatio = (float)w / h;
     for (int l = 0; l < nl; l++) {
@@ -1178,7 +1248,30 @@ static int build_plan(GforbExtractor* E, int w, int h) {
         if (l > 0) {
             L.xtab = (int)tabs.size(); linear_table(E->levels[l - 1].w, L.w, tabs);
             L.ytab = (int)tabs.size(); linear_table(E->levels[l - 1].h, L.h, tabs);
-        } else { L.xtab = L.ytab = 0; }
+            const auto refl = [](int p, int len) { if (len == 1) return 0; while (p < 0 || p >= len) p = p < 0 ? -p : 2 * (len - 1) - p; return p; };
+            if (tabs.size() & 1) tabs.push_back(make_int2(0, 0));        // qtab is read with 128-bit loads
+            L.qtab = (int)tabs.size();
+            for (int q = 0; q < (L.w + 2 * EDGE + 3) / 4; q++) {
+                int2 tx[4];
+                int lo = INT_MAX, hi = 0;
+                for (int k = 0; k < 4; k++) {
+                    tx[k] = tabs[L.xtab + refl(std::min(4 * q + k, L.w + 2 * EDGE - 1) - EDGE, L.w)];   // columns past w+32 are pitch padding
+                    lo = std::min(lo, tx[k].x); hi = std::max(hi, tx[k].x);
+                }
+                if (hi - lo > 6) wordsOk = false;                        // the taps of a quad must fit the 8-byte window
+                unsigned sel[2];
+                for (int pr = 0; pr < 2; pr++) {
+                    const int da = (tx[2 * pr].x - lo) & 7, db = (tx[2 * pr + 1].x - lo) & 7;
+                    sel[pr] = (unsigned)da | (unsigned)((da + 1) & 7) << 4 | (unsigned)db << 8 | (unsigned)((db + 1) & 7) << 12;
+                }
+                tabs.push_back(make_int2(lo, (int)(sel[0] | sel[1] << 16)));
+                tabs.push_back(make_int2(tx[0].y, tx[1].y));
+                tabs.push_back(make_int2(tx[2].y, tx[3].y));
+                tabs.push_back(make_int2(0, 0));
+            }
+            L.ybtab = (int)tabs.size();
+            for (int Y = 0; Y < L.rows; Y++) { const int2 e = tabs[L.ytab + refl(Y - EDGE, L.h)]; tabs.push_back(e); }
+        } else { L.xtab = L.ytab = L.qtab = L.ybtab = 0; }
         for (int i = 0; i < L.levelRows; i++) {
             const int iniY = minB + i * L.cellH - 3;
             float hY = (float)(L.cellH + 6);
@@ -1239,6 +1332,7 @@ static int build_plan(GforbExtractor* E, int w, int h) {
     E->kpCapTotal = kpBase;
     E->nCellsTotal = (int)E->cells.size();
     E->fnTasks[0] = fnTasks[0]; E->fnTasks[1] = fnTasks[1];
+    E->resizeWordsOk = wordsOk;
     E->blTasks[0] = blTasks[0]; E->blTasks[1] = blTasks[1];
     E->tiled = tiled;
     E->detPixPitch = (maxCellW + 16 + 3) & ~3;
@@ -1321,7 +1415,7 @@ int gforb_extractor_create(const GforbExtractorConfig* cfg, GforbExtractor** out
     cudaDeviceGetAttribute(&E->numSMs, cudaDevAttrMultiProcessorCount, cfg->device);
     build_ctor_tables(E);
     if (const char* dv = getenv("GFORB_DETECT")) E->detectVersion = atoi(dv);
-    if (const char* rv = getenv("GFORB_RESIZE")) E->resizeTma = !strcmp(rv, "tma") ? 1 : 0;
+    if (const char* rv = getenv("GFORB_RESIZE")) { E->resizeTma = !strcmp(rv, "tma") ? 1 : 0; E->resizeWords = !strcmp(rv, "words") ? 1 : (!strcmp(rv, "direct") || E->resizeTma) ? 0 : 2; }
     if (const char* kv = getenv("GFORB_KP")) E->kpV1 = !strcmp(kv, "v1") ? 1 : 0;
     if (const char* dv2 = getenv("GFORB_DESCRIBE")) E->describeSmem = !strcmp(dv2, "smem") ? 1 : 0;
     if (const char* tv = getenv("GFORB_FN_TALL")) E->fnTall = atoi(tv) ? 1 : 0;
@@ -1490,6 +1584,12 @@ int gforb_extract(GforbExtractor* E, const uint8_t* images, int w, int h, int st
         if (E->resizeTma && (size_t)RT_MAXSRC * E->levels[l - 1].pitch <= 48 * 1024)
             k_resize_tma<<<dim3((D.rows + RT_ROWS - 1) / RT_ROWS, batch), 256, (size_t)RT_MAXSRC * E->levels[l - 1].pitch, st>>>(
                 spyr, E->d_pyr, E->framePyr, E->levels[l - 1], D, E->d_tabs, quads);
+        else if (E->resizeWords == 1 && E->resizeWordsOk)
+            k_resize2<4><<<dim3((quads * nBands + 255) / 256, batch), 256, 0, st>>>(spyr, E->d_pyr, E->framePyr, E->levels[l - 1], D, E->d_tabs, quads, nBands);
+        else if (E->resizeWords == 2 && E->resizeWordsOk) {
+            const int nB8 = (D.rows + 7) / 8;
+            k_resize2<8><<<dim3((quads * nB8 + 255) / 256, batch), 256, 0, st>>>(spyr, E->d_pyr, E->framePyr, E->levels[l - 1], D, E->d_tabs, quads, nB8);
+        }
         else
             k_resize<<<dim3((quads * nBands + 255) / 256, batch), 256, 0, st>>>(spyr, E->d_pyr, E->framePyr, E->levels[l - 1], D, E->d_tabs, quads, nBands);
         launches++;

@@ -19,6 +19,16 @@ def _cmp_frame(orc, ex_cpu, img, b, kps, desc, counts):
     assert np.array_equal(gd, d)
 
 
+def _same_outputs(a, b):
+    """(keypoints, descriptors, counts) of two runs agree byte for byte on the rows that were written (rows beyond counts[b]
+    are never written by gforb_extract and hold whatever the allocation held)"""
+    assert np.array_equal(a[2], b[2])
+    for f in range(len(a[2])):
+        n = int(a[2][f])
+        assert a[0][f, :n].tobytes() == b[0][f, :n].tobytes(), f
+        assert np.array_equal(a[1][f, :n], b[1][f, :n]), f
+
+
 @pytest.mark.parametrize("w,h,nf", [(640, 480, 1000), (752, 480, 1000), (1241, 376, 2000), (200, 152, 300)])
 def test_extract_matches_oracle(orc, w, h, nf):
     from gf_orb_slam_b200 import ORBextractor
@@ -97,21 +107,25 @@ def test_variants(orc, blur_variant, retain_variant):
     _cmp_frame(orc, ex_cpu, img, 0, kps, desc, counts)
 
 
-def test_resize_variants_agree(monkeypatch):
+@pytest.mark.parametrize("size,nf", [((1241, 376), 2000), ((752, 480), 1000), ((200, 152), 500)])
+def test_resize_variants_agree(monkeypatch, size, nf):
     """the pyramid resize with source rows staged by cp.async.bulk (GFORB_RESIZE=tma, the A/B partner recorded in
-    profiles/r2_ncu_summary.txt) writes the same pyramid bytes and the same keypoints / descriptors as the default kernel"""
+    profiles/r2_ncu_summary.txt) and with aligned word loads + dp2a (GFORB_RESIZE=words / words8: k_resize2 with 4- / 8-row bands) write the same pyramid
+    bytes -- ring and pitch padding columns included -- and the same keypoints / descriptors as the byte-gather kernel"""
     from gf_orb_slam_b200 import ORBextractor
-    imgs = np.stack([synth.textured_frame(1241, 376, seed=40 + i) for i in range(2)])
+    w, h = size
+    imgs = np.stack([synth.textured_frame(w, h, seed=40 + i) for i in range(2)])
     res = []
-    for v in ("direct", "tma"):
+    for v in ("direct", "tma", "words", "words8"):
         monkeypatch.setenv("GFORB_RESIZE", v)
-        ex = ORBextractor(2000, 1.2, 8, max_width=1241, max_height=376, max_batch=2)
+        ex = ORBextractor(nf, 1.2, 8, max_width=w, max_height=h, max_batch=2)
         kps, desc, counts = ex.extract_batch(imgs)
         res.append((kps.copy(), desc.copy(), counts.copy(), [ex.debug_level(1, l, 0).copy() for l in range(8)]))
-    a, b = res
-    assert np.array_equal(a[2], b[2]) and a[0].tobytes() == b[0].tobytes() and np.array_equal(a[1], b[1])
-    for l in range(8):
-        assert np.array_equal(a[3][l], b[3][l]), l
+    a = res[0]
+    for b in res[1:]:
+        _same_outputs(a, b)
+        for l in range(8):
+            assert np.array_equal(a[3][l], b[3][l]), l
 
 
 @pytest.mark.parametrize("size,nf", [((752, 480), 1000), ((1241, 376), 2000), ((200, 152), 1500)])
@@ -136,7 +150,7 @@ def test_kernel_generations_agree(monkeypatch, knob, size, nf):
         kps, desc, counts = ex.extract_batch(imgs)
         res.append((kps.copy(), desc.copy(), counts.copy(), [ex.debug_level(2, l, 1)[16:-16, 16:-16].copy() for l in range(8)]))
     a, b = res
-    assert np.array_equal(a[2], b[2]) and a[0].tobytes() == b[0].tobytes() and np.array_equal(a[1], b[1])
+    _same_outputs(a, b)
     for l in range(8):
         assert np.array_equal(a[3][l], b[3][l]), l
     assert a[2].min() > 50
@@ -157,7 +171,7 @@ def test_retain_variants_agree(monkeypatch, size, nf, variant):
         kps, desc, counts = ex.extract_batch(imgs)
         res.append((kps.copy(), desc.copy(), counts.copy()))
     a, b = res
-    assert np.array_equal(a[2], b[2]) and a[0].tobytes() == b[0].tobytes() and np.array_equal(a[1], b[1])
+    _same_outputs(a, b)
     assert a[2].min() > nf // 2
 
 
