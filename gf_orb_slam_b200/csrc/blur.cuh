@@ -127,6 +127,9 @@ __device__ __forceinline__ uint32_t dp2a_lo_u32(uint32_t a, uint32_t b, uint32_t
     return d;
 }
 
+// QD = rows in flight ahead of the one being filtered (1, 2, 3 or 6: must divide the 6-phase unroll so that every queue slot is a
+// fixed register that is consumed directly, never copied while its load is in flight)
+template <int QD>
 __global__ void __launch_bounds__(BL2_WARPS * 32) k_blur3(const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blr,
                                                           size_t framePyr, const LevelPlan* __restrict__ levels, int nLevels,
                                                           int tasksPerFrame, int variant, int bv) {
@@ -149,18 +152,23 @@ __global__ void __launch_bounds__(BL2_WARPS * 32) k_blur3(const uint8_t* __restr
     const unsigned full = 0xffffffffu;
     const int hoff = lane < 16 ? -4 : 4;
     const uint8_t* lp = roi + (ptrdiff_t)(Y0 - 3) * L.pitch + xl;
-    uint32_t nw1 = __ldg(reinterpret_cast<const uint32_t*>(lp));
-    uint32_t nh = __ldg(reinterpret_cast<const uint32_t*>(lp + hoff));
+    uint32_t qw[QD], qh[QD];
+#pragma unroll
+    for (int i = 0; i < QD; i++) {
+        qw[i] = __ldg(reinterpret_cast<const uint32_t*>(lp + (ptrdiff_t)i * L.pitch));
+        qh[i] = __ldg(reinterpret_cast<const uint32_t*>(lp + (ptrdiff_t)i * L.pitch + hoff));
+    }
+    lp += (ptrdiff_t)(QD - 1) * L.pitch;
     uint32_t Q[6][4];            // row pairs {h(r-1), h(r)} of pixels x .. x+3 for the last 6 rows r, slot = phase
     uint32_t pA = 0, pB = 0;     // horizontal results of the previous row
     const int Rend = Y1 + 2;
 
     auto phase = [&](auto PHc, int R) {
         constexpr int PH = decltype(PHc)::value;
-        const uint32_t w1 = nw1, hw = nh;
+        const uint32_t w1 = qw[PH % QD], hw = qh[PH % QD];
         lp += L.pitch;
-        nw1 = __ldg(reinterpret_cast<const uint32_t*>(lp));      // row Rend + 1 <= h + 3 is inside the bordered plane
-        nh = __ldg(reinterpret_cast<const uint32_t*>(lp + hoff));
+        qw[PH % QD] = __ldg(reinterpret_cast<const uint32_t*>(lp));      // rows up to Rend + QD <= h + 2 + 6 are inside the bordered plane (16 ring rows)
+        qh[PH % QD] = __ldg(reinterpret_cast<const uint32_t*>(lp + hoff));
         uint32_t w0 = __shfl_up_sync(full, w1, 1), w2 = __shfl_down_sync(full, w1, 1);
         if (lane == 0) w0 = hw;
         if (lane == 31) w2 = hw;

@@ -235,15 +235,23 @@ __global__ void __launch_bounds__(EM_WARPS * 32) k_cell_emit(const uint8_t* __re
     const int nChunk = (C.x1 - xa + 15) >> 4;
     const int items = nChunk * Hc;
     int total = 0, n20 = 0;
-    for (int it0 = 0; it0 < items; it0 += 32) {
-        const int id = it0 + lane;
-        uint4 v = make_uint4(0, 0, 0, 0);
-        int y = 0, xc = 0;
+    // the chunk of the NEXT iteration is requested before this one is scanned (the loop was stalled on its own load:
+    // ncu long-scoreboard 5.2 per issue)
+    uint4 vn = make_uint4(0, 0, 0, 0);
+    int yn = 0, xn = 0;
+    auto fetch = [&](int id) {
+        vn = make_uint4(0, 0, 0, 0);
         if (id < items) {
             const int r = id / nChunk, ch = id - r * nChunk;
-            y = C.y0 + r; xc = xa + (ch << 4);
-            v = __ldg(reinterpret_cast<const uint4*>(roi + (ptrdiff_t)y * L.pitch + xc));
+            yn = C.y0 + r; xn = xa + (ch << 4);
+            vn = __ldg(reinterpret_cast<const uint4*>(roi + (ptrdiff_t)yn * L.pitch + xn));
         }
+    };
+    fetch(lane);
+    for (int it0 = 0; it0 < items; it0 += 32) {
+        const uint4 v = vn;
+        const int y = yn, xc = xn;
+        fetch(it0 + 32 + lane);
         uint32_t w[4] = {v.x, v.y, v.z, v.w};
         uint32_t nzmask = 0;                                    // bit k: byte k is a survivor inside [x0, x1)
         if (v.x | v.y | v.z | v.w) {

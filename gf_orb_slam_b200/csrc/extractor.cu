@@ -1091,6 +1091,7 @@ struct GforbExtractor {
     std::vector<CellPlan> cells;
     size_t framePyr = 0, frameCand = 0, frameKp = 0;
     int kpCapTotal = 0, nCellsTotal = 0, detSmem = 0, detPixPitch = 0, fnTasks[2] = {0, 0}, blTasks[2] = {0, 0};
+    int blurQD = 2;                     // GFORB_BLUR_QD: input rows in flight ahead of the filtered one in k_blur3 (1, 2, 3; B200: 0.346 / 0.309 / 0.302 ms per 250 frames, pipelined 83.6k / 84.7k / 84.3k frames/s)
     int blurV2 = 0;                     // GFORB_BLUR=v2: second-generation blur (vertical pass on unpacked 32-bit lane-ops) instead of k_blur3 (IDP.2A row pairs)
     int fnTall = -1;                    // GFORB_FN_TALL=0/1 pins the strip height of k_fast_nms; -1: tall strips once the batch fills the GPU several times
     bool tiled = true;
@@ -1419,6 +1420,7 @@ int gforb_extractor_create(const GforbExtractorConfig* cfg, GforbExtractor** out
     if (const char* kv = getenv("GFORB_KP")) E->kpV1 = !strcmp(kv, "v1") ? 1 : 0;
     if (const char* dv2 = getenv("GFORB_DESCRIBE")) E->describeSmem = !strcmp(dv2, "smem") ? 1 : 0;
     if (const char* tv = getenv("GFORB_FN_TALL")) E->fnTall = atoi(tv) ? 1 : 0;
+    if (const char* qd = getenv("GFORB_BLUR_QD")) E->blurQD = atoi(qd);
     if (const char* bv2 = getenv("GFORB_BLUR")) E->blurV2 = !strcmp(bv2, "v2") ? 1 : 0;
 
     GF_CUDA_OK(cudaMemcpyToSymbol(g_pattern, h_pattern, sizeof(h_pattern)));
@@ -1626,8 +1628,13 @@ int gforb_extract(GforbExtractor* E, const uint8_t* images, int w, int h, int st
         k_blur2<<<dim3((E->blTasks[bv] + BL2_WARPS - 1) / BL2_WARPS, batch), BL2_WARPS * 32, 0, fork ? E->ownStream : st>>>(
             E->d_pyr, E->d_blr, E->framePyr, E->d_levels, nl, E->blTasks[bv], c.blur_variant, bv);
     else
-        k_blur3<<<dim3((E->blTasks[bv] + BL2_WARPS - 1) / BL2_WARPS, batch), BL2_WARPS * 32, 0, fork ? E->ownStream : st>>>(
-            E->d_pyr, E->d_blr, E->framePyr, E->d_levels, nl, E->blTasks[bv], c.blur_variant, bv);
+    {
+        const dim3 bg((E->blTasks[bv] + BL2_WARPS - 1) / BL2_WARPS, batch);
+        cudaStream_t bs = fork ? E->ownStream : st;
+        if (E->blurQD == 2) k_blur3<2><<<bg, BL2_WARPS * 32, 0, bs>>>(E->d_pyr, E->d_blr, E->framePyr, E->d_levels, nl, E->blTasks[bv], c.blur_variant, bv);
+        else if (E->blurQD == 3) k_blur3<3><<<bg, BL2_WARPS * 32, 0, bs>>>(E->d_pyr, E->d_blr, E->framePyr, E->d_levels, nl, E->blTasks[bv], c.blur_variant, bv);
+        else k_blur3<1><<<bg, BL2_WARPS * 32, 0, bs>>>(E->d_pyr, E->d_blr, E->framePyr, E->d_levels, nl, E->blTasks[bv], c.blur_variant, bv);
+    }
     launches++;
     end();
     stageStream = st;
