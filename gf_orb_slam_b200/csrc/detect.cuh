@@ -216,7 +216,7 @@ __global__ void __launch_bounds__(EM_WARPS * 32) k_cell_emit(const uint8_t* __re
                                                              const CellPlan* __restrict__ cells, int nCellsTotal,
                                                              uint32_t* __restrict__ cand, size_t frameCand,
                                                              int* __restrict__ cnt7, int* __restrict__ cnt20, int iniTh,
-                                                             int* __restrict__ errflag) {
+                                                             int* __restrict__ errflag, const __grid_constant__ KpLevels KL, int useKL) {
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int cellId = blockIdx.x * EM_WARPS + warp, b = blockIdx.y;
@@ -228,7 +228,9 @@ __global__ void __launch_bounds__(EM_WARPS * 32) k_cell_emit(const uint8_t* __re
         if (lane == 0) { cnt7[ci] = 0; cnt20[ci] = 0; }
         return;
     }
-    const LevelPlan L = levels[C.level];
+    KpLevel L;                                                  // only off and pitch are used
+    if (useKL) L = KL.lv[C.level];
+    else { L.off = levels[C.level].off; L.pitch = levels[C.level].pitch; }
     const uint8_t* roi = smap + (size_t)b * framePyr + L.off + (size_t)EDGE * L.pitch + EDGE;
     uint32_t* out = cand + (size_t)b * frameCand + C.candBase;
     const int xa = C.x0 & ~15;                                  // plane column 16 + xa is 16-byte aligned

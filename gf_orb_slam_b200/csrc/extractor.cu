@@ -38,6 +38,11 @@ struct LevelPlan {
     int fnStripsX, fnRows[2], fnTaskBase[2];   // k_fast_nms strips (detect.cuh): [0] rows <= 64 per strip (small batches), [1] <= 128
     int blStripsX, blRows[2], blTaskBase[2];   // k_blur2 strips (blur.cuh), same two strip heights
 };
+// per-level constants that travel as a kernel parameter (constant bank, indexed by a warp-uniform level) instead of a
+// dependent global load of the LevelPlan: the row-mapped keypoint kernels and k_cell_emit (<= KP_MAX_LEVELS levels)
+static const int KP_MAX_LEVELS = 16;
+struct KpLevel { unsigned long long off; int pitch, kpBase, w, h, scaledPatchSize; float scale; };
+struct KpLevels { KpLevel lv[KP_MAX_LEVELS]; };
 struct CellPlan {
     int level, x0, y0, x1, y1;    // interior rectangle in level ROI coordinates [x0,x1) x [y0,y1) (may be empty)
     int skipped;                  // 1: the reference `continue`s before FAST (hX<=0 / hY<=0)
@@ -862,26 +867,45 @@ __global__ void __launch_bounds__(256) k_orient(const uint8_t* __restrict__ pyr,
 // blurs the ROI in place and leaves the ring untouched).
 // ROWMAP (default): warp per output row j < nfeatures (kp_row_to_slot); otherwise warp per slot of the per-level lists
 // (kpCapTotal slots, ~3.5 x nfeatures, most of which exit right after the level search: GFORB_KP=v1).
-__device__ __forceinline__ bool kp_row_to_slot(int j, int b, int nLevels, const int* __restrict__ lvlCount, int& l, int& i);
-template <bool ROWMAP>
+// The per-level constants the row-mapped keypoint kernels need travel as a kernel parameter (constant bank, indexed by the
+// warp-uniform level) and the output row -> (level, list index) map is ONE load round: lane l reads the count of level l, a
+// shuffle scan gives the prefix, a ballot the level.  (The first row-mapped build walked the counts with an early exit --
+// up to nLevels dependent loads -- and then fetched the LevelPlan from global memory: k_orient2 ran at 19.6 long-scoreboard
+// stalls per issued instruction.)
+__device__ __forceinline__ bool kp_row_to_slot(int j, int b, int nLevels, const int* __restrict__ lvlCount, int lane, int& l, int& i, int& total) {
+    const unsigned full = 0xffffffffu;
+    const int c = lane < nLevels ? lvlCount[b * nLevels + lane] : 0;
+    int inc = c;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const int t = __shfl_up_sync(full, inc, d); if (lane >= d) inc += t; }
+    total = __shfl_sync(full, inc, 31);
+    const unsigned m = __ballot_sync(full, lane < nLevels && j < inc);
+    if (!m) return false;
+    l = __ffs(m) - 1;
+    i = j - (__shfl_sync(full, inc, l) - __shfl_sync(full, c, l));
+    return true;
+}
+template <bool ROWMAP, bool MAGIC>
 __global__ void __launch_bounds__(256) k_describe(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ blr,
                                                   size_t framePyr, const LevelPlan* __restrict__ levels, int nLevels,
                                                   const uint32_t* __restrict__ lvlKp, size_t frameKp, int kpCapTotal,
                                                   const int* __restrict__ lvlCount,
                                                   const GforbKeyPoint* __restrict__ kps, uint8_t* __restrict__ desc,
-                                                  int nfeatures) {
+                                                  int nfeatures, const __grid_constant__ KpLevels KL) {
     const int slot0 = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), b = blockIdx.y, lane = threadIdx.x & 31;
     int l = 0, base = 0, i, slot = slot0;
+    KpLevel L;
     if (ROWMAP) {
-        if (slot0 >= nfeatures || !kp_row_to_slot(slot0, b, nLevels, lvlCount, l, i)) return;
+        int total;
+        if (slot0 >= nfeatures || !kp_row_to_slot(slot0, b, nLevels, lvlCount, lane, l, i, total)) return;
         base = slot0 - i;
+        L = KL.lv[l];
+        slot = L.kpBase + i;
     } else {
         if (slot >= kpCapTotal) return;
         while (l + 1 < nLevels && slot >= levels[l + 1].kpBase) { base += lvlCount[b * nLevels + l]; l++; }
-    }
-    const LevelPlan L = levels[l];
-    if (ROWMAP) slot = L.kpBase + i;
-    else {
+        const LevelPlan G = levels[l];
+        L.off = G.off; L.pitch = G.pitch; L.kpBase = G.kpBase; L.w = G.w; L.h = G.h;
         i = slot - L.kpBase;
         if (i >= lvlCount[b * nLevels + l]) return;
     }
@@ -902,8 +926,11 @@ __global__ void __launch_bounds__(256) k_describe(const uint8_t* __restrict__ py
 #pragma unroll
         for (int q = 0; q < 2; q++) {
             const float px = (float)(signed char)(pw[t] >> (16 * q)), py = (float)(signed char)(pw[t] >> (16 * q + 8));
-            int iy = cv_round(__fadd_rn(__fmul_rn(px, bb), __fmul_rn(py, a)));
-            int ix = cv_round(__fsub_rn(__fmul_rn(px, a), __fmul_rn(py, bb)));
+            const float fy = __fadd_rn(__fmul_rn(px, bb), __fmul_rn(py, a)), fx = __fsub_rn(__fmul_rn(px, a), __fmul_rn(py, bb));
+            // MAGIC: cvRound by adding 1.5 * 2^23 (the float add rounds to nearest-even and leaves the integer in the mantissa,
+            // bit image 0x4B400000 + n; identical to __float2int_rn for |v| < 2^22) -- keeps 32 conversions per lane off the XU pipe
+            const int iy = MAGIC ? __float_as_int(__fadd_rn(fy, 12582912.f)) - 0x4B400000 : cv_round(fy);
+            const int ix = MAGIC ? __float_as_int(__fadd_rn(fx, 12582912.f)) - 0x4B400000 : cv_round(fx);
             int x = cx + ix, y = cy + iy;
             const uint8_t* src = (x >= 0 && x < L.w && y >= 0 && y < L.h) ? B : P;
             tv[q] = src[(ptrdiff_t)y * L.pitch + x];
@@ -918,15 +945,6 @@ __global__ void __launch_bounds__(256) k_describe(const uint8_t* __restrict__ py
 // follow from the per-level counts) instead of one warp per slot of the over-provisioned per-level lists (kpCapTotal ~ 3.5 x
 // nfeatures at the reference's defaults).  k_orient2 is the default (GFORB_KP=v1: k_orient + slot-mapped k_describe);
 // k_describe2 is an A/B LOSER kept selectable (GFORB_DESCRIBE=smem) -- see its comment.
-__device__ __forceinline__ bool kp_row_to_slot(int j, int b, int nLevels, const int* __restrict__ lvlCount, int& l, int& i) {
-    int base = 0;
-    for (l = 0; l < nLevels; l++) {
-        const int n = lvlCount[b * nLevels + l];
-        if (j < base + n) { i = j - base; return true; }
-        base += n;
-    }
-    return false;
-}
 
 // IC_Angle as in k_orient; the task weights come from g_orientW (coalesced 8-byte loads into registers) instead of a
 // table that every CTA rebuilt in shared memory through divergent __constant__ reads.
@@ -935,17 +953,14 @@ __global__ void __launch_bounds__(256) k_orient2(const uint8_t* __restrict__ pyr
                                                  const uint32_t* __restrict__ lvlKp, size_t frameKp,
                                                  const int* __restrict__ lvlCount, GforbKeyPoint* __restrict__ kps,
                                                  int32_t* __restrict__ counts, int nfeatures,
-                                                 const float* __restrict__ lvlResp) {
+                                                 const float* __restrict__ lvlResp, const __grid_constant__ KpLevels KL) {
     const int j = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), b = blockIdx.y, lane = threadIdx.x & 31;
     if (j >= nfeatures) return;
-    if (j == 0 && lane == 0) {
-        int tot = 0;
-        for (int q = 0; q < nLevels; q++) tot += lvlCount[b * nLevels + q];
-        counts[b] = tot;
-    }
-    int l, i;
-    if (!kp_row_to_slot(j, b, nLevels, lvlCount, l, i)) return;
-    const LevelPlan L = levels[l];
+    int l, i, total;
+    const bool live = kp_row_to_slot(j, b, nLevels, lvlCount, lane, l, i, total);
+    if (j == 0 && lane == 0) counts[b] = total;
+    if (!live) return;
+    const KpLevel L = KL.lv[l];
     const int slot = L.kpBase + i;
     const uint32_t e = lvlKp[(size_t)b * frameKp + slot];
     const int x = e & 0xfff, y = (e >> 12) & 0xfff, score = e >> 24;
@@ -1001,8 +1016,8 @@ __global__ void __launch_bounds__(256) k_describe2(const uint8_t* __restrict__ p
     __shared__ __align__(16) uint8_t s_patch[8][DS_ROWS * DS_PITCH];
     const int j = blockIdx.x * 8 + (threadIdx.x >> 5), b = blockIdx.y, lane = threadIdx.x & 31;
     if (j >= nfeatures) return;
-    int l, i;
-    if (!kp_row_to_slot(j, b, nLevels, lvlCount, l, i)) return;
+    int l, i, total;
+    if (!kp_row_to_slot(j, b, nLevels, lvlCount, lane, l, i, total)) return;
     const LevelPlan L = levels[l];
     const uint32_t e = lvlKp[(size_t)b * frameKp + L.kpBase + i];
     const int cx = e & 0xfff, cy = (e >> 12) & 0xfff;
@@ -1106,6 +1121,7 @@ struct GforbExtractor {
     int2* d_qtVsz = nullptr;
     size_t frameQtKeys = 0, frameQtNodes = 0, capQtKeys = 0, capQtTmp = 0, capQtNodes = 0, capQtVsz = 0;
     int retainSeq = 0;                  // GFORB_RETAIN=seq: retainBest's nth_element on one lane (the first-generation path)
+    KpLevels kpLevels;                  // per-level constants of the row-mapped keypoint kernels (kernel parameter), filled by build_plan
     int describeSmem = 0;               // GFORB_DESCRIBE=smem: k_describe2 (tap window staged in shared memory; A/B loser)
     int kpV1 = 0;                       // GFORB_KP=v1: first-generation k_orient / k_describe (warp per list slot, byte gathers from L1)
     int resizeWords = 2;                // k_resize2 (aligned word loads + dp2a) with 8-row bands (default; GFORB_RESIZE=words: 4-row bands, =direct: the byte-gather k_resize);
@@ -1334,6 +1350,12 @@ static int build_plan(GforbExtractor* E, int w, int h) {
     E->nCellsTotal = (int)E->cells.size();
     E->fnTasks[0] = fnTasks[0]; E->fnTasks[1] = fnTasks[1];
     E->resizeWordsOk = wordsOk;
+    memset(&E->kpLevels, 0, sizeof(E->kpLevels));
+    for (int l = 0; l < (int)E->levels.size() && l < KP_MAX_LEVELS; l++) {
+        const LevelPlan& P = E->levels[l];
+        KpLevel& K = E->kpLevels.lv[l];
+        K.off = P.off; K.pitch = P.pitch; K.kpBase = P.kpBase; K.w = P.w; K.h = P.h; K.scaledPatchSize = P.scaledPatchSize; K.scale = P.scale;
+    }
     E->blTasks[0] = blTasks[0]; E->blTasks[1] = blTasks[1];
     E->tiled = tiled;
     E->detPixPitch = (maxCellW + 16 + 3) & ~3;
@@ -1418,7 +1440,8 @@ int gforb_extractor_create(const GforbExtractorConfig* cfg, GforbExtractor** out
     if (const char* dv = getenv("GFORB_DETECT")) E->detectVersion = atoi(dv);
     if (const char* rv = getenv("GFORB_RESIZE")) { E->resizeTma = !strcmp(rv, "tma") ? 1 : 0; E->resizeWords = !strcmp(rv, "words") ? 1 : (!strcmp(rv, "direct") || E->resizeTma) ? 0 : 2; }
     if (const char* kv = getenv("GFORB_KP")) E->kpV1 = !strcmp(kv, "v1") ? 1 : 0;
-    if (const char* dv2 = getenv("GFORB_DESCRIBE")) E->describeSmem = !strcmp(dv2, "smem") ? 1 : 0;
+    if (cfg->nlevels > KP_MAX_LEVELS) E->kpV1 = 1;          // the row-mapped kernels carry the level constants of <= 16 levels as a parameter
+    if (const char* dv2 = getenv("GFORB_DESCRIBE")) E->describeSmem = !strcmp(dv2, "smem") ? 1 : !strcmp(dv2, "magic") ? 2 : 0;
     if (const char* tv = getenv("GFORB_FN_TALL")) E->fnTall = atoi(tv) ? 1 : 0;
     if (const char* qd = getenv("GFORB_BLUR_QD")) E->blurQD = atoi(qd);
     if (const char* bv2 = getenv("GFORB_BLUR")) E->blurV2 = !strcmp(bv2, "v2") ? 1 : 0;
@@ -1606,7 +1629,7 @@ int gforb_extract(GforbExtractor* E, const uint8_t* images, int w, int h, int st
             E->d_pyr, E->d_blr, E->framePyr, E->d_levels, nl, E->fnTasks[fv], c.minThFAST, fv); launches++;
         k_cell_emit<<<dim3((E->nCellsTotal + EM_WARPS - 1) / EM_WARPS, batch), EM_WARPS * 32, 0, st>>>(
             E->d_blr, E->framePyr, E->d_levels, E->d_cells, E->nCellsTotal, E->d_cand, E->frameCand, E->d_cnt7, E->d_cnt20,
-            c.iniThFAST, E->d_err); launches++;
+            c.iniThFAST, E->d_err, E->kpLevels, nl <= KP_MAX_LEVELS ? 1 : 0); launches++;
     } else {
         k_detect<<<dim3(E->nCellsTotal, batch), DET_THREADS, E->detSmem, st>>>(
             E->d_pyr, E->framePyr, E->d_levels, E->d_cells, E->nCellsTotal, E->d_cand, E->frameCand, E->d_cnt7, E->d_cnt20,
@@ -1678,17 +1701,20 @@ int gforb_extract(GforbExtractor* E, const uint8_t* images, int w, int h, int st
     else
         k_orient2<<<dim3((c.nfeatures + 7) / 8, batch), 256, 0, st>>>(E->d_pyr, E->framePyr, E->d_levels, nl, E->d_lvlKp,
                                                                        E->frameKp, E->d_lvlCount, dk, dc, c.nfeatures,
-                                                                       harris ? E->d_lvlResp : nullptr);
+                                                                       harris ? E->d_lvlResp : nullptr, E->kpLevels);
     launches++;
     end();
     if (fork) GF_CUDA_OK(cudaStreamWaitEvent(st, E->evJoin, 0));
     begin("describe");
     if (E->kpV1)
-        k_describe<false><<<dim3((E->kpCapTotal + 7) / 8, batch), 256, 0, st>>>(E->d_pyr, E->d_blr, E->framePyr, E->d_levels, nl, E->d_lvlKp,
-                                                                                 E->frameKp, E->kpCapTotal, E->d_lvlCount, dk, dd, c.nfeatures);
-    else if (!E->describeSmem)
-        k_describe<true><<<dim3((c.nfeatures + 7) / 8, batch), 256, 0, st>>>(E->d_pyr, E->d_blr, E->framePyr, E->d_levels, nl, E->d_lvlKp,
-                                                                              E->frameKp, E->kpCapTotal, E->d_lvlCount, dk, dd, c.nfeatures);
+        k_describe<false, false><<<dim3((E->kpCapTotal + 7) / 8, batch), 256, 0, st>>>(E->d_pyr, E->d_blr, E->framePyr, E->d_levels, nl, E->d_lvlKp,
+                                                                                 E->frameKp, E->kpCapTotal, E->d_lvlCount, dk, dd, c.nfeatures, E->kpLevels);
+    else if (E->describeSmem == 0)
+        k_describe<true, false><<<dim3((c.nfeatures + 7) / 8, batch), 256, 0, st>>>(E->d_pyr, E->d_blr, E->framePyr, E->d_levels, nl, E->d_lvlKp,
+                                                                              E->frameKp, E->kpCapTotal, E->d_lvlCount, dk, dd, c.nfeatures, E->kpLevels);
+    else if (E->describeSmem == 2)
+        k_describe<true, true><<<dim3((c.nfeatures + 7) / 8, batch), 256, 0, st>>>(E->d_pyr, E->d_blr, E->framePyr, E->d_levels, nl, E->d_lvlKp,
+                                                                              E->frameKp, E->kpCapTotal, E->d_lvlCount, dk, dd, c.nfeatures, E->kpLevels);
     else
         k_describe2<<<dim3((c.nfeatures + 7) / 8, batch), 256, 0, st>>>(E->d_pyr, E->d_blr, E->framePyr, E->d_levels, nl, E->d_lvlKp,
                                                                          E->frameKp, E->d_lvlCount, dk, dd, c.nfeatures);

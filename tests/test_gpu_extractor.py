@@ -129,7 +129,7 @@ def test_resize_variants_agree(monkeypatch, size, nf):
 
 
 @pytest.mark.parametrize("size,nf", [((752, 480), 1000), ((1241, 376), 2000), ((200, 152), 1500)])
-@pytest.mark.parametrize("knob", ["GFORB_KP=v1", "GFORB_DESCRIBE=smem", "GFORB_BLUR=v2", "GFORB_FN_TALL=0", "GFORB_FN_TALL=1"])
+@pytest.mark.parametrize("knob", ["GFORB_KP=v1", "GFORB_DESCRIBE=smem", "GFORB_DESCRIBE=magic", "GFORB_BLUR=v2", "GFORB_BLUR_QD=1", "GFORB_BLUR_QD=3", "GFORB_FN_TALL=0", "GFORB_FN_TALL=1"])
 def test_kernel_generations_agree(monkeypatch, knob, size, nf):
     """A/B partners of the extractor kernels against the default build, byte for byte (keypoints incl. angles, descriptors,
     counts, blurred planes): GFORB_KP=v1 (first-generation k_orient / slot-mapped k_describe instead of k_orient2 and the
@@ -142,7 +142,7 @@ def test_kernel_generations_agree(monkeypatch, knob, size, nf):
     imgs = np.stack([synth.textured_frame(w, h, seed=70 + i) for i in range(3)])
     res = []
     for v in (None, knob):
-        for k in ("GFORB_KP", "GFORB_DESCRIBE", "GFORB_BLUR", "GFORB_FN_TALL"):
+        for k in ("GFORB_KP", "GFORB_DESCRIBE", "GFORB_BLUR", "GFORB_BLUR_QD", "GFORB_FN_TALL"):
             monkeypatch.delenv(k, raising=False)
         if v:
             monkeypatch.setenv(*v.split("="))
