@@ -8,7 +8,7 @@ import csv
 import json
 import sys
 
-STAGE_OF = {"k_border0": "pyramid", "k_resize": "pyramid", "k_ring": "pyramid", "k_fast_nms": "detect", "k_cell_emit": "detect",
+STAGE_OF = {"k_border0": "pyramid", "k_resize": "pyramid", "k_resize2": "pyramid", "k_ring": "pyramid", "k_fast_nms": "detect", "k_cell_emit": "detect",
             "k_detect": "detect", "k_quota": "select", "k_cell_retain": "select", "k_level_retain": "select", "k_orient": "orient", "k_orient2": "orient",
             "k_blur2": "blur", "k_blur3": "blur", "k_describe": "describe", "k_describe2": "describe", "k_grid_build": "match", "k_candidates": "match", "k_resolve": "match",
             "k_build_info": "info", "k_select": "gf_select", "k_select_ahead": "gf_select"}
