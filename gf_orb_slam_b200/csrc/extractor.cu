@@ -40,7 +40,7 @@ struct LevelPlan {
 };
 // per-level constants that travel as a kernel parameter (constant bank, indexed by a warp-uniform level) instead of a
 // dependent global load of the LevelPlan: the row-mapped keypoint kernels and k_cell_emit (<= KP_MAX_LEVELS levels)
-static const int KP_MAX_LEVELS = 16;
+static const int KP_MAX_LEVELS = MAX_LEVELS;   // = the create-time limit on nlevels (common.cuh), so the global-memory fallbacks are never taken today
 struct KpLevel { unsigned long long off; int pitch, kpBase, w, h, scaledPatchSize; float scale; };
 struct KpLevels { KpLevel lv[KP_MAX_LEVELS]; };
 struct CellPlan {
