@@ -172,7 +172,11 @@ int gforb_frontend_create(const GforbFrontEndConfig* cfg, GforbFrontEnd** out) {
     oc.fu = cfg->fu; oc.fv = cfg->fv; oc.nRows = cfg->height; oc.nCols = cfg->width; oc.Cx = cfg->Cx; oc.Cy = cfg->Cy; oc.k1 = cfg->k1; oc.k2 = cfg->k2;
     oc.dx = cfg->dx; oc.dy = cfg->dy; oc.max_batch = cfg->max_batch; oc.max_points = cfg->nfeatures; oc.device = cfg->device;
     if ((rc = gforb_obs_create(&oc, &F->obs))) return fail(rc);
-    if (cfg->overlap) gforb_obs_set_select_residency(F->obs, 3);      // it shares the SMs with the next step's extraction
+    // Register budget of the selection kernel while it shares the SMs with the next step's extraction: 0 = by waves (two CTAs per
+    // SM at 168 registers unless a third saves a wave), 3 = always the 128-register build.  Round 2 ran 3 until the extraction got
+    // faster; alternating A/B on the last build (250-frame batches): 85.3 k -> 87.5 k frames/s device-resident with 0, end to end
+    // equal (85.8 k), the matcher stage 2.7 -> 1.5 ms because its one-warp-per-frame resolver finds free slots sooner.
+    if (cfg->overlap) gforb_obs_set_select_residency(F->obs, env_int("GFORB_SEL_RESIDENCY", 0));
 
     const size_t B = F->B, nf = F->nf, k = F->k, px = (size_t)cfg->width * cfg->height;
     for (int i = 0; i < F->nb && !rc; i++) {
