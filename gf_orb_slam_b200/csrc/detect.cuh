@@ -241,13 +241,17 @@ __global__ void __launch_bounds__(EM_WARPS * 32) k_cell_emit(const uint8_t* __re
     // ncu long-scoreboard 5.2 per issue)
     uint4 vn = make_uint4(0, 0, 0, 0);
     int yn = 0, xn = 0;
+    // (row, chunk) of this lane's item advance by 32 items per iteration without a division
+    int fr = lane / nChunk, fc = lane - fr * nChunk;
+    const int q32 = 32 / nChunk, r32 = 32 - q32 * nChunk;
     auto fetch = [&](int id) {
         vn = make_uint4(0, 0, 0, 0);
         if (id < items) {
-            const int r = id / nChunk, ch = id - r * nChunk;
-            yn = C.y0 + r; xn = xa + (ch << 4);
+            yn = C.y0 + fr; xn = xa + (fc << 4);
             vn = __ldg(reinterpret_cast<const uint4*>(roi + (ptrdiff_t)yn * L.pitch + xn));
         }
+        fr += q32; fc += r32;
+        if (fc >= nChunk) { fc -= nChunk; fr++; }
     };
     fetch(lane);
     for (int it0 = 0; it0 < items; it0 += 32) {
