@@ -711,7 +711,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--seq-frames", type=int, default=2000, help="frames of the sequence one step walks through (config C2: 2000)")
-    ap.add_argument("--batch", type=int, default=250, help="frames per front-end batch (a step is ceil(chunk / batch) batches per GPU)")
+    ap.add_argument("--batch", type=int, default=296, help="most frames per front-end batch (a step is ceil(chunk / batch) equal batches per GPU; 296 = 2 x 148 SMs, one wave of the selection kernel at two CTAs per SM: 7 batches of 286 frames at N = 1)")
     ap.add_argument("--cpu-frames", type=int, default=256, help="frames of the cpu_baseline sample")
     ap.add_argument("--ref-frames", type=int, default=0, help="frames per step of the --impl reference arm (0: 8 per host thread)")
     ap.add_argument("--no-cpu", action="store_true")
